@@ -1,0 +1,261 @@
+/*
+ * nimb200.h -- C ABI of the B200 multi-chain MCMC back end for NIMBLE models.
+ *
+ * Everything that crosses this boundary is a plain pointer, a size or a
+ * scalar: no torch types, no SEXPs, no C++ classes.  The R glue (.Call shim,
+ * see INTEGRATION.md) and the Python host layer (nimble_b200/_capi.py, ctypes)
+ * both bind exactly these symbols.
+ *
+ * Paths below are relative to the reference tree, P/ = packages/nimble/.
+ *
+ * The unit that crosses is the *node table*: a flat description of a lowered
+ * model (what compileNimble turns declInfo / maps / samplerConfs into).  It
+ * replaces, for the sampling path only, the generated C++ classes
+ *   - nodeFun / indexedNodeInfo            P/inst/include/nimble/nodeFun.h:134-249
+ *   - NodeVectorClassNew / NodeInstruction P/inst/include/nimble/accessorClasses.h:50-62
+ *   - copierVectorClass / nimCopy          P/inst/CppCode/accessorClasses.cpp:549-572
+ *   - the generated sampler classes        P/R/MCMC_samplers.R, P/R/MCMC_conjugacy.R
+ */
+#ifndef NIMB200_H
+#define NIMB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NIMB200_TABLE_VERSION 1
+#define NIMB200_MAX_PARAM 3
+#define NIMB200_MAX_BLOCK_D 64 /* largest RW_block dimension */
+
+/* ---- distributions: Rmath canonical parameterisation, the "Rdist" column of
+ * P/R/distributions_inputList.R:20-149.  The lowering layer appends the
+ * reparameterisation ops (sd = 1/sqrt(tau), scale = 1/rate ...) to the
+ * parameter programs, exactly where NIMBLE inserts lifted nodes. */
+enum {
+  NIMB_DNORM = 1,  /* (mean, sd)        inputList.R:144-149 */
+  NIMB_DGAMMA = 2, /* (shape, scale)    inputList.R:103-110 */
+  NIMB_DPOIS = 3,  /* (lambda)          inputList.R:59-62   */
+  NIMB_DBINOM = 4, /* (size, prob); dbern = size 1, inputList.R:20-31 */
+  NIMB_DBETA = 5,  /* (shape1, shape2)  inputList.R:70-75   */
+  NIMB_DLOGIS = 6, /* (location, scale) inputList.R:139-142 */
+  NIMB_DCAT = 7,   /* (prob[1:K]); K in fam_arg[0]; P/inst/CppCode/dists.cpp:914-934 */
+  NIMB_DEXP = 8    /* (rate): dexp_nimble, P/inst/CppCode/dists.cpp:1804-1807; inputList.R:96-100 */
+};
+
+/* ---- expression programs: postfix, evaluated per (node instance i, chain c).
+ * One op = one IEEE-754 double operation or one libm call, so the CPU oracle
+ * and the device evaluate the same rounding sequence.  Deterministic nodes of
+ * the BUGS model (lifted nodes, links: P/R/BUGS_mathCompatibility.R:3-12) are
+ * inlined here instead of being stored per chain. */
+typedef struct nimb200_op {
+  int32_t op;
+  int32_t a, b, c;
+  double k;
+} nimb200_op;
+
+enum {
+  NIMB_OP_CONST = 1, /* push k */
+  NIMB_OP_DATA = 2,  /* push darr[a][IDX]          (b = index mode, c = its argument) */
+  NIMB_OP_CVAR = 3,  /* push state[a]              per-chain scalar */
+  NIMB_OP_CVARN = 4, /* push state[a + IDX]        (b = index mode, c = its argument) */
+  NIMB_OP_INPROD = 5, /* push sum_{j<k} darr[a][i*c + j] * state[b + j], left to right
+                         (inprod: BUGS_mathCompatibility.R:38-39, Utils.h:251) */
+  NIMB_OP_DATAJ = 6, /* push darr[a][IDX*c... ] vector element j: darr[a][i*c + j] (dcat prob rows) */
+  NIMB_OP_CVARJ = 7, /* push state[a + j]          vector element j (dcat prob in chain state) */
+  /* binary */
+  NIMB_OP_ADD = 16,
+  NIMB_OP_SUB = 17,
+  NIMB_OP_MUL = 18,
+  NIMB_OP_DIV = 19,
+  NIMB_OP_POW = 20,
+  /* unary */
+  NIMB_OP_NEG = 32,
+  NIMB_OP_EXP = 33,
+  NIMB_OP_LOG = 34,
+  NIMB_OP_SQRT = 35,
+  NIMB_OP_ILOGIT = 36, /* 1/(1+exp(-x))  Utils.h:187 */
+  NIMB_OP_LOGIT = 37,  /* log(x/(1-x))   Utils.h:191 */
+  NIMB_OP_INV = 38,    /* 1/x */
+  NIMB_OP_SQ = 39,     /* x*x */
+  NIMB_OP_ABS = 40,
+  NIMB_OP_LOG1P = 41,
+  NIMB_OP_ICLOGLOG = 42, /* 1-exp(-exp(x)) Utils.h:189 */
+  NIMB_OP_STEP = 43      /* x>=0 ? 1 : 0   Utils.h:199 */
+};
+
+/* index modes for NIMB_OP_DATA / NIMB_OP_CVARN: node index i -> element index */
+enum {
+  NIMB_IDX_I = 0,    /* i */
+  NIMB_IDX_DIV = 1,  /* i / c      (outer index of a nested loop, inner extent c) */
+  NIMB_IDX_MOD = 2,  /* i % c */
+  NIMB_IDX_IARR = 3  /* iarr[c][i] (0-based group index, e.g. grp[i]) */
+};
+
+/* ---- one BUGS declaration = a family of n stochastic node instances
+ * (one nodeFun subclass per declaration in the reference,
+ * P/R/nimbleFunction_nodeFunctionNew.R:179-216). */
+typedef struct nimb200_decl {
+  int32_t dist;       /* NIMB_D* */
+  int32_t n;          /* node instances; node i is instance i of the declaration */
+  int32_t value_kind; /* 0: data, value = darr[value_ref][i]; 1: per-chain, state[value_ref + i] */
+  int32_t value_ref;
+  int32_t nparam;
+  int32_t prog_off[NIMB200_MAX_PARAM]; /* parameter programs, offsets into ops[] */
+  int32_t prog_len[NIMB200_MAX_PARAM];
+  int32_t family;     /* NIMB_FAM_*: 0 = generic interpreter, else a fused kernel the host recognised */
+  int32_t fam_arg[4];
+} nimb200_decl;
+
+enum {
+  NIMB_FAM_GENERIC = 0,
+  /* y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))):
+   * fam_arg = {X darr id, beta slot base, p, row stride of X} */
+  NIMB_FAM_BERN_LOGIT_INPROD = 1
+};
+
+/* ---- node selections: which instances of a declaration depend on target t */
+enum {
+  NIMB_SEL_ALL = 0,    /* every instance, for every target */
+  NIMB_SEL_SAME = 1,   /* instance a + t */
+  NIMB_SEL_STRIDE = 2, /* instances t*a .. t*a + a - 1 */
+  NIMB_SEL_SEG = 3,    /* instances iarr[a][t] .. iarr[a][t+1]-1 (sorted groups) */
+  NIMB_SEL_CSR = 4,    /* instances iarr[b][ iarr[a][t] .. iarr[a][t+1]-1 ] */
+  NIMB_SEL_RANGE = 5   /* instances a .. b-1, for every target */
+};
+
+/* parameter codes for nimb200_dep.param: 0..2 = canonical parameter index; the alternative
+ * parameters NIMBLE derives from the canonical ones (altParams, distributions_inputList.R:106,147) */
+enum {
+  NIMB_PARAM_RATE = 16, /* 1/scale   of dgamma(shape, scale) */
+  NIMB_PARAM_TAU = 17   /* sd^-2     of dnorm(mean, sd) */
+};
+
+/* conjugate link of a dependent on the target, P/R/MCMC_conjugacy.R:1397-1524 */
+enum { NIMB_LINK_IDENTITY = 0, NIMB_LINK_ADDITIVE = 1, NIMB_LINK_MULTIPLICATIVE = 2, NIMB_LINK_LINEAR = 3 };
+
+typedef struct nimb200_dep {
+  int32_t decl;
+  int32_t sel, a, b;
+  int32_t stage; /* 0: the target's own prior node(s) ("ProposalStage", MCMC_samplers.R:660-663);
+                    1: stochastic dependents ("DepStage") */
+  int32_t link;  /* conjugate samplers only */
+  int32_t param; /* conjugate samplers only: canonical parameter index of the dependent that the
+                    target enters (lambda, mean, scale<-rate ...), probed as in MCMC_conjugacy.R:766-820 */
+  int32_t pad;
+} nimb200_dep;
+
+/* ---- samplers: one entry = n_targets conditionally independent scalar targets that the
+ * reference would visit one after another with the same sampler type (or one RW_block). */
+enum {
+  NIMB_SAMPLER_RW = 1,         /* MCMC_samplers.R:320-461 */
+  NIMB_SAMPLER_RW_BLOCK = 2,   /* MCMC_samplers.R:643-810 */
+  NIMB_SAMPLER_BINARY = 3,     /* MCMC_samplers.R:115-152 */
+  NIMB_SAMPLER_CONJ_GAMMA = 4, /* dgamma prior; dpois / dgamma(rate) / dnorm(tau) dependents, MCMC_conjugacy.R:80-93 */
+  NIMB_SAMPLER_CONJ_NORMAL = 5 /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
+};
+
+typedef struct nimb200_sampler {
+  int32_t type;
+  int32_t n_targets;   /* scalar samplers: T targets at slots target_slot + t; RW_block: 1 */
+  int32_t target_slot;
+  int32_t d;           /* RW_block dimension (target slots target_slot .. +d-1); else 1 */
+  int32_t dep_off, n_dep; /* into deps[] (stage-0 entries first) */
+  int32_t log_scale;   /* RW: control$log */
+  int32_t reflective;  /* RW: control$reflective */
+  int32_t adaptive;
+  int32_t adapt_interval;
+  int32_t adapt_scale_only; /* RW_block */
+  int32_t tries;            /* RW_block */
+  int32_t propcov_darr;     /* RW_block: darr id of a d*d column-major matrix, -1 = identity */
+  int32_t pad;
+  double scale;
+  double adapt_factor_exponent;
+  double lower, upper;      /* reflective RW bounds */
+} nimb200_sampler;
+
+typedef struct nimb200_table {
+  int32_t version;  /* NIMB200_TABLE_VERSION */
+  int32_t n_slots;  /* doubles of per-chain state (all non-data stochastic nodes) */
+  int32_t n_darr;   /* shared (chain-invariant) double arrays: data and constants */
+  int32_t n_iarr;   /* shared int32 arrays: group indices, segment offsets */
+  const double *const *darr;
+  const int64_t *darr_len;
+  const int32_t *const *iarr;
+  const int64_t *iarr_len;
+  int32_t n_ops;
+  int32_t n_decl;
+  const nimb200_op *ops;
+  const nimb200_decl *decl;
+  int32_t n_samplers;
+  int32_t n_deps;
+  const nimb200_sampler *samplers; /* in samplerExecutionOrder, MCMC_build.R:287-290 */
+  const nimb200_dep *deps;
+  int32_t n_monitors;
+  int32_t pad;
+  const int32_t *monitor_slots; /* state slots copied to mvSamples, MCMC_build.R:294-303 */
+} nimb200_table;
+
+typedef struct nimb200_model nimb200_model; /* opaque; owns all device buffers */
+
+/* Every function returns 0 on success, non-zero on error; the message is read with
+ * nimb200_last_error() (thread-local).  Replaces NIMERROR/Rf_error, Utils.h:60. */
+const char *nimb200_last_error(void);
+int nimb200_version(void);
+
+/* compileNimble(model, mcmc) for the sampling path: validates the table, uploads the shared
+ * arrays once, allocates chain-major state for nchains chains on CUDA device `device`.
+ * Replaces populateNodeFxnVectorNew_internal / populateIndexedNodeInfoTable / populateCopierVector,
+ * P/inst/CppCode/accessorClasses.cpp:961-1060.  first_chain is the global index of chain 0 of this
+ * model (chain-sharded multi-GPU runs); it only enters the RNG key. */
+int nimb200_model_create(const nimb200_table *table, int32_t nchains, int32_t first_chain, int32_t device,
+                         nimb200_model **out);
+int nimb200_model_free(nimb200_model *m);
+
+/* model$setInits / values(model, nodes) <- v for every chain at once,
+ * P/inst/CppCode/accessorClasses.cpp:513-545.  Host layout: [nchains][n_slots]. */
+int nimb200_set_values(nimb200_model *m, const double *values);
+int nimb200_get_values(nimb200_model *m, double *values);
+
+/* model$calculate(nodes): sum of log-densities of instances [lo,hi) of one declaration, one value per
+ * chain (P/inst/CppCode/accessorClasses.cpp:49-57).  When the range is the whole declaration the
+ * per-chain block sum is cached as that declaration's logProb. */
+int nimb200_calculate(nimb200_model *m, int32_t decl, int32_t lo, int32_t hi, double *out_nchains);
+/* same, but one value per node instance and chain: out[(i-lo)*nchains + c] (the logProb_x[i] the
+ * reference stores, nimbleFunction_nodeFunctionNew.R:207). */
+int nimb200_calculate_nodes(nimb200_model *m, int32_t decl, int32_t lo, int32_t hi, double *out);
+/* model$calculateDiff(nodes) on a whole declaration: new block sum minus the cached one, cache updated
+ * (nodeFunctionNew.R:208-209, accessorClasses.cpp:237-245). */
+int nimb200_calculateDiff(nimb200_model *m, int32_t decl, double *out_nchains);
+/* model$getLogProb(nodes) on a whole declaration: the cached block sum (accessorClasses.cpp:256-264). */
+int nimb200_getLogProb(nimb200_model *m, int32_t decl, double *out_nchains);
+
+/* Cmcmc$run(niter, nburnin, thin, reset): MCMC_build.R:217-321.  All chains advance together.
+ * reset != 0: samplers reset, iteration counter and sample buffer cleared, the model is initialised
+ * (every node calculated once, initializeModel.R:78-96).  reset == 0 continues the chains and appends.
+ * seed keys the counter-based RNG (DESIGN.md "draws"). */
+int nimb200_mcmc_run(nimb200_model *m, int64_t niter, int64_t nburnin, int32_t thin, int32_t reset,
+                     uint64_t seed);
+/* as.matrix(mvSamples) for every chain: out[c][row][col], rows = saved samples, cols = monitors
+ * (types_util.R:199-214).  *nrows_out receives the row count; out may be NULL to query it. */
+int nimb200_mcmc_samples(nimb200_model *m, double *out, int64_t *nrows_out);
+/* device-side time of the last nimb200_mcmc_run in milliseconds (CUDA events on the run stream),
+ * and how many kernels it launched. */
+int nimb200_mcmc_last_timing(nimb200_model *m, double *ms_out, int64_t *launches_out);
+/* sampler state read-back (scale, acceptance counters, proposal covariance): the fields the reference
+ * keeps in the sampler objects, MCMC_samplers.R:449-459, 793-808.
+ * what: 0 scale [T][C]; 1 timesAdapted [T][C]; 2 propCov [d*d][C] (RW_block). */
+int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, double *out, int64_t cap);
+
+/* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1) or gamma(shape a, scale 1)
+ * variates (kind 2) that sampler `sampler` would consume on the device for (chain, iter, target), so the
+ * host can replay identical draws into another implementation. */
+int nimb200_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target,
+                  int32_t kind, double a, int32_t n, double *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NIMB200_H */

@@ -1,0 +1,168 @@
+"""ctypes binding of the C ABI in include/nimb200.h (libnimb200.so, the sm_100a library).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is present, every call
+raises.  (The same `Backend` class can bind a library that exports the identical entry points under
+another prefix; the test suite uses that to drive the CPU oracle through the very same host code.)
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import table as T
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnimb200.so")
+
+_dp = C.POINTER(C.c_double)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_dp)
+
+
+class BackendError(RuntimeError):
+    pass
+
+
+class Backend:
+    """Thin object wrapper over the C entry points `<prefix>model_create`, `<prefix>mcmc_run`, ..."""
+
+    def __init__(self, path=LIB_PATH, prefix="nimb200_", has_device=True, name="b200"):
+        if not os.path.exists(path):
+            raise BackendError("%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)" % path)
+        self.lib = C.CDLL(path)
+        self.prefix, self.has_device, self.name, self.path = prefix, has_device, name, path
+        L, P = self.lib, prefix
+        vp = C.c_void_p
+
+        def fn(name_, argtypes, restype=C.c_int):
+            f = getattr(L, P + name_)
+            f.argtypes, f.restype = argtypes, restype
+            return f
+        self._err = fn("last_error", [], C.c_char_p)
+        if has_device:
+            self._create = fn("model_create", [C.POINTER(T.Table), C.c_int32, C.c_int32, C.c_int32, C.POINTER(vp)])
+        else:
+            self._create = fn("model_create", [C.POINTER(T.Table), C.c_int32, C.c_int32, C.POINTER(vp)])
+        self._free = fn("model_free", [vp])
+        self._set = fn("set_values", [vp, _dp])
+        self._get = fn("get_values", [vp, _dp])
+        self._calc = fn("calculate", [vp, C.c_int32, C.c_int32, C.c_int32, _dp])
+        self._calc_nodes = fn("calculate_nodes", [vp, C.c_int32, C.c_int32, C.c_int32, _dp])
+        self._calc_diff = fn("calculateDiff", [vp, C.c_int32, _dp])
+        self._get_lp = fn("getLogProb", [vp, C.c_int32, _dp])
+        self._run = fn("mcmc_run", [vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_uint64])
+        self._samples = fn("mcmc_samples", [vp, _dp, C.POINTER(C.c_int64)])
+        self._sstate = fn("sampler_state", [vp, C.c_int32, C.c_int32, _dp, C.c_int64])
+        self._draws = fn("draws", [C.c_uint64, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double,
+                                   C.c_int32, _dp])
+        if has_device:
+            self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
+
+    def check(self, rc):
+        if rc != 0:
+            msg = self._err()
+            raise BackendError((msg or b"unknown error").decode())
+
+    def create(self, packed_table, nchains, first_chain=0, device=0):
+        h = C.c_void_p()
+        if self.has_device:
+            self.check(self._create(C.byref(packed_table), nchains, first_chain, device, C.byref(h)))
+        else:
+            self.check(self._create(C.byref(packed_table), nchains, first_chain, C.byref(h)))
+        return h
+
+    def draws(self, seed, chain, it, sampler, target, kind, a, n):
+        out = np.empty(n)
+        self.check(self._draws(seed, chain, it, sampler, target, kind, a, n, _ptr(out)))
+        return out
+
+
+class DeviceModel:
+    """One compiled model instance: nchains chains resident on one device (or in the oracle)."""
+
+    def __init__(self, backend, builder, nchains, first_chain=0, device=0):
+        self.backend, self.builder, self.C = backend, builder, nchains
+        self.packed = builder.pack()
+        self.n_slots, self.n_mon = builder.n_slots, len(builder.monitors)
+        self.h = backend.create(self.packed, nchains, first_chain, device)
+
+    def close(self):
+        if self.h is not None and self.h.value:
+            self.backend._free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_values(self, v):
+        v = np.ascontiguousarray(v, dtype=np.float64)
+        assert v.shape == (self.C, self.n_slots), v.shape
+        self.backend.check(self.backend._set(self.h, _ptr(v)))
+
+    def get_values(self):
+        out = np.empty((self.C, self.n_slots))
+        self.backend.check(self.backend._get(self.h, _ptr(out)))
+        return out
+
+    def calculate(self, decl, lo=0, hi=None):
+        hi = self.builder.decls[decl].n if hi is None else hi
+        out = np.empty(self.C)
+        self.backend.check(self.backend._calc(self.h, decl, lo, hi, _ptr(out)))
+        return out
+
+    def calculate_nodes(self, decl, lo=0, hi=None):
+        hi = self.builder.decls[decl].n if hi is None else hi
+        out = np.empty((hi - lo, self.C))
+        self.backend.check(self.backend._calc_nodes(self.h, decl, lo, hi, _ptr(out)))
+        return out
+
+    def calculateDiff(self, decl):
+        out = np.empty(self.C)
+        self.backend.check(self.backend._calc_diff(self.h, decl, _ptr(out)))
+        return out
+
+    def getLogProb(self, decl):
+        out = np.empty(self.C)
+        self.backend.check(self.backend._get_lp(self.h, decl, _ptr(out)))
+        return out
+
+    def run(self, niter, nburnin=0, thin=1, reset=True, seed=0):
+        self.backend.check(self.backend._run(self.h, niter, nburnin, thin, 1 if reset else 0, seed))
+
+    def samples(self):
+        n = C.c_int64()
+        self.backend.check(self.backend._samples(self.h, None, C.byref(n)))
+        out = np.empty((self.C, n.value, self.n_mon))
+        if out.size:
+            self.backend.check(self.backend._samples(self.h, _ptr(out), C.byref(n)))
+        return out
+
+    def sampler_state(self, sampler, what):
+        s = self.builder.samplers[sampler]
+        Tn = 1 if s.type == T.SAMPLER_RW_BLOCK else s.n_targets
+        n = (s.d * s.d if what == 2 else Tn) * self.C
+        out = np.empty(n)
+        self.backend.check(self.backend._sstate(self.h, sampler, what, _ptr(out), n))
+        return out.reshape(-1, self.C)
+
+    def last_timing(self):
+        ms, k = C.c_double(), C.c_int64()
+        self.backend.check(self.backend._timing(self.h, C.byref(ms), C.byref(k)))
+        return ms.value, k.value
+
+
+_default = None
+
+
+def default_backend():
+    """The CUDA library.  Fails loudly when it is missing; nothing else is ever substituted."""
+    global _default
+    if _default is None:
+        _default = Backend()
+    return _default

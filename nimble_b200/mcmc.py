@@ -1,0 +1,677 @@
+"""configureMCMC / buildMCMC / compileNimble / runMCMC for the B200 back end.
+
+Same names, argument meaning and error behaviour as the reference's R functions:
+  configureMCMC   P/R/MCMC_configuration.R:1362-1396 (default sampler assignment :340-446)
+  buildMCMC       P/R/MCMC_build.R:101-215 (setup) / :217-321 (run)
+  compileNimble   P/R/nimbleProject.R:1115-1215 (here: lower to the node table of include/nimb200.h)
+  runMCMC         P/R/MCMC_run.R:82-213
+The difference the back end exists for: runMCMC materialises the initial values of all chains first and
+advances every chain in ONE batched device run, instead of the sequential chain loop at MCMC_run.R:127-153.
+"""
+import numpy as np
+
+from . import _capi
+from . import table as T
+from .model import Model, ModelError, tree_reads_var
+
+
+# ----------------------------------------------------------------------------- conjugacy (MCMC_conjugacy.R)
+def _linear_form(tree, var):
+    """Is `tree` a + b*target?  Returns None (not linear) or (has_offset, has_coeff).
+    Counterpart of cc_checkLinearity, P/R/MCMC_conjugacy.R:1397-1524."""
+    if not tree_reads_var(tree, var):
+        return "free"
+    k = tree[0]
+    if k == "cvar":
+        return (False, False)
+    if k == "inprod":
+        return (False, True)
+    if k == "un" and tree[1] == T.OP_NEG:
+        f = _linear_form(tree[2], var)
+        return None if f in (None, "free") else (f[0], True)
+    if k == "bin":
+        op, l, r = tree[1], tree[2], tree[3]
+        fl, fr = _linear_form(l, var), _linear_form(r, var)
+        if fl is None or fr is None:
+            return None
+        if op in (T.OP_ADD, T.OP_SUB):
+            if fl == "free":
+                return (True, fr[1] or op == T.OP_SUB)
+            if fr == "free":
+                return (True, fl[1])
+            return (fl[0] or fr[0], True)
+        if op == T.OP_MUL:
+            if fl == "free":
+                return (fr[0], True)
+            if fr == "free":
+                return (fl[0], True)
+            return None
+        if op == T.OP_DIV and fr == "free":
+            return (fl[0], True)
+    return None
+
+
+def _link_code(f):
+    off, co = f
+    if off and co:
+        return T.LINK_LINEAR
+    if off:
+        return T.LINK_ADDITIVE
+    if co:
+        return T.LINK_MULTIPLICATIVE
+    return T.LINK_IDENTITY
+
+
+def check_conjugacy(model, decl):
+    """Returns (sampler type, {dependent decl index: (link, param code)}) or None.
+    Relationship table: P/R/MCMC_conjugacy.R:80-93 (dgamma prior), :109-115 (dnorm prior)."""
+    var = decl.var
+    if decl.dist not in (T.DGAMMA, T.DNORM):
+        return None
+    if any(v == var for v, _ in decl.reads()):
+        return None
+    info = {}
+    for dep in model.dependents(var):
+        if dep is decl:
+            continue
+        bp = dep.bugs_params
+
+        def only_in(name_):
+            return name_ in bp and all(not tree_reads_var(t, var) for k, t in bp.items() if k != name_)
+        if decl.dist == T.DGAMMA:
+            if dep.dist == T.DPOIS and only_in("lambda"):
+                pname, code = "lambda", 0
+            elif dep.dist == T.DGAMMA and only_in("rate"):
+                pname, code = "rate", T.PARAM_RATE
+            elif dep.dist == T.DNORM and only_in("tau"):
+                pname, code = "tau", T.PARAM_TAU
+            elif dep.dist == T.DEXP and only_in("rate"):
+                pname, code = "rate", 0
+            else:
+                return None
+            f = _linear_form(bp[pname], var)
+            if f in (None, "free") or f[0]:  # gamma prior: identity or multiplicative links only
+                return None
+        else:
+            if dep.dist == T.DNORM and only_in("mean"):
+                pname, code = "mean", 0
+            else:
+                return None
+            f = _linear_form(bp[pname], var)
+            if f in (None, "free"):
+                return None
+        info[dep.index] = (_link_code(f), code)
+    if not info:
+        return None
+    return (T.SAMPLER_CONJ_GAMMA if decl.dist == T.DGAMMA else T.SAMPLER_CONJ_NORMAL), info
+
+
+# ----------------------------------------------------------------------------- configuration
+class SamplerConf:
+    """samplerConf: name, target, control (P/R/MCMC_configuration.R:2-42)."""
+
+    def __init__(self, type_, var, positions, control=None, conj=None):
+        self.type, self.var, self.positions = type_, var, np.asarray(positions, dtype=np.int64)
+        self.control, self.conj = dict(control or {}), conj
+        self.name = T.SAMPLER_NAMES[type_]
+
+    def target_names(self, model):
+        return model.element_names(self.var, self.positions)
+
+
+class MCMCconf:
+    """MCMCconf: the ordered sampler list and the monitors (P/R/MCMC_configuration.R:73)."""
+
+    def __init__(self, model, monitors=None, thin=1, useConjugacy=True, nodes=None, control=None,
+                 multivariateNodesAsScalars=False, autoBlock=False):
+        if autoBlock:
+            raise NotImplementedError("autoBlock is outside the B200 sampling path")
+        self.model, self.thin, self.samplerConfs = model, thin, []
+        self.monitors = list(monitors) if monitors is not None else model.top_level_vars()
+        self.control_defaults = dict(control or {})
+        use = set(nodes) if nodes is not None else None
+        for var in model.topo_vars():
+            if use is not None and var not in use:
+                continue
+            for decl in model.decl_of(var):
+                self._add_default(decl, useConjugacy)
+
+    # default assignment rules, MCMC_configuration.R:340-446: conjugate -> binary -> (discrete: unsupported) -> RW
+    def _add_default(self, decl, useConjugacy):
+        model = self.model
+        conj = check_conjugacy(model, decl) if useConjugacy else None
+        if conj is not None:
+            self.samplerConfs.append(SamplerConf(conj[0], decl.var, decl.pos, self.control_defaults, conj=conj[1]))
+            return
+        if decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0):
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_BINARY, decl.var, decl.pos, self.control_defaults))
+            return
+        if decl.dist in (T.DPOIS, T.DBINOM, T.DCAT):
+            raise NotImplementedError(
+                "node %s: default sampler for a non-binary discrete node (slice / categorical) is not part of the "
+                "B200 sampling path; unknown samplers are a hard error, there is no CPU fallback" % decl.var)
+        self.samplerConfs.append(SamplerConf(T.SAMPLER_RW, decl.var, decl.pos, self.control_defaults))
+
+    def _resolve_target(self, target):
+        """'beta', 'beta[3]', 'beta[1:50]' or a list of those -> (var, positions)."""
+        import re
+        targets = [target] if isinstance(target, str) else list(target)
+        var, pos = None, []
+        for tname in targets:
+            m = re.match(r"^\s*([A-Za-z_.][\w.]*)\s*(?:\[(.*)\])?\s*$", tname)
+            if not m or m.group(1) not in self.model.var_slot:
+                raise ModelError("unknown target node %r" % tname)
+            if var not in (None, m.group(1)):
+                raise NotImplementedError("a sampler over several variables is not supported")
+            var = m.group(1)
+            shape = self.model.var_shape[var]
+            if m.group(2) is None:
+                pos.extend(range(int(np.prod(shape)) if shape else 1))
+                continue
+            subs = []
+            for part, s in zip(m.group(2).split(","), shape):
+                part = part.strip()
+                if part == "":
+                    subs.append(np.arange(1, s + 1))
+                elif ":" in part:
+                    a, b = part.split(":")
+                    subs.append(np.arange(int(a), int(b) + 1))
+                else:
+                    subs.append(np.array([int(part)]))
+            grid = np.meshgrid(*subs, indexing="ij")
+            flat, mult = np.zeros(grid[0].size, dtype=np.int64), 1
+            for g, s in zip(grid, shape):
+                flat += (g.reshape(-1, order="F") - 1) * mult
+                mult *= s
+            pos.extend(flat.tolist())
+        return var, np.array(pos, dtype=np.int64)
+
+    def addSampler(self, target, type="RW", control=None, **kw):
+        """conf$addSampler(target, type, control): P/R/MCMC_configuration.R:554-714."""
+        ctrl = dict(self.control_defaults)
+        ctrl.update(control or {})
+        ctrl.update(kw)
+        var, pos = self._resolve_target(target)
+        tname = type.replace("sampler_", "")
+        if tname == "RW":
+            if len(pos) > 1:
+                raise ValueError("cannot use RW sampler on more than one target; try RW_block sampler")
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_RW, var, pos, ctrl))
+        elif tname == "RW_block":
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_RW_BLOCK, var, pos, ctrl))
+        elif tname == "binary":
+            if len(pos) > 1:
+                raise ValueError("cannot use binary sampler on more than one target node")
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_BINARY, var, pos, ctrl))
+        elif tname == "conjugate":
+            for decl in self.model.decl_of(var):
+                conj = check_conjugacy(self.model, decl)
+                if conj is None:
+                    raise ValueError("no conjugate relationship found for %s" % var)
+                self.samplerConfs.append(SamplerConf(conj[0], var, pos, ctrl, conj=conj[1]))
+        else:
+            raise NotImplementedError("sampler type %r is not part of the B200 sampling path (supported: RW, "
+                                      "RW_block, binary, conjugate); there is no CPU fallback" % type)
+        return self
+
+    def removeSamplers(self, target=None):
+        if target is None:
+            self.samplerConfs = []
+            return self
+        var, pos = self._resolve_target(target)
+        keep = []
+        for s in self.samplerConfs:
+            if s.var != var:
+                keep.append(s)
+                continue
+            left = np.setdiff1d(s.positions, pos)
+            if left.size and s.type != T.SAMPLER_RW_BLOCK and left.size < s.positions.size:
+                s.positions = left
+                keep.append(s)
+            elif left.size == s.positions.size:
+                keep.append(s)
+        self.samplerConfs = keep
+        return self
+
+    removeSampler = removeSamplers
+
+    def addMonitors(self, *names):
+        for n_ in names:
+            for x in ([n_] if isinstance(n_, str) else n_):
+                if x not in self.monitors:
+                    self.monitors.append(x)
+        return self
+
+    def setMonitors(self, *names):
+        self.monitors = []
+        return self.addMonitors(*names)
+
+    def resetMonitors(self):
+        self.monitors = []
+        return self
+
+    def getSamplers(self):
+        return list(self.samplerConfs)
+
+    def printSamplers(self):
+        lines = []
+        for i, s in enumerate(self.samplerConfs):
+            names = s.target_names(self.model)
+            tgt = names[0] if len(names) == 1 else "%s .. %s (%d nodes)" % (names[0], names[-1], len(names))
+            lines.append("[%d] %s sampler: %s" % (i + 1, s.name, tgt))
+        print("\n".join(lines))
+        return lines
+
+
+def configureMCMC(model, monitors=None, thin=1, useConjugacy=True, nodes=None, control=None, **kw):
+    if not isinstance(model, Model):
+        raise TypeError("configureMCMC: first argument must be a model")
+    return MCMCconf(model, monitors, thin, useConjugacy, nodes, control, **kw)
+
+
+# ----------------------------------------------------------------------------- lowering to the node table
+class _Lowering:
+    def __init__(self, model, conf):
+        self.model, self.conf = model, conf
+        self.b = T.TableBuilder()
+        self.b.n_slots = model.n_slots
+        self._dcache = {}
+        self.decl_ids = {}
+        self.colnames = []
+        self.sampler_map = []  # table sampler index -> (SamplerConf, element positions)
+
+    # -- shared arrays (deduplicated)
+    def _darr(self, a):
+        a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1)
+        key = (a.size, float(a[0]) if a.size else 0.0, float(a[-1]) if a.size else 0.0, float(a[::max(1, a.size // 64)].sum()))
+        for cand in self._dcache.get(key, []):
+            if np.array_equal(self.b.darr[cand], a):
+                return cand
+        i = self.b.add_darr(a)
+        self._dcache.setdefault(key, []).append(i)
+        return i
+
+    def _flatten(self, tree, decl, ops):
+        k = tree[0]
+        if k == "const":
+            ops.append((T.OP_CONST, 0, 0, 0, tree[1]))
+        elif k == "data":
+            v, n = tree[1], decl.n
+            J = decl.loop_extents[-1] if len(decl.loop_extents) > 1 else 0
+            if J > 1 and n % J == 0 and np.all(v.reshape(-1, J) == v.reshape(-1, J)[:, :1]):
+                ops.append((T.OP_DATA, self._darr(v.reshape(-1, J)[:, 0]), T.IDX_DIV, J, 0.0))
+            else:
+                ops.append((T.OP_DATA, self._darr(v), T.IDX_I, 0, 0.0))
+        elif k == "cvar":
+            slot, pos = self.model.var_slot[tree[1]], tree[2]
+            if np.isscalar(pos) or isinstance(pos, (int, np.integer)):
+                ops.append((T.OP_CVAR, slot + int(pos), 0, 0, 0.0))
+            else:
+                n = decl.n
+                ar = np.arange(n)
+                J = decl.loop_extents[-1] if len(decl.loop_extents) > 1 else 0
+                if np.all(pos - pos[0] == ar):
+                    ops.append((T.OP_CVARN, slot + int(pos[0]), T.IDX_I, 0, 0.0))
+                elif J > 1 and np.all(pos - pos[0] == ar // J):
+                    ops.append((T.OP_CVARN, slot + int(pos[0]), T.IDX_DIV, J, 0.0))
+                else:
+                    ops.append((T.OP_CVARN, slot, T.IDX_IARR, self.b.add_iarr(pos), 0.0))
+        elif k == "inprod":
+            X, var, lo, p = tree[1], tree[2], tree[3], tree[4]
+            ops.append((T.OP_INPROD, self._darr(X), self.model.var_slot[var] + lo, p, float(p)))
+        elif k == "dataj":
+            ops.append((T.OP_DATAJ, self._darr(tree[1]), 0, tree[1].shape[1], 0.0))
+        elif k == "cvarj":
+            ops.append((T.OP_CVARJ, self.model.var_slot[tree[1]] + tree[2], 0, 0, 0.0))
+        elif k == "un":
+            self._flatten(tree[2], decl, ops)
+            ops.append((tree[1], 0, 0, 0, 0.0))
+        elif k == "bin":
+            self._flatten(tree[2], decl, ops)
+            self._flatten(tree[3], decl, ops)
+            ops.append((tree[1], 0, 0, 0, 0.0))
+        else:
+            raise ModelError("cannot flatten %r" % (k,))
+
+    def _add_decl(self, decl):
+        d = T.Decl()
+        d.dist, d.n, d.nparam = decl.dist, decl.n, len(decl.params)
+        if decl.is_data:
+            d.value_kind, d.value_ref = 0, self._darr(decl.values)
+        else:
+            base = self.model.var_slot[decl.var]
+            if not np.all(decl.pos - decl.pos[0] == np.arange(decl.n)):
+                raise ModelError("%s: elements of a latent variable must be declared in storage order" % decl.var)
+            d.value_kind, d.value_ref = 1, base + int(decl.pos[0])
+        for i, tree in enumerate(decl.params):
+            ops = []
+            self._flatten(tree, decl, ops)
+            d.prog_off[i], d.prog_len[i] = self.b.add_prog(ops)
+        d.family = T.FAM_GENERIC
+        if decl.dist == T.DCAT:
+            d.fam_arg[0] = decl.K
+        # fused family: y[i] ~ dbern(ilogit(inprod(X[i,], beta)))
+        if (decl.dist == T.DBINOM and decl.is_data and decl.params[0] == ("const", 1.0)
+                and decl.params[1][0] == "un" and decl.params[1][1] == T.OP_ILOGIT and decl.params[1][2][0] == "inprod"):
+            ip = decl.params[1][2]
+            d.family = T.FAM_BERN_LOGIT_INPROD
+            d.fam_arg[0] = self._darr(ip[1])
+            d.fam_arg[1] = self.model.var_slot[ip[2]] + ip[3]
+            d.fam_arg[2] = ip[4]
+            d.fam_arg[3] = ip[4]
+        self.b.decls.append(d)
+        return len(self.b.decls) - 1
+
+    # -- which nodes of `dep` read which target (relative position) of var
+    def _target_of_nodes(self, dep, var, pos0, Tn):
+        reads = [p for v, p in dep.reads() if v == var]
+        if not reads:
+            return None
+        if any(isinstance(p, tuple) for p in reads):
+            return "multi"
+        arrs = [np.full(dep.n, int(p), dtype=np.int64) if np.isscalar(p) or isinstance(p, (int, np.integer)) else p
+                for p in reads]
+        for a in arrs[1:]:
+            if not np.array_equal(a, arrs[0]):
+                return "multi"
+        return arrs[0] - pos0
+
+    def _selection(self, tgt, n, Tn):
+        """tgt[node] = target index (or out of [0,Tn)): pick the cheapest selection form."""
+        ar = np.arange(n)
+        inside = (tgt >= 0) & (tgt < Tn)
+        if Tn == 1:
+            if np.all(inside):
+                return (T.SEL_ALL, 0, 0)
+            nodes = np.nonzero(inside)[0]
+            if nodes.size and np.all(np.diff(nodes) == 1):
+                return (T.SEL_RANGE, int(nodes[0]), int(nodes[-1]) + 1)
+            return (T.SEL_CSR, self.b.add_iarr(np.array([0, nodes.size])), self.b.add_iarr(nodes))
+        if np.all(inside):
+            if n == Tn and np.all(tgt == ar):
+                return (T.SEL_SAME, 0, 0)
+            if n % Tn == 0 and np.all(tgt == ar // (n // Tn)):
+                return (T.SEL_STRIDE, n // Tn, 0)
+            if np.all(np.diff(tgt) >= 0):
+                off = np.searchsorted(tgt, np.arange(Tn + 1), side="left")
+                return (T.SEL_SEG, self.b.add_iarr(off), 0)
+        nodes = np.nonzero(inside)[0]
+        order = nodes[np.argsort(tgt[nodes], kind="stable")]
+        off = np.searchsorted(tgt[order], np.arange(Tn + 1), side="left")
+        return (T.SEL_CSR, self.b.add_iarr(off), self.b.add_iarr(order))
+
+    def _emit_sampler(self, sc, positions, vectorised):
+        model, b = self.model, self.b
+        var = sc.var
+        decl = [d for d in model.decl_of(var) if np.isin(positions[0], d.pos)][0]
+        pos0, Tn = int(positions[0]), (len(positions) if vectorised else 1)
+        block = sc.type == T.SAMPLER_RW_BLOCK
+        d = len(positions) if block else 1
+        s = T.Sampler()
+        s.type, s.n_targets, s.d = sc.type, (1 if block else Tn), d
+        s.target_slot = model.var_slot[var] + pos0
+        ctl = sc.control
+        s.log_scale = int(bool(ctl.get("log", False)))
+        s.reflective = int(bool(ctl.get("reflective", False)))
+        s.adaptive = int(bool(ctl.get("adaptive", True)))
+        s.adapt_interval = int(ctl.get("adaptInterval", 200))
+        s.adapt_scale_only = int(bool(ctl.get("adaptScaleOnly", False)))
+        s.tries = int(ctl.get("tries", 1))
+        s.scale = float(ctl.get("scale", 1.0))
+        s.adapt_factor_exponent = float(ctl.get("adaptFactorExponent", 0.8))
+        s.lower, s.upper = float(ctl.get("lower", -np.inf)), float(ctl.get("upper", np.inf))
+        s.propcov_darr = -1
+        if s.log_scale and s.reflective:
+            raise ValueError("cannot use reflective RW sampler on a log scale (i.e. with options log=TRUE and reflective=TRUE")
+        if s.adapt_factor_exponent < 0:
+            raise ValueError("cannot use RW sampler with adaptFactorExponent control parameter less than 0")
+        if s.scale < 0:
+            raise ValueError("cannot use RW sampler with scale control parameter less than 0")
+        if block:
+            if d > T.MAX_BLOCK_D:
+                raise ValueError("RW_block dimension %d exceeds the supported maximum %d" % (d, T.MAX_BLOCK_D))
+            pc = ctl.get("propCov", "identity")
+            if not isinstance(pc, str):
+                pc = np.asarray(pc, dtype=np.float64)
+                if pc.shape != (d, d):
+                    raise ValueError("propCov matrix must have dimension %d x %d" % (d, d))
+                if not np.allclose(pc, pc.T):
+                    raise ValueError("propCov matrix must be symmetric")
+                s.propcov_darr = b.add_darr(pc.reshape(-1, order="F"))
+        s.dep_off = len(b.deps)
+        span = d if block else Tn
+        # stage 0: the target's own prior nodes
+        node0 = int(np.nonzero(decl.pos == pos0)[0][0])
+        dep0 = T.Dep()
+        dep0.decl, dep0.stage = self.decl_ids[decl.index], 0
+        if block or Tn == 1:
+            dep0.sel, dep0.a, dep0.b = T.SEL_RANGE, node0, node0 + span
+        else:
+            dep0.sel, dep0.a = T.SEL_SAME, node0
+        b.deps.append(dep0)
+        # stage 1: stochastic dependents
+        for dep in model.dependents(var):
+            tgt = self._target_of_nodes(dep, var, pos0, span)
+            if tgt is None:
+                continue
+            if isinstance(tgt, str):  # node reads several elements: every node depends on every target
+                if not block and Tn > 1:
+                    raise ModelError("internal: non-separable dependents in a vectorised sampler")
+                reads = [p for v, p in dep.reads() if v == var]
+                hit = False
+                for p in reads:
+                    if isinstance(p, tuple):
+                        hit |= (p[1] < pos0 + span) and (p[1] + p[2] > pos0)
+                    else:
+                        pa = np.asarray(p)
+                        hit |= bool(np.any((pa >= pos0) & (pa < pos0 + span)))
+                if not hit:
+                    continue
+                sel = (T.SEL_ALL, 0, 0)
+            elif block:
+                inside = (tgt >= 0) & (tgt < span)
+                if not np.any(inside):
+                    continue
+                sel = self._selection(np.where(inside, 0, -1), dep.n, 1)
+            else:
+                if not np.any((tgt >= 0) & (tgt < Tn)):
+                    continue
+                sel = self._selection(tgt, dep.n, Tn)
+            if dep is decl:
+                if block:
+                    continue
+                raise ModelError("%s: a node's own declaration reads the variable; not supported" % var)
+            de = T.Dep()
+            de.decl, de.stage = self.decl_ids[dep.index], 1
+            de.sel, de.a, de.b = sel
+            if sc.conj is not None:
+                if dep.index not in sc.conj:
+                    raise ModelError("internal: conjugate dependent missing")
+                de.link, de.param = sc.conj[dep.index]
+            b.deps.append(de)
+        s.n_dep = len(b.deps) - s.dep_off
+        b.samplers.append(s)
+        self.sampler_map.append((sc, np.asarray(positions)))
+
+    def _separable(self, sc):
+        """Can the targets of this scalar sampler be updated as one parallel sweep?  True when no
+        stochastic node depends on two different targets and no target's prior reads another target
+        (conditional independence given the rest), so that the sweep equals the reference's sequential visits."""
+        model, var, pos = self.model, sc.var, sc.positions
+        if len(pos) == 1:
+            return True
+        if not np.all(np.diff(pos) == 1):
+            return False
+        decls = [d for d in model.decl_of(var) if np.any(np.isin(pos, d.pos))]
+        if len(decls) != 1:
+            return False
+        for dep in model.dependents(var):
+            if dep is decls[0]:
+                return False
+            tgt = self._target_of_nodes(dep, var, int(pos[0]), len(pos))
+            if isinstance(tgt, str):
+                return False
+        return True
+
+    def run(self):
+        model, b = self.model, self.b
+        for d in model.decls:
+            self.decl_ids[d.index] = self._add_decl(d)
+        for sc in self.conf.samplerConfs:
+            if sc.type == T.SAMPLER_RW_BLOCK:
+                if not np.all(np.diff(sc.positions) == 1):
+                    raise NotImplementedError("RW_block targets must be contiguous elements of one variable")
+                self._emit_sampler(sc, sc.positions, False)
+            elif self._separable(sc):
+                self._emit_sampler(sc, sc.positions, True)
+            else:
+                for p in sc.positions:
+                    self._emit_sampler(sc, np.array([p]), False)
+        for name_ in self.conf.monitors:
+            if name_ not in model.var_slot:
+                raise ModelError("monitor %s is not a stochastic non-data variable of the model" % name_)
+            shape = model.var_shape[name_]
+            size = int(np.prod(shape)) if shape else 1
+            b.monitors.extend(range(model.var_slot[name_], model.var_slot[name_] + size))
+            self.colnames.extend(model.element_names(name_, np.arange(size)))
+        return b
+
+
+# ----------------------------------------------------------------------------- buildMCMC / compileNimble / runMCMC
+class MCMC:
+    """Uncompiled MCMC object (buildMCMC's return value).  Only its compiled form can run here."""
+    name = "MCMC"
+
+    def __init__(self, conf):
+        self.conf, self.model = conf, conf.model
+        self.monitors, self.thinFromConfVec = list(conf.monitors), [conf.thin, conf.thin]
+
+    def run(self, *a, **k):
+        raise RuntimeError("uncompiled MCMC execution is not available in the B200 back end; call compileNimble() first")
+
+
+def buildMCMC(conf, **kw):
+    if isinstance(conf, Model):
+        conf = configureMCMC(conf, **kw)
+    if not isinstance(conf, MCMCconf):
+        raise TypeError("buildMCMC: argument must be an MCMC configuration or a model")
+    return MCMC(conf)
+
+
+class SampleMatrix(np.ndarray):
+    """as.matrix(mvSamples): rows = saved iterations, columns = monitored scalar nodes (types_util.R:199-214)."""
+
+    def __new__(cls, a, colnames):
+        obj = np.asarray(a).view(cls)
+        obj.colnames = list(colnames)
+        return obj
+
+    def __array_finalize__(self, obj):
+        self.colnames = getattr(obj, "colnames", None)
+
+    def col(self, name_):
+        return np.asarray(self[:, self.colnames.index(name_)])
+
+
+class CompiledMCMC:
+    """Cmcmc: owns the lowered table and, once the chain count is known, the device-resident model."""
+    name = "MCMC"
+
+    def __init__(self, mcmc, backend=None, device=0, first_chain=0):
+        self.Robject, self.model, self.conf = mcmc, mcmc.model, mcmc.conf
+        self.backend = backend if backend is not None else _capi.default_backend()
+        self.device, self.first_chain = device, first_chain
+        self.lowering = _Lowering(self.model, self.conf)
+        self.builder = self.lowering.run()
+        self.colnames = self.lowering.colnames
+        self.thinFromConfVec = mcmc.thinFromConfVec
+        self.dm = None
+        self.mvSamples = None
+
+    def _ensure(self, nchains):
+        if self.dm is None or self.dm.C != nchains:
+            if self.dm is not None:
+                self.dm.close()
+            self.dm = _capi.DeviceModel(self.backend, self.builder, nchains, self.first_chain, self.device)
+        return self.dm
+
+    def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0):
+        """All chains at once.  inits_matrix: [nchains][n_slots] (ignored when reset is False)."""
+        if niter < 0:
+            raise ValueError("cannot specify niter < 0")
+        if nburnin < 0:
+            raise ValueError("cannot specify nburnin < 0")
+        if nburnin > niter:
+            raise ValueError("cannot specify nburnin > niter")
+        thin = self.thinFromConfVec[0] if thin in (None, -1) else thin
+        if thin < 1:
+            raise ValueError("cannot use thin < 1")
+        if thin != int(thin):
+            raise ValueError("cannot use non-integer thin")
+        if not reset and nburnin != 0:
+            raise ValueError("cannot specify nburnin when using reset = FALSE.")
+        dm = self._ensure(inits_matrix.shape[0])
+        if reset:
+            dm.set_values(inits_matrix)
+        dm.run(int(niter), int(nburnin), int(thin), reset, int(seed))
+        self.mvSamples = dm.samples()
+        return self.mvSamples
+
+    def run(self, niter, nburnin=0, thin=-1, reset=True, inits=None, seed=0, **_ignored):
+        """mcmc$run(niter, ...) for a single chain (compatibility route)."""
+        init = self.model.init_vector(inits)[None, :]
+        if not reset and self.dm is not None:
+            init = self.dm.get_values()
+        self.run_chains(init, niter, nburnin, thin, reset, seed)
+
+    def as_matrix(self, chain=0):
+        return SampleMatrix(self.mvSamples[chain], self.colnames)
+
+
+def compileNimble(*objs, backend=None, device=0, first_chain=0, **_ignored):
+    """compileNimble(model, mcmc): returns the compiled MCMC (and the model, if it was passed too)."""
+    out = []
+    for o in objs:
+        if isinstance(o, MCMC):
+            out.append(CompiledMCMC(o, backend, device, first_chain))
+        elif isinstance(o, Model):
+            out.append(o)
+        else:
+            raise TypeError("compileNimble: cannot compile object of type %s" % type(o).__name__)
+    return out[0] if len(out) == 1 else tuple(out)
+
+
+def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setSeed=False, samplesAsCodaMCMC=False,
+            summary=False, progressBar=False, **_ignored):
+    """runMCMC(mcmc, niter, nburnin, thin, inits, nchains, setSeed): P/R/MCMC_run.R:82-213.
+
+    inits: a dict (same values for every chain), a list of nchains dicts, or a callable returning a dict,
+    evaluated once per chain in chain order exactly as the reference does (MCMC_run.R:135-142).
+    setSeed: False, True (seed 0, per-chain streams keyed by chain index) or an int seed."""
+    if getattr(mcmc, "name", None) != "MCMC":
+        raise TypeError("mcmc argument must be a NIMBLE MCMC algorithm")
+    if not isinstance(mcmc, CompiledMCMC):
+        raise TypeError("mcmc argument must be a *compiled* NIMBLE MCMC algorithm")
+    if isinstance(inits, (list, tuple)) and len(inits) != nchains and len(inits) != 1:
+        raise ValueError("inits list must be of length nchains")
+    seed = 0 if setSeed in (False, True, None) else int(setSeed)
+    if setSeed is False:
+        seed = int(np.random.SeedSequence().entropy % (1 << 63))
+    rows = []
+    for i in range(nchains):
+        if callable(inits):
+            these = inits()
+        elif isinstance(inits, (list, tuple)):
+            these = inits[i if len(inits) > 1 else 0]
+        else:
+            these = inits
+        rows.append(mcmc.model.init_vector(these))
+    samples = mcmc.run_chains(np.stack(rows), niter, nburnin, thin, True, seed)
+    mats = [SampleMatrix(samples[c], mcmc.colnames) for c in range(nchains)]
+    result = mats[0] if nchains == 1 else {"chain%d" % (c + 1): mats[c] for c in range(nchains)}
+    if summary:
+        from .ess import samples_summary
+        allc = np.concatenate(mats, axis=0)
+        summ = samples_summary(allc, mcmc.colnames)
+        return {"samples": result, "summary": summ}
+    return result

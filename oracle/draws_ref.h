@@ -1,0 +1,18 @@
+/* draws_ref.h -- TEST INFRASTRUCTURE (parity oracle); see draws_ref.c */
+#ifndef DRAWS_REF_H
+#define DRAWS_REF_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+void ref_unif2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t k,
+               double *u1, double *u2);
+void ref_normal2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t k,
+                 double *z0, double *z1);
+double ref_rgamma(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a);
+double ref_det_log(double x);
+double ref_det_exp(double x);
+#ifdef __cplusplus
+}
+#endif
+#endif
