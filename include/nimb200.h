@@ -249,6 +249,12 @@ int nimb200_mcmc_last_timing(nimb200_model *m, double *ms_out, int64_t *launches
  * what: 0 scale [T][C]; 1 timesAdapted [T][C]; 2 propCov [d*d][C] (RW_block). */
 int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, double *out, int64_t cap);
 
+/* measurement hooks for bench.py (no counterpart in the reference, whose only profiling hook is
+ * run(time=TRUE), MCMC_build.R:281-285): average device milliseconds of one launch of the block-sum kernel
+ * behind nimb200_calculate(decl, whole range), and live FP64 peaks (DFMA loop, FP64 mma.sync loop). */
+int nimb200_time_calculate(nimb200_model *m, int32_t decl, int32_t reps, double *ms_avg);
+int nimb200_measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflops);
+
 /* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1) or gamma(shape a, scale 1)
  * variates (kind 2) that sampler `sampler` would consume on the device for (chain, iter, target), so the
  * host can replay identical draws into another implementation. */

@@ -60,6 +60,8 @@ class Backend:
                                    C.c_int32, _dp])
         if has_device:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
+            self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
+            self._peaks = fn("measure_fp64_peaks", [C.c_int, _dp, _dp])
 
     def check(self, rc):
         if rc != 0:
@@ -73,6 +75,11 @@ class Backend:
         else:
             self.check(self._create(C.byref(packed_table), nchains, first_chain, C.byref(h)))
         return h
+
+    def fp64_peaks(self, device=0):
+        a, b = C.c_double(), C.c_double()
+        self.check(self._peaks(device, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def draws(self, seed, chain, it, sampler, target, kind, a, n):
         out = np.empty(n)
@@ -150,6 +157,11 @@ class DeviceModel:
         out = np.empty(n)
         self.backend.check(self.backend._sstate(self.h, sampler, what, _ptr(out), n))
         return out.reshape(-1, self.C)
+
+    def time_calculate(self, decl, reps=5):
+        ms = C.c_double()
+        self.backend.check(self.backend._time_calc(self.h, decl, reps, C.byref(ms)))
+        return ms.value
 
     def last_timing(self):
         ms, k = C.c_double(), C.c_int64()

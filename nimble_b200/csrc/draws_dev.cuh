@@ -1,0 +1,178 @@
+// draws_dev.cuh -- counter-based random draws (DESIGN.md "draws"): Philox4x32-10 keyed by (seed, chain),
+// counter (iteration, sampler, target, call).  Replaces the reference's use of R's global RNG
+// (unif_rand / norm_rand, P/inst/CppCode/Utils.cpp:61, dists.cpp:954,1155; rgamma in the generated conjugate
+// samplers, P/R/MCMC_conjugacy.R:1100): one independent, reproducible stream per chain, no shared state.
+//
+// Every floating-point step is written with round-to-nearest intrinsics (__dadd_rn, __dmul_rn, __fma_rn,
+// __ddiv_rn, __dsqrt_rn) so the compiler can neither fuse nor reorder them: a host implementation that
+// performs the same IEEE operations produces bit-identical normals, uniforms and gamma variates.
+#pragma once
+#include <cstdint>
+
+namespace nimb {
+
+struct DrawKey {
+  uint64_t seed;
+  uint32_t chain;    // global chain index
+  uint64_t iter;
+  uint32_t sampler;
+  uint32_t target;
+};
+
+__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0;
+    uint32_t n1 = (uint32_t)p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    uint32_t n3 = (uint32_t)p0;
+    c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+}
+
+__device__ __forceinline__ double bits2unif(uint32_t lo, uint32_t hi) {
+  uint64_t m = (((uint64_t)hi << 32) | lo) >> 12;
+  return __dmul_rn(__dadd_rn((double)m, 0.5), 2.220446049250313e-16);
+}
+
+__device__ __forceinline__ void unif2(const DrawKey& k, uint32_t call, double& u1, double& u2) {
+  uint32_t c[4];
+  c[0] = (uint32_t)k.iter;
+  c[1] = (k.sampler & 0xffffu) | ((uint32_t)((k.iter >> 32) & 0xffffu) << 16);
+  c[2] = k.target;
+  c[3] = call;
+  philox4x32_10(c, (uint32_t)k.seed, (uint32_t)(k.seed >> 32) ^ k.chain);
+  u1 = bits2unif(c[0], c[1]);
+  u2 = bits2unif(c[2], c[3]);
+}
+
+__device__ __forceinline__ double det_log(double x) {
+  uint64_t b = (uint64_t)__double_as_longlong(x);
+  int e = (int)(b >> 52) - 1023;
+  double m = __longlong_as_double((long long)((b & 0xFFFFFFFFFFFFFull) | 0x3FF0000000000000ull));
+  if (m > 1.4142135623730951) { m = __dmul_rn(m, 0.5); e += 1; }
+  double f = __dadd_rn(m, -1.0);
+  double s = __ddiv_rn(f, __dadd_rn(m, 1.0));
+  double z = __dmul_rn(s, s);
+  double p = 1.0 / 23.0;
+  p = __fma_rn(p, z, 1.0 / 21.0);
+  p = __fma_rn(p, z, 1.0 / 19.0);
+  p = __fma_rn(p, z, 1.0 / 17.0);
+  p = __fma_rn(p, z, 1.0 / 15.0);
+  p = __fma_rn(p, z, 1.0 / 13.0);
+  p = __fma_rn(p, z, 1.0 / 11.0);
+  p = __fma_rn(p, z, 1.0 / 9.0);
+  p = __fma_rn(p, z, 1.0 / 7.0);
+  p = __fma_rn(p, z, 1.0 / 5.0);
+  p = __fma_rn(p, z, 1.0 / 3.0);
+  p = __fma_rn(p, z, 1.0);
+  double t = __dmul_rn(s, p);
+  return __fma_rn((double)e, 0.6931471805599453, __dmul_rn(2.0, t));
+}
+
+__device__ __forceinline__ double det_exp(double x) {
+  if (x < -700.0) return 0.0;
+  double kd = rint(__dmul_rn(x, 1.4426950408889634));
+  double r = __fma_rn(-kd, 6.93147180369123816490e-01, x);
+  r = __fma_rn(-kd, 1.90821492927058770002e-10, r);
+  double p = 1.0 / 87178291200.0;
+  p = __fma_rn(p, r, 1.0 / 6227020800.0);
+  p = __fma_rn(p, r, 1.0 / 479001600.0);
+  p = __fma_rn(p, r, 1.0 / 39916800.0);
+  p = __fma_rn(p, r, 1.0 / 3628800.0);
+  p = __fma_rn(p, r, 1.0 / 362880.0);
+  p = __fma_rn(p, r, 1.0 / 40320.0);
+  p = __fma_rn(p, r, 1.0 / 5040.0);
+  p = __fma_rn(p, r, 1.0 / 720.0);
+  p = __fma_rn(p, r, 1.0 / 120.0);
+  p = __fma_rn(p, r, 1.0 / 24.0);
+  p = __fma_rn(p, r, 1.0 / 6.0);
+  p = __fma_rn(p, r, 0.5);
+  p = __fma_rn(p, r, 1.0);
+  p = __fma_rn(p, r, 1.0);
+  return __dmul_rn(p, __longlong_as_double((long long)((uint64_t)((long long)kd + 1023) << 52)));
+}
+
+__device__ __forceinline__ void det_sincos2pi(double u, double& s, double& c) {
+  double a = __dmul_rn(u, 8.0);
+  int o = (int)a;
+  double f = __dadd_rn(a, -(double)o);
+  double th = __dmul_rn(f, 0.7853981633974483);
+  double z = __dmul_rn(th, th);
+  double ps = 1.0 / 355687428096000.0;
+  ps = __fma_rn(ps, z, -1.0 / 1307674368000.0);
+  ps = __fma_rn(ps, z, 1.0 / 6227020800.0);
+  ps = __fma_rn(ps, z, -1.0 / 39916800.0);
+  ps = __fma_rn(ps, z, 1.0 / 362880.0);
+  ps = __fma_rn(ps, z, -1.0 / 5040.0);
+  ps = __fma_rn(ps, z, 1.0 / 120.0);
+  ps = __fma_rn(ps, z, -1.0 / 6.0);
+  ps = __fma_rn(ps, z, 1.0);
+  double sn = __dmul_rn(th, ps);
+  double pc = -1.0 / 6402373705728000.0;
+  pc = __fma_rn(pc, z, 1.0 / 20922789888000.0);
+  pc = __fma_rn(pc, z, -1.0 / 87178291200.0);
+  pc = __fma_rn(pc, z, 1.0 / 479001600.0);
+  pc = __fma_rn(pc, z, -1.0 / 3628800.0);
+  pc = __fma_rn(pc, z, 1.0 / 40320.0);
+  pc = __fma_rn(pc, z, -1.0 / 720.0);
+  pc = __fma_rn(pc, z, 1.0 / 24.0);
+  pc = __fma_rn(pc, z, -0.5);
+  pc = __fma_rn(pc, z, 1.0);
+  double cs = pc;
+  if (o & 1) {
+    double s2 = __dmul_rn(__dadd_rn(sn, cs), 0.7071067811865476);
+    double c2 = __dmul_rn(__dadd_rn(cs, -sn), 0.7071067811865476);
+    sn = s2; cs = c2;
+  }
+  double t;
+  switch (o >> 1) {
+    case 0: break;
+    case 1: t = sn; sn = cs; cs = -t; break;
+    case 2: sn = -sn; cs = -cs; break;
+    default: t = sn; sn = -cs; cs = t; break;
+  }
+  s = sn; c = cs;
+}
+
+__device__ __forceinline__ void normal2(const DrawKey& k, uint32_t call, double& z0, double& z1) {
+  double u1, u2, s, c;
+  unif2(k, call, u1, u2);
+  double r = __dsqrt_rn(__dmul_rn(-2.0, det_log(u1)));
+  det_sincos2pi(u2, s, c);
+  z0 = __dmul_rn(r, c);
+  z1 = __dmul_rn(r, s);
+}
+
+// Marsaglia-Tsang gamma(a, 1): call 0 = boost uniform (a < 1), trip m: normal = call 1+2m, uniform = call 2+2m.
+__device__ __forceinline__ double rgamma1(const DrawKey& k, double a) {
+  double boost = 1.0, u, dummy, x, v;
+  if (!(a > 0.0) || !isfinite(a)) return NAN;
+  if (a < 1.0) {
+    unif2(k, 0, u, dummy);
+    boost = det_exp(__ddiv_rn(det_log(u), a));
+    a = __dadd_rn(a, 1.0);
+  }
+  double d = __dadd_rn(a, -(1.0 / 3.0));
+  double c = __ddiv_rn(1.0 / 3.0, __dsqrt_rn(d));
+  v = 1.0;
+  for (int m = 0; m < 64; m++) {
+    normal2(k, 1 + 2 * m, x, dummy);
+    v = __dadd_rn(1.0, __dmul_rn(c, x));
+    if (v <= 0.0) continue;
+    v = __dmul_rn(__dmul_rn(v, v), v);
+    unif2(k, 2 + 2 * m, u, dummy);
+    double x2 = __dmul_rn(x, x);
+    if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) break;
+    double lhs = det_log(u);
+    double rhs = __dadd_rn(__dmul_rn(0.5, x2), __dmul_rn(d, __dadd_rn(__dadd_rn(1.0, -v), det_log(v))));
+    if (lhs < rhs) break;
+  }
+  return __dmul_rn(__dmul_rn(d, v), boost);
+}
+
+}  // namespace nimb

@@ -1,0 +1,1271 @@
+// engine.cu -- node-table interpreter kernels, samplers, MCMC driver and the C ABI (include/nimb200.h).
+//
+// Replaces, for the sampling path, the reference's per-node virtual dispatch
+//   calculate / calculateDiff / getLogProb loops    P/inst/CppCode/accessorClasses.cpp:49-57, 237-264
+//   nimCopy model <-> mvSaved                        P/inst/CppCode/accessorClasses.cpp:549-572
+//   sampler_RW / RW_block / binary / conjugate       P/R/MCMC_samplers.R, P/R/MCMC_conjugacy.R
+//   MCMC::run                                        P/R/MCMC_build.R:217-321
+// with kernels that advance ALL chains at once over chain-major state.
+//
+// Two execution shapes:
+//   sweep  one thread per (target, chain): the whole scalar sampler step, sequential over that target's
+//          dependents (many conditionally independent targets, or few dependents);
+//   wide   one target per chain with a large dependent set: (node tile x chain tile) blocks evaluate the
+//          dependents, per-chain partial sums go to scratch and are reduced in fixed order, then a per-chain
+//          kernel decides / commits.  Per-dependency block sums of the current state are cached so an MH
+//          step costs one pass over the dependents, like calculateDiff against stored logProbs.
+//
+// Compiled with -fmad=false: a*b+c stays two roundings, as in the reference's x86-64 build.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <set>
+#include "draws_dev.cuh"
+#include "engine.cuh"
+#include "nmath_dev.cuh"
+
+using namespace nimb;
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+static int fail(const std::string& s) { g_err = s; return 1; }
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      char b_[512];                                                                           \
+      snprintf(b_, sizeof b_, "CUDA error %s at %s:%d", cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return fail(b_);                                                                        \
+    }                                                                                         \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------------ interpreter
+__device__ __forceinline__ int idx_of(const DevTab& T, int mode, int arg, int i) {
+  switch (mode) {
+    case NIMB_IDX_I: return i;
+    case NIMB_IDX_DIV: return i / arg;
+    case NIMB_IDX_MOD: return i % arg;
+    default: return T.iarr[arg][i];
+  }
+}
+
+__device__ __forceinline__ double ld_state(const DevTab& T, int slot, int c, int ov_slot, double ov_val) {
+  return slot == ov_slot ? ov_val : T.state[(size_t)slot * T.C + c];
+}
+
+__device__ double eval_prog(const DevTab& T, int c, int off, int len, int i, int j, int ov_slot, double ov_val) {
+  double stk[16];
+  int sp = 0;
+  const nimb200_op* ops = T.ops + off;
+  for (int q = 0; q < len; q++) {
+    const nimb200_op o = ops[q];
+    switch (o.op) {
+      case NIMB_OP_CONST: stk[sp++] = o.k; break;
+      case NIMB_OP_DATA: stk[sp++] = T.darr[o.a][idx_of(T, o.b, o.c, i)]; break;
+      case NIMB_OP_CVAR: stk[sp++] = ld_state(T, o.a, c, ov_slot, ov_val); break;
+      case NIMB_OP_CVARN: stk[sp++] = ld_state(T, o.a + idx_of(T, o.b, o.c, i), c, ov_slot, ov_val); break;
+      case NIMB_OP_INPROD: {
+        const double* x = T.darr[o.a] + (size_t)i * o.c;
+        int p = (int)o.k;
+        double s = 0.0;
+        for (int jj = 0; jj < p; jj++) s += x[jj] * ld_state(T, o.b + jj, c, ov_slot, ov_val);
+        stk[sp++] = s;
+        break;
+      }
+      case NIMB_OP_DATAJ: stk[sp++] = T.darr[o.a][(size_t)i * o.c + j]; break;
+      case NIMB_OP_CVARJ: stk[sp++] = ld_state(T, o.a + j, c, ov_slot, ov_val); break;
+      case NIMB_OP_ADD: sp--; stk[sp - 1] = stk[sp - 1] + stk[sp]; break;
+      case NIMB_OP_SUB: sp--; stk[sp - 1] = stk[sp - 1] - stk[sp]; break;
+      case NIMB_OP_MUL: sp--; stk[sp - 1] = stk[sp - 1] * stk[sp]; break;
+      case NIMB_OP_DIV: sp--; stk[sp - 1] = stk[sp - 1] / stk[sp]; break;
+      case NIMB_OP_POW: sp--; stk[sp - 1] = pow(stk[sp - 1], stk[sp]); break;
+      case NIMB_OP_NEG: stk[sp - 1] = -stk[sp - 1]; break;
+      case NIMB_OP_EXP: stk[sp - 1] = exp(stk[sp - 1]); break;
+      case NIMB_OP_LOG: stk[sp - 1] = log(stk[sp - 1]); break;
+      case NIMB_OP_SQRT: stk[sp - 1] = sqrt(stk[sp - 1]); break;
+      case NIMB_OP_ILOGIT: stk[sp - 1] = 1. / (1. + exp(-stk[sp - 1])); break;
+      case NIMB_OP_LOGIT: stk[sp - 1] = log(stk[sp - 1] / (1. - stk[sp - 1])); break;
+      case NIMB_OP_INV: stk[sp - 1] = 1. / stk[sp - 1]; break;
+      case NIMB_OP_SQ: stk[sp - 1] = stk[sp - 1] * stk[sp - 1]; break;
+      case NIMB_OP_ABS: stk[sp - 1] = fabs(stk[sp - 1]); break;
+      case NIMB_OP_LOG1P: stk[sp - 1] = log1p(stk[sp - 1]); break;
+      case NIMB_OP_ICLOGLOG: stk[sp - 1] = 1. - exp(-exp(stk[sp - 1])); break;
+      case NIMB_OP_STEP: stk[sp - 1] = stk[sp - 1] >= 0 ? 1. : 0.; break;
+      default: return NAN;
+    }
+  }
+  return stk[0];
+}
+
+__device__ __forceinline__ double node_value(const DevTab& T, const nimb200_decl& d, int i, int c, int ov_slot,
+                                             double ov_val) {
+  return d.value_kind ? ld_state(T, d.value_ref + i, c, ov_slot, ov_val) : T.darr[d.value_ref][i];
+}
+
+// getParam_0D_double (accessorClasses.h:210-224): canonical parameter or one of the derived alternatives
+__device__ double get_param(const DevTab& T, int di, int i, int c, int code, int ov_slot, double ov_val) {
+  const nimb200_decl& d = T.decl[di];
+  if (code < NIMB200_MAX_PARAM) return eval_prog(T, c, d.prog_off[code], d.prog_len[code], i, 0, ov_slot, ov_val);
+  double p1 = eval_prog(T, c, d.prog_off[1], d.prog_len[1], i, 0, ov_slot, ov_val);
+  if (code == NIMB_PARAM_RATE) return 1.0 / p1;
+  if (code == NIMB_PARAM_TAU) return pow(p1, -2.0);
+  return NAN;
+}
+
+// one nodeFunction::calculate body: d<dist>(value, params, log = 1)
+__device__ double calc_node(const DevTab& T, int di, int i, int c, int ov_slot, double ov_val) {
+  const nimb200_decl& d = T.decl[di];
+  double x = node_value(T, d, i, c, ov_slot, ov_val);
+  if (d.dist == NIMB_DCAT) {  // P/inst/CppCode/dists.cpp:914-934
+    int K = d.fam_arg[0];
+    double sum = 0.0, sel = 0.0;
+    bool anynan = isnan(x), anyneg = false;
+    int xi = isnan(x) ? 0 : (int)nearbyint(x);
+    for (int j = 0; j < K; j++) {
+      double pj = eval_prog(T, c, d.prog_off[0], d.prog_len[0], i, j, ov_slot, ov_val);
+      anynan |= isnan(pj);
+      anyneg |= pj < 0;
+      sum += pj;
+      if (j == xi - 1) sel = pj;
+    }
+    if (anynan || anyneg) return NAN;
+    if (r_nonint(x)) return -INFINITY;
+    x = nearbyint(x);
+    if (x > K || x < 1) return -INFINITY;
+    return log(sel) - log(sum);
+  }
+  double p0 = eval_prog(T, c, d.prog_off[0], d.prog_len[0], i, 0, ov_slot, ov_val), p1 = 0;
+  if (d.nparam > 1) p1 = eval_prog(T, c, d.prog_off[1], d.prog_len[1], i, 0, ov_slot, ov_val);
+  switch (d.dist) {
+    case NIMB_DNORM: return dnorm(x, p0, p1);
+    case NIMB_DGAMMA: return dgamma(x, p0, p1);
+    case NIMB_DPOIS: return dpois(x, p0);
+    case NIMB_DBINOM: return dbinom(x, p0, p1);
+    case NIMB_DBETA: return dbeta(x, p0, p1);
+    case NIMB_DLOGIS: return dlogis(x, p0, p1);
+    case NIMB_DEXP: return dexp_nimble(x, p0);
+  }
+  return NAN;
+}
+
+struct Sel { int lo, hi; const int32_t* idx; };
+__device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, int t) {
+  Sel s; s.idx = nullptr;
+  switch (dp.sel) {
+    case NIMB_SEL_ALL: s.lo = 0; s.hi = T.decl[dp.decl].n; break;
+    case NIMB_SEL_SAME: s.lo = dp.a + t; s.hi = s.lo + 1; break;
+    case NIMB_SEL_STRIDE: s.lo = t * dp.a; s.hi = s.lo + dp.a; break;
+    case NIMB_SEL_SEG: s.lo = T.iarr[dp.a][t]; s.hi = T.iarr[dp.a][t + 1]; break;
+    case NIMB_SEL_CSR: s.lo = T.iarr[dp.a][t]; s.hi = T.iarr[dp.a][t + 1]; s.idx = T.iarr[dp.b]; break;
+    default: s.lo = dp.a; s.hi = dp.b; break;
+  }
+  return s;
+}
+
+// conjugate contribution of one dependent node (P/R/MCMC_conjugacy.R:80-93, 109-115; probing :766-820)
+__device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep& dp, int node, int c, int slot, bool gam,
+                                             double& c0, double& c1) {
+  const nimb200_decl& dd = T.decl[dp.decl];
+  double value = node_value(T, dd, node, c, -1, 0.0);
+  double par = 0, offset = 0, coeff = 1;
+  if (dd.dist == NIMB_DNORM) par = gam ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
+  else if (dd.dist == NIMB_DGAMMA) par = get_param(T, dp.decl, node, c, 0, -1, 0.0);
+  if (dp.link == NIMB_LINK_ADDITIVE || dp.link == NIMB_LINK_LINEAR) offset = get_param(T, dp.decl, node, c, dp.param, slot, 0.0);
+  if (dp.link == NIMB_LINK_LINEAR) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0) - offset;
+  if (dp.link == NIMB_LINK_MULTIPLICATIVE) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0);
+  if (gam) {
+    if (dd.dist == NIMB_DPOIS) { c0 += value; c1 += coeff; }
+    else if (dd.dist == NIMB_DGAMMA) { c0 += par; c1 += coeff * value; }
+    else if (dd.dist == NIMB_DEXP) { c0 += 1.0; c1 += coeff * value; }
+    else if (dd.dist == NIMB_DNORM) { c0 += 1. / 2; c1 += coeff / 2 * ((value - par) * (value - par)); }
+  } else {
+    c0 += coeff * (value - offset) * par;
+    c1 += coeff * coeff * par;
+  }
+}
+
+__device__ __forceinline__ DrawKey make_key(const DevTab& T, uint64_t seed, uint64_t iter, int sid, int t, int c) {
+  DrawKey k; k.seed = seed; k.chain = (uint32_t)(T.first_chain + c); k.iter = iter; k.sampler = (uint32_t)sid; k.target = (uint32_t)t;
+  return k;
+}
+
+// decide(): P/inst/CppCode/Utils.cpp:54-63 (the uniform is only consulted when it is needed)
+__device__ __forceinline__ bool decide(double lMHr, const DrawKey& k, uint32_t call) {
+  if (isnan(lMHr)) return false;
+  if (lMHr > 0) return true;
+  double u, u2;
+  unif2(k, call, u, u2);
+  return u < exp(lMHr);
+}
+
+// sampler_RW::adaptiveProcedure, P/R/MCMC_samplers.R:388-420
+__device__ __forceinline__ void rw_adapt(const nimb200_sampler& sp, const SamplerDev& S, size_t q, bool jump) {
+  int ran = S.timesRan[q] + 1, acc = S.timesAccepted[q] + (jump ? 1 : 0);
+  if (ran % sp.adapt_interval == 0) {
+    double acceptanceRate = (double)acc / (double)ran;
+    int adapted = S.timesAdapted[q] + 1;
+    S.timesAdapted[q] = adapted;
+    double gamma1 = 1 / pow((double)adapted + 3, sp.adapt_factor_exponent);
+    double gamma2 = 10 * gamma1;
+    double adaptFactor = exp(gamma2 * (acceptanceRate - 0.44));
+    double sc = S.scale[q] * adaptFactor;
+    if (sp.reflective && sc >= 0.5 * (sp.upper - sp.lower)) sc = 0.5 * (sp.upper - sp.lower);
+    S.scale[q] = sc;
+    ran = 0; acc = 0;
+  }
+  S.timesRan[q] = ran;
+  S.timesAccepted[q] = acc;
+}
+
+__device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double cur, double scale, double z, double& propLogScale) {
+  double prop;
+  propLogScale = 0;
+  if (sp.log_scale) {
+    propLogScale = 0.0 + scale * z;
+    prop = cur * exp(propLogScale);
+  } else
+    prop = cur + scale * z;
+  if (sp.reflective) {
+    while (prop < sp.lower || prop > sp.upper) {
+      if (prop < sp.lower) prop = 2 * sp.lower - prop;
+      if (prop > sp.upper) prop = 2 * sp.upper - prop;
+    }
+  }
+  return prop;
+}
+
+// ------------------------------------------------------------------------------------------------ sweep kernels
+// One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
+// 32 lanes of a warp read the same data node and 32 consecutive chain copies of each state slot.
+__global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S) {
+  const nimb200_sampler sp = T.samplers[sid];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = (int)(gid % T.C);
+  size_t tq = gid / T.C;
+  if (tq >= (size_t)sp.n_targets) return;
+  int t = (int)tq;
+  int slot = sp.target_slot + t;
+  size_t q = (size_t)t * T.C + c;
+  DrawKey key = make_key(T, seed, iter, sid, t, c);
+  double* sv = T.state + (size_t)slot * T.C + c;
+  double cur = *sv;
+
+  if (sp.type == NIMB_SAMPLER_RW) {  // MCMC_samplers.R:352-386
+    double z, z1, propLogScale;
+    normal2(key, 0, z, z1);
+    double prop = rw_proposal(sp, cur, S.scale[q], z, propLogScale);
+    double lp0 = 0, lp1 = 0;
+    for (int e = 0; e < sp.n_dep; e++) {
+      const nimb200_dep dp = T.deps[sp.dep_off + e];
+      Sel s = sel_of(T, dp, t);
+      for (int k = s.lo; k < s.hi; k++) {
+        int node = s.idx ? s.idx[k] : k;
+        double nw = calc_node(T, dp.decl, node, c, slot, prop);
+        double od = calc_node(T, dp.decl, node, c, -1, 0.0);
+        if (dp.stage == 0) lp0 += nw - od; else lp1 += nw - od;
+      }
+    }
+    bool jump;
+    if (lp0 == -INFINITY) jump = false;
+    else jump = decide(lp0 + lp1 + propLogScale, key, 1);
+    if (jump) *sv = prop;
+    if (sp.adaptive) rw_adapt(sp, S, q, jump);
+    return;
+  }
+  if (sp.type == NIMB_SAMPLER_BINARY) {  // MCMC_samplers.R:127-151
+    double other = 1 - cur;
+    double currentLogProb = 0, otherPrior = 0, otherDeps = 0;
+    for (int e = 0; e < sp.n_dep; e++) {
+      const nimb200_dep dp = T.deps[sp.dep_off + e];
+      Sel s = sel_of(T, dp, t);
+      for (int k = s.lo; k < s.hi; k++) {
+        int node = s.idx ? s.idx[k] : k;
+        currentLogProb += calc_node(T, dp.decl, node, c, -1, 0.0);
+        double o = calc_node(T, dp.decl, node, c, slot, other);
+        if (dp.stage == 0) otherPrior += o; else otherDeps += o;
+      }
+    }
+    double otherLogProb = (otherPrior == -INFINITY) ? otherPrior : otherPrior + otherDeps;
+    double acceptanceProb = 1 / (exp(currentLogProb - otherLogProb) + 1);
+    double u, u2;
+    unif2(key, 0, u, u2);
+    bool jump = (!isnan(acceptanceProb)) & (u < acceptanceProb);
+    if (jump) *sv = other;
+    return;
+  }
+  // conjugate: MCMC_conjugacy.R:651-692
+  bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  const nimb200_dep tp = T.deps[sp.dep_off];
+  int tnode = sel_of(T, tp, t).lo;
+  double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+  double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
+  double c0 = 0, c1 = 0;
+  for (int e = 0; e < sp.n_dep; e++) {
+    const nimb200_dep dp = T.deps[sp.dep_off + e];
+    if (dp.stage != 1) continue;
+    Sel s = sel_of(T, dp, t);
+    for (int k = s.lo; k < s.hi; k++) conj_contrib(T, dp, s.idx ? s.idx[k] : k, c, slot, gam, c0, c1);
+  }
+  double nv;
+  if (gam) {
+    double shape = prior0 + c0, scale = 1 / (prior1 + c1);
+    nv = rgamma1(key, shape) * scale;
+  } else {
+    double mean = (prior0 * prior1 + c0) / (prior1 + c1), sd = pow(prior1 + c1, -0.5), z, z1;
+    normal2(key, 0, z, z1);
+    nv = mean + sd * z;
+  }
+  *sv = nv;
+}
+
+// ------------------------------------------------------------------------------------------------ wide kernels
+// (node tile x chain tile) evaluation of instances [lo,hi) (through idx if given) of one declaration.
+// MODE 0: per-chain partial sums of log-densities -> partials[tile][C]
+// MODE 1: per-node log-densities -> out_nodes[(k-lo)*C + c]
+// MODE 2: conjugate contributions (two sums)     -> partials[tile][2][C]
+template <int MODE>
+__global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int cw_log2, int npt, double* partials,
+                       double* out_nodes, nimb200_dep dp, int slot, int gam) {
+  extern __shared__ double sh[];
+  int cw = 1 << cw_log2, nl = blockDim.x >> cw_log2;
+  int lane_c = threadIdx.x & (cw - 1), lane_n = threadIdx.x >> cw_log2;
+  int c = blockIdx.y * cw + lane_c;
+  int tile0 = lo + blockIdx.x * (nl * npt);
+  double a0 = 0, a1 = 0;
+  if (c < T.C) {
+    for (int q = 0; q < npt; q++) {
+      int k = tile0 + q * nl + lane_n;
+      if (k >= hi) break;
+      int node = idx ? idx[k] : k;
+      if (MODE == 0) a0 += calc_node(T, di, node, c, -1, 0.0);
+      else if (MODE == 1) out_nodes[(size_t)(k - lo) * T.C + c] = calc_node(T, di, node, c, -1, 0.0);
+      else conj_contrib(T, dp, node, c, slot, gam != 0, a0, a1);
+    }
+  }
+  if (MODE == 1) return;
+  sh[threadIdx.x] = a0;
+  if (MODE == 2) sh[blockDim.x + threadIdx.x] = a1;
+  __syncthreads();
+  if (lane_n == 0 && c < T.C) {
+    double s0 = 0, s1 = 0;
+    for (int j = 0; j < nl; j++) {
+      s0 += sh[(j << cw_log2) + lane_c];
+      if (MODE == 2) s1 += sh[blockDim.x + (j << cw_log2) + lane_c];
+    }
+    if (MODE == 0) partials[(size_t)blockIdx.x * T.C + c] = s0;
+    else {
+      partials[((size_t)blockIdx.x * 2) * T.C + c] = s0;
+      partials[((size_t)blockIdx.x * 2 + 1) * T.C + c] = s1;
+    }
+  }
+}
+
+// fixed-order reduction of the tile partials: dst[k][c] = sum_b partials[b][k][c]
+__global__ void k_reduce(const double* partials, int nb, int K, int C, double* dst0, double* dst1) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  for (int kk = 0; kk < K; kk++) {
+    double s = 0;
+    for (int b = 0; b < nb; b++) s += partials[((size_t)b * K + kk) * C + c];
+    (kk == 0 ? dst0 : dst1)[c] = s;
+  }
+}
+
+// wide RW: proposal for every chain; the old value is parked in tsave
+__global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* tsave, double* pls) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_sampler sp = T.samplers[sid];
+  DrawKey key = make_key(T, seed, iter, sid, 0, c);
+  double* sv = T.state + (size_t)sp.target_slot * T.C + c;
+  double z, z1, propLogScale;
+  normal2(key, 0, z, z1);
+  double cur = *sv;
+  tsave[c] = cur;
+  *sv = rw_proposal(sp, cur, S.scale[c], z, propLogScale);
+  pls[c] = propLogScale;
+}
+
+// wide RW_block: rmnorm_chol(values, chol_propCov_scale, prec_param = 0), dists.cpp:1132-1164
+__global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, int tr, SamplerDev S, double* tsave) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_sampler sp = T.samplers[sid];
+  int d = sp.d, npair = (d + 1) / 2;
+  DrawKey key = make_key(T, seed, iter, sid, 0, c);
+  double x[NIMB200_MAX_BLOCK_D];
+  for (int j = 0; j < npair; j++) {
+    double z0, z1;
+    normal2(key, tr * (npair + 1) + j, z0, z1);
+    x[2 * j] = z0;
+    if (2 * j + 1 < d) x[2 * j + 1] = z1;
+  }
+  const double* U = S.cholScale;
+  for (int j = d - 1; j >= 0; j--) {  // x := U^T x in the reference-BLAS dtrmv('U','T','N') order
+    double temp = x[j] * U[(size_t)(j + j * d) * T.C + c];
+    for (int i = j - 1; i >= 0; i--) temp += U[(size_t)(i + j * d) * T.C + c] * x[i];
+    x[j] = temp;
+  }
+  for (int j = 0; j < d; j++) {
+    double* sv = T.state + (size_t)(sp.target_slot + j) * T.C + c;
+    double cur = *sv;
+    tsave[(size_t)j * T.C + c] = cur;
+    *sv = x[j] + cur;
+  }
+}
+
+// wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
+__global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
+                            double* depcache, const double* tsave, const double* pls) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_sampler sp = T.samplers[sid];
+  DrawKey key = make_key(T, seed, iter, sid, 0, c);
+  double lp0 = 0, lp1 = 0;
+  for (int e = 0; e < sp.n_dep; e++) {
+    double diff = newsum[(size_t)e * T.C + c] - depcache[(size_t)(sp.dep_off + e) * T.C + c];
+    if (T.deps[sp.dep_off + e].stage == 0) lp0 += diff; else lp1 += diff;
+  }
+  bool jump;
+  if (lp0 == -INFINITY) jump = false;
+  else jump = decide(lp0 + lp1 + (pls ? pls[c] : 0.0), key, call);
+  int d = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1;
+  if (jump) {
+    for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)(sp.dep_off + e) * T.C + c] = newsum[(size_t)e * T.C + c];
+  } else {
+    for (int j = 0; j < d; j++) T.state[(size_t)(sp.target_slot + j) * T.C + c] = tsave[(size_t)j * T.C + c];
+  }
+  if (!sp.adaptive) return;
+  if (sp.type == NIMB_SAMPLER_RW) { rw_adapt(sp, S, c, jump); return; }
+  // RW_block adaptiveProcedure, first half (MCMC_samplers.R:716-722); the covariance step is k_block_adapt
+  int ran = S.timesRan[c] + 1;
+  S.timesRan[c] = ran;
+  if (jump) S.timesAccepted[c] += 1;
+  if (!sp.adapt_scale_only)
+    for (int j = 0; j < d; j++)
+      S.empirSamp[((size_t)(ran - 1) + (size_t)j * sp.adapt_interval) * T.C + c] = T.state[(size_t)(sp.target_slot + j) * T.C + c];
+}
+
+// RW_block adaptation every adaptInterval iterations: one block per chain (MCMC_samplers.R:723-756,
+// calcAdaptationFactor MCMC_utils.R:177-205).  Loop orders match the oracle so results are bit-identical.
+__global__ void k_block_adapt(DevTab T, int sid, SamplerDev S) {
+  __shared__ double U[NIMB200_MAX_BLOCK_D * NIMB200_MAX_BLOCK_D];  // propCov, overwritten in place by its upper factor
+  __shared__ double s_gamma1, s_scale, s_diag;
+  const nimb200_sampler sp = T.samplers[sid];
+  int c = blockIdx.x, d = sp.d, AI = sp.adapt_interval, C = T.C;
+  int tid = threadIdx.x, nt = blockDim.x;
+  if (tid == 0) {
+    const double optAR[5] = {0.44, 0.35, 0.32, 0.25, 0.234};
+    int ran = S.timesRan[c];
+    double acceptanceRate = (double)S.timesAccepted[c] / (double)ran;
+    int adapted = S.timesAdapted[c] + 1;
+    S.timesAdapted[c] = adapted;
+    double gamma1 = 1 / pow((double)adapted + 3, sp.adapt_factor_exponent);
+    double adaptFactor = exp(10 * gamma1 * (acceptanceRate - optAR[d > 5 ? 4 : d - 1]));
+    s_gamma1 = gamma1;
+    s_scale = S.scale[c] * adaptFactor;
+    S.scale[c] = s_scale;
+  }
+  __syncthreads();
+  if (!sp.adapt_scale_only) {
+    for (int j = tid; j < d; j += nt) {  // centre the columns of empirSamp
+      double mu = 0;
+      for (int r = 0; r < AI; r++) mu += S.empirSamp[((size_t)r + (size_t)j * AI) * C + c];
+      mu = mu / AI;
+      for (int r = 0; r < AI; r++) S.empirSamp[((size_t)r + (size_t)j * AI) * C + c] -= mu;
+    }
+    __syncthreads();
+    int ran = S.timesRan[c];
+    for (int e = tid; e < d * d; e += nt) {  // propCov += gamma1 * (E'E/(n-1) - propCov)
+      int a = e % d, b = e / d;
+      double acc = 0;
+      for (int r = 0; r < AI; r++)
+        acc += S.empirSamp[((size_t)r + (size_t)a * AI) * C + c] * S.empirSamp[((size_t)r + (size_t)b * AI) * C + c];
+      double ec = acc / (double)(ran - 1);
+      double pc = S.propCov[(size_t)e * C + c];
+      pc = pc + s_gamma1 * (ec - pc);
+      S.propCov[(size_t)e * C + c] = pc;
+      U[e] = pc;
+    }
+    __syncthreads();
+    for (int j = 0; j < d; j++) {  // column Cholesky, upper factor
+      if (tid == 0) {
+        double s = U[j + j * d];
+        for (int k = 0; k < j; k++) s -= U[k + j * d] * U[k + j * d];
+        s = sqrt(s);
+        U[j + j * d] = s;
+        s_diag = s;
+      }
+      __syncthreads();
+      for (int i = j + 1 + tid; i < d; i += nt) {
+        double v = U[j + i * d];
+        for (int k = 0; k < j; k++) v -= U[k + j * d] * U[k + i * d];
+        U[j + i * d] = v / s_diag;
+      }
+      __syncthreads();
+    }
+    for (int e = tid; e < d * d; e += nt) S.chol[(size_t)e * C + c] = (e % d) <= (e / d) ? U[e] : 0.0;
+    __syncthreads();
+  }
+  for (int e = tid; e < d * d; e += nt) S.cholScale[(size_t)e * C + c] = S.chol[(size_t)e * C + c] * s_scale;
+  if (tid == 0) { S.timesRan[c] = 0; S.timesAccepted[c] = 0; }
+}
+
+// wide conjugate: draw from the posterior given the reduced contributions
+__global__ void k_conj_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, const double* contrib /*[n_dep][2][C]*/) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_sampler sp = T.samplers[sid];
+  bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  DrawKey key = make_key(T, seed, iter, sid, 0, c);
+  const nimb200_dep tp = T.deps[sp.dep_off];
+  int tnode = sel_of(T, tp, 0).lo;
+  double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+  double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
+  double c0 = 0, c1 = 0;
+  for (int e = 0; e < sp.n_dep; e++) {
+    if (T.deps[sp.dep_off + e].stage != 1) continue;
+    c0 += contrib[((size_t)e * 2) * T.C + c];
+    c1 += contrib[((size_t)e * 2 + 1) * T.C + c];
+  }
+  double nv;
+  if (gam) {
+    double shape = prior0 + c0, scale = 1 / (prior1 + c1);
+    nv = rgamma1(key, shape) * scale;
+  } else {
+    double mean = (prior0 * prior1 + c0) / (prior1 + c1), sd = pow(prior1 + c1, -0.5), z, z1;
+    normal2(key, 0, z, z1);
+    nv = mean + sd * z;
+  }
+  T.state[(size_t)sp.target_slot * T.C + c] = nv;
+}
+
+__global__ void k_sampler_reset(DevTab T, int sid, SamplerDev S, const double* propcov0 /*d*d col-major or null*/) {
+  const nimb200_sampler sp = T.samplers[sid];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+  if (gid >= (size_t)TT * T.C) return;
+  S.scale[gid] = sp.scale;
+  S.timesRan[gid] = 0; S.timesAccepted[gid] = 0; S.timesAdapted[gid] = 0;
+}
+
+// chol(propCov) at reset: one block per chain (propCov is the same for all chains at reset)
+__global__ void k_block_reset(DevTab T, int sid, SamplerDev S, const double* propcov0) {
+  __shared__ double U[NIMB200_MAX_BLOCK_D * NIMB200_MAX_BLOCK_D];
+  __shared__ double s_diag;
+  const nimb200_sampler sp = T.samplers[sid];
+  int c = blockIdx.x, d = sp.d, C = T.C, tid = threadIdx.x, nt = blockDim.x;
+  for (int e = tid; e < d * d; e += nt) {
+    U[e] = propcov0 ? propcov0[e] : ((e % d) == (e / d) ? 1.0 : 0.0);
+    S.propCov[(size_t)e * C + c] = U[e];
+  }
+  __syncthreads();
+  for (int j = 0; j < d; j++) {
+    if (tid == 0) {
+      double s = U[j + j * d];
+      for (int k = 0; k < j; k++) s -= U[k + j * d] * U[k + j * d];
+      s = sqrt(s);
+      U[j + j * d] = s;
+      s_diag = s;
+    }
+    __syncthreads();
+    for (int i = j + 1 + tid; i < d; i += nt) {
+      double v = U[j + i * d];
+      for (int k = 0; k < j; k++) v -= U[k + j * d] * U[k + i * d];
+      U[j + i * d] = v / s_diag;
+    }
+    __syncthreads();
+  }
+  for (int e = tid; e < d * d; e += nt) {
+    double u = (e % d) <= (e / d) ? U[e] : 0.0;
+    S.chol[(size_t)e * C + c] = u;
+    S.cholScale[(size_t)e * C + c] = u * sp.scale;
+  }
+}
+
+// mvSamples row: nimCopy(model -> mvSamples, nodes = monitors), MCMC_build.R:294-303
+__global__ void k_monitor(DevTab T, const int32_t* mon, int nmon, double* row /*[nmon][C]*/) {
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)nmon * T.C) return;
+  int c = (int)(gid % T.C), j = (int)(gid / T.C);
+  row[gid] = T.state[(size_t)mon[j] * T.C + c];
+}
+
+// [rows][nmon][C] -> [C][rows][nmon]
+__global__ void k_samples_out(const double* src, double* dst, int64_t rows, int nmon, int C) {
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)rows * nmon * C;
+  if (gid >= total) return;
+  int c = (int)(gid % C);
+  size_t rj = gid / C;
+  dst[(size_t)c * rows * nmon + rj] = src[gid];
+}
+
+// [C][n] host layout <-> [n][C] device layout
+__global__ void k_transpose(const double* src, double* dst, int rows, int cols) {  // src[rows][cols] -> dst[cols][rows]
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)rows * cols) return;
+  int r = (int)(gid / cols), q = (int)(gid % cols);
+  dst[(size_t)q * rows + r] = src[gid];
+}
+
+__global__ void k_draws(uint64_t seed, int chain, uint64_t iter, int sampler, int target, int kind, double a, int n, double* out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  DrawKey key; key.seed = seed; key.chain = (uint32_t)chain; key.iter = iter; key.sampler = (uint32_t)sampler; key.target = (uint32_t)target;
+  double x0, x1;
+  if (kind == 0) { normal2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
+  else if (kind == 1) { unif2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
+  else { key.target = (uint32_t)(target + k); out[k] = rgamma1(key, a); }
+}
+
+// ------------------------------------------------------------------------------------------------ host model
+struct nimb200_model {
+  int device = 0, C = 0, first_chain = 0;
+  nimb200_table t{};  // host copy (arrays below)
+  std::vector<nimb200_op> ops;
+  std::vector<nimb200_decl> decl;
+  std::vector<nimb200_sampler> samplers;
+  std::vector<nimb200_dep> deps;
+  std::vector<int32_t> monitors;
+  std::vector<int64_t> darr_len, iarr_len;
+  std::vector<double*> d_darr;
+  std::vector<int32_t*> d_iarr;
+  DevTab T{};
+  void* d_ops = nullptr; void* d_decl = nullptr; void* d_samplers = nullptr; void* d_deps = nullptr;
+  void* d_darr_tab = nullptr; void* d_iarr_tab = nullptr;
+  int32_t* d_mon = nullptr;
+  double* d_state = nullptr;
+  double* d_stage = nullptr;    // staging for host<->device transposes, n_slots*C
+  double* d_lpcache = nullptr;  // [n_decl][C] block sums behind calculate/calculateDiff/getLogProb
+  double* d_depcache = nullptr; // [n_deps][C] block sums of the CURRENT state per dependency entry
+  double* d_newsum = nullptr;   // [max_dep][2][C]
+  double* d_tsave = nullptr;    // [MAX_BLOCK_D][C]
+  double* d_pls = nullptr;      // [C]
+  double* d_partials = nullptr; // scratch: tile partial sums
+  size_t partials_cap = 0;
+  std::vector<SamplerDev> sdev;
+  std::vector<char> wide;       // per sampler: wide path?
+  std::vector<char> dep_valid;  // per dependency entry: depcache row valid?
+  std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
+  std::vector<int> ran;         // RW_block: iterations since last adaptation
+  std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
+  double* d_samples = nullptr;  // [cap][nmon][C]
+  int64_t rows = 0, cap = 0, iter_done = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double last_ms = 0;
+  int64_t last_launches = 0, launches = 0;
+  std::vector<void*> allocs;
+};
+
+static const int EVAL_THREADS = 256;
+static const int EVAL_NPT = 32;
+
+template <class Tp>
+static int dev_alloc(nimb200_model* m, Tp** p, size_t count) {
+  void* q = nullptr;
+  CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(Tp)));
+  m->allocs.push_back(q);
+  *p = (Tp*)q;
+  return 0;
+}
+
+static int cw_log2_for(int C) {
+  int l = 0;
+  while ((1 << l) < C && l < 5) l++;
+  return l;
+}
+
+static int eval_tiles(int C, int count) {
+  int nl = EVAL_THREADS >> cw_log2_for(C);
+  int per = nl * EVAL_NPT;
+  return (count + per - 1) / per;
+}
+
+// evaluate instances [lo,hi) (through idx) of declaration di for all chains; reduced sums land in dst0 (dst1)
+static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, const int32_t* idx, double* dst0, double* dst1,
+                           const nimb200_dep* dp, int slot, int gam) {
+  int C = m->C;
+  int cwl = cw_log2_for(C), cw = 1 << cwl;
+  int count = hi - lo;
+  if (count <= 0) {
+    CK(cudaMemsetAsync(dst0, 0, sizeof(double) * C, m->stream));
+    if (dst1) CK(cudaMemsetAsync(dst1, 0, sizeof(double) * C, m->stream));
+    return 0;
+  }
+  const nimb200_decl& d = m->decl[di];
+  if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di] && lo == 0 && hi == d.n && !idx) {
+    int nt = fused_bern_logit_tiles(d.n);
+    if ((size_t)nt * C > m->partials_cap) return fail("internal: partials scratch too small (fused)");
+    fused_bern_logit_launch(m->d_xpad[di], m->d_darr[d.value_ref], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C,
+                            m->d_partials, m->stream);
+    m->launches++;
+    k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
+    m->launches++;
+    CK(cudaGetLastError());
+    return 0;
+  }
+  int nt = eval_tiles(C, count);
+  int K = mode == 2 ? 2 : 1;
+  if ((size_t)nt * K * C > m->partials_cap) return fail("internal: partials scratch too small");
+  dim3 grid(nt, (C + cw - 1) / cw);
+  nimb200_dep dd{};
+  if (dp) dd = *dp;
+  size_t shm = sizeof(double) * EVAL_THREADS * K;
+  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
+  else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
+  m->launches++;
+  k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
+  m->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+struct HostSel { int lo, hi; const int32_t* idx; };
+static HostSel host_sel(nimb200_model* m, const nimb200_dep& dp, const std::vector<std::vector<int32_t>>& h_iarr) {
+  HostSel s{0, 0, nullptr};
+  switch (dp.sel) {
+    case NIMB_SEL_ALL: s.lo = 0; s.hi = m->decl[dp.decl].n; break;
+    case NIMB_SEL_SAME: s.lo = dp.a; s.hi = dp.a + 1; break;
+    case NIMB_SEL_STRIDE: s.lo = 0; s.hi = dp.a; break;
+    case NIMB_SEL_SEG: s.lo = h_iarr[dp.a][0]; s.hi = h_iarr[dp.a][1]; break;
+    case NIMB_SEL_CSR: s.lo = h_iarr[dp.a][0]; s.hi = h_iarr[dp.a][1]; s.idx = m->d_iarr[dp.b]; break;
+    default: s.lo = dp.a; s.hi = dp.b; break;
+  }
+  return s;
+}
+
+struct ModelHostExtra {
+  std::vector<std::vector<int32_t>> h_iarr;
+};
+static std::vector<std::pair<nimb200_model*, ModelHostExtra*>> g_extra;
+static ModelHostExtra* extra_of(nimb200_model* m) {
+  for (auto& p : g_extra) if (p.first == m) return p.second;
+  return nullptr;
+}
+
+static size_t dep_count_t0(nimb200_model* m, const nimb200_sampler& sp) {
+  ModelHostExtra* ex = extra_of(m);
+  size_t n = 0;
+  for (int e = 0; e < sp.n_dep; e++) {
+    HostSel s = host_sel(m, m->deps[sp.dep_off + e], ex->h_iarr);
+    n += (size_t)std::max(0, s.hi - s.lo);
+  }
+  return n;
+}
+
+static int validate_table(const nimb200_table* t) {
+  if (!t) return fail("null table");
+  if (t->version != NIMB200_TABLE_VERSION) return fail("node table version mismatch");
+  if (t->n_slots < 0 || t->n_decl < 0 || t->n_ops < 0) return fail("negative table size");
+  for (int i = 0; i < t->n_decl; i++) {
+    const nimb200_decl& d = t->decl[i];
+    if (d.dist < NIMB_DNORM || d.dist > NIMB_DEXP) return fail("unknown distribution id in declaration");
+    if (d.n < 0) return fail("negative node count");
+    if (d.value_kind == 0) {
+      if (d.value_ref < 0 || d.value_ref >= t->n_darr || t->darr_len[d.value_ref] < d.n) return fail("data array too short for declaration");
+    } else if (d.value_ref < 0 || d.value_ref + d.n > t->n_slots) return fail("declaration values outside the chain state");
+    for (int p = 0; p < d.nparam; p++) {
+      if (d.prog_off[p] < 0 || d.prog_off[p] + d.prog_len[p] > t->n_ops) return fail("parameter program outside ops[]");
+      int depth = 0, maxd = 0;
+      for (int q = 0; q < d.prog_len[p]; q++) {
+        int op = t->ops[d.prog_off[p] + q].op;
+        if (op >= NIMB_OP_CONST && op <= NIMB_OP_CVARJ) depth++;
+        else if (op >= NIMB_OP_ADD && op <= NIMB_OP_POW) depth--;
+        else if (op < NIMB_OP_NEG || op > NIMB_OP_STEP) return fail("unknown op code in parameter program");
+        maxd = std::max(maxd, depth);
+        if (depth < 1) return fail("malformed parameter program (stack underflow)");
+      }
+      if (depth != 1) return fail("malformed parameter program");
+      if (maxd > 16) return fail("parameter program needs more than 16 stack entries");
+    }
+  }
+  for (int s = 0; s < t->n_samplers; s++) {
+    const nimb200_sampler& sp = t->samplers[s];
+    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_CONJ_NORMAL)
+      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm); there is no CPU fallback");
+    if (sp.type == NIMB_SAMPLER_RW_BLOCK && (sp.d < 1 || sp.d > NIMB200_MAX_BLOCK_D)) return fail("RW_block dimension out of range");
+    if (sp.dep_off < 0 || sp.dep_off + sp.n_dep > t->n_deps || sp.n_dep < 1) return fail("sampler dependency range outside deps[]");
+    if (t->deps[sp.dep_off].stage != 0) return fail("first dependency entry of a sampler must be the target's own declaration");
+    if (sp.adaptive && sp.adapt_interval < 1) return fail("adaptInterval must be >= 1");
+    if (sp.tries < 1 && sp.type == NIMB_SAMPLER_RW_BLOCK) return fail("tries must be >= 1");
+  }
+  for (int i = 0; i < t->n_monitors; i++)
+    if (t->monitor_slots[i] < 0 || t->monitor_slots[i] >= t->n_slots) return fail("monitor slot out of range");
+  return 0;
+}
+
+extern "C" const char* nimb200_last_error(void) { return g_err.c_str(); }
+extern "C" int nimb200_version(void) { return NIMB200_TABLE_VERSION; }
+
+extern "C" int nimb200_model_free(nimb200_model* m) {
+  if (!m) return 0;
+  cudaSetDevice(m->device);
+  if (m->stream) cudaStreamSynchronize(m->stream);
+  for (void* p : m->allocs) cudaFree(p);
+  if (m->d_samples) cudaFree(m->d_samples);
+  if (m->ev0) cudaEventDestroy(m->ev0);
+  if (m->ev1) cudaEventDestroy(m->ev1);
+  if (m->stream) cudaStreamDestroy(m->stream);
+  for (size_t i = 0; i < g_extra.size(); i++)
+    if (g_extra[i].first == m) { delete g_extra[i].second; g_extra.erase(g_extra.begin() + i); break; }
+  delete m;
+  return 0;
+}
+
+extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int32_t first_chain, int32_t device,
+                                    nimb200_model** out) {
+  if (!out) return fail("null output pointer");
+  *out = nullptr;
+  if (validate_table(t)) return 1;
+  if (nchains < 1) return fail("nchains must be >= 1");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+    return fail("no CUDA device available: the B200 back end has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail("CUDA device index out of range");
+  CK(cudaSetDevice(device));
+  nimb200_model* m = new nimb200_model();
+  ModelHostExtra* ex = new ModelHostExtra();
+  g_extra.push_back({m, ex});
+  m->device = device; m->C = nchains; m->first_chain = first_chain;
+  m->t = *t;
+  m->ops.assign(t->ops, t->ops + t->n_ops);
+  m->decl.assign(t->decl, t->decl + t->n_decl);
+  m->samplers.assign(t->samplers, t->samplers + t->n_samplers);
+  m->deps.assign(t->deps, t->deps + t->n_deps);
+  m->monitors.assign(t->monitor_slots, t->monitor_slots + t->n_monitors);
+  int rc = 0;
+#define TRY(x) do { if ((rc = (x)) != 0) { nimb200_model_free(m); return rc; } } while (0)
+#define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fail(std::string("CUDA error ") + cudaGetErrorString(e_)); nimb200_model_free(m); return 1; } } while (0)
+  TRYCU(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  TRYCU(cudaEventCreate(&m->ev0));
+  TRYCU(cudaEventCreate(&m->ev1));
+  // shared arrays: uploaded once, resident for the life of the model
+  m->d_darr.resize(t->n_darr); m->d_iarr.resize(t->n_iarr);
+  ex->h_iarr.resize(t->n_iarr);
+  for (int i = 0; i < t->n_darr; i++) {
+    TRY(dev_alloc(m, &m->d_darr[i], (size_t)t->darr_len[i]));
+    TRYCU(cudaMemcpyAsync(m->d_darr[i], t->darr[i], sizeof(double) * t->darr_len[i], cudaMemcpyHostToDevice, m->stream));
+  }
+  for (int i = 0; i < t->n_iarr; i++) {
+    TRY(dev_alloc(m, &m->d_iarr[i], (size_t)t->iarr_len[i]));
+    TRYCU(cudaMemcpyAsync(m->d_iarr[i], t->iarr[i], sizeof(int32_t) * t->iarr_len[i], cudaMemcpyHostToDevice, m->stream));
+    ex->h_iarr[i].assign(t->iarr[i], t->iarr[i] + t->iarr_len[i]);
+  }
+  auto up = [&](void** dst, const void* src, size_t bytes) -> int {
+    void* q = nullptr;
+    CK(cudaMalloc(&q, std::max<size_t>(bytes, 8)));
+    m->allocs.push_back(q);
+    if (bytes) CK(cudaMemcpyAsync(q, src, bytes, cudaMemcpyHostToDevice, m->stream));
+    *dst = q;
+    return 0;
+  };
+  TRY(up(&m->d_ops, m->ops.data(), sizeof(nimb200_op) * m->ops.size()));
+  TRY(up(&m->d_decl, m->decl.data(), sizeof(nimb200_decl) * m->decl.size()));
+  TRY(up(&m->d_samplers, m->samplers.data(), sizeof(nimb200_sampler) * m->samplers.size()));
+  TRY(up(&m->d_deps, m->deps.data(), sizeof(nimb200_dep) * m->deps.size()));
+  TRY(up(&m->d_darr_tab, m->d_darr.data(), sizeof(double*) * m->d_darr.size()));
+  TRY(up(&m->d_iarr_tab, m->d_iarr.data(), sizeof(int32_t*) * m->d_iarr.size()));
+  void* dm = nullptr;
+  TRY(up(&dm, m->monitors.data(), sizeof(int32_t) * m->monitors.size()));
+  m->d_mon = (int32_t*)dm;
+  size_t C = nchains;
+  TRY(dev_alloc(m, &m->d_state, (size_t)t->n_slots * C));
+  TRY(dev_alloc(m, &m->d_stage, (size_t)t->n_slots * C));
+  TRY(dev_alloc(m, &m->d_lpcache, (size_t)t->n_decl * C));
+  TRY(dev_alloc(m, &m->d_depcache, (size_t)t->n_deps * C));
+  int maxdep = 1;
+  for (auto& sp : m->samplers) maxdep = std::max(maxdep, sp.n_dep);
+  TRY(dev_alloc(m, &m->d_newsum, (size_t)maxdep * 2 * C));
+  TRY(dev_alloc(m, &m->d_tsave, (size_t)NIMB200_MAX_BLOCK_D * C));
+  TRY(dev_alloc(m, &m->d_pls, C));
+  TRYCU(cudaMemsetAsync(m->d_state, 0, sizeof(double) * t->n_slots * C, m->stream));
+  TRYCU(cudaMemsetAsync(m->d_lpcache, 0, sizeof(double) * t->n_decl * C, m->stream));
+  // scratch for tile partial sums: sized for the largest declaration
+  size_t pc = 1;
+  for (auto& d : m->decl) {
+    pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
+    if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
+  }
+  TRY(dev_alloc(m, &m->d_partials, pc));
+  m->partials_cap = pc;
+  m->T.ops = (const nimb200_op*)m->d_ops; m->T.decl = (const nimb200_decl*)m->d_decl;
+  m->T.deps = (const nimb200_dep*)m->d_deps; m->T.samplers = (const nimb200_sampler*)m->d_samplers;
+  m->T.darr = (const double* const*)m->d_darr_tab; m->T.iarr = (const int32_t* const*)m->d_iarr_tab;
+  m->T.state = m->d_state; m->T.n_slots = t->n_slots; m->T.C = nchains; m->T.first_chain = first_chain;
+  // fused family: re-lay X once (row-major, rows padded to a multiple of 4 doubles)
+  m->d_xpad.assign(m->decl.size(), nullptr);
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    nimb200_decl& d = m->decl[i];
+    if (d.family != NIMB_FAM_BERN_LOGIT_INPROD) continue;
+    int xid = d.fam_arg[0], p = d.fam_arg[2], ld = d.fam_arg[3];
+    bool ok = d.value_kind == 0 && xid >= 0 && xid < t->n_darr && p >= 1 && p <= 64 && ld >= p &&
+              t->darr_len[xid] >= (int64_t)d.n * ld && d.fam_arg[1] >= 0 && d.fam_arg[1] + p <= t->n_slots;
+    for (int q = 0; ok && q < d.n; q++) {  // the fused kernel assumes Bernoulli data in {0, 1}
+      double yv = t->darr[d.value_ref][q];
+      ok = (yv == 0.0 || yv == 1.0);
+    }
+    if (!ok) { d.family = NIMB_FAM_GENERIC; continue; }
+    size_t len = fused_bern_logit_xpad_len(d.n, p);
+    if (len == 0) { d.family = NIMB_FAM_GENERIC; continue; }
+    TRY(dev_alloc(m, &m->d_xpad[i], len));
+    fused_bern_logit_prepare_x(m->d_darr[xid], d.n, p, ld, m->d_xpad[i], m->stream);
+  }
+  // sampler state + execution shape
+  m->sdev.resize(m->samplers.size());
+  m->wide.assign(m->samplers.size(), 0);
+  m->ran.assign(m->samplers.size(), 0);
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+    SamplerDev& S = m->sdev[s];
+    TRY(dev_alloc(m, &S.scale, (size_t)TT * C));
+    TRY(dev_alloc(m, &S.timesRan, (size_t)TT * C));
+    TRY(dev_alloc(m, &S.timesAccepted, (size_t)TT * C));
+    TRY(dev_alloc(m, &S.timesAdapted, (size_t)TT * C));
+    S.propCov = S.chol = S.cholScale = S.empirSamp = nullptr;
+    if (sp.type == NIMB_SAMPLER_RW_BLOCK) {
+      size_t dd = (size_t)sp.d * sp.d;
+      TRY(dev_alloc(m, &S.propCov, dd * C));
+      TRY(dev_alloc(m, &S.chol, dd * C));
+      TRY(dev_alloc(m, &S.cholScale, dd * C));
+      TRY(dev_alloc(m, &S.empirSamp, (size_t)sp.adapt_interval * sp.d * C));
+      TRYCU(cudaMemsetAsync(S.empirSamp, 0, sizeof(double) * sp.adapt_interval * sp.d * C, m->stream));
+      m->wide[s] = 1;
+    } else if (sp.n_targets == 1 && sp.type != NIMB_SAMPLER_BINARY && dep_count_t0(m, sp) > 2048) {
+      m->wide[s] = 1;
+    }
+  }
+  // which cached dependency sums does each sampler invalidate: every entry (of any sampler) on a declaration it touches
+  m->dep_valid.assign(m->deps.size(), 0);
+  m->invalidates.resize(m->samplers.size());
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    std::set<int> touched;
+    for (int e = 0; e < sp.n_dep; e++) touched.insert(m->deps[sp.dep_off + e].decl);
+    for (size_t g = 0; g < m->deps.size(); g++) {
+      bool own = (int)g >= sp.dep_off && (int)g < sp.dep_off + sp.n_dep;
+      if (touched.count(m->deps[g].decl) && !(own && m->wide[s] && sp.type != NIMB_SAMPLER_CONJ_GAMMA && sp.type != NIMB_SAMPLER_CONJ_NORMAL))
+        m->invalidates[s].push_back((int)g);
+    }
+  }
+  TRYCU(cudaStreamSynchronize(m->stream));
+  *out = m;
+  return 0;
+}
+
+extern "C" int nimb200_set_values(nimb200_model* m, const double* v) {
+  if (!m || !v) return fail("null argument");
+  CK(cudaSetDevice(m->device));
+  size_t n = (size_t)m->t.n_slots * m->C;
+  if (n == 0) return 0;
+  CK(cudaMemcpyAsync(m->d_stage, v, sizeof(double) * n, cudaMemcpyHostToDevice, m->stream));
+  k_transpose<<<(unsigned)((n + 255) / 256), 256, 0, m->stream>>>(m->d_stage, m->d_state, m->C, m->t.n_slots);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(m->stream));
+  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  return 0;
+}
+
+extern "C" int nimb200_get_values(nimb200_model* m, double* v) {
+  if (!m || !v) return fail("null argument");
+  CK(cudaSetDevice(m->device));
+  size_t n = (size_t)m->t.n_slots * m->C;
+  if (n == 0) return 0;
+  k_transpose<<<(unsigned)((n + 255) / 256), 256, 0, m->stream>>>(m->d_state, m->d_stage, m->t.n_slots, m->C);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(v, m->d_stage, sizeof(double) * n, cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return 0;
+}
+
+static int check_range(nimb200_model* m, int di, int lo, int hi) {
+  if (!m) return fail("null model");
+  if (di < 0 || di >= (int)m->decl.size()) return fail("declaration index out of range");
+  if (lo < 0 || hi > m->decl[di].n || lo > hi) return fail("node range outside the declaration");
+  return 0;
+}
+
+extern "C" int nimb200_calculate(nimb200_model* m, int32_t di, int32_t lo, int32_t hi, double* out) {
+  if (check_range(m, di, lo, hi)) return 1;
+  CK(cudaSetDevice(m->device));
+  bool whole = lo == 0 && hi == m->decl[di].n;
+  double* dst = whole ? m->d_lpcache + (size_t)di * m->C : m->d_pls;
+  if (launch_eval_sum(m, 0, di, lo, hi, nullptr, dst, nullptr, nullptr, -1, 0)) return 1;
+  CK(cudaMemcpyAsync(out, dst, sizeof(double) * m->C, cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return 0;
+}
+
+extern "C" int nimb200_calculate_nodes(nimb200_model* m, int32_t di, int32_t lo, int32_t hi, double* out) {
+  if (check_range(m, di, lo, hi)) return 1;
+  CK(cudaSetDevice(m->device));
+  size_t n = (size_t)(hi - lo) * m->C;
+  if (n == 0) return 0;
+  double* d_out = nullptr;
+  CK(cudaMalloc(&d_out, sizeof(double) * n));
+  int cwl = cw_log2_for(m->C), cw = 1 << cwl;
+  dim3 grid(eval_tiles(m->C, hi - lo), (m->C + cw - 1) / cw);
+  nimb200_dep dd{};
+  k_eval<1><<<grid, EVAL_THREADS, 0, m->stream>>>(m->T, di, lo, hi, nullptr, cwl, EVAL_NPT, nullptr, d_out, dd, -1, 0);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, m->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+  cudaFree(d_out);
+  if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+__global__ void k_diff_update(double* cache, const double* nw, double* out, int C) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  out[c] = nw[c] - cache[c];
+  cache[c] = nw[c];
+}
+
+extern "C" int nimb200_calculateDiff(nimb200_model* m, int32_t di, double* out) {
+  if (check_range(m, di, 0, 0)) return 1;
+  CK(cudaSetDevice(m->device));
+  if (launch_eval_sum(m, 0, di, 0, m->decl[di].n, nullptr, m->d_newsum, nullptr, nullptr, -1, 0)) return 1;
+  k_diff_update<<<(m->C + 127) / 128, 128, 0, m->stream>>>(m->d_lpcache + (size_t)di * m->C, m->d_newsum, m->d_pls, m->C);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, m->d_pls, sizeof(double) * m->C, cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return 0;
+}
+
+// bench.py: average device time of `reps` back-to-back launches of the block-sum kernel of declaration di
+// (the kernel calculate() uses), CUDA events on the launching stream.
+extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps, double* ms_avg) {
+  if (check_range(m, di, 0, 0)) return 1;
+  if (reps < 1 || !ms_avg) return fail("bad argument");
+  CK(cudaSetDevice(m->device));
+  double* dst = m->d_newsum;
+  if (launch_eval_sum(m, 0, di, 0, m->decl[di].n, nullptr, dst, nullptr, nullptr, -1, 0)) return 1;  // warm
+  CK(cudaStreamSynchronize(m->stream));
+  const nimb200_decl& d = m->decl[di];
+  bool fused = d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di];
+  int C = m->C, cwl = cw_log2_for(C), cw = 1 << cwl;
+  CK(cudaEventRecord(m->ev0, m->stream));
+  for (int r = 0; r < reps; r++) {
+    if (fused)
+      fused_bern_logit_launch(m->d_xpad[di], m->d_darr[d.value_ref], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
+    else {
+      dim3 grid(eval_tiles(C, d.n), (C + cw - 1) / cw);
+      nimb200_dep dd{};
+      k_eval<0><<<grid, EVAL_THREADS, sizeof(double) * EVAL_THREADS, m->stream>>>(m->T, di, 0, d.n, nullptr, cwl, EVAL_NPT, m->d_partials, nullptr, dd, -1, 0);
+    }
+  }
+  CK(cudaEventRecord(m->ev1, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  CK(cudaGetLastError());
+  float ms = 0;
+  CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
+  *ms_avg = ms / reps;
+  return 0;
+}
+
+extern "C" int nimb200_getLogProb(nimb200_model* m, int32_t di, double* out) {
+  if (check_range(m, di, 0, 0)) return 1;
+  CK(cudaSetDevice(m->device));
+  CK(cudaMemcpyAsync(out, m->d_lpcache + (size_t)di * m->C, sizeof(double) * m->C, cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ MCMC driver
+static int ensure_dep_sums(nimb200_model* m, int s) {  // block sums of the current state for sampler s's dependencies
+  const nimb200_sampler& sp = m->samplers[s];
+  ModelHostExtra* ex = extra_of(m);
+  for (int e = 0; e < sp.n_dep; e++) {
+    int g = sp.dep_off + e;
+    if (m->dep_valid[g]) continue;
+    const nimb200_dep& dp = m->deps[g];
+    HostSel hs = host_sel(m, dp, ex->h_iarr);
+    if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)g * m->C, nullptr, nullptr, -1, 0)) return 1;
+    m->dep_valid[g] = 1;
+  }
+  return 0;
+}
+
+static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
+  const nimb200_sampler& sp = m->samplers[s];
+  ModelHostExtra* ex = extra_of(m);
+  int C = m->C;
+  const int TB = 128;
+  if (!m->wide[s]) {
+    size_t total = (size_t)sp.n_targets * C;
+    k_sweep<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s]);
+    m->launches++;
+  } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL) {
+    bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+    for (int e = 0; e < sp.n_dep; e++) {
+      const nimb200_dep& dp = m->deps[sp.dep_off + e];
+      if (dp.stage != 1) continue;
+      HostSel hs = host_sel(m, dp, ex->h_iarr);
+      if (launch_eval_sum(m, 2, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + ((size_t)e * 2) * C, m->d_newsum + ((size_t)e * 2 + 1) * C,
+                          &dp, sp.target_slot, gam ? 1 : 0)) return 1;
+    }
+    k_conj_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->d_newsum);
+    m->launches++;
+  } else {
+    int tries = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.tries : 1;
+    int npair = (sp.d + 1) / 2;
+    for (int tr = 0; tr < tries; tr++) {
+      if (ensure_dep_sums(m, s)) return 1;
+      if (sp.type == NIMB_SAMPLER_RW)
+        k_rw_propose<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls);
+      else
+        k_block_propose<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
+      m->launches++;
+      for (int e = 0; e < sp.n_dep; e++) {
+        const nimb200_dep& dp = m->deps[sp.dep_off + e];
+        HostSel hs = host_sel(m, dp, ex->h_iarr);
+        if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
+      }
+      int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;
+      k_mh_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache,
+                                                           m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr);
+      m->launches++;
+      if (sp.type == NIMB_SAMPLER_RW_BLOCK && sp.adaptive) {
+        m->ran[s]++;
+        if (m->ran[s] % sp.adapt_interval == 0) {
+          k_block_adapt<<<C, 128, 0, m->stream>>>(m->T, s, m->sdev[s]);
+          m->launches++;
+          m->ran[s] = 0;
+        }
+      }
+    }
+  }
+  for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin, int32_t thin, int32_t reset, uint64_t seed) {
+  if (!m) return fail("null model");
+  if (niter < 0) return fail("cannot specify niter < 0");
+  if (nburnin < 0) return fail("cannot specify nburnin < 0");
+  if (nburnin > niter) return fail("cannot specify nburnin > niter");
+  if (thin < 1) return fail("cannot use thin < 1");
+  if (!reset && nburnin != 0) return fail("cannot specify nburnin when using reset = FALSE.");
+  CK(cudaSetDevice(m->device));
+  int C = m->C, nmon = (int)m->monitors.size();
+  if (reset) {
+    m->rows = 0; m->iter_done = 0;
+    for (size_t s = 0; s < m->samplers.size(); s++) {
+      const nimb200_sampler& sp = m->samplers[s];
+      int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+      size_t total = (size_t)TT * C;
+      k_sampler_reset<<<(unsigned)((total + 127) / 128), 128, 0, m->stream>>>(m->T, (int)s, m->sdev[s], nullptr);
+      if (sp.type == NIMB_SAMPLER_RW_BLOCK)
+        k_block_reset<<<C, 64, 0, m->stream>>>(m->T, (int)s, m->sdev[s], sp.propcov_darr >= 0 ? m->d_darr[sp.propcov_darr] : nullptr);
+      m->ran[s] = 0;
+    }
+    CK(cudaGetLastError());
+  }
+  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  int64_t addrows = (niter - nburnin) / thin;
+  if (m->rows + addrows > m->cap) {  // resize(mvSamples, ...), MCMC_build.R:262
+    int64_t ncap = m->rows + addrows;
+    double* ns = nullptr;
+    CK(cudaMalloc(&ns, std::max<size_t>(1, (size_t)ncap * nmon * C) * sizeof(double)));
+    if (m->d_samples && m->rows)
+      CK(cudaMemcpyAsync(ns, m->d_samples, sizeof(double) * (size_t)m->rows * nmon * C, cudaMemcpyDeviceToDevice, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    if (m->d_samples) cudaFree(m->d_samples);
+    m->d_samples = ns; m->cap = ncap;
+  }
+  m->launches = 0;
+  CK(cudaEventRecord(m->ev0, m->stream));
+  for (int64_t it = 1; it <= niter; it++) {
+    uint64_t git = (uint64_t)(m->iter_done + it);
+    for (size_t s = 0; s < m->samplers.size(); s++)
+      if (run_sampler(m, (int)s, seed, git)) return 1;
+    if (it > nburnin && (it - nburnin) % thin == 0 && nmon > 0) {
+      size_t total = (size_t)nmon * C;
+      k_monitor<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples + (size_t)m->rows * total);
+      m->launches++;
+      m->rows++;
+    } else if (it > nburnin && (it - nburnin) % thin == 0) m->rows++;
+  }
+  CK(cudaEventRecord(m->ev1, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  CK(cudaGetLastError());
+  float ms = 0;
+  CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
+  m->last_ms = ms; m->last_launches = m->launches;
+  m->iter_done += niter;
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_samples(nimb200_model* m, double* out, int64_t* nrows_out) {
+  if (!m) return fail("null model");
+  if (nrows_out) *nrows_out = m->rows;
+  if (!out) return 0;
+  CK(cudaSetDevice(m->device));
+  int nmon = (int)m->monitors.size();
+  size_t total = (size_t)m->rows * nmon * m->C;
+  if (total == 0) return 0;
+  double* tmp = nullptr;
+  CK(cudaMalloc(&tmp, sizeof(double) * total));
+  k_samples_out<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->d_samples, tmp, m->rows, nmon, m->C);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, sizeof(double) * total, cudaMemcpyDeviceToHost, m->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+  cudaFree(tmp);
+  if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_last_timing(nimb200_model* m, double* ms_out, int64_t* launches_out) {
+  if (!m) return fail("null model");
+  if (ms_out) *ms_out = m->last_ms;
+  if (launches_out) *launches_out = m->last_launches;
+  return 0;
+}
+
+__global__ void k_i2d(const int32_t* src, double* dst, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = (double)src[i];
+}
+
+extern "C" int nimb200_sampler_state(nimb200_model* m, int32_t s, int32_t what, double* out, int64_t cap) {
+  if (!m || !out) return fail("null argument");
+  if (s < 0 || s >= (int)m->samplers.size()) return fail("bad sampler index");
+  CK(cudaSetDevice(m->device));
+  const nimb200_sampler& sp = m->samplers[s];
+  int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+  size_t n;
+  const double* src = nullptr;
+  double* tmp = nullptr;
+  if (what == 0) { n = (size_t)TT * m->C; src = m->sdev[s].scale; }
+  else if (what == 1) {
+    n = (size_t)TT * m->C;
+    CK(cudaMalloc(&tmp, sizeof(double) * n));
+    k_i2d<<<(unsigned)((n + 255) / 256), 256, 0, m->stream>>>(m->sdev[s].timesAdapted, tmp, n);
+    src = tmp;
+  } else if (what == 2 && sp.type == NIMB_SAMPLER_RW_BLOCK) { n = (size_t)sp.d * sp.d * m->C; src = m->sdev[s].propCov; }
+  else return fail("bad state selector");
+  if ((int64_t)n > cap) { if (tmp) cudaFree(tmp); return fail("output too small"); }
+  cudaError_t e = cudaMemcpyAsync(out, src, sizeof(double) * n, cudaMemcpyDeviceToHost, m->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
+  if (tmp) cudaFree(tmp);
+  if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target, int32_t kind,
+                             double a, int32_t n, double* out) {
+  if (!out || n < 0) return fail("bad argument");
+  if (n == 0) return 0;
+  double* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(double) * n));
+  k_draws<<<(n + 127) / 128, 128>>>(seed, chain, (uint64_t)iter, sampler, target, kind, a, n, d);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpy(out, d, sizeof(double) * n, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}

@@ -1,0 +1,43 @@
+// engine.cuh -- shared declarations of the sm_100a library (host model object + device table view).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "../../include/nimb200.h"
+
+namespace nimb {
+
+// Device view of the node table + chain-major state.  Passed to kernels by value.
+struct DevTab {
+  const nimb200_op* ops;
+  const nimb200_decl* decl;
+  const nimb200_dep* deps;
+  const nimb200_sampler* samplers;
+  const double* const* darr;
+  const int32_t* const* iarr;
+  double* state;  // [n_slots][C]: chain index fastest, so a warp reads 32 chains' copies of one node coalesced
+  int n_slots, C, first_chain;
+};
+
+// Per-sampler adaptive state, all [T][C] (or [d*d][C], [AI*d][C]) chain-fastest.
+struct SamplerDev {
+  double* scale;
+  int32_t* timesRan;
+  int32_t* timesAccepted;
+  int32_t* timesAdapted;
+  double* propCov;
+  double* chol;
+  double* cholScale;
+  double* empirSamp;
+};
+
+// fused y[i] ~ dbern(ilogit(X[i,] . beta)) block sum (fused_logit.cu).  partials: [n_tiles][C].
+// Returns the number of node tiles written (0 if the shape is unsupported and the generic kernel must run).
+int fused_bern_logit_tiles(int n);
+size_t fused_bern_logit_xpad_len(int n, int p);
+void fused_bern_logit_prepare_x(const double* X_rowmajor_dev, int n, int p, int ld, double* Xpad_dev, cudaStream_t st);
+void fused_bern_logit_launch(const double* Xpad, const double* y, int n, int p, const double* state, int beta_slot,
+                             int C, double* partials, cudaStream_t st);
+
+}  // namespace nimb

@@ -1,0 +1,80 @@
+// peaks.cu -- live FP64 peak measurements for the roofline denominators (bench.py).
+// MEASURED_PEAKS.json carries an HBM copy figure and a bf16 GEMM figure but no FP64 figure, and the hot
+// kernels of this path are FP64: a dependent-free DFMA loop (FP64 pipe) and an mma.sync m8n8k4 f64 loop
+// (FP64 tensor pipe) are timed with CUDA events, best of several launches.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdint>
+
+namespace {
+
+__global__ void k_dfma_peak(double* out, int iters, double seed) {
+  double a[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) a[j] = seed + j + threadIdx.x * 1e-9;
+  double b = 1.0000001, c = 1e-7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) a[j] = fma(a[j], b, c);
+  }
+  double s = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) s += a[j];
+  if (s == 12345.678) out[0] = s;
+}
+
+__global__ void k_dmma_peak(double* out, int iters, double seed) {
+  double d[8][2];
+#pragma unroll
+  for (int j = 0; j < 8; j++) d[j][0] = d[j][1] = 0.0;
+  double a = seed + (threadIdx.x & 31) * 1e-3, b = 1.0 + (threadIdx.x & 31) * 1e-4;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int j = 0; j < 8; j++)
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(d[j][0]), "+d"(d[j][1]) : "d"(a), "d"(b));
+  }
+  double s = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) s += d[j][0] + d[j][1];
+  if (s == 12345.678) out[0] = s;
+}
+
+}  // namespace
+
+extern "C" int nimb200_measure_fp64_peaks(int device, double* dfma_tflops, double* dmma_tflops) {
+  if (cudaSetDevice(device) != cudaSuccess) return 1;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 1;
+  double* out = nullptr;
+  if (cudaMalloc(&out, 8) != cudaSuccess) return 1;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int threads = 256, blocks = prop.multiProcessorCount * 8, iters = 4096;
+  double best_f = 0, best_m = 0;
+  for (int rep = 0; rep < 6; rep++) {
+    float ms = 0;
+    cudaEventRecord(e0);
+    k_dfma_peak<<<blocks, threads>>>(out, iters, 1.0);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    double flops = 2.0 * 8 * iters * (double)threads * blocks;
+    if (rep > 0) best_f = std::max(best_f, flops / (ms * 1e-3) / 1e12);
+    cudaEventRecord(e0);
+    k_dmma_peak<<<blocks, threads>>>(out, iters, 1.0);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    double mflops = 2.0 * 8 * 8 * 4 * 8 * iters * (double)(threads / 32) * blocks;
+    if (rep > 0) best_m = std::max(best_m, mflops / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  if (cudaGetLastError() != cudaSuccess) return 1;
+  *dfma_tflops = best_f;
+  *dmma_tflops = best_m;
+  return 0;
+}

@@ -440,15 +440,29 @@ class _Lowering:
                 s.propcov_darr = b.add_darr(pc.reshape(-1, order="F"))
         s.dep_off = len(b.deps)
         span = d if block else Tn
-        # stage 0: the target's own prior nodes
-        node0 = int(np.nonzero(decl.pos == pos0)[0][0])
-        dep0 = T.Dep()
-        dep0.decl, dep0.stage = self.decl_ids[decl.index], 0
-        if block or Tn == 1:
-            dep0.sel, dep0.a, dep0.b = T.SEL_RANGE, node0, node0 + span
+        # stage 0: the target's own prior nodes (a block may span several declarations of the variable)
+        if block:
+            for dcl in model.decl_of(var):
+                nodes = np.nonzero((dcl.pos >= pos0) & (dcl.pos < pos0 + span))[0]
+                if not nodes.size:
+                    continue
+                dep0 = T.Dep()
+                dep0.decl, dep0.stage = self.decl_ids[dcl.index], 0
+                if np.all(np.diff(nodes) == 1):
+                    dep0.sel, dep0.a, dep0.b = T.SEL_RANGE, int(nodes[0]), int(nodes[-1]) + 1
+                else:
+                    dep0.sel = T.SEL_CSR
+                    dep0.a, dep0.b = b.add_iarr(np.array([0, nodes.size])), b.add_iarr(nodes)
+                b.deps.append(dep0)
         else:
-            dep0.sel, dep0.a = T.SEL_SAME, node0
-        b.deps.append(dep0)
+            node0 = int(np.nonzero(decl.pos == pos0)[0][0])
+            dep0 = T.Dep()
+            dep0.decl, dep0.stage = self.decl_ids[decl.index], 0
+            if Tn == 1:
+                dep0.sel, dep0.a, dep0.b = T.SEL_RANGE, node0, node0 + 1
+            else:
+                dep0.sel, dep0.a = T.SEL_SAME, node0
+            b.deps.append(dep0)
         # stage 1: stochastic dependents
         for dep in model.dependents(var):
             tgt = self._target_of_nodes(dep, var, pos0, span)
@@ -477,7 +491,7 @@ class _Lowering:
                 if not np.any((tgt >= 0) & (tgt < Tn)):
                     continue
                 sel = self._selection(tgt, dep.n, Tn)
-            if dep is decl:
+            if dep.var == var and not dep.is_data:
                 if block:
                     continue
                 raise ModelError("%s: a node's own declaration reads the variable; not supported" % var)

@@ -48,6 +48,7 @@ typedef struct ref_model {
   uint64_t evals;              /* stochastic node evaluations (logProb evals) */
 } ref_model;
 
+static __thread uint64_t tl_evals; /* per-thread evaluation counter (flushed into the model at the end of a run) */
 static char g_err[512];
 const char *ref_last_error(void) { return g_err; }
 static int fail(const char *msg) { snprintf(g_err, sizeof g_err, "%s", msg); return 1; }
@@ -124,7 +125,7 @@ static double get_param(const ref_model *m, const double *st, int di, int i, int
 static double calc_node(ref_model *m, const double *st, int di, int i) {
   const nimb200_decl *d = m->t.decl + di;
   double x = node_value(m, st, d, i), p0 = 0, p1 = 0;
-  m->evals++;
+  tl_evals++;
   if (d->dist == NIMB_DCAT) {
     int K = d->fam_arg[0], j;
     double pr[256], *pp = pr, r;
@@ -679,6 +680,8 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
       }
     }
   }
+  __atomic_fetch_add(&m->evals, tl_evals, __ATOMIC_RELAXED);
+  tl_evals = 0;
   return 0;
 }
 int ref_mcmc_finish(ref_model *m, int64_t niter, int64_t nburnin, int32_t thin) {
@@ -729,7 +732,7 @@ int ref_sampler_state(ref_model *m, int32_t s, int32_t what, double *out, int64_
   return fail("bad state selector");
 }
 
-uint64_t ref_eval_count(ref_model *m) { return m->evals; }
+uint64_t ref_eval_count(ref_model *m) { uint64_t v = m->evals + tl_evals; return v; }
 
 int ref_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target, int32_t kind, double a,
               int32_t n, double *out) {

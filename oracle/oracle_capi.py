@@ -36,9 +36,10 @@ def oracle_backend():
         for name in ("dnorm", "dgamma", "dbinom", "dbeta", "dlogis"):
             f = getattr(b.lib, "ref_" + name)
             f.argtypes, f.restype = [C.c_double] * 3, C.c_double
-        for name in ("dpois", "dexp_nimble", "stirlerr", "bd0", "lbeta"):
+        for name in ("dpois", "dexp_nimble", "bd0", "lbeta"):
             f = getattr(b.lib, "ref_" + name)
             f.argtypes, f.restype = [C.c_double] * 2, C.c_double
+        b.lib.ref_stirlerr.argtypes, b.lib.ref_stirlerr.restype = [C.c_double], C.c_double
         b.lib.ref_dcat.argtypes, b.lib.ref_dcat.restype = [C.c_double, C.POINTER(C.c_double), C.c_int], C.c_double
         _backend = b
     return _backend

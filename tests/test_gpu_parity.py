@@ -1,0 +1,237 @@
+"""GPU: the CUDA path (through the C ABI, libnimb200.so) against the CPU oracle on identical lowered tables,
+identical initial values and identical counter-based draws.
+
+Tolerances (north_star): log-densities and block sums within 1e-12 relative; MCMC trajectories are compared
+at 1e-9 relative over a few hundred iterations (draws are bit-identical, densities differ by <= 1-2 ulp through
+libm vs CUDA exp/log/pow/lgamma, block sums by summation order), which also proves every accept/reject decision
+agreed -- one flipped decision would move a chain by O(1)."""
+import os
+
+import numpy as np
+import pytest
+
+import nimble_b200 as nb
+from nimble_b200 import configs
+from nimble_b200 import table as T
+from tests import small_models as sm
+from tests.helpers import compile_on, pooled, rel_err, run
+
+pytestmark = pytest.mark.gpu
+RTOL_LP = 1e-12
+RTOL_TRAJ = 1e-9
+
+
+def pair(oracle, b200, conf, nchains, inits):
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    do, dg = co._ensure(nchains), cg._ensure(nchains)
+    do.set_values(inits)
+    dg.set_values(inits)
+    return co, cg, do, dg
+
+
+def test_set_get_values_roundtrip(b200):
+    m, conf = sm.SMALL["glmm"]()
+    cg = compile_on(b200, conf)
+    v = sm.random_inits(m, 7, 1)
+    d = cg._ensure(7)
+    d.set_values(v)
+    assert np.array_equal(d.get_values(), v)
+
+
+@pytest.mark.parametrize("nchains", [1, 9, 70])
+def test_per_node_logprob_every_distribution(oracle, b200, nchains):
+    m, conf = sm.all_dists()
+    inits = sm.random_inits(m, nchains, 42)
+    co, cg, do, dg = pair(oracle, b200, conf, nchains, inits)
+    for di, d in enumerate(co.builder.decls):
+        a, b = dg.calculate_nodes(di), do.calculate_nodes(di)
+        assert a.shape == (d.n, nchains)
+        assert np.all(np.isfinite(b)), T.DIST_NAMES[d.dist]
+        assert rel_err(a, b).max() < RTOL_LP, (T.DIST_NAMES[d.dist], rel_err(a, b).max())
+
+
+def test_special_values_match(oracle, b200):
+    # -Inf / NaN / +Inf outcomes must agree exactly (they drive early rejection in the samplers)
+    code = """{ s ~ dgamma(1,1)
+      for (i in 1:6) { yn[i] ~ dnorm(0, sd = s - c[i])
+                       yp[i] ~ dpois(s * c[i])
+                       yb[i] ~ dbern(s * c[i] / 3)
+                       yg[i] ~ dgamma(c[i], rate = s) } }"""
+    consts = {"c": [0.0, 0.5, 1.0, 2.0, 3.0, 4.0]}
+    data = {"yn": [0, 0, 1, 0, 0, 0], "yp": [0, 1, 2.5, -1, 3, 0], "yb": [0, 1, 1, 0, 1, 2], "yg": [0, 0, 0, -1, 1, 2]}
+    m = nb.nimbleModel(code, constants=consts, data=data, inits={"s": 1.0})
+    conf = nb.configureMCMC(m, useConjugacy=False)
+    co, cg, do, dg = pair(oracle, b200, conf, 2, np.array([[1.0], [2.0]]))
+    for di in range(len(co.builder.decls)):
+        a, b = dg.calculate_nodes(di), do.calculate_nodes(di)
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b)), di
+        assert rel_err(a, b).max() < RTOL_LP
+
+
+def test_calculate_calculateDiff_getLogProb_semantics(oracle, b200):
+    m, conf = sm.SMALL["glmm"]()
+    co, cg, do, dg = pair(oracle, b200, conf, 5, sm.random_inits(m, 5, 3))
+    y = len(co.builder.decls) - 1
+    s_g, s_o = dg.calculate(y), do.calculate(y)
+    assert rel_err(s_g, s_o).max() < RTOL_LP
+    assert rel_err(dg.getLogProb(y), s_g).max() == 0.0              # stored block logProb
+    assert rel_err(dg.calculate(y, 100, 1300), do.calculate(y, 100, 1300)).max() < RTOL_LP
+    v2 = sm.random_inits(m, 5, 4)
+    dg.set_values(v2)
+    do.set_values(v2)
+    d_g, d_o = dg.calculateDiff(y), do.calculateDiff(y)             # new - stored, stored <- new
+    assert np.max(np.abs(d_g - d_o)) < 1e-9 * np.max(np.abs(s_o))
+    assert rel_err(dg.getLogProb(y), do.getLogProb(y)).max() < RTOL_LP
+    assert np.max(np.abs(dg.calculateDiff(y))) == 0.0
+    with pytest.raises(Exception, match="range"):
+        dg.calculate(y, 10, 10 ** 9)
+
+
+@pytest.mark.parametrize("name,nchains", [("pump", 4), ("pump", 33), ("logistic", 5), ("lmm", 5), ("lmm_perm", 3),
+                                          ("occupancy", 6), ("glmm", 5)])
+def test_mcmc_trajectories_match_oracle(oracle, b200, name, nchains):
+    m, conf = sm.SMALL[name]()
+    inits = sm.random_inits(m, nchains, 7, spread=0.1)
+    if name == "occupancy":
+        inits[:, m.var_slot["z"]:m.var_slot["z"] + 300] = 1.0
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    niter = 450  # crosses the adaptation steps at 200 and 400
+    so, sg = run(co, inits, niter, 50, seed=5), run(cg, inits, niter, 50, seed=5)
+    assert so.shape == sg.shape == (nchains, 400, len(co.colnames))
+    err = rel_err(sg, so)
+    assert err.max() < RTOL_TRAJ, (name, err.max(), np.unravel_index(err.argmax(), err.shape))
+    assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
+    for s, sp in enumerate(co.builder.samplers):
+        if sp.type in (T.SAMPLER_RW, T.SAMPLER_RW_BLOCK):
+            assert rel_err(cg.dm.sampler_state(s, 0), co.dm.sampler_state(s, 0)).max() < RTOL_TRAJ
+            assert np.array_equal(cg.dm.sampler_state(s, 1), co.dm.sampler_state(s, 1))
+        if sp.type == T.SAMPLER_RW_BLOCK:
+            assert rel_err(cg.dm.sampler_state(s, 2), co.dm.sampler_state(s, 2)).max() < 1e-8
+
+
+def test_logistic_generic_kernel_matches_fused(oracle, b200):
+    m, conf = configs.logistic(N=2000, p=50, seed=8)
+    inits = sm.random_inits(m, 70, 9, spread=0.2)
+    cg = compile_on(b200, conf)
+    dg = cg._ensure(70)
+    dg.set_values(inits)
+    y = len(cg.builder.decls) - 1
+    fused = dg.calculate(y)
+    os.environ["NIMB200_NO_FUSED"] = "1"
+    try:
+        cg2 = compile_on(b200, conf)
+        d2 = cg2._ensure(70)
+        d2.set_values(inits)
+        generic = d2.calculate(y)
+    finally:
+        del os.environ["NIMB200_NO_FUSED"]
+    co = compile_on(oracle, conf)
+    do = co._ensure(70)
+    do.set_values(inits)
+    ref = do.calculate(y)
+    assert rel_err(generic, ref).max() < RTOL_LP
+    assert rel_err(fused, ref).max() < RTOL_LP
+
+
+@pytest.mark.parametrize("N,p,C", [(1, 1, 1), (127, 3, 2), (129, 50, 65), (5000, 50, 130), (4097, 64, 64)])
+def test_fused_logistic_block_sum_shapes(oracle, b200, N, p, C):
+    m, conf = configs.logistic(N=N, p=max(p, 2), seed=N)
+    rng = np.random.default_rng(N)
+    inits = np.tile(m.init_vector(), (C, 1))
+    bs = m.var_slot["beta"]
+    inits[:, bs:bs + max(p, 2)] = rng.standard_normal((C, max(p, 2))) * 1.5
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(C), co._ensure(C)
+    dg.set_values(inits)
+    do.set_values(inits)
+    y = len(cg.builder.decls) - 1
+    assert rel_err(dg.calculate(y), do.calculate(y)).max() < RTOL_LP
+
+
+def test_fused_logistic_extreme_linear_predictors(oracle, b200):
+    # |eta| up to ~40: p underflows / q == 0 branches of dbinom_raw must agree, including -Inf
+    m, conf = configs.logistic(N=600, p=4, seed=3)
+    C = 8
+    inits = np.tile(m.init_vector(), (C, 1))
+    bs = m.var_slot["beta"]
+    inits[:, bs] = np.array([-45, -20, -8, -1, 1, 8, 20, 45.0])
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(C), co._ensure(C)
+    dg.set_values(inits)
+    do.set_values(inits)
+    y = len(cg.builder.decls) - 1
+    a, b = dg.calculate(y), do.calculate(y)
+    assert np.array_equal(np.isinf(a), np.isinf(b))
+    assert rel_err(a, b).max() < 1e-9  # ill-conditioned 1-p for |eta| > 9: see DESIGN.md "conditioning"
+
+
+def test_known_answers_on_gpu(b200):
+    # the reference's own fixtures, on the CUDA path: test-mcmc.R:164-179 and :1379-1443
+    m, conf = sm.SMALL["pump"]()
+    cg = compile_on(b200, conf)
+    s = pooled(run(cg, np.tile(m.init_vector(), (64, 1)), 3000, 500, seed=2))
+    mean = dict(zip(cg.colnames, s.mean(0)))
+    for name, want, tol in (("theta[1]", 0.06, 0.01), ("theta[2]", 0.10, 0.01), ("theta[9]", 1.58, 0.05),
+                            ("theta[10]", 1.97, 0.05), ("alpha", 0.73, 0.1), ("beta", 0.98, 0.1)):
+        assert abs(mean[name] - want) < tol, (name, mean[name])
+    m, conf = sm.binary_model()
+    cg = compile_on(b200, conf)
+    s = pooled(run(cg, np.tile(m.init_vector(), (256, 1)), 2000, 0, seed=9))
+    for k, v in dict(a=.5, b=.6, c=.05, d=.2, e=.9, f=.9525, g=.0475, h=.5).items():
+        assert abs(s[:, cg.colnames.index(k)].mean() - v) < 0.0025, k
+    m, conf = sm.binary_out_of_bounds()
+    assert np.all(run(compile_on(b200, conf), np.tile(m.init_vector(), (5, 1)), 100, 0) == 1.0)
+
+
+def test_reset_false_continuation_on_gpu(b200):
+    m, conf = sm.SMALL["logistic"]()
+    init = sm.random_inits(m, 3, 1, 0.1)
+    cg = compile_on(b200, conf)
+    a = run(cg, init, 250, 0, seed=4).copy()
+    b = run(cg, init, 210, 0, seed=4, reset=False)
+    c = run(compile_on(b200, conf), init, 460, 0, seed=4)
+    assert np.array_equal(b[:, :250], a) and np.array_equal(b, c)
+
+
+def test_first_chain_offsets_the_streams(b200):
+    # chain sharding: rank r runs chains [r*K, (r+1)*K) with first_chain = r*K and must reproduce them exactly
+    m, conf = sm.SMALL["pump"]()
+    init = np.tile(m.init_vector(), (6, 1))
+    full = run(compile_on(b200, conf), init, 120, 0, seed=8)
+    part = nb.compileNimble(nb.buildMCMC(conf), backend=b200, first_chain=4)
+    assert np.array_equal(run(part, init[:2], 120, 0, seed=8), full[4:6])
+
+
+def test_bad_tables_fail_loudly(b200):
+    m, conf = sm.SMALL["pump"]()
+    cg = compile_on(b200, conf)
+    cg.builder.samplers[0].type = 99
+    with pytest.raises(Exception, match="no CPU fallback"):
+        cg._ensure(2)
+    cg = compile_on(b200, conf)
+    cg.builder.decls[0].dist = 77
+    with pytest.raises(Exception, match="unknown distribution"):
+        cg._ensure(2)
+
+
+def test_full_size_logistic_properties(oracle, b200):
+    # BASELINE.json configs[1] at full size (N = 1e6, p = 50): size-independent checks.
+    m, conf = configs.logistic()
+    C = 128
+    inits = np.stack([m.init_vector(i) for i in configs.logistic_inits(50, C)])
+    inits[0, m.var_slot["beta"]:m.var_slot["beta"] + 50] = 0.0
+    cg = compile_on(b200, conf)
+    dg = cg._ensure(C)
+    dg.set_values(inits)
+    y = len(cg.builder.decls) - 1
+    total = dg.calculate(y)
+    assert abs(total[0] - 1_000_000 * np.log(0.5)) < 1e-12 * 1_000_000        # beta = 0: every node is log(1/2)
+    parts = sum(dg.calculate(y, lo, lo + 250_000) for lo in range(0, 1_000_000, 250_000))  # generic range kernel
+    assert rel_err(parts, total).max() < RTOL_LP                                 # additivity across node ranges
+    co = compile_on(oracle, conf)
+    do = co._ensure(2)
+    do.set_values(inits[:2])
+    lo, hi = 431_000, 441_000
+    d2 = compile_on(b200, conf)._ensure(2)
+    d2.set_values(inits[:2])
+    assert rel_err(d2.calculate(y, lo, hi), do.calculate(y, lo, hi)).max() < RTOL_LP

@@ -1,0 +1,154 @@
+"""CPU: the host layer (BUGS parsing, lowering to the node table, default sampler assignment, conjugacy
+detection, error behaviour).  Mirrors the reference's configuration tests, P/tests/testthat/test-mcmc.R:1684-1900."""
+import numpy as np
+import pytest
+
+import nimble_b200 as nb
+from nimble_b200 import table as T
+from nimble_b200.mcmc import _Lowering
+from tests import small_models as sm
+
+
+def lower(conf):
+    return _Lowering(conf.model, conf).run()
+
+
+def test_parse_nested_loops_and_links():
+    m, conf = sm.SMALL["occupancy"]()
+    names = [d.var for d in m.decls]
+    assert names == ["b0", "a0", "b1", "a1", "z", "y"]
+    y = m.decls[-1]
+    assert y.n == 300 * 4 and y.dist == T.DBINOM and y.is_data
+    # logit(p[i,j]) <- ... was inverted and inlined: prob = z[i] * ilogit(a0 + a1*w[i,j])
+    prob = y.params[1]
+    assert prob[0] == "bin" and prob[1] == T.OP_MUL and prob[3][0] == "un" and prob[3][1] == T.OP_ILOGIT
+
+
+def test_default_samplers_per_config():
+    kinds = {k: [(s.name, s.var) for s in f()[1].samplerConfs] for k, f in sm.SMALL.items()}
+    assert kinds["pump"] == [("RW", "alpha"), ("conjugate_dgamma", "beta"), ("conjugate_dgamma", "theta")]
+    assert kinds["logistic"] == [("RW", "tau_b"), ("conjugate_dnorm", "mu_b"), ("RW_block", "beta")]
+    assert kinds["lmm"] == [("conjugate_dnorm", "mu"), ("RW", "sig_u"), ("RW", "sig_e"), ("conjugate_dnorm", "u")]
+    assert kinds["occupancy"] == [("RW", "b0"), ("RW", "a0"), ("RW", "b1"), ("RW", "a1"), ("binary", "z")]
+    assert kinds["glmm"] == [("RW", "a"), ("conjugate_dgamma", "b"), ("RW", "b0"), ("RW", "b1"),
+                             ("conjugate_dgamma", "lam")]
+
+
+def test_conjugacy_links():
+    # MCMC_conjugacy.R:80-93,109-115; link classes as in cc_checkLinearity (:1397-1524)
+    m, _ = sm.SMALL["pump"]()
+    t, info = nb.check_conjugacy(m, m.decl_of("theta")[0])
+    assert t == T.SAMPLER_CONJ_GAMMA and list(info.values()) == [(T.LINK_MULTIPLICATIVE, 0)]
+    t, info = nb.check_conjugacy(m, m.decl_of("beta")[0])
+    assert list(info.values()) == [(T.LINK_IDENTITY, T.PARAM_RATE)]
+    assert nb.check_conjugacy(m, m.decl_of("alpha")[0]) is None  # dexp prior: not in the table
+    m, _ = sm.SMALL["lmm"]()
+    t, info = nb.check_conjugacy(m, m.decl_of("mu")[0])
+    assert t == T.SAMPLER_CONJ_NORMAL and list(info.values()) == [(T.LINK_ADDITIVE, 0)]
+    m, _ = sm.very_simple()
+    t, info = nb.check_conjugacy(m, m.decl_of("x")[0])
+    assert list(info.values()) == [(T.LINK_ADDITIVE, 0)]
+
+
+def test_conjugacy_not_detected_through_nonlinear_link():
+    # test-mcmc.R:1684-1793: conjugacy is lost through exp()
+    code = "{ a ~ dnorm(0, 1)\n for (i in 1:3) { y[i] ~ dnorm(exp(a), 1) } }"
+    m = nb.nimbleModel(code, data={"y": [0.1, 0.2, 0.3]}, inits={"a": 0.0})
+    assert nb.check_conjugacy(m, m.decl_of("a")[0]) is None
+    code = "{ a ~ dnorm(0, 1)\n for (i in 1:3) { y[i] ~ dnorm(3 + 2 * a * x[i], 1) } }"
+    m = nb.nimbleModel(code, constants={"x": [1.0, 2.0, 3.0]}, data={"y": [0.1, 0.2, 0.3]}, inits={"a": 0.0})
+    assert list(nb.check_conjugacy(m, m.decl_of("a")[0])[1].values()) == [(T.LINK_LINEAR, 0)]
+    # target in two parameters of the dependent -> not conjugate
+    code = "{ a ~ dgamma(1, 1)\n y ~ dnorm(a, tau = a) }"
+    m = nb.nimbleModel(code, data={"y": 0.5}, inits={"a": 1.0})
+    assert nb.check_conjugacy(m, m.decl_of("a")[0]) is None
+
+
+def test_selections_and_vectorisation():
+    m, conf = sm.SMALL["glmm"]()
+    b = lower(conf)
+    lam = [s for s in b.samplers if s.type == T.SAMPLER_CONJ_GAMMA and s.n_targets == 40][0]
+    deps = [b.deps[lam.dep_off + e] for e in range(lam.n_dep)]
+    assert [d.stage for d in deps] == [0, 1]
+    assert deps[0].sel == T.SEL_SAME and deps[1].sel == T.SEL_STRIDE and deps[1].a == 100
+    assert deps[1].link == T.LINK_MULTIPLICATIVE
+    m, conf = sm.SMALL["lmm_perm"]()
+    b = lower(conf)
+    u = [s for s in b.samplers if s.n_targets == 30][0]
+    dep = b.deps[u.dep_off + 1]
+    assert dep.sel == T.SEL_CSR
+    off, idx = b.iarr[dep.a], b.iarr[dep.b]
+    grp = m.constants["grp"].astype(int)
+    for g in (0, 7, 29):
+        assert np.all(grp[idx[off[g]:off[g + 1]]] == g + 1)
+    m, conf = sm.SMALL["occupancy"]()
+    b = lower(conf)
+    z = [s for s in b.samplers if s.type == T.SAMPLER_BINARY][0]
+    assert z.n_targets == 300 and b.deps[z.dep_off + 1].sel == T.SEL_STRIDE and b.deps[z.dep_off + 1].a == 4
+
+
+def test_fused_family_recognised_and_monitors():
+    m, conf = sm.SMALL["logistic"]()
+    cm_b = lower(conf)
+    y = cm_b.decls[-1]
+    assert y.family == T.FAM_BERN_LOGIT_INPROD and y.fam_arg[2] == 7
+    assert len(cm_b.monitors) == 2 + 7
+    blk = cm_b.samplers[-1]
+    assert blk.type == T.SAMPLER_RW_BLOCK and blk.d == 7 and blk.n_dep == 2
+    assert cm_b.deps[blk.dep_off].sel == T.SEL_RANGE and cm_b.deps[blk.dep_off + 1].sel == T.SEL_ALL
+
+
+def test_non_separable_targets_fall_back_to_sequential():
+    code = "{ for (j in 1:3) { b[j] ~ dnorm(0, 1) }\n for (i in 1:5) { y[i] ~ dpois(exp(inprod(X[i,1:3], b[1:3]))) } }"
+    X = np.arange(15.0).reshape(5, 3) / 10
+    m = nb.nimbleModel(code, constants={"X": X}, data={"y": [1, 0, 2, 3, 1]}, inits={"b": [0.0, 0.0, 0.0]})
+    b = lower(nb.configureMCMC(m))
+    assert [s.n_targets for s in b.samplers] == [1, 1, 1]
+    assert [s.target_slot for s in b.samplers] == [0, 1, 2]
+
+
+def test_errors_match_reference_behaviour():
+    m, conf = sm.SMALL["pump"]()
+    with pytest.raises(ValueError, match="more than one target"):      # MCMC_samplers.R:348
+        conf.addSampler("theta", type="RW")
+    with pytest.raises(NotImplementedError, match="no CPU fallback"):
+        conf.addSampler("alpha", type="slice")
+    with pytest.raises(nb.ModelError):
+        conf.addSampler("nosuch", type="RW")
+    with pytest.raises(RuntimeError, match="compileNimble"):
+        nb.buildMCMC(conf).run(10)
+    with pytest.raises(TypeError):
+        nb.runMCMC(nb.buildMCMC(conf), niter=10)                        # MCMC_run.R:100 (is.Cnf)
+    with pytest.raises(ValueError, match="log=TRUE and reflective=TRUE"):  # MCMC_samplers.R:350
+        conf.addSampler("alpha", type="RW", control={"log": True, "reflective": True})
+        lower(conf)
+    with pytest.raises(nb.ModelError, match="initial values"):
+        nb.nimbleModel("{ a ~ dnorm(0,1) }").init_vector()
+    with pytest.raises(nb.ModelError, match="outside the supported set"):
+        nb.nimbleModel("{ a ~ dweib(1,1) }", inits={"a": 1})
+
+
+def test_runmcmc_shapes_and_names(oracle):
+    m, conf = sm.SMALL["pump"]()
+    cm = nb.compileNimble(nb.buildMCMC(conf), backend=oracle)
+    one = nb.runMCMC(cm, niter=50, nburnin=10, nchains=1, setSeed=3)
+    assert one.shape == (40, 12) and one.colnames[:3] == ["alpha", "beta", "theta[1]"]
+    three = nb.runMCMC(cm, niter=50, nburnin=10, nchains=3, setSeed=3, inits=lambda: {"alpha": 2.0})
+    assert list(three) == ["chain1", "chain2", "chain3"]              # MCMC_run.R:183-189
+    assert not np.array_equal(three["chain1"], three["chain2"])
+    out = nb.runMCMC(cm, niter=50, nchains=2, setSeed=3, summary=True)
+    assert "Mean" in out["summary"]["alpha"]
+    with pytest.raises(ValueError, match="length nchains"):
+        nb.runMCMC(cm, niter=5, nchains=3, inits=[{}, {}])
+
+
+def test_ess_estimator():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(4000)
+    assert 3000 < nb.effective_size(x) < 5000
+    ar = np.empty(4000)
+    ar[0] = 0
+    for i in range(1, 4000):
+        ar[i] = 0.9 * ar[i - 1] + x[i]
+    ess = nb.effective_size(ar)
+    assert 100 < ess < 400  # theory: n (1-rho)/(1+rho) = 210

@@ -1,0 +1,117 @@
+"""CPU: pin the oracle's samplers and driver against the known-answer fixtures the reference's own MCMC tests
+hold (P/tests/testthat/test-mcmc.R), with the reference's tolerances.  These are the only reference fixtures
+for this path that do not depend on R's Mersenne-Twister stream."""
+import numpy as np
+import pytest
+
+import nimble_b200 as nb
+from tests import small_models as sm
+from tests.helpers import compile_on, pooled, run
+
+
+def test_pump_posterior_means(oracle):
+    # test-mcmc.R:164-179 (means +- tolerance); JAGS table P/inst/classic-bugs/vol1/pump/bench-test1.R
+    m, conf = sm.SMALL["pump"]()
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 10000, 1000, seed=11))
+    mean = dict(zip(cm.colnames, s.mean(0)))
+    for name, want, tol in (("theta[1]", 0.06, 0.01), ("theta[2]", 0.10, 0.01), ("theta[9]", 1.58, 0.05),
+                            ("theta[10]", 1.97, 0.05), ("alpha", 0.73, 0.1), ("beta", 0.98, 0.1)):
+        assert abs(mean[name] - want) < tol, (name, mean[name])
+    sd = dict(zip(cm.colnames, s.std(0)))
+    assert abs(sd["alpha"] - 0.2721) < 0.03 and abs(sd["beta"] - 0.5488) < 0.06
+
+
+def test_pump_default_samplers(oracle):
+    # mcmcTestLog_Correct.Rout pump block: RW on alpha, conjugate_dgamma_dgamma on beta, conjugate on theta[i]
+    m, conf = sm.SMALL["pump"]()
+    kinds = [(s.name, s.var) for s in conf.samplerConfs]
+    assert kinds == [("RW", "alpha"), ("conjugate_dgamma", "beta"), ("conjugate_dgamma", "theta")]
+
+
+def test_very_simple(oracle):
+    # test-mcmc.R:209-227
+    m, conf = sm.very_simple()
+    assert [s.name for s in conf.samplerConfs][0] == "conjugate_dnorm"
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 10000, 500, seed=3))
+    x, z = s[:, cm.colnames.index("x")], s[:, cm.colnames.index("z")]
+    assert abs(x.mean() - 6 / 5) < 0.1 and abs(z.mean() - 5) < 0.1
+    assert abs(x.std() - 1 / np.sqrt(5)) < 0.05 and abs(z.std() - 0.5) < 0.05
+
+
+@pytest.mark.parametrize("kind", ["default", "block_scalars", "block_vector", "rw"])
+def test_basic_block(oracle, kind):
+    # test-mcmc.R:284-332
+    m, conf = sm.basic_block(kind)
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 10000, 1000, seed=5))
+    assert np.all(np.abs(s.mean(0) - np.array([-2 / 3, 0, 2 / 3])) < 0.1)
+    assert np.all(np.abs(s.var(0) - 1 / 3) < 0.05)
+
+
+def test_binary_sampler(oracle):
+    # test-mcmc.R:1379-1443
+    m, conf = sm.binary_model()
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 50000, 0, seed=9))
+    want = dict(a=.5, b=.6, c=.05, d=.2, e=.9, f=.9525, g=.0475, h=.5)
+    for k, v in want.items():
+        assert abs(s[:, cm.colnames.index(k)].mean() - v) < 0.004, k
+
+
+def test_binary_out_of_bounds(oracle):
+    # test-mcmc.R:1445-1469: NaN / -Inf logProbs must never be accepted
+    m, conf = sm.binary_out_of_bounds()
+    assert [s.name for s in conf.samplerConfs] == ["binary", "binary"]
+    cm = compile_on(oracle, conf)
+    s = run(cm, np.tile(m.init_vector(), (3, 1)), 100, 0, seed=0)
+    assert np.all(s == 1.0)
+
+
+def test_rw_block_adapts_to_correlated_target(oracle):
+    # spirit of test-mcmc.R:597-666 (RW_block recovers a non-trivial covariance), on independent normals with
+    # very different scales: mean (1,2,3), var (1,2,3)
+    code = "{ x[1] ~ dnorm(1, var = 1)\n x[2] ~ dnorm(2, var = 2)\n x[3] ~ dnorm(3, var = 3) }"
+    m = nb.nimbleModel(code, inits={"x": [0.0, 0.0, 0.0]})
+    conf = nb.configureMCMC(m, nodes=[], monitors=["x"])
+    conf.addSampler("x[1:3]", type="RW_block")
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 30000, 5000, seed=21))
+    assert np.all(np.abs(s.mean(0) - np.array([1, 2, 3])) < 0.15)
+    assert np.all(np.abs(s.var(0) - np.array([1, 2, 3])) < 0.35)
+    pc = cm.dm.sampler_state(0, 2)[:, 0].reshape(3, 3)
+    assert pc[0, 0] < pc[1, 1] < pc[2, 2]
+
+
+def test_reset_false_continues_and_appends(oracle):
+    # MCMC_build.R:243-263: reset=FALSE keeps sampler state and appends to mvSamples
+    m, conf = sm.SMALL["pump"]()
+    cm = compile_on(oracle, conf)
+    init = np.tile(m.init_vector(), (2, 1))
+    a = run(cm, init, 300, 0, seed=4).copy()
+    b = run(cm, init, 200, 0, seed=4, reset=False)
+    assert b.shape[1] == 500 and np.array_equal(b[:, :300], a)
+    cm2 = compile_on(oracle, conf)
+    c = run(cm2, init, 500, 0, seed=4)
+    assert np.array_equal(b, c)  # continuation == one long run (same counter-based draws)
+
+
+def test_thin_and_burnin_rows(oracle):
+    m, conf = sm.SMALL["pump"]()
+    cm = compile_on(oracle, conf)
+    s = run(cm, np.tile(m.init_vector(), (1, 1)), 103, 13, thin=4, seed=1)
+    assert s.shape[1] == (103 - 13) // 4
+    full = run(compile_on(oracle, conf), np.tile(m.init_vector(), (1, 1)), 103, 0, seed=1)
+    assert np.array_equal(s[0], full[0][13 + 3::4][: s.shape[1]])
+
+
+def test_run_argument_errors(oracle):
+    # MCMC_build.R:231-240
+    m, conf = sm.SMALL["pump"]()
+    cm = compile_on(oracle, conf)
+    init = np.tile(m.init_vector(), (1, 1))
+    for kw, msg in ((dict(niter=-1), "niter < 0"), (dict(niter=5, nburnin=-1), "nburnin < 0"),
+                    (dict(niter=5, nburnin=6), "nburnin > niter"), (dict(niter=5, thin=0), "thin < 1")):
+        with pytest.raises(ValueError, match=msg):
+            cm.run_chains(init, **kw)
