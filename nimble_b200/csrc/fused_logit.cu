@@ -239,7 +239,7 @@ void fused_bern_logit_launch(const double* Xpad, const double* y, int n, int p, 
   size_t smem = sizeof(double) * ((size_t)FT_M * P4 + (size_t)P4 * LDB + FT_M + 4 * FT_NC) + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_fused_bern_logit, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(k_fused_bern_logit, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
     attr_set = true;
   }
   int chunks = chunks_for(n);
