@@ -698,8 +698,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di] && lo == 0 && hi == d.n && !idx) {
     int nt = fused_bern_logit_tiles(d.n);
     if ((size_t)nt * C > m->partials_cap) return fail("internal: partials scratch too small (fused)");
-    fused_bern_logit_launch(m->d_xpad[di], m->d_darr[d.value_ref], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C,
-                            m->d_partials, m->stream);
+    fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
     m->launches++;
     k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
     m->launches++;
@@ -910,7 +909,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     size_t len = fused_bern_logit_xpad_len(d.n, p);
     if (len == 0) { d.family = NIMB_FAM_GENERIC; continue; }
     TRY(dev_alloc(m, &m->d_xpad[i], len));
-    fused_bern_logit_prepare_x(m->d_darr[xid], d.n, p, ld, m->d_xpad[i], m->stream);
+    fused_bern_logit_prepare_x(m->d_darr[xid], m->d_darr[d.value_ref], d.n, p, ld, m->d_xpad[i], m->stream);
   }
   // sampler state + execution shape
   m->sdev.resize(m->samplers.size());
@@ -1050,7 +1049,7 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
   CK(cudaEventRecord(m->ev0, m->stream));
   for (int r = 0; r < reps; r++) {
     if (fused)
-      fused_bern_logit_launch(m->d_xpad[di], m->d_darr[d.value_ref], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
+      fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
     else {
       dim3 grid(eval_tiles(C, d.n), (C + cw - 1) / cw);
       nimb200_dep dd{};

@@ -36,8 +36,9 @@ struct SamplerDev {
 // Returns the number of node tiles written (0 if the shape is unsupported and the generic kernel must run).
 int fused_bern_logit_tiles(int n);
 size_t fused_bern_logit_xpad_len(int n, int p);
-void fused_bern_logit_prepare_x(const double* X_rowmajor_dev, int n, int p, int ld, double* Xpad_dev, cudaStream_t st);
-void fused_bern_logit_launch(const double* Xpad, const double* y, int n, int p, const double* state, int beta_slot,
-                             int C, double* partials, cudaStream_t st);
+void fused_bern_logit_prepare_x(const double* X_rowmajor_dev, const double* y_dev, int n, int p, int ld, double* Xpad_dev,
+                                cudaStream_t st);
+void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
+                             cudaStream_t st);
 
 }  // namespace nimb

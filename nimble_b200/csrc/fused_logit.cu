@@ -21,10 +21,11 @@
 
 namespace nimb {
 
-static const int FT_M = 128;      // nodes per tile
-static const int FT_NC = 64;      // chains per block
+static const int FT_M = 128;      // nodes per tile (one TMA bulk copy)
+static const int FT_NC = 64;      // chains per block: 4 warps x 16 chains, two such warp groups split the rows
 static const int FT_THREADS = 256;
 static const int FT_MAXP4 = 64;
+static const int FT_MAXK = FT_MAXP4 / 4;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -55,126 +56,113 @@ __device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, do
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-// bd0(x, np) with x = 1 (nmath/bd0.c), as reached from dbinom_raw with n = 1
-__device__ __forceinline__ double bd0_one(double np) {
-  if (!isfinite(np) || np == 0.0) return NAN;
-  if (fabs(1.0 - np) < 0.1 * (1.0 + np)) {
-    double v = (1.0 - np) / (1.0 + np);
-    double s = (1.0 - np) * v;
-    if (fabs(s) < DBL_MIN) return s;
-    double ej = 2 * v;
-    v = v * v;
-    for (int j = 1; j < 1000; j++) {
-      ej *= v;
-      double s1 = s + ej / (double)((j << 1) + 1);
-      if (s1 == s) return s1;
-      s = s1;
-    }
-  }
-  return log(1.0 / np) + np - 1.0;
-}
-
-// dbinom(y, 1, ilogit(eta), log = 1) for y in {0, 1}: nmath dbinom -> dbinom_raw(x, 1, p, 1-p)
-__device__ __forceinline__ double bern_logit_lp(double eta, double y) {
-  double p = 1. / (1. + exp(-eta));
-  if (isnan(p)) return p;
-  double q = 1 - p;
-  if (y == 0.0) {
-    if (p == 0) return 0.;
-    if (q == 0) return -INFINITY;
-    return (p < 0.1) ? -bd0_one(q) - p : log(q);
-  }
-  if (p == 0) return -INFINITY;
-  if (q == 0) return 0.;
-  return (q < 0.1) ? -bd0_one(p) - q : log(p);
+// dbinom(y, 1, ilogit(eta), log = 1) for y in {0, 1}.
+// nmath: dbinom -> dbinom_raw(x, 1, p, q = 1-p):  x = 0: p < 0.1 ? -bd0(1, q) - p : log(q);  x = 1: q < 0.1 ? -bd0(1, p) - q : log(p)
+// (plus p == 0 / q == 0 shortcuts).  In exact arithmetic -bd0(1, q) - p = log(q) + ((1 - q) - p), i.e. log(q) plus the rounding
+// error of q = fl(1 - p), and -bd0(1, p) - q = log(p) because 1 - p is exact for p > 0.9.  So every branch is
+//   log(t) + corr,  t = y ? p : q,  corr = y ? 0 : ((1 - q) - p) / q
+// to < 1e-15 relative, with the same p = 1/(1 + exp(-eta)) rounding sequence as Utils.h:187 and the same limits
+// (p == 0: y=0 -> 0, y=1 -> -Inf;  q == 0: y=0 -> -Inf, y=1 -> 0).  No data-dependent loop, no divergent branch.
+__device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {
+  double e = exp(-eta);
+  double p = 1.0 / (1.0 + e);
+  double q = 1.0 - p;
+  double t = y1 ? p : q;
+  double delta = (1.0 - q) - p;                       // exact
+  double corr = (y1 || q == 0.0) ? 0.0 : delta * (double)__frcp_rn((float)q);
+  return log(t) + corr;
 }
 
 // grid: (node chunks, chain tiles).  partials[blockIdx.x][C]
+// smem: 2 stages x { X tile [FT_M][P4], y tile [FT_M] }, 2 mbarriers.
 __global__ void __launch_bounds__(FT_THREADS, 2)
-k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y, int n, int P4, int p,
+k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ ypad, int n, int P4, int p,
                    const double* __restrict__ state, int beta_slot, int C, int tiles_per_chunk,
                    double* __restrict__ partials) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int LDB = FT_NC + 4;  // (k*LDB*2 + n*2) mod 32 distinct over a half warp -> conflict-free B fragments
-  double* Xs = (double*)smem_raw;                       // [FT_M][P4]
-  double* Bs = Xs + FT_M * P4;                          // [P4][LDB]
-  double* ys = Bs + P4 * LDB;                           // [FT_M]
-  double* red = ys + FT_M;                              // [4][FT_NC]
-  uint64_t* bar = (uint64_t*)(red + 4 * FT_NC);
+  const int stage_doubles = FT_M * P4 + FT_M;
+  double* stage0 = (double*)smem_raw;
+  double* red = stage0 + 2 * stage_doubles;             // [2][FT_NC]
+  uint64_t* bar = (uint64_t*)(red + 2 * FT_NC);          // [2]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp & 3, wn = warp >> 2;              // warp tile: nodes wm*32.., chains wn*32..
-  const int chain0 = blockIdx.y * FT_NC;
+  const int wn = warp & 3, wg = warp >> 2;               // warp: chains wn*16 .. +15, rows wg*64 .. +63 of each tile
+  const int chain0 = blockIdx.y * FT_NC + wn * 16;
+  const int nk = P4 >> 2;
 
-  for (int e = tid; e < P4 * FT_NC; e += FT_THREADS) {  // stage this block's beta columns (zero padded)
-    int k = e / FT_NC, cc = e % FT_NC;
-    int c = chain0 + cc;
-    Bs[k * LDB + cc] = (k < p && c < C) ? state[(size_t)(beta_slot + k) * C + c] : 0.0;
+  // B fragments stay in registers for the whole kernel: beta[k0 + lane%4][chain0 + nt*8 + lane/4]
+  double bf[FT_MAXK][2];
+#pragma unroll
+  for (int ks = 0; ks < FT_MAXK; ks++) {
+#pragma unroll
+    for (int nt = 0; nt < 2; nt++) {
+      int k = ks * 4 + (lane & 3), c = chain0 + nt * 8 + (lane >> 2);
+      bf[ks][nt] = (ks < nk && k < p && c < C) ? state[(size_t)(beta_slot + k) * C + c] : 0.0;
+    }
   }
   if (tid == 0) {
-    mbar_init(bar, 1);
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
-  double csum[8];
-#pragma unroll
-  for (int j = 0; j < 8; j++) csum[j] = 0.0;
-
+  double csum[4] = {0.0, 0.0, 0.0, 0.0};
   const int ntiles_total = (n + FT_M - 1) / FT_M;
   const int tile_lo = blockIdx.x * tiles_per_chunk;
   const int tile_hi = min(ntiles_total, tile_lo + tiles_per_chunk);
-  const uint32_t tile_bytes = (uint32_t)(FT_M * P4 * sizeof(double));
-  uint32_t phase = 0;
+  const uint32_t x_bytes = (uint32_t)(FT_M * P4 * sizeof(double)), y_bytes = (uint32_t)(FT_M * sizeof(double));
 
+  if (tid == 0 && tile_lo < tile_hi) {
+    mbar_expect_tx(&bar[0], x_bytes + y_bytes);
+    bulk_g2s(stage0, Xpad + (size_t)tile_lo * FT_M * P4, x_bytes, &bar[0]);
+    bulk_g2s(stage0 + FT_M * P4, ypad + (size_t)tile_lo * FT_M, y_bytes, &bar[0]);
+  }
   for (int tile = tile_lo; tile < tile_hi; tile++) {
-    const int node0 = tile * FT_M;
-    if (tid == 0) {
-      mbar_expect_tx(bar, tile_bytes);
-      bulk_g2s(Xs, Xpad + (size_t)node0 * P4, tile_bytes, bar);
+    const int it = tile - tile_lo, b = it & 1;
+    if (tid == 0 && tile + 1 < tile_hi) {  // prefetch the next tile into the other stage (freed by the last __syncthreads)
+      double* nxt = stage0 + (b ^ 1) * stage_doubles;
+      mbar_expect_tx(&bar[b ^ 1], x_bytes + y_bytes);
+      bulk_g2s(nxt, Xpad + (size_t)(tile + 1) * FT_M * P4, x_bytes, &bar[b ^ 1]);
+      bulk_g2s(nxt + FT_M * P4, ypad + (size_t)(tile + 1) * FT_M, y_bytes, &bar[b ^ 1]);
     }
-    if (tid < FT_M) ys[tid] = (node0 + tid < n) ? y[node0 + tid] : -1.0;  // -1 marks padding rows
-    mbar_wait(bar, phase);
-    phase ^= 1;
-    __syncthreads();
-
-    double acc[4][4][2];
+    mbar_wait(&bar[b], (uint32_t)((it >> 1) & 1));
+    const double* Xs = stage0 + b * stage_doubles;
+    const double* ys = Xs + FT_M * P4;
+    const double* xa = Xs + (wg * 64 + (lane >> 2)) * P4 + (lane & 3);
+#pragma unroll 1
+    for (int mp = 0; mp < 4; mp++) {  // two 8-row m-tiles at a time -> 4 independent accumulator chains
+      double acc[2][2][2] = {{{0.0, 0.0}, {0.0, 0.0}}, {{0.0, 0.0}, {0.0, 0.0}}};
+      const double* x0 = xa + (mp * 16) * P4;
 #pragma unroll
-    for (int a = 0; a < 4; a++)
+      for (int ks = 0; ks < FT_MAXK; ks++) {
+        if (ks < nk) {
+          double a0 = x0[ks * 4], a1 = x0[8 * P4 + ks * 4];
+          dmma_m8n8k4(acc[0][0][0], acc[0][0][1], a0, bf[ks][0]);
+          dmma_m8n8k4(acc[0][1][0], acc[0][1][1], a0, bf[ks][1]);
+          dmma_m8n8k4(acc[1][0][0], acc[1][0][1], a1, bf[ks][0]);
+          dmma_m8n8k4(acc[1][1][0], acc[1][1][1], a1, bf[ks][1]);
+        }
+      }
+      // epilogue on the accumulators: lane holds row (lane>>2) of each m-tile, columns 2*(lane&3)+{0,1} of each n-tile
 #pragma unroll
-      for (int b = 0; b < 4; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
-
-    const double* xa = Xs + (wm * 32 + (lane >> 2)) * P4 + (lane & 3);
-    const double* bb = Bs + (lane & 3) * LDB + wn * 32 + (lane >> 2);
-    for (int k0 = 0; k0 < P4; k0 += 4) {
-      double af[4], bf[4];
+      for (int mt = 0; mt < 2; mt++) {
+        double yv = ys[wg * 64 + mp * 16 + mt * 8 + (lane >> 2)];
+        bool live = yv >= 0.0, y1 = yv != 0.0;          // -1 marks the zero-padded rows past n
 #pragma unroll
-      for (int a = 0; a < 4; a++) af[a] = xa[a * 8 * P4 + k0];
-#pragma unroll
-      for (int b = 0; b < 4; b++) bf[b] = bb[k0 * LDB + b * 8];
-#pragma unroll
-      for (int a = 0; a < 4; a++)
-#pragma unroll
-        for (int b = 0; b < 4; b++) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
-    }
-    // epilogue on the accumulators: lane holds rows (lane>>2) of each m-tile, columns 2*(lane&3)+{0,1} of each n-tile
-#pragma unroll
-    for (int a = 0; a < 4; a++) {
-      double yv = ys[wm * 32 + a * 8 + (lane >> 2)];
-      if (yv >= 0.0) {
-#pragma unroll
-        for (int b = 0; b < 4; b++) {
-          csum[b * 2 + 0] += bern_logit_lp(acc[a][b][0], yv);
-          csum[b * 2 + 1] += bern_logit_lp(acc[a][b][1], yv);
+        for (int nt = 0; nt < 2; nt++) {
+          double l0 = bern_logit_lp(acc[mt][nt][0], y1), l1 = bern_logit_lp(acc[mt][nt][1], y1);
+          csum[nt * 2 + 0] += live ? l0 : 0.0;
+          csum[nt * 2 + 1] += live ? l1 : 0.0;
         }
       }
     }
-    __syncthreads();  // everyone is done with Xs / ys before the next bulk copy lands
+    __syncthreads();  // everyone is done with stage b before it is refilled
   }
 
-  // reduce over the 8 row-lanes of the warp (lanes with equal lane&3), then over the 4 node-warps
+  // reduce over the 8 row-lanes of the warp (lanes with equal lane&3), then over the 2 row groups
 #pragma unroll
-  for (int j = 0; j < 8; j++) {
+  for (int j = 0; j < 4; j++) {
     double v = csum[j];
     v += __shfl_xor_sync(0xffffffffu, v, 4);
     v += __shfl_xor_sync(0xffffffffu, v, 8);
@@ -183,25 +171,27 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
   }
   if ((lane >> 2) == 0) {
 #pragma unroll
-    for (int b = 0; b < 4; b++) {
-      red[wm * FT_NC + wn * 32 + b * 8 + 2 * (lane & 3) + 0] = csum[b * 2 + 0];
-      red[wm * FT_NC + wn * 32 + b * 8 + 2 * (lane & 3) + 1] = csum[b * 2 + 1];
+    for (int nt = 0; nt < 2; nt++) {
+      red[wg * FT_NC + wn * 16 + nt * 8 + 2 * (lane & 3) + 0] = csum[nt * 2 + 0];
+      red[wg * FT_NC + wn * 16 + nt * 8 + 2 * (lane & 3) + 1] = csum[nt * 2 + 1];
     }
   }
   __syncthreads();
   if (tid < FT_NC) {
-    int c = chain0 + tid;
-    if (c < C) partials[(size_t)blockIdx.x * C + c] = ((red[tid] + red[FT_NC + tid]) + red[2 * FT_NC + tid]) + red[3 * FT_NC + tid];
+    int c = blockIdx.y * FT_NC + tid;
+    if (c < C) partials[(size_t)blockIdx.x * C + c] = red[tid] + red[FT_NC + tid];
   }
 }
 
 // X [n][ld] (first p columns used) -> Xpad [ntiles*FT_M][P4], zero padded
-__global__ void k_pad_x(const double* __restrict__ X, int n, int p, int ld, int P4, size_t total, double* __restrict__ Xpad) {
+__global__ void k_pad_x(const double* __restrict__ X, const double* __restrict__ y, int n, int p, int ld, int P4, size_t total,
+                        double* __restrict__ Xpad, double* __restrict__ ypad) {
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= total) return;
   size_t i = gid / P4;
   int k = (int)(gid % P4);
   Xpad[gid] = (i < (size_t)n && k < p) ? X[i * ld + k] : 0.0;
+  if (k == 0) ypad[i] = i < (size_t)n ? y[i] : -1.0;  // -1 marks padding rows
 }
 
 static int p4_of(int p) { return (p + 3) & ~3; }
@@ -219,34 +209,35 @@ static int chunks_for(int n) {
 
 int fused_bern_logit_tiles(int n) { return chunks_for(n); }
 
+// doubles needed for the padded copy: X tiles [ntiles*FT_M][P4] followed by y tiles [ntiles*FT_M]
 size_t fused_bern_logit_xpad_len(int n, int p) {
   if (p < 1 || p4_of(p) > FT_MAXP4) return 0;
   if (getenv("NIMB200_NO_FUSED")) return 0;
   size_t ntiles = (size_t)(n + FT_M - 1) / FT_M;
-  return ntiles * FT_M * p4_of(p);
+  return ntiles * FT_M * p4_of(p) + ntiles * FT_M;
+}
+static size_t xpad_x_len(int n, int p) { return (size_t)((n + FT_M - 1) / FT_M) * FT_M * p4_of(p); }
+
+void fused_bern_logit_prepare_x(const double* X, const double* y, int n, int p, int ld, double* Xpad, cudaStream_t st) {
+  int P4 = p4_of(p);
+  size_t total = xpad_x_len(n, p);
+  k_pad_x<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(X, y, n, p, ld, P4, total, Xpad, Xpad + total);
 }
 
-void fused_bern_logit_prepare_x(const double* X, int n, int p, int ld, double* Xpad, cudaStream_t st) {
+void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
+                             cudaStream_t st) {
   int P4 = p4_of(p);
-  size_t total = fused_bern_logit_xpad_len(n, p);
-  k_pad_x<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(X, n, p, ld, P4, total, Xpad);
-}
-
-void fused_bern_logit_launch(const double* Xpad, const double* y, int n, int p, const double* state, int beta_slot, int C,
-                             double* partials, cudaStream_t st) {
-  int P4 = p4_of(p);
-  int LDB = FT_NC + 4;
-  size_t smem = sizeof(double) * ((size_t)FT_M * P4 + (size_t)P4 * LDB + FT_M + 4 * FT_NC) + 16;
+  size_t smem = sizeof(double) * (2 * ((size_t)FT_M * P4 + FT_M) + 2 * FT_NC) + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_fused_bern_logit, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+    cudaFuncSetAttribute(k_fused_bern_logit, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
     attr_set = true;
   }
   int chunks = chunks_for(n);
   int ntiles = (n + FT_M - 1) / FT_M;
   int tpc = (ntiles + chunks - 1) / chunks;
   dim3 grid(chunks, (C + FT_NC - 1) / FT_NC);
-  k_fused_bern_logit<<<grid, FT_THREADS, smem, st>>>(Xpad, y, n, P4, p, state, beta_slot, C, tpc, partials);
+  k_fused_bern_logit<<<grid, FT_THREADS, smem, st>>>(Xpad, Xpad + xpad_x_len(n, p), n, P4, p, state, beta_slot, C, tpc, partials);
 }
 
 }  // namespace nimb
