@@ -255,6 +255,22 @@ int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, doubl
 int nimb200_time_calculate(nimb200_model *m, int32_t decl, int32_t reps, double *ms_avg);
 int nimb200_measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflops);
 
+/* No counterpart in the reference (NIMBLE has no device code and nothing in it is asked to run without
+ * allocating).  Per-chain block log-probability of y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))) -- the quantity
+ * nimb200_calculate() returns for such a declaration -- for callers that must not allocate device memory: a host
+ * program whose own memory manager owns the whole GPU (start-up arena, fixed per-worker budget), or a steady-state
+ * loop that cannot afford the device-wide synchronisation of cudaMalloc/cudaFree.  Needs no nimb200_model.
+ * All pointers are DEVICE pointers supplied by the caller: X row-major [n][ld] (first p columns used), y [n] in {0,1},
+ * beta [p][nchains] (chain index fastest, like the model state), out [nchains].  The work is enqueued on cuda_stream
+ * (a cudaStream_t, NULL = default stream) and is NOT synchronised.  The kernel's scratch is a built-in device array:
+ * nchains <= NIMB200_NOALLOC_MAX_CHAINS and p <= 64, otherwise an error is returned; the array (2.3 MiB) stays
+ * resident on every GPU that loaded the library; the first call on a device looks its address up, so make that call
+ * before starting any stream capture; calls share the array, so calls that overlap on one GPU race (each call
+ * rewrites all of the array it reads, nothing needs clearing in between).  Calls no cudaMalloc/cudaFree. */
+#define NIMB200_NOALLOC_MAX_CHAINS 2048
+int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
+                                             const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);
+
 /* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1) or gamma(shape a, scale 1)
  * variates (kind 2) that sampler `sampler` would consume on the device for (chain, iter, target), so the
  * host can replay identical draws into another implementation. */

@@ -29,6 +29,7 @@ using namespace nimb;
 // ------------------------------------------------------------------------------------------------ errors
 static thread_local std::string g_err;
 static int fail(const std::string& s) { g_err = s; return 1; }
+namespace nimb { void set_error(const std::string& s) { g_err = s; } }  // for entry points in other translation units
 #define CK(call)                                                                              \
   do {                                                                                        \
     cudaError_t e_ = (call);                                                                  \
