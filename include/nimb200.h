@@ -254,6 +254,12 @@ int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, doubl
  * behind nimb200_calculate(decl, whole range), and live FP64 peaks (DFMA loop, FP64 mma.sync loop). */
 int nimb200_time_calculate(nimb200_model *m, int32_t decl, int32_t reps, double *ms_avg);
 int nimb200_measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflops);
+/* same, for a loop that issues FP64 mma.sync and DFMA together (equal flops of each): tells whether the FP64 tensor
+ * sub-pipe and the FP64 pipe add up or share their multipliers. */
+int nimb200_measure_fp64_mixed(int device, double *tflops);
+/* diagnostic: the fused kernels' own exp (which=0) / log (1) / reciprocal (2) / dbern-logit log-density for y=0 (3),
+ * y=1 (4) applied to a host array, so that tests can measure their accuracy against libm. */
+int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
 
 /* No counterpart in the reference (NIMBLE has no device code and nothing in it is asked to run without
  * allocating).  Per-chain block log-probability of y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))) -- the quantity

@@ -1,0 +1,97 @@
+// fastmath.cuh -- FP64 exp / log / reciprocal for the fused kernels (sm_100a).
+//
+// Why not CUDA's exp()/log(): in the fused logistic kernel they were ~2/3 of the issued instructions without being
+// FP64 work -- nvcc materialises every 64-bit polynomial coefficient with a UMOV / IMAD.MOV pair at each use (ncu,
+// profiles/r1a_summary.md: 198 warp instructions per 32 evaluations, 61 of them FP64).  Here the coefficients sit in
+// __constant__ memory and enter the DFMAs as constant-bank operands, the range reduction is the minimum integer work,
+// and there is no slow-path call.  Accuracy target: <= 1 ulp-ish (checked against libm on the GPU by
+// tests/test_gpu_parity.py::test_fastmath_accuracy), far inside the 1e-12 parity bar.
+#pragma once
+#include <cstdint>
+
+namespace nimb {
+
+// exp: r^k/k! for k = 13 .. 2 (Horner order), |r| <= ln2/2  ->  truncation < 4e-18 relative
+__device__ __constant__ double c_exp_poly[12] = {
+    1.0 / 6227020800.0, 1.0 / 479001600.0, 1.0 / 39916800.0, 1.0 / 3628800.0, 1.0 / 362880.0, 1.0 / 40320.0,
+    1.0 / 5040.0,       1.0 / 720.0,       1.0 / 120.0,      1.0 / 24.0,      1.0 / 6.0,      0.5};
+// log: 2*atanh(s) = 2s (1 + z/3 + z^2/5 + ...), z = s^2 <= 0.0295: 1/(2j+1) for j = 10 .. 1
+__device__ __constant__ double c_log_poly[10] = {1.0 / 21.0, 1.0 / 19.0, 1.0 / 17.0, 1.0 / 15.0, 1.0 / 13.0,
+                                                 1.0 / 11.0, 1.0 / 9.0,  1.0 / 7.0,  1.0 / 5.0,  1.0 / 3.0};
+__device__ __constant__ double c_misc[6] = {
+    1.4426950408889634,       // log2(e)
+    6755399441055744.0,       // 2^52 + 2^51: round-to-integer magic
+    -6.93147180559945286e-01, // -ln2_hi
+    -2.31904681384629956e-17, // -ln2_lo
+    6.93147180559945286e-01,  // ln2_hi
+    2.31904681384629956e-17   // ln2_lo
+};
+
+__device__ __forceinline__ double rcp_approx(double a) {  // >= 20 good bits (MUFU.RCP64H)
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  return y;
+}
+
+// 1/a for normal a in [2^-1000, 2^1000]: three Newton steps, last one on the residual (faithfully rounded)
+__device__ __forceinline__ double rcp_f64(double a) {
+  double y = rcp_approx(a);
+  double e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  return fma(y, e, y);
+}
+
+__device__ __forceinline__ double exp_f64(double x) {
+  x = fmin(fmax(x, -746.0), 710.0);  // beyond: 0 / +Inf after scaling anyway (NaN passes through fmin/fmax? no: handled by caller)
+  double t = fma(x, c_misc[0], c_misc[1]);
+  int n = __double2loint(t);
+  t = t - c_misc[1];
+  double r = fma(t, c_misc[2], x);
+  r = fma(t, c_misc[3], r);
+  double p = c_exp_poly[0];
+#pragma unroll
+  for (int j = 1; j < 12; j++) p = fma(p, r, c_exp_poly[j]);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  int n1 = n >> 1, n2 = n - n1;
+  double s1 = __hiloint2double((n1 + 1023) << 20, 0), s2 = __hiloint2double((n2 + 1023) << 20, 0);
+  return (p * s1) * s2;
+}
+
+// log(t) for t >= 0 (t = 0 -> -Inf, +Inf -> +Inf, NaN -> NaN)
+__device__ __forceinline__ double log_f64(double t) {
+  int hi = __double2hiint(t), lo = __double2loint(t);
+  int k = 0;
+  if (hi < 0x00100000) {  // zero, subnormal (or negative: not produced by the callers)
+    if (t == 0.0) return -INFINITY;
+    t = t * 18014398509481984.0;  // 2^54
+    hi = __double2hiint(t); lo = __double2loint(t);
+    k = -54;
+  }
+  if (hi >= 0x7ff00000) return t + t;  // Inf / NaN
+  k += (hi >> 20) - 1023;
+  hi = (hi & 0x000fffff) | 0x3ff00000;
+  if (hi > 0x3ff6a09e) { hi -= 0x00100000; k += 1; }  // m > sqrt(2): halve
+  double m = __hiloint2double(hi, lo);
+  double f = m - 1.0, g = m + 1.0;
+  double y = rcp_approx(g);
+  double e = fma(-g, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-g, y, 1.0);
+  y = fma(y, e, y);
+  double s = f * y;
+  s = fma(fma(-s, g, f), y, s);  // one residual correction of the quotient
+  double z = s * s;
+  double P = c_log_poly[0];
+#pragma unroll
+  for (int j = 1; j < 10; j++) P = fma(P, z, c_log_poly[j]);
+  double s2 = s + s;
+  double lm = fma(s2 * z, P, s2);  // 2s + 2s z P
+  double kd = (double)k;
+  return fma(kd, c_misc[4], fma(kd, c_misc[5], lm));
+}
+
+}  // namespace nimb

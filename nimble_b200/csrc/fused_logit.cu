@@ -18,6 +18,7 @@
 #include <cstdint>
 #include <cstdlib>
 #include "engine.cuh"
+#include "fastmath.cuh"
 
 namespace nimb {
 
@@ -63,41 +64,165 @@ __device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, do
 //   log(t) + corr,  t = y ? p : q,  corr = y ? 0 : ((1 - q) - p) / q
 // to < 1e-15 relative, with the same p = 1/(1 + exp(-eta)) rounding sequence as Utils.h:187 and the same limits
 // (p == 0: y=0 -> 0, y=1 -> -Inf;  q == 0: y=0 -> -Inf, y=1 -> 0).  No data-dependent loop, no divergent branch.
-__device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {
-  double e = exp(-eta);
-  double p = 1.0 / (1.0 + e);
+//
+// W values are carried through every step together (statement-level interleaving): the dependent DFMA chains of
+// exp / reciprocal / log are long, and with 4 resident warps per scheduler the FP64 pipe only fills when each warp
+// offers several independent chains (ncu round 1: "wait" was the top stall reason of the scalar version).
+
+// exact but slow: |eta| so large that exp(-eta) overflows (eta < -690), or NaN.  Library exp / division / log.
+__device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
+  double p = 1.0 / (1.0 + exp(-eta));
+  if (p != p) return p;
   double q = 1.0 - p;
   double t = y1 ? p : q;
-  double delta = (1.0 - q) - p;                       // exact
-  double corr = (y1 || q == 0.0) ? 0.0 : delta * (double)__frcp_rn((float)q);
+  double corr = (y1 || q == 0.0) ? 0.0 : ((1.0 - q) - p) / q;
   return log(t) + corr;
 }
 
-// grid: (node chunks, chain tiles).  partials[blockIdx.x][C]
-// smem: 2 stages x { X tile [FT_M][P4], y tile [FT_M] }, 2 mbarriers.
+template <int W>
+__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W]) {
+  bool slow = false;
+#pragma unroll
+  for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
+  if (__any_sync(0xffffffffu, slow)) {  // warp-uniform, practically never taken
+#pragma unroll
+    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1);
+    return;
+  }
+  double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
+  int n[W];
+  // ---- e = exp(-eta), -eta in [-inf, 690].  Below -708 the result only has to vanish against 1 (d = 1 + e = 1), so the
+  // argument is clamped there and 2^n can be applied by one integer add to the exponent field (always a normal number).
+#pragma unroll
+  for (int j = 0; j < W; j++) x[j] = fmax(-eta[j], -708.0);
+#pragma unroll
+  for (int j = 0; j < W; j++) t[j] = fma(x[j], c_misc[0], c_misc[1]);
+#pragma unroll
+  for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_misc[1]; }
+#pragma unroll
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_misc[2], x[j]);
+#pragma unroll
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_misc[3], r[j]);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(c_exp_poly[0], r[j], c_exp_poly[1]);
+#pragma unroll
+  for (int c = 2; c < 12; c++) {
+#pragma unroll
+    for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_exp_poly[c]);
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+  for (int j = 0; j < W; j++) e[j] = __hiloint2double(__double2hiint(pl[j]) + (n[j] << 20), __double2loint(pl[j]));
+  // ---- p = 1/(1+e): d in [1, 1e300]; two Newton steps on a >= 20-bit seed (faithful rounding)
+#pragma unroll
+  for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];
+#pragma unroll
+  for (int j = 0; j < W; j++) p[j] = rcp_approx(d[j]);
+#pragma unroll
+  for (int it = 0; it < 2; it++) {
+#pragma unroll
+    for (int j = 0; j < W; j++) u[j] = fma(-d[j], p[j], 1.0);
+#pragma unroll
+    for (int j = 0; j < W; j++) p[j] = fma(p[j], u[j], p[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) {  // last step on the residual: correctly rounded in all but rare cases
+    u[j] = fma(-d[j], p[j], 1.0);
+    p[j] = fma(p[j], u[j], p[j]);
+  }
+  // ---- t = y ? p : q.  For y = 0 the rounding error delta of q = fl(1-p) is added back inside the logarithm:
+  // log(q) + delta/q = log(q + delta) to first order, and q + delta enters as f = (m - 1) + delta * 2^-k.
+#pragma unroll
+  for (int j = 0; j < W; j++) q[j] = 1.0 - p[j];
+  double m[W], f[W], g[W], yv[W], s[W], z[W], P[W], kd[W], dl[W];
+  bool zero[W];
+#pragma unroll
+  for (int j = 0; j < W; j++) {
+    dl[j] = y1 ? 0.0 : (1.0 - q[j]) - p[j];  // exact
+    t[j] = y1 ? p[j] : q[j];
+  }
+  // ---- log(t), t = 0 or a normal number in [2^-1000, 1]
+#pragma unroll
+  for (int j = 0; j < W; j++) {
+    int hi = __double2hiint(t[j]), lo = __double2loint(t[j]);
+    zero[j] = (hi | lo) == 0;
+    int k = (hi >> 20) - 1023;
+    hi = (hi & 0x000fffff) | 0x3ff00000;
+    bool big = hi > 0x3ff6a09e;  // m > sqrt(2): halve
+    hi = big ? hi - 0x00100000 : hi;
+    k = big ? k + 1 : k;
+    m[j] = __hiloint2double(hi, lo);
+    kd[j] = (double)k;
+    dl[j] = dl[j] * __hiloint2double((1023 - k) << 20, 0);  // delta * 2^-k (delta = 0 for y = 1)
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) { f[j] = (m[j] - 1.0) + dl[j]; g[j] = m[j] + 1.0; }
+#pragma unroll
+  for (int j = 0; j < W; j++) yv[j] = rcp_approx(g[j]);
+#pragma unroll
+  for (int it = 0; it < 2; it++) {
+#pragma unroll
+    for (int j = 0; j < W; j++) u[j] = fma(-g[j], yv[j], 1.0);
+#pragma unroll
+    for (int j = 0; j < W; j++) yv[j] = fma(yv[j], u[j], yv[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) s[j] = f[j] * yv[j];
+#pragma unroll
+  for (int j = 0; j < W; j++) z[j] = s[j] * s[j];
+#pragma unroll
+  for (int j = 0; j < W; j++) P[j] = fma(c_log_poly[0], z[j], c_log_poly[1]);
+#pragma unroll
+  for (int c = 2; c < 10; c++) {
+#pragma unroll
+    for (int j = 0; j < W; j++) P[j] = fma(P[j], z[j], c_log_poly[c]);
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) {
+    double s2 = s[j] + s[j];
+    double lm = fma(s2 * z[j], P[j], s2);
+    double lg = fma(kd[j], c_misc[4], fma(kd[j], c_misc[5], lm));
+    out[j] = zero[j] ? -INFINITY : lg;
+  }
+}
+
+__device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)
+  double in[1] = {eta}, o[1];
+  bern_logit_lp_vec<1>(in, y1, o);
+  return o[0];
+}
+
+// grid: (chain tiles, node chunks): the chain tiles of one node chunk are scheduled together and share its X tiles
+// through L2.  partials[chunk][C]
+// smem: 2 stages x { X tile [FT_M][P4], y tile [FT_M] }, 2 mbarriers.   NK = k-steps of 4 (P4 = 4*NK).
+template <int NK>
 __global__ void __launch_bounds__(FT_THREADS, 2)
-k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ ypad, int n, int P4, int p,
+k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ ypad, int n, int p,
                    const double* __restrict__ state, int beta_slot, int C, int tiles_per_chunk,
                    double* __restrict__ partials) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int stage_doubles = FT_M * P4 + FT_M;
+  constexpr int P4 = 4 * NK;
+  constexpr int stage_doubles = FT_M * P4 + FT_M;
   double* stage0 = (double*)smem_raw;
   double* red = stage0 + 2 * stage_doubles;             // [2][FT_NC]
   uint64_t* bar = (uint64_t*)(red + 2 * FT_NC);          // [2]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int wn = warp & 3, wg = warp >> 2;               // warp: chains wn*16 .. +15, rows wg*64 .. +63 of each tile
-  const int chain0 = blockIdx.y * FT_NC + wn * 16;
-  const int nk = P4 >> 2;
+  const int chain0 = blockIdx.x * FT_NC + wn * 16;
+  const int chunk = blockIdx.y;
 
   // B fragments stay in registers for the whole kernel: beta[k0 + lane%4][chain0 + nt*8 + lane/4]
-  double bf[FT_MAXK][2];
+  double bf[NK][2];
 #pragma unroll
-  for (int ks = 0; ks < FT_MAXK; ks++) {
+  for (int ks = 0; ks < NK; ks++) {
 #pragma unroll
     for (int nt = 0; nt < 2; nt++) {
       int k = ks * 4 + (lane & 3), c = chain0 + nt * 8 + (lane >> 2);
-      bf[ks][nt] = (ks < nk && k < p && c < C) ? state[(size_t)(beta_slot + k) * C + c] : 0.0;
+      bf[ks][nt] = (k < p && c < C) ? state[(size_t)(beta_slot + k) * C + c] : 0.0;
     }
   }
   if (tid == 0) {
@@ -109,7 +234,7 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
 
   double csum[4] = {0.0, 0.0, 0.0, 0.0};
   const int ntiles_total = (n + FT_M - 1) / FT_M;
-  const int tile_lo = blockIdx.x * tiles_per_chunk;
+  const int tile_lo = chunk * tiles_per_chunk;
   const int tile_hi = min(ntiles_total, tile_lo + tiles_per_chunk);
   const uint32_t x_bytes = (uint32_t)(FT_M * P4 * sizeof(double)), y_bytes = (uint32_t)(FT_M * sizeof(double));
 
@@ -132,29 +257,25 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
     const double* xa = Xs + (wg * 64 + (lane >> 2)) * P4 + (lane & 3);
 #pragma unroll 1
     for (int mp = 0; mp < 4; mp++) {  // two 8-row m-tiles at a time -> 4 independent accumulator chains
-      double acc[2][2][2] = {{{0.0, 0.0}, {0.0, 0.0}}, {{0.0, 0.0}, {0.0, 0.0}}};
+      double acc[2][4] = {{0.0, 0.0, 0.0, 0.0}, {0.0, 0.0, 0.0, 0.0}};  // [m-tile][n-tile*2 + column]
       const double* x0 = xa + (mp * 16) * P4;
 #pragma unroll
-      for (int ks = 0; ks < FT_MAXK; ks++) {
-        if (ks < nk) {
-          double a0 = x0[ks * 4], a1 = x0[8 * P4 + ks * 4];
-          dmma_m8n8k4(acc[0][0][0], acc[0][0][1], a0, bf[ks][0]);
-          dmma_m8n8k4(acc[0][1][0], acc[0][1][1], a0, bf[ks][1]);
-          dmma_m8n8k4(acc[1][0][0], acc[1][0][1], a1, bf[ks][0]);
-          dmma_m8n8k4(acc[1][1][0], acc[1][1][1], a1, bf[ks][1]);
-        }
+      for (int ks = 0; ks < NK; ks++) {
+        double a0 = x0[ks * 4], a1 = x0[8 * P4 + ks * 4];
+        dmma_m8n8k4(acc[0][0], acc[0][1], a0, bf[ks][0]);
+        dmma_m8n8k4(acc[0][2], acc[0][3], a0, bf[ks][1]);
+        dmma_m8n8k4(acc[1][0], acc[1][1], a1, bf[ks][0]);
+        dmma_m8n8k4(acc[1][2], acc[1][3], a1, bf[ks][1]);
       }
       // epilogue on the accumulators: lane holds row (lane>>2) of each m-tile, columns 2*(lane&3)+{0,1} of each n-tile
 #pragma unroll
       for (int mt = 0; mt < 2; mt++) {
         double yv = ys[wg * 64 + mp * 16 + mt * 8 + (lane >> 2)];
         bool live = yv >= 0.0, y1 = yv != 0.0;          // -1 marks the zero-padded rows past n
+        double lp[4];
+        bern_logit_lp_vec<4>(acc[mt], y1, lp);
 #pragma unroll
-        for (int nt = 0; nt < 2; nt++) {
-          double l0 = bern_logit_lp(acc[mt][nt][0], y1), l1 = bern_logit_lp(acc[mt][nt][1], y1);
-          csum[nt * 2 + 0] += live ? l0 : 0.0;
-          csum[nt * 2 + 1] += live ? l1 : 0.0;
-        }
+        for (int j = 0; j < 4; j++) csum[j] += live ? lp[j] : 0.0;
       }
     }
     __syncthreads();  // everyone is done with stage b before it is refilled
@@ -178,8 +299,8 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
   }
   __syncthreads();
   if (tid < FT_NC) {
-    int c = blockIdx.y * FT_NC + tid;
-    if (c < C) partials[(size_t)blockIdx.x * C + c] = red[tid] + red[FT_NC + tid];
+    int c = blockIdx.x * FT_NC + tid;
+    if (c < C) partials[(size_t)chunk * C + c] = red[tid] + red[FT_NC + tid];
   }
 }
 
@@ -194,7 +315,9 @@ __global__ void k_pad_x(const double* __restrict__ X, const double* __restrict__
   if (k == 0) ypad[i] = i < (size_t)n ? y[i] : -1.0;  // -1 marks padding rows
 }
 
-static int p4_of(int p) { return (p + 3) & ~3; }
+// k-steps are specialised at compile time: NK in {4, 8, 13, 16}; rows are padded to 4*NK doubles
+static int nk_of(int p) { int nk = (p + 3) / 4; return nk <= 4 ? 4 : nk <= 8 ? 8 : nk <= 13 ? 13 : 16; }
+static int p4_of(int p) { return 4 * nk_of(p); }
 
 static int g_chunks_cache_n = -1, g_chunks_cache = 0;
 static int chunks_for(int n) {
@@ -211,7 +334,7 @@ int fused_bern_logit_tiles(int n) { return chunks_for(n); }
 
 // doubles needed for the padded copy: X tiles [ntiles*FT_M][P4] followed by y tiles [ntiles*FT_M]
 size_t fused_bern_logit_xpad_len(int n, int p) {
-  if (p < 1 || p4_of(p) > FT_MAXP4) return 0;
+  if (p < 1 || p > FT_MAXP4) return 0;
   if (getenv("NIMB200_NO_FUSED")) return 0;
   size_t ntiles = (size_t)(n + FT_M - 1) / FT_M;
   return ntiles * FT_M * p4_of(p) + ntiles * FT_M;
@@ -224,20 +347,55 @@ void fused_bern_logit_prepare_x(const double* X, const double* y, int n, int p, 
   k_pad_x<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(X, y, n, p, ld, P4, total, Xpad, Xpad + total);
 }
 
-void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
-                             cudaStream_t st) {
-  int P4 = p4_of(p);
-  size_t smem = sizeof(double) * (2 * ((size_t)FT_M * P4 + FT_M) + 2 * FT_NC) + 16;
+template <int NK>
+static void launch_nk(const double* Xpad, const double* ypad, int n, int p, const double* state, int beta_slot, int C,
+                      int chunks, int tpc, double* partials, cudaStream_t st) {
+  size_t smem = sizeof(double) * (2 * ((size_t)FT_M * 4 * NK + FT_M) + 2 * FT_NC) + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_fused_bern_logit, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+    cudaFuncSetAttribute(k_fused_bern_logit<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr_set = true;
   }
+  dim3 grid((C + FT_NC - 1) / FT_NC, chunks);
+  k_fused_bern_logit<NK><<<grid, FT_THREADS, smem, st>>>(Xpad, ypad, n, p, state, beta_slot, C, tpc, partials);
+}
+
+void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
+                             cudaStream_t st) {
   int chunks = chunks_for(n);
   int ntiles = (n + FT_M - 1) / FT_M;
   int tpc = (ntiles + chunks - 1) / chunks;
-  dim3 grid(chunks, (C + FT_NC - 1) / FT_NC);
-  k_fused_bern_logit<<<grid, FT_THREADS, smem, st>>>(Xpad, Xpad + xpad_x_len(n, p), n, P4, p, state, beta_slot, C, tpc, partials);
+  const double* ypad = Xpad + xpad_x_len(n, p);
+  switch (nk_of(p)) {
+    case 4: launch_nk<4>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
+    case 8: launch_nk<8>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
+    case 13: launch_nk<13>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
+    default: launch_nk<16>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
+  }
+}
+
+__global__ void k_debug_math(int which, const double* __restrict__ x, int n, double* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double v = x[i];
+  out[i] = which == 0 ? exp_f64(v) : which == 1 ? log_f64(v) : which == 2 ? rcp_f64(v)
+         : which == 3 ? bern_logit_lp(v, false) : bern_logit_lp(v, true);
 }
 
 }  // namespace nimb
+
+// diagnostic: evaluates the kernels' own exp (0) / log (1) / reciprocal (2) / Bernoulli-logit log-density for y = 0 (3)
+// and y = 1 (4) on a host array, so tests can measure their accuracy against libm.
+extern "C" int nimb200_debug_math(int32_t which, const double* x, int32_t n, double* out) {
+  if (!x || !out || n < 0 || which < 0 || which > 4) return 1;
+  if (n == 0) return 0;
+  double *dx = nullptr, *dout = nullptr;
+  if (cudaMalloc(&dx, sizeof(double) * n) != cudaSuccess) return 1;
+  if (cudaMalloc(&dout, sizeof(double) * n) != cudaSuccess) { cudaFree(dx); return 1; }
+  cudaMemcpy(dx, x, sizeof(double) * n, cudaMemcpyHostToDevice);
+  nimb::k_debug_math<<<(n + 255) / 256, 256>>>(which, dx, n, dout);
+  cudaError_t e = cudaMemcpy(out, dout, sizeof(double) * n, cudaMemcpyDeviceToHost);
+  cudaFree(dx);
+  cudaFree(dout);
+  return e == cudaSuccess ? 0 : 1;
+}

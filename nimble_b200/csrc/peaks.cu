@@ -40,7 +40,62 @@ __global__ void k_dmma_peak(double* out, int iters, double seed) {
   if (s == 12345.678) out[0] = s;
 }
 
+// DMMA and DFMA issued together: do the FP64 tensor sub-pipe and the FP64 pipe add up, or share their multipliers?
+__global__ void k_mixed_peak(double* out, int iters, double seed) {
+  double d[4][2], a8[8];
+#pragma unroll
+  for (int j = 0; j < 4; j++) d[j][0] = d[j][1] = 0.0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) a8[j] = seed + j + threadIdx.x * 1e-9;
+  double a = seed + (threadIdx.x & 31) * 1e-3, b = 1.0 + (threadIdx.x & 31) * 1e-4, bb = 1.0000001, c = 1e-7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(d[j][0]), "+d"(d[j][1]) : "d"(a), "d"(b));
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) a8[j] = fma(a8[j], bb, c);
+  }
+  double s = 0;
+#pragma unroll
+  for (int j = 0; j < 4; j++) s += d[j][0] + d[j][1];
+#pragma unroll
+  for (int j = 0; j < 8; j++) s += a8[j];
+  if (s == 12345.678) out[0] = s;
+}
+
 }  // namespace
+
+// flops of a loop that issues 4 DMMA (2048 flop/warp) and 32 DFMA (2048 flop/warp) per iteration
+extern "C" int nimb200_measure_fp64_mixed(int device, double* tflops) {
+  if (cudaSetDevice(device) != cudaSuccess) return 1;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 1;
+  double* out = nullptr;
+  if (cudaMalloc(&out, 8) != cudaSuccess) return 1;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int threads = 256, blocks = prop.multiProcessorCount * 8, iters = 4096;
+  double best = 0;
+  for (int rep = 0; rep < 5; rep++) {
+    float ms = 0;
+    cudaEventRecord(e0);
+    k_mixed_peak<<<blocks, threads>>>(out, iters, 1.0);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(&ms, e0, e1);
+    double flops = (4.0 * 2 * 256 + 32.0 * 2 * 32) * iters * (double)(threads / 32) * blocks;
+    if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  *tflops = best;
+  return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
 
 extern "C" int nimb200_measure_fp64_peaks(int device, double* dfma_tflops, double* dmma_tflops) {
   if (cudaSetDevice(device) != cudaSuccess) return 1;

@@ -235,3 +235,49 @@ def test_full_size_logistic_properties(oracle, b200):
     d2 = compile_on(b200, conf)._ensure(2)
     d2.set_values(inits[:2])
     assert rel_err(d2.calculate(y, lo, hi), do.calculate(y, lo, hi)).max() < RTOL_LP
+
+
+def test_fastmath_accuracy(b200, oracle):
+    """The fused kernels' own exp / log / reciprocal against libm (numpy), and the fused Bernoulli-logit
+    log-density against the oracle's dbinom(y, 1, ilogit(eta)) over the whole range of linear predictors."""
+    import ctypes as C
+    f = b200.lib.nimb200_debug_math
+    f.argtypes = [C.c_int32, C.POINTER(C.c_double), C.c_int32, C.POINTER(C.c_double)]
+    dp = C.POINTER(C.c_double)
+
+    def dev(which, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        out = np.empty_like(x)
+        assert f(which, x.ctypes.data_as(dp), x.size, out.ctypes.data_as(dp)) == 0
+        return out
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(-745, 709, 200000), rng.uniform(-40, 40, 200000), rng.normal(0, 1e-3, 1000),
+                        [0.0, -0.0, 709.7, -745.1, -760.0, 720.0, 1e-300]])
+    with np.errstate(over="ignore", under="ignore"):
+        want = np.exp(x)
+    got = dev(0, x)
+    ok = np.isfinite(want) & (want > 1e-300)
+    assert np.max(np.abs(got[ok] - want[ok]) / want[ok]) < 4e-16
+    assert np.all(got[want == np.inf] == np.inf) and np.all(got[x < -750] == 0.0)
+    t = np.concatenate([rng.uniform(0, 1, 200000), np.exp(rng.uniform(-700, 0, 200000)), 1 - np.exp(rng.uniform(-36, 0, 50000)),
+                        [1.0, 0.5, 2.0 ** -1074, 2.0 ** -1022, 0.7071067811865476, 0.7071067811865475]])
+    got, want = dev(1, t), np.log(t)
+    assert np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)) < 4e-16
+    assert dev(1, np.array([0.0]))[0] == -np.inf and np.isnan(dev(1, np.array([np.nan]))[0])
+    d = np.concatenate([1 + np.exp(rng.uniform(-40, 700, 200000)), [1.0, 2.0, 3.0]])
+    assert np.max(np.abs(dev(2, d) * d - 1.0)) < 4e-16
+    # the fused log-density against the oracle's nmath path, node by node
+    eta = np.concatenate([rng.uniform(-8, 8, 100000), rng.uniform(-40, 40, 20000), [-800.0, -745.0, -37.0, 36.7, 37.5, 800.0, 0.0]])
+    ref = oracle.lib
+    for which, yv in ((3, 0.0), (4, 1.0)):
+        got = dev(which, eta)
+        with np.errstate(over="ignore"):
+            p = 1.0 / (1.0 + np.exp(-eta))
+        want = np.array([ref.ref_dbinom(yv, 1.0, float(pp)) for pp in p])
+        assert np.array_equal(np.isinf(got), np.isinf(want)), which
+        fin = np.isfinite(want)
+        # well-conditioned range: 1e-12 relative; beyond |eta| ~ 9 the reference value itself moves by more than that per ulp of exp
+        wc = fin & (np.abs(eta) <= 8)
+        assert np.max(np.abs(got[wc] - want[wc]) / np.maximum(np.abs(want[wc]), 1e-300)) < 1e-12
+        assert np.max(np.abs(got[fin] - want[fin])) < 2e-2      # noise level of log(1 - p) itself near p = 1 - 1e-13
+        assert np.isnan(dev(which, np.array([np.nan]))[0])
