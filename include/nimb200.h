@@ -249,6 +249,15 @@ int nimb200_mcmc_last_timing(nimb200_model *m, double *ms_out, int64_t *launches
  * what: 0 scale [T][C]; 1 timesAdapted [T][C]; 2 propCov [d*d][C] (RW_block). */
 int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, double *out, int64_t cap);
 
+/* Data-node sharding across the GPUs of one node (the reference has no counterpart, one core walks all
+ * N nodes).  Every rank creates the same model (same table, chains and seed), then calls nimb200_enable_data_sharding:
+ * data declarations with >= min_nodes instances are split into contiguous slices, and each block sum / conjugate
+ * contribution that involves a sharded declaration is all-reduced (sum, FP64) over NCCL inside the library, after
+ * which all ranks take identical decisions.  id128 is the 128-byte ncclUniqueId produced by nimb200_nccl_unique_id on
+ * one rank and distributed by the host (NULL: slices without a communicator, block sums stay per-rank partial sums). */
+int nimb200_nccl_unique_id(void *id128);
+int nimb200_enable_data_sharding(nimb200_model *m, int32_t nranks, int32_t rank, const void *id128, int32_t min_nodes);
+
 /* measurement hooks for bench.py (no counterpart in the reference, whose only profiling hook is
  * run(time=TRUE), MCMC_build.R:281-285): average device milliseconds of one launch of the block-sum kernel
  * behind nimb200_calculate(decl, whole range), and live FP64 peaks (DFMA loop, FP64 mma.sync loop). */

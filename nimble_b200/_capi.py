@@ -62,6 +62,8 @@ class Backend:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
             self._peaks = fn("measure_fp64_peaks", [C.c_int, _dp, _dp])
+            self._nccl_id = fn("nccl_unique_id", [C.c_void_p])
+            self._shard = fn("enable_data_sharding", [vp, C.c_int32, C.c_int32, C.c_void_p, C.c_int32])
 
     def check(self, rc):
         if rc != 0:
@@ -75,6 +77,12 @@ class Backend:
         else:
             self.check(self._create(C.byref(packed_table), nchains, first_chain, C.byref(h)))
         return h
+
+    def nccl_unique_id(self):
+        """128-byte ncclUniqueId (bytes); produce on one rank, hand to all ranks of the data-sharded group."""
+        buf = C.create_string_buffer(128)
+        self.check(self._nccl_id(buf))
+        return buf.raw
 
     def fp64_peaks(self, device=0):
         a, b = C.c_double(), C.c_double()
@@ -157,6 +165,11 @@ class DeviceModel:
         out = np.empty(n)
         self.backend.check(self.backend._sstate(self.h, sampler, what, _ptr(out), n))
         return out.reshape(-1, self.C)
+
+    def enable_data_sharding(self, nranks, rank, unique_id=None, min_nodes=65536):
+        """Split large data declarations across the ranks of a group; unique_id=None keeps block sums as partial sums."""
+        buf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
+        self.backend.check(self.backend._shard(self.h, nranks, rank, buf, min_nodes))
 
     def time_calculate(self, decl, reps=5):
         ms = C.c_double()

@@ -149,7 +149,7 @@ __device__ double calc_node(const DevTab& T, int di, int i, int c, int ov_slot, 
   return NAN;
 }
 
-struct Sel { int lo, hi; const int32_t* idx; };
+struct Sel { int lo, hi; const int32_t* idx; int nlo, nhi; };  // [nlo,nhi): node instances this rank owns (data sharding)
 __device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, int t) {
   Sel s; s.idx = nullptr;
   switch (dp.sel) {
@@ -160,8 +160,13 @@ __device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, in
     case NIMB_SEL_CSR: s.lo = T.iarr[dp.a][t]; s.hi = T.iarr[dp.a][t + 1]; s.idx = T.iarr[dp.b]; break;
     default: s.lo = dp.a; s.hi = dp.b; break;
   }
+  s.nlo = T.shard_lo[dp.decl]; s.nhi = T.shard_hi[dp.decl];
+  if (!s.idx) { s.lo = max(s.lo, s.nlo); s.hi = min(s.hi, s.nhi); }
   return s;
 }
+// does this rank account for declaration `decl` in a quantity that is summed over ranks?  Sharded declarations:
+// every rank, its own slice.  Replicated declarations: rank 0 only.
+__device__ __forceinline__ bool counts_here(const DevTab& T, int decl) { return T.rank == 0 || T.sharded[decl]; }
 
 // conjugate contribution of one dependent node (P/R/MCMC_conjugacy.R:80-93, 109-115; probing :766-820)
 __device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep& dp, int node, int c, int slot, bool gam,
@@ -238,7 +243,10 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 // ------------------------------------------------------------------------------------------------ sweep kernels
 // One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
 // 32 lanes of a warp read the same data node and 32 consecutive chain copies of each state slot.
-__global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S) {
+// PHASE 0: everything in one kernel.  Data-sharded models split it: PHASE 1 accumulates this rank's share of the
+// per-(target, chain) sums into buf[t][k][c] (k < 3), the host all-reduces buf, PHASE 2 decides / draws from it.
+template <int PHASE>
+__global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* buf) {
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int c = (int)(gid % T.C);
@@ -250,42 +258,54 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   DrawKey key = make_key(T, seed, iter, sid, t, c);
   double* sv = T.state + (size_t)slot * T.C + c;
   double cur = *sv;
+  double v0 = 0, v1 = 0, v2 = 0;
+  double* bp = buf + ((size_t)t * 3) * T.C + c;
+  if (PHASE == 2) { v0 = bp[0]; v1 = bp[(size_t)T.C]; v2 = bp[2 * (size_t)T.C]; }
 
   if (sp.type == NIMB_SAMPLER_RW) {  // MCMC_samplers.R:352-386
     double z, z1, propLogScale;
     normal2(key, 0, z, z1);
     double prop = rw_proposal(sp, cur, S.scale[q], z, propLogScale);
-    double lp0 = 0, lp1 = 0;
-    for (int e = 0; e < sp.n_dep; e++) {
-      const nimb200_dep dp = T.deps[sp.dep_off + e];
-      Sel s = sel_of(T, dp, t);
-      for (int k = s.lo; k < s.hi; k++) {
-        int node = s.idx ? s.idx[k] : k;
-        double nw = calc_node(T, dp.decl, node, c, slot, prop);
-        double od = calc_node(T, dp.decl, node, c, -1, 0.0);
-        if (dp.stage == 0) lp0 += nw - od; else lp1 += nw - od;
+    if (PHASE != 2) {
+      for (int e = 0; e < sp.n_dep; e++) {
+        const nimb200_dep dp = T.deps[sp.dep_off + e];
+        if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
+        Sel s = sel_of(T, dp, t);
+        for (int k = s.lo; k < s.hi; k++) {
+          int node = s.idx ? s.idx[k] : k;
+          if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
+          double nw = calc_node(T, dp.decl, node, c, slot, prop);
+          double od = calc_node(T, dp.decl, node, c, -1, 0.0);
+          if (dp.stage == 0) v0 += nw - od; else v1 += nw - od;
+        }
       }
     }
+    if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = 0.0; return; }
     bool jump;
-    if (lp0 == -INFINITY) jump = false;
-    else jump = decide(lp0 + lp1 + propLogScale, key, 1);
+    if (v0 == -INFINITY) jump = false;
+    else jump = decide(v0 + v1 + propLogScale, key, 1);
     if (jump) *sv = prop;
     if (sp.adaptive) rw_adapt(sp, S, q, jump);
     return;
   }
   if (sp.type == NIMB_SAMPLER_BINARY) {  // MCMC_samplers.R:127-151
     double other = 1 - cur;
-    double currentLogProb = 0, otherPrior = 0, otherDeps = 0;
-    for (int e = 0; e < sp.n_dep; e++) {
-      const nimb200_dep dp = T.deps[sp.dep_off + e];
-      Sel s = sel_of(T, dp, t);
-      for (int k = s.lo; k < s.hi; k++) {
-        int node = s.idx ? s.idx[k] : k;
-        currentLogProb += calc_node(T, dp.decl, node, c, -1, 0.0);
-        double o = calc_node(T, dp.decl, node, c, slot, other);
-        if (dp.stage == 0) otherPrior += o; else otherDeps += o;
+    if (PHASE != 2) {
+      for (int e = 0; e < sp.n_dep; e++) {
+        const nimb200_dep dp = T.deps[sp.dep_off + e];
+        if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
+        Sel s = sel_of(T, dp, t);
+        for (int k = s.lo; k < s.hi; k++) {
+          int node = s.idx ? s.idx[k] : k;
+          if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
+          v0 += calc_node(T, dp.decl, node, c, -1, 0.0);
+          double o = calc_node(T, dp.decl, node, c, slot, other);
+          if (dp.stage == 0) v1 += o; else v2 += o;
+        }
       }
     }
+    if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = v2; return; }
+    double currentLogProb = v0, otherPrior = v1, otherDeps = v2;
     double otherLogProb = (otherPrior == -INFINITY) ? otherPrior : otherPrior + otherDeps;
     double acceptanceProb = 1 / (exp(currentLogProb - otherLogProb) + 1);
     double u, u2;
@@ -296,23 +316,30 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   }
   // conjugate: MCMC_conjugacy.R:651-692
   bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  if (PHASE != 2) {
+    for (int e = 0; e < sp.n_dep; e++) {
+      const nimb200_dep dp = T.deps[sp.dep_off + e];
+      if (dp.stage != 1) continue;
+      if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
+      Sel s = sel_of(T, dp, t);
+      for (int k = s.lo; k < s.hi; k++) {
+        int node = s.idx ? s.idx[k] : k;
+        if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
+        conj_contrib(T, dp, node, c, slot, gam, v0, v1);
+      }
+    }
+  }
+  if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = 0.0; return; }
   const nimb200_dep tp = T.deps[sp.dep_off];
-  int tnode = sel_of(T, tp, t).lo;
+  int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
   double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
   double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
-  double c0 = 0, c1 = 0;
-  for (int e = 0; e < sp.n_dep; e++) {
-    const nimb200_dep dp = T.deps[sp.dep_off + e];
-    if (dp.stage != 1) continue;
-    Sel s = sel_of(T, dp, t);
-    for (int k = s.lo; k < s.hi; k++) conj_contrib(T, dp, s.idx ? s.idx[k] : k, c, slot, gam, c0, c1);
-  }
   double nv;
   if (gam) {
-    double shape = prior0 + c0, scale = 1 / (prior1 + c1);
+    double shape = prior0 + v0, scale = 1 / (prior1 + v1);
     nv = rgamma1(key, shape) * scale;
   } else {
-    double mean = (prior0 * prior1 + c0) / (prior1 + c1), sd = pow(prior1 + c1, -0.5), z, z1;
+    double mean = (prior0 * prior1 + v0) / (prior1 + v1), sd = pow(prior1 + v1, -0.5), z, z1;
     normal2(key, 0, z, z1);
     nv = mean + sd * z;
   }
@@ -338,6 +365,7 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
       int k = tile0 + q * nl + lane_n;
       if (k >= hi) break;
       int node = idx ? idx[k] : k;
+      if (idx && (node < T.shard_lo[di] || node >= T.shard_hi[di])) continue;
       if (MODE == 0) a0 += calc_node(T, di, node, c, -1, 0.0);
       else if (MODE == 1) out_nodes[(size_t)(k - lo) * T.C + c] = calc_node(T, di, node, c, -1, 0.0);
       else conj_contrib(T, dp, node, c, slot, gam != 0, a0, a1);
@@ -520,7 +548,7 @@ __global__ void k_conj_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, c
   bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
   DrawKey key = make_key(T, seed, iter, sid, 0, c);
   const nimb200_dep tp = T.deps[sp.dep_off];
-  int tnode = sel_of(T, tp, 0).lo;
+  int tnode = tp.a;  // stage-0 entry of a single-target sampler: RANGE(node, node+1)
   double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
   double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
   double c0 = 0, c1 = 0;
@@ -651,6 +679,14 @@ struct nimb200_model {
   std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
   std::vector<int> ran;         // RW_block: iterations since last adaptation
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
+  // data-node sharding (nimb200_enable_data_sharding)
+  int rank = 0, nranks = 1;
+  std::vector<int32_t> shard_lo, shard_hi, sharded;
+  int32_t *d_shard_lo = nullptr, *d_shard_hi = nullptr, *d_sharded = nullptr;
+  void* nccl_comm = nullptr;
+  double* d_sweepbuf = nullptr;  // [T][3][C] partial sums of a sharded sweep
+  size_t sweepbuf_cap = 0;
+  std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
   cudaStream_t stream = nullptr;
@@ -659,6 +695,45 @@ struct nimb200_model {
   int64_t last_launches = 0, launches = 0;
   std::vector<void*> allocs;
 };
+
+// ------------------------------------------------------------------------------------------------ NCCL (dlopen)
+// Only the data-sharded mode needs a collective: one all-reduce (sum, FP64) of per-chain partial sums per block-sum
+// evaluation.  NCCL is loaded at run time (the copy torch already mapped if there is one) so that the library has no
+// link-time dependency on it and single-GPU users never touch it.
+#include <dlfcn.h>
+namespace {
+struct NcclId { char internal[128]; };
+typedef int (*fn_getid)(NcclId*);
+typedef int (*fn_init)(void**, int, NcclId, int);
+typedef int (*fn_allreduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_destroy)(void*);
+typedef const char* (*fn_errstr)(int);
+struct NcclApi {
+  void* h = nullptr;
+  fn_getid getid = nullptr; fn_init init = nullptr; fn_allreduce allreduce = nullptr; fn_destroy destroy = nullptr;
+  fn_errstr errstr = nullptr;
+};
+NcclApi g_nccl;
+int load_nccl() {
+  if (g_nccl.h) return 0;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    g_nccl.h = dlopen(nm, RTLD_NOW | RTLD_NOLOAD);
+    if (g_nccl.h) break;
+  }
+  for (int i = 0; !g_nccl.h && i < 2; i++) g_nccl.h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+  if (!g_nccl.h) return 1;
+  g_nccl.getid = (fn_getid)dlsym(g_nccl.h, "ncclGetUniqueId");
+  g_nccl.init = (fn_init)dlsym(g_nccl.h, "ncclCommInitRank");
+  g_nccl.allreduce = (fn_allreduce)dlsym(g_nccl.h, "ncclAllReduce");
+  g_nccl.destroy = (fn_destroy)dlsym(g_nccl.h, "ncclCommDestroy");
+  g_nccl.errstr = (fn_errstr)dlsym(g_nccl.h, "ncclGetErrorString");
+  if (!g_nccl.getid || !g_nccl.init || !g_nccl.allreduce || !g_nccl.destroy) { g_nccl.h = nullptr; return 1; }
+  return 0;
+}
+}  // namespace
+
+static int allreduce_sum(nimb200_model* m, double* buf, size_t count);
 
 static const int EVAL_THREADS = 256;
 static const int EVAL_NPT = 32;
@@ -688,22 +763,31 @@ static int eval_tiles(int C, int count) {
 static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, const int32_t* idx, double* dst0, double* dst1,
                            const nimb200_dep* dp, int slot, int gam) {
   int C = m->C;
+  if (!idx) { lo = std::max(lo, (int)m->shard_lo[di]); hi = std::max(lo, std::min(hi, (int)m->shard_hi[di])); }
   int cwl = cw_log2_for(C), cw = 1 << cwl;
   int count = hi - lo;
+  const nimb200_decl& d = m->decl[di];
   if (count <= 0) {
     CK(cudaMemsetAsync(dst0, 0, sizeof(double) * C, m->stream));
     if (dst1) CK(cudaMemsetAsync(dst1, 0, sizeof(double) * C, m->stream));
+    if (m->nranks > 1 && m->sharded[di] && m->nccl_comm) {
+      if (allreduce_sum(m, dst0, C)) return 1;
+      if (dst1 && allreduce_sum(m, dst1, C)) return 1;
+    }
     return 0;
   }
-  const nimb200_decl& d = m->decl[di];
-  if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di] && lo == 0 && hi == d.n && !idx) {
+  bool shard = m->nranks > 1 && m->sharded[di];
+  if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di] && !idx && (lo % 128) == 0 &&
+      (hi == d.n || (hi % 128) == 0)) {
     int nt = fused_bern_logit_tiles(d.n);
     if ((size_t)nt * C > m->partials_cap) return fail("internal: partials scratch too small (fused)");
-    fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
+    fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, lo / 128,
+                            (hi + 127) / 128, m->stream);
     m->launches++;
     k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
     m->launches++;
     CK(cudaGetLastError());
+    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
     return 0;
   }
   int nt = eval_tiles(C, count);
@@ -719,6 +803,17 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
   m->launches++;
   CK(cudaGetLastError());
+  if (shard && m->nccl_comm) {
+    if (allreduce_sum(m, dst0, C)) return 1;
+    if (dst1 && allreduce_sum(m, dst1, C)) return 1;
+  }
+  return 0;
+}
+
+static int allreduce_sum(nimb200_model* m, double* buf, size_t count) {
+  int rc = g_nccl.allreduce(buf, buf, count, /*ncclDouble*/ 8, /*ncclSum*/ 0, m->nccl_comm, m->stream);
+  if (rc != 0) return fail(std::string("ncclAllReduce failed: ") + (g_nccl.errstr ? g_nccl.errstr(rc) : "?"));
+  m->launches++;
   return 0;
 }
 
@@ -733,6 +828,7 @@ static HostSel host_sel(nimb200_model* m, const nimb200_dep& dp, const std::vect
     case NIMB_SEL_CSR: s.lo = h_iarr[dp.a][0]; s.hi = h_iarr[dp.a][1]; s.idx = m->d_iarr[dp.b]; break;
     default: s.lo = dp.a; s.hi = dp.b; break;
   }
+  if (!s.idx && !m->shard_lo.empty()) { s.lo = std::max(s.lo, m->shard_lo[dp.decl]); s.hi = std::min(s.hi, m->shard_hi[dp.decl]); if (s.hi < s.lo) s.hi = s.lo; }
   return s;
 }
 
@@ -805,6 +901,7 @@ extern "C" int nimb200_model_free(nimb200_model* m) {
   if (m->stream) cudaStreamSynchronize(m->stream);
   for (void* p : m->allocs) cudaFree(p);
   if (m->d_samples) cudaFree(m->d_samples);
+  if (m->nccl_comm && g_nccl.destroy) g_nccl.destroy(m->nccl_comm);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->stream) cudaStreamDestroy(m->stream);
@@ -894,6 +991,16 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->T.deps = (const nimb200_dep*)m->d_deps; m->T.samplers = (const nimb200_sampler*)m->d_samplers;
   m->T.darr = (const double* const*)m->d_darr_tab; m->T.iarr = (const int32_t* const*)m->d_iarr_tab;
   m->T.state = m->d_state; m->T.n_slots = t->n_slots; m->T.C = nchains; m->T.first_chain = first_chain;
+  m->shard_lo.assign(m->decl.size(), 0); m->shard_hi.resize(m->decl.size()); m->sharded.assign(m->decl.size(), 0);
+  for (size_t i = 0; i < m->decl.size(); i++) m->shard_hi[i] = m->decl[i].n;
+  TRY(dev_alloc(m, &m->d_shard_lo, m->decl.size()));
+  TRY(dev_alloc(m, &m->d_shard_hi, m->decl.size()));
+  TRY(dev_alloc(m, &m->d_sharded, m->decl.size()));
+  TRYCU(cudaMemcpyAsync(m->d_shard_lo, m->shard_lo.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  TRYCU(cudaMemcpyAsync(m->d_shard_hi, m->shard_hi.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  TRYCU(cudaMemcpyAsync(m->d_sharded, m->sharded.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
+  m->sweep_sharded.assign(m->samplers.size(), 0);
   // fused family: re-lay X once (row-major, rows padded to a multiple of 4 doubles)
   m->d_xpad.assign(m->decl.size(), nullptr);
   for (size_t i = 0; i < m->decl.size(); i++) {
@@ -1050,7 +1157,7 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
   CK(cudaEventRecord(m->ev0, m->stream));
   for (int r = 0; r < reps; r++) {
     if (fused)
-      fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, m->stream);
+      fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, 0, (d.n + 127) / 128, m->stream);
     else {
       dim3 grid(eval_tiles(C, d.n), (C + cw - 1) / cw);
       nimb200_dep dd{};
@@ -1071,6 +1178,65 @@ extern "C" int nimb200_getLogProb(nimb200_model* m, int32_t di, double* out) {
   CK(cudaSetDevice(m->device));
   CK(cudaMemcpyAsync(out, m->d_lpcache + (size_t)di * m->C, sizeof(double) * m->C, cudaMemcpyDeviceToHost, m->stream));
   CK(cudaStreamSynchronize(m->stream));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ data-node sharding
+extern "C" int nimb200_nccl_unique_id(void* id128) {
+  if (!id128) return fail("null argument");
+  if (load_nccl()) return fail("NCCL library (libnccl.so.2) could not be loaded");
+  NcclId id;
+  int rc = g_nccl.getid(&id);
+  if (rc != 0) return fail("ncclGetUniqueId failed");
+  memcpy(id128, &id, sizeof id);
+  return 0;
+}
+
+// Every rank of a data-sharded group calls this on its own model (same table, same chains, same seed) before the
+// first run.  Data declarations with at least min_nodes instances are split into contiguous, 128-aligned slices;
+// id128 == NULL keeps the slices but creates no communicator (block sums are then this rank's partial sums: used by
+// tests that add the parts up themselves).
+extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, int32_t rank, const void* id128, int32_t min_nodes) {
+  if (!m) return fail("null model");
+  if (nranks < 1 || rank < 0 || rank >= nranks) return fail("bad rank / nranks");
+  CK(cudaSetDevice(m->device));
+  m->rank = rank; m->nranks = nranks;
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    const nimb200_decl& d = m->decl[i];
+    bool sh = nranks > 1 && d.value_kind == 0 && d.n >= min_nodes;
+    m->sharded[i] = sh ? 1 : 0;
+    if (sh) {
+      int64_t per = ((int64_t)d.n + nranks - 1) / nranks;
+      per = (per + 127) / 128 * 128;
+      m->shard_lo[i] = (int32_t)std::min<int64_t>(d.n, per * rank);
+      m->shard_hi[i] = (int32_t)std::min<int64_t>(d.n, per * (rank + 1));
+    } else { m->shard_lo[i] = 0; m->shard_hi[i] = d.n; }
+  }
+  CK(cudaMemcpyAsync(m->d_shard_lo, m->shard_lo.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  CK(cudaMemcpyAsync(m->d_shard_hi, m->shard_hi.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  CK(cudaMemcpyAsync(m->d_sharded, m->sharded.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  m->T.rank = rank; m->T.nranks = nranks;
+  size_t need = 0;
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    bool touch = false;
+    for (int e = 0; e < sp.n_dep; e++) touch |= m->sharded[m->deps[sp.dep_off + e].decl] != 0;
+    m->sweep_sharded[s] = touch ? 1 : 0;
+    if (touch && !m->wide[s]) need = std::max(need, (size_t)sp.n_targets * 3 * m->C);
+  }
+  if (need > m->sweepbuf_cap) {
+    if (dev_alloc(m, &m->d_sweepbuf, need)) return 1;
+    m->sweepbuf_cap = need;
+  }
+  if (nranks > 1 && id128) {
+    if (load_nccl()) return fail("NCCL library (libnccl.so.2) could not be loaded");
+    NcclId id;
+    memcpy(&id, id128, sizeof id);
+    int rc = g_nccl.init(&m->nccl_comm, nranks, id, rank);
+    if (rc != 0) return fail(std::string("ncclCommInitRank failed: ") + (g_nccl.errstr ? g_nccl.errstr(rc) : "?"));
+  }
+  CK(cudaStreamSynchronize(m->stream));
+  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   return 0;
 }
 
@@ -1096,8 +1262,19 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const int TB = 128;
   if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;
-    k_sweep<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s]);
-    m->launches++;
+    unsigned nb = (unsigned)((total + TB - 1) / TB);
+    if (m->nranks > 1 && m->sweep_sharded[s]) {  // partial sums -> all-reduce -> decide / draw
+      size_t need = total * 3;
+      if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");
+      k_sweep<1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
+      m->launches++;
+      if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
+      k_sweep<2><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
+      m->launches++;
+    } else {
+      k_sweep<0><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
+      m->launches++;
+    }
   } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL) {
     bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
     for (int e = 0; e < sp.n_dep; e++) {

@@ -18,6 +18,11 @@ struct DevTab {
   const int32_t* const* iarr;
   double* state;  // [n_slots][C]: chain index fastest, so a warp reads 32 chains' copies of one node coalesced
   int n_slots, C, first_chain;
+  // data-node sharding: this rank owns instances [shard_lo[d], shard_hi[d]) of declaration d (whole range if not sharded)
+  const int32_t* shard_lo;
+  const int32_t* shard_hi;
+  const int32_t* sharded;
+  int rank, nranks;
 };
 
 // Per-sampler adaptive state, all [T][C] (or [d*d][C], [AI*d][C]) chain-fastest.
@@ -38,7 +43,8 @@ int fused_bern_logit_tiles(int n);
 size_t fused_bern_logit_xpad_len(int n, int p);
 void fused_bern_logit_prepare_x(const double* X_rowmajor_dev, const double* y_dev, int n, int p, int ld, double* Xpad_dev,
                                 cudaStream_t st);
+// tiles [tile_begin, tile_end) of 128 nodes (data sharding gives each rank whole tiles)
 void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
-                             cudaStream_t st);
+                             int tile_begin, int tile_end, cudaStream_t st);
 
 }  // namespace nimb

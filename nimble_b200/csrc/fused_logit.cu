@@ -201,7 +201,7 @@ __device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scala
 template <int NK>
 __global__ void __launch_bounds__(FT_THREADS, 2)
 k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ ypad, int n, int p,
-                   const double* __restrict__ state, int beta_slot, int C, int tiles_per_chunk,
+                   const double* __restrict__ state, int beta_slot, int C, int tiles_per_chunk, int tile_begin, int tile_end,
                    double* __restrict__ partials) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int P4 = 4 * NK;
@@ -233,9 +233,8 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
   __syncthreads();
 
   double csum[4] = {0.0, 0.0, 0.0, 0.0};
-  const int ntiles_total = (n + FT_M - 1) / FT_M;
-  const int tile_lo = chunk * tiles_per_chunk;
-  const int tile_hi = min(ntiles_total, tile_lo + tiles_per_chunk);
+  const int tile_lo = tile_begin + chunk * tiles_per_chunk;
+  const int tile_hi = min(tile_end, tile_lo + tiles_per_chunk);
   const uint32_t x_bytes = (uint32_t)(FT_M * P4 * sizeof(double)), y_bytes = (uint32_t)(FT_M * sizeof(double));
 
   if (tid == 0 && tile_lo < tile_hi) {
@@ -349,7 +348,7 @@ void fused_bern_logit_prepare_x(const double* X, const double* y, int n, int p, 
 
 template <int NK>
 static void launch_nk(const double* Xpad, const double* ypad, int n, int p, const double* state, int beta_slot, int C,
-                      int chunks, int tpc, double* partials, cudaStream_t st) {
+                      int chunks, int tpc, int tb, int te, double* partials, cudaStream_t st) {
   size_t smem = sizeof(double) * (2 * ((size_t)FT_M * 4 * NK + FT_M) + 2 * FT_NC) + 16;
   static bool attr_set = false;
   if (!attr_set) {
@@ -357,20 +356,20 @@ static void launch_nk(const double* Xpad, const double* ypad, int n, int p, cons
     attr_set = true;
   }
   dim3 grid((C + FT_NC - 1) / FT_NC, chunks);
-  k_fused_bern_logit<NK><<<grid, FT_THREADS, smem, st>>>(Xpad, ypad, n, p, state, beta_slot, C, tpc, partials);
+  k_fused_bern_logit<NK><<<grid, FT_THREADS, smem, st>>>(Xpad, ypad, n, p, state, beta_slot, C, tpc, tb, te, partials);
 }
 
 void fused_bern_logit_launch(const double* Xpad, int n, int p, const double* state, int beta_slot, int C, double* partials,
-                             cudaStream_t st) {
+                             int tile_begin, int tile_end, cudaStream_t st) {
   int chunks = chunks_for(n);
-  int ntiles = (n + FT_M - 1) / FT_M;
-  int tpc = (ntiles + chunks - 1) / chunks;
+  int ntiles = std::max(0, tile_end - tile_begin);
+  int tpc = std::max(1, (ntiles + chunks - 1) / chunks);
   const double* ypad = Xpad + xpad_x_len(n, p);
   switch (nk_of(p)) {
-    case 4: launch_nk<4>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
-    case 8: launch_nk<8>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
-    case 13: launch_nk<13>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
-    default: launch_nk<16>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, partials, st); break;
+    case 4: launch_nk<4>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, tile_begin, tile_end, partials, st); break;
+    case 8: launch_nk<8>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, tile_begin, tile_end, partials, st); break;
+    case 13: launch_nk<13>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, tile_begin, tile_end, partials, st); break;
+    default: launch_nk<16>(Xpad, ypad, n, p, state, beta_slot, C, chunks, tpc, tile_begin, tile_end, partials, st); break;
   }
 }
 

@@ -281,3 +281,26 @@ def test_fastmath_accuracy(b200, oracle):
         assert np.max(np.abs(got[wc] - want[wc]) / np.maximum(np.abs(want[wc]), 1e-300)) < 1e-12
         assert np.max(np.abs(got[fin] - want[fin])) < 2e-2      # noise level of log(1 - p) itself near p = 1 - 1e-13
         assert np.isnan(dev(which, np.array([np.nan]))[0])
+
+
+@pytest.mark.parametrize("name", ["logistic_big", "lmm", "glmm", "occupancy"])
+def test_data_shards_add_up_to_the_whole(b200, name):
+    """Data-node sharding, arithmetic only (no communicator): the block sums of the R per-rank models add up to the
+    unsharded block sum, for the fused kernel (tile ranges) and the generic kernel (node ranges)."""
+    m, conf = (configs.logistic(N=5000, p=50, seed=6) if name == "logistic_big" else sm.SMALL[name]())
+    C, R = 6, 3
+    inits = sm.random_inits(m, C, 11, 0.1)
+    whole = compile_on(b200, conf)._ensure(C)
+    whole.set_values(inits)
+    for di, d in enumerate(whole.builder.decls):
+        if d.value_kind != 0:
+            continue
+        total = whole.calculate(di)
+        parts = np.zeros(C)
+        covered = 0
+        for r in range(R):
+            dm = compile_on(b200, conf)._ensure(C)
+            dm.enable_data_sharding(R, r, None, min_nodes=256)
+            dm.set_values(inits)
+            parts += dm.calculate(di)
+        assert rel_err(parts, total).max() < RTOL_LP, (name, di)

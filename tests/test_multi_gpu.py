@@ -1,0 +1,58 @@
+"""GPU, two ranks on two GPUs: data-node sharding with the NCCL all-reduce inside the library, and chain sharding.
+Skipped unless the box has at least two GPUs (never run two ranks on one GPU: kernels that wait on one another)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+def _data_shard_worker(rank, world, port, name, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import nimble_b200 as nb
+    from nimble_b200 import _capi
+    from tests import small_models as sm
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    backend = _capi.default_backend()
+    m, conf = sm.SMALL[name]()
+    C = 4
+    inits = sm.random_inits(m, C, 21, 0.1)
+    if name == "occupancy":
+        inits[:, m.var_slot["z"]:m.var_slot["z"] + 300] = 1.0
+    ids = [backend.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(ids, src=0)
+    cm = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=rank)
+    dm = cm._ensure(C)
+    dm.enable_data_sharding(world, rank, ids[0], min_nodes=256)
+    s = cm.run_chains(inits, 260, 10, 1, True, 17)
+    np.save(os.path.join(out_dir, "rank%d.npy" % rank), s)
+    if rank == 0:
+        ref = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=0)
+        np.save(os.path.join(out_dir, "single.npy"), ref.run_chains(inits, 260, 10, 1, True, 17))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["logistic", "lmm", "glmm", "occupancy"])
+def test_data_sharded_run_matches_single_gpu(tmp_path, name):
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    port = 29600 + os.getpid() % 2000
+    mp.spawn(_data_shard_worker, args=(2, port, name, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "rank0.npy"), np.load(tmp_path / "rank1.npy")
+    single = np.load(tmp_path / "single.npy")
+    assert np.array_equal(r0, r1)                    # every rank took identical decisions
+    err = np.abs(r0 - single) / np.maximum(1.0, np.abs(single))
+    assert err.max() < 1e-9, err.max()               # same chains as the unsharded run (summation order differs)
