@@ -62,6 +62,7 @@ class Backend:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
             self._peaks = fn("measure_fp64_peaks", [C.c_int, _dp, _dp])
+            self._mixed = fn("measure_fp64_mixed", [C.c_int, _dp])
             self._nccl_id = fn("nccl_unique_id", [C.c_void_p])
             self._shard = fn("enable_data_sharding", [vp, C.c_int32, C.c_int32, C.c_void_p, C.c_int32])
 
@@ -83,6 +84,11 @@ class Backend:
         buf = C.create_string_buffer(128)
         self.check(self._nccl_id(buf))
         return buf.raw
+
+    def fp64_mixed_peak(self, device=0):
+        a = C.c_double()
+        self.check(self._mixed(device, C.byref(a)))
+        return a.value
 
     def fp64_peaks(self, device=0):
         a, b = C.c_double(), C.c_double()
