@@ -149,6 +149,52 @@ __device__ double calc_node(const DevTab& T, int di, int i, int c, int ov_slot, 
   return NAN;
 }
 
+// Parameters whose programs do not read anything indexed by the node (sd = sig_e, shape = alpha, ...) are evaluated
+// once per thread instead of once per node; for dnorm the log(sd) term is carried along.  Results are bit-identical to
+// calc_node(): the same operations on the same values, only not repeated.
+struct Hoist { bool h0, h1; double p0, p1, l1; };
+__device__ __forceinline__ Hoist make_hoist(const DevTab& T, int di, int c, int ov_slot, double ov_val) {
+  const nimb200_decl& d = T.decl[di];
+  Hoist H; H.p0 = H.p1 = H.l1 = 0.0;
+  H.h0 = d.dist != NIMB_DCAT && T.pconst[3 * di] != 0;
+  H.h1 = d.dist != NIMB_DCAT && d.nparam > 1 && T.pconst[3 * di + 1] != 0;
+  if (H.h0) H.p0 = eval_prog(T, c, d.prog_off[0], d.prog_len[0], 0, 0, ov_slot, ov_val);
+  if (H.h1) {
+    H.p1 = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, ov_slot, ov_val);
+    if (d.dist == NIMB_DNORM) H.l1 = log(H.p1);
+  }
+  return H;
+}
+__device__ __forceinline__ double dnorm_logsd(double x, double mu, double sigma, double logsigma) {  // dnorm() with log(sigma) given
+  if (isnan(x) || isnan(mu) || isnan(sigma)) return x + mu + sigma;
+  if (sigma < 0) return NAN;
+  if (!isfinite(sigma)) return -INFINITY;
+  if (!isfinite(x) && mu == x) return NAN;
+  if (sigma == 0) return (x == mu) ? INFINITY : -INFINITY;
+  x = (x - mu) / sigma;
+  if (!isfinite(x)) return -INFINITY;
+  x = fabs(x);
+  if (x >= 2 * sqrt(DBL_MAX)) return -INFINITY;
+  return -(NIMB_LN_SQRT_2PI + 0.5 * x * x + logsigma);
+}
+__device__ double calc_node_h(const DevTab& T, int di, int i, int c, int ov_slot, double ov_val, const Hoist& H) {
+  const nimb200_decl& d = T.decl[di];
+  if (d.dist == NIMB_DCAT) return calc_node(T, di, i, c, ov_slot, ov_val);
+  double x = node_value(T, d, i, c, ov_slot, ov_val);
+  double p0 = H.h0 ? H.p0 : eval_prog(T, c, d.prog_off[0], d.prog_len[0], i, 0, ov_slot, ov_val), p1 = 0;
+  if (d.nparam > 1) p1 = H.h1 ? H.p1 : eval_prog(T, c, d.prog_off[1], d.prog_len[1], i, 0, ov_slot, ov_val);
+  switch (d.dist) {
+    case NIMB_DNORM: return H.h1 ? dnorm_logsd(x, p0, p1, H.l1) : dnorm(x, p0, p1);
+    case NIMB_DGAMMA: return dgamma(x, p0, p1);
+    case NIMB_DPOIS: return dpois(x, p0);
+    case NIMB_DBINOM: return dbinom(x, p0, p1);
+    case NIMB_DBETA: return dbeta(x, p0, p1);
+    case NIMB_DLOGIS: return dlogis(x, p0, p1);
+    case NIMB_DEXP: return dexp_nimble(x, p0);
+  }
+  return NAN;
+}
+
 struct Sel { int lo, hi; const int32_t* idx; int nlo, nhi; };  // [nlo,nhi): node instances this rank owns (data sharding)
 __device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, int t) {
   Sel s; s.idx = nullptr;
@@ -169,13 +215,25 @@ __device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, in
 __device__ __forceinline__ bool counts_here(const DevTab& T, int decl) { return T.rank == 0 || T.sharded[decl]; }
 
 // conjugate contribution of one dependent node (P/R/MCMC_conjugacy.R:80-93, 109-115; probing :766-820)
+// the dependent's parameter that the posterior needs besides the linked one (tau | mean of dnorm, shape of dgamma);
+// *hoisted is set when its program does not depend on the node, so the caller may reuse the value
+__device__ __forceinline__ double conj_par(const DevTab& T, const nimb200_dep& dp, int node, int c, bool gam, bool* hoistable) {
+  const nimb200_decl& dd = T.decl[dp.decl];
+  if (dd.dist == NIMB_DNORM) {
+    *hoistable = T.pconst[3 * dp.decl + (gam ? 0 : 1)] != 0;
+    return gam ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
+  }
+  if (dd.dist == NIMB_DGAMMA) { *hoistable = T.pconst[3 * dp.decl] != 0; return get_param(T, dp.decl, node, c, 0, -1, 0.0); }
+  *hoistable = true;
+  return 0.0;
+}
 __device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep& dp, int node, int c, int slot, bool gam,
-                                             double& c0, double& c1) {
+                                             double& c0, double& c1, bool have_par = false, double par_in = 0.0) {
   const nimb200_decl& dd = T.decl[dp.decl];
   double value = node_value(T, dd, node, c, -1, 0.0);
   double par = 0, offset = 0, coeff = 1;
-  if (dd.dist == NIMB_DNORM) par = gam ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
-  else if (dd.dist == NIMB_DGAMMA) par = get_param(T, dp.decl, node, c, 0, -1, 0.0);
+  bool dummy;
+  par = have_par ? par_in : conj_par(T, dp, node, c, gam, &dummy);
   if (dp.link == NIMB_LINK_ADDITIVE || dp.link == NIMB_LINK_LINEAR) offset = get_param(T, dp.decl, node, c, dp.param, slot, 0.0);
   if (dp.link == NIMB_LINK_LINEAR) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0) - offset;
   if (dp.link == NIMB_LINK_MULTIPLICATIVE) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0);
@@ -271,11 +329,12 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
         const nimb200_dep dp = T.deps[sp.dep_off + e];
         if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
         Sel s = sel_of(T, dp, t);
+        Hoist Hn = make_hoist(T, dp.decl, c, slot, prop), Ho = make_hoist(T, dp.decl, c, -1, 0.0);
         for (int k = s.lo; k < s.hi; k++) {
           int node = s.idx ? s.idx[k] : k;
           if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
-          double nw = calc_node(T, dp.decl, node, c, slot, prop);
-          double od = calc_node(T, dp.decl, node, c, -1, 0.0);
+          double nw = calc_node_h(T, dp.decl, node, c, slot, prop, Hn);
+          double od = calc_node_h(T, dp.decl, node, c, -1, 0.0, Ho);
           if (dp.stage == 0) v0 += nw - od; else v1 += nw - od;
         }
       }
@@ -295,11 +354,12 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
         const nimb200_dep dp = T.deps[sp.dep_off + e];
         if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
         Sel s = sel_of(T, dp, t);
+        Hoist Hn = make_hoist(T, dp.decl, c, slot, other), Ho = make_hoist(T, dp.decl, c, -1, 0.0);
         for (int k = s.lo; k < s.hi; k++) {
           int node = s.idx ? s.idx[k] : k;
           if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
-          v0 += calc_node(T, dp.decl, node, c, -1, 0.0);
-          double o = calc_node(T, dp.decl, node, c, slot, other);
+          v0 += calc_node_h(T, dp.decl, node, c, -1, 0.0, Ho);
+          double o = calc_node_h(T, dp.decl, node, c, slot, other, Hn);
           if (dp.stage == 0) v1 += o; else v2 += o;
         }
       }
@@ -322,10 +382,12 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
       if (dp.stage != 1) continue;
       if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
       Sel s = sel_of(T, dp, t);
+      bool hp = false;
+      double par = conj_par(T, dp, 0, c, gam, &hp);
       for (int k = s.lo; k < s.hi; k++) {
         int node = s.idx ? s.idx[k] : k;
         if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
-        conj_contrib(T, dp, node, c, slot, gam, v0, v1);
+        conj_contrib(T, dp, node, c, slot, gam, v0, v1, hp, par);
       }
     }
   }
@@ -361,14 +423,19 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
   int tile0 = lo + blockIdx.x * (nl * npt);
   double a0 = 0, a1 = 0;
   if (c < T.C) {
+    Hoist H;
+    if (MODE != 2) H = make_hoist(T, di, c, -1, 0.0);
+    bool hp = false;
+    double par = 0.0;
+    if (MODE == 2) par = conj_par(T, dp, 0, c, gam != 0, &hp);
     for (int q = 0; q < npt; q++) {
       int k = tile0 + q * nl + lane_n;
       if (k >= hi) break;
       int node = idx ? idx[k] : k;
       if (idx && (node < T.shard_lo[di] || node >= T.shard_hi[di])) continue;
-      if (MODE == 0) a0 += calc_node(T, di, node, c, -1, 0.0);
-      else if (MODE == 1) out_nodes[(size_t)(k - lo) * T.C + c] = calc_node(T, di, node, c, -1, 0.0);
-      else conj_contrib(T, dp, node, c, slot, gam != 0, a0, a1);
+      if (MODE == 0) a0 += calc_node_h(T, di, node, c, -1, 0.0, H);
+      else if (MODE == 1) out_nodes[(size_t)(k - lo) * T.C + c] = calc_node_h(T, di, node, c, -1, 0.0, H);
+      else conj_contrib(T, dp, node, c, slot, gam != 0, a0, a1, hp, par);
     }
   }
   if (MODE == 1) return;
@@ -389,15 +456,17 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
   }
 }
 
-// fixed-order reduction of the tile partials: dst[k][c] = sum_b partials[b][k][c]
-__global__ void k_reduce(const double* partials, int nb, int K, int C, double* dst0, double* dst1) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  for (int kk = 0; kk < K; kk++) {
-    double s = 0;
-    for (int b = 0; b < nb; b++) s += partials[((size_t)b * K + kk) * C + c];
-    (kk == 0 ? dst0 : dst1)[c] = s;
-  }
+// fixed-order reduction of the tile partials: dst[k][c] = sum_b partials[b][k][c].  One warp per (chain, k): lane l adds
+// tiles l, l+32, ... in order, then a butterfly over the lanes -- the same order every run, so sums are reproducible.
+__global__ void k_reduce(const double* __restrict__ partials, int nb, int K, int C, double* dst0, double* dst1) {
+  int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= C * K) return;
+  int c = w % C, kk = w / C;
+  double s = 0;
+  for (int b = lane; b < nb; b += 32) s += partials[((size_t)b * K + kk) * C + c];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) (kk == 0 ? dst0 : dst1)[c] = s;
 }
 
 // wide RW: proposal for every chain; the old value is parked in tsave
@@ -784,7 +853,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, lo / 128,
                             (hi + 127) / 128, m->stream);
     m->launches++;
-    k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
+    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
@@ -800,7 +869,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
   else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
   m->launches++;
-  k_reduce<<<(C + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
+  k_reduce<<<(C * K * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
   m->launches++;
   CK(cudaGetLastError());
   if (shard && m->nccl_comm) {
@@ -999,6 +1068,23 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   TRYCU(cudaMemcpyAsync(m->d_shard_lo, m->shard_lo.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
   TRYCU(cudaMemcpyAsync(m->d_shard_hi, m->shard_hi.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
   TRYCU(cudaMemcpyAsync(m->d_sharded, m->sharded.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
+  {
+    std::vector<int32_t> pc(3 * m->decl.size() + 1, 0);
+    for (size_t i = 0; i < m->decl.size(); i++)
+      for (int pp = 0; pp < m->decl[i].nparam && pp < 3; pp++) {
+        bool cst = true;
+        for (int q = 0; q < m->decl[i].prog_len[pp]; q++) {
+          int op = m->ops[m->decl[i].prog_off[pp] + q].op;
+          if (op == NIMB_OP_DATA || op == NIMB_OP_CVARN || op == NIMB_OP_INPROD || op == NIMB_OP_DATAJ || op == NIMB_OP_CVARJ) cst = false;
+        }
+        pc[3 * i + pp] = cst ? 1 : 0;
+      }
+    int32_t* dpc = nullptr;
+    TRY(dev_alloc(m, &dpc, pc.size()));
+    TRYCU(cudaMemcpyAsync(dpc, pc.data(), sizeof(int32_t) * pc.size(), cudaMemcpyHostToDevice, m->stream));
+    TRYCU(cudaStreamSynchronize(m->stream));
+    m->T.pconst = dpc;
+  }
   m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
   m->sweep_sharded.assign(m->samplers.size(), 0);
   // fused family: re-lay X once (row-major, rows padded to a multiple of 4 doubles)

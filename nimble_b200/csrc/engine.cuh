@@ -23,6 +23,8 @@ struct DevTab {
   const int32_t* shard_hi;
   const int32_t* sharded;
   int rank, nranks;
+  // pconst[3*d + p] != 0: parameter program p of declaration d does not depend on the node index (hoisted out of node loops)
+  const int32_t* pconst;
 };
 
 // Per-sampler adaptive state, all [T][C] (or [d*d][C], [AI*d][C]) chain-fastest.
