@@ -141,6 +141,16 @@ def cpu_baseline(a, conf, model, niter, warm=1):
             "ms_per_iteration_per_chain": dt / niter * 1e3, "seconds": dt}, samples, dt, chains
 
 
+def _emit(line):
+    """The JSON line goes to the process's ORIGINAL stdout; everything else that lands on fd 1 meanwhile (NCCL's version
+    banner, library chatter) has been diverted to stderr, so stdout carries exactly one line."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -162,7 +172,7 @@ def main():
                                               "here (no R / Rmath); this is its CPU restatement (oracle/), one chain per core"}),
                 "cpu_baseline": cb, "min_ess_per_sec": (mess / dt if mess is not None else None),
                 "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        _emit(line)
         return 0
 
     import torch
@@ -311,7 +321,7 @@ def main():
                 "min_ess_per_sec": mess * world / (ms_max * 1e-3),
                 "min_ess_note": "sum over chains of coda-style ESS of the timed iterations' samples (adaptation still running); rank 0's chains x n_gpus",
                 "evals_per_iteration_per_chain": evals_iter, "host_lowering_seconds": t_build, "full_protocol": full}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
