@@ -94,4 +94,25 @@ __device__ __forceinline__ double log_f64(double t) {
   return fma(kd, c_misc[4], fma(kd, c_misc[5], lm));
 }
 
+// ---- table-driven exp / log for the fused epilogue ------------------------------------------------------------
+// The FP64 multipliers are the saturated resource of the fused kernel (DMMA and DFMA share them), the load/store
+// units are idle: range reduction against small tables held in shared memory moves work from the former to the
+// latter.  exp: 64-entry 2^(j/64) table + degree-5 polynomial (12 FP64 instructions instead of 19); log: 129-entry
+// table of reciprocals / logarithms of the interval centres 1 + j/128 + degree-7 log1p (10 instead of 24, and no
+// reciprocal).  Tables: gen_math_tables.py (60-digit arithmetic).  <= 1 ulp; log keeps full relative accuracy as
+// t -> 1 (centre 1 has invc = 1, logc = 0; the binade [0.5, 1) has its own table with ln 2 already subtracted).
+#include "math_tables.inc"
+struct MathTab {
+  double expT[64];
+  double logA[129];
+  double logB[129];
+  double invc[129];
+};
+__device__ const MathTab g_mathtab = {NIMB_EXPT_INIT, NIMB_LOGA_INIT, NIMB_LOGB_INIT, NIMB_INVC_INIT};
+__device__ __constant__ double c_tab_misc[12] = {
+    NIMB_EXP_L, 6755399441055744.0, -NIMB_EXP_HI, -NIMB_EXP_LO,
+    1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0,                              // exp(r) = 1 + r (1 + r/2 + r^2/6 + r^3/24 + r^4/120)
+    0.6931471805599453,                                              // ln 2
+    1.0 / 7.0, -1.0 / 6.0, 1.0 / 5.0, -1.0 / 4.0};                   // log1p(r) = r + r^2 (-1/2 + r/3 - r^2/4 + ... + r^5/7)
+
 }  // namespace nimb

@@ -80,7 +80,7 @@ __device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
 }
 
 template <int W>
-__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W]) {
+__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const MathTab* __restrict__ tab) {
   bool slow = false;
 #pragma unroll
   for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
@@ -91,107 +91,84 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
   }
   double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
   int n[W];
-  // ---- e = exp(-eta), -eta in [-inf, 690].  Below -708 the result only has to vanish against 1 (d = 1 + e = 1), so the
-  // argument is clamped there and 2^n can be applied by one integer add to the exponent field (always a normal number).
+  // ---- e = exp(-eta): x = k ln2/64 + r, e = 2^(k>>6) T[k&63] (1 + r P(r)).  x is clamped at -708: below that e only has to
+  // vanish against 1, and 2^(k>>6) can then always be applied by one integer add to the exponent field.
 #pragma unroll
   for (int j = 0; j < W; j++) x[j] = fmax(-eta[j], -708.0);
 #pragma unroll
-  for (int j = 0; j < W; j++) t[j] = fma(x[j], c_misc[0], c_misc[1]);
+  for (int j = 0; j < W; j++) t[j] = fma(x[j], c_tab_misc[0], c_tab_misc[1]);
 #pragma unroll
-  for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_misc[1]; }
+  for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_tab_misc[1]; }
 #pragma unroll
-  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_misc[2], x[j]);
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[2], x[j]);
 #pragma unroll
-  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_misc[3], r[j]);
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[3], r[j]);
 #pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(c_exp_poly[0], r[j], c_exp_poly[1]);
+  for (int j = 0; j < W; j++) pl[j] = fma(r[j], c_tab_misc[4], c_tab_misc[5]);
 #pragma unroll
-  for (int c = 2; c < 12; c++) {
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_tab_misc[6]);
 #pragma unroll
-    for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_exp_poly[c]);
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 0.5);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+  for (int j = 0; j < W; j++) {
+    double T = tab->expT[n[j] & 63];
+    double v = fma(T * r[j], pl[j], T);
+    e[j] = __hiloint2double(__double2hiint(v) + ((n[j] >> 6) << 20), __double2loint(v));
   }
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
-#pragma unroll
-  for (int j = 0; j < W; j++) e[j] = __hiloint2double(__double2hiint(pl[j]) + (n[j] << 20), __double2loint(pl[j]));
-  // ---- p = 1/(1+e): d in [1, 1e300]; two Newton steps on a >= 20-bit seed (faithful rounding)
+  // ---- p = 1/(1+e): d in [1, 1e300]; Newton on a >= 20-bit seed, last step on the residual
 #pragma unroll
   for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];
 #pragma unroll
   for (int j = 0; j < W; j++) p[j] = rcp_approx(d[j]);
 #pragma unroll
-  for (int it = 0; it < 2; it++) {
+  for (int it = 0; it < 3; it++) {
 #pragma unroll
     for (int j = 0; j < W; j++) u[j] = fma(-d[j], p[j], 1.0);
 #pragma unroll
     for (int j = 0; j < W; j++) p[j] = fma(p[j], u[j], p[j]);
   }
-#pragma unroll
-  for (int j = 0; j < W; j++) {  // last step on the residual: correctly rounded in all but rare cases
-    u[j] = fma(-d[j], p[j], 1.0);
-    p[j] = fma(p[j], u[j], p[j]);
-  }
   // ---- t = y ? p : q.  For y = 0 the rounding error delta of q = fl(1-p) is added back inside the logarithm:
-  // log(q) + delta/q = log(q + delta) to first order, and q + delta enters as f = (m - 1) + delta * 2^-k.
+  // log(q) + delta/q = log(q + delta) to first order.
 #pragma unroll
   for (int j = 0; j < W; j++) q[j] = 1.0 - p[j];
-  double m[W], f[W], g[W], yv[W], s[W], z[W], P[W], kd[W], dl[W];
-  bool zero[W];
+  double dl[W];
 #pragma unroll
   for (int j = 0; j < W; j++) {
     dl[j] = y1 ? 0.0 : (1.0 - q[j]) - p[j];  // exact
     t[j] = y1 ? p[j] : q[j];
   }
-  // ---- log(t), t = 0 or a normal number in [2^-1000, 1]
+  // ---- log(t), t = 0 or a normal number in [2^-1000, 1]: t = 2^e m, m in [1,2), centre c = 1 + j/128 (j = 128 -> e+1, c = 1)
 #pragma unroll
   for (int j = 0; j < W; j++) {
     int hi = __double2hiint(t[j]), lo = __double2loint(t[j]);
-    zero[j] = (hi | lo) == 0;
-    int k = (hi >> 20) - 1023;
-    hi = (hi & 0x000fffff) | 0x3ff00000;
-    bool big = hi > 0x3ff6a09e;  // m > sqrt(2): halve
-    hi = big ? hi - 0x00100000 : hi;
-    k = big ? k + 1 : k;
-    m[j] = __hiloint2double(hi, lo);
-    kd[j] = (double)k;
-    dl[j] = dl[j] * __hiloint2double((1023 - k) << 20, 0);  // delta * 2^-k (delta = 0 for y = 1)
-  }
-#pragma unroll
-  for (int j = 0; j < W; j++) { f[j] = (m[j] - 1.0) + dl[j]; g[j] = m[j] + 1.0; }
-#pragma unroll
-  for (int j = 0; j < W; j++) yv[j] = rcp_approx(g[j]);
-#pragma unroll
-  for (int it = 0; it < 2; it++) {
-#pragma unroll
-    for (int j = 0; j < W; j++) u[j] = fma(-g[j], yv[j], 1.0);
-#pragma unroll
-    for (int j = 0; j < W; j++) yv[j] = fma(yv[j], u[j], yv[j]);
-  }
-#pragma unroll
-  for (int j = 0; j < W; j++) s[j] = f[j] * yv[j];
-#pragma unroll
-  for (int j = 0; j < W; j++) z[j] = s[j] * s[j];
-#pragma unroll
-  for (int j = 0; j < W; j++) P[j] = fma(c_log_poly[0], z[j], c_log_poly[1]);
-#pragma unroll
-  for (int c = 2; c < 10; c++) {
-#pragma unroll
-    for (int j = 0; j < W; j++) P[j] = fma(P[j], z[j], c_log_poly[c]);
-  }
-#pragma unroll
-  for (int j = 0; j < W; j++) {
-    double s2 = s[j] + s[j];
-    double lm = fma(s2 * z[j], P[j], s2);
-    double lg = fma(kd[j], c_misc[4], fma(kd[j], c_misc[5], lm));
-    out[j] = zero[j] ? -INFINITY : lg;
+    bool zero = (hi | lo) == 0;
+    int ex = (hi >> 20) - 1023;
+    int fr = hi & 0x000fffff;
+    int idx = (fr + 0x1000) >> 13;
+    ex += idx >> 7;
+    double m = __hiloint2double(fr | 0x3ff00000, lo);
+    double ic = tab->invc[idx];
+    bool em1 = ex == -1;
+    double lc = em1 ? tab->logB[idx] : tab->logA[idx];
+    double kd = em1 ? 0.0 : (double)ex;
+    double rr = fma(m, ic, -1.0);
+    rr = fma(dl[j] * __hiloint2double((1023 - (hi >> 20) + 1023) << 20, 0), ic, rr);  // + delta 2^-e / c
+    double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
+    Q = fma(Q, rr, c_tab_misc[10]);
+    Q = fma(Q, rr, c_tab_misc[11]);
+    Q = fma(Q, rr, 1.0 / 3.0);
+    Q = fma(Q, rr, -0.5);
+    double lp = fma(rr * rr, Q, rr);
+    double lg = fma(kd, c_tab_misc[7], lc + lp);
+    out[j] = zero ? -INFINITY : lg;
   }
 }
 
 __device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)
   double in[1] = {eta}, o[1];
-  bern_logit_lp_vec<1>(in, y1, o);
+  bern_logit_lp_vec<1>(in, y1, o, &g_mathtab);
   return o[0];
 }
 
@@ -209,6 +186,9 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
   double* stage0 = (double*)smem_raw;
   double* red = stage0 + 2 * stage_doubles;             // [2][FT_NC]
   uint64_t* bar = (uint64_t*)(red + 2 * FT_NC);          // [2]
+  MathTab* tab = (MathTab*)(bar + 2);                    // exp / log tables
+  for (int i = threadIdx.x; i < (int)(sizeof(MathTab) / sizeof(double)); i += FT_THREADS)
+    ((double*)tab)[i] = ((const double*)&g_mathtab)[i];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int wn = warp & 3, wg = warp >> 2;               // warp: chains wn*16 .. +15, rows wg*64 .. +63 of each tile
@@ -272,7 +252,7 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
         double yv = ys[wg * 64 + mp * 16 + mt * 8 + (lane >> 2)];
         bool live = yv >= 0.0, y1 = yv != 0.0;          // -1 marks the zero-padded rows past n
         double lp[4];
-        bern_logit_lp_vec<4>(acc[mt], y1, lp);
+        bern_logit_lp_vec<4>(acc[mt], y1, lp, tab);
 #pragma unroll
         for (int j = 0; j < 4; j++) csum[j] += live ? lp[j] : 0.0;
       }
@@ -349,7 +329,7 @@ void fused_bern_logit_prepare_x(const double* X, const double* y, int n, int p, 
 template <int NK>
 static void launch_nk(const double* Xpad, const double* ypad, int n, int p, const double* state, int beta_slot, int C,
                       int chunks, int tpc, int tb, int te, double* partials, cudaStream_t st) {
-  size_t smem = sizeof(double) * (2 * ((size_t)FT_M * 4 * NK + FT_M) + 2 * FT_NC) + 16;
+  size_t smem = sizeof(double) * (2 * ((size_t)FT_M * 4 * NK + FT_M) + 2 * FT_NC) + 16 + sizeof(MathTab);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_fused_bern_logit<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
