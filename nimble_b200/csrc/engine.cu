@@ -303,10 +303,13 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 // 32 lanes of a warp read the same data node and 32 consecutive chain copies of each state slot.
 // PHASE 0: everything in one kernel.  Data-sharded models split it: PHASE 1 accumulates this rank's share of the
 // per-(target, chain) sums into buf[t][k][c] (k < 3), the host all-reduces buf, PHASE 2 decides / draws from it.
-template <int PHASE>
+// LANES = 32: one WARP per (target, chain), its lanes stride over the dependent nodes and the partial sums meet in a fixed-order
+// butterfly -- used when there are few (target, chain) pairs but each has many dependents (tau_b / mu_b over 50 betas).
+template <int PHASE, int LANES>
 __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* buf) {
   const nimb200_sampler sp = T.samplers[sid];
-  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t gid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
+  const int lane = LANES == 1 ? 0 : (threadIdx.x & (LANES - 1));
   int c = (int)(gid % T.C);
   size_t tq = gid / T.C;
   if (tq >= (size_t)sp.n_targets) return;
@@ -330,7 +333,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
         if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
         Sel s = sel_of(T, dp, t);
         Hoist Hn = make_hoist(T, dp.decl, c, slot, prop), Ho = make_hoist(T, dp.decl, c, -1, 0.0);
-        for (int k = s.lo; k < s.hi; k++) {
+        for (int k = s.lo + lane; k < s.hi; k += LANES) {
           int node = s.idx ? s.idx[k] : k;
           if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
           double nw = calc_node_h(T, dp.decl, node, c, slot, prop, Hn);
@@ -338,6 +341,15 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
           if (dp.stage == 0) v0 += nw - od; else v1 += nw - od;
         }
       }
+    }
+    if (LANES > 1) {
+#pragma unroll
+      for (int o = LANES / 2; o > 0; o >>= 1) {
+        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+        v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+      }
+      if (lane != 0) return;
     }
     if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = 0.0; return; }
     bool jump;
@@ -355,7 +367,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
         if (PHASE == 1 && !counts_here(T, dp.decl)) continue;
         Sel s = sel_of(T, dp, t);
         Hoist Hn = make_hoist(T, dp.decl, c, slot, other), Ho = make_hoist(T, dp.decl, c, -1, 0.0);
-        for (int k = s.lo; k < s.hi; k++) {
+        for (int k = s.lo + lane; k < s.hi; k += LANES) {
           int node = s.idx ? s.idx[k] : k;
           if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
           v0 += calc_node_h(T, dp.decl, node, c, -1, 0.0, Ho);
@@ -363,6 +375,15 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
           if (dp.stage == 0) v1 += o; else v2 += o;
         }
       }
+    }
+    if (LANES > 1) {
+#pragma unroll
+      for (int o = LANES / 2; o > 0; o >>= 1) {
+        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+        v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+      }
+      if (lane != 0) return;
     }
     if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = v2; return; }
     double currentLogProb = v0, otherPrior = v1, otherDeps = v2;
@@ -384,12 +405,21 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
       Sel s = sel_of(T, dp, t);
       bool hp = false;
       double par = conj_par(T, dp, 0, c, gam, &hp);
-      for (int k = s.lo; k < s.hi; k++) {
+      for (int k = s.lo + lane; k < s.hi; k += LANES) {
         int node = s.idx ? s.idx[k] : k;
         if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
         conj_contrib(T, dp, node, c, slot, gam, v0, v1, hp, par);
       }
     }
+  }
+  if (LANES > 1) {
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) {
+      v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+      v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+      v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+    }
+    if (lane != 0) return;
   }
   if (PHASE == 1) { bp[0] = v0; bp[(size_t)T.C] = v1; bp[2 * (size_t)T.C] = 0.0; return; }
   const nimb200_dep tp = T.deps[sp.dep_off];
@@ -484,32 +514,32 @@ __global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, Sa
   pls[c] = propLogScale;
 }
 
-// wide RW_block: rmnorm_chol(values, chol_propCov_scale, prec_param = 0), dists.cpp:1132-1164
+// wide RW_block: rmnorm_chol(values, chol_propCov_scale, prec_param = 0), dists.cpp:1132-1164.
+// Block = 16 chains x 64 rows: thread (c, j) first draws the normals of pair j, then forms row j of x := U^T z with the
+// same descending accumulation order as the reference-BLAS dtrmv('U','T','N') loop, so the proposal is bit-identical to
+// the sequential version while 16 x d threads share the work and the U loads stay coalesced over chains.
 __global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, int tr, SamplerDev S, double* tsave) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= T.C) return;
+  __shared__ double z[NIMB200_MAX_BLOCK_D][16];
+  const int cl = threadIdx.x, j = threadIdx.y;
+  const int c = blockIdx.x * 16 + cl;
   const nimb200_sampler sp = T.samplers[sid];
-  int d = sp.d, npair = (d + 1) / 2;
-  DrawKey key = make_key(T, seed, iter, sid, 0, c);
-  double x[NIMB200_MAX_BLOCK_D];
-  for (int j = 0; j < npair; j++) {
+  const int d = sp.d, npair = (d + 1) / 2;
+  if (c < T.C && j < npair) {
+    DrawKey key = make_key(T, seed, iter, sid, 0, c);
     double z0, z1;
     normal2(key, tr * (npair + 1) + j, z0, z1);
-    x[2 * j] = z0;
-    if (2 * j + 1 < d) x[2 * j + 1] = z1;
+    z[2 * j][cl] = z0;
+    if (2 * j + 1 < d) z[2 * j + 1][cl] = z1;
   }
+  __syncthreads();
+  if (c >= T.C || j >= d) return;
   const double* U = S.cholScale;
-  for (int j = d - 1; j >= 0; j--) {  // x := U^T x in the reference-BLAS dtrmv('U','T','N') order
-    double temp = x[j] * U[(size_t)(j + j * d) * T.C + c];
-    for (int i = j - 1; i >= 0; i--) temp += U[(size_t)(i + j * d) * T.C + c] * x[i];
-    x[j] = temp;
-  }
-  for (int j = 0; j < d; j++) {
-    double* sv = T.state + (size_t)(sp.target_slot + j) * T.C + c;
-    double cur = *sv;
-    tsave[(size_t)j * T.C + c] = cur;
-    *sv = x[j] + cur;
-  }
+  double temp = z[j][cl] * U[(size_t)(j + j * d) * T.C + c];
+  for (int i = j - 1; i >= 0; i--) temp += U[(size_t)(i + j * d) * T.C + c] * z[i][cl];
+  double* sv = T.state + (size_t)(sp.target_slot + j) * T.C + c;
+  double cur = *sv;
+  tsave[(size_t)j * T.C + c] = cur;
+  *sv = temp + cur;
 }
 
 // wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
@@ -756,6 +786,7 @@ struct nimb200_model {
   double* d_sweepbuf = nullptr;  // [T][3][C] partial sums of a sharded sweep
   size_t sweepbuf_cap = 0;
   std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
+  std::vector<size_t> sweep_deps;   // per sampler: dependent nodes of target 0 (execution-shape heuristic)
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
   cudaStream_t stream = nullptr;
@@ -1108,11 +1139,13 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   // sampler state + execution shape
   m->sdev.resize(m->samplers.size());
   m->wide.assign(m->samplers.size(), 0);
+  m->sweep_deps.assign(m->samplers.size(), 0);
   m->ran.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
     SamplerDev& S = m->sdev[s];
+    m->sweep_deps[s] = dep_count_t0(m, sp);
     TRY(dev_alloc(m, &S.scale, (size_t)TT * C));
     TRY(dev_alloc(m, &S.timesRan, (size_t)TT * C));
     TRY(dev_alloc(m, &S.timesAccepted, (size_t)TT * C));
@@ -1348,17 +1381,22 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const int TB = 128;
   if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;
+    // few (target, chain) pairs with many dependents each: a warp per pair
+    bool warp_per_pair = total <= 65536 && m->sweep_deps[s] >= 16;
+    if (warp_per_pair) total *= 32;
     unsigned nb = (unsigned)((total + TB - 1) / TB);
     if (m->nranks > 1 && m->sweep_sharded[s]) {  // partial sums -> all-reduce -> decide / draw
       size_t need = total * 3;
       if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");
-      k_sweep<1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
+      if (warp_per_pair) k_sweep<1, 32><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
+      else k_sweep<1, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       m->launches++;
       if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
-      k_sweep<2><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
+      k_sweep<2, 1><<<(unsigned)(((size_t)sp.n_targets * C + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       m->launches++;
     } else {
-      k_sweep<0><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
+      if (warp_per_pair) k_sweep<0, 32><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
+      else k_sweep<0, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
       m->launches++;
     }
   } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL) {
@@ -1380,7 +1418,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       if (sp.type == NIMB_SAMPLER_RW)
         k_rw_propose<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls);
       else
-        k_block_propose<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
+        k_block_propose<<<(C + 15) / 16, dim3(16, NIMB200_MAX_BLOCK_D), 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
       m->launches++;
       for (int e = 0; e < sp.n_dep; e++) {
         const nimb200_dep& dp = m->deps[sp.dep_off + e];
