@@ -106,14 +106,17 @@ typedef struct nimb200_decl {
   int32_t prog_off[NIMB200_MAX_PARAM]; /* parameter programs, offsets into ops[] */
   int32_t prog_len[NIMB200_MAX_PARAM];
   int32_t family;     /* NIMB_FAM_*: 0 = generic interpreter, else a fused kernel the host recognised */
-  int32_t fam_arg[4];
+  int32_t fam_arg[6];
 } nimb200_decl;
 
 enum {
   NIMB_FAM_GENERIC = 0,
   /* y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))):
    * fam_arg = {X darr id, beta slot base, p, row stride of X} */
-  NIMB_FAM_BERN_LOGIT_INPROD = 1
+  NIMB_FAM_BERN_LOGIT_INPROD = 1,
+  /* y[i] ~ dpois(lam[G(i)] * exp(b0 + b1 * x[i])), G an index map (identity / i div c / int array):
+   * fam_arg = {x darr id, lam slot base, index mode, index argument, b0 slot, b1 slot} */
+  NIMB_FAM_POIS_LOGLIN = 2
 };
 
 /* ---- node selections: which instances of a declaration depend on target t */

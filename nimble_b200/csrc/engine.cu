@@ -23,6 +23,7 @@
 #include "draws_dev.cuh"
 #include "engine.cuh"
 #include "nmath_dev.cuh"
+#include "fastmath.cuh"
 
 using namespace nimb;
 
@@ -297,6 +298,8 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
   }
   return prop;
 }
+
+#include "fused_pois.cuh"
 
 // ------------------------------------------------------------------------------------------------ sweep kernels
 // One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
@@ -778,6 +781,8 @@ struct nimb200_model {
   std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
   std::vector<int> ran;         // RW_block: iterations since last adaptation
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
+  std::vector<double*> d_nodeconst;  // per decl: data-only node constants of the fused Poisson family (or null)
+  std::vector<char> pois_sweep;      // per sampler: conjugate sweep served by k_pois_conj_sweep
   // data-node sharding (nimb200_enable_data_sharding)
   int rank = 0, nranks = 1;
   std::vector<int32_t> shard_lo, shard_hi, sharded;
@@ -859,6 +864,16 @@ static int eval_tiles(int C, int count) {
   return (count + per - 1) / per;
 }
 
+static PoisArgs pois_args(nimb200_model* m, int di) {
+  const nimb200_decl& d = m->decl[di];
+  PoisArgs a;
+  a.y = m->d_darr[d.value_ref]; a.x = m->d_darr[d.fam_arg[0]]; a.A = m->d_nodeconst[di];
+  a.mode = d.fam_arg[2]; a.arg = d.fam_arg[3];
+  a.gidx = a.mode == NIMB_IDX_IARR ? m->d_iarr[a.arg] : nullptr;
+  a.lam_slot = d.fam_arg[1]; a.b0_slot = d.fam_arg[4]; a.b1_slot = d.fam_arg[5]; a.n = d.n;
+  return a;
+}
+
 // evaluate instances [lo,hi) (through idx) of declaration di for all chains; reduced sums land in dst0 (dst1)
 static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, const int32_t* idx, double* dst0, double* dst1,
                            const nimb200_dep* dp, int slot, int gam) {
@@ -885,6 +900,20 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
                             (hi + 127) / 128, m->stream);
     m->launches++;
     k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
+    m->launches++;
+    CK(cudaGetLastError());
+    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    return 0;
+  }
+  if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && C >= 32) {
+    PoisArgs pa = pois_args(m, di);
+    const int chunks = 64;
+    int npc = ((count + chunks - 1) / chunks + PF_TILE - 1) / PF_TILE * PF_TILE;
+    if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (poisson)");
+    dim3 grid((C + PF_THREADS - 1) / PF_THREADS, chunks);
+    k_pois_sum<<<grid, PF_THREADS, 0, m->stream>>>(m->T, pa, lo, hi, npc, m->d_partials);
+    m->launches++;
+    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
@@ -1084,6 +1113,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   for (auto& d : m->decl) {
     pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
     if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
+    if (d.family == NIMB_FAM_POIS_LOGLIN) pc = std::max(pc, (size_t)64 * C);
   }
   TRY(dev_alloc(m, &m->d_partials, pc));
   m->partials_cap = pc;
@@ -1136,6 +1166,30 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     TRY(dev_alloc(m, &m->d_xpad[i], len));
     fused_bern_logit_prepare_x(m->d_darr[xid], m->d_darr[d.value_ref], d.n, p, ld, m->d_xpad[i], m->stream);
   }
+  // fused Poisson family: validate, compute the data-only node constants once
+  m->d_nodeconst.assign(m->decl.size(), nullptr);
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    nimb200_decl& d = m->decl[i];
+    if (d.family != NIMB_FAM_POIS_LOGLIN) continue;
+    int xid = d.fam_arg[0], mode = d.fam_arg[2], arg = d.fam_arg[3];
+    bool ok = d.value_kind == 0 && d.dist == NIMB_DPOIS && xid >= 0 && xid < t->n_darr && t->darr_len[xid] >= d.n &&
+              d.fam_arg[4] >= 0 && d.fam_arg[4] < t->n_slots && d.fam_arg[5] >= 0 && d.fam_arg[5] < t->n_slots &&
+              !getenv("NIMB200_NO_FUSED");
+    if (ok && mode == NIMB_IDX_IARR) ok = arg >= 0 && arg < t->n_iarr && t->iarr_len[arg] >= d.n;
+    if (ok && (mode == NIMB_IDX_DIV || mode == NIMB_IDX_MOD)) ok = arg >= 1;
+    int64_t maxg = 0;
+    for (int q = 0; ok && q < d.n; q++) {  // counts must be non-negative integers; lam indices inside the state
+      double yv = t->darr[d.value_ref][q];
+      ok = yv >= 0.0 && yv == (double)(int64_t)yv && yv < 1e9;
+      int64_t g = mode == NIMB_IDX_I ? q : mode == NIMB_IDX_DIV ? q / arg : mode == NIMB_IDX_MOD ? q % arg : t->iarr[arg][q];
+      if (g < 0) ok = false;
+      maxg = std::max(maxg, g);
+    }
+    if (ok) ok = d.fam_arg[1] >= 0 && d.fam_arg[1] + maxg < t->n_slots;
+    if (!ok) { d.family = NIMB_FAM_GENERIC; continue; }
+    TRY(dev_alloc(m, &m->d_nodeconst[i], (size_t)d.n));
+    k_pois_nodeconst<<<(d.n + 255) / 256, 256, 0, m->stream>>>(m->d_darr[d.value_ref], d.n, m->d_nodeconst[i]);
+  }
   // sampler state + execution shape
   m->sdev.resize(m->samplers.size());
   m->wide.assign(m->samplers.size(), 0);
@@ -1162,6 +1216,16 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     } else if (sp.n_targets == 1 && sp.type != NIMB_SAMPLER_BINARY && dep_count_t0(m, sp) > 2048) {
       m->wide[s] = 1;
     }
+  }
+  m->pois_sweep.assign(m->samplers.size(), 0);
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    if (sp.type != NIMB_SAMPLER_CONJ_GAMMA || m->wide[s] || sp.n_dep != 2) continue;
+    const nimb200_dep& dp = m->deps[sp.dep_off + 1];
+    const nimb200_decl& dd = m->decl[dp.decl];
+    if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
+        dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0)
+      m->pois_sweep[s] = 1;
   }
   // which cached dependency sums does each sampler invalidate: every entry (of any sampler) on a declaration it touches
   m->dep_valid.assign(m->deps.size(), 0);
@@ -1379,7 +1443,12 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   ModelHostExtra* ex = extra_of(m);
   int C = m->C;
   const int TB = 128;
-  if (!m->wide[s]) {
+  if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+    size_t total = (size_t)sp.n_targets * C;
+    k_pois_conj_sweep<<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(
+        m->T, s, seed, iter, pois_args(m, m->deps[sp.dep_off + 1].decl));
+    m->launches++;
+  } else if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;
     // few (target, chain) pairs with many dependents each: a warp per pair
     bool warp_per_pair = total <= 65536 && m->sweep_deps[s] >= 16;

@@ -12,13 +12,13 @@
 namespace nimb {
 
 // exp: r^k/k! for k = 13 .. 2 (Horner order), |r| <= ln2/2  ->  truncation < 4e-18 relative
-__device__ __constant__ double c_exp_poly[12] = {
+static __device__ __constant__ double c_exp_poly[12] = {
     1.0 / 6227020800.0, 1.0 / 479001600.0, 1.0 / 39916800.0, 1.0 / 3628800.0, 1.0 / 362880.0, 1.0 / 40320.0,
     1.0 / 5040.0,       1.0 / 720.0,       1.0 / 120.0,      1.0 / 24.0,      1.0 / 6.0,      0.5};
 // log: 2*atanh(s) = 2s (1 + z/3 + z^2/5 + ...), z = s^2 <= 0.0295: 1/(2j+1) for j = 10 .. 1
-__device__ __constant__ double c_log_poly[10] = {1.0 / 21.0, 1.0 / 19.0, 1.0 / 17.0, 1.0 / 15.0, 1.0 / 13.0,
+static __device__ __constant__ double c_log_poly[10] = {1.0 / 21.0, 1.0 / 19.0, 1.0 / 17.0, 1.0 / 15.0, 1.0 / 13.0,
                                                  1.0 / 11.0, 1.0 / 9.0,  1.0 / 7.0,  1.0 / 5.0,  1.0 / 3.0};
-__device__ __constant__ double c_misc[6] = {
+static __device__ __constant__ double c_misc[6] = {
     1.4426950408889634,       // log2(e)
     6755399441055744.0,       // 2^52 + 2^51: round-to-integer magic
     -6.93147180559945286e-01, // -ln2_hi
@@ -108,11 +108,49 @@ struct MathTab {
   double logB[129];
   double invc[129];
 };
-__device__ const MathTab g_mathtab = {NIMB_EXPT_INIT, NIMB_LOGA_INIT, NIMB_LOGB_INIT, NIMB_INVC_INIT};
-__device__ __constant__ double c_tab_misc[12] = {
+static __device__ const MathTab g_mathtab = {NIMB_EXPT_INIT, NIMB_LOGA_INIT, NIMB_LOGB_INIT, NIMB_INVC_INIT};
+static __device__ __constant__ double c_tab_misc[12] = {
     NIMB_EXP_L, 6755399441055744.0, -NIMB_EXP_HI, -NIMB_EXP_LO,
     1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0,                              // exp(r) = 1 + r (1 + r/2 + r^2/6 + r^3/24 + r^4/120)
     0.6931471805599453,                                              // ln 2
     1.0 / 7.0, -1.0 / 6.0, 1.0 / 5.0, -1.0 / 4.0};                   // log1p(r) = r + r^2 (-1/2 + r/3 - r^2/4 + ... + r^5/7)
+
+// scalar forms of the table-driven functions (tab: the tables, normally a shared-memory copy)
+__device__ __forceinline__ double exp_tab(double x, const MathTab* __restrict__ tab) {  // x in [-708, 709]
+  double t = fma(x, c_tab_misc[0], c_tab_misc[1]);
+  int n = __double2loint(t);
+  t = t - c_tab_misc[1];
+  double r = fma(t, c_tab_misc[2], x);
+  r = fma(t, c_tab_misc[3], r);
+  double pl = fma(r, c_tab_misc[4], c_tab_misc[5]);
+  pl = fma(pl, r, c_tab_misc[6]);
+  pl = fma(pl, r, 0.5);
+  pl = fma(pl, r, 1.0);
+  double T = tab->expT[n & 63];
+  double v = fma(T * r, pl, T);
+  return __hiloint2double(__double2hiint(v) + ((n >> 6) << 20), __double2loint(v));
+}
+__device__ __forceinline__ double log_tab(double t, const MathTab* __restrict__ tab) {  // t: positive normal number
+  int hi = __double2hiint(t), lo = __double2loint(t);
+  int ex = (hi >> 20) - 1023;
+  int fr = hi & 0x000fffff;
+  int idx = (fr + 0x1000) >> 13;
+  ex += idx >> 7;
+  double m = __hiloint2double(fr | 0x3ff00000, lo);
+  bool em1 = ex == -1;
+  double lc = em1 ? tab->logB[idx] : tab->logA[idx];
+  double kd = em1 ? 0.0 : (double)ex;
+  double rr = fma(m, tab->invc[idx], -1.0);
+  double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
+  Q = fma(Q, rr, c_tab_misc[10]);
+  Q = fma(Q, rr, c_tab_misc[11]);
+  Q = fma(Q, rr, 1.0 / 3.0);
+  Q = fma(Q, rr, -0.5);
+  double lp = fma(rr * rr, Q, rr);
+  return fma(kd, c_tab_misc[7], lc + lp);
+}
+__device__ __forceinline__ void load_mathtab(MathTab* dst, int tid, int nthreads) {
+  for (int i = tid; i < (int)(sizeof(MathTab) / sizeof(double)); i += nthreads) ((double*)dst)[i] = ((const double*)&g_mathtab)[i];
+}
 
 }  // namespace nimb

@@ -359,8 +359,45 @@ class _Lowering:
             d.fam_arg[1] = self.model.var_slot[ip[2]] + ip[3]
             d.fam_arg[2] = ip[4]
             d.fam_arg[3] = ip[4]
+        self._match_pois_loglin(decl, d)
         self.b.decls.append(d)
         return len(self.b.decls) - 1
+
+    def _match_pois_loglin(self, decl, d):
+        """y[i] ~ dpois(lam[G(i)] * exp(b0 + b1 * x[i])) (any commutative arrangement) -> fused Poisson family."""
+        if decl.dist != T.DPOIS or not decl.is_data:
+            return
+        t = decl.params[0]
+        if t[0] != "bin" or t[1] != T.OP_MUL:
+            return
+        for lam, ex in ((t[2], t[3]), (t[3], t[2])):
+            if lam[0] != "cvar" or ex[0] != "un" or ex[1] != T.OP_EXP:
+                continue
+            lin = ex[2]
+            if lin[0] != "bin" or lin[1] != T.OP_ADD:
+                continue
+            for b0, bx in ((lin[2], lin[3]), (lin[3], lin[2])):
+                if b0[0] != "cvar" or not isinstance(b0[2], (int, np.integer)) or bx[0] != "bin" or bx[1] != T.OP_MUL:
+                    continue
+                for b1, x in ((bx[2], bx[3]), (bx[3], bx[2])):
+                    if b1[0] != "cvar" or not isinstance(b1[2], (int, np.integer)) or x[0] != "data":
+                        continue
+                    ops = []
+                    self._flatten(lam, decl, ops)
+                    op, a, bmode, carg, _ = ops[0]
+                    if op == T.OP_CVAR:
+                        base, mode, arg = a, T.IDX_DIV, max(decl.n, 1)      # one lam for every node
+                    else:
+                        base, mode, arg = a, bmode, carg
+                    xops = []
+                    self._flatten(x, decl, xops)
+                    if xops[0][2] != T.IDX_I:
+                        continue
+                    d.family = T.FAM_POIS_LOGLIN
+                    d.fam_arg[0], d.fam_arg[1], d.fam_arg[2], d.fam_arg[3] = xops[0][1], base, mode, arg
+                    d.fam_arg[4] = self.model.var_slot[b0[1]] + int(b0[2])
+                    d.fam_arg[5] = self.model.var_slot[b1[1]] + int(b1[2])
+                    return
 
     # -- which nodes of `dep` read which target (relative position) of var
     def _target_of_nodes(self, dep, var, pos0, Tn):

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header_sizes():
     from nimble_b200 import table as T
     assert ctypes.sizeof(T.Op) == 24
-    assert ctypes.sizeof(T.Decl) == 4 * (5 + 3 + 3 + 1 + 4)
+    assert ctypes.sizeof(T.Decl) == 4 * (5 + 3 + 3 + 1 + 6)
     assert ctypes.sizeof(T.Dep) == 32
     assert ctypes.sizeof(T.Sampler) == 14 * 4 + 4 * 8
 

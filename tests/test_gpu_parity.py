@@ -304,3 +304,36 @@ def test_data_shards_add_up_to_the_whole(b200, name):
             dm.set_values(inits)
             parts += dm.calculate(di)
         assert rel_err(parts, total).max() < RTOL_LP, (name, di)
+
+
+def test_pois_family_block_sums_and_edges(oracle, b200):
+    """Fused Poisson log-linear family (C >= 32 chains) against the oracle, including chains that must take the exact
+    per-element path: lam = 0, lam < 0, overflowing and underflowing linear predictors."""
+    m, conf = sm.SMALL["glmm"]()
+    C = 70
+    inits = sm.random_inits(m, C, 5, 0.3)
+    lam0, b0s = m.var_slot["lam"], m.var_slot["b0"]
+    inits[3, lam0 + 2] = 0.0
+    inits[4, lam0 + 5] = -1.0
+    inits[5, b0s] = 800.0
+    inits[6, b0s] = -800.0
+    inits[7, b0s] = np.nan
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(C), co._ensure(C)
+    dg.set_values(inits)
+    do.set_values(inits)
+    y = len(cg.builder.decls) - 1
+    assert cg.builder.decls[y].family == T.FAM_POIS_LOGLIN
+    a, b = dg.calculate(y), do.calculate(y)
+    assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b))
+    assert rel_err(a, b).max() < RTOL_LP, rel_err(a, b).max()
+    assert rel_err(dg.calculate(y, 256, 3072), do.calculate(y, 256, 3072)).max() < RTOL_LP
+
+
+def test_pois_family_trajectories(oracle, b200):
+    m, conf = sm.SMALL["glmm"]()
+    inits = sm.random_inits(m, 40, 8, 0.1)
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 260, 10, seed=3), run(cg, inits, 260, 10, seed=3)
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
