@@ -116,7 +116,11 @@ enum {
   NIMB_FAM_BERN_LOGIT_INPROD = 1,
   /* y[i] ~ dpois(lam[G(i)] * exp(b0 + b1 * x[i])), G an index map (identity / i div c / int array):
    * fam_arg = {x darr id, lam slot base, index mode, index argument, b0 slot, b1 slot} */
-  NIMB_FAM_POIS_LOGLIN = 2
+  NIMB_FAM_POIS_LOGLIN = 2,
+  /* y[i] ~ dnorm(A + v[G(i)], sd = S), A and S chain-level programs (no node index), v gathered through an index map:
+   * fam_arg = {ops offset of A, length of A, v slot base, index mode (-1: no gathered term), index argument, 0};
+   * S is the declaration's own second parameter program */
+  NIMB_FAM_NORM_GATHER = 3
 };
 
 /* ---- node selections: which instances of a declaration depend on target t */

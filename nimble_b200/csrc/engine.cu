@@ -300,6 +300,7 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 }
 
 #include "fused_pois.cuh"
+#include "fused_norm.cuh"
 
 // ------------------------------------------------------------------------------------------------ sweep kernels
 // One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
@@ -783,6 +784,10 @@ struct nimb200_model {
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
   std::vector<double*> d_nodeconst;  // per decl: data-only node constants of the fused Poisson family (or null)
   std::vector<char> pois_sweep;      // per sampler: conjugate sweep served by k_pois_conj_sweep
+  std::vector<char> norm_ok;         // per decl: streaming normal family usable
+  std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
+  std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_conj_sweep
+  double* d_normtmp = nullptr;       // [2][C]
   // data-node sharding (nimb200_enable_data_sharding)
   int rank = 0, nranks = 1;
   std::vector<int32_t> shard_lo, shard_hi, sharded;
@@ -874,15 +879,32 @@ static PoisArgs pois_args(nimb200_model* m, int di) {
   return a;
 }
 
+static NormArgs norm_args(nimb200_model* m, int di) {
+  const nimb200_decl& d = m->decl[di];
+  NormArgs a;
+  a.y = m->d_darr[d.value_ref];
+  a.a_off = d.fam_arg[0]; a.a_len = d.fam_arg[1]; a.v_slot = d.fam_arg[2]; a.mode = d.fam_arg[3]; a.arg = d.fam_arg[4];
+  a.gidx = a.mode == NIMB_IDX_IARR ? m->d_iarr[a.arg] : nullptr;
+  a.decl = di;
+  return a;
+}
+static int norm_blocks(int count) {
+  if (count <= 0) return 1;
+  int npb = std::max(NF_THREADS, ((count + 1183) / 1184 + NF_THREADS - 1) / NF_THREADS * NF_THREADS);
+  return (count + npb - 1) / npb;
+}
+
 // evaluate instances [lo,hi) (through idx) of declaration di for all chains; reduced sums land in dst0 (dst1)
 static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, const int32_t* idx, double* dst0, double* dst1,
                            const nimb200_dep* dp, int slot, int gam) {
   int C = m->C;
+  const int gcount = std::max(0, hi - lo);  // size of the selection before it is cut down to this rank's slice
   if (!idx) { lo = std::max(lo, (int)m->shard_lo[di]); hi = std::max(lo, std::min(hi, (int)m->shard_hi[di])); }
   int cwl = cw_log2_for(C), cw = 1 << cwl;
   int count = hi - lo;
   const nimb200_decl& d = m->decl[di];
-  if (count <= 0) {
+  const bool norm_family = d.family == NIMB_FAM_NORM_GATHER && m->norm_ok[di] && (mode == 0 || mode == 2);
+  if (count <= 0 && !(norm_family && gcount > 0)) {
     CK(cudaMemsetAsync(dst0, 0, sizeof(double) * C, m->stream));
     if (dst1) CK(cudaMemsetAsync(dst1, 0, sizeof(double) * C, m->stream));
     if (m->nranks > 1 && m->sharded[di] && m->nccl_comm) {
@@ -903,6 +925,30 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    return 0;
+  }
+  if (d.family == NIMB_FAM_NORM_GATHER && m->norm_ok[di] &&
+      (mode == 0 || (mode == 2 && dp && dp->param == 0 && (dp->link == NIMB_LINK_ADDITIVE || dp->link == NIMB_LINK_IDENTITY) &&
+                     !gam && !(d.fam_arg[3] >= 0 && slot >= d.fam_arg[2] && slot < d.fam_arg[2] + m->norm_vspan[di])))) {
+    NormArgs na = norm_args(m, di);
+    int nb = norm_blocks(count);
+    int npb = std::max(NF_THREADS, ((std::max(count, 1) + nb - 1) / nb + NF_THREADS - 1) / NF_THREADS * NF_THREADS);
+    nb = std::max(1, (count + npb - 1) / npb);
+    if ((size_t)nb * 2 * C > m->partials_cap) return fail("internal: partials scratch too small (normal)");
+    dim3 grid(nb, (C + NF_CT - 1) / NF_CT);
+    if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
+    else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
+    m->launches++;
+    k_reduce<<<(C * 2 * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nb, 2, C, m->d_normtmp, m->d_normtmp + C);
+    m->launches++;
+    if (shard && m->nccl_comm && allreduce_sum(m, m->d_normtmp, 2 * (size_t)C)) return 1;
+    // nodes behind the sums: after an all-reduce the whole selection, otherwise (single rank, or slices without a communicator,
+    // where the caller adds the per-rank block sums up) what this rank walked
+    int total_count = (shard && m->nccl_comm) ? gcount : count;
+    if (mode == 0) k_norm_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, total_count, m->d_normtmp, dst0);
+    else k_norm_conj_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, total_count, m->d_normtmp, dst0, dst1);
+    m->launches++;
+    CK(cudaGetLastError());
     return 0;
   }
   if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && C >= 32) {
@@ -1114,6 +1160,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
     if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
     if (d.family == NIMB_FAM_POIS_LOGLIN) pc = std::max(pc, (size_t)64 * C);
+    if (d.family == NIMB_FAM_NORM_GATHER) pc = std::max(pc, (size_t)(norm_blocks(d.n) + 1) * 2 * C);
   }
   TRY(dev_alloc(m, &m->d_partials, pc));
   m->partials_cap = pc;
@@ -1165,6 +1212,43 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (len == 0) { d.family = NIMB_FAM_GENERIC; continue; }
     TRY(dev_alloc(m, &m->d_xpad[i], len));
     fused_bern_logit_prepare_x(m->d_darr[xid], m->d_darr[d.value_ref], d.n, p, ld, m->d_xpad[i], m->stream);
+  }
+  // streaming normal family: validate
+  m->norm_ok.assign(m->decl.size(), 0);
+  m->norm_vspan.assign(m->decl.size(), 0);
+  TRY(dev_alloc(m, &m->d_normtmp, 2 * C));
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    nimb200_decl& d = m->decl[i];
+    if (d.family != NIMB_FAM_NORM_GATHER) continue;
+    int aoff = d.fam_arg[0], alen = d.fam_arg[1], vs = d.fam_arg[2], mode = d.fam_arg[3], arg = d.fam_arg[4];
+    bool ok = d.value_kind == 0 && d.dist == NIMB_DNORM && d.nparam == 2 && aoff >= 0 && alen >= 1 && aoff + alen <= t->n_ops &&
+              !getenv("NIMB200_NO_FUSED");
+    auto chain_level = [&](int off, int len) {
+      int depth = 0;
+      for (int q = 0; q < len; q++) {
+        int op = t->ops[off + q].op;
+        if (op == NIMB_OP_DATA || op == NIMB_OP_CVARN || op == NIMB_OP_INPROD || op == NIMB_OP_DATAJ || op == NIMB_OP_CVARJ) return false;
+        if (op >= NIMB_OP_CONST && op <= NIMB_OP_CVARJ) depth++;
+        else if (op >= NIMB_OP_ADD && op <= NIMB_OP_POW) depth--;
+        if (depth < 1 || depth > 16) return false;
+      }
+      return depth == 1;
+    };
+    if (ok) ok = chain_level(aoff, alen) && chain_level(d.prog_off[1], d.prog_len[1]);
+    int64_t maxg = -1;
+    if (ok && mode >= 0) {
+      if (mode == NIMB_IDX_IARR) ok = arg >= 0 && arg < t->n_iarr && t->iarr_len[arg] >= d.n;
+      if (ok && (mode == NIMB_IDX_DIV || mode == NIMB_IDX_MOD)) ok = arg >= 1;
+      for (int q = 0; ok && q < d.n; q++) {
+        int64_t g = mode == NIMB_IDX_I ? q : mode == NIMB_IDX_DIV ? q / arg : mode == NIMB_IDX_MOD ? q % arg : t->iarr[arg][q];
+        if (g < 0) ok = false;
+        maxg = std::max(maxg, g);
+      }
+      if (ok) ok = vs >= 0 && vs + maxg < t->n_slots;
+    }
+    if (!ok) { d.family = NIMB_FAM_GENERIC; continue; }
+    m->norm_ok[i] = 1;
+    m->norm_vspan[i] = (int)(maxg + 1);
   }
   // fused Poisson family: validate, compute the data-only node constants once
   m->d_nodeconst.assign(m->decl.size(), nullptr);
@@ -1226,6 +1310,22 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
         dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0)
       m->pois_sweep[s] = 1;
+  }
+  m->norm_sweep.assign(m->samplers.size(), 0);
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    if (sp.type != NIMB_SAMPLER_CONJ_NORMAL || m->wide[s] || sp.n_dep != 2) continue;
+    const nimb200_dep& dp = m->deps[sp.dep_off + 1];
+    const nimb200_decl& dd = m->decl[dp.decl];
+    if (!(dp.stage == 1 && dd.family == NIMB_FAM_NORM_GATHER && m->norm_ok[dp.decl] && dd.fam_arg[3] >= 0 && dp.param == 0 &&
+          (dp.link == NIMB_LINK_ADDITIVE || dp.link == NIMB_LINK_IDENTITY) && sp.target_slot == dd.fam_arg[2] &&
+          m->deps[sp.dep_off].stage == 0)) continue;
+    bool a_reads_target = false;  // A must not read the gathered vector itself
+    for (int q = 0; q < dd.fam_arg[1]; q++) {
+      const nimb200_op& o = m->ops[dd.fam_arg[0] + q];
+      if (o.op == NIMB_OP_CVAR && o.a >= sp.target_slot && o.a < sp.target_slot + sp.n_targets) a_reads_target = true;
+    }
+    if (!a_reads_target) m->norm_sweep[s] = 1;
   }
   // which cached dependency sums does each sampler invalidate: every entry (of any sampler) on a declaration it touches
   m->dep_valid.assign(m->deps.size(), 0);
@@ -1443,7 +1543,10 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   ModelHostExtra* ex = extra_of(m);
   int C = m->C;
   const int TB = 128;
-  if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+  if (!m->wide[s] && m->norm_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+    k_norm_conj_sweep<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, seed, iter, norm_args(m, m->deps[sp.dep_off + 1].decl));
+    m->launches++;
+  } else if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
     size_t total = (size_t)sp.n_targets * C;
     k_pois_conj_sweep<<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(
         m->T, s, seed, iter, pois_args(m, m->deps[sp.dep_off + 1].decl));

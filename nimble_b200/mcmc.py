@@ -360,8 +360,51 @@ class _Lowering:
             d.fam_arg[2] = ip[4]
             d.fam_arg[3] = ip[4]
         self._match_pois_loglin(decl, d)
+        self._match_norm_gather(decl, d)
         self.b.decls.append(d)
         return len(self.b.decls) - 1
+
+    @staticmethod
+    def _chain_level(tree):
+        """True if the expression reads nothing that depends on the node index."""
+        k = tree[0]
+        if k == "const":
+            return True
+        if k == "cvar":
+            return isinstance(tree[2], (int, np.integer))
+        if k == "un":
+            return _Lowering._chain_level(tree[2])
+        if k == "bin":
+            return _Lowering._chain_level(tree[2]) and _Lowering._chain_level(tree[3])
+        return False
+
+    def _match_norm_gather(self, decl, d):
+        """y[i] ~ dnorm(A + v[G(i)], sd = S) with A, S chain-level -> streaming normal family."""
+        if decl.dist != T.DNORM or not decl.is_data or not self._chain_level(decl.params[1]):
+            return
+        mean = decl.params[0]
+        A, v = None, None
+        if self._chain_level(mean):
+            A = mean
+        elif mean[0] == "cvar":
+            A, v = ("const", 0.0), mean
+        elif mean[0] == "bin" and mean[1] == T.OP_ADD:
+            for x, y in ((mean[2], mean[3]), (mean[3], mean[2])):
+                if self._chain_level(x) and y[0] == "cvar" and not isinstance(y[2], (int, np.integer)):
+                    A, v = x, y
+                    break
+        if A is None:
+            return
+        aops = []
+        self._flatten(A, decl, aops)
+        d.fam_arg[0], d.fam_arg[1] = self.b.add_prog(aops)
+        d.fam_arg[3] = -1
+        if v is not None:
+            vops = []
+            self._flatten(v, decl, vops)
+            op, a, bmode, carg, _ = vops[0]
+            d.fam_arg[2], d.fam_arg[3], d.fam_arg[4] = a, bmode, carg
+        d.family = T.FAM_NORM_GATHER
 
     def _match_pois_loglin(self, decl, d):
         """y[i] ~ dpois(lam[G(i)] * exp(b0 + b1 * x[i])) (any commutative arrangement) -> fused Poisson family."""

@@ -337,3 +337,39 @@ def test_pois_family_trajectories(oracle, b200):
     so, sg = run(co, inits, 260, 10, seed=3), run(cg, inits, 260, 10, seed=3)
     assert rel_err(sg, so).max() < RTOL_TRAJ
     assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
+
+
+def test_norm_family_block_sums_and_edges(oracle, b200):
+    """Streaming normal family against the oracle, including chains with sd <= 0 / Inf / NaN and non-finite means."""
+    for name in ("lmm", "lmm_perm"):
+        m, conf = sm.SMALL[name]()
+        C = 13
+        inits = sm.random_inits(m, C, 5, 0.3)
+        se, mu = m.var_slot["sig_e"], m.var_slot["mu"]
+        inits[3, se] = 0.0
+        inits[4, se] = -1.0
+        inits[5, se] = np.inf
+        inits[6, se] = np.nan
+        inits[7, mu] = np.inf
+        inits[8, mu] = np.nan
+        cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+        dg, do = cg._ensure(C), co._ensure(C)
+        dg.set_values(inits)
+        do.set_values(inits)
+        y = len(cg.builder.decls) - 1
+        assert cg.builder.decls[y].family == T.FAM_NORM_GATHER
+        a, b = dg.calculate(y), do.calculate(y)
+        assert np.array_equal(np.isnan(a), np.isnan(b)), (a, b)
+        assert np.array_equal(np.isinf(a), np.isinf(b)) and np.array_equal(np.sign(a[np.isinf(a)]), np.sign(b[np.isinf(b)]))
+        assert rel_err(a, b).max() < RTOL_LP, rel_err(a, b).max()
+        assert rel_err(dg.calculate(y, 100, 4211), do.calculate(y, 100, 4211)).max() < RTOL_LP
+    # sd == 0 with every residual exactly zero -> +Inf, as dnorm(x, x, 0)
+    m = nb.nimbleModel("{ s ~ dgamma(1,1)\n a ~ dnorm(0, 1)\n for (i in 1:5) { y[i] ~ dnorm(a, sd = s) } }", data={"y": [2.0] * 5},
+                       inits={"s": 0.0, "a": 2.0})
+    conf = nb.configureMCMC(m, useConjugacy=False)
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(2), co._ensure(2)
+    v = np.array([[0.0, 2.0], [0.0, 2.5]])
+    dg.set_values(v)
+    do.set_values(v)
+    assert np.array_equal(dg.calculate(2), do.calculate(2)) and dg.calculate(2)[0] == np.inf and dg.calculate(2)[1] == -np.inf
