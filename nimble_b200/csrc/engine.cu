@@ -890,7 +890,7 @@ static NormArgs norm_args(nimb200_model* m, int di) {
 }
 static int norm_blocks(int count) {
   if (count <= 0) return 1;
-  int npb = std::max(NF_THREADS, ((count + 1183) / 1184 + NF_THREADS - 1) / NF_THREADS * NF_THREADS);
+  int npb = std::max(4 * NF_THREADS, ((count + 443) / 444 + 4 * NF_THREADS - 1) / (4 * NF_THREADS) * (4 * NF_THREADS));
   return (count + npb - 1) / npb;
 }
 
@@ -932,21 +932,24 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
                      !gam && !(d.fam_arg[3] >= 0 && slot >= d.fam_arg[2] && slot < d.fam_arg[2] + m->norm_vspan[di])))) {
     NormArgs na = norm_args(m, di);
     int nb = norm_blocks(count);
-    int npb = std::max(NF_THREADS, ((std::max(count, 1) + nb - 1) / nb + NF_THREADS - 1) / NF_THREADS * NF_THREADS);
+    int npb = std::max(4 * NF_THREADS, ((std::max(count, 1) + nb - 1) / nb + 4 * NF_THREADS - 1) / (4 * NF_THREADS) * (4 * NF_THREADS));
     nb = std::max(1, (count + npb - 1) / npb);
-    if ((size_t)nb * 2 * C > m->partials_cap) return fail("internal: partials scratch too small (normal)");
+    if ((size_t)nb * C > m->partials_cap) return fail("internal: partials scratch too small (normal)");
     dim3 grid(nb, (C + NF_CT - 1) / NF_CT);
     if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
     else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
     m->launches++;
-    k_reduce<<<(C * 2 * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nb, 2, C, m->d_normtmp, m->d_normtmp + C);
-    m->launches++;
-    if (shard && m->nccl_comm && allreduce_sum(m, m->d_normtmp, 2 * (size_t)C)) return 1;
-    // nodes behind the sums: after an all-reduce the whole selection, otherwise (single rank, or slices without a communicator,
-    // where the caller adds the per-rank block sums up) what this rank walked
-    int total_count = (shard && m->nccl_comm) ? gcount : count;
-    if (mode == 0) k_norm_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, total_count, m->d_normtmp, dst0);
-    else k_norm_conj_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, total_count, m->d_normtmp, dst0, dst1);
+    if (!(shard && m->nccl_comm)) {
+      if (mode == 0) k_norm_reduce_finish<0><<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->T, na, lo, hi, idx, m->d_partials, nb, dst0, dst1);
+      else k_norm_reduce_finish<1><<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->T, na, lo, hi, idx, m->d_partials, nb, dst0, dst1);
+    } else {
+      k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nb, 1, C, m->d_normtmp, nullptr);
+      m->launches++;
+      if (allreduce_sum(m, m->d_normtmp, (size_t)C)) return 1;
+      // after the all-reduce the sums cover the whole selection, not only this rank's slice
+      if (mode == 0) k_norm_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, gcount, m->d_normtmp, dst0);
+      else k_norm_conj_finish<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, na, gcount, m->d_normtmp, dst0, dst1);
+    }
     m->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -1003,7 +1006,7 @@ static HostSel host_sel(nimb200_model* m, const nimb200_dep& dp, const std::vect
     case NIMB_SEL_CSR: s.lo = h_iarr[dp.a][0]; s.hi = h_iarr[dp.a][1]; s.idx = m->d_iarr[dp.b]; break;
     default: s.lo = dp.a; s.hi = dp.b; break;
   }
-  if (!s.idx && !m->shard_lo.empty()) { s.lo = std::max(s.lo, m->shard_lo[dp.decl]); s.hi = std::min(s.hi, m->shard_hi[dp.decl]); if (s.hi < s.lo) s.hi = s.lo; }
+  // NOT cut down to this rank's slice here: launch_eval_sum does that itself and needs the size of the whole selection
   return s;
 }
 
@@ -1437,9 +1440,12 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
   const nimb200_decl& d = m->decl[di];
   bool fused = d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di];
   int C = m->C, cwl = cw_log2_for(C), cw = 1 << cwl;
+  bool family = d.family == NIMB_FAM_NORM_GATHER || d.family == NIMB_FAM_POIS_LOGLIN;
   CK(cudaEventRecord(m->ev0, m->stream));
   for (int r = 0; r < reps; r++) {
-    if (fused)
+    if (family) {  // streaming families: the whole block-sum evaluation (main kernel + the small reduce / finish kernels)
+      if (launch_eval_sum(m, 0, di, 0, d.n, nullptr, dst, nullptr, nullptr, -1, 0)) return 1;
+    } else if (fused)
       fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, 0, (d.n + 127) / 128, m->stream);
     else {
       dim3 grid(eval_tiles(C, d.n), (C + cw - 1) / cw);
@@ -1543,7 +1549,18 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   ModelHostExtra* ex = extra_of(m);
   int C = m->C;
   const int TB = 128;
-  if (!m->wide[s] && m->norm_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+  if (!m->wide[s] && m->norm_sweep[s] && m->nranks > 1 && m->sweep_sharded[s]) {
+    // data-sharded: per-target (sum y, count) of this rank's slice -> all-reduce (2 doubles per target) -> draws
+    size_t need = (size_t)sp.n_targets * 2;
+    if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");
+    NormArgs na = norm_args(m, m->deps[sp.dep_off + 1].decl);
+    k_norm_group_sums<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_sweepbuf);
+    m->launches++;
+    if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
+    size_t total = (size_t)sp.n_targets * C;
+    k_norm_conj_draw<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, na, m->d_sweepbuf);
+    m->launches++;
+  } else if (!m->wide[s] && m->norm_sweep[s]) {
     k_norm_conj_sweep<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, seed, iter, norm_args(m, m->deps[sp.dep_off + 1].decl));
     m->launches++;
   } else if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
@@ -1558,7 +1575,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     if (warp_per_pair) total *= 32;
     unsigned nb = (unsigned)((total + TB - 1) / TB);
     if (m->nranks > 1 && m->sweep_sharded[s]) {  // partial sums -> all-reduce -> decide / draw
-      size_t need = total * 3;
+      size_t need = (size_t)sp.n_targets * C * 3;
       if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");
       if (warp_per_pair) k_sweep<1, 32><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       else k_sweep<1, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);

@@ -35,71 +35,131 @@ __device__ __forceinline__ int norm_index(const NormArgs& a, int i) {
 static const int NF_THREADS = 256;
 static const int NF_CT = 8;  // chains per thread
 
-// grid (node blocks, chain groups of NF_CT).  MODE 0: out[blk][0][c] = sum d^2, out[blk][1][c] = #(d == 0)
-//                                              MODE 1: out[blk][0][c] = sum d (A evaluated with ov_slot := 0), out[blk][1][c] = 0
+// grid (node blocks, chain groups of NF_CT).  MODE 0: out[blk][c] = sum d^2;  MODE 1: out[blk][c] = sum d with A evaluated
+// under ov_slot := 0 (the conjugate sampler's offset probing).  Per (node, chain): one gathered load, two adds, one fma.
 template <int MODE>
 __global__ void __launch_bounds__(NF_THREADS)
 k_norm_stream(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, const int32_t* idx, int ov_slot, double* __restrict__ partials) {
-  __shared__ double red[2][NF_CT][NF_THREADS / 32];
+  __shared__ double red[NF_CT][NF_THREADS / 32];
+  __shared__ double sA[NF_CT];
   const int c0 = blockIdx.y * NF_CT;
-  double A[NF_CT], s0[NF_CT], s1[NF_CT];
+  if (threadIdx.x < NF_CT)  // the chain-level term once per block, not once per thread
+    sA[threadIdx.x] = eval_prog(T, min(c0 + (int)threadIdx.x, T.C - 1), a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
+  __syncthreads();
+  double A[NF_CT], s0[NF_CT];
+  int co[NF_CT];
 #pragma unroll
-  for (int k = 0; k < NF_CT; k++) {
-    int c = min(c0 + k, T.C - 1);
-    A[k] = eval_prog(T, c, a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
-    s0[k] = 0.0; s1[k] = 0.0;
-  }
+  for (int k = 0; k < NF_CT; k++) { A[k] = sA[k]; s0[k] = 0.0; co[k] = min(c0 + k, T.C - 1); }
   const int b_lo = lo + blockIdx.x * nodes_per_block, b_hi = min(hi, b_lo + nodes_per_block);
-  for (int k0 = b_lo + threadIdx.x; k0 < b_hi; k0 += NF_THREADS) {
-    int node = idx ? idx[k0] : k0;
-    if (idx && (node < T.shard_lo[a.decl] || node >= T.shard_hi[a.decl])) continue;
-    double yv = a.y[node];
-    const double* vp = a.mode >= 0 ? T.state + (size_t)(a.v_slot + norm_index(a, node)) * T.C : nullptr;
+  const int slo = T.shard_lo[a.decl], shi = T.shard_hi[a.decl];
+  const double* __restrict__ vbase = T.state + (size_t)a.v_slot * T.C;
+  // four nodes per trip, their loads issued together: what matters for an HBM-bound pass is bytes in flight per thread
+  // (prefetching the next trip as well was tried and lost to register pressure)
+  for (int k0 = b_lo + threadIdx.x; k0 < b_hi; k0 += 4 * NF_THREADS) {
+    double yv[4];
+    int gi[4];
 #pragma unroll
-    for (int k = 0; k < NF_CT; k++) {
-      int c = min(c0 + k, T.C - 1);
-      double m = vp ? A[k] + vp[c] : A[k];
-      double d = yv - m;
-      if (MODE == 0) { s0[k] = fma(d, d, s0[k]); s1[k] += d == 0.0 ? 1.0 : 0.0; }
-      else s0[k] += d;
+    for (int u = 0; u < 4; u++) {
+      int kk = k0 + u * NF_THREADS;
+      bool ok = kk < b_hi;
+      int node = ok ? (idx ? __ldg(idx + kk) : kk) : -1;
+      if (idx && ok && (node < slo || node >= shi)) node = -1;
+      yv[u] = node >= 0 ? __ldg(a.y + node) : 0.0;
+      gi[u] = node < 0 ? -1 : (a.mode < 0 ? 0 : (a.mode == NIMB_IDX_IARR ? __ldg(a.gidx + node) : norm_index(a, node)));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (gi[u] < 0) continue;
+      if (a.mode >= 0) {
+        const double* __restrict__ vp = vbase + (size_t)gi[u] * T.C;
+#pragma unroll
+        for (int k = 0; k < NF_CT; k++) {
+          double d = yv[u] - (A[k] + vp[co[k]]);
+          if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < NF_CT; k++) {
+          double d = yv[u] - A[k];
+          if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+        }
+      }
     }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < NF_CT; k++) {
-    double v0 = s0[k], v1 = s1[k];
+    double v0 = s0[k];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { v0 += __shfl_xor_sync(0xffffffffu, v0, o); v1 += __shfl_xor_sync(0xffffffffu, v1, o); }
-    if (lane == 0) { red[0][k][warp] = v0; red[1][k][warp] = v1; }
+    for (int o = 16; o > 0; o >>= 1) v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+    if (lane == 0) red[k][warp] = v0;
   }
   __syncthreads();
-  if (threadIdx.x < 2 * NF_CT) {
-    int which = threadIdx.x / NF_CT, k = threadIdx.x % NF_CT, c = c0 + k;
+  if (threadIdx.x < NF_CT) {
+    int k = threadIdx.x, c = c0 + k;
     if (c < T.C) {
       double s = 0.0;
-      for (int w = 0; w < NF_THREADS / 32; w++) s += red[which][k][w];
-      partials[((size_t)blockIdx.x * 2 + which) * T.C + c] = s;
+      for (int w = 0; w < NF_THREADS / 32; w++) s += red[k][w];
+      partials[(size_t)blockIdx.x * T.C + c] = s;
     }
   }
 }
 
-// per chain: (sum d^2, #zeros) -> sum of log-densities, with nmath's dnorm special cases
-__global__ void k_norm_finish(DevTab T, NormArgs a, int count, const double* __restrict__ SZ /*[2][C]*/, double* __restrict__ dst) {
+// sd == 0 (degenerate): dnorm is +Inf where y == mean and -Inf elsewhere, so the sum depends on how many residuals are
+// exactly zero.  Counted here by a plain loop, only for the chain that needs it.
+__device__ double norm_sd0_sum(const DevTab& T, const NormArgs& a, int c, int lo, int hi, const int32_t* idx) {
+  double A = eval_prog(T, c, a.a_off, a.a_len, 0, 0, -1, 0.0);
+  long zeros = 0, n = 0;
+  for (int k = lo; k < hi; k++) {
+    int node = idx ? idx[k] : k;
+    if (idx && (node < T.shard_lo[a.decl] || node >= T.shard_hi[a.decl])) continue;
+    double m = a.mode >= 0 ? A + T.state[(size_t)(a.v_slot + norm_index(a, node)) * T.C + c] : A;
+    zeros += (a.y[node] - m == 0.0);
+    n++;
+  }
+  return n == 0 ? 0.0 : (zeros == n ? INFINITY : (zeros == 0 ? -INFINITY : NAN));
+}
+
+__device__ __forceinline__ double norm_sum_from_ss(double sigma, double S, int count) {
+  double n = (double)count;
+  if (count == 0) return 0.0;
+  if (isnan(sigma) || isnan(S)) return sigma + S;
+  if (sigma < 0) return NAN;
+  if (!isfinite(sigma)) return -INFINITY;
+  double q = S / (sigma * sigma);
+  return !isfinite(q) ? -INFINITY : -(n * (NIMB_LN_SQRT_2PI + log(sigma)) + 0.5 * q);
+}
+
+// all-reduced path: per chain sum d^2 -> sum of log-densities (sd == 0 gives NaN here: the zero count is not exchanged)
+__global__ void k_norm_finish(DevTab T, NormArgs a, int count, const double* __restrict__ SS, double* __restrict__ dst) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_decl& d = T.decl[a.decl];
   double sigma = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, -1, 0.0);
-  double S = SZ[c], Z = SZ[(size_t)T.C + c], n = (double)count, r;
-  if (count == 0) r = 0.0;
-  else if (isnan(sigma) || isnan(S)) r = sigma + S;
-  else if (sigma < 0) r = NAN;
-  else if (!isfinite(sigma)) r = -INFINITY;
-  else if (sigma == 0) r = (Z == n) ? INFINITY : (Z == 0.0 ? -INFINITY : NAN);
-  else {
-    double q = S / (sigma * sigma);
-    r = !isfinite(q) ? -INFINITY : -(n * (NIMB_LN_SQRT_2PI + log(sigma)) + 0.5 * q);
+  dst[c] = (sigma == 0 && count > 0 && !isnan(SS[c])) ? NAN : norm_sum_from_ss(sigma, SS[c], count);
+}
+
+// single-rank path: reduce the block partials and finish in one launch (one warp per chain, fixed order)
+template <int MODE>
+__global__ void k_norm_reduce_finish(DevTab T, NormArgs a, int lo, int hi, const int32_t* idx, const double* __restrict__ partials,
+                                     int nb, double* __restrict__ dst0, double* __restrict__ dst1) {
+  int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (c >= T.C) return;
+  double S = 0.0;
+  for (int b = lane; b < nb; b += 32) S += partials[(size_t)b * T.C + c];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+  if (lane != 0) return;
+  int count = hi - lo;
+  if (MODE == 1) {
+    double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
+    dst0[c] = S * tau;
+    dst1[c] = (double)count * tau;
+    return;
   }
-  dst[c] = r;
+  const nimb200_decl& d = T.decl[a.decl];
+  double sigma = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, -1, 0.0);
+  dst0[c] = (sigma == 0 && count > 0 && !isnan(S)) ? norm_sd0_sum(T, a, c, lo, hi, idx) : norm_sum_from_ss(sigma, S, count);
 }
 
 // per chain: sum of residuals -> (contribution_mean, contribution_tau)
@@ -154,6 +214,55 @@ k_norm_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, NormArgs a) {
     normal2(key, 0, z, z1);
     T.state[(size_t)slot * T.C + c] = mean + sd * z;
   }
+}
+
+// data-sharded form of the sweep: phase 1 leaves this rank's (sum y, count) per target in gs[t][2] (chain independent, so the
+// all-reduce between the phases carries 2 doubles per target); phase 2 is one thread per (target, chain).
+__global__ void __launch_bounds__(128)
+k_norm_group_sums(DevTab T, int sid, NormArgs a, double* __restrict__ gs) {
+  __shared__ double red[4];
+  __shared__ int cred[4];
+  const nimb200_sampler sp = T.samplers[sid];
+  const int t = blockIdx.x;
+  const nimb200_dep dp = T.deps[sp.dep_off + 1];
+  Sel s = sel_of(T, dp, t);
+  double acc = 0.0;
+  int cnt = 0;
+  for (int k = s.lo + threadIdx.x; k < s.hi; k += 128) {
+    int node = s.idx ? s.idx[k] : k;
+    if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
+    acc += a.y[node];
+    cnt++;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o); }
+  if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = acc; cred[threadIdx.x >> 5] = cnt; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    gs[2 * (size_t)t] = ((red[0] + red[1]) + red[2]) + red[3];
+    gs[2 * (size_t)t + 1] = (double)(cred[0] + cred[1] + cred[2] + cred[3]);
+  }
+}
+
+__global__ void k_norm_conj_draw(DevTab T, int sid, uint64_t seed, uint64_t iter, NormArgs a, const double* __restrict__ gs) {
+  const nimb200_sampler sp = T.samplers[sid];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = (int)(gid % T.C);
+  size_t tq = gid / T.C;
+  if (tq >= (size_t)sp.n_targets) return;
+  int t = (int)tq;
+  const double ysum = gs[2 * (size_t)t], n = gs[2 * (size_t)t + 1];
+  const nimb200_dep tp = T.deps[sp.dep_off];
+  const int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
+  double A = eval_prog(T, c, a.a_off, a.a_len, 0, 0, -1, 0.0);
+  double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
+  double cm = (ysum - n * A) * tau, ct = n * tau;
+  double prior_mean = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+  double prior_tau = get_param(T, tp.decl, tnode, c, NIMB_PARAM_TAU, -1, 0.0);
+  DrawKey key = make_key(T, seed, iter, sid, t, c);
+  double mean = (prior_mean * prior_tau + cm) / (prior_tau + ct), sd = pow(prior_tau + ct, -0.5), z, z1;
+  normal2(key, 0, z, z1);
+  T.state[(size_t)(sp.target_slot + t) * T.C + c] = mean + sd * z;
 }
 
 }  // namespace nimb
