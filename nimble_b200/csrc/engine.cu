@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <array>
 #include <set>
 #include "draws_dev.cuh"
 #include "engine.cuh"
@@ -548,14 +549,14 @@ __global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter,
 
 // wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
 __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
-                            double* depcache, const double* tsave, const double* pls) {
+                            double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_sampler sp = T.samplers[sid];
   DrawKey key = make_key(T, seed, iter, sid, 0, c);
   double lp0 = 0, lp1 = 0;
   for (int e = 0; e < sp.n_dep; e++) {
-    double diff = newsum[(size_t)e * T.C + c] - depcache[(size_t)(sp.dep_off + e) * T.C + c];
+    double diff = newsum[(size_t)e * T.C + c] - depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c];
     if (T.deps[sp.dep_off + e].stage == 0) lp0 += diff; else lp1 += diff;
   }
   bool jump;
@@ -563,7 +564,7 @@ __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int
   else jump = decide(lp0 + lp1 + (pls ? pls[c] : 0.0), key, call);
   int d = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1;
   if (jump) {
-    for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)(sp.dep_off + e) * T.C + c] = newsum[(size_t)e * T.C + c];
+    for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c] = newsum[(size_t)e * T.C + c];
   } else {
     for (int j = 0; j < d; j++) T.state[(size_t)(sp.target_slot + j) * T.C + c] = tsave[(size_t)j * T.C + c];
   }
@@ -778,7 +779,9 @@ struct nimb200_model {
   size_t partials_cap = 0;
   std::vector<SamplerDev> sdev;
   std::vector<char> wide;       // per sampler: wide path?
-  std::vector<char> dep_valid;  // per dependency entry: depcache row valid?
+  std::vector<char> dep_valid;  // per cache slot: depcache row valid?
+  std::vector<int32_t> dep_slot; // dependency entry -> cache slot: entries of wide samplers with the same (declaration, selection) share one
+  int32_t* d_dep_slot = nullptr;
   std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
   std::vector<int> ran;         // RW_block: iterations since last adaptation
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
@@ -1330,18 +1333,41 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     }
     if (!a_reads_target) m->norm_sweep[s] = 1;
   }
-  // which cached dependency sums does each sampler invalidate: every entry (of any sampler) on a declaration it touches
-  m->dep_valid.assign(m->deps.size(), 0);
+  // Cache slots: the block sum of the CURRENT state over (declaration, selection).  Entries of wide samplers whose selection
+  // does not depend on the target share a slot, so b1's step can reuse what b0's step just committed instead of re-evaluating
+  // the dependents.  A sampler invalidates every slot on a declaration it touches, except -- for a wide MH sampler -- the slots
+  // of its own entries, which its accept/reject step keeps equal to the state it leaves behind.
+  m->dep_slot.assign(m->deps.size(), 0);
+  {
+    std::vector<std::array<int, 4>> keys;
+    for (size_t g = 0; g < m->deps.size(); g++) {
+      const nimb200_dep& dp = m->deps[g];
+      std::array<int, 4> key = {dp.decl, dp.sel, dp.a, dp.b};
+      bool shareable = dp.sel == NIMB_SEL_ALL || dp.sel == NIMB_SEL_RANGE;
+      int slot = -1;
+      if (shareable)
+        for (size_t q = 0; q < keys.size(); q++)
+          if (keys[q] == key) { slot = (int)q; break; }
+      if (slot < 0) { slot = (int)keys.size(); keys.push_back(shareable ? key : std::array<int, 4>{-1, (int)g, 0, 0}); }
+      m->dep_slot[g] = slot;
+    }
+    m->dep_valid.assign(keys.size(), 0);
+    void* ds = nullptr;
+    TRY(up(&ds, m->dep_slot.data(), sizeof(int32_t) * m->dep_slot.size()));
+    m->d_dep_slot = (int32_t*)ds;
+  }
   m->invalidates.resize(m->samplers.size());
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
-    std::set<int> touched;
-    for (int e = 0; e < sp.n_dep; e++) touched.insert(m->deps[sp.dep_off + e].decl);
-    for (size_t g = 0; g < m->deps.size(); g++) {
-      bool own = (int)g >= sp.dep_off && (int)g < sp.dep_off + sp.n_dep;
-      if (touched.count(m->deps[g].decl) && !(own && m->wide[s] && sp.type != NIMB_SAMPLER_CONJ_GAMMA && sp.type != NIMB_SAMPLER_CONJ_NORMAL))
-        m->invalidates[s].push_back((int)g);
+    std::set<int> touched, own, inval;
+    bool keeps_own = m->wide[s] && sp.type != NIMB_SAMPLER_CONJ_GAMMA && sp.type != NIMB_SAMPLER_CONJ_NORMAL;
+    for (int e = 0; e < sp.n_dep; e++) {
+      touched.insert(m->deps[sp.dep_off + e].decl);
+      if (keeps_own) own.insert(m->dep_slot[sp.dep_off + e]);
     }
+    for (size_t g = 0; g < m->deps.size(); g++)
+      if (touched.count(m->deps[g].decl) && !own.count(m->dep_slot[g])) inval.insert(m->dep_slot[g]);
+    m->invalidates[s].assign(inval.begin(), inval.end());
   }
   TRYCU(cudaStreamSynchronize(m->stream));
   *out = m;
@@ -1534,12 +1560,12 @@ static int ensure_dep_sums(nimb200_model* m, int s) {  // block sums of the curr
   const nimb200_sampler& sp = m->samplers[s];
   ModelHostExtra* ex = extra_of(m);
   for (int e = 0; e < sp.n_dep; e++) {
-    int g = sp.dep_off + e;
-    if (m->dep_valid[g]) continue;
+    int g = sp.dep_off + e, slot = m->dep_slot[g];
+    if (m->dep_valid[slot]) continue;
     const nimb200_dep& dp = m->deps[g];
     HostSel hs = host_sel(m, dp, ex->h_iarr);
-    if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)g * m->C, nullptr, nullptr, -1, 0)) return 1;
-    m->dep_valid[g] = 1;
+    if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)slot * m->C, nullptr, nullptr, -1, 0)) return 1;
+    m->dep_valid[slot] = 1;
   }
   return 0;
 }
@@ -1615,7 +1641,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
         if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
       }
       int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;
-      k_mh_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache,
+      k_mh_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
                                                            m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr);
       m->launches++;
       if (sp.type == NIMB_SAMPLER_RW_BLOCK && sp.adaptive) {
