@@ -893,7 +893,7 @@ static NormArgs norm_args(nimb200_model* m, int di) {
 }
 static int norm_blocks(int count) {
   if (count <= 0) return 1;
-  int npb = std::max(4 * NF_THREADS, ((count + 443) / 444 + 4 * NF_THREADS - 1) / (4 * NF_THREADS) * (4 * NF_THREADS));
+  int npb = std::max(4 * NF_THREADS, ((count + 591) / 592 + 4 * NF_THREADS - 1) / (4 * NF_THREADS) * (4 * NF_THREADS));
   return (count + npb - 1) / npb;
 }
 
@@ -939,7 +939,18 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     nb = std::max(1, (count + npb - 1) / npb);
     if ((size_t)nb * C > m->partials_cap) return fail("internal: partials scratch too small (normal)");
     dim3 grid(nb, (C + NF_CT - 1) / NF_CT);
-    if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
+    // contiguous, 16-byte aligned ranges stream through the TMA ring; index lists and odd offsets use plain loads
+    bool tma_ok = !idx && (lo % 4) == 0 && (npb % NT_TILE) == 0 && !getenv("NIMB200_NO_TMA");
+    if (tma_ok) {
+      static bool attr = false;
+      if (!attr) {
+        cudaFuncSetAttribute(k_norm_stream_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM);
+        cudaFuncSetAttribute(k_norm_stream_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM);
+        attr = true;
+      }
+      if (mode == 0) k_norm_stream_tma<0><<<grid, NF_THREADS, NT_SMEM, m->stream>>>(m->T, na, lo, hi, npb, -1, m->d_partials);
+      else k_norm_stream_tma<1><<<grid, NF_THREADS, NT_SMEM, m->stream>>>(m->T, na, lo, hi, npb, slot, m->d_partials);
+    } else if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
     else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
     m->launches++;
     if (!(shard && m->nccl_comm)) {

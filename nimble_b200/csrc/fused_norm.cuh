@@ -11,6 +11,7 @@
 // or NaN through the arithmetic.  Conjugate contributions (MCMC_conjugacy.R:109-115, additive link, coeff = 1):
 // contribution_mean = tau sum_i (y_i - offset_i), contribution_tau = n tau with offset_i = A(target = 0) + v[G(i)].
 #pragma once
+#include "tma_util.cuh"
 
 namespace nimb {
 
@@ -104,6 +105,113 @@ k_norm_stream(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, const i
     }
   }
 }
+
+// TMA-staged form of k_norm_stream for contiguous node ranges: y (and the group-index array) travel HBM -> shared memory as
+// 1-D bulk copies through a 4-stage mbarrier ring, so each CTA keeps 48 KB of loads in flight without spending registers on
+// them; the threads only touch shared memory and the (L2-resident) gathered vector.  Same arithmetic as k_norm_stream.
+static const int NT_TILE = 1024;   // nodes per stage
+static const int NT_STAGES = 4;
+template <int MODE>
+__global__ void __launch_bounds__(NF_THREADS)
+k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int ov_slot, double* __restrict__ partials) {
+  extern __shared__ __align__(128) unsigned char nsm[];
+  double* ys = (double*)nsm;                                         // [NT_STAGES][NT_TILE]
+  int32_t* gs = (int32_t*)(ys + NT_STAGES * NT_TILE);                // [NT_STAGES][NT_TILE]
+  uint64_t* bar = (uint64_t*)(gs + NT_STAGES * NT_TILE);             // [NT_STAGES]
+  double* red = (double*)(bar + NT_STAGES);                          // [NF_CT][NF_THREADS/32]
+  double* sA = red + NF_CT * (NF_THREADS / 32);                      // [NF_CT]
+  const bool use_idx = a.mode == NIMB_IDX_IARR;
+  const int c0 = blockIdx.y * NF_CT;
+  if (threadIdx.x < NF_CT)
+    sA[threadIdx.x] = eval_prog(T, min(c0 + (int)threadIdx.x, T.C - 1), a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NT_STAGES; s++) tma::mbar_init(&bar[s], 1);
+    tma::fence_init();
+  }
+  __syncthreads();
+  double A[NF_CT], s0[NF_CT];
+  int co[NF_CT];
+#pragma unroll
+  for (int k = 0; k < NF_CT; k++) { A[k] = sA[k]; s0[k] = 0.0; co[k] = min(c0 + k, T.C - 1); }
+  const int b_lo = lo + blockIdx.x * nodes_per_block, b_hi = min(hi, b_lo + nodes_per_block);
+  const int ntile = b_hi > b_lo ? (b_hi - b_lo + NT_TILE - 1) / NT_TILE : 0;
+  const double* __restrict__ vbase = T.state + (size_t)a.v_slot * T.C;
+  const bool vec = (T.C % 2) == 0 && c0 + NF_CT <= T.C && ((size_t)a.v_slot * T.C + c0) % 2 == 0;
+  auto issue = [&](int tile) {  // thread 0 only: full tiles by TMA (the ragged last tile is loaded by the threads themselves)
+    int n0 = b_lo + tile * NT_TILE;
+    if (n0 + NT_TILE > b_hi) return;
+    int s = tile % NT_STAGES;
+    uint32_t bytes = NT_TILE * 8 + (use_idx ? NT_TILE * 4 : 0);
+    tma::expect_tx(&bar[s], bytes);
+    tma::bulk_g2s(ys + s * NT_TILE, a.y + n0, NT_TILE * 8, &bar[s]);
+    if (use_idx) tma::bulk_g2s(gs + s * NT_TILE, a.gidx + n0, NT_TILE * 4, &bar[s]);
+  };
+  if (threadIdx.x == 0)
+    for (int tl = 0; tl < NT_STAGES - 1 && tl < ntile; tl++) issue(tl);
+  for (int tile = 0; tile < ntile; tile++) {
+    const int s = tile % NT_STAGES, n0 = b_lo + tile * NT_TILE;
+    const bool full = n0 + NT_TILE <= b_hi;
+    if (threadIdx.x == 0 && tile + NT_STAGES - 1 < ntile) issue(tile + NT_STAGES - 1);  // refill the stage freed last trip
+    if (full) tma::wait(&bar[s], (uint32_t)((tile / NT_STAGES) & 1));
+    else {
+      for (int q = threadIdx.x; q < b_hi - n0; q += NF_THREADS) { ys[s * NT_TILE + q] = a.y[n0 + q]; if (use_idx) gs[s * NT_TILE + q] = a.gidx[n0 + q]; }
+      __syncthreads();
+    }
+    const int cnt = min(NT_TILE, b_hi - n0);
+#pragma unroll
+    for (int u = 0; u < NT_TILE / NF_THREADS; u++) {
+      int q = u * NF_THREADS + threadIdx.x;
+      if (q < cnt) {
+        double yv = ys[s * NT_TILE + q];
+        if (a.mode >= 0) {
+          int g = use_idx ? gs[s * NT_TILE + q] : norm_index(a, n0 + q);
+          const double* __restrict__ vp = vbase + (size_t)g * T.C;
+          if (vec) {  // the CTA's 8 chain copies of v[g] are 64 contiguous, 16-byte aligned bytes: four 128-bit loads
+            const double2* __restrict__ v2 = reinterpret_cast<const double2*>(vp + c0);
+            double2 w0 = v2[0], w1 = v2[1], w2 = v2[2], w3 = v2[3];
+            double vv[NF_CT] = {w0.x, w0.y, w1.x, w1.y, w2.x, w2.y, w3.x, w3.y};
+#pragma unroll
+            for (int k = 0; k < NF_CT; k++) {
+              double d = yv - (A[k] + vv[k]);
+              if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < NF_CT; k++) {
+              double d = yv - (A[k] + vp[co[k]]);
+              if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < NF_CT; k++) {
+            double d = yv - A[k];
+            if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+          }
+        }
+      }
+    }
+    __syncthreads();  // stage s may be refilled from the next trip on
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NF_CT; k++) {
+    double v0 = s0[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+    if (lane == 0) red[k * (NF_THREADS / 32) + warp] = v0;
+  }
+  __syncthreads();
+  if (threadIdx.x < NF_CT) {
+    int k = threadIdx.x, c = c0 + k;
+    if (c < T.C) {
+      double sm = 0.0;
+      for (int w = 0; w < NF_THREADS / 32; w++) sm += red[k * (NF_THREADS / 32) + w];
+      partials[(size_t)blockIdx.x * T.C + c] = sm;
+    }
+  }
+}
+static const size_t NT_SMEM = (size_t)NT_STAGES * NT_TILE * 12 + NT_STAGES * 8 + (NF_CT * (NF_THREADS / 32) + NF_CT) * 8;
 
 // sd == 0 (degenerate): dnorm is +Inf where y == mean and -Inf elsewhere, so the sum depends on how many residuals are
 // exactly zero.  Counted here by a plain loop, only for the chain that needs it.
