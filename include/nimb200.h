@@ -120,7 +120,10 @@ enum {
   /* y[i] ~ dnorm(A + v[G(i)], sd = S), A and S chain-level programs (no node index), v gathered through an index map:
    * fam_arg = {ops offset of A, length of A, v slot base, index mode (-1: no gathered term), index argument, 0};
    * S is the declaration's own second parameter program */
-  NIMB_FAM_NORM_GATHER = 3
+  NIMB_FAM_NORM_GATHER = 3,
+  /* v[i] ~ dbern(gate[G(i)] * ilogit(c0 + c1 * x[i])), v data or latent, gate an optional latent 0/1 vector:
+   * fam_arg = {x darr id, c0 slot, c1 slot, gate slot base (-1: none), gate index mode, gate index argument} */
+  NIMB_FAM_BERN_LOGIT_LIN = 4
 };
 
 /* ---- node selections: which instances of a declaration depend on target t */

@@ -302,6 +302,7 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 
 #include "fused_pois.cuh"
 #include "fused_norm.cuh"
+#include "fused_bern.cuh"
 
 // ------------------------------------------------------------------------------------------------ sweep kernels
 // One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
@@ -787,6 +788,8 @@ struct nimb200_model {
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
   std::vector<double*> d_nodeconst;  // per decl: data-only node constants of the fused Poisson family (or null)
   std::vector<char> pois_sweep;      // per sampler: conjugate sweep served by k_pois_conj_sweep
+  std::vector<char> bern_ok;         // per decl: Bernoulli-logit-linear family usable
+  std::vector<char> bern_sweep;      // per sampler: binary sweep served by k_bernlin_binary_sweep
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
   std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_conj_sweep
@@ -882,6 +885,24 @@ static PoisArgs pois_args(nimb200_model* m, int di) {
   return a;
 }
 
+static BernArgs bern_args(nimb200_model* m, int di) {
+  const nimb200_decl& d = m->decl[di];
+  BernArgs a;
+  a.x = m->d_darr[d.fam_arg[0]];
+  a.vdata = d.value_kind == 0 ? m->d_darr[d.value_ref] : nullptr;
+  a.v_slot = d.value_kind == 1 ? d.value_ref : -1;
+  a.c0_slot = d.fam_arg[1]; a.c1_slot = d.fam_arg[2]; a.gate_slot = d.fam_arg[3]; a.gmode = d.fam_arg[4]; a.garg = d.fam_arg[5];
+  a.gidx = (a.gate_slot >= 0 && a.gmode == NIMB_IDX_IARR) ? m->d_iarr[a.garg] : nullptr;
+  a.n = d.n;
+  return a;
+}
+// node chunks for the lane = chain block-sum kernels: enough CTAs to fill the machine several times over, at most 512
+static int family_chunks(int C, int count, int tile) {
+  int ctiles = (C + 31) / 32;
+  int want = (148 * 24 + ctiles - 1) / ctiles;
+  int maxc = std::max(1, (count + tile - 1) / tile);
+  return std::max(1, std::min(512, std::min(want, maxc)));
+}
 static NormArgs norm_args(nimb200_model* m, int di) {
   const nimb200_decl& d = m->decl[di];
   NormArgs a;
@@ -968,12 +989,26 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     CK(cudaGetLastError());
     return 0;
   }
+  if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_LIN && m->bern_ok[di] && !idx && C >= 32) {
+    BernArgs ba = bern_args(m, di);
+    const int chunks = family_chunks(C, count, BF_TILE);
+    int npc = ((count + chunks - 1) / chunks + BF_TILE - 1) / BF_TILE * BF_TILE;
+    if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (bernoulli)");
+    dim3 grid((C + 31) / 32, chunks);
+    k_bernlin_sum<<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    m->launches++;
+    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
+    m->launches++;
+    CK(cudaGetLastError());
+    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    return 0;
+  }
   if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && C >= 32) {
     PoisArgs pa = pois_args(m, di);
-    const int chunks = 64;
+    const int chunks = family_chunks(C, count, PF_TILE);
     int npc = ((count + chunks - 1) / chunks + PF_TILE - 1) / PF_TILE * PF_TILE;
     if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (poisson)");
-    dim3 grid((C + PF_THREADS - 1) / PF_THREADS, chunks);
+    dim3 grid((C + 31) / 32, chunks);
     k_pois_sum<<<grid, PF_THREADS, 0, m->stream>>>(m->T, pa, lo, hi, npc, m->d_partials);
     m->launches++;
     k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
@@ -1176,7 +1211,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   for (auto& d : m->decl) {
     pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
     if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
-    if (d.family == NIMB_FAM_POIS_LOGLIN) pc = std::max(pc, (size_t)64 * C);
+    if (d.family == NIMB_FAM_POIS_LOGLIN || d.family == NIMB_FAM_BERN_LOGIT_LIN) pc = std::max(pc, (size_t)512 * C);
     if (d.family == NIMB_FAM_NORM_GATHER) pc = std::max(pc, (size_t)(norm_blocks(d.n) + 1) * 2 * C);
   }
   TRY(dev_alloc(m, &m->d_partials, pc));
@@ -1229,6 +1264,28 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (len == 0) { d.family = NIMB_FAM_GENERIC; continue; }
     TRY(dev_alloc(m, &m->d_xpad[i], len));
     fused_bern_logit_prepare_x(m->d_darr[xid], m->d_darr[d.value_ref], d.n, p, ld, m->d_xpad[i], m->stream);
+  }
+  // Bernoulli-logit-linear family: validate
+  m->bern_ok.assign(m->decl.size(), 0);
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    nimb200_decl& d = m->decl[i];
+    if (d.family != NIMB_FAM_BERN_LOGIT_LIN) continue;
+    int xid = d.fam_arg[0], gs = d.fam_arg[3], gm = d.fam_arg[4], ga = d.fam_arg[5];
+    bool ok = d.dist == NIMB_DBINOM && xid >= 0 && xid < t->n_darr && t->darr_len[xid] >= d.n && d.fam_arg[1] >= 0 &&
+              d.fam_arg[1] < t->n_slots && d.fam_arg[2] >= 0 && d.fam_arg[2] < t->n_slots && !getenv("NIMB200_NO_FUSED");
+    if (ok && gs >= 0) {
+      if (gm == NIMB_IDX_IARR) ok = ga >= 0 && ga < t->n_iarr && t->iarr_len[ga] >= d.n;
+      if (ok && (gm == NIMB_IDX_DIV || gm == NIMB_IDX_MOD)) ok = ga >= 1;
+      int64_t maxg = 0;
+      for (int q = 0; ok && q < d.n; q++) {
+        int64_t g = gm == NIMB_IDX_I ? q : gm == NIMB_IDX_DIV ? q / ga : gm == NIMB_IDX_MOD ? q % ga : t->iarr[ga][q];
+        if (g < 0) ok = false;
+        maxg = std::max(maxg, g);
+      }
+      if (ok) ok = gs + maxg < t->n_slots;
+    }
+    if (!ok) { d.family = NIMB_FAM_GENERIC; continue; }
+    m->bern_ok[i] = 1;
   }
   // streaming normal family: validate
   m->norm_ok.assign(m->decl.size(), 0);
@@ -1327,6 +1384,18 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
         dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0)
       m->pois_sweep[s] = 1;
+  }
+  m->bern_sweep.assign(m->samplers.size(), 0);
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    if (sp.type != NIMB_SAMPLER_BINARY || m->wide[s] || sp.n_dep != 2) continue;
+    const nimb200_dep &d0 = m->deps[sp.dep_off], &d1 = m->deps[sp.dep_off + 1];
+    const nimb200_decl &z = m->decl[d0.decl], &y = m->decl[d1.decl];
+    if (d0.stage == 0 && d1.stage == 1 && z.family == NIMB_FAM_BERN_LOGIT_LIN && m->bern_ok[d0.decl] && z.value_kind == 1 &&
+        z.fam_arg[3] < 0 && (d0.sel == NIMB_SEL_SAME || d0.sel == NIMB_SEL_RANGE) &&
+        z.value_ref + (d0.sel == NIMB_SEL_SAME ? d0.a : d0.a) == sp.target_slot && y.family == NIMB_FAM_BERN_LOGIT_LIN &&
+        m->bern_ok[d1.decl] && y.value_kind == 0 && y.fam_arg[3] == sp.target_slot)
+      m->bern_sweep[s] = 1;
   }
   m->norm_sweep.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -1586,7 +1655,12 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   ModelHostExtra* ex = extra_of(m);
   int C = m->C;
   const int TB = 128;
-  if (!m->wide[s] && m->norm_sweep[s] && m->nranks > 1 && m->sweep_sharded[s]) {
+  if (!m->wide[s] && m->bern_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+    size_t total = (size_t)sp.n_targets * C;
+    k_bernlin_binary_sweep<<<(unsigned)((total + BF_THREADS - 1) / BF_THREADS), BF_THREADS, 0, m->stream>>>(
+        m->T, s, seed, iter, bern_args(m, m->deps[sp.dep_off].decl), bern_args(m, m->deps[sp.dep_off + 1].decl));
+    m->launches++;
+  } else if (!m->wide[s] && m->norm_sweep[s] && m->nranks > 1 && m->sweep_sharded[s]) {
     // data-sharded: per-target (sum y, count) of this rank's slice -> all-reduce (2 doubles per target) -> draws
     size_t need = (size_t)sp.n_targets * 2;
     if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");

@@ -19,6 +19,7 @@
 #include <cstdlib>
 #include "engine.cuh"
 #include "fastmath.cuh"
+#include "bern_logit.cuh"
 
 namespace nimb {
 
@@ -55,121 +56,6 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 
 __device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
-}
-
-// dbinom(y, 1, ilogit(eta), log = 1) for y in {0, 1}.
-// nmath: dbinom -> dbinom_raw(x, 1, p, q = 1-p):  x = 0: p < 0.1 ? -bd0(1, q) - p : log(q);  x = 1: q < 0.1 ? -bd0(1, p) - q : log(p)
-// (plus p == 0 / q == 0 shortcuts).  In exact arithmetic -bd0(1, q) - p = log(q) + ((1 - q) - p), i.e. log(q) plus the rounding
-// error of q = fl(1 - p), and -bd0(1, p) - q = log(p) because 1 - p is exact for p > 0.9.  So every branch is
-//   log(t) + corr,  t = y ? p : q,  corr = y ? 0 : ((1 - q) - p) / q
-// to < 1e-15 relative, with the same p = 1/(1 + exp(-eta)) rounding sequence as Utils.h:187 and the same limits
-// (p == 0: y=0 -> 0, y=1 -> -Inf;  q == 0: y=0 -> -Inf, y=1 -> 0).  No data-dependent loop, no divergent branch.
-//
-// W values are carried through every step together (statement-level interleaving): the dependent DFMA chains of
-// exp / reciprocal / log are long, and with 4 resident warps per scheduler the FP64 pipe only fills when each warp
-// offers several independent chains (ncu round 1: "wait" was the top stall reason of the scalar version).
-
-// exact but slow: |eta| so large that exp(-eta) overflows (eta < -690), or NaN.  Library exp / division / log.
-__device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
-  double p = 1.0 / (1.0 + exp(-eta));
-  if (p != p) return p;
-  double q = 1.0 - p;
-  double t = y1 ? p : q;
-  double corr = (y1 || q == 0.0) ? 0.0 : ((1.0 - q) - p) / q;
-  return log(t) + corr;
-}
-
-template <int W>
-__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const MathTab* __restrict__ tab) {
-  bool slow = false;
-#pragma unroll
-  for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
-  if (__any_sync(0xffffffffu, slow)) {  // warp-uniform, practically never taken
-#pragma unroll
-    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1);
-    return;
-  }
-  double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
-  int n[W];
-  // ---- e = exp(-eta): x = k ln2/64 + r, e = 2^(k>>6) T[k&63] (1 + r P(r)).  x is clamped at -708: below that e only has to
-  // vanish against 1, and 2^(k>>6) can then always be applied by one integer add to the exponent field.
-#pragma unroll
-  for (int j = 0; j < W; j++) x[j] = fmax(-eta[j], -708.0);
-#pragma unroll
-  for (int j = 0; j < W; j++) t[j] = fma(x[j], c_tab_misc[0], c_tab_misc[1]);
-#pragma unroll
-  for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_tab_misc[1]; }
-#pragma unroll
-  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[2], x[j]);
-#pragma unroll
-  for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[3], r[j]);
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(r[j], c_tab_misc[4], c_tab_misc[5]);
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_tab_misc[6]);
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 0.5);
-#pragma unroll
-  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
-#pragma unroll
-  for (int j = 0; j < W; j++) {
-    double T = tab->expT[n[j] & 63];
-    double v = fma(T * r[j], pl[j], T);
-    e[j] = __hiloint2double(__double2hiint(v) + ((n[j] >> 6) << 20), __double2loint(v));
-  }
-  // ---- p = 1/(1+e): d in [1, 1e300]; Newton on a >= 20-bit seed, last step on the residual
-#pragma unroll
-  for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];
-#pragma unroll
-  for (int j = 0; j < W; j++) p[j] = rcp_approx(d[j]);
-#pragma unroll
-  for (int it = 0; it < 3; it++) {
-#pragma unroll
-    for (int j = 0; j < W; j++) u[j] = fma(-d[j], p[j], 1.0);
-#pragma unroll
-    for (int j = 0; j < W; j++) p[j] = fma(p[j], u[j], p[j]);
-  }
-  // ---- t = y ? p : q.  For y = 0 the rounding error delta of q = fl(1-p) is added back inside the logarithm:
-  // log(q) + delta/q = log(q + delta) to first order.
-#pragma unroll
-  for (int j = 0; j < W; j++) q[j] = 1.0 - p[j];
-  double dl[W];
-#pragma unroll
-  for (int j = 0; j < W; j++) {
-    dl[j] = y1 ? 0.0 : (1.0 - q[j]) - p[j];  // exact
-    t[j] = y1 ? p[j] : q[j];
-  }
-  // ---- log(t), t = 0 or a normal number in [2^-1000, 1]: t = 2^e m, m in [1,2), centre c = 1 + j/128 (j = 128 -> e+1, c = 1)
-#pragma unroll
-  for (int j = 0; j < W; j++) {
-    int hi = __double2hiint(t[j]), lo = __double2loint(t[j]);
-    bool zero = (hi | lo) == 0;
-    int ex = (hi >> 20) - 1023;
-    int fr = hi & 0x000fffff;
-    int idx = (fr + 0x1000) >> 13;
-    ex += idx >> 7;
-    double m = __hiloint2double(fr | 0x3ff00000, lo);
-    double ic = tab->invc[idx];
-    bool em1 = ex == -1;
-    double lc = em1 ? tab->logB[idx] : tab->logA[idx];
-    double kd = em1 ? 0.0 : (double)ex;
-    double rr = fma(m, ic, -1.0);
-    rr = fma(dl[j] * __hiloint2double((1023 - (hi >> 20) + 1023) << 20, 0), ic, rr);  // + delta 2^-e / c
-    double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
-    Q = fma(Q, rr, c_tab_misc[10]);
-    Q = fma(Q, rr, c_tab_misc[11]);
-    Q = fma(Q, rr, 1.0 / 3.0);
-    Q = fma(Q, rr, -0.5);
-    double lp = fma(rr * rr, Q, rr);
-    double lg = fma(kd, c_tab_misc[7], lc + lp);
-    out[j] = zero ? -INFINITY : lg;
-  }
-}
-
-__device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)
-  double in[1] = {eta}, o[1];
-  bern_logit_lp_vec<1>(in, y1, o, &g_mathtab);
-  return o[0];
 }
 
 // grid: (chain tiles, node chunks): the chain tiles of one node chunk are scheduled together and share its X tiles

@@ -56,17 +56,19 @@ __global__ void k_pois_nodeconst(const double* __restrict__ y, int n, double* __
 }
 
 static const int PF_THREADS = 256;  // chains per block
-static const int PF_TILE = 256;     // nodes staged per step
+static const int PF_TILE = 1024;    // nodes staged per step
 
-// block sums: grid (chain tiles, node chunks); thread = one chain, walks the chunk's nodes (data broadcast from shared
-// memory, lam gathers coalesced over the 32 chains of a warp).  partials[chunk][C].
+// block sums: grid (chain tiles of 32, node chunks); lane = chain (lam gathers coalesced over the warp), the 8 warps of a
+// CTA share the staged node tile (warp w takes the w-th run of 32 consecutive nodes).  partials[chunk][C].
 __global__ void __launch_bounds__(PF_THREADS)
 k_pois_sum(DevTab T, PoisArgs a, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
   __shared__ double sy[PF_TILE], sx[PF_TILE], sA[PF_TILE];
   __shared__ int sg[PF_TILE];
+  __shared__ double red[PF_THREADS / 32][32];
   __shared__ MathTab tab;
   load_mathtab(&tab, threadIdx.x, PF_THREADS);
-  const int c = blockIdx.x * PF_THREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = PF_THREADS / 32;
+  const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
   const int cc = live ? c : T.C - 1;
   const double b0 = T.state[(size_t)a.b0_slot * T.C + cc], b1 = T.state[(size_t)a.b1_slot * T.C + cc];
@@ -76,27 +78,31 @@ k_pois_sum(DevTab T, PoisArgs a, int lo, int hi, int nodes_per_chunk, double* __
   double lam = 0.0;
   for (int t0 = c_lo; t0 < c_hi; t0 += PF_TILE) {
     __syncthreads();
-    int i = t0 + threadIdx.x;
-    if (i < c_hi) { sy[threadIdx.x] = a.y[i]; sx[threadIdx.x] = a.x[i]; sA[threadIdx.x] = a.A[i]; sg[threadIdx.x] = pois_lam_index(a, i); }
+    for (int q = threadIdx.x; q < PF_TILE && t0 + q < c_hi; q += PF_THREADS) {
+      int i = t0 + q;
+      sy[q] = a.y[i]; sx[q] = a.x[i]; sA[q] = a.A[i]; sg[q] = pois_lam_index(a, i);
+    }
     __syncthreads();
     int cnt = min(PF_TILE, c_hi - t0);
-    int k = 0;
-    for (; k + 1 < cnt; k += 2) {  // two nodes per trip: independent chains for the FP64 pipe
-      int g0 = sg[k], g1 = sg[k + 1];
-      if (g0 != gprev) { lam = T.state[(size_t)(a.lam_slot + g0) * T.C + cc]; gprev = g0; }
-      double lam0 = lam;
-      if (g1 != gprev) { lam = T.state[(size_t)(a.lam_slot + g1) * T.C + cc]; gprev = g1; }
-      double lam1 = lam;
-      acc0 += pois_lp(sy[k], sA[k], lam0, fma(b1, sx[k], b0), &tab);
-      acc1 += pois_lp(sy[k + 1], sA[k + 1], lam1, fma(b1, sx[k + 1], b0), &tab);
-    }
-    if (k < cnt) {
+    const int per = PF_TILE / nw, k_hi = min(cnt, (warp + 1) * per);
+    for (int k = warp * per; k < k_hi; k += 2) {  // a contiguous run per warp (consecutive nodes mostly share lam), two nodes per trip
       int g0 = sg[k];
       if (g0 != gprev) { lam = T.state[(size_t)(a.lam_slot + g0) * T.C + cc]; gprev = g0; }
       acc0 += pois_lp(sy[k], sA[k], lam, fma(b1, sx[k], b0), &tab);
+      if (k + 1 < k_hi) {
+        int g1 = sg[k + 1];
+        if (g1 != gprev) { lam = T.state[(size_t)(a.lam_slot + g1) * T.C + cc]; gprev = g1; }
+        acc1 += pois_lp(sy[k + 1], sA[k + 1], lam, fma(b1, sx[k + 1], b0), &tab);
+      }
     }
   }
-  if (live) partials[(size_t)blockIdx.y * T.C + c] = acc0 + acc1;
+  red[warp][lane] = acc0 + acc1;
+  __syncthreads();
+  if (warp == 0 && live) {
+    double s = 0.0;
+    for (int w = 0; w < nw; w++) s += red[w][lane];
+    partials[(size_t)blockIdx.y * T.C + c] = s;
+  }
 }
 
 // conjugate gamma-Poisson sweep over the lam[g] targets (MCMC_conjugacy.R:80-93: contribution_shape = value,

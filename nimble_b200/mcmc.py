@@ -361,6 +361,7 @@ class _Lowering:
             d.fam_arg[3] = ip[4]
         self._match_pois_loglin(decl, d)
         self._match_norm_gather(decl, d)
+        self._match_bern_logit_lin(decl, d)
         self.b.decls.append(d)
         return len(self.b.decls) - 1
 
@@ -405,6 +406,45 @@ class _Lowering:
             op, a, bmode, carg, _ = vops[0]
             d.fam_arg[2], d.fam_arg[3], d.fam_arg[4] = a, bmode, carg
         d.family = T.FAM_NORM_GATHER
+
+    def _match_bern_logit_lin(self, decl, d):
+        """v[i] ~ dbern(gate[G(i)] * ilogit(c0 + c1 * x[i])) (gate optional) -> Bernoulli-logit-linear family."""
+        if d.family != T.FAM_GENERIC or decl.dist != T.DBINOM or decl.params[0] != ("const", 1.0):
+            return
+        prob, gate = decl.params[1], None
+        if prob[0] == "bin" and prob[1] == T.OP_MUL:
+            for g, q in ((prob[2], prob[3]), (prob[3], prob[2])):
+                if g[0] == "cvar" and q[0] == "un" and q[1] == T.OP_ILOGIT:
+                    gate, prob = g, q
+                    break
+        if prob[0] != "un" or prob[1] != T.OP_ILOGIT:
+            return
+        lin = prob[2]
+        if lin[0] != "bin" or lin[1] != T.OP_ADD:
+            return
+        for c0, cx in ((lin[2], lin[3]), (lin[3], lin[2])):
+            if c0[0] != "cvar" or not isinstance(c0[2], (int, np.integer)) or cx[0] != "bin" or cx[1] != T.OP_MUL:
+                continue
+            for c1, x in ((cx[2], cx[3]), (cx[3], cx[2])):
+                if c1[0] != "cvar" or not isinstance(c1[2], (int, np.integer)) or x[0] != "data":
+                    continue
+                xops = []
+                self._flatten(x, decl, xops)
+                if xops[0][2] != T.IDX_I:
+                    continue
+                d.fam_arg[0] = xops[0][1]
+                d.fam_arg[1] = self.model.var_slot[c0[1]] + int(c0[2])
+                d.fam_arg[2] = self.model.var_slot[c1[1]] + int(c1[2])
+                d.fam_arg[3] = -1
+                if gate is not None:
+                    gops = []
+                    self._flatten(gate, decl, gops)
+                    op, a, bmode, carg, _ = gops[0]
+                    if op == T.OP_CVAR:
+                        a, bmode, carg = a, T.IDX_DIV, max(decl.n, 1)
+                    d.fam_arg[3], d.fam_arg[4], d.fam_arg[5] = a, bmode, carg
+                d.family = T.FAM_BERN_LOGIT_LIN
+                return
 
     def _match_pois_loglin(self, decl, d):
         """y[i] ~ dpois(lam[G(i)] * exp(b0 + b1 * x[i])) (any commutative arrangement) -> fused Poisson family."""

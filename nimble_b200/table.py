@@ -22,7 +22,7 @@ OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_POW = 16, 17, 18, 19, 20
 OP_NEG, OP_EXP, OP_LOG, OP_SQRT, OP_ILOGIT, OP_LOGIT, OP_INV, OP_SQ, OP_ABS, OP_LOG1P, OP_ICLOGLOG, OP_STEP = (
     32, 33, 34, 35, 36, 37, 38, 39, 40, 41, 42, 43)
 IDX_I, IDX_DIV, IDX_MOD, IDX_IARR = 0, 1, 2, 3
-FAM_GENERIC, FAM_BERN_LOGIT_INPROD, FAM_POIS_LOGLIN, FAM_NORM_GATHER = 0, 1, 2, 3
+FAM_GENERIC, FAM_BERN_LOGIT_INPROD, FAM_POIS_LOGLIN, FAM_NORM_GATHER, FAM_BERN_LOGIT_LIN = 0, 1, 2, 3, 4
 SEL_ALL, SEL_SAME, SEL_STRIDE, SEL_SEG, SEL_CSR, SEL_RANGE = 0, 1, 2, 3, 4, 5
 PARAM_RATE, PARAM_TAU = 16, 17
 LINK_IDENTITY, LINK_ADDITIVE, LINK_MULTIPLICATIVE, LINK_LINEAR = 0, 1, 2, 3

@@ -373,3 +373,38 @@ def test_norm_family_block_sums_and_edges(oracle, b200):
     dg.set_values(v)
     do.set_values(v)
     assert np.array_equal(dg.calculate(2), do.calculate(2)) and dg.calculate(2)[0] == np.inf and dg.calculate(2)[1] == -np.inf
+
+
+def test_bern_family_block_sums_and_edges(oracle, b200):
+    """Bernoulli-logit-linear family (occupancy model) against the oracle for >= 32 chains: the data declaration with its
+    latent gate, the latent declaration itself, and chains that must take the exact path (gate / value not 0 or 1, NaN)."""
+    m, conf = sm.SMALL["occupancy"]()
+    C = 40
+    inits = sm.random_inits(m, C, 4, 0.3)
+    z0 = m.var_slot["z"]
+    rng = np.random.default_rng(1)
+    inits[:, z0:z0 + 300] = (rng.random((C, 300)) < 0.6).astype(float)
+    inits[3, z0 + 5] = 0.5      # gate / value that is neither 0 nor 1
+    inits[4, m.var_slot["a0"]] = 60.0
+    inits[5, m.var_slot["a0"]] = -800.0
+    inits[6, m.var_slot["b1"]] = np.nan
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(C), co._ensure(C)
+    dg.set_values(inits)
+    do.set_values(inits)
+    fams = [d.family for d in cg.builder.decls]
+    assert fams[-2:] == [T.FAM_BERN_LOGIT_LIN, T.FAM_BERN_LOGIT_LIN]
+    for di in (len(fams) - 2, len(fams) - 1):
+        a, b = dg.calculate(di), do.calculate(di)
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b)), di
+        assert rel_err(a, b).max() < RTOL_LP, (di, rel_err(a, b).max())
+
+
+def test_bern_family_trajectories(oracle, b200):
+    m, conf = sm.SMALL["occupancy"]()
+    inits = sm.random_inits(m, 40, 8, 0.1)
+    inits[:, m.var_slot["z"]:m.var_slot["z"] + 300] = 1.0
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 260, 10, seed=3), run(cg, inits, 260, 10, seed=3)
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert np.array_equal(cg.dm.get_values()[:, m.var_slot["z"]:], co.dm.get_values()[:, m.var_slot["z"]:])
