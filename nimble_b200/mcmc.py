@@ -721,6 +721,7 @@ class CompiledMCMC:
         self.thinFromConfVec = mcmc.thinFromConfVec
         self.dm = None
         self.mvSamples = None
+        self.check_initial_logprobs = True  # initializeModel's NaN / -Inf warnings (MCMC_build.R:241)
 
     def _ensure(self, nchains):
         if self.dm is None or self.dm.C != nchains:
@@ -747,9 +748,25 @@ class CompiledMCMC:
         dm = self._ensure(inits_matrix.shape[0])
         if reset:
             dm.set_values(inits_matrix)
+        if self.check_initial_logprobs:
+            self._initialize_model_checks(dm)
         dm.run(int(niter), int(nburnin), int(thin), reset, int(seed))
         self.mvSamples = dm.samples()
         return self.mvSamples
+
+    def _initialize_model_checks(self, dm):
+        """The warnings of initializeModel (P/R/initializeModel.R:97-139): every declaration is calculated once for every
+        chain before sampling starts; NaN / -Inf log-probabilities are reported, sampling goes on regardless."""
+        import warnings
+        for di, decl in enumerate(self.model.decls):
+            lp = dm.calculate(di)
+            kind = "data node" if decl.is_data else "stochastic node"
+            if np.any(np.isnan(lp)):
+                warnings.warn("problem initializing %s %s: logProb is NA or NaN (%d of %d chains)."
+                              % (kind, decl.var, int(np.isnan(lp).sum()), lp.size), RuntimeWarning, stacklevel=3)
+            elif np.any(lp == -np.inf):
+                warnings.warn("problem initializing %s %s: logProb is -Inf (%d of %d chains)."
+                              % (kind, decl.var, int((lp == -np.inf).sum()), lp.size), RuntimeWarning, stacklevel=3)
 
     def run(self, niter, nburnin=0, thin=-1, reset=True, inits=None, seed=0, **_ignored):
         """mcmc$run(niter, ...) for a single chain (compatibility route)."""

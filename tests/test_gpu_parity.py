@@ -408,3 +408,19 @@ def test_bern_family_trajectories(oracle, b200):
     so, sg = run(co, inits, 260, 10, seed=3), run(cg, inits, 260, 10, seed=3)
     assert rel_err(sg, so).max() < RTOL_TRAJ
     assert np.array_equal(cg.dm.get_values()[:, m.var_slot["z"]:], co.dm.get_values()[:, m.var_slot["z"]:])
+
+
+def test_posteriors_agree_within_monte_carlo_error(oracle, b200):
+    """north_star, third criterion: independent GPU and CPU runs (different seeds, different chains) give posterior means and
+    variances that agree within Monte Carlo standard error (ESS by the coda-style estimator applied to both sides)."""
+    m, conf = sm.SMALL["logistic"]()
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    sg = run(cg, sm.random_inits(m, 64, 1, 0.1), 3000, 1000, seed=101)
+    so = run(co, sm.random_inits(m, 8, 2, 0.1), 3000, 1000, seed=202)
+    for j, name in enumerate(cg.colnames):
+        eg = sum(nb.effective_size(sg[c, :, j]) for c in range(sg.shape[0]))
+        eo = sum(nb.effective_size(so[c, :, j]) for c in range(so.shape[0]))
+        vg, vo = sg[:, :, j].var(), so[:, :, j].var()
+        mcse = np.sqrt(vg / max(eg, 1.0) + vo / max(eo, 1.0))
+        assert abs(sg[:, :, j].mean() - so[:, :, j].mean()) < 5 * mcse, (name, sg[:, :, j].mean(), so[:, :, j].mean(), mcse)
+        assert abs(np.log(vg / vo)) < 0.6, (name, vg, vo)

@@ -152,3 +152,12 @@ def test_ess_estimator():
         ar[i] = 0.9 * ar[i - 1] + x[i]
     ess = nb.effective_size(ar)
     assert 100 < ess < 400  # theory: n (1-rho)/(1+rho) = 210
+
+
+def test_initialize_model_warnings(oracle):
+    # initializeModel.R:97-139: NaN / -Inf logProbs of the initial state are reported, sampling continues
+    code = "{ s ~ dgamma(1, 1)\n for (i in 1:3) { y[i] ~ dnorm(0, sd = s) } }"
+    m = nb.nimbleModel(code, data={"y": [0.1, 0.2, 0.3]}, inits={"s": -1.0})
+    cm = nb.compileNimble(nb.buildMCMC(nb.configureMCMC(m)), backend=oracle)
+    with pytest.warns(RuntimeWarning, match="logProb is"):
+        nb.runMCMC(cm, niter=5, setSeed=1)
