@@ -251,7 +251,8 @@ __device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep&
 }
 
 __device__ __forceinline__ DrawKey make_key(const DevTab& T, uint64_t seed, uint64_t iter, int sid, int t, int c) {
-  DrawKey k; k.seed = seed; k.chain = (uint32_t)(T.first_chain + c); k.iter = iter; k.sampler = (uint32_t)sid; k.target = (uint32_t)t;
+  DrawKey k; k.seed = seed; k.chain = (uint32_t)(T.first_chain + c); k.iter = T.ctr ? (uint64_t)T.ctr[0] : iter;
+  k.sampler = (uint32_t)sid; k.target = (uint32_t)t;
   return k;
 }
 
@@ -725,6 +726,20 @@ __global__ void k_monitor(DevTab T, const int32_t* mon, int nmon, double* row /*
   row[gid] = T.state[(size_t)mon[j] * T.C + c];
 }
 
+// graph-replayable form: decides from the device iteration counter whether this iteration is saved and where
+// (iteration it = ctr[0] - iter0 of this run; rows_before rows were already in the buffer)
+__global__ void k_monitor_ctr(DevTab T, const int32_t* mon, int nmon, double* samples, long long rows_before, long long iter0,
+                              long long nburnin, int thin) {
+  long long it = (long long)T.ctr[0] - iter0;
+  if (it <= nburnin || (it - nburnin) % thin != 0) return;
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)nmon * T.C) return;
+  int c = (int)(gid % T.C), j = (int)(gid / T.C);
+  long long row = rows_before + (it - nburnin) / thin - 1;
+  samples[(size_t)row * nmon * T.C + gid] = T.state[(size_t)mon[j] * T.C + c];
+}
+__global__ void k_bump_iter(unsigned long long* ctr) { ctr[0] += 1; }
+
 // [rows][nmon][C] -> [C][rows][nmon]
 __global__ void k_samples_out(const double* src, double* dst, int64_t rows, int nmon, int C) {
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -803,6 +818,8 @@ struct nimb200_model {
   size_t sweepbuf_cap = 0;
   std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
   std::vector<size_t> sweep_deps;   // per sampler: dependent nodes of target 0 (execution-shape heuristic)
+  unsigned long long* d_ctr = nullptr;  // device iteration counter (DevTab::ctr)
+  cudaGraphExec_t graph_exec = nullptr;
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
   cudaStream_t stream = nullptr;
@@ -1129,6 +1146,7 @@ extern "C" int nimb200_model_free(nimb200_model* m) {
   for (void* p : m->allocs) cudaFree(p);
   if (m->d_samples) cudaFree(m->d_samples);
   if (m->nccl_comm && g_nccl.destroy) g_nccl.destroy(m->nccl_comm);
+  if (m->graph_exec) cudaGraphExecDestroy(m->graph_exec);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->stream) cudaStreamDestroy(m->stream);
@@ -1245,6 +1263,9 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     TRYCU(cudaStreamSynchronize(m->stream));
     m->T.pconst = dpc;
   }
+  TRY(dev_alloc(m, &m->d_ctr, 2));
+  TRYCU(cudaMemsetAsync(m->d_ctr, 0, 2 * sizeof(unsigned long long), m->stream));
+  m->T.ctr = m->d_ctr;
   m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
   m->sweep_sharded.assign(m->samplers.size(), 0);
   // fused family: re-lay X once (row-major, rows padded to a multiple of 4 doubles)
@@ -1682,7 +1703,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   } else if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;
     // few (target, chain) pairs with many dependents each: a warp per pair
-    bool warp_per_pair = total <= 65536 && m->sweep_deps[s] >= 16;
+    bool warp_per_pair = total <= 65536 && m->sweep_deps[s] >= 8;
     if (warp_per_pair) total *= 32;
     unsigned nb = (unsigned)((total + TB - 1) / TB);
     if (m->nranks > 1 && m->sweep_sharded[s]) {  // partial sums -> all-reduce -> decide / draw
@@ -1779,18 +1800,79 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     m->d_samples = ns; m->cap = ncap;
   }
   m->launches = 0;
+  {
+    unsigned long long first = (unsigned long long)(m->iter_done + 1);
+    CK(cudaMemcpyAsync(m->d_ctr, &first, sizeof first, cudaMemcpyHostToDevice, m->stream));
+  }
+  const int64_t rows_before = m->rows, iter0 = m->iter_done;
+  // One iteration = a fixed sequence of launches once the pattern of valid cached sums has settled, so it is captured into a
+  // CUDA graph and replayed (launch latency is what bounds small models).  Iterations in which an RW_block adaptation kernel is
+  // due run through the ordinary launch path; so does everything when a NCCL all-reduce is part of the sequence.
+  const char* genv = getenv("NIMB200_GRAPH");
+  const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8;
+  if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
+  int64_t graph_launches = 0;
+  std::vector<char> valid_prev;
+  auto adapt_due = [&]() {
+    for (size_t s = 0; s < m->samplers.size(); s++) {
+      const nimb200_sampler& sp = m->samplers[s];
+      if (sp.type != NIMB_SAMPLER_RW_BLOCK || !sp.adaptive) continue;
+      for (int k = 1; k <= sp.tries; k++)
+        if ((m->ran[s] + k) % sp.adapt_interval == 0) return true;
+    }
+    return false;
+  };
+  auto one_iteration = [&](uint64_t git) -> int {
+    for (size_t s = 0; s < m->samplers.size(); s++)
+      if (run_sampler(m, (int)s, seed, git)) return 1;
+    if (nmon > 0) {
+      size_t total = (size_t)nmon * C;
+      k_monitor_ctr<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples, rows_before, iter0, nburnin, thin);
+      m->launches++;
+    }
+    k_bump_iter<<<1, 1, 0, m->stream>>>(m->d_ctr);
+    m->launches++;
+    return 0;
+  };
   CK(cudaEventRecord(m->ev0, m->stream));
   for (int64_t it = 1; it <= niter; it++) {
     uint64_t git = (uint64_t)(m->iter_done + it);
-    for (size_t s = 0; s < m->samplers.size(); s++)
-      if (run_sampler(m, (int)s, seed, git)) return 1;
-    if (it > nburnin && (it - nburnin) % thin == 0 && nmon > 0) {
-      size_t total = (size_t)nmon * C;
-      k_monitor<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples + (size_t)m->rows * total);
-      m->launches++;
-      m->rows++;
-    } else if (it > nburnin && (it - nburnin) % thin == 0) m->rows++;
+    bool due = adapt_due();
+    if (m->graph_exec && !due) {
+      CK(cudaGraphLaunch(m->graph_exec, m->stream));
+      m->launches += graph_launches;
+      for (size_t s = 0; s < m->samplers.size(); s++)
+        if (m->samplers[s].type == NIMB_SAMPLER_RW_BLOCK && m->samplers[s].adaptive) m->ran[s] += m->samplers[s].tries;
+      continue;
+    }
+    bool capture = want_graph && !m->graph_exec && !due && it >= 3 && valid_prev == m->dep_valid;
+    valid_prev = m->dep_valid;
+    if (capture) {
+      std::vector<int> ran_before = m->ran;
+      int64_t l0 = m->launches;
+      cudaGraph_t g = nullptr;
+      bool ok = cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+      if (ok && one_iteration(git)) ok = false;
+      if (cudaStreamEndCapture(m->stream, &g) != cudaSuccess || !g) ok = false;
+      if (ok && m->dep_valid != valid_prev) ok = false;  // the cache pattern must repeat for the replay to be valid
+      if (ok && cudaGraphInstantiate(&m->graph_exec, g, 0) != cudaSuccess) { m->graph_exec = nullptr; ok = false; }
+      if (g) cudaGraphDestroy(g);
+      graph_launches = m->launches - l0;
+      m->launches = l0;
+      if (ok) {
+        CK(cudaGraphLaunch(m->graph_exec, m->stream));  // capturing did not execute anything
+        m->launches += graph_launches;
+        continue;
+      }
+      cudaGetLastError();
+      m->ran = ran_before;  // nothing ran: fall back to ordinary launches for good
+      m->dep_valid = valid_prev;
+      if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
+      valid_prev.assign(1, 2);  // never equal again -> no further capture attempts
+    }
+    if (one_iteration(git)) return 1;
   }
+  m->rows += (niter - nburnin) / thin;
   CK(cudaEventRecord(m->ev1, m->stream));
   CK(cudaStreamSynchronize(m->stream));
   CK(cudaGetLastError());

@@ -25,6 +25,9 @@ struct DevTab {
   int rank, nranks;
   // pconst[3*d + p] != 0: parameter program p of declaration d does not depend on the node index (hoisted out of node loops)
   const int32_t* pconst;
+  // ctr[0]: global iteration index of the iteration being executed (device resident so that one captured CUDA graph can be
+  // replayed for every iteration); kernels read it instead of their `iter` argument
+  const unsigned long long* ctr;
 };
 
 // Per-sampler adaptive state, all [T][C] (or [d*d][C], [AI*d][C]) chain-fastest.
