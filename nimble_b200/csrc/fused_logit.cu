@@ -27,7 +27,6 @@ static const int FT_M = 128;      // nodes per tile (one TMA bulk copy)
 static const int FT_NC = 64;      // chains per block: 4 warps x 16 chains, two such warp groups split the rows
 static const int FT_THREADS = 256;
 static const int FT_MAXP4 = 64;
-static const int FT_MAXK = FT_MAXP4 / 4;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
