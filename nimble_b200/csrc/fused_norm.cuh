@@ -137,6 +137,10 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
   const int ntile = b_hi > b_lo ? (b_hi - b_lo + NT_TILE - 1) / NT_TILE : 0;
   const double* __restrict__ vbase = T.state + (size_t)a.v_slot * T.C;
   const bool vec = (T.C % 2) == 0 && c0 + NF_CT <= T.C && ((size_t)a.v_slot * T.C + c0) % 2 == 0;
+  double mk[NF_CT];
+  int gprev = -1;
+#pragma unroll
+  for (int k = 0; k < NF_CT; k++) mk[k] = 0.0;
   auto issue = [&](int tile) {  // thread 0 only: full tiles by TMA (the ragged last tile is loaded by the threads themselves)
     int n0 = b_lo + tile * NT_TILE;
     if (n0 + NT_TILE > b_hi) return;
@@ -165,22 +169,23 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
         double yv = ys[s * NT_TILE + q];
         if (a.mode >= 0) {
           int g = use_idx ? gs[s * NT_TILE + q] : norm_index(a, n0 + q);
-          const double* __restrict__ vp = vbase + (size_t)g * T.C;
-          if (vec) {  // the CTA's 8 chain copies of v[g] are 64 contiguous, 16-byte aligned bytes: four 128-bit loads
-            const double2* __restrict__ v2 = reinterpret_cast<const double2*>(vp + c0);
-            double2 w0 = v2[0], w1 = v2[1], w2 = v2[2], w3 = v2[3];
-            double vv[NF_CT] = {w0.x, w0.y, w1.x, w1.y, w2.x, w2.y, w3.x, w3.y};
+          if (g != gprev) {  // the per-chain means A + v[g] are kept while the thread stays in one group (sorted data: most trips)
+            gprev = g;
+            const double* __restrict__ vp = vbase + (size_t)g * T.C;
+            if (vec) {  // the CTA's 8 chain copies of v[g] are 64 contiguous, 16-byte aligned bytes: four 128-bit loads
+              const double2* __restrict__ v2 = reinterpret_cast<const double2*>(vp + c0);
+              double2 w0 = v2[0], w1 = v2[1], w2 = v2[2], w3 = v2[3];
+              mk[0] = A[0] + w0.x; mk[1] = A[1] + w0.y; mk[2] = A[2] + w1.x; mk[3] = A[3] + w1.y;
+              mk[4] = A[4] + w2.x; mk[5] = A[5] + w2.y; mk[6] = A[6] + w3.x; mk[7] = A[7] + w3.y;
+            } else {
 #pragma unroll
-            for (int k = 0; k < NF_CT; k++) {
-              double d = yv - (A[k] + vv[k]);
-              if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
+              for (int k = 0; k < NF_CT; k++) mk[k] = A[k] + vp[co[k]];
             }
-          } else {
+          }
 #pragma unroll
-            for (int k = 0; k < NF_CT; k++) {
-              double d = yv - (A[k] + vp[co[k]]);
-              if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
-            }
+          for (int k = 0; k < NF_CT; k++) {
+            double d = yv - mk[k];
+            if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
           }
         } else {
 #pragma unroll
