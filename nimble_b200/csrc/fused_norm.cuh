@@ -107,7 +107,8 @@ k_norm_stream(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, const i
 }
 
 // TMA-staged form of k_norm_stream for contiguous node ranges: y (and the group-index array) travel HBM -> shared memory as
-// 1-D bulk copies through a 4-stage mbarrier ring, so each CTA keeps 48 KB of loads in flight without spending registers on
+// 1-D bulk copies through a 4-stage ring of full / empty mbarriers (producer: thread 0; consumers: the 8 warps, each arriving on
+// the stage's empty barrier when it is done, so there is no CTA-wide barrier per tile), so each CTA keeps 48 KB of loads in flight without spending registers on
 // them; the threads only touch shared memory and the (L2-resident) gathered vector.  Same arithmetic as k_norm_stream.
 static const int NT_TILE = 1024;   // nodes per stage
 static const int NT_STAGES = 4;
@@ -117,15 +118,16 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
   extern __shared__ __align__(128) unsigned char nsm[];
   double* ys = (double*)nsm;                                         // [NT_STAGES][NT_TILE]
   int32_t* gs = (int32_t*)(ys + NT_STAGES * NT_TILE);                // [NT_STAGES][NT_TILE]
-  uint64_t* bar = (uint64_t*)(gs + NT_STAGES * NT_TILE);             // [NT_STAGES]
-  double* red = (double*)(bar + NT_STAGES);                          // [NF_CT][NF_THREADS/32]
+  uint64_t* bar = (uint64_t*)(gs + NT_STAGES * NT_TILE);             // full[NT_STAGES] (TMA landed), empty[NT_STAGES] (all warps done)
+  uint64_t* ebar = bar + NT_STAGES;
+  double* red = (double*)(bar + 2 * NT_STAGES);                          // [NF_CT][NF_THREADS/32]
   double* sA = red + NF_CT * (NF_THREADS / 32);                      // [NF_CT]
   const bool use_idx = a.mode == NIMB_IDX_IARR;
   const int c0 = blockIdx.y * NF_CT;
   if (threadIdx.x < NF_CT)
     sA[threadIdx.x] = eval_prog(T, min(c0 + (int)threadIdx.x, T.C - 1), a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
   if (threadIdx.x == 0) {
-    for (int s = 0; s < NT_STAGES; s++) tma::mbar_init(&bar[s], 1);
+    for (int s = 0; s < NT_STAGES; s++) { tma::mbar_init(&bar[s], 1); tma::mbar_init(&ebar[s], NF_THREADS / 32); }
     tma::fence_init();
   }
   __syncthreads();
@@ -145,6 +147,8 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
     int n0 = b_lo + tile * NT_TILE;
     if (n0 + NT_TILE > b_hi) return;
     int s = tile % NT_STAGES;
+    // the stage is free once every warp has arrived on its empty barrier for the previous use (no CTA-wide barrier per tile)
+    if (tile >= NT_STAGES) tma::wait(&ebar[s], (uint32_t)((tile / NT_STAGES - 1) & 1));
     uint32_t bytes = NT_TILE * 8 + (use_idx ? NT_TILE * 4 : 0);
     tma::expect_tx(&bar[s], bytes);
     tma::bulk_g2s(ys + s * NT_TILE, a.y + n0, NT_TILE * 8, &bar[s]);
@@ -157,7 +161,8 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
     const bool full = n0 + NT_TILE <= b_hi;
     if (threadIdx.x == 0 && tile + NT_STAGES - 1 < ntile) issue(tile + NT_STAGES - 1);  // refill the stage freed last trip
     if (full) tma::wait(&bar[s], (uint32_t)((tile / NT_STAGES) & 1));
-    else {
+    else {  // ragged last tile: every warp has consumed all earlier tiles once it is past this barrier
+      __syncthreads();
       for (int q = threadIdx.x; q < b_hi - n0; q += NF_THREADS) { ys[s * NT_TILE + q] = a.y[n0 + q]; if (use_idx) gs[s * NT_TILE + q] = a.gidx[n0 + q]; }
       __syncthreads();
     }
@@ -196,7 +201,10 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
         }
       }
     }
-    __syncthreads();  // stage s may be refilled from the next trip on
+    if (full) {  // this warp is done with stage s
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) tma::arrive(&ebar[s]);
+    }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -216,7 +224,7 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int
     }
   }
 }
-static const size_t NT_SMEM = (size_t)NT_STAGES * NT_TILE * 12 + NT_STAGES * 8 + (NF_CT * (NF_THREADS / 32) + NF_CT) * 8;
+static const size_t NT_SMEM = (size_t)NT_STAGES * NT_TILE * 12 + 2 * NT_STAGES * 8 + (NF_CT * (NF_THREADS / 32) + NF_CT) * 8;
 
 // sd == 0 (degenerate): dnorm is +Inf where y == mean and -Inf elsewhere, so the sum depends on how many residuals are
 // exactly zero.  Counted here by a plain loop, only for the chain that needs it.

@@ -13,6 +13,9 @@ __device__ __forceinline__ void fence_init() { asm volatile("fence.mbarrier_init
 __device__ __forceinline__ void expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"
