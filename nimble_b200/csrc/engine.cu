@@ -780,6 +780,7 @@ struct nimb200_model {
   std::vector<int64_t> darr_len, iarr_len;
   std::vector<double*> d_darr;
   std::vector<int32_t*> d_iarr;
+  std::vector<std::vector<int32_t>> h_iarr;  // host copies of the int arrays (segment offsets are read when launches are sized)
   DevTab T{};
   void* d_ops = nullptr; void* d_decl = nullptr; void* d_samplers = nullptr; void* d_deps = nullptr;
   void* d_darr_tab = nullptr; void* d_iarr_tab = nullptr;
@@ -1076,20 +1077,10 @@ static HostSel host_sel(nimb200_model* m, const nimb200_dep& dp, const std::vect
   return s;
 }
 
-struct ModelHostExtra {
-  std::vector<std::vector<int32_t>> h_iarr;
-};
-static std::vector<std::pair<nimb200_model*, ModelHostExtra*>> g_extra;
-static ModelHostExtra* extra_of(nimb200_model* m) {
-  for (auto& p : g_extra) if (p.first == m) return p.second;
-  return nullptr;
-}
-
 static size_t dep_count_t0(nimb200_model* m, const nimb200_sampler& sp) {
-  ModelHostExtra* ex = extra_of(m);
   size_t n = 0;
   for (int e = 0; e < sp.n_dep; e++) {
-    HostSel s = host_sel(m, m->deps[sp.dep_off + e], ex->h_iarr);
+    HostSel s = host_sel(m, m->deps[sp.dep_off + e], m->h_iarr);
     n += (size_t)std::max(0, s.hi - s.lo);
   }
   return n;
@@ -1150,8 +1141,6 @@ extern "C" int nimb200_model_free(nimb200_model* m) {
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
   if (m->stream) cudaStreamDestroy(m->stream);
-  for (size_t i = 0; i < g_extra.size(); i++)
-    if (g_extra[i].first == m) { delete g_extra[i].second; g_extra.erase(g_extra.begin() + i); break; }
   delete m;
   return 0;
 }
@@ -1168,8 +1157,6 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   if (device < 0 || device >= ndev) return fail("CUDA device index out of range");
   CK(cudaSetDevice(device));
   nimb200_model* m = new nimb200_model();
-  ModelHostExtra* ex = new ModelHostExtra();
-  g_extra.push_back({m, ex});
   m->device = device; m->C = nchains; m->first_chain = first_chain;
   m->t = *t;
   m->ops.assign(t->ops, t->ops + t->n_ops);
@@ -1185,7 +1172,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   TRYCU(cudaEventCreate(&m->ev1));
   // shared arrays: uploaded once, resident for the life of the model
   m->d_darr.resize(t->n_darr); m->d_iarr.resize(t->n_iarr);
-  ex->h_iarr.resize(t->n_iarr);
+  m->h_iarr.resize(t->n_iarr);
   for (int i = 0; i < t->n_darr; i++) {
     TRY(dev_alloc(m, &m->d_darr[i], (size_t)t->darr_len[i]));
     TRYCU(cudaMemcpyAsync(m->d_darr[i], t->darr[i], sizeof(double) * t->darr_len[i], cudaMemcpyHostToDevice, m->stream));
@@ -1193,7 +1180,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   for (int i = 0; i < t->n_iarr; i++) {
     TRY(dev_alloc(m, &m->d_iarr[i], (size_t)t->iarr_len[i]));
     TRYCU(cudaMemcpyAsync(m->d_iarr[i], t->iarr[i], sizeof(int32_t) * t->iarr_len[i], cudaMemcpyHostToDevice, m->stream));
-    ex->h_iarr[i].assign(t->iarr[i], t->iarr[i] + t->iarr_len[i]);
+    m->h_iarr[i].assign(t->iarr[i], t->iarr[i] + t->iarr_len[i]);
   }
   auto up = [&](void** dst, const void* src, size_t bytes) -> int {
     void* q = nullptr;
@@ -1659,12 +1646,11 @@ extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, in
 // ------------------------------------------------------------------------------------------------ MCMC driver
 static int ensure_dep_sums(nimb200_model* m, int s) {  // block sums of the current state for sampler s's dependencies
   const nimb200_sampler& sp = m->samplers[s];
-  ModelHostExtra* ex = extra_of(m);
   for (int e = 0; e < sp.n_dep; e++) {
     int g = sp.dep_off + e, slot = m->dep_slot[g];
     if (m->dep_valid[slot]) continue;
     const nimb200_dep& dp = m->deps[g];
-    HostSel hs = host_sel(m, dp, ex->h_iarr);
+    HostSel hs = host_sel(m, dp, m->h_iarr);
     if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)slot * m->C, nullptr, nullptr, -1, 0)) return 1;
     m->dep_valid[slot] = 1;
   }
@@ -1673,7 +1659,6 @@ static int ensure_dep_sums(nimb200_model* m, int s) {  // block sums of the curr
 
 static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const nimb200_sampler& sp = m->samplers[s];
-  ModelHostExtra* ex = extra_of(m);
   int C = m->C;
   const int TB = 128;
   if (!m->wide[s] && m->bern_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
@@ -1725,7 +1710,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     for (int e = 0; e < sp.n_dep; e++) {
       const nimb200_dep& dp = m->deps[sp.dep_off + e];
       if (dp.stage != 1) continue;
-      HostSel hs = host_sel(m, dp, ex->h_iarr);
+      HostSel hs = host_sel(m, dp, m->h_iarr);
       if (launch_eval_sum(m, 2, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + ((size_t)e * 2) * C, m->d_newsum + ((size_t)e * 2 + 1) * C,
                           &dp, sp.target_slot, gam ? 1 : 0)) return 1;
     }
@@ -1743,7 +1728,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       m->launches++;
       for (int e = 0; e < sp.n_dep; e++) {
         const nimb200_dep& dp = m->deps[sp.dep_off + e];
-        HostSel hs = host_sel(m, dp, ex->h_iarr);
+        HostSel hs = host_sel(m, dp, m->h_iarr);
         if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
       }
       int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;

@@ -1,0 +1,146 @@
+"""GPU edge cases of the sampling path against the CPU oracle: groups with no dependents, one-node declarations, one chain,
+the largest supported RW_block, degenerate run lengths.  Same tolerances as test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import nimble_b200 as nb
+from nimble_b200 import configs
+from nimble_b200 import table as T
+from tests import small_models as sm
+from tests.helpers import compile_on, rel_err, run
+
+pytestmark = pytest.mark.gpu
+RTOL_LP = 1e-12
+RTOL_TRAJ = 1e-9
+
+
+def _lmm_with_groups(grp, G, seed):
+    rng = np.random.default_rng(seed)
+    grp = np.asarray(grp)
+    y = 2.0 + rng.standard_normal(G)[grp - 1] + 1.5 * rng.standard_normal(grp.size)
+    m = nb.nimbleModel(configs.LMM_CODE, constants={"N": grp.size, "G": G, "grp": grp}, data={"y": y},
+                       inits={"mu": 0.0, "sig_u": 1.0, "sig_e": 1.0, "u": np.zeros(G)})
+    conf = nb.configureMCMC(m, monitors=["mu", "sig_u", "sig_e", "u"])
+    for v in ("sig_u", "sig_e"):
+        conf.removeSamplers(v)
+        conf.addSampler(v, type="RW", control={"log": True})
+    return m, conf
+
+
+def _glmm_with_groups(grp, G, seed):
+    rng = np.random.default_rng(seed)
+    grp = np.asarray(grp)
+    x = rng.standard_normal(grp.size)
+    y = rng.poisson(rng.gamma(2.0, 0.5, G)[grp - 1] * np.exp(0.5 + 0.3 * x)).astype(np.float64)
+    m = nb.nimbleModel(configs.GLMM_CODE, constants={"N": grp.size, "G": G, "grp": grp, "x": x}, data={"y": y},
+                       inits={"a": 1.0, "b": 1.0, "b0": 0.0, "b1": 0.0, "lam": np.ones(G)})
+    conf = nb.configureMCMC(m, monitors=["a", "b", "b0", "b1", "lam"])
+    conf.removeSamplers("a")
+    conf.addSampler("a", type="RW", control={"log": True})
+    return m, conf
+
+
+def _groups(G, empty, per, rng=None):
+    live = [g for g in range(1, G + 1) if g not in empty]
+    grp = np.repeat(live, per)
+    return rng.permutation(grp) if rng is not None else grp
+
+
+@pytest.mark.parametrize("build,permute,nchains", [(_lmm_with_groups, False, 5), (_lmm_with_groups, True, 5),
+                                                   (_lmm_with_groups, True, 40), (_glmm_with_groups, False, 5),
+                                                   (_glmm_with_groups, True, 40)])
+def test_groups_without_dependents(oracle, b200, build, permute, nchains):
+    """Random effects whose group holds no observation (first, middle, last and two adjacent groups): their conjugate
+    update has no contributions and draws from the prior.  (The reference would hand such end nodes to
+    posterior_predictive, MCMC_configuration.R:368, which draws from the same distribution.)"""
+    G, empty = 14, {1, 6, 7, 14}
+    grp = _groups(G, empty, 37, np.random.default_rng(3) if permute else None)
+    m, conf = build(grp, G, 11)
+    inits = sm.random_inits(m, nchains, 7, spread=0.1)
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 230, 20, seed=5), run(cg, inits, 230, 20, seed=5)
+    assert np.all(np.isfinite(so))
+    err = rel_err(sg, so)
+    assert err.max() < RTOL_TRAJ, (err.max(), np.unravel_index(err.argmax(), err.shape))
+    y = len(cg.builder.decls) - 1
+    assert rel_err(cg.dm.calculate(y), co.dm.calculate(y)).max() < RTOL_LP
+
+
+@pytest.mark.parametrize("nchains", [1, 33])
+def test_single_node_declarations(oracle, b200, nchains):
+    """N = 1, G = 1 (every declaration has one instance) and a one-observation logistic regression with p = 1."""
+    for m, conf in (_lmm_with_groups([1], 1, 2), _glmm_with_groups([1], 1, 3), configs.logistic(N=1, p=1, seed=4)):
+        inits = sm.random_inits(m, nchains, 9, spread=0.1)
+        co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+        so, sg = run(co, inits, 230, 0, seed=2), run(cg, inits, 230, 0, seed=2)
+        assert so.shape == sg.shape and np.all(np.isfinite(so))
+        assert rel_err(sg, so).max() < RTOL_TRAJ
+
+
+@pytest.mark.parametrize("name", ["pump", "logistic", "lmm", "lmm_perm", "occupancy", "glmm"])
+def test_one_chain(oracle, b200, name):
+    """nchains = 1 is the reference's own default (runMCMC(nchains = 1)): one live lane per warp everywhere."""
+    m, conf = sm.SMALL[name]()
+    inits = sm.random_inits(m, 1, 13, spread=0.1)
+    if name == "occupancy":
+        inits[:, m.var_slot["z"]:m.var_slot["z"] + 300] = 1.0
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 220, 10, seed=9), run(cg, inits, 220, 10, seed=9)
+    assert so.shape == sg.shape == (1, 210, len(co.colnames))
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
+
+
+def _block_model(d):
+    code = "{ for (i in 1:d) { x[i] ~ dnorm(0, sd = 2)\n y[i] ~ dnorm(x[i], sd = s[i]) } }"
+    rng = np.random.default_rng(d)
+    m = nb.nimbleModel(code, constants={"d": d, "s": 0.5 + rng.random(d)}, data={"y": rng.standard_normal(d)},
+                       inits={"x": np.zeros(d)})
+    conf = nb.configureMCMC(m, nodes=[], monitors=["x"])
+    return m, conf
+
+
+def test_largest_block_and_one_beyond(oracle, b200):
+    """RW_block at the largest supported dimension (64: the in-place Cholesky and the 16 x 64 proposal tile are sized for
+    it), across adaptation steps, then one dimension beyond, which must be refused before anything runs."""
+    m, conf = _block_model(T.MAX_BLOCK_D)
+    conf.addSampler("x[1:%d]" % T.MAX_BLOCK_D, type="RW_block", control={"adaptInterval": 50, "scale": 0.3})
+    inits = sm.random_inits(m, 18, 3, spread=0.2)
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 180, 0, seed=6), run(cg, inits, 180, 0, seed=6)
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert rel_err(cg.dm.sampler_state(0, 2), co.dm.sampler_state(0, 2)).max() < 1e-8
+    assert np.array_equal(cg.dm.sampler_state(0, 1), co.dm.sampler_state(0, 1))
+    assert len(np.unique(so[0, :, 0])) > 5                     # the block does move
+    m, conf = _block_model(T.MAX_BLOCK_D + 1)
+    conf.addSampler("x[1:%d]" % (T.MAX_BLOCK_D + 1), type="RW_block")
+    with pytest.raises(ValueError, match="exceeds the supported maximum"):
+        compile_on(b200, conf)._ensure(2)
+
+
+def test_block_dimension_is_checked_by_the_library(b200):
+    """The same limit at the C ABI: a table whose RW_block has d = 65 is rejected by nimb200_model_create."""
+    m, conf = _block_model(4)
+    conf.addSampler("x[1:4]", type="RW_block")
+    cg = compile_on(b200, conf)
+    cg.builder.samplers[0].d = T.MAX_BLOCK_D + 1
+    with pytest.raises(Exception, match="RW_block dimension"):
+        cg._ensure(2)
+
+
+def test_degenerate_run_lengths(oracle, b200):
+    """niter = 0, nburnin = niter and thin > niter - nburnin give zero rows and leave (resp. advance) the state as the
+    reference's run() does (MCMC_build.R:231-263); argument errors carry the reference's messages."""
+    m, conf = sm.SMALL["pump"]()
+    init = sm.random_inits(m, 3, 1, 0.1)
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    s = run(cg, init, 0, 0, seed=1)
+    assert s.shape == (3, 0, len(cg.colnames)) and np.array_equal(cg.dm.get_values(), init)
+    for niter, nburnin, thin in ((7, 7, 1), (7, 2, 6), (1, 0, 1)):
+        so, sg = run(co, init, niter, nburnin, thin, seed=2), run(cg, init, niter, nburnin, thin, seed=2)
+        assert so.shape == sg.shape == (3, (niter - nburnin) // thin, len(cg.colnames))
+        assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
+    for kw, msg in ((dict(niter=-1), "niter < 0"), (dict(niter=5, nburnin=-1), "nburnin < 0"),
+                    (dict(niter=5, nburnin=6), "nburnin > niter"), (dict(niter=5, thin=0), "thin < 1")):
+        with pytest.raises(ValueError, match=msg):
+            cg.run_chains(init, **kw)
