@@ -928,6 +928,7 @@ static NormArgs norm_args(nimb200_model* m, int di) {
   a.a_off = d.fam_arg[0]; a.a_len = d.fam_arg[1]; a.v_slot = d.fam_arg[2]; a.mode = d.fam_arg[3]; a.arg = d.fam_arg[4];
   a.gidx = a.mode == NIMB_IDX_IARR ? m->d_iarr[a.arg] : nullptr;
   a.decl = di;
+  a.a_slot = (a.a_len == 1 && m->ops[a.a_off].op == NIMB_OP_CVAR) ? m->ops[a.a_off].a : -1;
   return a;
 }
 static int norm_blocks(int count) {
@@ -979,16 +980,22 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     if ((size_t)nb * C > m->partials_cap) return fail("internal: partials scratch too small (normal)");
     dim3 grid(nb, (C + NF_CT - 1) / NF_CT);
     // contiguous, 16-byte aligned ranges stream through the TMA ring; index lists and odd offsets use plain loads
-    bool tma_ok = !idx && (lo % 4) == 0 && (npb % NT_TILE) == 0 && !getenv("NIMB200_NO_TMA");
+    bool tma_ok = !idx && (lo % 4) == 0 && count > 0 && !getenv("NIMB200_NO_TMA");
     if (tma_ok) {
-      static bool attr = false;
-      if (!attr) {
-        cudaFuncSetAttribute(k_norm_stream_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM);
-        cudaFuncSetAttribute(k_norm_stream_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NT_SMEM);
-        attr = true;
-      }
-      if (mode == 0) k_norm_stream_tma<0><<<grid, NF_THREADS, NT_SMEM, m->stream>>>(m->T, na, lo, hi, npb, -1, m->d_partials);
-      else k_norm_stream_tma<1><<<grid, NF_THREADS, NT_SMEM, m->stream>>>(m->T, na, lo, hi, npb, slot, m->d_partials);
+      const int npw = norm_tma_nodes_per_warp(count);
+      nb = norm_tma_blocks(count);
+      if ((size_t)nb * C > m->partials_cap) return fail("internal: partials scratch too small (normal, staged)");
+      grid = dim3(nb, (C + NF_CT - 1) / NF_CT);
+      const int ix = na.mode < 0 ? 0 : (na.mode == NIMB_IDX_IARR ? 1 : 2);
+#define NIMB_NORM_TMA(M, I)                                                                                        \
+  do {                                                                                                             \
+    static bool attr = false;                                                                                      \
+    if (!attr) { cudaFuncSetAttribute(k_norm_stream_tma<M, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NW_SMEM); attr = true; } \
+    k_norm_stream_tma<M, I><<<grid, NF_THREADS, NW_SMEM, m->stream>>>(m->T, na, lo, hi, npw, M == 1 ? slot : -1, m->d_partials); \
+  } while (0)
+      if (mode == 0) { if (ix == 0) NIMB_NORM_TMA(0, 0); else if (ix == 1) NIMB_NORM_TMA(0, 1); else NIMB_NORM_TMA(0, 2); }
+      else { if (ix == 0) NIMB_NORM_TMA(1, 0); else if (ix == 1) NIMB_NORM_TMA(1, 1); else NIMB_NORM_TMA(1, 2); }
+#undef NIMB_NORM_TMA
     } else if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
     else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
     m->launches++;
@@ -1217,7 +1224,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
     if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
     if (d.family == NIMB_FAM_POIS_LOGLIN || d.family == NIMB_FAM_BERN_LOGIT_LIN) pc = std::max(pc, (size_t)512 * C);
-    if (d.family == NIMB_FAM_NORM_GATHER) pc = std::max(pc, (size_t)(norm_blocks(d.n) + 1) * 2 * C);
+    if (d.family == NIMB_FAM_NORM_GATHER) pc = std::max(pc, (size_t)(std::max(norm_blocks(d.n), norm_tma_blocks(d.n)) + 1) * 2 * C);
   }
   TRY(dev_alloc(m, &m->d_partials, pc));
   m->partials_cap = pc;

@@ -21,6 +21,7 @@ struct NormArgs {
   int mode, arg;        // index map (NIMB_IDX_*), mode < 0: no gathered term
   int v_slot;           // slot base of the gathered vector
   int a_off, a_len;     // chain-level program A
+  int a_slot;           // >= 0: A is just this state slot (read directly, no interpreter)
   int decl;
 };
 
@@ -106,125 +107,134 @@ k_norm_stream(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, const i
   }
 }
 
-// TMA-staged form of k_norm_stream for contiguous node ranges: y (and the group-index array) travel HBM -> shared memory as
-// 1-D bulk copies through a 4-stage ring of full / empty mbarriers (producer: thread 0; consumers: the 8 warps, each arriving on
-// the stage's empty barrier when it is done, so there is no CTA-wide barrier per tile), so each CTA keeps 48 KB of loads in flight without spending registers on
-// them; the threads only touch shared memory and the (L2-resident) gathered vector.  Same arithmetic as k_norm_stream.
-static const int NT_TILE = 1024;   // nodes per stage
-static const int NT_STAGES = 4;
-template <int MODE>
-__global__ void __launch_bounds__(NF_THREADS)
-k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_block, int ov_slot, double* __restrict__ partials) {
+// TMA-staged form of k_norm_stream for contiguous node ranges.  Every warp is autonomous: it owns a contiguous run of nodes
+// and a private 3-stage ring of 256-node stages (y and the group-index array arrive as 1-D bulk copies, completion on the
+// stage's mbarrier); lane 0 refills a stage right after the warp's __syncwarp, so the main loop has no cross-warp
+// synchronisation at all and a CTA keeps 48 KB of loads in flight without spending registers on them (3 CTAs per SM).
+// Because a warp walks consecutive nodes, the per-chain means A + v[g] stay in registers while it remains inside one
+// group (sorted data: a gather every ~4 stages).  IDX: 0 = no gathered term, 1 = index array (staged), 2 = computed index.  Same arithmetic as
+// k_norm_stream.
+static const int NW_TILE = 256;                        // nodes per stage
+static const int NW_STAGES = 3;
+static const int NW_STAGE_BYTES = NW_TILE * 12;        // y [256] doubles, then g [256] ints
+static const int NW_WARPS = NF_THREADS / 32;
+static const size_t NW_SMEM = (size_t)NW_WARPS * NW_STAGES * NW_STAGE_BYTES + NW_WARPS * NW_STAGES * 8 + (NF_CT * NW_WARPS + NF_CT) * 8;
+template <int MODE, int IDX>
+__global__ void __launch_bounds__(NF_THREADS, 3)
+k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_warp, int ov_slot, double* __restrict__ partials) {
   extern __shared__ __align__(128) unsigned char nsm[];
-  double* ys = (double*)nsm;                                         // [NT_STAGES][NT_TILE]
-  int32_t* gs = (int32_t*)(ys + NT_STAGES * NT_TILE);                // [NT_STAGES][NT_TILE]
-  uint64_t* bar = (uint64_t*)(gs + NT_STAGES * NT_TILE);             // full[NT_STAGES] (TMA landed), empty[NT_STAGES] (all warps done)
-  uint64_t* ebar = bar + NT_STAGES;
-  double* red = (double*)(bar + 2 * NT_STAGES);                          // [NF_CT][NF_THREADS/32]
-  double* sA = red + NF_CT * (NF_THREADS / 32);                      // [NF_CT]
-  const bool use_idx = a.mode == NIMB_IDX_IARR;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned char* ring = nsm + warp * (NW_STAGES * NW_STAGE_BYTES);
+  uint64_t* bar = (uint64_t*)(nsm + NW_WARPS * NW_STAGES * NW_STAGE_BYTES) + warp * NW_STAGES;
+  double* red = (double*)(nsm + NW_WARPS * NW_STAGES * NW_STAGE_BYTES + NW_WARPS * NW_STAGES * 8);  // [NF_CT][NW_WARPS]
+  double* sA = red + NF_CT * NW_WARPS;                                                              // [NF_CT]
   const int c0 = blockIdx.y * NF_CT;
-  if (threadIdx.x < NF_CT)
-    sA[threadIdx.x] = eval_prog(T, min(c0 + (int)threadIdx.x, T.C - 1), a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < NT_STAGES; s++) { tma::mbar_init(&bar[s], 1); tma::mbar_init(&ebar[s], NF_THREADS / 32); }
+  const long long w0 = (long long)lo + ((long long)blockIdx.x * NW_WARPS + warp) * nodes_per_warp;
+  const int w_lo = (int)min((long long)hi, w0), w_hi = (int)min((long long)hi, w0 + nodes_per_warp);
+  const int ntile = (w_hi - w_lo + NW_TILE - 1) / NW_TILE;
+  auto issue = [&](int tile) {  // lane 0: whole and 4-node-multiple stages by TMA (a ragged global tail is read directly)
+    const int n0 = w_lo + tile * NW_TILE, cnt = min(NW_TILE, w_hi - n0);
+    if (cnt & 3) return;
+    unsigned char* st = ring + (tile % NW_STAGES) * NW_STAGE_BYTES;
+    uint64_t* b = &bar[tile % NW_STAGES];
+    tma::expect_tx(b, (uint32_t)(cnt * 8 + (IDX == 1 ? cnt * 4 : 0)));
+    tma::bulk_g2s(st, a.y + n0, (uint32_t)(cnt * 8), b);
+    if (IDX == 1) tma::bulk_g2s(st + NW_TILE * 8, a.gidx + n0, (uint32_t)(cnt * 4), b);
+  };
+  // the first copies start before anything else; warp 1 meanwhile evaluates the chain-level term (dependent global loads)
+  if (lane == 0) {
+    for (int s = 0; s < NW_STAGES; s++) tma::mbar_init(&bar[s], 1);
     tma::fence_init();
+    for (int tl = 0; tl < NW_STAGES - 1 && tl < ntile; tl++) issue(tl);
+  }
+  if (warp == 1 && lane < NF_CT) {
+    const int c = min(c0 + lane, T.C - 1);
+    if (a.a_slot >= 0) sA[lane] = (MODE == 1 && a.a_slot == ov_slot) ? 0.0 : T.state[(size_t)a.a_slot * T.C + c];
+    else sA[lane] = eval_prog(T, c, a.a_off, a.a_len, 0, 0, MODE == 1 ? ov_slot : -1, 0.0);
   }
   __syncthreads();
-  double A[NF_CT], s0[NF_CT];
-  int co[NF_CT];
+  double s0[NF_CT], mk[NF_CT];  // the chain-level terms stay in shared memory: they are only needed when the group changes
 #pragma unroll
-  for (int k = 0; k < NF_CT; k++) { A[k] = sA[k]; s0[k] = 0.0; co[k] = min(c0 + k, T.C - 1); }
-  const int b_lo = lo + blockIdx.x * nodes_per_block, b_hi = min(hi, b_lo + nodes_per_block);
-  const int ntile = b_hi > b_lo ? (b_hi - b_lo + NT_TILE - 1) / NT_TILE : 0;
-  const double* __restrict__ vbase = T.state + (size_t)a.v_slot * T.C;
+  for (int k = 0; k < NF_CT; k++) { mk[k] = sA[k]; s0[k] = 0.0; }
+  const double* __restrict__ vb = T.state + (size_t)a.v_slot * T.C + c0;
   const bool vec = (T.C % 2) == 0 && c0 + NF_CT <= T.C && ((size_t)a.v_slot * T.C + c0) % 2 == 0;
-  double mk[NF_CT];
   int gprev = -1;
+  auto step = [&](double yv, int g) {
+    if (IDX != 0 && g != gprev) {  // new group: the CTA's 8 chain copies of v[g] are 64 contiguous bytes
+      gprev = g;
+      const double* __restrict__ vp = vb + (long long)g * (long long)T.C;
+      if (vec) {
+        const double2* __restrict__ v2 = reinterpret_cast<const double2*>(vp);
+        double2 q0 = v2[0], q1 = v2[1], q2 = v2[2], q3 = v2[3];
+        mk[0] = sA[0] + q0.x; mk[1] = sA[1] + q0.y; mk[2] = sA[2] + q1.x; mk[3] = sA[3] + q1.y;
+        mk[4] = sA[4] + q2.x; mk[5] = sA[5] + q2.y; mk[6] = sA[6] + q3.x; mk[7] = sA[7] + q3.y;
+      } else {
 #pragma unroll
-  for (int k = 0; k < NF_CT; k++) mk[k] = 0.0;
-  auto issue = [&](int tile) {  // thread 0 only: full tiles by TMA (the ragged last tile is loaded by the threads themselves)
-    int n0 = b_lo + tile * NT_TILE;
-    if (n0 + NT_TILE > b_hi) return;
-    int s = tile % NT_STAGES;
-    // the stage is free once every warp has arrived on its empty barrier for the previous use (no CTA-wide barrier per tile)
-    if (tile >= NT_STAGES) tma::wait(&ebar[s], (uint32_t)((tile / NT_STAGES - 1) & 1));
-    uint32_t bytes = NT_TILE * 8 + (use_idx ? NT_TILE * 4 : 0);
-    tma::expect_tx(&bar[s], bytes);
-    tma::bulk_g2s(ys + s * NT_TILE, a.y + n0, NT_TILE * 8, &bar[s]);
-    if (use_idx) tma::bulk_g2s(gs + s * NT_TILE, a.gidx + n0, NT_TILE * 4, &bar[s]);
-  };
-  if (threadIdx.x == 0)
-    for (int tl = 0; tl < NT_STAGES - 1 && tl < ntile; tl++) issue(tl);
-  for (int tile = 0; tile < ntile; tile++) {
-    const int s = tile % NT_STAGES, n0 = b_lo + tile * NT_TILE;
-    const bool full = n0 + NT_TILE <= b_hi;
-    if (threadIdx.x == 0 && tile + NT_STAGES - 1 < ntile) issue(tile + NT_STAGES - 1);  // refill the stage freed last trip
-    if (full) tma::wait(&bar[s], (uint32_t)((tile / NT_STAGES) & 1));
-    else {  // ragged last tile: every warp has consumed all earlier tiles once it is past this barrier
-      __syncthreads();
-      for (int q = threadIdx.x; q < b_hi - n0; q += NF_THREADS) { ys[s * NT_TILE + q] = a.y[n0 + q]; if (use_idx) gs[s * NT_TILE + q] = a.gidx[n0 + q]; }
-      __syncthreads();
-    }
-    const int cnt = min(NT_TILE, b_hi - n0);
-#pragma unroll
-    for (int u = 0; u < NT_TILE / NF_THREADS; u++) {
-      int q = u * NF_THREADS + threadIdx.x;
-      if (q < cnt) {
-        double yv = ys[s * NT_TILE + q];
-        if (a.mode >= 0) {
-          int g = use_idx ? gs[s * NT_TILE + q] : norm_index(a, n0 + q);
-          if (g != gprev) {  // the per-chain means A + v[g] are kept while the thread stays in one group (sorted data: most trips)
-            gprev = g;
-            const double* __restrict__ vp = vbase + (size_t)g * T.C;
-            if (vec) {  // the CTA's 8 chain copies of v[g] are 64 contiguous, 16-byte aligned bytes: four 128-bit loads
-              const double2* __restrict__ v2 = reinterpret_cast<const double2*>(vp + c0);
-              double2 w0 = v2[0], w1 = v2[1], w2 = v2[2], w3 = v2[3];
-              mk[0] = A[0] + w0.x; mk[1] = A[1] + w0.y; mk[2] = A[2] + w1.x; mk[3] = A[3] + w1.y;
-              mk[4] = A[4] + w2.x; mk[5] = A[5] + w2.y; mk[6] = A[6] + w3.x; mk[7] = A[7] + w3.y;
-            } else {
-#pragma unroll
-              for (int k = 0; k < NF_CT; k++) mk[k] = A[k] + vp[co[k]];
-            }
-          }
-#pragma unroll
-          for (int k = 0; k < NF_CT; k++) {
-            double d = yv - mk[k];
-            if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
-          }
-        } else {
-#pragma unroll
-          for (int k = 0; k < NF_CT; k++) {
-            double d = yv - A[k];
-            if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
-          }
-        }
+        for (int k = 0; k < NF_CT; k++) mk[k] = sA[k] + vp[min(k, T.C - 1 - c0)];
       }
     }
-    if (full) {  // this warp is done with stage s
-      __syncwarp();
-      if ((threadIdx.x & 31) == 0) tma::arrive(&ebar[s]);
+#pragma unroll
+    for (int k = 0; k < NF_CT; k++) {
+      double d = yv - mk[k];
+      if (MODE == 0) s0[k] = fma(d, d, s0[k]); else s0[k] += d;
     }
+  };
+  for (int tile = 0; tile < ntile; tile++) {
+    const int s = tile % NW_STAGES, n0 = w_lo + tile * NW_TILE, cnt = min(NW_TILE, w_hi - n0);
+    // stage (tile - 1) % NW_STAGES was released by the __syncwarp that ended the previous trip
+    if (lane == 0 && tile + NW_STAGES - 1 < ntile) issue(tile + NW_STAGES - 1);
+    if (!(cnt & 3)) {
+      tma::wait(&bar[s], (uint32_t)((tile / NW_STAGES) & 1));
+      const unsigned char* st = ring + s * NW_STAGE_BYTES;
+      if (cnt == NW_TILE) {  // lane: nodes 64 j + 2 lane + {0, 1}, j = 0..3 (conflict-free 128- / 64-bit shared loads)
+#pragma unroll
+        for (int j = 0; j < NW_TILE / 64; j++) {
+          const double2 yy = reinterpret_cast<const double2*>(st)[j * 32 + lane];
+          int2 gg = make_int2(0, 0);
+          if (IDX == 1) gg = reinterpret_cast<const int2*>(st + NW_TILE * 8)[j * 32 + lane];
+          else if (IDX == 2) gg = make_int2(norm_index(a, n0 + j * 64 + 2 * lane), norm_index(a, n0 + j * 64 + 2 * lane + 1));
+          step(yy.x, gg.x);
+          step(yy.y, gg.y);
+        }
+      } else {
+        for (int q = lane; q < cnt; q += 32)
+          step(reinterpret_cast<const double*>(st)[q],
+               IDX == 1 ? reinterpret_cast<const int32_t*>(st + NW_TILE * 8)[q] : (IDX == 2 ? norm_index(a, n0 + q) : 0));
+      }
+    } else {
+      for (int q = lane; q < cnt; q += 32)
+        step(a.y[n0 + q], IDX == 1 ? a.gidx[n0 + q] : (IDX == 2 ? norm_index(a, n0 + q) : 0));
+    }
+    __syncwarp();
   }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < NF_CT; k++) {
     double v0 = s0[k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v0 += __shfl_xor_sync(0xffffffffu, v0, o);
-    if (lane == 0) red[k * (NF_THREADS / 32) + warp] = v0;
+    if (lane == 0) red[k * NW_WARPS + warp] = v0;
   }
   __syncthreads();
   if (threadIdx.x < NF_CT) {
     int k = threadIdx.x, c = c0 + k;
     if (c < T.C) {
       double sm = 0.0;
-      for (int w = 0; w < NF_THREADS / 32; w++) sm += red[k * (NF_THREADS / 32) + w];
+      for (int w = 0; w < NW_WARPS; w++) sm += red[k * NW_WARPS + w];
       partials[(size_t)blockIdx.x * T.C + c] = sm;
     }
   }
 }
-static const size_t NT_SMEM = (size_t)NT_STAGES * NT_TILE * 12 + 2 * NT_STAGES * 8 + (NF_CT * (NF_THREADS / 32) + NF_CT) * 8;
+// launch geometry of the TMA form: at most 444 CTAs (3 per SM), every warp a 4-node multiple of at least one stage
+static inline int norm_tma_nodes_per_warp(int count) {
+  long long warps = std::min<long long>(444LL * NW_WARPS, ((long long)count + NW_TILE - 1) / NW_TILE);
+  if (warps < 1) warps = 1;
+  long long npw = ((long long)count + warps - 1) / warps;
+  return (int)((npw + 3) / 4 * 4);
+}
+static inline int norm_tma_blocks(int count) {
+  long long per_block = (long long)norm_tma_nodes_per_warp(count) * NW_WARPS;
+  return (int)std::max<long long>(1, ((long long)count + per_block - 1) / per_block);
+}
 
 // sd == 0 (degenerate): dnorm is +Inf where y == mean and -Inf elsewhere, so the sum depends on how many residuals are
 // exactly zero.  Counted here by a plain loop, only for the chain that needs it.
