@@ -808,7 +808,9 @@ struct nimb200_model {
   std::vector<char> bern_sweep;      // per sampler: binary sweep served by k_bernlin_binary_sweep
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
-  std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_conj_sweep
+  std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_group_sums + k_norm_conj_draw
+  std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
+  std::vector<char> norm_gs_valid;   // is computed (and, data-sharded, all-reduced) once and kept until the shards change
   double* d_normtmp = nullptr;       // [2][C]
   // data-node sharding (nimb200_enable_data_sharding)
   int rank = 0, nranks = 1;
@@ -887,9 +889,17 @@ static int cw_log2_for(int C) {
   return l;
 }
 
+// nodes per thread of k_eval: 32 for large declarations; halved until the grid has two CTAs per SM, so that a small
+// declaration (a prior block of 1e4 random effects, 8 chains) is one interpreter pass per thread and not 32 in sequence
+static int eval_npt(int C, int count) {
+  int cwl = cw_log2_for(C), nl = EVAL_THREADS >> cwl, ct = (C + (1 << cwl) - 1) >> cwl;
+  int npt = EVAL_NPT;
+  while (npt > 1 && (long long)((count + nl * npt - 1) / (nl * npt)) * ct < 296) npt >>= 1;
+  return npt;
+}
 static int eval_tiles(int C, int count) {
   int nl = EVAL_THREADS >> cw_log2_for(C);
-  int per = nl * EVAL_NPT;
+  int per = nl * eval_npt(C, count);
   return (count + per - 1) / per;
 }
 
@@ -1049,8 +1059,8 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   nimb200_dep dd{};
   if (dp) dd = *dp;
   size_t shm = sizeof(double) * EVAL_THREADS * K;
-  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
-  else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, EVAL_NPT, m->d_partials, nullptr, dd, slot, gam);
+  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, nullptr, dd, slot, gam);
+  else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, nullptr, dd, slot, gam);
   m->launches++;
   k_reduce<<<(C * K * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
   m->launches++;
@@ -1221,7 +1231,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   // scratch for tile partial sums: sized for the largest declaration
   size_t pc = 1;
   for (auto& d : m->decl) {
-    pc = std::max(pc, (size_t)eval_tiles(nchains, d.n) * 2 * C);
+    pc = std::max(pc, (size_t)std::max(eval_tiles(nchains, d.n), 592) * 2 * C);  // sub-ranges never need more than 592 tiles
     if (d.family == NIMB_FAM_BERN_LOGIT_INPROD) pc = std::max(pc, (size_t)fused_bern_logit_tiles(d.n) * C);
     if (d.family == NIMB_FAM_POIS_LOGLIN || d.family == NIMB_FAM_BERN_LOGIT_LIN) pc = std::max(pc, (size_t)512 * C);
     if (d.family == NIMB_FAM_NORM_GATHER) pc = std::max(pc, (size_t)(std::max(norm_blocks(d.n), norm_tma_blocks(d.n)) + 1) * 2 * C);
@@ -1413,6 +1423,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       m->bern_sweep[s] = 1;
   }
   m->norm_sweep.assign(m->samplers.size(), 0);
+  m->d_norm_gs.assign(m->samplers.size(), nullptr);
+  m->norm_gs_valid.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     if (sp.type != NIMB_SAMPLER_CONJ_NORMAL || m->wide[s] || sp.n_dep != 2) continue;
@@ -1426,7 +1438,10 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       const nimb200_op& o = m->ops[dd.fam_arg[0] + q];
       if (o.op == NIMB_OP_CVAR && o.a >= sp.target_slot && o.a < sp.target_slot + sp.n_targets) a_reads_target = true;
     }
-    if (!a_reads_target) m->norm_sweep[s] = 1;
+    if (!a_reads_target) {
+      m->norm_sweep[s] = 1;
+      TRY(dev_alloc(m, &m->d_norm_gs[s], (size_t)sp.n_targets * 2));
+    }
   }
   // Cache slots: the block sum of the CURRENT state over (declaration, selection).  Entries of wide samplers whose selection
   // does not depend on the target share a slot, so b1's step can reuse what b0's step just committed instead of re-evaluating
@@ -1522,7 +1537,7 @@ extern "C" int nimb200_calculate_nodes(nimb200_model* m, int32_t di, int32_t lo,
   int cwl = cw_log2_for(m->C), cw = 1 << cwl;
   dim3 grid(eval_tiles(m->C, hi - lo), (m->C + cw - 1) / cw);
   nimb200_dep dd{};
-  k_eval<1><<<grid, EVAL_THREADS, 0, m->stream>>>(m->T, di, lo, hi, nullptr, cwl, EVAL_NPT, nullptr, d_out, dd, -1, 0);
+  k_eval<1><<<grid, EVAL_THREADS, 0, m->stream>>>(m->T, di, lo, hi, nullptr, cwl, eval_npt(m->C, hi - lo), nullptr, d_out, dd, -1, 0);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, sizeof(double) * n, cudaMemcpyDeviceToHost, m->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
@@ -1571,7 +1586,7 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
     else {
       dim3 grid(eval_tiles(C, d.n), (C + cw - 1) / cw);
       nimb200_dep dd{};
-      k_eval<0><<<grid, EVAL_THREADS, sizeof(double) * EVAL_THREADS, m->stream>>>(m->T, di, 0, d.n, nullptr, cwl, EVAL_NPT, m->d_partials, nullptr, dd, -1, 0);
+      k_eval<0><<<grid, EVAL_THREADS, sizeof(double) * EVAL_THREADS, m->stream>>>(m->T, di, 0, d.n, nullptr, cwl, eval_npt(C, d.n), m->d_partials, nullptr, dd, -1, 0);
     }
   }
   CK(cudaEventRecord(m->ev1, m->stream));
@@ -1611,6 +1626,7 @@ extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, in
   if (nranks < 1 || rank < 0 || rank >= nranks) return fail("bad rank / nranks");
   CK(cudaSetDevice(m->device));
   m->rank = rank; m->nranks = nranks;
+  std::fill(m->norm_gs_valid.begin(), m->norm_gs_valid.end(), 0);
   for (size_t i = 0; i < m->decl.size(); i++) {
     const nimb200_decl& d = m->decl[i];
     bool sh = nranks > 1 && d.value_kind == 0 && d.n >= min_nodes;
@@ -1673,19 +1689,18 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     k_bernlin_binary_sweep<<<(unsigned)((total + BF_THREADS - 1) / BF_THREADS), BF_THREADS, 0, m->stream>>>(
         m->T, s, seed, iter, bern_args(m, m->deps[sp.dep_off].decl), bern_args(m, m->deps[sp.dep_off + 1].decl));
     m->launches++;
-  } else if (!m->wide[s] && m->norm_sweep[s] && m->nranks > 1 && m->sweep_sharded[s]) {
-    // data-sharded: per-target (sum y, count) of this rank's slice -> all-reduce (2 doubles per target) -> draws
-    size_t need = (size_t)sp.n_targets * 2;
-    if (need > m->sweepbuf_cap) return fail("internal: sweep buffer too small");
-    NormArgs na = norm_args(m, m->deps[sp.dep_off + 1].decl);
-    k_norm_group_sums<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_sweepbuf);
-    m->launches++;
-    if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
-    size_t total = (size_t)sp.n_targets * C;
-    k_norm_conj_draw<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, na, m->d_sweepbuf);
-    m->launches++;
   } else if (!m->wide[s] && m->norm_sweep[s]) {
-    k_norm_conj_sweep<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, seed, iter, norm_args(m, m->deps[sp.dep_off + 1].decl));
+    // per-target (sum y, count) depend on the data only: computed on first use (data-sharded: this rank's slice, then one
+    // all-reduce of 2 doubles per target) and kept; every later sweep is just the draws
+    NormArgs na = norm_args(m, m->deps[sp.dep_off + 1].decl);
+    if (!m->norm_gs_valid[s]) {
+      k_norm_group_sums<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_norm_gs[s]);
+      m->launches++;
+      if (m->nranks > 1 && m->sweep_sharded[s] && m->nccl_comm && allreduce_sum(m, m->d_norm_gs[s], (size_t)sp.n_targets * 2)) return 1;
+      m->norm_gs_valid[s] = 1;
+    }
+    size_t total = (size_t)sp.n_targets * C;
+    k_norm_conj_draw<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, na, m->d_norm_gs[s]);
     m->launches++;
   } else if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
     size_t total = (size_t)sp.n_targets * C;

@@ -303,52 +303,10 @@ __global__ void k_norm_conj_finish(DevTab T, NormArgs a, int count, const double
   dst1[c] = (double)count * tau;
 }
 
-// conjugate normal-normal sweep over the gathered vector's elements (targets v[t]): one block per target.
-// Phase 1: the block adds up y over the target's nodes (chain independent, fixed order); phase 2: one thread per chain
-// forms contribution_mean = tau (sum y - n A), contribution_tau = n tau, draws and writes.
-__global__ void __launch_bounds__(128)
-k_norm_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, NormArgs a) {
-  __shared__ double red[4];
-  __shared__ double s_sum;
-  const nimb200_sampler sp = T.samplers[sid];
-  const int t = blockIdx.x;
-  const nimb200_dep dp = T.deps[sp.dep_off + 1];
-  Sel s = sel_of(T, dp, t);
-  double acc = 0.0;
-  int cnt = 0;
-  for (int k = s.lo + threadIdx.x; k < s.hi; k += 128) {
-    int node = s.idx ? s.idx[k] : k;
-    if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
-    acc += a.y[node];
-    cnt++;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o); }
-  __shared__ int cred[4];
-  if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = acc; cred[threadIdx.x >> 5] = cnt; }
-  __syncthreads();
-  if (threadIdx.x == 0) { s_sum = ((red[0] + red[1]) + red[2]) + red[3]; cred[0] = cred[0] + cred[1] + cred[2] + cred[3]; }
-  __syncthreads();
-  const double ysum = s_sum;
-  const double n = (double)cred[0];
-  const nimb200_dep tp = T.deps[sp.dep_off];
-  const int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
-  const int slot = sp.target_slot + t;
-  for (int c = threadIdx.x; c < T.C; c += 128) {
-    double A = eval_prog(T, c, a.a_off, a.a_len, 0, 0, -1, 0.0);
-    double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
-    double cm = (ysum - n * A) * tau, ct = n * tau;
-    double prior_mean = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
-    double prior_tau = get_param(T, tp.decl, tnode, c, NIMB_PARAM_TAU, -1, 0.0);
-    DrawKey key = make_key(T, seed, iter, sid, t, c);
-    double mean = (prior_mean * prior_tau + cm) / (prior_tau + ct), sd = pow(prior_tau + ct, -0.5), z, z1;
-    normal2(key, 0, z, z1);
-    T.state[(size_t)slot * T.C + c] = mean + sd * z;
-  }
-}
-
-// data-sharded form of the sweep: phase 1 leaves this rank's (sum y, count) per target in gs[t][2] (chain independent, so the
-// all-reduce between the phases carries 2 doubles per target); phase 2 is one thread per (target, chain).
+// Conjugate normal-normal sweep over the gathered vector's elements (targets v[t]).  (sum y, count) over a target's nodes
+// depend on the data only: k_norm_group_sums leaves this rank's share in gs[t][2] once (one block per target, fixed order;
+// data-sharded runs all-reduce the 2 doubles per target), k_norm_conj_draw is one thread per (target, chain) forming
+// contribution_mean = tau (sum y - n A), contribution_tau = n tau, drawing and writing.
 __global__ void __launch_bounds__(128)
 k_norm_group_sums(DevTab T, int sid, NormArgs a, double* __restrict__ gs) {
   __shared__ double red[4];
