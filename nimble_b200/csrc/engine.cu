@@ -802,7 +802,7 @@ struct nimb200_model {
   std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
   std::vector<int> ran;         // RW_block: iterations since last adaptation
   std::vector<double*> d_xpad;  // per decl: padded X for the fused family (or null)
-  std::vector<double*> d_nodeconst;  // per decl: data-only node constants of the fused Poisson family (or null)
+  std::vector<void*> d_nodeconst;    // per decl: packed nodes (PoisNode: y, x, data-only constant, lam index) of the fused Poisson family, or null
   std::vector<char> pois_sweep;      // per sampler: conjugate sweep served by k_pois_conj_sweep
   std::vector<char> bern_ok;         // per decl: Bernoulli-logit-linear family usable
   std::vector<char> bern_sweep;      // per sampler: binary sweep served by k_bernlin_binary_sweep
@@ -906,7 +906,7 @@ static int eval_tiles(int C, int count) {
 static PoisArgs pois_args(nimb200_model* m, int di) {
   const nimb200_decl& d = m->decl[di];
   PoisArgs a;
-  a.y = m->d_darr[d.value_ref]; a.x = m->d_darr[d.fam_arg[0]]; a.A = m->d_nodeconst[di];
+  a.y = m->d_darr[d.value_ref]; a.x = m->d_darr[d.fam_arg[0]];
   a.mode = d.fam_arg[2]; a.arg = d.fam_arg[3];
   a.gidx = a.mode == NIMB_IDX_IARR ? m->d_iarr[a.arg] : nullptr;
   a.lam_slot = d.fam_arg[1]; a.b0_slot = d.fam_arg[4]; a.b1_slot = d.fam_arg[5]; a.n = d.n;
@@ -1044,7 +1044,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     int npc = ((count + chunks - 1) / chunks + PF_TILE - 1) / PF_TILE * PF_TILE;
     if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (poisson)");
     dim3 grid((C + 31) / 32, chunks);
-    k_pois_sum<<<grid, PF_THREADS, 0, m->stream>>>(m->T, pa, lo, hi, npc, m->d_partials);
+    k_pois_sum<<<grid, PF_THREADS, 0, m->stream>>>(m->T, pa, (const PoisNode*)m->d_nodeconst[di], lo, hi, npc, m->d_partials);
     m->launches++;
     k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
     m->launches++;
@@ -1370,8 +1370,10 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     }
     if (ok) ok = d.fam_arg[1] >= 0 && d.fam_arg[1] + maxg < t->n_slots;
     if (!ok) { d.family = NIMB_FAM_GENERIC; continue; }
-    TRY(dev_alloc(m, &m->d_nodeconst[i], (size_t)d.n));
-    k_pois_nodeconst<<<(d.n + 255) / 256, 256, 0, m->stream>>>(m->d_darr[d.value_ref], d.n, m->d_nodeconst[i]);
+    PoisNode* pk = nullptr;
+    TRY(dev_alloc(m, &pk, (size_t)d.n));
+    m->d_nodeconst[i] = pk;
+    k_pois_pack<<<(d.n + 255) / 256, 256, 0, m->stream>>>(pois_args(m, (int)i), pk);
   }
   // sampler state + execution shape
   m->sdev.resize(m->samplers.size());

@@ -3,14 +3,15 @@
 //
 // The generic interpreter spends > 1000 instructions per evaluation on this declaration: the postfix program, CUDA's
 // exp, and nmath's dpois_raw with its stirlerr table look-up (divergent constant-memory index), log(2 pi y) and the
-// bd0 Taylor loop -- most of which depends on the data only.  Here
-//   A[i] = -0.5 log(2 pi y[i]) - stirlerr(y[i])  is computed once per model (data only, same nmath functions),
-//   mu   = lam * exp(b0 + b1 x)                   table-driven exp (fastmath.cuh),
-//   lp   = y == 0 ? -mu : A - (y log(y / mu) + mu - y)      bd0 in its closed form (no series, no divergence).
-// nmath evaluates bd0 by a Taylor series when y ~ mu to keep its RELATIVE accuracy; the closed form has absolute error
-// ~ 2e-16 y, which relative to lp (|lp| >= |A| ~ 0.5 log(2 pi y) for y >= 1) is < 1e-13 for counts up to ~1e3:
-// inside the 1e-12 parity bar (tests/test_gpu_parity.py::test_pois_family_*).  Anything unusual (lam <= 0, NaN,
-// overflowing linear predictor, mu outside [1e-290, 1e290]) takes the exact generic path per element.
+// bd0 Taylor loop -- most of which depends on the data only.  With mu = lam exp(eta), eta = b0 + b1 x:
+//   dpois_raw(y, mu) = -stirlerr(y) - 0.5 log(2 pi y) - (y log(y / mu) + mu - y)
+//                    = A[i] + y (log lam + eta) - mu,      A[i] = -stirlerr(y) - 0.5 log(2 pi y) + y - y log y   (data only)
+// so per (node, chain) only one table-driven exp (fastmath.cuh) remains: no logarithm, no reciprocal, no series, no
+// divergence; log lam is taken when the group changes, and y = 0 needs no special case (A = 0, lp = -mu).
+// nmath evaluates bd0 by a Taylor series when y ~ mu to keep its RELATIVE accuracy; this form has absolute error
+// ~ 2e-16 y log y, which relative to lp (|lp| >= 0.5 log(2 pi y) for y >= 1) stays below 4e-13 for counts up to 1024:
+// inside the 1e-12 parity bar (tests/test_gpu_parity.py::test_pois_family_*).  Anything else (y > 1024, lam <= 0, NaN,
+// |eta| >= 700, mu outside [2^-963, 2^964)) takes the exact generic path per element, after the hot loop.
 #pragma once
 
 namespace nimb {
@@ -18,7 +19,6 @@ namespace nimb {
 struct PoisArgs {
   const double* y;
   const double* x;
-  const double* A;       // node constants
   const int32_t* gidx;   // index array (mode NIMB_IDX_IARR) or null
   int mode, arg;         // index map i -> lam element
   int lam_slot, b0_slot, b1_slot;
@@ -34,67 +34,132 @@ __device__ __forceinline__ int pois_lam_index(const PoisArgs& a, int i) {
   }
 }
 
-__device__ __forceinline__ double pois_lp(double y, double A, double lam, double eta, const MathTab* tab) {
-  bool ok = lam > 0.0 && lam < 1e300 && eta > -700.0 && eta < 700.0;
-  double mu = 0.0;
-  if (ok) {
-    mu = lam * exp_tab(eta, tab);
-    ok = mu > 1e-290 && mu < 1e290;
-  }
-  if (!ok) return dpois(y, lam * exp(eta));  // exact generic path (rare)
-  if (y == 0.0) return -mu;
-  double q = y * rcp_f64(mu);
-  return A - fma(y, log_tab(q, tab), mu - y);
-}
+// one staged node: 32 bytes, built once per model by k_pois_pack (x is NaN for nodes that must take the exact path)
+struct __align__(16) PoisNode {
+  double y, x, A;
+  int g, pad;
+};
+static const double PF_YMAX = 1024.0;
 
-// node constants A[i] = -0.5 log(2 pi y) - stirlerr(y), the data-only part of nmath's dpois_raw
-__global__ void k_pois_nodeconst(const double* __restrict__ y, int n, double* __restrict__ A) {
+__global__ void k_pois_pack(PoisArgs a, PoisNode* __restrict__ out) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  double v = y[i];
-  A[i] = v > 0.0 ? -0.5 * log(NIMB_2PI * v) + (-stirlerr(v)) : 0.0;
+  if (i >= a.n) return;
+  double v = a.y[i];
+  PoisNode nd;
+  nd.y = v;
+  nd.x = v <= PF_YMAX ? a.x[i] : NAN;
+  nd.A = v > 0.0 ? (-0.5 * log(NIMB_2PI * v) + (-stirlerr(v))) + fma(-v, log(v), v) : 0.0;
+  nd.g = pois_lam_index(a, i);
+  nd.pad = 0;
+  out[i] = nd;
 }
 
-static const int PF_THREADS = 256;  // chains per block
+// fast form; ok = false -> the value is discarded and the element is redone by pois_exact_run
+__device__ __forceinline__ double pois_fast(const PoisNode& nd, double lam, double L, double b0, double b1,
+                                            const double* __restrict__ expT, const double (&K)[7], bool& ok) {
+  const double eta = fma(b1, nd.x, b0);
+  double t = fma(eta, K[0], K[1]);
+  const int n = __double2loint(t);
+  t = t - K[1];
+  double r = fma(t, K[2], eta);
+  r = fma(t, K[3], r);
+  double pl = fma(r, K[4], K[5]);
+  pl = fma(pl, r, K[6]);
+  pl = fma(pl, r, 0.5);
+  pl = fma(pl, r, 1.0);
+  const double Tj = expT[n & 63];
+  const double v = fma(Tj * r, pl, Tj);
+  const double e = __hiloint2double(__double2hiint(v) + ((n >> 6) << 20), __double2loint(v));
+  const double mu = lam * e;
+  ok = (unsigned)(__double2hiint(eta) & 0x7fffffff) < 0x4085e000u &&                       // |eta| < 700, not NaN
+       (unsigned)(__double2hiint(mu) - 0x03c00000) < (unsigned)(0x7c300000 - 0x03c00000);  // 2^-963 <= mu < 2^964, not NaN
+  return fma(nd.y, L + eta, nd.A) - mu;
+}
+
+// exact generic path for the elements of a run that pois_fast refused (rare: kept out of line, out of the hot loop)
+__device__ __noinline__ double pois_exact_run(const double* __restrict__ ya, const double* __restrict__ xa, const PoisNode* sn,
+                                              int k_lo, int k_hi, int t0, const double* lamp, size_t C, double b0, double b1,
+                                              const double* expT) {
+  double K[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
+  double s = 0.0;
+  for (int k = k_lo; k < k_hi; k++) {
+    const PoisNode nd = sn[k];
+    const double lam = lamp[(size_t)nd.g * C];
+    const bool lam_ok = lam > 0.0 && lam < 1e300;
+    bool ok;
+    pois_fast(nd, lam_ok ? lam : NAN, 0.0, b0, b1, expT, K, ok);
+    if (!ok) s += dpois(ya[t0 + k], lam * exp(fma(b1, xa[t0 + k], b0)));
+  }
+  return s;
+}
+
+static const int PF_THREADS = 256;  // 8 warps x 32 chains
 static const int PF_TILE = 1024;    // nodes staged per step
 
 // block sums: grid (chain tiles of 32, node chunks); lane = chain (lam gathers coalesced over the warp), the 8 warps of a
-// CTA share the staged node tile (warp w takes the w-th run of 32 consecutive nodes).  partials[chunk][C].
-__global__ void __launch_bounds__(PF_THREADS)
-k_pois_sum(DevTab T, PoisArgs a, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
-  __shared__ double sy[PF_TILE], sx[PF_TILE], sA[PF_TILE];
-  __shared__ int sg[PF_TILE];
+// CTA share the staged node tile (warp w takes the w-th run of 128 consecutive nodes, two nodes per trip so that two
+// independent dependency chains are in flight).  partials[chunk][C].
+__global__ void __launch_bounds__(PF_THREADS, 3)
+k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
+  __shared__ PoisNode sn[PF_TILE];
   __shared__ double red[PF_THREADS / 32][32];
-  __shared__ MathTab tab;
-  load_mathtab(&tab, threadIdx.x, PF_THREADS);
+  __shared__ double expT[64];
+  if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = PF_THREADS / 32;
   const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
   const int cc = live ? c : T.C - 1;
-  const double b0 = T.state[(size_t)a.b0_slot * T.C + cc], b1 = T.state[(size_t)a.b1_slot * T.C + cc];
+  const size_t C = (size_t)T.C;
+  const double b0 = T.state[(size_t)a.b0_slot * C + cc], b1 = T.state[(size_t)a.b1_slot * C + cc];
+  const double* __restrict__ lamp = T.state + (size_t)a.lam_slot * C + cc;
   const int c_lo = lo + blockIdx.y * nodes_per_chunk, c_hi = min(hi, c_lo + nodes_per_chunk);
+  double K[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
   double acc0 = 0.0, acc1 = 0.0;
   int gprev = -1;
-  double lam = 0.0;
+  double lam = 0.0, L = 0.0;
   for (int t0 = c_lo; t0 < c_hi; t0 += PF_TILE) {
+    const int cnt = min(PF_TILE, c_hi - t0);
     __syncthreads();
-    for (int q = threadIdx.x; q < PF_TILE && t0 + q < c_hi; q += PF_THREADS) {
-      int i = t0 + q;
-      sy[q] = a.y[i]; sx[q] = a.x[i]; sA[q] = a.A[i]; sg[q] = pois_lam_index(a, i);
+    {  // the packed nodes of a tile are contiguous: 16-byte coalesced copies
+      const int4* __restrict__ src = reinterpret_cast<const int4*>(pk + t0);
+      int4* dst = reinterpret_cast<int4*>(sn);
+      for (int q = threadIdx.x; q < cnt * 2; q += PF_THREADS) dst[q] = src[q];
     }
     __syncthreads();
-    int cnt = min(PF_TILE, c_hi - t0);
-    const int per = PF_TILE / nw, k_hi = min(cnt, (warp + 1) * per);
-    for (int k = warp * per; k < k_hi; k += 2) {  // a contiguous run per warp (consecutive nodes mostly share lam), two nodes per trip
-      int g0 = sg[k];
-      if (g0 != gprev) { lam = T.state[(size_t)(a.lam_slot + g0) * T.C + cc]; gprev = g0; }
-      acc0 += pois_lp(sy[k], sA[k], lam, fma(b1, sx[k], b0), &tab);
-      if (k + 1 < k_hi) {
-        int g1 = sg[k + 1];
-        if (g1 != gprev) { lam = T.state[(size_t)(a.lam_slot + g1) * T.C + cc]; gprev = g1; }
-        acc1 += pois_lp(sy[k + 1], sA[k + 1], lam, fma(b1, sx[k + 1], b0), &tab);
-      }
+    const int per = PF_TILE / nw, k_lo = warp * per, k_hi = min(cnt, (warp + 1) * per);
+    bool bad = false;
+    auto regroup = [&](int g) {  // new group: this chain's lam and its logarithm (non-positive / huge / NaN -> exact path)
+      gprev = g;
+      lam = lamp[(size_t)g * C];
+      if (!(lam > 0.0 && lam < 1e300)) lam = NAN;
+      L = log(lam);
+    };
+    int k = k_lo;
+    for (; k + 1 < k_hi; k += 2) {
+      const PoisNode n0 = sn[k], n1 = sn[k + 1];
+      if (n0.g != gprev) regroup(n0.g);
+      const double lam0 = lam, L0 = L;
+      if (n1.g != gprev) regroup(n1.g);
+      bool ok0, ok1;
+      const double v0 = pois_fast(n0, lam0, L0, b0, b1, expT, K, ok0);
+      const double v1 = pois_fast(n1, lam, L, b0, b1, expT, K, ok1);
+      acc0 += ok0 ? v0 : 0.0;
+      acc1 += ok1 ? v1 : 0.0;
+      bad |= !(ok0 && ok1);
     }
+    if (k < k_hi) {
+      const PoisNode n0 = sn[k];
+      if (n0.g != gprev) regroup(n0.g);
+      bool ok0;
+      const double v0 = pois_fast(n0, lam, L, b0, b1, expT, K, ok0);
+      acc0 += ok0 ? v0 : 0.0;
+      bad |= !ok0;
+    }
+    if (bad) acc1 += pois_exact_run(a.y, a.x, sn, k_lo, k_hi, t0, lamp, C, b0, b1, expT);
   }
   red[warp][lane] = acc0 + acc1;
   __syncthreads();
