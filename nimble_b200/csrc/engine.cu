@@ -809,6 +809,8 @@ struct nimb200_model {
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
   std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_group_sums + k_norm_conj_draw
+  std::vector<double*> d_pois_ysum;  // per Poisson conjugate sweep: [n_targets] sum of the counts over each target's nodes (data only)
+  std::vector<char> pois_ysum_valid;
   std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
   std::vector<char> norm_gs_valid;   // is computed (and, data-sharded, all-reduced) once and kept until the shards change
   double* d_normtmp = nullptr;       // [2][C]
@@ -1403,14 +1405,18 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     }
   }
   m->pois_sweep.assign(m->samplers.size(), 0);
+  m->d_pois_ysum.assign(m->samplers.size(), nullptr);
+  m->pois_ysum_valid.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     if (sp.type != NIMB_SAMPLER_CONJ_GAMMA || m->wide[s] || sp.n_dep != 2) continue;
     const nimb200_dep& dp = m->deps[sp.dep_off + 1];
     const nimb200_decl& dd = m->decl[dp.decl];
     if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
-        dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0)
+        dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0) {
       m->pois_sweep[s] = 1;
+      TRY(dev_alloc(m, &m->d_pois_ysum[s], (size_t)sp.n_targets));
+    }
   }
   m->bern_sweep.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -1629,6 +1635,7 @@ extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, in
   CK(cudaSetDevice(m->device));
   m->rank = rank; m->nranks = nranks;
   std::fill(m->norm_gs_valid.begin(), m->norm_gs_valid.end(), 0);
+  std::fill(m->pois_ysum_valid.begin(), m->pois_ysum_valid.end(), 0);
   for (size_t i = 0; i < m->decl.size(); i++) {
     const nimb200_decl& d = m->decl[i];
     bool sh = nranks > 1 && d.value_kind == 0 && d.n >= min_nodes;
@@ -1706,8 +1713,14 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     m->launches++;
   } else if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
     size_t total = (size_t)sp.n_targets * C;
-    k_pois_conj_sweep<<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(
-        m->T, s, seed, iter, pois_args(m, m->deps[sp.dep_off + 1].decl));
+    PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
+    if (!m->pois_ysum_valid[s]) {
+      k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s]);
+      m->launches++;
+      m->pois_ysum_valid[s] = 1;
+    }
+    k_pois_conj_sweep<<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa,
+                                                                                                     m->d_pois_ysum[s]);
     m->launches++;
   } else if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;

@@ -170,13 +170,26 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
   }
 }
 
+// sum of the counts over each target's nodes: data only, computed once per sampler (counts are integers: exact in any order)
+__global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, double* __restrict__ ysum) {
+  const nimb200_sampler sp = T.samplers[sid];
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= sp.n_targets) return;
+  const nimb200_dep dp = T.deps[sp.dep_off + 1];
+  Sel s = sel_of(T, dp, t);
+  double c0 = 0.0;
+  for (int k = s.lo; k < s.hi; k++) c0 += a.y[s.idx ? s.idx[k] : k];
+  ysum[t] = c0;
+}
+
 // conjugate gamma-Poisson sweep over the lam[g] targets (MCMC_conjugacy.R:80-93: contribution_shape = value,
 // contribution_rate = coeff, coeff = the dependent's lambda with the target set to 1 = exp(b0 + b1 x)).
-// thread = (target g, chain c), chains fastest.
+// thread = (target g, chain c), chains fastest: the 32 lanes of a warp read the same node (one broadcast load) and differ
+// in (b0, b1).  Two nodes per trip (two independent dependency chains), range check on the exponent bits.
 __global__ void __launch_bounds__(PF_THREADS)
-k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a) {
-  __shared__ MathTab tab;
-  load_mathtab(&tab, threadIdx.x, PF_THREADS);
+k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum) {
+  __shared__ double expT[64];
+  if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -187,22 +200,43 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a) {
   const double b0 = T.state[(size_t)a.b0_slot * T.C + c], b1 = T.state[(size_t)a.b1_slot * T.C + c];
   const nimb200_dep dp = T.deps[sp.dep_off + 1];
   Sel s = sel_of(T, dp, t);
-  double c0 = 0.0, c1 = 0.0;
-  bool exact = !(b0 == b0 && b1 == b1);
-  for (int k = s.lo; k < s.hi; k++) {
-    int node = s.idx ? s.idx[k] : k;
-    double eta = fma(b1, a.x[node], b0);
-    exact |= !(eta > -700.0 && eta < 700.0);
-    c0 += a.y[node];
-    c1 += exp_tab(fmin(fmax(eta, -700.0), 700.0), &tab);
+  double K[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
+  auto expf = [&](double eta, unsigned& worst) {  // exp_tab with the range check folded into a running maximum of |eta|'s high word
+    worst = max(worst, (unsigned)(__double2hiint(eta) & 0x7fffffff));
+    double tt = fma(eta, K[0], K[1]);
+    const int n = __double2loint(tt);
+    tt = tt - K[1];
+    double r = fma(tt, K[2], eta);
+    r = fma(tt, K[3], r);
+    double pl = fma(r, K[4], K[5]);
+    pl = fma(pl, r, K[6]);
+    pl = fma(pl, r, 0.5);
+    pl = fma(pl, r, 1.0);
+    const double Tj = expT[n & 63];
+    const double v = fma(Tj * r, pl, Tj);
+    return __hiloint2double(__double2hiint(v) + ((n >> 6) << 20), __double2loint(v));
+  };
+  double c1 = 0.0, c1b = 0.0;
+  unsigned worst = 0;
+  int k = s.lo;
+  for (; k + 1 < s.hi; k += 2) {
+    const int n0 = s.idx ? s.idx[k] : k, n1 = s.idx ? s.idx[k + 1] : k + 1;
+    const double x0 = a.x[n0], x1 = a.x[n1];
+    c1 += expf(fma(b1, x0, b0), worst);
+    c1b += expf(fma(b1, x1, b0), worst);
   }
-  if (exact) {  // overflowing / NaN linear predictor somewhere: redo with the library exp
+  if (k < s.hi) c1 += expf(fma(b1, a.x[s.idx ? s.idx[k] : k], b0), worst);
+  c1 += c1b;
+  if (worst >= 0x4085e000u) {  // |eta| >= 700 or NaN somewhere: redo with the library exp
     c1 = 0.0;
-    for (int k = s.lo; k < s.hi; k++) {
-      int node = s.idx ? s.idx[k] : k;
+    for (int kk = s.lo; kk < s.hi; kk++) {
+      int node = s.idx ? s.idx[kk] : kk;
       c1 += 1.0 * exp(b0 + b1 * a.x[node]);
     }
   }
+  const double c0 = ysum[t];
   const nimb200_dep tp = T.deps[sp.dep_off];
   int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
   double prior_shape = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
