@@ -18,7 +18,8 @@ namespace nimb {
 // exactly, which needs no reciprocal and no correction term (23 FP64 instructions instead of 35).  For a <= 6 the reference's own
 // value (p rounded, then log) and this one each carry <= 2e-16 absolute error on a result >= 2.5e-3 in magnitude, so they agree
 // to < 2e-13 relative; beyond 6 the rounding of p = fl(1/(1+e)) starts to matter (q = 1 - p loses bits, q == 0 from eta = 37) and
-// the general path below reproduces it step by step.  The choice is a warp vote, so the epilogue stays convergent.
+// the general path below reproduces it step by step.  The choice is a warp vote (VOTE), so the fused epilogue stays convergent;
+// callers whose lanes have already diverged (VOTE = false) choose per lane.
 //
 // W values are carried through every step together (statement-level interleaving): the dependent DFMA chains of
 // exp / reciprocal / log are long, and with 4 resident warps per scheduler the FP64 pipe only fills when each warp
@@ -46,11 +47,12 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
   }
   double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
   int n[W];
-  if (VOTE) {
+  {
     unsigned amax = 0;
 #pragma unroll
     for (int j = 0; j < W; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
-    if (__all_sync(0xffffffffu, amax < 0x40180000u)) {  // every |eta| < 6 (NaN fails the test)
+    const bool mod = amax < 0x40180000u;  // every |eta| < 6 (NaN fails the test)
+    if (VOTE ? __all_sync(0xffffffffu, mod) : mod) {
 #pragma unroll
       for (int j = 0; j < W; j++) x[j] = -fabs(eta[j]);
 #pragma unroll
