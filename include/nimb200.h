@@ -164,7 +164,8 @@ enum {
   NIMB_SAMPLER_RW_BLOCK = 2,   /* MCMC_samplers.R:643-810 */
   NIMB_SAMPLER_BINARY = 3,     /* MCMC_samplers.R:115-152 */
   NIMB_SAMPLER_CONJ_GAMMA = 4, /* dgamma prior; dpois / dgamma(rate) / dnorm(tau) dependents, MCMC_conjugacy.R:80-93 */
-  NIMB_SAMPLER_CONJ_NORMAL = 5 /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
+  NIMB_SAMPLER_CONJ_NORMAL = 5, /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
+  NIMB_SAMPLER_CONJ_BETA = 6    /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
 };
 
 typedef struct nimb200_sampler {
@@ -296,8 +297,8 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
 int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
                                              const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);
 
-/* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1) or gamma(shape a, scale 1)
- * variates (kind 2) that sampler `sampler` would consume on the device for (chain, iter, target), so the
+/* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1), gamma(shape a, scale 1)
+ * variates (kind 2) or beta(a, 1 + a/2) variates (kind 3) that sampler `sampler` would consume on the device for (chain, iter, target), so the
  * host can replay identical draws into another implementation. */
 int nimb200_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target,
                   int32_t kind, double a, int32_t n, double *out);

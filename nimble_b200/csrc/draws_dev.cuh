@@ -149,11 +149,11 @@ __device__ __forceinline__ void normal2(const DrawKey& k, uint32_t call, double&
 }
 
 // Marsaglia-Tsang gamma(a, 1): call 0 = boost uniform (a < 1), trip m: normal = call 1+2m, uniform = call 2+2m.
-__device__ __forceinline__ double rgamma1(const DrawKey& k, double a) {
+__device__ __forceinline__ double rgamma1(const DrawKey& k, double a, uint32_t base = 0) {
   double boost = 1.0, u, dummy, x, v;
   if (!(a > 0.0) || !isfinite(a)) return NAN;
   if (a < 1.0) {
-    unif2(k, 0, u, dummy);
+    unif2(k, base, u, dummy);
     boost = det_exp(__ddiv_rn(det_log(u), a));
     a = __dadd_rn(a, 1.0);
   }
@@ -161,11 +161,11 @@ __device__ __forceinline__ double rgamma1(const DrawKey& k, double a) {
   double c = __ddiv_rn(1.0 / 3.0, __dsqrt_rn(d));
   v = 1.0;
   for (int m = 0; m < 64; m++) {
-    normal2(k, 1 + 2 * m, x, dummy);
+    normal2(k, base + 1 + 2 * m, x, dummy);
     v = __dadd_rn(1.0, __dmul_rn(c, x));
     if (v <= 0.0) continue;
     v = __dmul_rn(__dmul_rn(v, v), v);
-    unif2(k, 2 + 2 * m, u, dummy);
+    unif2(k, base + 2 + 2 * m, u, dummy);
     double x2 = __dmul_rn(x, x);
     if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) break;
     double lhs = det_log(u);
@@ -173,6 +173,12 @@ __device__ __forceinline__ double rgamma1(const DrawKey& k, double a) {
     if (lhs < rhs) break;
   }
   return __dmul_rn(__dmul_rn(d, v), boost);
+}
+
+// beta(a, b) = X / (X + Y), X ~ gamma(a) on calls 0.., Y ~ gamma(b) on calls 256.. of the same counter
+__device__ __forceinline__ double rbeta1(const DrawKey& k, double a, double b) {
+  double x = rgamma1(k, a, 0), y = rgamma1(k, b, 256);
+  return __ddiv_rn(x, __dadd_rn(x, y));
 }
 
 }  // namespace nimb

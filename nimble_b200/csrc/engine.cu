@@ -219,17 +219,22 @@ __device__ __forceinline__ bool counts_here(const DevTab& T, int decl) { return 
 // conjugate contribution of one dependent node (P/R/MCMC_conjugacy.R:80-93, 109-115; probing :766-820)
 // the dependent's parameter that the posterior needs besides the linked one (tau | mean of dnorm, shape of dgamma);
 // *hoisted is set when its program does not depend on the node, so the caller may reuse the value
-__device__ __forceinline__ double conj_par(const DevTab& T, const nimb200_dep& dp, int node, int c, bool gam, bool* hoistable) {
+// conjugate kind: 0 = dnorm prior, 1 = dgamma prior, 2 = dbeta prior
+__host__ __device__ __forceinline__ int conj_kind(int sampler_type) {
+  return sampler_type == NIMB_SAMPLER_CONJ_GAMMA ? 1 : (sampler_type == NIMB_SAMPLER_CONJ_BETA ? 2 : 0);
+}
+__device__ __forceinline__ double conj_par(const DevTab& T, const nimb200_dep& dp, int node, int c, int gam, bool* hoistable) {
   const nimb200_decl& dd = T.decl[dp.decl];
+  if (dd.dist == NIMB_DBINOM) { *hoistable = T.pconst[3 * dp.decl] != 0; return get_param(T, dp.decl, node, c, 0, -1, 0.0); }  // size
   if (dd.dist == NIMB_DNORM) {
-    *hoistable = T.pconst[3 * dp.decl + (gam ? 0 : 1)] != 0;
-    return gam ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
+    *hoistable = T.pconst[3 * dp.decl + (gam == 1 ? 0 : 1)] != 0;
+    return gam == 1 ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
   }
   if (dd.dist == NIMB_DGAMMA) { *hoistable = T.pconst[3 * dp.decl] != 0; return get_param(T, dp.decl, node, c, 0, -1, 0.0); }
   *hoistable = true;
   return 0.0;
 }
-__device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep& dp, int node, int c, int slot, bool gam,
+__device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep& dp, int node, int c, int slot, int gam,
                                              double& c0, double& c1, bool have_par = false, double par_in = 0.0) {
   const nimb200_decl& dd = T.decl[dp.decl];
   double value = node_value(T, dd, node, c, -1, 0.0);
@@ -239,7 +244,9 @@ __device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep&
   if (dp.link == NIMB_LINK_ADDITIVE || dp.link == NIMB_LINK_LINEAR) offset = get_param(T, dp.decl, node, c, dp.param, slot, 0.0);
   if (dp.link == NIMB_LINK_LINEAR) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0) - offset;
   if (dp.link == NIMB_LINK_MULTIPLICATIVE) coeff = get_param(T, dp.decl, node, c, dp.param, slot, 1.0);
-  if (gam) {
+  if (gam == 2) {  // MCMC_conjugacy.R:4-8: dbern (value, 1 - value), dbin (value, size - value)
+    c0 += value; c1 += par - value;
+  } else if (gam == 1) {
     if (dd.dist == NIMB_DPOIS) { c0 += value; c1 += coeff; }
     else if (dd.dist == NIMB_DGAMMA) { c0 += par; c1 += coeff * value; }
     else if (dd.dist == NIMB_DEXP) { c0 += 1.0; c1 += coeff * value; }
@@ -403,7 +410,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
     return;
   }
   // conjugate: MCMC_conjugacy.R:651-692
-  bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  const int gam = conj_kind(sp.type);
   if (PHASE != 2) {
     for (int e = 0; e < sp.n_dep; e++) {
       const nimb200_dep dp = T.deps[sp.dep_off + e];
@@ -432,9 +439,11 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   const nimb200_dep tp = T.deps[sp.dep_off];
   int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
   double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
-  double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
+  double prior1 = get_param(T, tp.decl, tnode, c, gam == 2 ? 1 : (gam == 1 ? NIMB_PARAM_RATE : NIMB_PARAM_TAU), -1, 0.0);
   double nv;
-  if (gam) {
+  if (gam == 2) {
+    nv = rbeta1(key, prior0 + v0, prior1 + v1);
+  } else if (gam == 1) {
     double shape = prior0 + v0, scale = 1 / (prior1 + v1);
     nv = rgamma1(key, shape) * scale;
   } else {
@@ -464,7 +473,7 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
     if (MODE != 2) H = make_hoist(T, di, c, -1, 0.0);
     bool hp = false;
     double par = 0.0;
-    if (MODE == 2) par = conj_par(T, dp, 0, c, gam != 0, &hp);
+    if (MODE == 2) par = conj_par(T, dp, 0, c, gam, &hp);
     for (int q = 0; q < npt; q++) {
       int k = tile0 + q * nl + lane_n;
       if (k >= hi) break;
@@ -472,7 +481,7 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
       if (idx && (node < T.shard_lo[di] || node >= T.shard_hi[di])) continue;
       if (MODE == 0) a0 += calc_node_h(T, di, node, c, -1, 0.0, H);
       else if (MODE == 1) out_nodes[(size_t)(k - lo) * T.C + c] = calc_node_h(T, di, node, c, -1, 0.0, H);
-      else conj_contrib(T, dp, node, c, slot, gam != 0, a0, a1, hp, par);
+      else conj_contrib(T, dp, node, c, slot, gam, a0, a1, hp, par);
     }
   }
   if (MODE == 1) return;
@@ -651,12 +660,12 @@ __global__ void k_conj_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, c
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_sampler sp = T.samplers[sid];
-  bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  const int gam = conj_kind(sp.type);
   DrawKey key = make_key(T, seed, iter, sid, 0, c);
   const nimb200_dep tp = T.deps[sp.dep_off];
   int tnode = tp.a;  // stage-0 entry of a single-target sampler: RANGE(node, node+1)
   double prior0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
-  double prior1 = get_param(T, tp.decl, tnode, c, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU, -1, 0.0);
+  double prior1 = get_param(T, tp.decl, tnode, c, gam == 2 ? 1 : (gam == 1 ? NIMB_PARAM_RATE : NIMB_PARAM_TAU), -1, 0.0);
   double c0 = 0, c1 = 0;
   for (int e = 0; e < sp.n_dep; e++) {
     if (T.deps[sp.dep_off + e].stage != 1) continue;
@@ -664,7 +673,9 @@ __global__ void k_conj_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, c
     c1 += contrib[((size_t)e * 2 + 1) * T.C + c];
   }
   double nv;
-  if (gam) {
+  if (gam == 2) {
+    nv = rbeta1(key, prior0 + c0, prior1 + c1);
+  } else if (gam == 1) {
     double shape = prior0 + c0, scale = 1 / (prior1 + c1);
     nv = rgamma1(key, shape) * scale;
   } else {
@@ -765,7 +776,8 @@ __global__ void k_draws(uint64_t seed, int chain, uint64_t iter, int sampler, in
   double x0, x1;
   if (kind == 0) { normal2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
   else if (kind == 1) { unif2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
-  else { key.target = (uint32_t)(target + k); out[k] = rgamma1(key, a); }
+  else if (kind == 2) { key.target = (uint32_t)(target + k); out[k] = rgamma1(key, a); }
+  else { key.target = (uint32_t)(target + k); out[k] = rbeta1(key, a, 1.0 + 0.5 * a); }
 }
 
 // ------------------------------------------------------------------------------------------------ host model
@@ -1133,8 +1145,8 @@ static int validate_table(const nimb200_table* t) {
   }
   for (int s = 0; s < t->n_samplers; s++) {
     const nimb200_sampler& sp = t->samplers[s];
-    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_CONJ_NORMAL)
-      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm); there is no CPU fallback");
+    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_CONJ_BETA)
+      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta); there is no CPU fallback");
     if (sp.type == NIMB_SAMPLER_RW_BLOCK && (sp.d < 1 || sp.d > NIMB200_MAX_BLOCK_D)) return fail("RW_block dimension out of range");
     if (sp.dep_off < 0 || sp.dep_off + sp.n_dep > t->n_deps || sp.n_dep < 1) return fail("sampler dependency range outside deps[]");
     if (t->deps[sp.dep_off].stage != 0) return fail("first dependency entry of a sampler must be the target's own declaration");
@@ -1478,7 +1490,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     std::set<int> touched, own, inval;
-    bool keeps_own = m->wide[s] && sp.type != NIMB_SAMPLER_CONJ_GAMMA && sp.type != NIMB_SAMPLER_CONJ_NORMAL;
+    bool keeps_own = m->wide[s] && sp.type != NIMB_SAMPLER_CONJ_GAMMA && sp.type != NIMB_SAMPLER_CONJ_NORMAL && sp.type != NIMB_SAMPLER_CONJ_BETA;
     for (int e = 0; e < sp.n_dep; e++) {
       touched.insert(m->deps[sp.dep_off + e].decl);
       if (keeps_own) own.insert(m->dep_slot[sp.dep_off + e]);
@@ -1742,14 +1754,14 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       else k_sweep<0, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
       m->launches++;
     }
-  } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL) {
-    bool gam = sp.type == NIMB_SAMPLER_CONJ_GAMMA;
+  } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL || sp.type == NIMB_SAMPLER_CONJ_BETA) {
+    const int gam = conj_kind(sp.type);
     for (int e = 0; e < sp.n_dep; e++) {
       const nimb200_dep& dp = m->deps[sp.dep_off + e];
       if (dp.stage != 1) continue;
       HostSel hs = host_sel(m, dp, m->h_iarr);
       if (launch_eval_sum(m, 2, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + ((size_t)e * 2) * C, m->d_newsum + ((size_t)e * 2 + 1) * C,
-                          &dp, sp.target_slot, gam ? 1 : 0)) return 1;
+                          &dp, sp.target_slot, gam)) return 1;
     }
     k_conj_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->d_newsum);
     m->launches++;

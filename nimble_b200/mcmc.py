@@ -64,9 +64,10 @@ def _link_code(f):
 
 def check_conjugacy(model, decl):
     """Returns (sampler type, {dependent decl index: (link, param code)}) or None.
-    Relationship table: P/R/MCMC_conjugacy.R:80-93 (dgamma prior), :109-115 (dnorm prior)."""
+    Relationship table: P/R/MCMC_conjugacy.R:4-15 (dbeta prior: dbern / dbin dependents, identity link),
+    :80-93 (dgamma prior), :109-115 (dnorm prior)."""
     var = decl.var
-    if decl.dist not in (T.DGAMMA, T.DNORM):
+    if decl.dist not in (T.DGAMMA, T.DNORM, T.DBETA):
         return None
     if any(v == var for v, _ in decl.reads()):
         return None
@@ -78,7 +79,15 @@ def check_conjugacy(model, decl):
 
         def only_in(name_):
             return name_ in bp and all(not tree_reads_var(t, var) for k, t in bp.items() if k != name_)
-        if decl.dist == T.DGAMMA:
+        if decl.dist == T.DBETA:
+            if dep.dist == T.DBINOM and only_in("prob"):
+                pname, code = "prob", 1
+            else:
+                return None
+            f = _linear_form(bp[pname], var)
+            if f in (None, "free") or f[0] or f[1]:  # beta prior: identity link only
+                return None
+        elif decl.dist == T.DGAMMA:
             if dep.dist == T.DPOIS and only_in("lambda"):
                 pname, code = "lambda", 0
             elif dep.dist == T.DGAMMA and only_in("rate"):
@@ -103,7 +112,8 @@ def check_conjugacy(model, decl):
         info[dep.index] = (_link_code(f), code)
     if not info:
         return None
-    return (T.SAMPLER_CONJ_GAMMA if decl.dist == T.DGAMMA else T.SAMPLER_CONJ_NORMAL), info
+    kind = {T.DGAMMA: T.SAMPLER_CONJ_GAMMA, T.DNORM: T.SAMPLER_CONJ_NORMAL, T.DBETA: T.SAMPLER_CONJ_BETA}[decl.dist]
+    return kind, info
 
 
 # ----------------------------------------------------------------------------- configuration

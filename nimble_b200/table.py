@@ -26,9 +26,10 @@ FAM_GENERIC, FAM_BERN_LOGIT_INPROD, FAM_POIS_LOGLIN, FAM_NORM_GATHER, FAM_BERN_L
 SEL_ALL, SEL_SAME, SEL_STRIDE, SEL_SEG, SEL_CSR, SEL_RANGE = 0, 1, 2, 3, 4, 5
 PARAM_RATE, PARAM_TAU = 16, 17
 LINK_IDENTITY, LINK_ADDITIVE, LINK_MULTIPLICATIVE, LINK_LINEAR = 0, 1, 2, 3
-SAMPLER_RW, SAMPLER_RW_BLOCK, SAMPLER_BINARY, SAMPLER_CONJ_GAMMA, SAMPLER_CONJ_NORMAL = 1, 2, 3, 4, 5
+SAMPLER_RW, SAMPLER_RW_BLOCK, SAMPLER_BINARY, SAMPLER_CONJ_GAMMA, SAMPLER_CONJ_NORMAL, SAMPLER_CONJ_BETA = 1, 2, 3, 4, 5, 6
 SAMPLER_NAMES = {SAMPLER_RW: "RW", SAMPLER_RW_BLOCK: "RW_block", SAMPLER_BINARY: "binary",
-                 SAMPLER_CONJ_GAMMA: "conjugate_dgamma", SAMPLER_CONJ_NORMAL: "conjugate_dnorm"}
+                 SAMPLER_CONJ_GAMMA: "conjugate_dgamma", SAMPLER_CONJ_NORMAL: "conjugate_dnorm",
+                 SAMPLER_CONJ_BETA: "conjugate_dbeta"}
 
 
 class Op(C.Structure):

@@ -152,11 +152,20 @@ void ref_normal2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler,
 /* Marsaglia-Tsang gamma(a, 1) on the counter stream: call k=0 is the boost uniform (a<1),
  * trip m uses call 1+2m for the normal and 2+2m for the uniform. */
 double ref_rgamma(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a) {
+  return ref_rgamma_at(seed, chain, iter, sampler, target, 0, a);
+}
+/* beta(a, b) = X / (X + Y), X ~ gamma(a) on calls 0.., Y ~ gamma(b) on calls 256.. of the same counter */
+double ref_rbeta(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a, double b) {
+  double x = ref_rgamma_at(seed, chain, iter, sampler, target, 0, a);
+  double y = ref_rgamma_at(seed, chain, iter, sampler, target, 256, b);
+  return x / (x + y);
+}
+double ref_rgamma_at(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t base, double a) {
   double boost = 1.0, d, c, x, v, u, x2, dummy, lhs, rhs;
   int m;
   if (!(a > 0.0) || !isfinite(a)) return NAN;
   if (a < 1.0) {
-    ref_unif2(seed, chain, iter, sampler, target, 0, &u, &dummy);
+    ref_unif2(seed, chain, iter, sampler, target, base, &u, &dummy);
     boost = ref_det_exp(ref_det_log(u) / a);
     a = a + 1.0;
   }
@@ -164,11 +173,11 @@ double ref_rgamma(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler
   c = (1.0 / 3.0) / sqrt(d);
   v = 1.0;
   for (m = 0; m < 64; m++) {
-    ref_normal2(seed, chain, iter, sampler, target, 1 + 2 * m, &x, &dummy);
+    ref_normal2(seed, chain, iter, sampler, target, base + 1 + 2 * m, &x, &dummy);
     v = 1.0 + c * x;
     if (v <= 0.0) continue;
     v = v * v * v;
-    ref_unif2(seed, chain, iter, sampler, target, 2 + 2 * m, &u, &dummy);
+    ref_unif2(seed, chain, iter, sampler, target, base + 2 + 2 * m, &u, &dummy);
     x2 = x * x;
     if (u < 1.0 - (0.0331 * x2) * x2) break;
     lhs = ref_det_log(u);

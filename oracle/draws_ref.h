@@ -10,6 +10,8 @@ void ref_unif2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, u
 void ref_normal2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t k,
                  double *z0, double *z1);
 double ref_rgamma(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a);
+double ref_rgamma_at(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t base, double a);
+double ref_rbeta(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a, double b);
 double ref_det_log(double x);
 double ref_det_exp(double x);
 #ifdef __cplusplus

@@ -412,9 +412,9 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
   int slot = sp->target_slot + t, q, pass;
   const nimb200_dep *tp = m->t.deps + sp->dep_off; /* stage-0 entry: the target's own declaration */
   int tnode = sel_of(m, tp, t).lo;
-  int gam = sp->type == NIMB_SAMPLER_CONJ_GAMMA;
-  double prior0 = get_param(m, st, tp->decl, tnode, 0);                                    /* prior_shape | prior_mean */
-  double prior1 = get_param(m, st, tp->decl, tnode, gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU); /* prior_rate | prior_tau */
+  int gam = sp->type == NIMB_SAMPLER_CONJ_GAMMA, bet = sp->type == NIMB_SAMPLER_CONJ_BETA;
+  double prior0 = get_param(m, st, tp->decl, tnode, 0);                                    /* prior_shape | prior_mean | prior_shape1 */
+  double prior1 = get_param(m, st, tp->decl, tnode, bet ? 1 : (gam ? NIMB_PARAM_RATE : NIMB_PARAM_TAU)); /* prior_rate | prior_tau | prior_shape2 */
   double contrib0 = 0, contrib1 = 0, saved_target = st[slot], newValue;
   /* count dependents to size the dep_* work arrays the generated code keeps */
   int ndeps = 0;
@@ -429,6 +429,7 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
        dgamma dependents need shape; dpois none */
     if (dd->dist == NIMB_DNORM) dpar[q] = gam ? get_param(m, st, di, node, 0) : get_param(m, st, di, node, NIMB_PARAM_TAU);
     else if (dd->dist == NIMB_DGAMMA) dpar[q] = get_param(m, st, di, node, 0);
+    else if (dd->dist == NIMB_DBINOM) dpar[q] = get_param(m, st, di, node, 0); /* size (1 for dbern) */
     else dpar[q] = 0;
     doff[q] = 0; dcoef[q] = 1;
     q++;
@@ -456,9 +457,12 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
   FOR_DEP_NODES(m, sp, t, 1, {
     const nimb200_decl *dd = m->t.decl + di;
     double value = dval[q], coeff = dcoef[q], offset = doff[q];
-    if (gam) { /* MCMC_conjugacy.R:80-93 */
+    if (bet) { /* MCMC_conjugacy.R:4-8: dbern value, 1 - value; dbin value, size - value */
+      contrib0 += value; contrib1 += dpar[q] - value;
+    } else if (gam) { /* MCMC_conjugacy.R:80-93 */
       if (dd->dist == NIMB_DPOIS) { contrib0 += value; contrib1 += coeff; }
       else if (dd->dist == NIMB_DGAMMA) { contrib0 += dpar[q]; contrib1 += coeff * value; }
+      else if (dd->dist == NIMB_DEXP) { contrib0 += 1; contrib1 += coeff * value; }
       else if (dd->dist == NIMB_DNORM) { contrib0 += 1. / 2; contrib1 += coeff / 2 * ((value - dpar[q]) * (value - dpar[q])); }
     } else { /* :109-115 */
       double tau = dpar[q];
@@ -469,7 +473,9 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
   });
   free(work);
   (void)saved_target;
-  if (gam) {
+  if (bet) {
+    newValue = ref_rbeta(seed, (uint32_t)(m->first_chain + c), iter, sid, t, prior0 + contrib0, prior1 + contrib1);
+  } else if (gam) {
     double shape = prior0 + contrib0, scale = 1 / (prior1 + contrib1);
     newValue = ref_rgamma(seed, (uint32_t)(m->first_chain + c), iter, sid, t, shape) * scale;
   } else {
@@ -666,7 +672,8 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
           case NIMB_SAMPLER_RW_BLOCK: run_RW_block(m, c, s, seed, git); break;
           case NIMB_SAMPLER_BINARY: for (t = 0; t < sp->n_targets; t++) run_binary(m, c, s, t, seed, git); break;
           case NIMB_SAMPLER_CONJ_GAMMA:
-          case NIMB_SAMPLER_CONJ_NORMAL: for (t = 0; t < sp->n_targets; t++) run_conjugate(m, c, s, t, seed, git); break;
+          case NIMB_SAMPLER_CONJ_NORMAL:
+          case NIMB_SAMPLER_CONJ_BETA: for (t = 0; t < sp->n_targets; t++) run_conjugate(m, c, s, t, seed, git); break;
           default: return fail("unknown sampler type");
         }
       }
@@ -741,7 +748,8 @@ int ref_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32
     double x0, x1;
     if (kind == 0) { ref_normal2(seed, chain, iter, sampler, target, k / 2, &x0, &x1); out[k] = (k & 1) ? x1 : x0; }
     else if (kind == 1) { ref_unif2(seed, chain, iter, sampler, target, k / 2, &x0, &x1); out[k] = (k & 1) ? x1 : x0; }
-    else out[k] = ref_rgamma(seed, chain, iter, sampler, target + k, a);
+    else if (kind == 2) out[k] = ref_rgamma(seed, chain, iter, sampler, target + k, a);
+    else out[k] = ref_rbeta(seed, chain, iter, sampler, target + k, a, 1.0 + 0.5 * a);
   }
   return 0;
 }

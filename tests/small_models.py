@@ -97,6 +97,32 @@ def all_dists():
     return m, nb.configureMCMC(m, useConjugacy=False)
 
 
+def beta_binomial():
+    """dbeta prior with dbern and dbin dependents (identity link), MCMC_conjugacy.R:4-15; test-mcmc.R:400-447 uses the same
+    relationship.  Posterior p ~ Beta(2 + sum y + sum z, 3 + sum(n - y) + sum(1 - z)): every iteration is an exact draw."""
+    rng = np.random.default_rng(12)
+    n = rng.integers(1, 9, 7).astype(float)
+    y = rng.binomial(n.astype(int), 0.3).astype(float)
+    z = (rng.random(5) < 0.3).astype(float)
+    code = """{ p ~ dbeta(2, 3)
+      for (i in 1:7) { y[i] ~ dbin(p, n[i]) }
+      for (j in 1:5) { z[j] ~ dbern(p) } }"""
+    m = nb.nimbleModel(code, constants={"n": n}, data={"y": y, "z": z}, inits={"p": 0.5})
+    post = (2 + y.sum() + z.sum(), 3 + (n - y).sum() + (1 - z).sum())
+    return m, nb.configureMCMC(m), post
+
+
+def gamma_exponential():
+    """dgamma prior on the rate of dexp dependents, multiplicative link (MCMC_conjugacy.R:89): posterior
+    lam ~ Gamma(2 + n, rate 1 + sum(c_i t_i))."""
+    rng = np.random.default_rng(13)
+    c = 0.5 + rng.random(9)
+    t = rng.exponential(0.7, 9)
+    code = "{ lam ~ dgamma(2, 1)\n for (i in 1:9) { t[i] ~ dexp(c[i] * lam) } }"
+    m = nb.nimbleModel(code, constants={"c": c}, data={"t": t}, inits={"lam": 1.0})
+    return m, nb.configureMCMC(m), (2 + 9, 1 + float((c * t).sum()))
+
+
 def random_inits(model, nchains, seed, spread=0.3):
     """Positive, chain-specific perturbations of the model's inits (works for the models above)."""
     rng = np.random.default_rng(seed)

@@ -11,6 +11,11 @@ def test_oracle_draw_moments(oracle):
     for a in (0.3, 1.0, 2.5, 40.0):
         g = oracle.draws(7, 3, 11, 2, 0, 2, a, 100000)
         assert abs(g.mean() - a) < 0.03 * max(1, a) and abs(g.var() - a) < 0.08 * max(1, a)
+    for a in (0.3, 6.5):  # kind 3: beta(a, 1 + a/2)
+        b = 1.0 + 0.5 * a
+        x = oracle.draws(7, 3, 11, 2, 0, 3, a, 100000)
+        assert 0 < x.min() and x.max() < 1
+        assert abs(x.mean() - a / (a + b)) < 0.005 and abs(x.var() - a * b / ((a + b) ** 2 * (a + b + 1))) < 0.003
 
 
 def test_oracle_streams_are_keyed(oracle):
@@ -34,7 +39,7 @@ def test_oracle_det_math(oracle):
 
 @pytest.mark.gpu
 def test_device_draws_bit_identical(oracle, b200):
-    for kind, a in ((0, 0.0), (1, 0.0), (2, 0.4), (2, 1.0), (2, 17.3)):
+    for kind, a in ((0, 0.0), (1, 0.0), (2, 0.4), (2, 1.0), (2, 17.3), (3, 0.3), (3, 6.5)):
         for key in ((5, 0, 1, 0, 0), (2 ** 40 + 9, 1023, 4999, 3, 77)):
             d = b200.draws(*key, kind, a, 4096)
             r = oracle.draws(*key, kind, a, 4096)

@@ -144,3 +144,30 @@ def test_degenerate_run_lengths(oracle, b200):
                     (dict(niter=5, nburnin=6), "nburnin > niter"), (dict(niter=5, thin=0), "thin < 1")):
         with pytest.raises(ValueError, match=msg):
             cg.run_chains(init, **kw)
+
+
+@pytest.mark.parametrize("nchains", [3, 40])
+def test_beta_and_gamma_exponential_conjugacy_match_oracle(oracle, b200, nchains):
+    """dbeta prior with dbern / dbin dependents and dgamma prior with dexp dependents: draws bit-compatible with the oracle
+    (two Marsaglia-Tsang gammas on disjoint call ranges of the same counter for the beta variate)."""
+    for build in (sm.beta_binomial, sm.gamma_exponential):
+        m, conf, _ = build()
+        inits = np.tile(m.init_vector(), (nchains, 1))
+        so, sg = run(compile_on(oracle, conf), inits, 300, 0, seed=8), run(compile_on(b200, conf), inits, 300, 0, seed=8)
+        assert rel_err(sg, so).max() < RTOL_TRAJ
+        assert len(np.unique(so[:, :, 0])) == so[:, :, 0].size
+
+
+def test_beta_conjugacy_wide_path(oracle, b200):
+    """One beta target with more dependents than a sweep thread takes (> 2048): contributions by k_eval<2> + k_conj_finish."""
+    rng = np.random.default_rng(5)
+    N = 5000
+    z = (rng.random(N) < 0.37).astype(float)
+    m = nb.nimbleModel("{ p ~ dbeta(1.5, 2.5)\n for (i in 1:N) { z[i] ~ dbern(p) } }", constants={"N": N}, data={"z": z},
+                       inits={"p": 0.5})
+    conf = nb.configureMCMC(m)
+    assert conf.samplerConfs[0].type == T.SAMPLER_CONJ_BETA
+    inits = np.tile(m.init_vector(), (6, 1))
+    so, sg = run(compile_on(oracle, conf), inits, 120, 0, seed=2), run(compile_on(b200, conf), inits, 120, 0, seed=2)
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert abs(so.mean() - (1.5 + z.sum()) / (4.0 + N)) < 0.002

@@ -115,3 +115,21 @@ def test_run_argument_errors(oracle):
                     (dict(niter=5, nburnin=6), "nburnin > niter"), (dict(niter=5, thin=0), "thin < 1")):
         with pytest.raises(ValueError, match=msg):
             cm.run_chains(init, **kw)
+
+
+def test_beta_binomial_and_gamma_exponential_conjugacy(oracle):
+    """Conjugate relationships beyond the two north_star names: every iteration is an exact posterior draw."""
+    from nimble_b200 import table as T
+    m, conf, (a, b) = sm.beta_binomial()
+    assert [s.type for s in conf.samplerConfs] == [T.SAMPLER_CONJ_BETA] and conf.samplerConfs[0].name == "conjugate_dbeta"
+    s = pooled(run(compile_on(oracle, conf), np.tile(m.init_vector(), (4, 1)), 5000, 0, seed=3))[:, 0]
+    mean, var = a / (a + b), a * b / ((a + b) ** 2 * (a + b + 1))
+    assert abs(s.mean() - mean) < 4 * np.sqrt(var / s.size) and abs(s.var() - var) < 0.05 * var
+    m, conf, (shape, rate) = sm.gamma_exponential()
+    assert [s.type for s in conf.samplerConfs] == [T.SAMPLER_CONJ_GAMMA]
+    s = pooled(run(compile_on(oracle, conf), np.tile(m.init_vector(), (4, 1)), 5000, 0, seed=4))[:, 0]
+    assert abs(s.mean() - shape / rate) < 4 * np.sqrt(shape / rate ** 2 / s.size)
+    assert abs(s.var() - shape / rate ** 2) < 0.06 * shape / rate ** 2
+    # a beta prior seen through anything but the identity link is not conjugate (falls back to RW)
+    m2 = nb.nimbleModel("{ p ~ dbeta(1, 1)\n y ~ dbin(0.5 * p, 10) }", data={"y": 3.0}, inits={"p": 0.5})
+    assert [s.type for s in nb.configureMCMC(m2).samplerConfs] == [T.SAMPLER_RW]
