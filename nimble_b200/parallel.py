@@ -56,3 +56,46 @@ def run_chain_sharded(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=N
     if rank != 0:
         return None
     return np.concatenate([g for g in gathered if g.shape[0] > 0], axis=0)
+
+
+def hybrid_layout(rank, world, data_shards):
+    """(chain group, shard index, number of chain groups) of `rank` in a chain-groups x data-shards layout: the ranks of
+    one chain group are consecutive, so on one NVSwitch box a group's all-reduce stays among neighbours."""
+    if data_shards < 1 or world % data_shards:
+        raise ValueError("world size %d is not a multiple of data_shards %d" % (world, data_shards))
+    return rank // data_shards, rank % data_shards, world // data_shards
+
+
+def run_hybrid(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, seed=0, data_shards=1, min_nodes=1 << 16):
+    """Chain groups x data shards (third row): the world is cut into world/data_shards chain groups; group g
+    owns chains chain_range(nchains, g, groups) and its data_shards ranks each hold a slice of every large data declaration,
+    all-reducing block sums inside the group only (one NCCL communicator per group, created inside the device library).
+    data_shards = 1 is plain chain sharding, data_shards = world plain data sharding.
+
+    mcmc_factory(first_chain, device_index) as for run_chain_sharded.  Returns on rank 0 the samples of all chains in global
+    chain order (None elsewhere)."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    g, shard, groups = hybrid_layout(rank, world, data_shards)
+    lo, hi = chain_range(nchains, g, groups)
+    if hi == lo:
+        raise ValueError("fewer chains (%d) than chain groups (%d)" % (nchains, groups))
+    local_dev = rank % max(1, torch.cuda.device_count())
+    cm = mcmc_factory(lo, local_dev)
+    rows = []
+    for c in range(lo, hi):
+        these = inits[c] if isinstance(inits, (list, tuple)) else inits
+        rows.append(cm.model.init_vector(these))
+    if data_shards > 1:
+        # every group leader makes an id; all ids travel in one collective and each rank picks its group's
+        ids = [None] * world
+        dist.all_gather_object(ids, cm.backend.nccl_unique_id() if shard == 0 else None)
+        dm = cm._ensure(hi - lo)
+        dm.enable_data_sharding(data_shards, shard, ids[g * data_shards], min_nodes=min_nodes)
+    local = cm.run_chains(np.stack(rows), niter, nburnin, thin, True, seed)
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(local if shard == 0 else None, gathered, dst=0)
+    if rank != 0:
+        return None
+    return np.concatenate([x for x in gathered if x is not None], axis=0)

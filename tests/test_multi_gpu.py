@@ -56,3 +56,48 @@ def test_data_sharded_run_matches_single_gpu(tmp_path, name):
     assert np.array_equal(r0, r1)                    # every rank took identical decisions
     err = np.abs(r0 - single) / np.maximum(1.0, np.abs(single))
     assert err.max() < 1e-9, err.max()               # same chains as the unsharded run (summation order differs)
+
+
+def _hybrid_worker(rank, world, port, name, data_shards, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import nimble_b200 as nb
+    from nimble_b200 import _capi, parallel
+    from tests import small_models as sm
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    backend = _capi.default_backend()
+    m, conf = sm.SMALL[name]()
+    C = 6
+    inits = sm.random_inits(m, C, 23, 0.1)
+
+    def factory(first_chain, dev):
+        return nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=dev, first_chain=first_chain)
+
+    # run_hybrid flattens per-chain inits through model.init_vector: let ready-made state vectors pass through
+    orig = m.init_vector
+    m.init_vector = lambda these=None: orig() if these is None else np.asarray(these, dtype=np.float64)
+    s = parallel.run_hybrid(factory, 200, 10, 1, nchains=C, inits=[inits[c] for c in range(C)], seed=19,
+                            data_shards=data_shards, min_nodes=256)
+    if rank == 0:
+        np.save(os.path.join(out_dir, "hybrid.npy"), s)
+        ref = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=0)
+        np.save(os.path.join(out_dir, "single.npy"), ref.run_chains(inits, 200, 10, 1, True, 19))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,data_shards", [(2, 1), (2, 2), (4, 2)])
+def test_hybrid_chain_groups_times_data_shards(tmp_path, world, data_shards):
+    """SURVEY.md 8e third row: chain groups x data shards, one NCCL communicator per group; (2,1) is plain chain sharding,
+    (2,2) plain data sharding, (4,2) two groups of two shards."""
+    if _ngpu() < world:
+        pytest.skip("needs %d GPUs" % world)
+    import torch.multiprocessing as mp
+    port = 29600 + (os.getpid() + 7 * world + data_shards) % 2000
+    mp.spawn(_hybrid_worker, args=(world, port, "lmm", data_shards, str(tmp_path)), nprocs=world, join=True)
+    h, single = np.load(tmp_path / "hybrid.npy"), np.load(tmp_path / "single.npy")
+    assert h.shape == single.shape
+    err = np.abs(h - single) / np.maximum(1.0, np.abs(single))
+    assert err.max() < 1e-9, err.max()

@@ -31,6 +31,15 @@ def _worker(rank, world, port, out_path):
     dist.destroy_process_group()
 
 
+def test_hybrid_layout():
+    from nimble_b200.parallel import hybrid_layout
+    assert [hybrid_layout(r, 8, 4) for r in range(8)] == [(0, 0, 2), (0, 1, 2), (0, 2, 2), (0, 3, 2), (1, 0, 2), (1, 1, 2),
+                                                          (1, 2, 2), (1, 3, 2)]
+    assert hybrid_layout(3, 4, 1) == (3, 0, 4) and hybrid_layout(3, 4, 4) == (0, 3, 1)
+    with pytest.raises(ValueError):
+        hybrid_layout(0, 6, 4)
+
+
 def test_chain_ranges_cover_everything():
     from nimble_b200.parallel import chain_range, node_range
     for n, w in ((5, 2), (1024, 8), (3, 4), (7, 7)):
