@@ -1723,17 +1723,28 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     size_t total = (size_t)sp.n_targets * C;
     k_norm_conj_draw<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, na, m->d_norm_gs[s]);
     m->launches++;
-  } else if (!m->wide[s] && m->pois_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+  } else if (!m->wide[s] && m->pois_sweep[s]) {
     size_t total = (size_t)sp.n_targets * C;
+    const bool sh = m->nranks > 1 && m->sweep_sharded[s];
     PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
     if (!m->pois_ysum_valid[s]) {
       k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s]);
       m->launches++;
+      if (sh && m->nccl_comm && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets)) return 1;
       m->pois_ysum_valid[s] = 1;
     }
-    k_pois_conj_sweep<<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa,
-                                                                                                     m->d_pois_ysum[s]);
-    m->launches++;
+    const unsigned nb = (unsigned)((total + PF_THREADS - 1) / PF_THREADS);
+    if (!sh) {
+      k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr);
+      m->launches++;
+    } else {  // data-sharded: this rank's share of every (target, chain) rate contribution -> all-reduce -> draws
+      if (total > m->sweepbuf_cap) return fail("internal: sweep buffer too small (poisson)");
+      k_pois_conj_sweep<1><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf);
+      m->launches++;
+      if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, total)) return 1;
+      k_pois_conj_sweep<2><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf);
+      m->launches++;
+    }
   } else if (!m->wide[s]) {
     size_t total = (size_t)sp.n_targets * C;
     // few (target, chain) pairs with many dependents each: a warp per pair

@@ -186,8 +186,11 @@ __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, double* __restr
 // contribution_rate = coeff, coeff = the dependent's lambda with the target set to 1 = exp(b0 + b1 x)).
 // thread = (target g, chain c), chains fastest: the 32 lanes of a warp read the same node (one broadcast load) and differ
 // in (b0, b1).  Two nodes per trip (two independent dependency chains), range check on the exponent bits.
+// PHASE 0: whole update.  Data-sharded runs: PHASE 1 leaves this rank's share of the rate contribution in part[t][c]
+// (sel_of clamps the target's nodes to the rank's slice), the caller all-reduces it, PHASE 2 draws from the reduced sums.
+template <int PHASE>
 __global__ void __launch_bounds__(PF_THREADS)
-k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum) {
+k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part) {
   __shared__ double expT[64];
   if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
   __syncthreads();
@@ -221,6 +224,7 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   double c1 = 0.0, c1b = 0.0;
   unsigned worst = 0;
   int k = s.lo;
+  if (PHASE == 2) { k = s.hi; c1 = part[(size_t)t * T.C + c]; }
   for (; k + 1 < s.hi; k += 2) {
     const int n0 = s.idx ? s.idx[k] : k, n1 = s.idx ? s.idx[k + 1] : k + 1;
     const double x0 = a.x[n0], x1 = a.x[n1];
@@ -236,6 +240,7 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
       c1 += 1.0 * exp(b0 + b1 * a.x[node]);
     }
   }
+  if (PHASE == 1) { part[(size_t)t * T.C + c] = c1; return; }
   const double c0 = ysum[t];
   const nimb200_dep tp = T.deps[sp.dep_off];
   int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
