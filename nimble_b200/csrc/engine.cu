@@ -739,15 +739,21 @@ __global__ void k_monitor(DevTab T, const int32_t* mon, int nmon, double* row /*
 
 // graph-replayable form: decides from the device iteration counter whether this iteration is saved and where
 // (iteration it = ctr[0] - iter0 of this run; rows_before rows were already in the buffer)
+// The last block to finish also advances the counter (every block has read it by then), which saves the separate launch.
 __global__ void k_monitor_ctr(DevTab T, const int32_t* mon, int nmon, double* samples, long long rows_before, long long iter0,
-                              long long nburnin, int thin) {
+                              long long nburnin, int thin, unsigned long long* ctr, unsigned int* ticket) {
   long long it = (long long)T.ctr[0] - iter0;
-  if (it <= nburnin || (it - nburnin) % thin != 0) return;
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (size_t)nmon * T.C) return;
-  int c = (int)(gid % T.C), j = (int)(gid / T.C);
-  long long row = rows_before + (it - nburnin) / thin - 1;
-  samples[(size_t)row * nmon * T.C + gid] = T.state[(size_t)mon[j] * T.C + c];
+  if (it > nburnin && (it - nburnin) % thin == 0 && gid < (size_t)nmon * T.C) {
+    int c = (int)(gid % T.C), j = (int)(gid / T.C);
+    long long row = rows_before + (it - nburnin) / thin - 1;
+    samples[(size_t)row * nmon * T.C + gid] = T.state[(size_t)mon[j] * T.C + c];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ticket, 1u) == gridDim.x - 1) { *ticket = 0; ctr[0] += 1; }
+  }
 }
 __global__ void k_bump_iter(unsigned long long* ctr) { ctr[0] += 1; }
 
@@ -836,6 +842,7 @@ struct nimb200_model {
   std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
   std::vector<size_t> sweep_deps;   // per sampler: dependent nodes of target 0 (execution-shape heuristic)
   unsigned long long* d_ctr = nullptr;  // device iteration counter (DevTab::ctr)
+  unsigned int* d_ticket = nullptr;     // block ticket of k_monitor_ctr (the last block advances the counter)
   cudaGraphExec_t graph_exec = nullptr;
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
@@ -1073,11 +1080,15 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   nimb200_dep dd{};
   if (dp) dd = *dp;
   size_t shm = sizeof(double) * EVAL_THREADS * K;
-  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, nullptr, dd, slot, gam);
+  // a single tile (scalar priors, small declarations) is its own sum: the kernel writes the destination directly
+  const bool direct = nt == 1 && mode == 0;
+  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), direct ? dst0 : m->d_partials, nullptr, dd, slot, gam);
   else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, nullptr, dd, slot, gam);
   m->launches++;
-  k_reduce<<<(C * K * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
-  m->launches++;
+  if (!direct) {
+    k_reduce<<<(C * K * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
+    m->launches++;
+  }
   CK(cudaGetLastError());
   if (shard && m->nccl_comm) {
     if (allreduce_sum(m, dst0, C)) return 1;
@@ -1283,6 +1294,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   }
   TRY(dev_alloc(m, &m->d_ctr, 2));
   TRYCU(cudaMemsetAsync(m->d_ctr, 0, 2 * sizeof(unsigned long long), m->stream));
+  TRY(dev_alloc(m, &m->d_ticket, 1));
+  TRYCU(cudaMemsetAsync(m->d_ticket, 0, sizeof(unsigned int), m->stream));
   m->T.ctr = m->d_ctr;
   m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
   m->sweep_sharded.assign(m->samplers.size(), 0);
@@ -1872,11 +1885,13 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       if (run_sampler(m, (int)s, seed, git)) return 1;
     if (nmon > 0) {
       size_t total = (size_t)nmon * C;
-      k_monitor_ctr<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples, rows_before, iter0, nburnin, thin);
+      k_monitor_ctr<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples, rows_before, iter0, nburnin, thin,
+                                                                          m->d_ctr, m->d_ticket);
+      m->launches++;
+    } else {
+      k_bump_iter<<<1, 1, 0, m->stream>>>(m->d_ctr);
       m->launches++;
     }
-    k_bump_iter<<<1, 1, 0, m->stream>>>(m->d_ctr);
-    m->launches++;
     return 0;
   };
   CK(cudaEventRecord(m->ev0, m->stream));

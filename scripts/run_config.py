@@ -6,7 +6,7 @@ import nimble_b200 as nb
 from nimble_b200 import configs, _capi
 
 name = sys.argv[1]
-defaults = {"pump": (4, 2000), "logistic": (1024, 20), "lmm": (8, 20), "occupancy": (64, 20), "glmm": (8192, 5)}
+defaults = {"pump": (4, 2000), "logistic": (1024, 20), "lmm": (8, 400), "occupancy": (64, 100), "glmm": (8192, 5)}
 C = int(sys.argv[2]) if len(sys.argv) > 2 else defaults[name][0]
 K = int(sys.argv[3]) if len(sys.argv) > 3 else defaults[name][1]
 scale = float(sys.argv[4]) if len(sys.argv) > 4 else 1.0
