@@ -13,13 +13,18 @@ namespace nimb {
 // to < 1e-15 relative, with the same p = 1/(1 + exp(-eta)) rounding sequence as Utils.h:187 and the same limits
 // (p == 0: y=0 -> 0, y=1 -> -Inf;  q == 0: y=0 -> -Inf, y=1 -> 0).  No data-dependent loop, no divergent branch.
 //
-// Moderate linear predictors (every |eta| of the warp's W x 32 values <= 6, i.e. all of a realistic regression): with a = |eta|
+// Moderate linear predictors (every |eta| of the warp's W x 32 values < 6, i.e. all of a realistic regression): with a = |eta|
 //   log p or log q = -log(1 + exp(-a)) - (y == (eta < 0) ? a : 0)
-// exactly, which needs no reciprocal and no correction term (23 FP64 instructions instead of 35).  For a <= 6 the reference's own
-// value (p rounded, then log) and this one each carry <= 2e-16 absolute error on a result >= 2.5e-3 in magnitude, so they agree
-// to < 2e-13 relative; beyond 6 the rounding of p = fl(1/(1+e)) starts to matter (q = 1 - p loses bits, q == 0 from eta = 37) and
-// the general path below reproduces it step by step.  The choice is a warp vote (VOTE), so the fused epilogue stays convergent;
-// callers whose lanes have already diverged (VOTE = false) choose per lane.
+// exactly: no reciprocal and no correction term.  Two forms.  (1) exp and log from the tables of fastmath.cuh: 25.6 FP64
+// instructions instead of 35.5 and three 8-byte look-ups -- the fused logistic kernel, whose FP64 multipliers are the saturated
+// resource.  (2) SOFTPLUS: log(1 + exp(-a)) read off a table of degree-8 Taylor polynomials (centres k * 3/32): 12 FP64
+// instructions, relative error <= 2.3e-16, but 80 bytes of shared-memory reads per value -- right for the latency-bound per-lane
+// callers (Bernoulli-logit-linear family), wrong for the fused kernel: with realistic predictors the lanes hit ~40 different
+// rows and the kernel turns shared-memory-bound (6.4 ms instead of 5.1; 4.8 only when all predictors are tiny).  For a < 6
+// the reference's own value (p rounded, then log) carries <= 2e-16 absolute error on a result >= 2.5e-3 in magnitude, so the two
+// agree to < 2e-13 relative; beyond 6 the rounding of p = fl(1/(1+e)) starts to matter (q = 1 - p loses bits, q == 0 from
+// eta = 37) and the general path below reproduces it step by step.  The choice is a warp vote (VOTE), so the fused epilogue
+// stays convergent; callers whose lanes have already diverged (VOTE = false) choose per lane.
 //
 // W values are carried through every step together (statement-level interleaving): the dependent DFMA chains of
 // exp / reciprocal / log are long, and with 4 resident warps per scheduler the FP64 pipe only fills when each warp
@@ -35,8 +40,10 @@ static __device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
   return log(t) + corr;
 }
 
-template <int W, bool VOTE = true>
-__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const MathTab* __restrict__ tab) {
+// SOFTPLUS: fast path on the softplus table sp (shared memory); else on the exp / log tables tab.  tab also serves the general path.
+template <int W, bool VOTE = true, bool SOFTPLUS = false>
+__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const double* __restrict__ sp,
+                                                  const MathTab* __restrict__ tab) {
   bool slow = false;
 #pragma unroll
   for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
@@ -53,49 +60,93 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
     for (int j = 0; j < W; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
     const bool mod = amax < 0x40180000u;  // every |eta| < 6 (NaN fails the test)
     if (VOTE ? __all_sync(0xffffffffu, mod) : mod) {
+      if (SOFTPLUS) {
 #pragma unroll
-      for (int j = 0; j < W; j++) x[j] = -fabs(eta[j]);
+        for (int j = 0; j < W; j++) x[j] = fabs(eta[j]);
 #pragma unroll
-      for (int j = 0; j < W; j++) t[j] = fma(x[j], c_tab_misc[0], c_tab_misc[1]);
+        for (int j = 0; j < W; j++) t[j] = fma(x[j], 32.0 / 3.0, 6755399441055744.0);  // k = round(a * 32/3) in the low word
 #pragma unroll
-      for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_tab_misc[1]; }
+        for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - 6755399441055744.0; }
 #pragma unroll
-      for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[2], x[j]);
+        for (int j = 0; j < W; j++) r[j] = fma(-t[j], 0.09375, x[j]);  // a - k * 3/32 (the product is exact)
+        const double2* row[W];
+        double2 c8[W], c6[W], c4[W], c2[W], c0[W];
 #pragma unroll
-      for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[3], r[j]);
+        for (int j = 0; j < W; j++) row[j] = reinterpret_cast<const double2*>(sp + n[j] * 10);
 #pragma unroll
-      for (int j = 0; j < W; j++) pl[j] = fma(r[j], c_tab_misc[4], c_tab_misc[5]);
+        for (int j = 0; j < W; j++) { c8[j] = row[j][4]; c6[j] = row[j][3]; }
 #pragma unroll
-      for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_tab_misc[6]);
+        for (int j = 0; j < W; j++) pl[j] = fma(c8[j].x, r[j], c6[j].y);
 #pragma unroll
-      for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 0.5);
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c6[j].x);
 #pragma unroll
-      for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+        for (int j = 0; j < W; j++) c4[j] = row[j][2];
 #pragma unroll
-      for (int j = 0; j < W; j++) {
-        double T = tab->expT[n[j] & 63];
-        double v = fma(T * r[j], pl[j], T);
-        e[j] = __hiloint2double(__double2hiint(v) + ((n[j] >> 6) << 20), __double2loint(v));
-      }
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c4[j].y);
 #pragma unroll
-      for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];  // in (1, 2]
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c4[j].x);
 #pragma unroll
-      for (int j = 0; j < W; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 only for d = 2 - (binade above: k = 1, c = 1)
-        int hi = __double2hiint(d[j]), lo = __double2loint(d[j]);
-        int fr = hi & 0x000fffff;
-        int idx = (fr + 0x1000) >> 13;
-        int k = ((hi >> 20) - 1023) + (idx >> 7);
-        double m = __hiloint2double(fr | 0x3ff00000, lo);
-        double rr = fma(m, tab->invc[idx], -1.0);
-        double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
-        Q = fma(Q, rr, c_tab_misc[10]);
-        Q = fma(Q, rr, c_tab_misc[11]);
-        Q = fma(Q, rr, 1.0 / 3.0);
-        Q = fma(Q, rr, -0.5);
-        double lp = fma(rr * rr, Q, rr);
-        double lg = fma((double)k, c_tab_misc[7], tab->logA[idx] + lp);
-        bool neg = __double2hiint(eta[j]) < 0;
-        out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
+        for (int j = 0; j < W; j++) c2[j] = row[j][1];
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c2[j].y);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c2[j].x);
+#pragma unroll
+        for (int j = 0; j < W; j++) c0[j] = row[j][0];
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c0[j].y);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c0[j].x);
+#pragma unroll
+        for (int j = 0; j < W; j++) {
+          bool neg = __double2hiint(eta[j]) < 0;
+          out[j] = (y1 == neg ? -x[j] : 0.0) - pl[j];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < W; j++) x[j] = -fabs(eta[j]);
+#pragma unroll
+        for (int j = 0; j < W; j++) t[j] = fma(x[j], c_tab_misc[0], c_tab_misc[1]);
+#pragma unroll
+        for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - c_tab_misc[1]; }
+#pragma unroll
+        for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[2], x[j]);
+#pragma unroll
+        for (int j = 0; j < W; j++) r[j] = fma(t[j], c_tab_misc[3], r[j]);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(r[j], c_tab_misc[4], c_tab_misc[5]);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], c_tab_misc[6]);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 0.5);
+#pragma unroll
+        for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+        for (int j = 0; j < W; j++) {
+          double T = tab->expT[n[j] & 63];
+          double v = fma(T * r[j], pl[j], T);
+          e[j] = __hiloint2double(__double2hiint(v) + ((n[j] >> 6) << 20), __double2loint(v));
+        }
+#pragma unroll
+        for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];  // in (1, 2]
+#pragma unroll
+        for (int j = 0; j < W; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 only for d = 2 - (binade above: k = 1, c = 1)
+          int hi = __double2hiint(d[j]), lo = __double2loint(d[j]);
+          int fr = hi & 0x000fffff;
+          int idx = (fr + 0x1000) >> 13;
+          int k = ((hi >> 20) - 1023) + (idx >> 7);
+          double m = __hiloint2double(fr | 0x3ff00000, lo);
+          double rr = fma(m, tab->invc[idx], -1.0);
+          double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
+          Q = fma(Q, rr, c_tab_misc[10]);
+          Q = fma(Q, rr, c_tab_misc[11]);
+          Q = fma(Q, rr, 1.0 / 3.0);
+          Q = fma(Q, rr, -0.5);
+          double lp = fma(rr * rr, Q, rr);
+          double lg = fma((double)k, c_tab_misc[7], tab->logA[idx] + lp);
+          bool neg = __double2hiint(eta[j]) < 0;
+          out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
+        }
       }
       return;
     }
@@ -177,16 +228,16 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
 
 __device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)
   double in[1] = {eta}, o[1];
-  bern_logit_lp_vec<1>(in, y1, o, &g_mathtab);
+  bern_logit_lp_vec<1, true, false>(in, y1, o, nullptr, &g_mathtab);
   return o[0];
 }
 
 
 // per-lane form without the warp vote, for callers whose lanes have already diverged
-__device__ __forceinline__ double bern_logit_lp1(double eta, bool y1, const MathTab* __restrict__ tab) {
+__device__ __forceinline__ double bern_logit_lp1(double eta, bool y1, const double* __restrict__ sp) {
   if (!(eta >= -690.0)) return bern_logit_lp_slow(eta, y1);
   double in[1] = {eta}, o[1];
-  bern_logit_lp_vec<1, false>(in, y1, o, tab);
+  bern_logit_lp_vec<1, false, true>(in, y1, o, sp, &g_mathtab);
   return o[0];
 }
 

@@ -109,6 +109,14 @@ struct MathTab {
   double invc[129];
 };
 static __device__ const MathTab g_mathtab = {NIMB_EXPT_INIT, NIMB_LOGA_INIT, NIMB_LOGB_INIT, NIMB_INVC_INIT};
+// softplus table: log(1 + exp(-a)) on [0, 6] as degree-8 Taylor polynomials about the centres k * 3/32, k = 0..64 (rows of 10
+// doubles: 9 coefficients + padding, so a row is five 16-byte loads).  |a - centre| <= 3/64: remainder < 1e-17.
+static const int SOFTPLUS_DOUBLES = NIMB_SOFTPLUS_ROWS * 10;
+struct SoftplusTab { double c[SOFTPLUS_DOUBLES]; };
+static __device__ __align__(16) const SoftplusTab g_softplus = {NIMB_SOFTPLUS_INIT};
+__device__ __forceinline__ void load_softplus(double* dst, int tid, int nthreads) {
+  for (int i = tid; i < SOFTPLUS_DOUBLES; i += nthreads) dst[i] = g_softplus.c[i];
+}
 static __device__ __constant__ double c_tab_misc[12] = {
     NIMB_EXP_L, 6755399441055744.0, -NIMB_EXP_HI, -NIMB_EXP_LO,
     1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0,                              // exp(r) = 1 + r (1 + r/2 + r^2/6 + r^3/24 + r^4/120)

@@ -32,7 +32,7 @@ __device__ __forceinline__ int bern_gate_index(const BernArgs& a, int i) {
   }
 }
 
-__device__ __forceinline__ double bernlin_lp(double v, double gate, double eta, const MathTab* tab) {
+__device__ __forceinline__ double bernlin_lp(double v, double gate, double eta, const double* tab) {
   bool v01 = v == 0.0 || v == 1.0;
   if (v01 && gate == 1.0) return bern_logit_lp1(eta, v != 0.0, tab);
   if (v01 && gate == 0.0 && eta == eta) return v == 0.0 ? 0.0 : -INFINITY;
@@ -49,8 +49,8 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
   __shared__ double sx[BF_TILE], sv[BF_TILE];
   __shared__ int sg[BF_TILE];
   __shared__ double red[BF_THREADS / 32][32];
-  __shared__ MathTab tab;
-  load_mathtab(&tab, threadIdx.x, BF_THREADS);
+  __shared__ __align__(16) double tab[SOFTPLUS_DOUBLES];
+  load_softplus(tab, threadIdx.x, BF_THREADS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = BF_THREADS / 32;
   const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
@@ -74,7 +74,7 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
     for (int k = warp * per; k < k_hi; k++) {  // a contiguous run per warp: consecutive nodes mostly share the gate
       if (a.gate_slot >= 0 && sg[k] != gprev) { gprev = sg[k]; gate = T.state[(size_t)(a.gate_slot + gprev) * T.C + cc]; }
       double v = a.vdata ? sv[k] : T.state[(size_t)(a.v_slot + t0 + k) * T.C + cc];
-      acc += bernlin_lp(v, gate, fma(c1, sx[k], c0), &tab);
+      acc += bernlin_lp(v, gate, fma(c1, sx[k], c0), tab);
     }
   }
   red[warp][lane] = acc;
@@ -90,8 +90,8 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
 // are the data nodes of  y ~ dbern(z[G] * ilogit(a0 + a1 w))  (py) selected by the sampler's stage-1 entry.
 __global__ void __launch_bounds__(BF_THREADS)
 k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs pz, BernArgs py) {
-  __shared__ MathTab tab;
-  load_mathtab(&tab, threadIdx.x, BF_THREADS);
+  __shared__ __align__(16) double tab[SOFTPLUS_DOUBLES];
+  load_softplus(tab, threadIdx.x, BF_THREADS);
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -106,14 +106,14 @@ k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs
   const double b0 = T.state[(size_t)pz.c0_slot * T.C + c], b1 = T.state[(size_t)pz.c1_slot * T.C + c];
   const double a0 = T.state[(size_t)py.c0_slot * T.C + c], a1 = T.state[(size_t)py.c1_slot * T.C + c];
   const double eta_z = fma(b1, pz.x[znode], b0);
-  double curPrior = bernlin_lp(cur, 1.0, eta_z, &tab), otherPrior = bernlin_lp(other, 1.0, eta_z, &tab);
+  double curPrior = bernlin_lp(cur, 1.0, eta_z, tab), otherPrior = bernlin_lp(other, 1.0, eta_z, tab);
   double curDeps = 0.0, otherDeps = 0.0;
   Sel s = sel_of(T, d1, t);
   for (int k = s.lo; k < s.hi; k++) {
     int node = s.idx ? s.idx[k] : k;
     double eta = fma(a1, py.x[node], a0), yv = py.vdata[node];
-    curDeps += bernlin_lp(yv, cur, eta, &tab);
-    otherDeps += bernlin_lp(yv, other, eta, &tab);
+    curDeps += bernlin_lp(yv, cur, eta, tab);
+    otherDeps += bernlin_lp(yv, other, eta, tab);
   }
   double currentLogProb = curPrior + curDeps;
   double otherLogProb = (otherPrior == -INFINITY) ? otherPrior : otherPrior + otherDeps;

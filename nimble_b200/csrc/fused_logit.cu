@@ -137,7 +137,7 @@ k_fused_bern_logit(const double* __restrict__ Xpad, const double* __restrict__ y
         double yv = ys[wg * 64 + mp * 16 + mt * 8 + (lane >> 2)];
         bool live = yv >= 0.0, y1 = yv != 0.0;          // -1 marks the zero-padded rows past n
         double lp[4];
-        bern_logit_lp_vec<4>(acc[mt], y1, lp, tab);
+        bern_logit_lp_vec<4>(acc[mt], y1, lp, nullptr, tab);
 #pragma unroll
         for (int j = 0; j < 4; j++) csum[j] += live ? lp[j] : 0.0;
       }
