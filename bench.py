@@ -254,11 +254,11 @@ def main():
         alg_bytes = 8.0 * a.n * a.p + 8.0 * a.n + 8.0 * a.p * C
         contraction_flops = 2.0 * a.n * a.p * C
         # FP64 work of the link + Bernoulli density per evaluation as the kernel implements it (DESIGN.md section 3,
-        # ncu profiles/r1f_summary.md): 25.6 FP64-pipe instructions on the reciprocal-free path every realistic linear
-        # predictor takes (table-driven exp 11, 1 + e, table-driven log 11, glue 2.6; 35.5 on the general path);
+        # ncu profiles/r1f_summary.md): 24.8 FP64-pipe instructions on the reciprocal-free path every realistic linear
+        # predictor takes (table-driven exp 11, 1 + e, table-driven log 10, glue 2.8; 35.5 on the general path);
         # one instruction = one multiplier slot = 2 flop in the units of the FMA peak.  Implementation-counted,
         # reported next to the strict figure.
-        epi_flops = 2.0 * 25.6 * a.n * C
+        epi_flops = 2.0 * 24.8 * a.n * C
         ach = contraction_flops / (k_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "k_fused_bern_logit", "achieved": ach, "peak": dmma, "unit": "TFLOP/s",
                 "frac": ach / dmma if dmma else None,
@@ -272,7 +272,7 @@ def main():
                 "algorithmic_bytes": alg_bytes, "kernel_ms": k_ms, "evals_per_s_kernel": a.n * C / (k_ms * 1e-3),
                 "fp64_units": {"achieved": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12, "peak": mixed, "unit": "TFLOP/s",
                                "frac": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12 / mixed if mixed else None,
-                               "what": "contraction + 25.6 FP64 instructions per evaluation of link and density (as implemented, ncu-counted), "
+                               "what": "contraction + 24.8 FP64 instructions per evaluation of link and density (as implemented, ncu-counted), "
                                        "against the measured DMMA+DFMA mixed peak"},
                 "hbm": {"achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,

@@ -130,20 +130,17 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
 #pragma unroll
         for (int j = 0; j < W; j++) d[j] = 1.0 + e[j];  // in (1, 2]
 #pragma unroll
-        for (int j = 0; j < W; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 only for d = 2 - (binade above: k = 1, c = 1)
-          int hi = __double2hiint(d[j]), lo = __double2loint(d[j]);
-          int fr = hi & 0x000fffff;
-          int idx = (fr + 0x1000) >> 13;
-          int k = ((hi >> 20) - 1023) + (idx >> 7);
-          double m = __hiloint2double(fr | 0x3ff00000, lo);
-          double rr = fma(m, tab->invc[idx], -1.0);
+        for (int j = 0; j < W; j++) {  // log(d), d in (1, 2]: centre c = 1 + idx/128; idx = 128 (d >= 2 - 1/256) has c = 2:
+          // invc[128] = 0.5 and the logarithm of the centre is ln 2 -- no exponent arithmetic on this path
+          const int idx = (__double2hiint(d[j]) - 0x3ff00000 + 0x1000) >> 13;
+          double rr = fma(d[j], tab->invc[idx], -1.0);
           double Q = fma(rr, c_tab_misc[8], c_tab_misc[9]);
           Q = fma(Q, rr, c_tab_misc[10]);
           Q = fma(Q, rr, c_tab_misc[11]);
           Q = fma(Q, rr, 1.0 / 3.0);
           Q = fma(Q, rr, -0.5);
           double lp = fma(rr * rr, Q, rr);
-          double lg = fma((double)k, c_tab_misc[7], tab->logA[idx] + lp);
+          double lg = (idx == 128 ? c_tab_misc[7] : tab->logA[idx]) + lp;
           bool neg = __double2hiint(eta[j]) < 0;
           out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
         }
