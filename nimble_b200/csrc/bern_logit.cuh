@@ -13,17 +13,18 @@ namespace nimb {
 // to < 1e-15 relative, with the same p = 1/(1 + exp(-eta)) rounding sequence as Utils.h:187 and the same limits
 // (p == 0: y=0 -> 0, y=1 -> -Inf;  q == 0: y=0 -> -Inf, y=1 -> 0).  No data-dependent loop, no divergent branch.
 //
-// Moderate linear predictors (every |eta| of the warp's W x 32 values < 6, i.e. all of a realistic regression): with a = |eta|
+// Moderate linear predictors (every |eta| of the warp's W x 32 values < 8, < 6 for the table form; i.e. all of a realistic
+// regression): with a = |eta|
 //   log p or log q = -log(1 + exp(-a)) - (y == (eta < 0) ? a : 0)
 // exactly: no reciprocal and no correction term.  Two forms.  (1) exp and log from the tables of fastmath.cuh: 25.6 FP64
 // instructions instead of 35.5 and three 8-byte look-ups -- the fused logistic kernel, whose FP64 multipliers are the saturated
 // resource.  (2) SOFTPLUS: log(1 + exp(-a)) read off a table of degree-8 Taylor polynomials (centres k * 3/32): 12 FP64
 // instructions, relative error <= 2.3e-16, but 80 bytes of shared-memory reads per value -- right for the latency-bound per-lane
 // callers (Bernoulli-logit-linear family), wrong for the fused kernel: with realistic predictors the lanes hit ~40 different
-// rows and the kernel turns shared-memory-bound (6.4 ms instead of 5.1; 4.8 only when all predictors are tiny).  For a < 6
-// the reference's own value (p rounded, then log) carries <= 2e-16 absolute error on a result >= 2.5e-3 in magnitude, so the two
-// agree to < 2e-13 relative; beyond 6 the rounding of p = fl(1/(1+e)) starts to matter (q = 1 - p loses bits, q == 0 from
-// eta = 37) and the general path below reproduces it step by step.  The choice is a warp vote (VOTE), so the fused epilogue
+// rows and the kernel turns shared-memory-bound (6.4 ms instead of 5.1; 4.8 only when all predictors are tiny).  For a < 8
+// the reference's own value (p rounded, then log) carries <= 2e-16 absolute error on a result >= 3.4e-4 in magnitude, so the two
+// agree to < 7e-13 relative (< 2e-13 for a < 6); beyond that the rounding of p = fl(1/(1+e)) matters (q = 1 - p loses bits,
+// q == 0 from eta = 37) and the general path below reproduces it step by step.  The choice is a warp vote (VOTE), so the fused epilogue
 // stays convergent; callers whose lanes have already diverged (VOTE = false) choose per lane.
 //
 // W values are carried through every step together (statement-level interleaving): the dependent DFMA chains of
@@ -44,21 +45,13 @@ static __device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
 template <int W, bool VOTE = true, bool SOFTPLUS = false>
 __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const double* __restrict__ sp,
                                                   const MathTab* __restrict__ tab) {
-  bool slow = false;
-#pragma unroll
-  for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
-  if (VOTE ? __any_sync(0xffffffffu, slow) : slow) {  // warp-uniform with VOTE, practically never taken
-#pragma unroll
-    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1);
-    return;
-  }
   double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
   int n[W];
-  {
+  {  // the moderate case is recognised on the exponent bits (integer pipe), before anything touches the FP64 pipe
     unsigned amax = 0;
 #pragma unroll
     for (int j = 0; j < W; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
-    const bool mod = amax < 0x40180000u;  // every |eta| < 6 (NaN fails the test)
+    const bool mod = amax < (SOFTPLUS ? 0x40180000u : 0x40200000u);  // every |eta| < 6 (table range) / < 8 (NaN fails the test)
     if (VOTE ? __all_sync(0xffffffffu, mod) : mod) {
       if (SOFTPLUS) {
 #pragma unroll
@@ -104,7 +97,7 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
         }
       } else {
 #pragma unroll
-        for (int j = 0; j < W; j++) x[j] = -fabs(eta[j]);
+        for (int j = 0; j < W; j++) x[j] = __hiloint2double(__double2hiint(eta[j]) | (int)0x80000000, __double2loint(eta[j]));  // -|eta|
 #pragma unroll
         for (int j = 0; j < W; j++) t[j] = fma(x[j], c_tab_misc[0], c_tab_misc[1]);
 #pragma unroll
@@ -147,6 +140,14 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
       }
       return;
     }
+  }
+  bool slow = false;
+#pragma unroll
+  for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
+  if (VOTE ? __any_sync(0xffffffffu, slow) : slow) {  // warp-uniform with VOTE, practically never taken
+#pragma unroll
+    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1);
+    return;
   }
   // ---- e = exp(-eta): x = k ln2/64 + r, e = 2^(k>>6) T[k&63] (1 + r P(r)).  x is clamped at -708: below that e only has to
   // vanish against 1, and 2^(k>>6) can then always be applied by one integer add to the exponent field.
