@@ -165,7 +165,9 @@ enum {
   NIMB_SAMPLER_BINARY = 3,     /* MCMC_samplers.R:115-152 */
   NIMB_SAMPLER_CONJ_GAMMA = 4, /* dgamma prior; dpois / dgamma(rate) / dnorm(tau) dependents, MCMC_conjugacy.R:80-93 */
   NIMB_SAMPLER_CONJ_NORMAL = 5, /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
-  NIMB_SAMPLER_CONJ_BETA = 6    /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
+  NIMB_SAMPLER_CONJ_BETA = 6,   /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
+  NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7 /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
+                                           distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbern) and recalculate it */
 };
 
 typedef struct nimb200_sampler {

@@ -337,6 +337,25 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   double* bp = buf + ((size_t)t * 3) * T.C + c;
   if (PHASE == 2) { v0 = bp[0]; v1 = bp[(size_t)T.C]; v2 = bp[2 * (size_t)T.C]; }
 
+  if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {  // MCMC_samplers.R:97-101 for a terminal node: simulate the target, nothing to decide
+    if (PHASE == 1 || lane != 0) return;
+    const nimb200_dep tp = T.deps[sp.dep_off];
+    const int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
+    const nimb200_decl& d = T.decl[tp.decl];
+    const double p0 = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+    const double p1 = d.nparam > 1 ? get_param(T, tp.decl, tnode, c, 1, -1, 0.0) : 0.0;
+    double u, u2, nv = NAN;
+    switch (d.dist) {
+      case NIMB_DNORM: normal2(key, 0, u, u2); nv = p0 + p1 * u; break;
+      case NIMB_DGAMMA: nv = rgamma1(key, p0) * p1; break;
+      case NIMB_DBETA: nv = rbeta1(key, p0, p1); break;
+      case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; break;
+      case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); break;
+      case NIMB_DBINOM: unif2(key, 0, u, u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+    }
+    *sv = nv;
+    return;
+  }
   if (sp.type == NIMB_SAMPLER_RW) {  // MCMC_samplers.R:352-386
     double z, z1, propLogScale;
     normal2(key, 0, z, z1);
@@ -1156,11 +1175,17 @@ static int validate_table(const nimb200_table* t) {
   }
   for (int s = 0; s < t->n_samplers; s++) {
     const nimb200_sampler& sp = t->samplers[s];
-    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_CONJ_BETA)
-      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta); there is no CPU fallback");
+    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_POSTERIOR_PREDICTIVE)
+      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta, posterior_predictive); there is no CPU fallback");
     if (sp.type == NIMB_SAMPLER_RW_BLOCK && (sp.d < 1 || sp.d > NIMB200_MAX_BLOCK_D)) return fail("RW_block dimension out of range");
     if (sp.dep_off < 0 || sp.dep_off + sp.n_dep > t->n_deps || sp.n_dep < 1) return fail("sampler dependency range outside deps[]");
     if (t->deps[sp.dep_off].stage != 0) return fail("first dependency entry of a sampler must be the target's own declaration");
+    if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {
+      const nimb200_decl& pd = t->decl[t->deps[sp.dep_off].decl];
+      const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP ||
+                      pd.dist == NIMB_DLOGIS || pd.dist == NIMB_DBINOM;
+      if (!ok || sp.n_dep != 1) return fail("posterior_predictive: unsupported target distribution, or the target has dependents");
+    }
     if (sp.adaptive && sp.adapt_interval < 1) return fail("adaptInterval must be >= 1");
     if (sp.tries < 1 && sp.type == NIMB_SAMPLER_RW_BLOCK) return fail("tries must be >= 1");
   }

@@ -145,10 +145,24 @@ class MCMCconf:
                 continue
             for decl in model.decl_of(var):
                 self._add_default(decl, useConjugacy)
+        # posterior predictive samplers run last (MCMC_configuration.R:236)
+        pp = [sc for sc in self.samplerConfs if sc.type == T.SAMPLER_POSTERIOR_PREDICTIVE]
+        self.samplerConfs = [sc for sc in self.samplerConfs if sc.type != T.SAMPLER_POSTERIOR_PREDICTIVE] + pp
 
     # default assignment rules, MCMC_configuration.R:340-446: conjugate -> binary -> (discrete: unsupported) -> RW
+    _PP_DISTS = (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS)
+
+    def _is_terminal(self, decl):
+        return not [d for d in self.model.dependents(decl.var) if d is not decl]
+
     def _add_default(self, decl, useConjugacy):
         model = self.model
+        # terminal (end) nodes are posterior predictive: simulated from their own distribution, MCMC_configuration.R:283-285, 368
+        # (a predictive node that has predictive descendants keeps its ordinary sampler here)
+        if self._is_terminal(decl) and (decl.dist in self._PP_DISTS or
+                                        (decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0))):
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, decl.var, decl.pos, self.control_defaults))
+            return
         conj = check_conjugacy(model, decl) if useConjugacy else None
         if conj is not None:
             self.samplerConfs.append(SamplerConf(conj[0], decl.var, decl.pos, self.control_defaults, conj=conj[1]))
@@ -219,9 +233,17 @@ class MCMCconf:
                 if conj is None:
                     raise ValueError("no conjugate relationship found for %s" % var)
                 self.samplerConfs.append(SamplerConf(conj[0], var, pos, ctrl, conj=conj[1]))
+        elif tname == "posterior_predictive":
+            for decl in self.model.decl_of(var):
+                if not self._is_terminal(decl):
+                    # MCMC_samplers.R:93-94
+                    raise ValueError("posterior_predictive sampler should not be assigned to non-posterior-predictive nodes")
+                if not (decl.dist in self._PP_DISTS or (decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0))):
+                    raise NotImplementedError("posterior_predictive: no device variate generator for the distribution of %s" % var)
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl))
         else:
             raise NotImplementedError("sampler type %r is not part of the B200 sampling path (supported: RW, "
-                                      "RW_block, binary, conjugate); there is no CPU fallback" % type)
+                                      "RW_block, binary, conjugate, posterior_predictive); there is no CPU fallback" % type)
         return self
 
     def removeSamplers(self, target=None):

@@ -489,6 +489,36 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
   copy_lp(m, c, sp, t, -1, 1);
 }
 
+/* sampler_posterior_predictive::run (MCMC_samplers.R:97-101) for a terminal node: model$simulate(target), calculate, copy.
+ * The variate generators are the counter-based ones of draws_ref.c (call 0.. of the sampler's counter), not R's. */
+static int run_posterior_predictive(ref_model *m, int c, int sid, int t, uint64_t seed, uint64_t iter) {
+  const nimb200_sampler *sp = m->t.samplers + sid;
+  double *st = m->state + (size_t)c * m->t.n_slots;
+  int slot = sp->target_slot + t;
+  const nimb200_dep *tp = m->t.deps + sp->dep_off;
+  int tnode = sel_of(m, tp, t).lo;
+  const nimb200_decl *d = m->t.decl + tp->decl;
+  uint32_t chain = (uint32_t)(m->first_chain + c);
+  double p0 = get_param(m, st, tp->decl, tnode, 0), p1 = d->nparam > 1 ? get_param(m, st, tp->decl, tnode, 1) : 0.0;
+  double u, u2, nv;
+  switch (d->dist) {
+    case NIMB_DNORM: ref_normal2(seed, chain, iter, sid, t, 0, &u, &u2); nv = p0 + p1 * u; break;
+    case NIMB_DGAMMA: nv = ref_rgamma(seed, chain, iter, sid, t, p0) * p1; break;
+    case NIMB_DBETA: nv = ref_rbeta(seed, chain, iter, sid, t, p0, p1); break;
+    case NIMB_DEXP: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
+    case NIMB_DLOGIS: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
+    case NIMB_DBINOM:
+      if (p0 != 1.0) return fail("posterior_predictive: dbin with size != 1 is not supported");
+      ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+    default: return fail("posterior_predictive: unsupported distribution");
+  }
+  st[slot] = nv;
+  calculate_deps(m, c, sp, t, -1);
+  copy_targets(m, c, sp, t, 1);
+  copy_lp(m, c, sp, t, -1, 1);
+  return 0;
+}
+
 /* ------------------------------------------------------------------ model life cycle */
 int ref_model_create(const nimb200_table *t, int32_t nchains, int32_t first_chain, ref_model **out) {
   ref_model *m;
@@ -674,6 +704,9 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
           case NIMB_SAMPLER_CONJ_GAMMA:
           case NIMB_SAMPLER_CONJ_NORMAL:
           case NIMB_SAMPLER_CONJ_BETA: for (t = 0; t < sp->n_targets; t++) run_conjugate(m, c, s, t, seed, git); break;
+          case NIMB_SAMPLER_POSTERIOR_PREDICTIVE:
+            for (t = 0; t < sp->n_targets; t++) if (run_posterior_predictive(m, c, s, t, seed, git)) return 1;
+            break;
           default: return fail("unknown sampler type");
         }
       }

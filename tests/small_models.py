@@ -123,6 +123,20 @@ def gamma_exponential():
     return m, nb.configureMCMC(m), (2 + 9, 1 + float((c * t).sum()))
 
 
+def predictive_nodes():
+    """One terminal (posterior predictive) node per distribution the device can simulate, all driven by one latent a."""
+    code = """{ a ~ dgamma(2, 1)
+      y ~ dnorm(a, 1)
+      pn ~ dnorm(a, sd = 2)
+      pg ~ dgamma(a, 2)
+      pb ~ dbeta(2, a)
+      pe ~ dexp(a)
+      pl ~ dlogis(a, 2)
+      pz ~ dbern(0.3) }"""
+    m = nb.nimbleModel(code, data={"y": 1.5}, inits={"a": 1.0, "pn": 0.0, "pg": 1.0, "pb": 0.5, "pe": 1.0, "pl": 0.0, "pz": 0.0})
+    return m, nb.configureMCMC(m, monitors=["a", "pn", "pg", "pb", "pe", "pl", "pz"])
+
+
 def random_inits(model, nchains, seed, spread=0.3):
     """Positive, chain-specific perturbations of the model's inits (works for the models above)."""
     rng = np.random.default_rng(seed)

@@ -171,3 +171,16 @@ def test_beta_conjugacy_wide_path(oracle, b200):
     so, sg = run(compile_on(oracle, conf), inits, 120, 0, seed=2), run(compile_on(b200, conf), inits, 120, 0, seed=2)
     assert rel_err(sg, so).max() < RTOL_TRAJ
     assert abs(so.mean() - (1.5 + z.sum()) / (4.0 + N)) < 0.002
+
+
+@pytest.mark.parametrize("nchains", [2, 37])
+def test_posterior_predictive_matches_oracle(oracle, b200, nchains):
+    """Terminal nodes simulated on the device from the same counter-based variates as the oracle: bit-compatible draws for
+    dnorm, dgamma, dbeta, dexp, dlogis and dbern targets, and the reference's own predictive fixture (test-mcmc.R:209-227)."""
+    for build in (sm.predictive_nodes, sm.very_simple):
+        m, conf = build()
+        assert conf.samplerConfs[-1].type == T.SAMPLER_POSTERIOR_PREDICTIVE
+        inits = np.tile(m.init_vector(), (nchains, 1))
+        so, sg = run(compile_on(oracle, conf), inits, 300, 0, seed=4), run(compile_on(b200, conf), inits, 300, 0, seed=4)
+        assert np.all(np.isfinite(so))
+        assert rel_err(sg, so).max() < RTOL_TRAJ

@@ -133,3 +133,30 @@ def test_beta_binomial_and_gamma_exponential_conjugacy(oracle):
     # a beta prior seen through anything but the identity link is not conjugate (falls back to RW)
     m2 = nb.nimbleModel("{ p ~ dbeta(1, 1)\n y ~ dbin(0.5 * p, 10) }", data={"y": 3.0}, inits={"p": 0.5})
     assert [s.type for s in nb.configureMCMC(m2).samplerConfs] == [T.SAMPLER_RW]
+
+
+def test_posterior_predictive_sampler(oracle):
+    """SURVEY.md 8f rank 1 (first part): terminal nodes get sampler_posterior_predictive (MCMC_configuration.R:283-285, 368),
+    listed last (:236); each draw is the node's own distribution given the current parents (MCMC_samplers.R:97-101)."""
+    from nimble_b200 import table as T
+    m, conf = sm.very_simple()                      # test-mcmc.R:209-227: z is the predictive node
+    assert [(s.name, s.var) for s in conf.samplerConfs] == [("conjugate_dnorm", "x"), ("posterior_predictive", "z")]
+    m, conf = sm.predictive_nodes()
+    assert [s.name for s in conf.samplerConfs] == ["RW"] + ["posterior_predictive"] * 6
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 30000, 1000, seed=5))
+    col = {n: s[:, i] for i, n in enumerate(cm.colnames)}
+    a = col["a"]
+    se = lambda x: 6 * x.std() / np.sqrt(x.size / 20)          # a's chain is autocorrelated: generous Monte Carlo band
+    assert abs(col["pn"].mean() - a.mean()) < se(col["pn"]) and abs(col["pn"].var() - (4 + a.var())) < 0.4
+    assert abs(col["pg"].mean() - (a / 2).mean()) < se(col["pg"])
+    assert abs(col["pb"].mean() - (2 / (2 + a)).mean()) < se(col["pb"]) and col["pb"].min() > 0 and col["pb"].max() <= 1
+    assert abs(col["pe"].mean() - (1 / a).mean()) < 0.08 * (1 / a).mean()
+    assert abs(col["pl"].mean() - a.mean()) < se(col["pl"]) and abs(col["pl"].var() - (np.pi ** 2 / 12 + a.var())) < 0.2  # dlogis(location, rate = 2)
+    assert set(np.unique(col["pz"])) == {0.0, 1.0} and abs(col["pz"].mean() - 0.3) < 0.01
+    # explicit assignment and its guard
+    conf2 = nb.configureMCMC(m, nodes=["a"])
+    conf2.addSampler("pg", type="posterior_predictive")
+    assert conf2.samplerConfs[-1].type == T.SAMPLER_POSTERIOR_PREDICTIVE
+    with pytest.raises(ValueError, match="non-posterior-predictive"):
+        conf2.addSampler("a", type="posterior_predictive")
