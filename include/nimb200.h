@@ -166,8 +166,11 @@ enum {
   NIMB_SAMPLER_CONJ_GAMMA = 4, /* dgamma prior; dpois / dgamma(rate) / dnorm(tau) dependents, MCMC_conjugacy.R:80-93 */
   NIMB_SAMPLER_CONJ_NORMAL = 5, /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
   NIMB_SAMPLER_CONJ_BETA = 6,   /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
-  NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7 /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
-                                           distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbern) and recalculate it */
+  NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7, /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
+                                            distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbern) and recalculate it */
+  NIMB_SAMPLER_SLICE = 8 /* MCMC_samplers.R:864-972: stepping-out / shrinkage slice sampler with width adaptation; discrete
+                            targets (dpois, dbin, dcat) are floored.  scale = sliceWidth, tries = sliceMaxSteps,
+                            pad = maxContractions, adaptive / adapt_interval as for RW */
 };
 
 typedef struct nimb200_sampler {

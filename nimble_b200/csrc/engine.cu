@@ -473,6 +473,80 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   *sv = nv;
 }
 
+// ------------------------------------------------------------------------------------------------ slice sampler
+// sampler_slice (MCMC_samplers.R:864-972), one thread per (target, chain): the number of log-density evaluations is data
+// dependent (stepping out, then shrinkage), so the whole update is one loop in one thread over the target's dependents with the
+// candidate value in the override register.  Uniforms: call 0 = (auxiliary exponential, interval offset), call 1 = (split of
+// maxSteps, first candidate), call 2 + j = j-th shrinkage candidate.
+__device__ double slice_lp(const DevTab& T, const nimb200_sampler& sp, int t, int c, int slot, double value) {
+  double lp[2] = {0.0, 0.0};
+  for (int stage = 0; stage < 2; stage++) {
+    for (int e = 0; e < sp.n_dep; e++) {
+      const nimb200_dep dp = T.deps[sp.dep_off + e];
+      if (dp.stage != stage) continue;
+      Sel s = sel_of(T, dp, t);
+      for (int k = s.lo; k < s.hi; k++) {
+        int node = s.idx ? s.idx[k] : k;
+        lp[stage] += calc_node(T, dp.decl, node, c, slot, value);
+      }
+    }
+    if (stage == 0 && lp[0] == -INFINITY) return -INFINITY;  // setAndCalculateTarget: prior -Inf short-circuits
+  }
+  return lp[0] + lp[1];
+}
+__global__ void k_slice(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S) {
+  const nimb200_sampler sp = T.samplers[sid];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = (int)(gid % T.C);
+  size_t tq = gid / T.C;
+  if (tq >= (size_t)sp.n_targets) return;
+  int t = (int)tq, slot = sp.target_slot + t;
+  size_t q = (size_t)t * T.C + c;
+  DrawKey key = make_key(T, seed, iter, sid, t, c);
+  double* sv = T.state + (size_t)slot * T.C + c;
+  const int tdist = T.decl[T.deps[sp.dep_off].decl].dist;
+  const bool discrete = tdist == NIMB_DPOIS || tdist == NIMB_DBINOM || tdist == NIMB_DCAT;
+  const double eps = 1e-15, x0 = *sv, width = S.scale[q];
+  auto f = [&](double v) { return slice_lp(T, sp, t, c, slot, discrete ? floor(v) : v); };
+  double ua, ub, uc, ud;
+  unif2(key, 0, ua, ub);
+  unif2(key, 1, uc, ud);
+  const double u = f(x0) - (-det_log(ua));
+  double L = x0 - ub * width, R = L + width;
+  int maxStepsL = (int)floor(uc * (double)sp.tries), maxStepsR = sp.tries - 1 - maxStepsL;
+  double lp = f(L);
+  while (maxStepsL > 0 && !isnan(lp) && lp >= u) { L = L - width; lp = f(L); maxStepsL--; }
+  lp = f(R);
+  while (maxStepsR > 0 && !isnan(lp) && lp >= u) { R = R + width; lp = f(R); maxStepsR--; }
+  double x1 = L + ud * (R - L);
+  lp = f(x1);
+  int nc = 0;
+  while ((isnan(lp) || lp < u) && (R - L) / (fabs(R) + fabs(L) + eps) > eps && nc < sp.pad) {
+    if (x1 < x0) L = x1; else R = x1;
+    double ue, uf;
+    unif2(key, 2 + nc, ue, uf);
+    x1 = L + ue * (R - L);
+    lp = f(x1);
+    nc++;
+  }
+  if ((R - L) / (fabs(R) + fabs(L) + eps) <= eps || nc == sp.pad) return;  // invalid state / collapsed interval: keep the old value
+  *sv = discrete ? floor(x1) : x1;
+  if (sp.adaptive) {  // adaptiveProcedure: width -> 2 x mean jump, with weight (3/4)^timesAdapted
+    int ran = S.timesRan[q] + 1;
+    double sum = S.propCov[q] + fabs(x1 - x0);
+    if (ran % sp.adapt_interval == 0) {
+      double af = 1.0;
+      for (int i = 0; i < S.timesAdapted[q]; i++) af = af * 0.75;
+      double meanJump = sum / (double)ran;
+      S.scale[q] = width + (2 * meanJump - width) * af;
+      S.timesAdapted[q] += 1;
+      ran = 0; sum = 0.0;
+    }
+    S.timesRan[q] = ran;
+    S.propCov[q] = sum;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ wide kernels
 // (node tile x chain tile) evaluation of instances [lo,hi) (through idx if given) of one declaration.
 // MODE 0: per-chain partial sums of log-densities -> partials[tile][C]
@@ -712,6 +786,7 @@ __global__ void k_sampler_reset(DevTab T, int sid, SamplerDev S, const double* p
   if (gid >= (size_t)TT * T.C) return;
   S.scale[gid] = sp.scale;
   S.timesRan[gid] = 0; S.timesAccepted[gid] = 0; S.timesAdapted[gid] = 0;
+  if (sp.type == NIMB_SAMPLER_SLICE) S.propCov[gid] = 0.0;  // sumJumps
 }
 
 // chol(propCov) at reset: one block per chain (propCov is the same for all chains at reset)
@@ -1175,8 +1250,9 @@ static int validate_table(const nimb200_table* t) {
   }
   for (int s = 0; s < t->n_samplers; s++) {
     const nimb200_sampler& sp = t->samplers[s];
-    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_POSTERIOR_PREDICTIVE)
-      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta, posterior_predictive); there is no CPU fallback");
+    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_SLICE)
+      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta, posterior_predictive, slice); there is no CPU fallback");
+    if (sp.type == NIMB_SAMPLER_SLICE && (sp.tries < 1 || sp.pad < 1 || !(sp.scale > 0))) return fail("slice: sliceWidth, sliceMaxSteps and maxContractions must be positive");
     if (sp.type == NIMB_SAMPLER_RW_BLOCK && (sp.d < 1 || sp.d > NIMB200_MAX_BLOCK_D)) return fail("RW_block dimension out of range");
     if (sp.dep_off < 0 || sp.dep_off + sp.n_dep > t->n_deps || sp.n_dep < 1) return fail("sampler dependency range outside deps[]");
     if (t->deps[sp.dep_off].stage != 0) return fail("first dependency entry of a sampler must be the target's own declaration");
@@ -1450,6 +1526,9 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       TRY(dev_alloc(m, &S.empirSamp, (size_t)sp.adapt_interval * sp.d * C));
       TRYCU(cudaMemsetAsync(S.empirSamp, 0, sizeof(double) * sp.adapt_interval * sp.d * C, m->stream));
       m->wide[s] = 1;
+    } else if (sp.type == NIMB_SAMPLER_SLICE) {
+      TRY(dev_alloc(m, &S.propCov, (size_t)TT * C));  // sumJumps
+      if (dep_count_t0(m, sp) > 2048) { nimb200_model_free(m); return fail("slice sampler over more than 2048 dependents per target is not supported"); }
     } else if (sp.n_targets == 1 && sp.type != NIMB_SAMPLER_BINARY && dep_count_t0(m, sp) > 2048) {
       m->wide[s] = 1;
     }
@@ -1743,7 +1822,12 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const nimb200_sampler& sp = m->samplers[s];
   int C = m->C;
   const int TB = 128;
-  if (!m->wide[s] && m->bern_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
+  if (sp.type == NIMB_SAMPLER_SLICE) {
+    if (m->nranks > 1 && m->sweep_sharded[s]) return fail("slice sampler over data-sharded dependents is not supported");
+    size_t total = (size_t)sp.n_targets * C;
+    k_slice<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s]);
+    m->launches++;
+  } else if (!m->wide[s] && m->bern_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
     size_t total = (size_t)sp.n_targets * C;
     k_bernlin_binary_sweep<<<(unsigned)((total + BF_THREADS - 1) / BF_THREADS), BF_THREADS, 0, m->stream>>>(
         m->T, s, seed, iter, bern_args(m, m->deps[sp.dep_off].decl), bern_args(m, m->deps[sp.dep_off + 1].decl));

@@ -170,10 +170,13 @@ class MCMCconf:
         if decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0):
             self.samplerConfs.append(SamplerConf(T.SAMPLER_BINARY, decl.var, decl.pos, self.control_defaults))
             return
-        if decl.dist in (T.DPOIS, T.DBINOM, T.DCAT):
+        if decl.dist == T.DCAT:
             raise NotImplementedError(
-                "node %s: default sampler for a non-binary discrete node (slice / categorical) is not part of the "
-                "B200 sampling path; unknown samplers are a hard error, there is no CPU fallback" % decl.var)
+                "node %s: the default sampler of a dcat node (categorical) is not part of the B200 sampling path; "
+                "unknown samplers are a hard error, there is no CPU fallback" % decl.var)
+        if decl.dist in (T.DPOIS, T.DBINOM):  # other discrete nodes: slice, MCMC_configuration.R:428
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_SLICE, decl.var, decl.pos, self.control_defaults))
+            return
         self.samplerConfs.append(SamplerConf(T.SAMPLER_RW, decl.var, decl.pos, self.control_defaults))
 
     def _resolve_target(self, target):
@@ -233,6 +236,10 @@ class MCMCconf:
                 if conj is None:
                     raise ValueError("no conjugate relationship found for %s" % var)
                 self.samplerConfs.append(SamplerConf(conj[0], var, pos, ctrl, conj=conj[1]))
+        elif tname == "slice":
+            if len(pos) > 1:
+                raise ValueError("cannot use slice sampler on more than one target node")  # MCMC_samplers.R:891
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_SLICE, var, pos, ctrl))
         elif tname == "posterior_predictive":
             for decl in self.model.decl_of(var):
                 if not self._is_terminal(decl):
@@ -243,7 +250,7 @@ class MCMCconf:
             self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl))
         else:
             raise NotImplementedError("sampler type %r is not part of the B200 sampling path (supported: RW, "
-                                      "RW_block, binary, conjugate, posterior_predictive); there is no CPU fallback" % type)
+                                      "RW_block, binary, conjugate, posterior_predictive, slice); there is no CPU fallback" % type)
         return self
 
     def removeSamplers(self, target=None):
@@ -573,6 +580,12 @@ class _Lowering:
         s.adapt_factor_exponent = float(ctl.get("adaptFactorExponent", 0.8))
         s.lower, s.upper = float(ctl.get("lower", -np.inf)), float(ctl.get("upper", np.inf))
         s.propcov_darr = -1
+        if sc.type == T.SAMPLER_SLICE:  # MCMC_samplers.R:869-874
+            s.scale = float(ctl.get("sliceWidth", 1.0))
+            s.tries = int(ctl.get("sliceMaxSteps", 100))
+            s.pad = int(ctl.get("maxContractions", 1000))
+            if s.scale <= 0 or s.tries < 1 or s.pad < 1:
+                raise ValueError("slice sampler: sliceWidth, sliceMaxSteps and maxContractions must be positive")
         if s.log_scale and s.reflective:
             raise ValueError("cannot use reflective RW sampler on a log scale (i.e. with options log=TRUE and reflective=TRUE")
         if s.adapt_factor_exponent < 0:

@@ -27,10 +27,11 @@ SEL_ALL, SEL_SAME, SEL_STRIDE, SEL_SEG, SEL_CSR, SEL_RANGE = 0, 1, 2, 3, 4, 5
 PARAM_RATE, PARAM_TAU = 16, 17
 LINK_IDENTITY, LINK_ADDITIVE, LINK_MULTIPLICATIVE, LINK_LINEAR = 0, 1, 2, 3
 SAMPLER_RW, SAMPLER_RW_BLOCK, SAMPLER_BINARY, SAMPLER_CONJ_GAMMA, SAMPLER_CONJ_NORMAL, SAMPLER_CONJ_BETA = 1, 2, 3, 4, 5, 6
-SAMPLER_POSTERIOR_PREDICTIVE = 7
+SAMPLER_POSTERIOR_PREDICTIVE, SAMPLER_SLICE = 7, 8
 SAMPLER_NAMES = {SAMPLER_RW: "RW", SAMPLER_RW_BLOCK: "RW_block", SAMPLER_BINARY: "binary",
                  SAMPLER_CONJ_GAMMA: "conjugate_dgamma", SAMPLER_CONJ_NORMAL: "conjugate_dnorm",
-                 SAMPLER_CONJ_BETA: "conjugate_dbeta", SAMPLER_POSTERIOR_PREDICTIVE: "posterior_predictive"}
+                 SAMPLER_CONJ_BETA: "conjugate_dbeta", SAMPLER_POSTERIOR_PREDICTIVE: "posterior_predictive",
+                 SAMPLER_SLICE: "slice"}
 
 
 class Op(C.Structure):

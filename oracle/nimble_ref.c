@@ -29,7 +29,7 @@
 #include "nmath_ref.h"
 
 typedef struct {
-  double scale, scale0, gamma1;
+  double scale, scale0, gamma1, sumJumps;
   long timesRan, timesAccepted, timesAdapted;
   double *propCov, *propCov0, *chol, *cholScale, *empirSamp; /* RW_block, column-major d x d / adaptInterval x d */
 } SState;
@@ -254,7 +254,7 @@ static void chol_upper(const double *A, double *U, int d) {
 }
 
 static void sampler_reset(const nimb200_sampler *sp, SState *s, int adaptInterval) {
-  s->scale = s->scale0; s->timesRan = s->timesAccepted = s->timesAdapted = 0; s->gamma1 = 0;
+  s->scale = s->scale0; s->timesRan = s->timesAccepted = s->timesAdapted = 0; s->gamma1 = 0; s->sumJumps = 0;
   if (sp->type == NIMB_SAMPLER_RW_BLOCK) {
     int d = sp->d, i;
     memcpy(s->propCov, s->propCov0, sizeof(double) * d * d);
@@ -489,6 +489,68 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
   copy_lp(m, c, sp, t, -1, 1);
 }
 
+/* sampler_slice::run (MCMC_samplers.R:893-938) with setAndCalculateTarget (:941-949) and adaptiveProcedure (:950-965).
+ * Uniforms from the sampler's counter: call 0 = (auxiliary exponential, interval offset), call 1 = (split of maxSteps, first
+ * candidate), call 2 + j = j-th shrinkage candidate.  getLogProb(calcNodes) is taken as (target) + (dependents). */
+static double slice_set_and_calc(ref_model *m, int c, const nimb200_sampler *sp, int t, int discrete, double value) {
+  double *st = m->state + (size_t)c * m->t.n_slots, lp;
+  st[sp->target_slot + t] = discrete ? floor(value) : value;
+  lp = calculate_deps(m, c, sp, t, 0);
+  if (lp == -INFINITY) return -INFINITY;
+  return lp + calculate_deps(m, c, sp, t, 1);
+}
+static void run_slice(ref_model *m, int c, int sid, int t, uint64_t seed, uint64_t iter) {
+  const nimb200_sampler *sp = m->t.samplers + sid;
+  double *st = m->state + (size_t)c * m->t.n_slots;
+  SState *S = m->ss[sid] + (size_t)t * m->C + c;
+  int slot = sp->target_slot + t;
+  int tdist = m->t.decl[m->t.deps[sp->dep_off].decl].dist;
+  int discrete = tdist == NIMB_DPOIS || tdist == NIMB_DBINOM || tdist == NIMB_DCAT;
+  uint32_t chain = (uint32_t)(m->first_chain + c);
+  const double eps = 1e-15, x0 = st[slot], width = S->scale;
+  double ua, ub, uc, ud, ue, uf, u, L, R, lp, x1, cur0;
+  int maxStepsL, maxStepsR, nc = 0;
+  ref_unif2(seed, chain, iter, sid, t, 0, &ua, &ub);
+  ref_unif2(seed, chain, iter, sid, t, 1, &uc, &ud);
+  cur0 = getLogProb_deps(m, c, sp, t, 0);
+  u = (cur0 == -INFINITY ? -INFINITY : cur0 + getLogProb_deps(m, c, sp, t, 1)) - (-ref_det_log(ua));
+  L = x0 - ub * width; R = L + width;
+  maxStepsL = (int)floor(uc * (double)sp->tries); maxStepsR = sp->tries - 1 - maxStepsL;
+  lp = slice_set_and_calc(m, c, sp, t, discrete, L);
+  while (maxStepsL > 0 && !isnan(lp) && lp >= u) { L = L - width; lp = slice_set_and_calc(m, c, sp, t, discrete, L); maxStepsL--; }
+  lp = slice_set_and_calc(m, c, sp, t, discrete, R);
+  while (maxStepsR > 0 && !isnan(lp) && lp >= u) { R = R + width; lp = slice_set_and_calc(m, c, sp, t, discrete, R); maxStepsR--; }
+  x1 = L + ud * (R - L);
+  lp = slice_set_and_calc(m, c, sp, t, discrete, x1);
+  while ((isnan(lp) || lp < u) && (R - L) / (fabs(R) + fabs(L) + eps) > eps && nc < sp->pad) {
+    if (x1 < x0) L = x1; else R = x1;
+    ref_unif2(seed, chain, iter, sid, t, 2 + nc, &ue, &uf);
+    x1 = L + ue * (R - L);
+    lp = slice_set_and_calc(m, c, sp, t, discrete, x1);
+    nc++;
+  }
+  if ((R - L) / (fabs(R) + fabs(L) + eps) <= eps || nc == sp->pad) {
+    copy_targets(m, c, sp, t, 0);
+    copy_lp(m, c, sp, t, -1, 0);
+    return;
+  }
+  copy_targets(m, c, sp, t, 1);
+  copy_lp(m, c, sp, t, -1, 1);
+  if (sp->adaptive) {
+    S->timesRan++;
+    S->sumJumps += fabs(x1 - x0);
+    if (S->timesRan % sp->adapt_interval == 0) {
+      double af = 1.0, meanJump;
+      long i;
+      for (i = 0; i < S->timesAdapted; i++) af = af * 0.75;
+      meanJump = S->sumJumps / (double)S->timesRan;
+      S->scale = width + (2 * meanJump - width) * af;
+      S->timesAdapted++;
+      S->timesRan = 0; S->sumJumps = 0;
+    }
+  }
+}
+
 /* sampler_posterior_predictive::run (MCMC_samplers.R:97-101) for a terminal node: model$simulate(target), calculate, copy.
  * The variate generators are the counter-based ones of draws_ref.c (call 0.. of the sampler's counter), not R's. */
 static int run_posterior_predictive(ref_model *m, int c, int sid, int t, uint64_t seed, uint64_t iter) {
@@ -704,6 +766,7 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
           case NIMB_SAMPLER_CONJ_GAMMA:
           case NIMB_SAMPLER_CONJ_NORMAL:
           case NIMB_SAMPLER_CONJ_BETA: for (t = 0; t < sp->n_targets; t++) run_conjugate(m, c, s, t, seed, git); break;
+          case NIMB_SAMPLER_SLICE: for (t = 0; t < sp->n_targets; t++) run_slice(m, c, s, t, seed, git); break;
           case NIMB_SAMPLER_POSTERIOR_PREDICTIVE:
             for (t = 0; t < sp->n_targets; t++) if (run_posterior_predictive(m, c, s, t, seed, git)) return 1;
             break;

@@ -137,6 +137,28 @@ def predictive_nodes():
     return m, nb.configureMCMC(m, monitors=["a", "pn", "pg", "pb", "pe", "pl", "pz"])
 
 
+def slice_targets():
+    """A discrete and a continuous node with known marginals under the slice sampler: x ~ Poisson(3.5), g ~ Gamma(3, rate 2)."""
+    m = nb.nimbleModel("{ x ~ dpois(3.5)\n g ~ dgamma(3, 2) }", inits={"x": 3.0, "g": 1.0})
+    conf = nb.configureMCMC(m, nodes=["x"])       # dpois end node: no device generator -> the discrete default, slice
+    conf.addSampler("g", type="slice")
+    return m, conf
+
+
+def latent_counts():
+    """N-mixture style model: latent Poisson counts (slice, the default for non-binary discrete nodes, MCMC_configuration.R:428)
+    under a binomial observation; gamma-Poisson and beta-binomial conjugacy on the latent layer."""
+    rng = np.random.default_rng(3)
+    Nt = rng.poisson(6.0, 12)
+    y = rng.binomial(Nt, 0.4).astype(float)
+    code = """{ lam ~ dgamma(2, 0.2)
+      p ~ dbeta(2, 2)
+      for (i in 1:12) { N[i] ~ dpois(lam)
+        y[i] ~ dbin(p, N[i]) } }"""
+    m = nb.nimbleModel(code, data={"y": y}, inits={"lam": 5.0, "p": 0.5, "N": y + 2})
+    return m, nb.configureMCMC(m, monitors=["lam", "p", "N"])
+
+
 def random_inits(model, nchains, seed, spread=0.3):
     """Positive, chain-specific perturbations of the model's inits (works for the models above)."""
     rng = np.random.default_rng(seed)

@@ -184,3 +184,21 @@ def test_posterior_predictive_matches_oracle(oracle, b200, nchains):
         so, sg = run(compile_on(oracle, conf), inits, 300, 0, seed=4), run(compile_on(b200, conf), inits, 300, 0, seed=4)
         assert np.all(np.isfinite(so))
         assert rel_err(sg, so).max() < RTOL_TRAJ
+
+
+@pytest.mark.parametrize("nchains", [3, 35])
+def test_slice_sampler_matches_oracle(oracle, b200, nchains):
+    """sampler_slice on the device (one thread per (target, chain), data-dependent stepping out and shrinkage) against the oracle:
+    same uniforms, same candidate sequence, same adapted widths -- for a discrete and a continuous target and for latent counts
+    under a binomial observation."""
+    for build in (sm.slice_targets, sm.latent_counts):
+        m, conf = build()
+        inits = np.tile(m.init_vector(), (nchains, 1))
+        co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+        so, sg = run(co, inits, 450, 0, seed=4), run(cg, inits, 450, 0, seed=4)
+        assert np.all(np.isfinite(so))
+        assert rel_err(sg, so).max() < RTOL_TRAJ
+        for s, sp in enumerate(co.builder.samplers):
+            if sp.type == T.SAMPLER_SLICE:
+                assert rel_err(cg.dm.sampler_state(s, 0), co.dm.sampler_state(s, 0)).max() < RTOL_TRAJ
+                assert np.array_equal(cg.dm.sampler_state(s, 1), co.dm.sampler_state(s, 1))

@@ -112,7 +112,7 @@ def test_errors_match_reference_behaviour():
     with pytest.raises(ValueError, match="more than one target"):      # MCMC_samplers.R:348
         conf.addSampler("theta", type="RW")
     with pytest.raises(NotImplementedError, match="no CPU fallback"):
-        conf.addSampler("alpha", type="slice")
+        conf.addSampler("alpha", type="AF_slice")
     with pytest.raises(nb.ModelError):
         conf.addSampler("nosuch", type="RW")
     with pytest.raises(RuntimeError, match="compileNimble"):

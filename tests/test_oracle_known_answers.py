@@ -160,3 +160,24 @@ def test_posterior_predictive_sampler(oracle):
     assert conf2.samplerConfs[-1].type == T.SAMPLER_POSTERIOR_PREDICTIVE
     with pytest.raises(ValueError, match="non-posterior-predictive"):
         conf2.addSampler("a", type="posterior_predictive")
+
+
+def test_slice_sampler(oracle):
+    """sampler_slice (MCMC_samplers.R:864-972), the default of non-binary discrete nodes."""
+    m, conf = sm.slice_targets()
+    assert [(s.name, s.var) for s in conf.samplerConfs] == [("slice", "x"), ("slice", "g")]
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 20000, 1000, seed=1))
+    assert np.all(s[:, 0] == np.floor(s[:, 0])) and s[:, 0].min() >= 0
+    assert abs(s[:, 0].mean() - 3.5) < 0.05 and abs(s[:, 0].var() - 3.5) < 0.15
+    assert abs(s[:, 1].mean() - 1.5) < 0.02 and abs(s[:, 1].var() - 0.75) < 0.04
+    w = cm.dm.sampler_state(1, 0)                       # adapted width -> 2 x mean jump (:950-958)
+    assert np.all((w > 1.2) & (w < 2.2)) and np.all(cm.dm.sampler_state(1, 1) == 20000 // 200)
+    m, conf = sm.latent_counts()
+    assert [(s.name, s.var) for s in conf.samplerConfs] == [("conjugate_dgamma", "lam"), ("conjugate_dbeta", "p"), ("slice", "N")]
+    cm = compile_on(oracle, conf)
+    s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 6000, 1000, seed=2))
+    N = s[:, 2:]
+    assert np.all(N == np.floor(N)) and 3 < s[:, 0].mean() < 12 and 0.2 < s[:, 1].mean() < 0.8
+    with pytest.raises(ValueError, match="more than one target"):
+        conf.addSampler("N[1:3]", type="slice")
