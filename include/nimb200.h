@@ -83,7 +83,10 @@ enum {
   NIMB_OP_ABS = 40,
   NIMB_OP_LOG1P = 41,
   NIMB_OP_ICLOGLOG = 42, /* 1-exp(-exp(x)) Utils.h:189 */
-  NIMB_OP_STEP = 43      /* x>=0 ? 1 : 0   Utils.h:199 */
+  NIMB_OP_STEP = 43,     /* x>=0 ? 1 : 0   Utils.h:199 */
+  /* dynamic indexing (mu[z[i]]): pop the 1-based index v; v an integer in [1, b] -> push the element, else NaN */
+  NIMB_OP_CVAR_IDX = 48, /* push state[a + v - 1] */
+  NIMB_OP_DATA_IDX = 49  /* push darr[a][v - 1] */
 };
 
 /* index modes for NIMB_OP_DATA / NIMB_OP_CVARN: node index i -> element index */
@@ -168,6 +171,8 @@ enum {
   NIMB_SAMPLER_CONJ_BETA = 6,   /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
   NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7, /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
                                             distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbern) and recalculate it */
+  NIMB_SAMPLER_CATEGORICAL = 9, /* MCMC_samplers.R:162-226: dcat target with K <= NIMB200_MAX_CATEGORIES categories: the conditional
+                                   log-density of every category, then rcat (dists.cpp:936-961) on exp(logProb - max) */
   NIMB_SAMPLER_SLICE = 8 /* MCMC_samplers.R:864-972: stepping-out / shrinkage slice sampler with width adaptation; discrete
                             targets (dpois, dbin, dcat) are floored.  scale = sliceWidth, tries = sliceMaxSteps,
                             pad = maxContractions, adaptive / adapt_interval as for RW */
@@ -298,6 +303,7 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
  * resident on every GPU that loaded the library; the first call on a device looks its address up, so make that call
  * before starting any stream capture; calls share the array, so calls that overlap on one GPU race (each call
  * rewrites all of the array it reads, nothing needs clearing in between).  Calls no cudaMalloc/cudaFree. */
+#define NIMB200_MAX_CATEGORIES 64 /* categorical sampler: categories per target */
 #define NIMB200_NOALLOC_MAX_CHAINS 2048
 int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
                                              const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);

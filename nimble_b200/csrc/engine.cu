@@ -66,6 +66,16 @@ __device__ double eval_prog(const DevTab& T, int c, int off, int len, int i, int
       case NIMB_OP_CONST: stk[sp++] = o.k; break;
       case NIMB_OP_DATA: stk[sp++] = T.darr[o.a][idx_of(T, o.b, o.c, i)]; break;
       case NIMB_OP_CVAR: stk[sp++] = ld_state(T, o.a, c, ov_slot, ov_val); break;
+      case NIMB_OP_CVAR_IDX: {
+        double v = stk[sp - 1];
+        stk[sp - 1] = (v >= 1.0 && v <= (double)o.b && v == floor(v)) ? ld_state(T, o.a + (int)v - 1, c, ov_slot, ov_val) : NAN;
+        break;
+      }
+      case NIMB_OP_DATA_IDX: {
+        double v = stk[sp - 1];
+        stk[sp - 1] = (v >= 1.0 && v <= (double)o.b && v == floor(v)) ? T.darr[o.a][(int)v - 1] : NAN;
+        break;
+      }
       case NIMB_OP_CVARN: stk[sp++] = ld_state(T, o.a + idx_of(T, o.b, o.c, i), c, ov_slot, ov_val); break;
       case NIMB_OP_INPROD: {
         const double* x = T.darr[o.a] + (size_t)i * o.c;
@@ -545,6 +555,40 @@ __global__ void k_slice(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
     S.timesRan[q] = ran;
     S.propCov[q] = sum;
   }
+}
+
+// sampler_categorical (MCMC_samplers.R:187-216), one thread per (target, chain): logProbs[i] for every category i (the current
+// one included: the state is up to date, so recomputing equals getLogProb), -Inf for a -Inf or NaN prior or a NaN total, then
+// probs = exp(logProbs - max) and rcat's linear scan on u * sum(probs) (dists.cpp:953-959).  exp is the deterministic one of the
+// draw stream so that the scan compares the same bits on both sides.
+__global__ void k_categorical(DevTab T, int sid, uint64_t seed, uint64_t iter) {
+  const nimb200_sampler sp = T.samplers[sid];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = (int)(gid % T.C);
+  size_t tq = gid / T.C;
+  if (tq >= (size_t)sp.n_targets) return;
+  int t = (int)tq, slot = sp.target_slot + t;
+  DrawKey key = make_key(T, seed, iter, sid, t, c);
+  double* sv = T.state + (size_t)slot * T.C + c;
+  const int K = T.decl[T.deps[sp.dep_off].decl].fam_arg[0];
+  double lps[NIMB200_MAX_CATEGORIES];
+  double maxLP = -INFINITY;
+  for (int i = 1; i <= K; i++) {
+    double lp = slice_lp(T, sp, t, c, slot, (double)i);  // prior first (-Inf short-circuits), then the dependents
+    if (isnan(lp)) lp = -INFINITY;
+    lps[i - 1] = lp;
+    maxLP = fmax(maxLP, lp);
+  }
+  double sum = 0.0;
+  for (int i = 0; i < K; i++) { lps[i] = det_exp(lps[i] - maxLP); sum += lps[i]; }
+  if (isnan(sum)) return;  // rcat gives NaN: newValue is NA, the state stays (MCMC_samplers.R:205)
+  double u, u2;
+  unif2(key, 0, u, u2);
+  u = u * sum;
+  double cum = lps[0];
+  int value = 1;
+  while (u > cum && value < K) { cum += lps[value]; value++; }
+  *sv = (double)value;
 }
 
 // ------------------------------------------------------------------------------------------------ wide kernels
@@ -1240,6 +1284,12 @@ static int validate_table(const nimb200_table* t) {
         int op = t->ops[d.prog_off[p] + q].op;
         if (op >= NIMB_OP_CONST && op <= NIMB_OP_CVARJ) depth++;
         else if (op >= NIMB_OP_ADD && op <= NIMB_OP_POW) depth--;
+        else if (op == NIMB_OP_CVAR_IDX || op == NIMB_OP_DATA_IDX) {
+          const nimb200_op& o = t->ops[d.prog_off[p] + q];
+          if (o.b < 1) return fail("dynamic index op: bad length");
+          if (op == NIMB_OP_CVAR_IDX && (o.a < 0 || o.a + o.b > t->n_slots)) return fail("dynamic index op: slots outside the chain state");
+          if (op == NIMB_OP_DATA_IDX && (o.a < 0 || o.a >= t->n_darr || t->darr_len[o.a] < o.b)) return fail("dynamic index op: array too short");
+        }
         else if (op < NIMB_OP_NEG || op > NIMB_OP_STEP) return fail("unknown op code in parameter program");
         maxd = std::max(maxd, depth);
         if (depth < 1) return fail("malformed parameter program (stack underflow)");
@@ -1250,12 +1300,17 @@ static int validate_table(const nimb200_table* t) {
   }
   for (int s = 0; s < t->n_samplers; s++) {
     const nimb200_sampler& sp = t->samplers[s];
-    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_SLICE)
-      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta, posterior_predictive, slice); there is no CPU fallback");
+    if (sp.type < NIMB_SAMPLER_RW || sp.type > NIMB_SAMPLER_CATEGORICAL)
+      return fail("unknown sampler type (supported: RW, RW_block, binary, conjugate dgamma/dnorm/dbeta, posterior_predictive, slice, categorical); there is no CPU fallback");
     if (sp.type == NIMB_SAMPLER_SLICE && (sp.tries < 1 || sp.pad < 1 || !(sp.scale > 0))) return fail("slice: sliceWidth, sliceMaxSteps and maxContractions must be positive");
     if (sp.type == NIMB_SAMPLER_RW_BLOCK && (sp.d < 1 || sp.d > NIMB200_MAX_BLOCK_D)) return fail("RW_block dimension out of range");
     if (sp.dep_off < 0 || sp.dep_off + sp.n_dep > t->n_deps || sp.n_dep < 1) return fail("sampler dependency range outside deps[]");
     if (t->deps[sp.dep_off].stage != 0) return fail("first dependency entry of a sampler must be the target's own declaration");
+    if (sp.type == NIMB_SAMPLER_CATEGORICAL) {
+      const nimb200_decl& cd = t->decl[t->deps[sp.dep_off].decl];
+      if (cd.dist != NIMB_DCAT || cd.fam_arg[0] < 1 || cd.fam_arg[0] > NIMB200_MAX_CATEGORIES)
+        return fail("categorical: the target must be a dcat node with at most 64 categories");
+    }
     if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {
       const nimb200_decl& pd = t->decl[t->deps[sp.dep_off].decl];
       const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP ||
@@ -1526,6 +1581,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       TRY(dev_alloc(m, &S.empirSamp, (size_t)sp.adapt_interval * sp.d * C));
       TRYCU(cudaMemsetAsync(S.empirSamp, 0, sizeof(double) * sp.adapt_interval * sp.d * C, m->stream));
       m->wide[s] = 1;
+    } else if (sp.type == NIMB_SAMPLER_CATEGORICAL) {
+      if (dep_count_t0(m, sp) > 2048) { nimb200_model_free(m); return fail("categorical sampler over more than 2048 dependents per target is not supported"); }
     } else if (sp.type == NIMB_SAMPLER_SLICE) {
       TRY(dev_alloc(m, &S.propCov, (size_t)TT * C));  // sumJumps
       if (dep_count_t0(m, sp) > 2048) { nimb200_model_free(m); return fail("slice sampler over more than 2048 dependents per target is not supported"); }
@@ -1822,7 +1879,12 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const nimb200_sampler& sp = m->samplers[s];
   int C = m->C;
   const int TB = 128;
-  if (sp.type == NIMB_SAMPLER_SLICE) {
+  if (sp.type == NIMB_SAMPLER_CATEGORICAL) {
+    if (m->nranks > 1 && m->sweep_sharded[s]) return fail("categorical sampler over data-sharded dependents is not supported");
+    size_t total = (size_t)sp.n_targets * C;
+    k_categorical<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter);
+    m->launches++;
+  } else if (sp.type == NIMB_SAMPLER_SLICE) {
     if (m->nranks > 1 && m->sweep_sharded[s]) return fail("slice sampler over data-sharded dependents is not supported");
     size_t total = (size_t)sp.n_targets * C;
     k_slice<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s]);

@@ -26,6 +26,12 @@ def _linear_form(tree, var):
         return (False, False)
     if k == "inprod":
         return (False, True)
+    if k == "dyn":
+        # mu[z[i]] as a function of one element of mu: that element (index equal) or another one -- offset and coefficient both
+        # depend on the node, found by the numerical probing; the index itself must not read the target
+        if tree_reads_var(tree[5], var):
+            return None
+        return (True, True)
     if k == "un" and tree[1] == T.OP_NEG:
         f = _linear_form(tree[2], var)
         return None if f in (None, "free") else (f[0], True)
@@ -170,10 +176,11 @@ class MCMCconf:
         if decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0):
             self.samplerConfs.append(SamplerConf(T.SAMPLER_BINARY, decl.var, decl.pos, self.control_defaults))
             return
-        if decl.dist == T.DCAT:
-            raise NotImplementedError(
-                "node %s: the default sampler of a dcat node (categorical) is not part of the B200 sampling path; "
-                "unknown samplers are a hard error, there is no CPU fallback" % decl.var)
+        if decl.dist == T.DCAT:  # MCMC_configuration.R:425
+            if decl.K > T.MAX_CATEGORIES:
+                raise NotImplementedError("node %s: categorical sampler supports at most %d categories" % (decl.var, T.MAX_CATEGORIES))
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_CATEGORICAL, decl.var, decl.pos, self.control_defaults))
+            return
         if decl.dist in (T.DPOIS, T.DBINOM):  # other discrete nodes: slice, MCMC_configuration.R:428
             self.samplerConfs.append(SamplerConf(T.SAMPLER_SLICE, decl.var, decl.pos, self.control_defaults))
             return
@@ -236,6 +243,12 @@ class MCMCconf:
                 if conj is None:
                     raise ValueError("no conjugate relationship found for %s" % var)
                 self.samplerConfs.append(SamplerConf(conj[0], var, pos, ctrl, conj=conj[1]))
+        elif tname == "categorical":
+            if len(pos) > 1:
+                raise ValueError("cannot use categorical sampler on more than one target node")  # MCMC_samplers.R:182
+            if any(d.dist != T.DCAT for d in self.model.decl_of(var)):
+                raise ValueError("Can only use categorical sampler on node with dcat distribution.")  # :183
+            self.samplerConfs.append(SamplerConf(T.SAMPLER_CATEGORICAL, var, pos, ctrl))
         elif tname == "slice":
             if len(pos) > 1:
                 raise ValueError("cannot use slice sampler on more than one target node")  # MCMC_samplers.R:891
@@ -250,7 +263,7 @@ class MCMCconf:
             self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl))
         else:
             raise NotImplementedError("sampler type %r is not part of the B200 sampling path (supported: RW, "
-                                      "RW_block, binary, conjugate, posterior_predictive, slice); there is no CPU fallback" % type)
+                                      "RW_block, binary, conjugate, posterior_predictive, slice, categorical); there is no CPU fallback" % type)
         return self
 
     def removeSamplers(self, target=None):
@@ -362,6 +375,12 @@ class _Lowering:
             ops.append((T.OP_DATAJ, self._darr(tree[1]), 0, tree[1].shape[1], 0.0))
         elif k == "cvarj":
             ops.append((T.OP_CVARJ, self.model.var_slot[tree[1]] + tree[2], 0, 0, 0.0))
+        elif k == "dyn":
+            self._flatten(tree[5], decl, ops)
+            if tree[1]:
+                ops.append((T.OP_CVAR_IDX, self.model.var_slot[tree[2]] + tree[3], tree[4], 0, 0.0))
+            else:
+                ops.append((T.OP_DATA_IDX, self._darr(tree[2]), tree[4], 0, 0.0))
         elif k == "un":
             self._flatten(tree[2], decl, ops)
             ops.append((tree[1], 0, 0, 0, 0.0))

@@ -65,6 +65,10 @@ def _collect_reads(tree, out):
         out.append((tree[2], ("block", tree[3], tree[4])))
     elif k == "cvarj":
         out.append((tree[1], ("block", tree[2], tree[3])))
+    elif k == "dyn":  # ("dyn", latent?, name | array, base, K, index tree): any element may be read, plus whatever the index reads
+        if tree[1]:
+            out.append((tree[2], ("block", tree[3], tree[4])))
+        _collect_reads(tree[5], out)
     elif k == "un":
         _collect_reads(tree[2], out)
     elif k == "bin":
@@ -234,6 +238,9 @@ class Model:
             name_, idx = e[1], e[2]
             if name_ in env and not idx:
                 return ("data", env[name_].astype(np.float64))
+            dyn = self._dynamic_index(name_, idx, env, n, depth)
+            if dyn is not None:
+                return dyn
             if name_ in self.var_slot:
                 ia = [self._index_array(x, env, n) for x in idx]
                 pos = self._positions(name_, ia, n)
@@ -254,6 +261,40 @@ class Model:
                 return ("data", vals)
             raise ModelError("variable %s is neither data, constant, nor defined in the model" % name_)
         raise ModelError("cannot lower expression %r" % (e,))
+
+    def _reads_latent(self, e):
+        """Does an index expression read a latent variable or a deterministic node (i.e. is it not static)?"""
+        k = e[0]
+        if k == "var":
+            if e[1] in self.var_slot or e[1] in self._determ:
+                return True
+            return any(self._reads_latent(x) for x in e[2] if x[0] != "range")
+        if k == "neg":
+            return self._reads_latent(e[1])
+        if k == "bin":
+            return self._reads_latent(e[2]) or self._reads_latent(e[3])
+        if k == "call":
+            return any(self._reads_latent(x) for x in e[2])
+        return False
+
+    def _dynamic_index(self, name_, idx, env, n, depth):
+        """mu[z[i]]: a vector (latent, constant or data) indexed by an expression that reads the chain state.  Returns
+        ("dyn", latent?, name | values, base position, K, index tree) or None when the index is static."""
+        if len(idx) != 1 or idx[0][0] == "range" or not self._reads_latent(idx[0]):
+            if any(x[0] != "range" and self._reads_latent(x) for x in idx):
+                raise ModelError("dynamic indexing is supported for vectors only: %s" % name_)
+            return None
+        itree = self._lower(idx[0], env, n, depth + 1)
+        if name_ in self.var_slot:
+            shape = self.var_shape[name_]
+            if len(shape) != 1:
+                raise ModelError("dynamic indexing is supported for vectors only: %s" % name_)
+            base = self._positions(name_, [np.full(1, 1, dtype=np.int64)], 1)
+            return ("dyn", True, name_, int(base[0]), int(shape[0]), itree)
+        src = self.constants.get(name_, self.data.get(name_))
+        if src is None or src.ndim != 1:
+            raise ModelError("dynamic indexing needs a latent, constant or data vector: %s" % name_)
+        return ("dyn", False, np.ascontiguousarray(src, dtype=np.float64), 0, int(src.size), itree)
 
     def _inline_determ(self, name_, idx, env, n, depth):
         """Replace a read of a deterministic node by its defining expression (links inverted)."""

@@ -18,6 +18,7 @@ DIST_NAMES = {DNORM: "dnorm", DGAMMA: "dgamma", DPOIS: "dpois", DBINOM: "dbinom"
               DLOGIS: "dlogis", DCAT: "dcat", DEXP: "dexp"}
 # ops
 OP_CONST, OP_DATA, OP_CVAR, OP_CVARN, OP_INPROD, OP_DATAJ, OP_CVARJ = 1, 2, 3, 4, 5, 6, 7
+OP_CVAR_IDX, OP_DATA_IDX = 48, 49
 OP_ADD, OP_SUB, OP_MUL, OP_DIV, OP_POW = 16, 17, 18, 19, 20
 OP_NEG, OP_EXP, OP_LOG, OP_SQRT, OP_ILOGIT, OP_LOGIT, OP_INV, OP_SQ, OP_ABS, OP_LOG1P, OP_ICLOGLOG, OP_STEP = (
     32, 33, 34, 35, 36, 37, 38, 39, 40, 41, 42, 43)
@@ -27,11 +28,12 @@ SEL_ALL, SEL_SAME, SEL_STRIDE, SEL_SEG, SEL_CSR, SEL_RANGE = 0, 1, 2, 3, 4, 5
 PARAM_RATE, PARAM_TAU = 16, 17
 LINK_IDENTITY, LINK_ADDITIVE, LINK_MULTIPLICATIVE, LINK_LINEAR = 0, 1, 2, 3
 SAMPLER_RW, SAMPLER_RW_BLOCK, SAMPLER_BINARY, SAMPLER_CONJ_GAMMA, SAMPLER_CONJ_NORMAL, SAMPLER_CONJ_BETA = 1, 2, 3, 4, 5, 6
-SAMPLER_POSTERIOR_PREDICTIVE, SAMPLER_SLICE = 7, 8
+SAMPLER_POSTERIOR_PREDICTIVE, SAMPLER_SLICE, SAMPLER_CATEGORICAL = 7, 8, 9
+MAX_CATEGORIES = 64
 SAMPLER_NAMES = {SAMPLER_RW: "RW", SAMPLER_RW_BLOCK: "RW_block", SAMPLER_BINARY: "binary",
                  SAMPLER_CONJ_GAMMA: "conjugate_dgamma", SAMPLER_CONJ_NORMAL: "conjugate_dnorm",
                  SAMPLER_CONJ_BETA: "conjugate_dbeta", SAMPLER_POSTERIOR_PREDICTIVE: "posterior_predictive",
-                 SAMPLER_SLICE: "slice"}
+                 SAMPLER_SLICE: "slice", SAMPLER_CATEGORICAL: "categorical"}
 
 
 class Op(C.Structure):

@@ -85,6 +85,16 @@ static double eval_prog(const ref_model *m, const double *st, int off, int len, 
       }
       case NIMB_OP_DATAJ: stk[sp++] = m->darr[o->a][(size_t)i * o->c + j]; break;
       case NIMB_OP_CVARJ: stk[sp++] = st[o->a + j]; break;
+      case NIMB_OP_CVAR_IDX: {
+        double v = stk[sp - 1];
+        stk[sp - 1] = (v >= 1.0 && v <= (double)o->b && v == floor(v)) ? st[o->a + (int)v - 1] : NAN;
+        break;
+      }
+      case NIMB_OP_DATA_IDX: {
+        double v = stk[sp - 1];
+        stk[sp - 1] = (v >= 1.0 && v <= (double)o->b && v == floor(v)) ? m->darr[o->a][(int)v - 1] : NAN;
+        break;
+      }
       case NIMB_OP_ADD: sp--; stk[sp - 1] = stk[sp - 1] + stk[sp]; break;
       case NIMB_OP_SUB: sp--; stk[sp - 1] = stk[sp - 1] - stk[sp]; break;
       case NIMB_OP_MUL: sp--; stk[sp - 1] = stk[sp - 1] * stk[sp]; break;
@@ -551,6 +561,32 @@ static void run_slice(ref_model *m, int c, int sid, int t, uint64_t seed, uint64
   }
 }
 
+/* sampler_categorical::run (MCMC_samplers.R:187-216); rcat: dists.cpp:936-961 with the uniform from the sampler's counter */
+static int run_categorical(ref_model *m, int c, int sid, int t, uint64_t seed, uint64_t iter) {
+  const nimb200_sampler *sp = m->t.samplers + sid;
+  double *st = m->state + (size_t)c * m->t.n_slots;
+  int slot = sp->target_slot + t, K = m->t.decl[m->t.deps[sp->dep_off].decl].fam_arg[0], i, value = 1;
+  double lps[NIMB200_MAX_CATEGORIES], maxLP = -INFINITY, sum = 0.0, u, u2, cum;
+  if (K > NIMB200_MAX_CATEGORIES) return fail("categorical: too many categories");
+  for (i = 1; i <= K; i++) {
+    double lp = slice_set_and_calc(m, c, sp, t, 0, (double)i);
+    if (isnan(lp)) lp = -INFINITY;
+    lps[i - 1] = lp;
+    maxLP = fmax(maxLP, lp);
+  }
+  for (i = 0; i < K; i++) { lps[i] = ref_det_exp(lps[i] - maxLP); sum += lps[i]; }
+  if (isnan(sum)) { copy_targets(m, c, sp, t, 0); calculate_deps(m, c, sp, t, -1); return 0; }
+  ref_unif2(seed, (uint32_t)(m->first_chain + c), iter, sid, t, 0, &u, &u2);
+  u = u * sum;
+  cum = lps[0];
+  while (u > cum && value < K) { cum += lps[value]; value++; }
+  st[slot] = (double)value;
+  calculate_deps(m, c, sp, t, -1);
+  copy_targets(m, c, sp, t, 1);
+  copy_lp(m, c, sp, t, -1, 1);
+  return 0;
+}
+
 /* sampler_posterior_predictive::run (MCMC_samplers.R:97-101) for a terminal node: model$simulate(target), calculate, copy.
  * The variate generators are the counter-based ones of draws_ref.c (call 0.. of the sampler's counter), not R's. */
 static int run_posterior_predictive(ref_model *m, int c, int sid, int t, uint64_t seed, uint64_t iter) {
@@ -767,6 +803,9 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
           case NIMB_SAMPLER_CONJ_NORMAL:
           case NIMB_SAMPLER_CONJ_BETA: for (t = 0; t < sp->n_targets; t++) run_conjugate(m, c, s, t, seed, git); break;
           case NIMB_SAMPLER_SLICE: for (t = 0; t < sp->n_targets; t++) run_slice(m, c, s, t, seed, git); break;
+          case NIMB_SAMPLER_CATEGORICAL:
+            for (t = 0; t < sp->n_targets; t++) if (run_categorical(m, c, s, t, seed, git)) return 1;
+            break;
           case NIMB_SAMPLER_POSTERIOR_PREDICTIVE:
             for (t = 0; t < sp->n_targets; t++) if (run_posterior_predictive(m, c, s, t, seed, git)) return 1;
             break;

@@ -159,6 +159,21 @@ def latent_counts():
     return m, nb.configureMCMC(m, monitors=["lam", "p", "N"])
 
 
+def gaussian_mixture():
+    """Finite mixture with latent labels: z[i] ~ dcat (categorical sampler, MCMC_configuration.R:425), dynamic indexing mu[z[i]]
+    into a latent vector and s[z[i]] into a constant one, conjugate normal updates of mu[k] whose dependents change with z."""
+    rng = np.random.default_rng(1)
+    zt = rng.integers(1, 4, 60)
+    mu_t = np.array([-4.0, 0.0, 5.0])
+    y = mu_t[zt - 1] + 0.7 * rng.standard_normal(60)
+    code = """{ for (k in 1:3) { mu[k] ~ dnorm(0, sd = 10) }
+      for (i in 1:60) { z[i] ~ dcat(w[1:3])
+        y[i] ~ dnorm(mu[z[i]], sd = s[z[i]]) } }"""
+    m = nb.nimbleModel(code, constants={"w": [0.3, 0.3, 0.4], "s": [0.7, 0.6, 0.8]}, data={"y": y},
+                       inits={"mu": [-1.0, 0.0, 1.0], "z": np.ones(60)})
+    return m, nb.configureMCMC(m, monitors=["mu", "z"]), (mu_t, zt)
+
+
 def random_inits(model, nchains, seed, spread=0.3):
     """Positive, chain-specific perturbations of the model's inits (works for the models above)."""
     rng = np.random.default_rng(seed)

@@ -202,3 +202,23 @@ def test_slice_sampler_matches_oracle(oracle, b200, nchains):
             if sp.type == T.SAMPLER_SLICE:
                 assert rel_err(cg.dm.sampler_state(s, 0), co.dm.sampler_state(s, 0)).max() < RTOL_TRAJ
                 assert np.array_equal(cg.dm.sampler_state(s, 1), co.dm.sampler_state(s, 1))
+
+
+@pytest.mark.parametrize("nchains", [2, 33])
+def test_categorical_sampler_and_dynamic_indexing_match_oracle(oracle, b200, nchains):
+    """Mixture labels drawn by the device categorical sampler equal the oracle's draw for draw; so do the conjugate updates of
+    the component means, whose dependents are found through mu[z[i]] at run time."""
+    m, conf, _ = sm.gaussian_mixture()
+    inits = np.tile(m.init_vector(), (nchains, 1))
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, inits, 300, 0, seed=6), run(cg, inits, 300, 0, seed=6)
+    assert np.array_equal(sg[:, :, 3:], so[:, :, 3:])          # labels: exact
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    y = len(cg.builder.decls) - 1
+    assert rel_err(cg.dm.calculate(y), co.dm.calculate(y)).max() < RTOL_LP
+    bad = inits.copy()
+    bad[0, m.var_slot["z"]] = 7.0                               # label outside 1..K: the indexed read is NaN on both sides
+    co.dm.set_values(bad)
+    cg.dm.set_values(bad)
+    a, b = cg.dm.calculate(y), co.dm.calculate(y)
+    assert np.isnan(a[0]) and np.isnan(b[0]) and rel_err(a[1:], b[1:]).max() < RTOL_LP

@@ -181,3 +181,26 @@ def test_slice_sampler(oracle):
     assert np.all(N == np.floor(N)) and 3 < s[:, 0].mean() < 12 and 0.2 < s[:, 1].mean() < 0.8
     with pytest.raises(ValueError, match="more than one target"):
         conf.addSampler("N[1:3]", type="slice")
+
+
+def test_categorical_sampler_and_dynamic_indexing(oracle):
+    """sampler_categorical (MCMC_samplers.R:162-226) on latent mixture labels; the dependents read
+    mu[z[i]] / s[z[i]] through the dynamic-index ops, and mu[k] stays conjugate (offset / coefficient found by probing)."""
+    from nimble_b200 import table as T
+    m, conf, (mu_t, zt) = sm.gaussian_mixture()
+    assert [(s.name, s.var, len(s.positions)) for s in conf.samplerConfs] == [("conjugate_dnorm", "mu", 3), ("categorical", "z", 60)]
+    cm = compile_on(oracle, conf)
+    ops = [o[0] for o in cm.builder.ops]
+    assert T.OP_CVAR_IDX in ops and T.OP_DATA_IDX in ops
+    assert [(s.type, s.n_targets) for s in cm.builder.samplers] == [(T.SAMPLER_CONJ_NORMAL, 1)] * 3 + [(T.SAMPLER_CATEGORICAL, 60)]
+    s = run(cm, np.tile(m.init_vector(), (2, 1)), 1500, 500, seed=1)
+    for ch in s:                                             # per chain: the labelling is only defined up to a permutation
+        mu, z = ch[:, :3].mean(0), np.round(np.median(ch[:, 3:], axis=0)).astype(int)
+        order = np.argsort(mu)
+        assert np.allclose(mu[order], mu_t, atol=0.5)
+        relabel = np.empty(3, dtype=int)
+        relabel[order] = np.arange(1, 4)
+        assert (relabel[z - 1] == zt).mean() > 0.95
+        assert set(np.unique(ch[:, 3:])) <= {1.0, 2.0, 3.0}
+    with pytest.raises(ValueError, match="dcat"):
+        conf.addSampler("mu[1]", type="categorical")
