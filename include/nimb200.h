@@ -308,6 +308,12 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
 int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
                                              const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);
 
+/* initializeModel (P/R/initializeModel.R:78-139): every non-data stochastic node whose value is NaN (a missing initial value)
+ * is simulated from its own distribution given its parents, declaration by declaration in the order given (parents first);
+ * variates come from the counter (seed, chain; iteration 0, sampler id 0x7fff0000 + declaration, target = node).  Supported
+ * for dnorm, dgamma, dbeta, dexp, dlogis and dbern nodes; a NaN left in any other declaration is an error. */
+int nimb200_initialize_model(nimb200_model *m, const int32_t *decl_order, int32_t n_order, uint64_t seed);
+
 /* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1), gamma(shape a, scale 1)
  * variates (kind 2) or beta(a, 1 + a/2) variates (kind 3) that sampler `sampler` would consume on the device for (chain, iter, target), so the
  * host can replay identical draws into another implementation. */

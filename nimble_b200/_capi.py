@@ -56,6 +56,7 @@ class Backend:
         self._run = fn("mcmc_run", [vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_uint64])
         self._samples = fn("mcmc_samples", [vp, _dp, C.POINTER(C.c_int64)])
         self._sstate = fn("sampler_state", [vp, C.c_int32, C.c_int32, _dp, C.c_int64])
+        self._init_model = fn("initialize_model", [vp, C.POINTER(C.c_int32), C.c_int32, C.c_uint64])
         self._draws = fn("draws", [C.c_uint64, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double,
                                    C.c_int32, _dp])
         if has_device:
@@ -152,6 +153,12 @@ class DeviceModel:
         out = np.empty(self.C)
         self.backend.check(self.backend._get_lp(self.h, decl, _ptr(out)))
         return out
+
+    def initialize_model(self, decl_order, seed=0):
+        """Simulate the non-data nodes whose value is NaN, declaration by declaration in `decl_order` (parents first)."""
+        order = np.ascontiguousarray(decl_order, dtype=np.int32)
+        self.backend.check(self.backend._init_model(self.h, order.ctypes.data_as(C.POINTER(C.c_int32)), int(order.size),
+                                                    int(seed)))
 
     def run(self, niter, nburnin=0, thin=1, reset=True, seed=0):
         self.backend.check(self.backend._run(self.h, niter, nburnin, thin, 1 if reset else 0, seed))

@@ -591,6 +591,37 @@ __global__ void k_categorical(DevTab T, int sid, uint64_t seed, uint64_t iter) {
   *sv = (double)value;
 }
 
+// initializeModel: simulate missing (NaN) values of one latent declaration from its own distribution (see nimb200.h)
+__device__ __forceinline__ bool simulate_node(const DevTab& T, int di, int node, int c, const DrawKey& key, double& nv) {
+  const nimb200_decl& d = T.decl[di];
+  const double p0 = get_param(T, di, node, c, 0, -1, 0.0);
+  const double p1 = d.nparam > 1 ? get_param(T, di, node, c, 1, -1, 0.0) : 0.0;
+  double u, u2;
+  switch (d.dist) {
+    case NIMB_DNORM: normal2(key, 0, u, u2); nv = p0 + p1 * u; return true;
+    case NIMB_DGAMMA: nv = rgamma1(key, p0) * p1; return true;
+    case NIMB_DBETA: nv = rbeta1(key, p0, p1); return true;
+    case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; return true;
+    case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); return true;
+    case NIMB_DBINOM:
+      if (p0 != 1.0) return false;
+      unif2(key, 0, u, u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); return true;
+  }
+  return false;
+}
+__global__ void k_init_simulate(DevTab T, int di, uint64_t seed, int* fail_flag) {
+  const nimb200_decl& d = T.decl[di];
+  size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (size_t)d.n * T.C) return;
+  int c = (int)(gid % T.C), node = (int)(gid / T.C);
+  double* sv = T.state + (size_t)(d.value_ref + node) * T.C + c;
+  if (!isnan(*sv)) return;
+  DrawKey key; key.seed = seed; key.chain = (uint32_t)(T.first_chain + c); key.iter = 0;
+  key.sampler = 0x7fff0000u + (uint32_t)di; key.target = (uint32_t)node;
+  double nv;
+  if (simulate_node(T, di, node, c, key, nv)) *sv = nv; else atomicExch(fail_flag, di + 1);
+}
+
 // ------------------------------------------------------------------------------------------------ wide kernels
 // (node tile x chain tile) evaluation of instances [lo,hi) (through idx if given) of one declaration.
 // MODE 0: per-chain partial sums of log-densities -> partials[tile][C]
@@ -2167,6 +2198,29 @@ extern "C" int nimb200_sampler_state(nimb200_model* m, int32_t s, int32_t what, 
   if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
   if (tmp) cudaFree(tmp);
   if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_initialize_model(nimb200_model* m, const int32_t* decl_order, int32_t n_order, uint64_t seed) {
+  if (!m || (!decl_order && n_order > 0) || n_order < 0) return fail("bad argument");
+  CK(cudaSetDevice(m->device));
+  int* d_flag = (int*)m->d_ticket;  // free between runs: the monitor kernel leaves it at zero
+  CK(cudaMemsetAsync(d_flag, 0, sizeof(int), m->stream));
+  for (int q = 0; q < n_order; q++) {
+    int di = decl_order[q];
+    if (di < 0 || di >= (int)m->decl.size()) return fail("declaration index out of range");
+    const nimb200_decl& d = m->decl[di];
+    if (d.value_kind != 1 || d.n == 0) continue;
+    size_t total = (size_t)d.n * m->C;
+    k_init_simulate<<<(unsigned)((total + 127) / 128), 128, 0, m->stream>>>(m->T, di, seed, d_flag);
+  }
+  int flag = 0;
+  CK(cudaMemcpyAsync(&flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  CK(cudaMemsetAsync(d_flag, 0, sizeof(int), m->stream));
+  if (flag) return fail("initializeModel: a missing initial value cannot be simulated (declaration " + std::to_string(flag - 1) +
+                        ": only dnorm, dgamma, dbeta, dexp, dlogis and dbern nodes can)");
+  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   return 0;
 }
 

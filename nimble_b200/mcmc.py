@@ -812,11 +812,26 @@ class CompiledMCMC:
         dm = self._ensure(inits_matrix.shape[0])
         if reset:
             dm.set_values(inits_matrix)
+            if np.any(np.isnan(inits_matrix)):
+                self._simulate_missing_inits(dm, inits_matrix, int(seed))
         if self.check_initial_logprobs:
             self._initialize_model_checks(dm)
         dm.run(int(niter), int(nburnin), int(thin), reset, int(seed))
         self.mvSamples = dm.samples()
         return self.mvSamples
+
+    def _simulate_missing_inits(self, dm, inits_matrix, seed):
+        """initializeModel (P/R/initializeModel.R:78-139): NA non-data nodes are simulated from their distributions, parents
+        first.  Refused up front when a variable with missing values has no device variate generator."""
+        model = self.model
+        missing = [v for v, s0 in model.var_slot.items()
+                   if np.any(np.isnan(inits_matrix[:, s0:s0 + (int(np.prod(model.var_shape[v])) if model.var_shape[v] else 1)]))]
+        bad = [v for v in missing if not model.simulable(v)]
+        if bad:
+            raise ModelError("initial values are required for %s: missing values can only be simulated for dnorm, dgamma, dbeta, "
+                             "dexp, dlogis and dbern nodes" % ", ".join(bad))
+        order = [self.lowering.decl_ids[d.index] for v in model.topo_vars() for d in model.decl_of(v)]
+        dm.initialize_model(order, seed)
 
     def _initialize_model_checks(self, dm):
         """The warnings of initializeModel (P/R/initializeModel.R:97-139): every declaration is calculated once for every

@@ -515,11 +515,14 @@ class Model:
             if name_ in vals:
                 v = np.asarray(vals[name_], dtype=np.float64)
                 out[slot:slot + size] = v.reshape(-1, order="F") if v.size == size else np.broadcast_to(v, size)
-        if np.any(np.isnan(out)):
-            missing = [n_ for n_, s in self.var_slot.items() if np.isnan(out[s])]
-            raise ModelError("initial values are required for every non-data stochastic node; missing: %s"
-                             % ", ".join(missing))
+        # missing values stay NaN (NA): initializeModel simulates them from their distributions before sampling starts
+        # (P/R/initializeModel.R:78-139; CompiledMCMC.run_chains -> nimb200_initialize_model)
         return out
+
+    def simulable(self, var):
+        """Can missing values of `var` be simulated on the device (a variate generator exists for its distribution)?"""
+        return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS) or
+                   (d.dist == T.DBINOM and d.params[0] == ("const", 1.0)) for d in self.decl_of(var))
 
 
 def nimbleCode(text):

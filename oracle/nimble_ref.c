@@ -876,6 +876,42 @@ int ref_sampler_state(ref_model *m, int32_t s, int32_t what, double *out, int64_
 
 uint64_t ref_eval_count(ref_model *m) { uint64_t v = m->evals + tl_evals; return v; }
 
+/* initializeModel: see nimb200_initialize_model in include/nimb200.h (initializeModel.R:78-139) */
+int ref_initialize_model(ref_model *m, const int32_t *decl_order, int32_t n_order, uint64_t seed) {
+  int q, c, node;
+  for (q = 0; q < n_order; q++) {
+    int di = decl_order[q];
+    const nimb200_decl *d;
+    if (di < 0 || di >= m->t.n_decl) return fail("declaration index out of range");
+    d = m->t.decl + di;
+    if (d->value_kind != 1) continue;
+    for (c = 0; c < m->C; c++) {
+      double *st = m->state + (size_t)c * m->t.n_slots;
+      uint32_t chain = (uint32_t)(m->first_chain + c);
+      for (node = 0; node < d->n; node++) {
+        double p0, p1, u, u2, nv;
+        uint32_t sid = 0x7fff0000u + (uint32_t)di;
+        if (!isnan(st[d->value_ref + node])) continue;
+        p0 = get_param(m, st, di, node, 0);
+        p1 = d->nparam > 1 ? get_param(m, st, di, node, 1) : 0.0;
+        switch (d->dist) {
+          case NIMB_DNORM: ref_normal2(seed, chain, 0, sid, node, 0, &u, &u2); nv = p0 + p1 * u; break;
+          case NIMB_DGAMMA: nv = ref_rgamma(seed, chain, 0, sid, node, p0) * p1; break;
+          case NIMB_DBETA: nv = ref_rbeta(seed, chain, 0, sid, node, p0, p1); break;
+          case NIMB_DEXP: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
+          case NIMB_DLOGIS: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
+          case NIMB_DBINOM:
+            if (p0 != 1.0) return fail("initializeModel: a missing initial value cannot be simulated");
+            ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+          default: return fail("initializeModel: a missing initial value cannot be simulated");
+        }
+        st[d->value_ref + node] = nv;
+      }
+    }
+  }
+  return 0;
+}
+
 int ref_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target, int32_t kind, double a,
               int32_t n, double *out) {
   int k;

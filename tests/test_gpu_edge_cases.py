@@ -222,3 +222,16 @@ def test_categorical_sampler_and_dynamic_indexing_match_oracle(oracle, b200, nch
     cg.dm.set_values(bad)
     a, b = cg.dm.calculate(y), co.dm.calculate(y)
     assert np.isnan(a[0]) and np.isnan(b[0]) and rel_err(a[1:], b[1:]).max() < RTOL_LP
+
+
+def test_missing_initial_values_simulated_like_the_oracle(oracle, b200):
+    """initializeModel on the device: NaN slots are simulated from the same counter-based variates, parents first, and the run
+    that follows is the oracle's run."""
+    from tests.test_oracle_known_answers import _missing_inits_model
+    m, conf = _missing_inits_model()
+    init = np.tile(m.init_vector(), (37, 1))
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    so, sg = run(co, init, 120, 0, seed=11), run(cg, init, 120, 0, seed=11)
+    assert np.all(np.isfinite(so)) and rel_err(sg, so).max() < RTOL_TRAJ
+    run(co, init, 0, 0, seed=5), run(cg, init, 0, 0, seed=5)
+    assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < 1e-15

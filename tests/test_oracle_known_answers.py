@@ -204,3 +204,37 @@ def test_categorical_sampler_and_dynamic_indexing(oracle):
         assert set(np.unique(ch[:, 3:])) <= {1.0, 2.0, 3.0}
     with pytest.raises(ValueError, match="dcat"):
         conf.addSampler("mu[1]", type="categorical")
+
+
+def _missing_inits_model():
+    code = """{ mu ~ dnorm(3, sd = 0.01)
+      s ~ dgamma(400, 200)
+      q ~ dbeta(200, 200)
+      for (g in 1:5) { u[g] ~ dnorm(mu, sd = 0.01) }
+      for (i in 1:20) { y[i] ~ dnorm(u[grp[i]], sd = s) }
+      k ~ dbern(q) }"""
+    m = nb.nimbleModel(code, constants={"grp": np.repeat(np.arange(1, 6), 4)}, data={"y": np.linspace(2, 4, 20)},
+                       inits={"s": 2.0})
+    return m, nb.configureMCMC(m, monitors=["mu", "s", "q", "u", "k"])
+
+
+def test_missing_initial_values_are_simulated(oracle):
+    """initializeModel (P/R/initializeModel.R:78-139): NA non-data nodes are simulated from their distributions, parents first;
+    given values are kept; a node without a variate generator must be given."""
+    m, conf = _missing_inits_model()
+    cm = compile_on(oracle, conf)
+    init = np.tile(m.init_vector(), (200, 1))
+    assert np.isnan(init[0, m.var_slot["mu"]]) and init[0, m.var_slot["s"]] == 2.0
+    run(cm, init, 0, 0, seed=3)
+    v = cm.dm.get_values()
+    mu, u = v[:, m.var_slot["mu"]], v[:, m.var_slot["u"]:m.var_slot["u"] + 5]
+    assert np.all(np.isfinite(v)) and np.all(v[:, m.var_slot["s"]] == 2.0)
+    assert abs(mu.mean() - 3) < 0.005 and 0.005 < mu.std() < 0.02
+    assert np.abs(u - mu[:, None]).max() < 0.06 and np.abs(u - 3).max() > np.abs(u - mu[:, None]).mean()   # children follow their own chain's parent
+    assert abs(v[:, m.var_slot["q"]].mean() - 0.5) < 0.01 and set(np.unique(v[:, m.var_slot["k"]])) == {0.0, 1.0}
+    again = compile_on(oracle, conf)
+    run(again, init, 0, 0, seed=3)
+    assert np.array_equal(again.dm.get_values(), v)                   # same seed, same simulated inits
+    m2 = nb.nimbleModel("{ lam ~ dgamma(2, 1)\n n ~ dpois(lam)\n y ~ dbin(0.5, n) }", data={"y": 2.0}, inits={"lam": 3.0})
+    with pytest.raises(nb.ModelError, match="initial values are required for n"):
+        run(compile_on(oracle, nb.configureMCMC(m2)), np.tile(m2.init_vector(), (2, 1)), 5, 0, seed=1)
