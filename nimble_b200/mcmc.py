@@ -139,11 +139,14 @@ class MCMCconf:
     """MCMCconf: the ordered sampler list and the monitors (P/R/MCMC_configuration.R:73)."""
 
     def __init__(self, model, monitors=None, thin=1, useConjugacy=True, nodes=None, control=None,
-                 multivariateNodesAsScalars=False, autoBlock=False):
+                 multivariateNodesAsScalars=False, autoBlock=False, monitors2=None, thin2=1):
         if autoBlock:
             raise NotImplementedError("autoBlock is outside the B200 sampling path")
         self.model, self.thin, self.samplerConfs = model, thin, []
         self.monitors = list(monitors) if monitors is not None else model.top_level_vars()
+        # second monitor set with its own thinning interval -> mvSamples2 (MCMC_configuration.R `monitors2`, `thin2`)
+        self.monitors2 = [monitors2] if isinstance(monitors2, str) else list(monitors2 or [])
+        self.thin2 = thin2
         self.control_defaults = dict(control or {})
         use = set(nodes) if nodes is not None else None
         for var in model.topo_vars():
@@ -292,6 +295,21 @@ class MCMCconf:
             for x in ([n_] if isinstance(n_, str) else n_):
                 if x not in self.monitors:
                     self.monitors.append(x)
+        return self
+
+    def addMonitors2(self, *names):
+        for n_ in names:
+            for x in ([n_] if isinstance(n_, str) else n_):
+                if x not in self.monitors2:
+                    self.monitors2.append(x)
+        return self
+
+    def setThin(self, thin):
+        self.thin = thin
+        return self
+
+    def setThin2(self, thin2):
+        self.thin2 = thin2
         return self
 
     def setMonitors(self, *names):
@@ -725,13 +743,26 @@ class _Lowering:
             else:
                 for p in sc.positions:
                     self._emit_sampler(sc, np.array([p]), False)
-        for name_ in self.conf.monitors:
-            if name_ not in model.var_slot:
-                raise ModelError("monitor %s is not a stochastic non-data variable of the model" % name_)
-            shape = model.var_shape[name_]
-            size = int(np.prod(shape)) if shape else 1
-            b.monitors.extend(range(model.var_slot[name_], model.var_slot[name_] + size))
-            self.colnames.extend(model.element_names(name_, np.arange(size)))
+        # the device records ONE set of columns: monitors, then those of monitors2 that are not among them; run_chains splits
+        # the rows and columns into mvSamples / mvSamples2 again
+        self.cols1, self.cols2, self.colnames2 = [], [], []
+        seen = {}
+        for which, names in ((1, self.conf.monitors), (2, getattr(self.conf, "monitors2", []))):
+            for name_ in names:
+                if name_ not in model.var_slot:
+                    raise ModelError("monitor %s is not a stochastic non-data variable of the model" % name_)
+                shape = model.var_shape[name_]
+                size = int(np.prod(shape)) if shape else 1
+                if name_ not in seen:
+                    seen[name_] = len(b.monitors)
+                    b.monitors.extend(range(model.var_slot[name_], model.var_slot[name_] + size))
+                cols = list(range(seen[name_], seen[name_] + size))
+                if which == 1:
+                    self.cols1.extend(cols)
+                    self.colnames.extend(model.element_names(name_, np.arange(size)))
+                else:
+                    self.cols2.extend(cols)
+                    self.colnames2.extend(model.element_names(name_, np.arange(size)))
         return b
 
 
@@ -742,7 +773,8 @@ class MCMC:
 
     def __init__(self, conf):
         self.conf, self.model = conf, conf.model
-        self.monitors, self.thinFromConfVec = list(conf.monitors), [conf.thin, conf.thin]
+        self.monitors, self.monitors2 = list(conf.monitors), list(getattr(conf, "monitors2", []))
+        self.thinFromConfVec = [conf.thin, getattr(conf, "thin2", conf.thin)]
 
     def run(self, *a, **k):
         raise RuntimeError("uncompiled MCMC execution is not available in the B200 back end; call compileNimble() first")
@@ -781,7 +813,8 @@ class CompiledMCMC:
         self.device, self.first_chain = device, first_chain
         self.lowering = _Lowering(self.model, self.conf)
         self.builder = self.lowering.run()
-        self.colnames = self.lowering.colnames
+        self.colnames, self.colnames2 = self.lowering.colnames, self.lowering.colnames2
+        self.mvSamples2 = None
         self.thinFromConfVec = mcmc.thinFromConfVec
         self.dm = None
         self.mvSamples = None
@@ -794,7 +827,7 @@ class CompiledMCMC:
             self.dm = _capi.DeviceModel(self.backend, self.builder, nchains, self.first_chain, self.device)
         return self.dm
 
-    def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0):
+    def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0, thin2=None):
         """All chains at once.  inits_matrix: [nchains][n_slots] (ignored when reset is False)."""
         if niter < 0:
             raise ValueError("cannot specify niter < 0")
@@ -816,8 +849,26 @@ class CompiledMCMC:
                 self._simulate_missing_inits(dm, inits_matrix, int(seed))
         if self.check_initial_logprobs:
             self._initialize_model_checks(dm)
-        dm.run(int(niter), int(nburnin), int(thin), reset, int(seed))
-        self.mvSamples = dm.samples()
+        low = self.lowering
+        if not low.cols2:
+            dm.run(int(niter), int(nburnin), int(thin), reset, int(seed))
+            self.mvSamples = dm.samples()
+            return self.mvSamples
+        # monitors2 / thin2 (MCMC_build.R:294-303): record the union of the columns every gcd(thin, thin2) iterations, then
+        # take each set's own rows -- sample k of a set sits at post-burn-in iteration k * its thinning interval
+        thin2 = self.thinFromConfVec[1] if thin2 in (None, -1) else thin2
+        if thin2 < 1 or thin2 != int(thin2):
+            raise ValueError("cannot use thin2 < 1")
+        if not reset:
+            raise NotImplementedError("reset = FALSE with a second monitor set is not supported")
+        g = int(np.gcd(int(thin), int(thin2)))
+        dm.run(int(niter), int(nburnin), g, reset, int(seed))
+        allrows = dm.samples()
+        n1, n2 = (int(niter) - int(nburnin)) // int(thin), (int(niter) - int(nburnin)) // int(thin2)
+        r1 = (np.arange(1, n1 + 1) * (int(thin) // g) - 1).astype(np.int64)
+        r2 = (np.arange(1, n2 + 1) * (int(thin2) // g) - 1).astype(np.int64)
+        self.mvSamples = np.ascontiguousarray(allrows[:, r1][:, :, low.cols1])
+        self.mvSamples2 = np.ascontiguousarray(allrows[:, r2][:, :, low.cols2])
         return self.mvSamples
 
     def _simulate_missing_inits(self, dm, inits_matrix, seed):
@@ -872,7 +923,7 @@ def compileNimble(*objs, backend=None, device=0, first_chain=0, **_ignored):
 
 
 def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setSeed=False, samplesAsCodaMCMC=False,
-            summary=False, progressBar=False, **_ignored):
+            summary=False, progressBar=False, thin2=None, **_ignored):
     """runMCMC(mcmc, niter, nburnin, thin, inits, nchains, setSeed): P/R/MCMC_run.R:82-213.
 
     inits: a dict (same values for every chain), a list of nchains dicts, or a callable returning a dict,
@@ -896,12 +947,19 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
         else:
             these = inits
         rows.append(mcmc.model.init_vector(these))
-    samples = mcmc.run_chains(np.stack(rows), niter, nburnin, thin, True, seed)
+    samples = mcmc.run_chains(np.stack(rows), niter, nburnin, thin, True, seed, thin2=thin2)
     mats = [SampleMatrix(samples[c], mcmc.colnames) for c in range(nchains)]
     result = mats[0] if nchains == 1 else {"chain%d" % (c + 1): mats[c] for c in range(nchains)}
+    ret = {"samples": result}
+    has2 = bool(mcmc.lowering.cols2)
+    if has2:  # MCMC_run.R:145-151, 183-207: a second list of matrices, `samples2`
+        mats2 = [SampleMatrix(mcmc.mvSamples2[c], mcmc.colnames2) for c in range(nchains)]
+        ret["samples2"] = mats2[0] if nchains == 1 else {"chain%d" % (c + 1): mats2[c] for c in range(nchains)}
     if summary:
         from .ess import samples_summary
-        allc = np.concatenate(mats, axis=0)
-        summ = samples_summary(allc, mcmc.colnames)
-        return {"samples": result, "summary": summ}
-    return result
+        summ = samples_summary(np.concatenate(mats, axis=0), mcmc.colnames)
+        if has2:
+            summ2 = samples_summary(np.concatenate(mats2, axis=0), mcmc.colnames2)
+            summ = {**summ, **summ2} if isinstance(summ, dict) else summ
+        ret["summary"] = summ
+    return ret["samples"] if len(ret) == 1 else ret

@@ -238,3 +238,23 @@ def test_missing_initial_values_are_simulated(oracle):
     m2 = nb.nimbleModel("{ lam ~ dgamma(2, 1)\n n ~ dpois(lam)\n y ~ dbin(0.5, n) }", data={"y": 2.0}, inits={"lam": 3.0})
     with pytest.raises(nb.ModelError, match="initial values are required for n"):
         run(compile_on(oracle, nb.configureMCMC(m2)), np.tile(m2.init_vector(), (2, 1)), 5, 0, seed=1)
+
+
+def test_monitors2_and_thin2(oracle):
+    """A second monitor set with its own thinning interval (configureMCMC(monitors2 =, thin2 =), runMCMC(thin2 =);
+    MCMC_build.R:294-303, MCMC_run.R:145-151): each set's rows are those of a run that records that set alone."""
+    m, _ = sm.SMALL["pump"]()
+    conf = nb.configureMCMC(m, monitors=["alpha", "beta"], monitors2=["theta", "beta"], thin=3, thin2=5)
+    cm = compile_on(oracle, conf)
+    out = nb.runMCMC(cm, niter=103, nburnin=13, nchains=2, setSeed=9, summary=True)
+    assert set(out) == {"samples", "samples2", "summary"}
+    s1, s2 = out["samples"], out["samples2"]
+    assert s1["chain1"].shape == (30, 2) and s2["chain2"].shape == (18, 11)
+    assert list(s2["chain1"].colnames)[:2] == ["theta[1]", "theta[2]"] and list(s2["chain1"].colnames)[-1] == "beta"
+    a = nb.runMCMC(compile_on(oracle, nb.configureMCMC(m, monitors=["alpha", "beta"], thin=3)), niter=103, nburnin=13, nchains=2, setSeed=9)
+    b = nb.runMCMC(compile_on(oracle, nb.configureMCMC(m, monitors=["theta", "beta"], thin=5)), niter=103, nburnin=13, nchains=2, setSeed=9)
+    for ch in ("chain1", "chain2"):
+        assert np.array_equal(np.asarray(s1[ch]), np.asarray(a[ch])) and np.array_equal(np.asarray(s2[ch]), np.asarray(b[ch]))
+    assert "theta[3]" in out["summary"] and "alpha" in out["summary"]
+    one = nb.runMCMC(cm, niter=20, nchains=1, setSeed=1, thin2=4)
+    assert np.asarray(one["samples2"]).shape == (5, 11) and np.asarray(one["samples"]).shape == (6, 2)
