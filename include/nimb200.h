@@ -308,6 +308,13 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
 int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
                                              const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);
 
+/* online conditional WAIC without grouping (P/R/MCMC_WAIC.R:209-282; call site MCMC_build.R:304-310): once enabled, every
+ * post-burn-in iteration of every chain updates, per data node, a running log-sum-exp of its log-density (lppd) and a Welford
+ * variance (pWAIC).  nimb200_mcmc_run(reset = 1) clears the statistics.  waic_get: out[0] = WAIC = -2 (lppd - pWAIC),
+ * out[1] = lppd, out[2] = pWAIC, out[3] = number of (iteration, chain) samples used.  Data-sharded models are not supported. */
+int nimb200_waic_enable(nimb200_model *m, int32_t enable);
+int nimb200_waic_get(nimb200_model *m, double *out4);
+
 /* initializeModel (P/R/initializeModel.R:78-139): every non-data stochastic node whose value is NaN (a missing initial value)
  * is simulated from its own distribution given its parents, declaration by declaration in the order given (parents first);
  * variates come from the counter (seed, chain; iteration 0, sampler id 0x7fff0000 + declaration, target = node).  Supported

@@ -56,6 +56,8 @@ class Backend:
         self._run = fn("mcmc_run", [vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_uint64])
         self._samples = fn("mcmc_samples", [vp, _dp, C.POINTER(C.c_int64)])
         self._sstate = fn("sampler_state", [vp, C.c_int32, C.c_int32, _dp, C.c_int64])
+        self._waic_enable = fn("waic_enable", [vp, C.c_int32])
+        self._waic_get = fn("waic_get", [vp, _dp])
         self._init_model = fn("initialize_model", [vp, C.POINTER(C.c_int32), C.c_int32, C.c_uint64])
         self._draws = fn("draws", [C.c_uint64, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double,
                                    C.c_int32, _dp])
@@ -153,6 +155,15 @@ class DeviceModel:
         out = np.empty(self.C)
         self.backend.check(self.backend._get_lp(self.h, decl, _ptr(out)))
         return out
+
+    def waic_enable(self, enable=True):
+        self.backend.check(self.backend._waic_enable(self.h, int(bool(enable))))
+
+    def waic_get(self):
+        """{'WAIC', 'lppd', 'pWAIC', 'n'} of the online conditional WAIC accumulated so far."""
+        out = np.empty(4)
+        self.backend.check(self.backend._waic_get(self.h, _ptr(out)))
+        return {"WAIC": float(out[0]), "lppd": float(out[1]), "pWAIC": float(out[2]), "n": int(out[3])}
 
     def initialize_model(self, decl_order, seed=0):
         """Simulate the non-data nodes whose value is NaN, declaration by declaration in `decl_order` (parents first)."""

@@ -622,6 +622,30 @@ __global__ void k_init_simulate(DevTab T, int di, uint64_t seed, int* fail_flag)
   if (simulate_node(T, di, node, c, key, nv)) *sv = nv; else atomicExch(fail_flag, di + 1);
 }
 
+// online WAIC (MCMC_WAIC.R:246-268): one thread per data node walks the chains of this iteration in order and updates the node's
+// running maximum / scaled sum (log-sum-exp) and Welford mean / sum of squares.  acc: [4][n] (max, sum, mean, ssq).
+__global__ void k_waic_update(DevTab T, int di, double* __restrict__ acc, long long iter0, long long nburnin, long long base_count) {
+  const long long it = (long long)T.ctr[0] - iter0;
+  if (it <= nburnin) return;
+  const int n = T.decl[di].n;
+  int node = blockIdx.x * blockDim.x + threadIdx.x;
+  if (node >= n) return;
+  double mx = acc[node], cs = acc[(size_t)n + node], mean = acc[2 * (size_t)n + node], ss = acc[3 * (size_t)n + node];
+  long long cnt = base_count + (it - nburnin - 1) * (long long)T.C;
+  for (int c = 0; c < T.C; c++) {
+    const double lp = calc_node(T, di, node, c, -1, 0.0);
+    cnt++;
+    if (cnt == 1) { mx = lp; cs = 1.0; }
+    else if (lp > mx) { cs = cs * exp(-lp + mx) + 1.0; mx = lp; }
+    else cs = cs + exp(lp - mx);
+    const double d1 = lp - mean;
+    mean = mean + d1 / (double)cnt;
+    const double d2 = lp - mean;
+    ss = ss + d1 * d2;
+  }
+  acc[node] = mx; acc[(size_t)n + node] = cs; acc[2 * (size_t)n + node] = mean; acc[3 * (size_t)n + node] = ss;
+}
+
 // ------------------------------------------------------------------------------------------------ wide kernels
 // (node tile x chain tile) evaluation of instances [lo,hi) (through idx if given) of one declaration.
 // MODE 0: per-chain partial sums of log-densities -> partials[tile][C]
@@ -1015,6 +1039,9 @@ struct nimb200_model {
   cudaGraphExec_t graph_exec = nullptr;
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
+  bool waic = false;                 // online WAIC enabled
+  std::vector<double*> d_waic;       // per data declaration: [4][n] accumulators (null for latent declarations)
+  int64_t waic_count = 0;            // (iteration, chain) samples accumulated so far
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0;
@@ -2034,8 +2061,14 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   if (!reset && nburnin != 0) return fail("cannot specify nburnin when using reset = FALSE.");
   CK(cudaSetDevice(m->device));
   int C = m->C, nmon = (int)m->monitors.size();
+  if (m->waic && m->nranks > 1) return fail("online WAIC on a data-sharded model is not supported");
   if (reset) {
     m->rows = 0; m->iter_done = 0;
+    if (m->waic) {
+      m->waic_count = 0;
+      for (size_t i = 0; i < m->decl.size(); i++)
+        if (m->d_waic[i]) CK(cudaMemsetAsync(m->d_waic[i], 0, sizeof(double) * 4 * m->decl[i].n, m->stream));
+    }
     for (size_t s = 0; s < m->samplers.size(); s++) {
       const nimb200_sampler& sp = m->samplers[s];
       int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
@@ -2082,9 +2115,17 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     }
     return false;
   };
+  const long long waic_base = m->waic_count;
   auto one_iteration = [&](uint64_t git) -> int {
     for (size_t s = 0; s < m->samplers.size(); s++)
       if (run_sampler(m, (int)s, seed, git)) return 1;
+    if (m->waic) {  // before the monitor kernel, whose last block advances the iteration counter
+      for (size_t i = 0; i < m->decl.size(); i++) {
+        if (!m->d_waic[i] || m->decl[i].n == 0) continue;
+        k_waic_update<<<(m->decl[i].n + 127) / 128, 128, 0, m->stream>>>(m->T, (int)i, m->d_waic[i], iter0, nburnin, waic_base);
+        m->launches++;
+      }
+    }
     if (nmon > 0) {
       size_t total = (size_t)nmon * C;
       k_monitor_ctr<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples, rows_before, iter0, nburnin, thin,
@@ -2142,6 +2183,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
   m->last_ms = ms; m->last_launches = m->launches;
   m->iter_done += niter;
+  if (m->waic) m->waic_count += (int64_t)(niter - nburnin) * C;
   return 0;
 }
 
@@ -2198,6 +2240,45 @@ extern "C" int nimb200_sampler_state(nimb200_model* m, int32_t s, int32_t what, 
   if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
   if (tmp) cudaFree(tmp);
   if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_waic_enable(nimb200_model* m, int32_t enable) {
+  if (!m) return fail("null model");
+  CK(cudaSetDevice(m->device));
+  if (enable && m->d_waic.empty()) {
+    m->d_waic.assign(m->decl.size(), nullptr);
+    for (size_t i = 0; i < m->decl.size(); i++) {
+      if (m->decl[i].value_kind != 0 || m->decl[i].n == 0) continue;
+      if (dev_alloc(m, &m->d_waic[i], (size_t)4 * m->decl[i].n)) return 1;
+      CK(cudaMemsetAsync(m->d_waic[i], 0, sizeof(double) * 4 * m->decl[i].n, m->stream));
+    }
+    m->waic_count = 0;
+  }
+  m->waic = enable != 0;
+  return 0;
+}
+
+extern "C" int nimb200_waic_get(nimb200_model* m, double* out4) {
+  if (!m || !out4) return fail("null argument");
+  if (m->d_waic.empty()) return fail("online WAIC was not enabled (nimb200_waic_enable)");
+  CK(cudaSetDevice(m->device));
+  CK(cudaStreamSynchronize(m->stream));
+  const double cnt = (double)m->waic_count;
+  double logsum = 0.0, ssq = 0.0;
+  long nnodes = 0;
+  std::vector<double> h;
+  for (size_t i = 0; i < m->decl.size(); i++) {
+    if (!m->d_waic[i]) continue;
+    const size_t n = (size_t)m->decl[i].n;
+    h.resize(4 * n);
+    CK(cudaMemcpy(h.data(), m->d_waic[i], sizeof(double) * 4 * n, cudaMemcpyDeviceToHost));
+    for (size_t j = 0; j < n; j++) { logsum += h[j] + log(h[n + j]); ssq += h[3 * n + j]; }  // MCMC_WAIC.R:276-278
+    nnodes += (long)n;
+  }
+  if (m->waic_count < 2) { out4[0] = out4[1] = out4[2] = NAN; out4[3] = cnt; return 0; }
+  const double lppd = logsum - (double)nnodes * log(cnt), pwaic = ssq / (cnt - 1.0);
+  out4[0] = -2.0 * (lppd - pwaic); out4[1] = lppd; out4[2] = pwaic; out4[3] = cnt;
   return 0;
 }
 

@@ -139,7 +139,7 @@ class MCMCconf:
     """MCMCconf: the ordered sampler list and the monitors (P/R/MCMC_configuration.R:73)."""
 
     def __init__(self, model, monitors=None, thin=1, useConjugacy=True, nodes=None, control=None,
-                 multivariateNodesAsScalars=False, autoBlock=False, monitors2=None, thin2=1):
+                 multivariateNodesAsScalars=False, autoBlock=False, monitors2=None, thin2=1, enableWAIC=False):
         if autoBlock:
             raise NotImplementedError("autoBlock is outside the B200 sampling path")
         self.model, self.thin, self.samplerConfs = model, thin, []
@@ -147,6 +147,7 @@ class MCMCconf:
         # second monitor set with its own thinning interval -> mvSamples2 (MCMC_configuration.R `monitors2`, `thin2`)
         self.monitors2 = [monitors2] if isinstance(monitors2, str) else list(monitors2 or [])
         self.thin2 = thin2
+        self.enableWAIC = bool(enableWAIC)   # online conditional WAIC, one data node per group (MCMC_configuration.R `enableWAIC`)
         self.control_defaults = dict(control or {})
         use = set(nodes) if nodes is not None else None
         for var in model.topo_vars():
@@ -785,6 +786,8 @@ def buildMCMC(conf, **kw):
         conf = configureMCMC(conf, **kw)
     if not isinstance(conf, MCMCconf):
         raise TypeError("buildMCMC: argument must be an MCMC configuration or a model")
+    if "enableWAIC" in kw:
+        conf.enableWAIC = bool(kw["enableWAIC"])
     return MCMC(conf)
 
 
@@ -819,13 +822,22 @@ class CompiledMCMC:
         self.dm = None
         self.mvSamples = None
         self.check_initial_logprobs = True  # initializeModel's NaN / -Inf warnings (MCMC_build.R:241)
+        self.enableWAIC = bool(getattr(self.conf, "enableWAIC", False))
 
     def _ensure(self, nchains):
         if self.dm is None or self.dm.C != nchains:
             if self.dm is not None:
                 self.dm.close()
             self.dm = _capi.DeviceModel(self.backend, self.builder, nchains, self.first_chain, self.device)
+            if self.enableWAIC:
+                self.dm.waic_enable(True)
         return self.dm
+
+    def getWAIC(self):
+        """mcmc$getWAIC(): the online WAIC of everything sampled since the last reset (MCMC_build.R:323-326, MCMC_WAIC.R:269-300)."""
+        if not self.enableWAIC or self.dm is None:
+            raise RuntimeError("WAIC was disabled based on the 'enableWAIC' argument to 'configureMCMC' or 'buildMCMC'")
+        return self.dm.waic_get()
 
     def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0, thin2=None):
         """All chains at once.  inits_matrix: [nchains][n_slots] (ignored when reset is False)."""
@@ -923,7 +935,7 @@ def compileNimble(*objs, backend=None, device=0, first_chain=0, **_ignored):
 
 
 def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setSeed=False, samplesAsCodaMCMC=False,
-            summary=False, progressBar=False, thin2=None, **_ignored):
+            summary=False, progressBar=False, thin2=None, WAIC=False, **_ignored):
     """runMCMC(mcmc, niter, nburnin, thin, inits, nchains, setSeed): P/R/MCMC_run.R:82-213.
 
     inits: a dict (same values for every chain), a list of nchains dicts, or a callable returning a dict,
@@ -962,4 +974,8 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
             summ2 = samples_summary(np.concatenate(mats2, axis=0), mcmc.colnames2)
             summ = {**summ, **summ2} if isinstance(summ, dict) else summ
         ret["summary"] = summ
+    if WAIC:  # MCMC_run.R:153-182: computed over all chains
+        if not mcmc.enableWAIC:
+            raise ValueError("mcmc argument must have been created with 'enableWAIC = TRUE' in order to calculate WAIC.")
+        ret["WAIC"] = mcmc.getWAIC()
     return ret["samples"] if len(ret) == 1 else ret

@@ -46,6 +46,9 @@ typedef struct ref_model {
   int64_t nrows, cap;
   int64_t iter_done;
   uint64_t evals;              /* stochastic node evaluations (logProb evals) */
+  int waic;                    /* online WAIC enabled (single-threaded runs only) */
+  double **waic_acc;           /* per data declaration [4][n]: max, scaled sum, mean, sum of squares (MCMC_WAIC.R:186-193) */
+  int64_t waic_count;          /* mcmcIter */
 } ref_model;
 
 static __thread uint64_t tl_evals; /* per-thread evaluation counter (flushed into the model at the end of a run) */
@@ -756,7 +759,15 @@ int ref_mcmc_prepare(ref_model *m, int64_t niter, int64_t nburnin, int32_t thin,
   if (nburnin > niter) return fail("cannot specify nburnin > niter");
   if (thin < 1) return fail("cannot use thin < 1");
   if (!reset && nburnin != 0) return fail("cannot specify nburnin when using reset = FALSE.");
-  if (reset) { m->nrows = 0; m->iter_done = 0; }
+  if (reset) {
+    m->nrows = 0; m->iter_done = 0;
+    if (m->waic_acc) {
+      int di;
+      m->waic_count = 0;
+      for (di = 0; di < T->n_decl; di++)
+        if (m->waic_acc[di]) memset(m->waic_acc[di], 0, sizeof(double) * 4 * T->decl[di].n);
+    }
+  }
   addrows = (niter - nburnin) / thin;
   if (m->nrows + addrows > m->cap || !m->samples) {
     int64_t ncap = m->nrows + addrows;
@@ -810,6 +821,26 @@ int ref_mcmc_run_range(ref_model *m, int64_t niter, int64_t nburnin, int32_t thi
             for (t = 0; t < sp->n_targets; t++) if (run_posterior_predictive(m, c, s, t, seed, git)) return 1;
             break;
           default: return fail("unknown sampler type");
+        }
+      }
+      if (iter > nburnin && m->waic) { /* waicFun$updateStats(), MCMC_build.R:304-310, MCMC_WAIC.R:209-268 (conditional, no groups) */
+        double cnt = (double)(++m->waic_count);
+        for (di = 0; di < T->n_decl; di++) {
+          int n = T->decl[di].n, node;
+          double *acc = m->waic_acc[di];
+          const double *lpv;
+          if (!acc) continue;
+          lpv = m->lp[di] + (size_t)c * n;
+          for (node = 0; node < n; node++) {
+            double lp = lpv[node], d1, d2;
+            if (m->waic_count == 1) { acc[node] = lp; acc[n + node] = 1.0; }
+            else if (lp > acc[node]) { acc[n + node] = acc[n + node] * exp(-lp + acc[node]) + 1.0; acc[node] = lp; }
+            else acc[n + node] = acc[n + node] + exp(lp - acc[node]);
+            d1 = lp - acc[2 * n + node];
+            acc[2 * n + node] = acc[2 * n + node] + d1 / cnt;
+            d2 = lp - acc[2 * n + node];
+            acc[3 * n + node] = acc[3 * n + node] + d1 * d2;
+          }
         }
       }
       if (iter > nburnin) {
@@ -875,6 +906,35 @@ int ref_sampler_state(ref_model *m, int32_t s, int32_t what, double *out, int64_
 }
 
 uint64_t ref_eval_count(ref_model *m) { uint64_t v = m->evals + tl_evals; return v; }
+
+int ref_waic_enable(ref_model *m, int32_t enable) {
+  int di;
+  if (enable && !m->waic_acc) {
+    m->waic_acc = (double **)calloc(m->t.n_decl + 1, sizeof(double *));
+    for (di = 0; di < m->t.n_decl; di++)
+      if (m->t.decl[di].value_kind == 0 && m->t.decl[di].n > 0) m->waic_acc[di] = (double *)calloc((size_t)4 * m->t.decl[di].n, sizeof(double));
+    m->waic_count = 0;
+  }
+  m->waic = enable != 0;
+  return 0;
+}
+int ref_waic_get(ref_model *m, double *out4) {
+  int di, j;
+  long nnodes = 0;
+  double logsum = 0, ssq = 0, cnt = (double)m->waic_count, lppd, pw;
+  if (!m->waic_acc) return fail("online WAIC was not enabled");
+  for (di = 0; di < m->t.n_decl; di++) {
+    int n = m->t.decl[di].n;
+    const double *acc = m->waic_acc[di];
+    if (!acc) continue;
+    for (j = 0; j < n; j++) { logsum += acc[j] + log(acc[n + j]); ssq += acc[3 * n + j]; }
+    nnodes += n;
+  }
+  if (m->waic_count < 2) { out4[0] = out4[1] = out4[2] = NAN; out4[3] = cnt; return 0; }
+  lppd = logsum - (double)nnodes * log(cnt); pw = ssq / (cnt - 1.0);
+  out4[0] = -2.0 * (lppd - pw); out4[1] = lppd; out4[2] = pw; out4[3] = cnt;
+  return 0;
+}
 
 /* initializeModel: see nimb200_initialize_model in include/nimb200.h (initializeModel.R:78-139) */
 int ref_initialize_model(ref_model *m, const int32_t *decl_order, int32_t n_order, uint64_t seed) {

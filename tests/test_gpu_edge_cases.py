@@ -235,3 +235,20 @@ def test_missing_initial_values_simulated_like_the_oracle(oracle, b200):
     assert np.all(np.isfinite(so)) and rel_err(sg, so).max() < RTOL_TRAJ
     run(co, init, 0, 0, seed=5), run(cg, init, 0, 0, seed=5)
     assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < 1e-15
+
+
+def test_online_waic_matches_oracle(oracle, b200):
+    """Online WAIC on the device (one thread per data node walking the chains of each post-burn-in iteration) against the
+    oracle's chain-by-chain accumulation: same statistics up to summation order, also across a reset = FALSE continuation."""
+    from tests.test_oracle_known_answers import _waic_case
+    m, conf = _waic_case()
+    inits = sm.random_inits(m, 5, 3, 0.1)
+    co, cg = compile_on(oracle, conf), compile_on(b200, conf)
+    run(co, inits, 260, 60, seed=8), run(cg, inits, 260, 60, seed=8)
+    wo, wg = co.getWAIC(), cg.getWAIC()
+    assert wo["n"] == wg["n"] == 200 * 5
+    for k in ("WAIC", "lppd", "pWAIC"):
+        assert abs(wg[k] - wo[k]) < 1e-9 * abs(wo[k]), (k, wg[k], wo[k])
+    run(co, inits, 50, 0, seed=8, reset=False), run(cg, inits, 50, 0, seed=8, reset=False)
+    wo, wg = co.getWAIC(), cg.getWAIC()
+    assert wo["n"] == wg["n"] == 250 * 5 and abs(wg["WAIC"] - wo["WAIC"]) < 1e-9 * abs(wo["WAIC"])

@@ -258,3 +258,34 @@ def test_monitors2_and_thin2(oracle):
     assert "theta[3]" in out["summary"] and "alpha" in out["summary"]
     one = nb.runMCMC(cm, niter=20, nchains=1, setSeed=1, thin2=4)
     assert np.asarray(one["samples2"]).shape == (5, 11) and np.asarray(one["samples"]).shape == (6, 2)
+
+
+def _waic_case():
+    m, _ = sm.SMALL["lmm"]()
+    conf = nb.configureMCMC(m, monitors=["mu", "sig_u", "sig_e", "u"], enableWAIC=True)
+    for v in ("sig_u", "sig_e"):
+        conf.removeSamplers(v)
+        conf.addSampler(v, type="RW", control={"log": True})
+    return m, conf
+
+
+def test_online_waic_equals_the_offline_formula(oracle):
+    """online conditional WAIC (MCMC_WAIC.R:209-282), accumulated over every post-burn-in iteration of every
+    chain, against lppd / pWAIC recomputed offline from the saved samples (the reference's calculateWAIC, MCMC_WAIC.R:49-75)."""
+    import scipy.stats as st
+    from scipy.special import logsumexp
+    m, conf = _waic_case()
+    cm = compile_on(oracle, conf)
+    out = nb.runMCMC(cm, niter=400, nburnin=100, nchains=2, setSeed=3, WAIC=True)
+    w = out["WAIC"]
+    S = np.concatenate([np.asarray(out["samples"]["chain1"]), np.asarray(out["samples"]["chain2"])])
+    cn, y, grp = list(cm.colnames), m.decls[-1].values, np.repeat(np.arange(30), 200)
+    mu, se = S[:, cn.index("mu")], S[:, cn.index("sig_e")]
+    u = S[:, [cn.index("u[%d]" % (g + 1)) for g in range(30)]]
+    lp = st.norm.logpdf(y[None, :], mu[:, None] + u[:, grp], se[:, None])
+    lppd, pw = (logsumexp(lp, axis=0) - np.log(lp.shape[0])).sum(), lp.var(axis=0, ddof=1).sum()
+    assert w["n"] == 600 and abs(w["lppd"] - lppd) < 1e-8 * abs(lppd) and abs(w["pWAIC"] - pw) < 1e-8 * pw
+    assert abs(w["WAIC"] + 2 * (lppd - pw)) < 1e-8 * abs(w["WAIC"])
+    plain = compile_on(oracle, nb.configureMCMC(m))
+    with pytest.raises(ValueError, match="enableWAIC = TRUE"):
+        nb.runMCMC(plain, niter=10, WAIC=True)
