@@ -1020,7 +1020,9 @@ struct nimb200_model {
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
   std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_group_sums + k_norm_conj_draw
-  std::vector<double*> d_pois_ysum;  // per Poisson conjugate sweep: [n_targets] sum of the counts over each target's nodes (data only)
+  std::vector<double*> d_pois_ysum;  // per Poisson conjugate sweep: [3][n_targets] data-only sums over each target's nodes (y, A, x y)
+  std::vector<int> pois_byp_slot;    // per such sweep: cache slot of the dependents' whole-declaration block sum it can refresh, or -1
+  std::vector<double*> d_pois_contrib; // [n_targets][C] per-(target, chain) shares of that block sum
   std::vector<char> pois_ysum_valid;
   std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
   std::vector<char> norm_gs_valid;   // is computed (and, data-sharded, all-reduced) once and kept until the shards change
@@ -1651,6 +1653,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->pois_sweep.assign(m->samplers.size(), 0);
   m->d_pois_ysum.assign(m->samplers.size(), nullptr);
   m->pois_ysum_valid.assign(m->samplers.size(), 0);
+  m->pois_byp_slot.assign(m->samplers.size(), -1);
+  m->d_pois_contrib.assign(m->samplers.size(), nullptr);
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     if (sp.type != NIMB_SAMPLER_CONJ_GAMMA || m->wide[s] || sp.n_dep != 2) continue;
@@ -1659,7 +1663,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
         dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0) {
       m->pois_sweep[s] = 1;
-      TRY(dev_alloc(m, &m->d_pois_ysum[s], (size_t)sp.n_targets));
+      TRY(dev_alloc(m, &m->d_pois_ysum[s], (size_t)sp.n_targets * 3));
     }
   }
   m->bern_sweep.assign(m->samplers.size(), 0);
@@ -1717,6 +1721,35 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     void* ds = nullptr;
     TRY(up(&ds, m->dep_slot.data(), sizeof(int32_t) * m->dep_slot.size()));
     m->d_dep_slot = (int32_t*)ds;
+  }
+  // A Poisson conjugate sweep whose targets together cover every node of the dependent declaration can hand the next MH step on
+  // that declaration its current-state block sum (fused_pois.cuh): needs a cache slot keyed on the whole declaration, counts
+  // small enough for the closed form (<= PF_YMAX) and no data sharding at run time.
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    if (!m->pois_sweep[s] || getenv("NIMB200_NO_BYPRODUCT")) continue;
+    const nimb200_sampler& sp = m->samplers[s];
+    const nimb200_dep& dp = m->deps[sp.dep_off + 1];
+    const nimb200_decl& dd = m->decl[dp.decl];
+    bool small = true;
+    for (int q = 0; q < dd.n && small; q++) small = t->darr[dd.value_ref][q] <= PF_YMAX;
+    // every node belongs to exactly one target?  (index map onto the targets: each node reads one lam element inside the block)
+    bool covers = dd.fam_arg[1] == sp.target_slot;
+    int64_t hit = 0;
+    {
+      const int mode = dd.fam_arg[2], arg = dd.fam_arg[3];
+      for (int q = 0; q < dd.n && covers; q++) {
+        int64_t g = mode == NIMB_IDX_I ? q : mode == NIMB_IDX_DIV ? q / arg : mode == NIMB_IDX_MOD ? q % arg : t->iarr[arg][q];
+        covers = g >= 0 && g < sp.n_targets;
+        hit++;
+      }
+    }
+    if (!small || !covers || hit != dd.n) continue;
+    for (size_t g = 0; g < m->deps.size(); g++) {
+      const nimb200_dep& o = m->deps[g];
+      bool whole = o.decl == dp.decl && (o.sel == NIMB_SEL_ALL || (o.sel == NIMB_SEL_RANGE && o.a == 0 && o.b == dd.n));
+      if (whole && ((int)g < sp.dep_off || (int)g >= sp.dep_off + sp.n_dep)) { m->pois_byp_slot[s] = m->dep_slot[g]; break; }
+    }
+    if (m->pois_byp_slot[s] >= 0) TRY(dev_alloc(m, &m->d_pois_contrib[s], (size_t)sp.n_targets * C));
   }
   m->invalidates.resize(m->samplers.size());
   for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -1937,6 +1970,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const nimb200_sampler& sp = m->samplers[s];
   int C = m->C;
   const int TB = 128;
+  int refreshed_slot = -1;  // cache slot this sampler leaves valid although it touches the slot's declaration
   if (sp.type == NIMB_SAMPLER_CATEGORICAL) {
     if (m->nranks > 1 && m->sweep_sharded[s]) return fail("categorical sampler over data-sharded dependents is not supported");
     size_t total = (size_t)sp.n_targets * C;
@@ -1970,21 +2004,30 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     const bool sh = m->nranks > 1 && m->sweep_sharded[s];
     PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
     if (!m->pois_ysum_valid[s]) {
-      k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s]);
+      k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[m->deps[sp.dep_off + 1].decl],
+                                                                           m->d_pois_ysum[s]);
       m->launches++;
-      if (sh && m->nccl_comm && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets)) return 1;
+      if (sh && m->nccl_comm && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets * 3)) return 1;
       m->pois_ysum_valid[s] = 1;
     }
     const unsigned nb = (unsigned)((total + PF_THREADS - 1) / PF_THREADS);
     if (!sh) {
-      k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr);
+      const bool byp = m->pois_byp_slot[s] >= 0 && m->nranks <= 1;
+      k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr,
+                                                           byp ? m->d_pois_contrib[s] : nullptr);
       m->launches++;
+      if (byp) {  // fixed-order sum over the targets -> the cached current-state block sum of the dependent declaration
+        k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_pois_contrib[s], sp.n_targets, 1, C,
+                                                              m->d_depcache + (size_t)m->pois_byp_slot[s] * C, nullptr);
+        m->launches++;
+        refreshed_slot = m->pois_byp_slot[s];
+      }
     } else {  // data-sharded: this rank's share of every (target, chain) rate contribution -> all-reduce -> draws
       if (total > m->sweepbuf_cap) return fail("internal: sweep buffer too small (poisson)");
-      k_pois_conj_sweep<1><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf);
+      k_pois_conj_sweep<1><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf, nullptr);
       m->launches++;
       if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, total)) return 1;
-      k_pois_conj_sweep<2><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf);
+      k_pois_conj_sweep<2><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf, nullptr);
       m->launches++;
     }
   } else if (!m->wide[s]) {
@@ -2048,6 +2091,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     }
   }
   for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
+  if (refreshed_slot >= 0) m->dep_valid[refreshed_slot] = 1;
   CK(cudaGetLastError());
   return 0;
 }

@@ -170,27 +170,37 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
   }
 }
 
-// sum of the counts over each target's nodes: data only, computed once per sampler (counts are integers: exact in any order)
-__global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, double* __restrict__ ysum) {
+// data-only sums over each target's nodes, computed once per sampler: stats[t] = sum y (integers: exact in any order),
+// stats[nT + t] = sum of the node constants A, stats[2 nT + t] = sum x y -- the last two serve the block-sum by-product below
+__global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode* __restrict__ pk, double* __restrict__ stats) {
   const nimb200_sampler sp = T.samplers[sid];
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= sp.n_targets) return;
   const nimb200_dep dp = T.deps[sp.dep_off + 1];
   Sel s = sel_of(T, dp, t);
-  double c0 = 0.0;
-  for (int k = s.lo; k < s.hi; k++) c0 += a.y[s.idx ? s.idx[k] : k];
-  ysum[t] = c0;
+  double c0 = 0.0, sa = 0.0, sxy = 0.0;
+  for (int k = s.lo; k < s.hi; k++) {
+    int node = s.idx ? s.idx[k] : k;
+    c0 += a.y[node];
+    sa += pk[node].A;
+    sxy += a.x[node] * a.y[node];
+  }
+  stats[t] = c0;
+  stats[(size_t)sp.n_targets + t] = sa;
+  stats[2 * (size_t)sp.n_targets + t] = sxy;
 }
 
 // conjugate gamma-Poisson sweep over the lam[g] targets (MCMC_conjugacy.R:80-93: contribution_shape = value,
 // contribution_rate = coeff, coeff = the dependent's lambda with the target set to 1 = exp(b0 + b1 x)).
 // thread = (target g, chain c), chains fastest: the 32 lanes of a warp read the same node (one broadcast load) and differ
 // in (b0, b1).  Two nodes per trip (two independent dependency chains), range check on the exponent bits.
-// PHASE 0: whole update.  Data-sharded runs: PHASE 1 leaves this rank's share of the rate contribution in part[t][c]
+// PHASE 0: whole update (contrib, if given, receives each (target, chain)'s share of the dependents' block sum under the new
+// value).  Data-sharded runs: PHASE 1 leaves this rank's share of the rate contribution in part[t][c]
 // (sel_of clamps the target's nodes to the rank's slice), the caller all-reduces it, PHASE 2 draws from the reduced sums.
 template <int PHASE>
 __global__ void __launch_bounds__(PF_THREADS)
-k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part) {
+k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part,
+                  double* __restrict__ contrib) {
   __shared__ double expT[64];
   if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
   __syncthreads();
@@ -248,7 +258,18 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   double prior_rate = get_param(T, tp.decl, tnode, c, NIMB_PARAM_RATE, -1, 0.0);
   DrawKey key = make_key(T, seed, iter, sid, t, c);
   double shape = prior_shape + c0, scale = 1 / (prior_rate + c1);
-  T.state[(size_t)(sp.target_slot + t) * T.C + c] = rgamma1(key, shape) * scale;
+  const double nl = rgamma1(key, shape) * scale;
+  T.state[(size_t)(sp.target_slot + t) * T.C + c] = nl;
+  if (PHASE == 0 && contrib) {
+    // by-product: the group's share of the dependents' block log-density under the value just drawn,
+    //   sum_i [A_i + y_i (log lam + b0 + b1 x_i) - lam exp(b0 + b1 x_i)] = SA + Sy (log lam + b0) + b1 Sxy - lam c1,
+    // so that the next MH step on this declaration finds its current-state sum without another pass over the nodes
+    const double sa = ysum[(size_t)sp.n_targets + t], sxy = ysum[2 * (size_t)sp.n_targets + t];
+    double v;
+    if (nl == 0.0) v = c0 == 0.0 ? 0.0 : -INFINITY;        // dpois(y, 0)
+    else v = ((sa + c0 * (log(nl) + b0)) + b1 * sxy) - nl * c1;
+    contrib[(size_t)t * T.C + c] = v;
+  }
 }
 
 }  // namespace nimb
