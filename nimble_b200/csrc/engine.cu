@@ -164,16 +164,23 @@ __device__ double calc_node(const DevTab& T, int di, int i, int c, int ov_slot, 
 // Parameters whose programs do not read anything indexed by the node (sd = sig_e, shape = alpha, ...) are evaluated
 // once per thread instead of once per node; for dnorm the log(sd) term is carried along.  Results are bit-identical to
 // calc_node(): the same operations on the same values, only not repeated.
-struct Hoist { bool h0, h1; double p0, p1, l1; };
+struct Hoist { bool h0, h1, gfast; double p0, p1, l1; };  // l1: log(sd) of dnorm, or -shape log(scale) - lgamma(shape) of dgamma
 __device__ __forceinline__ Hoist make_hoist(const DevTab& T, int di, int c, int ov_slot, double ov_val) {
   const nimb200_decl& d = T.decl[di];
-  Hoist H; H.p0 = H.p1 = H.l1 = 0.0;
+  Hoist H; H.p0 = H.p1 = H.l1 = 0.0; H.gfast = false;
   H.h0 = d.dist != NIMB_DCAT && T.pconst[3 * di] != 0;
   H.h1 = d.dist != NIMB_DCAT && d.nparam > 1 && T.pconst[3 * di + 1] != 0;
   if (H.h0) H.p0 = eval_prog(T, c, d.prog_off[0], d.prog_len[0], 0, 0, ov_slot, ov_val);
   if (H.h1) {
     H.p1 = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, ov_slot, ov_val);
     if (d.dist == NIMB_DNORM) H.l1 = log(H.p1);
+    // dgamma with chain-level shape and scale: the node-independent part once per thread, then (shape - 1) log x - x / scale per
+    // node instead of nmath's dpois_raw route (same density; the closed form loses digits to cancellation only for large
+    // shapes, which keep the exact route)
+    if (d.dist == NIMB_DGAMMA && H.h0 && H.p0 > 0.0 && H.p0 <= 64.0 && H.p1 > 0.0 && isfinite(H.p1)) {
+      H.gfast = true;
+      H.l1 = -H.p0 * log(H.p1) - lgamma(H.p0);
+    }
   }
   return H;
 }
@@ -197,7 +204,7 @@ __device__ double calc_node_h(const DevTab& T, int di, int i, int c, int ov_slot
   if (d.nparam > 1) p1 = H.h1 ? H.p1 : eval_prog(T, c, d.prog_off[1], d.prog_len[1], i, 0, ov_slot, ov_val);
   switch (d.dist) {
     case NIMB_DNORM: return H.h1 ? dnorm_logsd(x, p0, p1, H.l1) : dnorm(x, p0, p1);
-    case NIMB_DGAMMA: return dgamma(x, p0, p1);
+    case NIMB_DGAMMA: return (H.gfast && x > 0.0 && isfinite(x)) ? fma(p0 - 1.0, log(x), H.l1) - x / p1 : dgamma(x, p0, p1);
     case NIMB_DPOIS: return dpois(x, p0);
     case NIMB_DBINOM: return dbinom(x, p0, p1);
     case NIMB_DBETA: return dbeta(x, p0, p1);
