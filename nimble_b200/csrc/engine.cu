@@ -1024,6 +1024,8 @@ struct nimb200_model {
   std::vector<char> pois_sweep;      // per sampler: conjugate sweep served by k_pois_conj_sweep
   std::vector<char> bern_ok;         // per decl: Bernoulli-logit-linear family usable
   std::vector<char> bern_sweep;      // per sampler: binary sweep served by k_bernlin_binary_sweep
+  std::vector<std::array<int, 2>> bern_byp_slot;  // per such sweep: cache slots of the whole-declaration block sums (own declaration,
+  std::vector<double*> d_bern_contrib;            // dependents) it can refresh, or -1; [2][n_targets][C] per-(site, chain) shares
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
   std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_group_sums + k_norm_conj_draw
@@ -1758,6 +1760,38 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     }
     if (m->pois_byp_slot[s] >= 0) TRY(dev_alloc(m, &m->d_pois_contrib[s], (size_t)sp.n_targets * C));
   }
+  // The binary sweep of the occupancy family evaluates, for the state it leaves behind, every node of the sites' own declaration and
+  // of the visits' declaration: when its targets cover both declarations it refreshes their cached block sums (fused_bern.cuh).
+  m->bern_byp_slot.assign(m->samplers.size(), std::array<int, 2>{-1, -1});
+  m->d_bern_contrib.assign(m->samplers.size(), nullptr);
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    if (!m->bern_sweep[s] || getenv("NIMB200_NO_BYPRODUCT")) continue;
+    const nimb200_sampler& sp = m->samplers[s];
+    const nimb200_dep &d0 = m->deps[sp.dep_off], &d1 = m->deps[sp.dep_off + 1];
+    const nimb200_decl &z = m->decl[d0.decl], &y = m->decl[d1.decl];
+    bool covers = sp.n_targets == z.n && z.value_ref == sp.target_slot;
+    {
+      const int mode = y.fam_arg[4], arg = y.fam_arg[5];
+      for (int q = 0; q < y.n && covers; q++) {
+        int64_t g = mode == NIMB_IDX_I ? q : mode == NIMB_IDX_DIV ? q / arg : mode == NIMB_IDX_MOD ? q % arg : t->iarr[arg][q];
+        covers = g >= 0 && g < sp.n_targets;
+      }
+    }
+    if (!covers) continue;
+    std::array<int, 2> slots{-1, -1};
+    for (size_t g = 0; g < m->deps.size(); g++) {
+      if ((int)g >= sp.dep_off && (int)g < sp.dep_off + sp.n_dep) continue;
+      const nimb200_dep& o = m->deps[g];
+      for (int k = 0; k < 2; k++) {
+        const int decl = k == 0 ? d0.decl : d1.decl, n = k == 0 ? z.n : y.n;
+        if (slots[k] < 0 && o.decl == decl && (o.sel == NIMB_SEL_ALL || (o.sel == NIMB_SEL_RANGE && o.a == 0 && o.b == n))) slots[k] = m->dep_slot[g];
+      }
+    }
+    if (slots[0] < 0 || slots[1] < 0) continue;
+    if ((size_t)((sp.n_targets + CS_ROWS - 1) / CS_ROWS) * C > m->partials_cap) continue;  // column-sum partials live in d_partials
+    m->bern_byp_slot[s] = slots;
+    TRY(dev_alloc(m, &m->d_bern_contrib[s], (size_t)2 * sp.n_targets * C));
+  }
   m->invalidates.resize(m->samplers.size());
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
@@ -1977,7 +2011,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   const nimb200_sampler& sp = m->samplers[s];
   int C = m->C;
   const int TB = 128;
-  int refreshed_slot = -1;  // cache slot this sampler leaves valid although it touches the slot's declaration
+  std::vector<int> refreshed;  // cache slots this sampler leaves valid although it touches their declarations
   if (sp.type == NIMB_SAMPLER_CATEGORICAL) {
     if (m->nranks > 1 && m->sweep_sharded[s]) return fail("categorical sampler over data-sharded dependents is not supported");
     size_t total = (size_t)sp.n_targets * C;
@@ -1990,9 +2024,22 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     m->launches++;
   } else if (!m->wide[s] && m->bern_sweep[s] && !(m->nranks > 1 && m->sweep_sharded[s])) {
     size_t total = (size_t)sp.n_targets * C;
+    const bool byp = m->bern_byp_slot[s][0] >= 0 && m->nranks <= 1;
+    double* cz = byp ? m->d_bern_contrib[s] : nullptr;
+    double* cy = byp ? m->d_bern_contrib[s] + total : nullptr;
     k_bernlin_binary_sweep<<<(unsigned)((total + BF_THREADS - 1) / BF_THREADS), BF_THREADS, 0, m->stream>>>(
-        m->T, s, seed, iter, bern_args(m, m->deps[sp.dep_off].decl), bern_args(m, m->deps[sp.dep_off + 1].decl));
+        m->T, s, seed, iter, bern_args(m, m->deps[sp.dep_off].decl), bern_args(m, m->deps[sp.dep_off + 1].decl), cz, cy);
     m->launches++;
+    if (byp) {
+      const int chunks = (sp.n_targets + CS_ROWS - 1) / CS_ROWS;
+      for (int k = 0; k < 2; k++) {
+        k_colsum<<<dim3((C + 31) / 32, chunks), 256, 0, m->stream>>>(k == 0 ? cz : cy, sp.n_targets, C, m->d_partials);
+        k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C,
+                                                              m->d_depcache + (size_t)m->bern_byp_slot[s][k] * C, nullptr);
+        m->launches += 2;
+        refreshed.push_back(m->bern_byp_slot[s][k]);
+      }
+    }
   } else if (!m->wide[s] && m->norm_sweep[s]) {
     // per-target (sum y, count) depend on the data only: computed on first use (data-sharded: this rank's slice, then one
     // all-reduce of 2 doubles per target) and kept; every later sweep is just the draws
@@ -2027,7 +2074,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
         k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_pois_contrib[s], sp.n_targets, 1, C,
                                                               m->d_depcache + (size_t)m->pois_byp_slot[s] * C, nullptr);
         m->launches++;
-        refreshed_slot = m->pois_byp_slot[s];
+        refreshed.push_back(m->pois_byp_slot[s]);
       }
     } else {  // data-sharded: this rank's share of every (target, chain) rate contribution -> all-reduce -> draws
       if (total > m->sweepbuf_cap) return fail("internal: sweep buffer too small (poisson)");
@@ -2098,7 +2145,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     }
   }
   for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
-  if (refreshed_slot >= 0) m->dep_valid[refreshed_slot] = 1;
+  for (int g : refreshed) m->dep_valid[g] = 1;
   CK(cudaGetLastError());
   return 0;
 }

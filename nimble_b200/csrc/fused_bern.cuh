@@ -89,7 +89,8 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
 // binary Gibbs sweep over latent 0/1 targets z[t] whose prior is  z[t] ~ dbern(ilogit(b0 + b1 xz[t]))  (pz) and whose dependents
 // are the data nodes of  y ~ dbern(z[G] * ilogit(a0 + a1 w))  (py) selected by the sampler's stage-1 entry.
 __global__ void __launch_bounds__(BF_THREADS)
-k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs pz, BernArgs py) {
+k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs pz, BernArgs py, double* __restrict__ contrib_z,
+                       double* __restrict__ contrib_y) {
   __shared__ __align__(16) double tab[SOFTPLUS_DOUBLES];
   load_softplus(tab, threadIdx.x, BF_THREADS);
   __syncthreads();
@@ -123,6 +124,38 @@ k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs
   unif2(key, 0, u, u2);
   bool jump = (!isnan(acceptanceProb)) & (u < acceptanceProb);
   if (jump) *sv = other;
+  // by-product: under the state it leaves behind, this site's share of the block log-density of its own declaration and of the
+  // visits' declaration -- their fixed-order sums over the sites refresh the cached current-state block sums, so the RW steps on
+  // the detection / occupancy coefficients that follow need no extra pass
+  if (contrib_z) {
+    contrib_z[(size_t)t * T.C + c] = jump ? otherPrior : curPrior;
+    contrib_y[(size_t)t * T.C + c] = jump ? otherDeps : curDeps;
+  }
+}
+
+// column sums of contrib[n][C] over chunks of rows, fixed order: partials[chunk][C] (lane = chain, the 8 warps of a block take
+// consecutive eighths of the chunk in turn and meet in shared memory)
+static const int CS_ROWS = 256;
+__global__ void __launch_bounds__(256)
+k_colsum(const double* __restrict__ contrib, int n, int C, double* __restrict__ partials) {
+  __shared__ double red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int r0 = blockIdx.y * CS_ROWS, r1 = min(n, r0 + CS_ROWS);
+  const int per = CS_ROWS / 8, lo = r0 + warp * per, hi = min(r1, lo + per);
+  double a0 = 0.0, a1 = 0.0;
+  if (c < C) {
+    int r = lo;
+    for (; r + 1 < hi; r += 2) { a0 += contrib[(size_t)r * C + c]; a1 += contrib[(size_t)(r + 1) * C + c]; }
+    if (r < hi) a0 += contrib[(size_t)r * C + c];
+  }
+  red[warp][lane] = a0 + a1;
+  __syncthreads();
+  if (warp == 0 && c < C) {
+    double s = 0.0;
+    for (int w = 0; w < 8; w++) s += red[w][lane];
+    partials[(size_t)blockIdx.y * C + c] = s;
+  }
 }
 
 }  // namespace nimb
