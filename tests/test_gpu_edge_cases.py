@@ -252,3 +252,21 @@ def test_online_waic_matches_oracle(oracle, b200):
     run(co, inits, 50, 0, seed=8, reset=False), run(cg, inits, 50, 0, seed=8, reset=False)
     wo, wg = co.getWAIC(), cg.getWAIC()
     assert wo["n"] == wg["n"] == 250 * 5 and abs(wg["WAIC"] - wo["WAIC"]) < 1e-9 * abs(wo["WAIC"])
+
+
+def test_sweep_by_products_keep_trajectories(oracle, b200, monkeypatch):
+    """The conjugate gamma sweep (Poisson family) and the binary sweep (occupancy family) refresh the cached block sums of the
+    declarations they touch; the MH steps that follow start from those sums.  Sizes chosen so that the coefficient samplers are
+    wide (> 2048 dependents) and the by-products are live; with them switched off the trajectories must stay the same."""
+    cases = [configs.glmm(N=4200, G=30, seed=14), configs.occupancy(S=2100, J=2, seed=15)]
+    for m, conf in cases:
+        inits = sm.random_inits(m, 40, 8, 0.1)
+        if "z" in m.var_slot:
+            inits[:, m.var_slot["z"]:m.var_slot["z"] + 2100] = 1.0
+        so = run(compile_on(oracle, conf), inits, 150, 0, seed=3)
+        sg = run(compile_on(b200, conf), inits, 150, 0, seed=3)
+        assert rel_err(sg, so).max() < RTOL_TRAJ
+        monkeypatch.setenv("NIMB200_NO_BYPRODUCT", "1")
+        plain = run(compile_on(b200, conf), inits, 150, 0, seed=3)
+        monkeypatch.delenv("NIMB200_NO_BYPRODUCT")
+        assert rel_err(plain, so).max() < RTOL_TRAJ and rel_err(plain, sg).max() < RTOL_TRAJ
