@@ -1212,6 +1212,18 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
       (mode == 0 || (mode == 2 && dp && dp->param == 0 && (dp->link == NIMB_LINK_ADDITIVE || dp->link == NIMB_LINK_IDENTITY) &&
                      !gam && !(d.fam_arg[3] >= 0 && slot >= d.fam_arg[2] && slot < d.fam_arg[2] + m->norm_vspan[di])))) {
     NormArgs na = norm_args(m, di);
+    if (mode == 2 && !idx && lo == 0 && hi == d.n && !shard && na.mode >= 0 && !getenv("NIMB200_NO_BYPRODUCT")) {
+      // the sweep over the gathered vector keeps (sum y, count) per group: G terms per chain instead of a pass over the nodes
+      for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {
+        const nimb200_sampler& o = m->samplers[s2];
+        if (!m->norm_sweep[s2] || !m->norm_gs_valid[s2] || m->deps[o.dep_off + 1].decl != di) continue;
+        if (o.target_slot != d.fam_arg[2] || o.n_targets != m->norm_vspan[di]) continue;
+        k_norm_conj_from_groups<<<C, 256, 0, m->stream>>>(m->T, na, m->d_norm_gs[s2], o.n_targets, slot, dst0, dst1);
+        m->launches++;
+        CK(cudaGetLastError());
+        return 0;
+      }
+    }
     int nb = norm_blocks(count);
     int npb = std::max(4 * NF_THREADS, ((std::max(count, 1) + nb - 1) / nb + 4 * NF_THREADS - 1) / (4 * NF_THREADS) * (4 * NF_THREADS));
     nb = std::max(1, (count + npb - 1) / npb);

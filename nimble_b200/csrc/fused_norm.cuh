@@ -303,6 +303,46 @@ __global__ void k_norm_conj_finish(DevTab T, NormArgs a, int count, const double
   dst1[c] = (double)count * tau;
 }
 
+// Conjugate contributions of the whole declaration to a target inside the chain-level term A (the LMM's mu), from the per-group
+// data-only sums gs[g] = (sum y, count) the sweep over v keeps:  sum_i (y_i - A(target := 0) - v[G(i)]) = sum_g (Sy_g - n_g (A0 + v_g)).
+// One block per chain, threads stride over the groups (four independent partial sums each, so the gathers overlap), fixed-order
+// butterfly and warp order: G terms per chain instead of a pass over the nodes.
+__global__ void __launch_bounds__(256)
+k_norm_conj_from_groups(DevTab T, NormArgs a, const double* __restrict__ gs, int G, int ov_slot,
+                        double* __restrict__ dst0, double* __restrict__ dst1) {
+  __shared__ double sR[8], sN[8];
+  const int c = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double A0 = eval_prog(T, c, a.a_off, a.a_len, 0, 0, ov_slot, 0.0);
+  const double* __restrict__ vb = T.state + (size_t)a.v_slot * T.C + c;
+  double R[4] = {0.0, 0.0, 0.0, 0.0}, cnt = 0.0;
+  for (int g0 = threadIdx.x; g0 < G; g0 += 4 * 256) {
+    double sy[4], n[4], v[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {  // all loads of a trip first (clamped index, no branch in between), then the arithmetic
+      const int g = min(g0 + u * 256, G - 1);
+      const double2 q = reinterpret_cast<const double2*>(gs)[g];
+      sy[u] = q.x; n[u] = g0 + u * 256 < G ? q.y : 0.0;
+      v[u] = vb[(size_t)g * T.C];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      R[u] += n[u] > 0.0 ? sy[u] - n[u] * (A0 + v[u]) : 0.0;   // an empty group contributes nothing, whatever its v holds
+      cnt += n[u];
+    }
+  }
+  double r = (R[0] + R[1]) + (R[2] + R[3]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { r += __shfl_xor_sync(0xffffffffu, r, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o); }
+  if (lane == 0) { sR[warp] = r; sN[warp] = cnt; }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  double rr = 0.0, nn = 0.0;
+  for (int w = 0; w < 8; w++) { rr += sR[w]; nn += sN[w]; }
+  const double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
+  dst0[c] = rr * tau;
+  dst1[c] = nn * tau;
+}
+
 // Conjugate normal-normal sweep over the gathered vector's elements (targets v[t]).  (sum y, count) over a target's nodes
 // depend on the data only: k_norm_group_sums leaves this rank's share in gs[t][2] once (one block per target, fixed order;
 // data-sharded runs all-reduce the 2 doubles per target), k_norm_conj_draw is one thread per (target, chain) forming
