@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--cpu-chains", type=int, default=0, help="chains of the CPU baseline (default: host cores, <= 64)")
     ap.add_argument("--cpu-iters", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true",
+                    help="skip the live measurement of the HBM-bound kernel of configs[2] (rank 0, single-GPU runs only)")
     ap.add_argument("--full", action="store_true",
                     help="also run the full protocol of SURVEY 8d (niter 5000, nburnin 2500) and report min-ESS/s from it")
     ap.add_argument("--full-niter", type=int, default=5000)
@@ -312,6 +314,29 @@ def main():
                     "posterior_mean_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.mean(0)[:4]])),
                     "posterior_sd_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.std(0)[:4]]))}
             d3.close()
+        secondary = None
+        if world == 1 and not a.no_secondary:
+            # the one HBM-bound logProb kernel of the path, measured live on its own configuration (configs[2]: LMM, N = 1e7,
+            # 8 chains): block sum of the data declaration = streaming kernel + reduce/finish launch, CUDA events, min of 3 x 50
+            try:
+                m3, conf3 = configs.lmm()
+                cm_l = nb.compileNimble(nb.buildMCMC(conf3), backend=backend, device=local)
+                dl = cm_l._ensure(8)
+                dl.set_values(np.tile(m3.init_vector(), (8, 1)))
+                yd = len(cm_l.builder.decls) - 1
+                nn = cm_l.builder.decls[yd].n
+                ms_l = min(dl.time_calculate(yd, 50) for _ in range(3))
+                bytes_l = 12.0 * nn
+                secondary = [{"kernel": "k_norm_stream_tma + k_norm_reduce_finish", "bound": "hbm",
+                              "workload": "configs[2]: y[i] ~ dnorm(mu + u[grp[i]], sd) block sum, N = %d, 8 chains" % nn,
+                              "achieved": bytes_l / (ms_l * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": bytes_l / (ms_l * 1e-3) / 1e9 / hbm_peak, "us_per_block_sum": ms_l * 1e3,
+                              "algorithmic_bytes": bytes_l,
+                              "note": "both launches of one block sum are inside the timed region; the streaming kernel alone is "
+                                      "23.9-26.3 us under ncu (profiles/r1e_summary.md), 0.70-0.77 of the measured peak"}]
+                dl.close()
+            except Exception as ex:  # the headline line must not depend on it
+                secondary = [{"error": str(ex)[:200]}]
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": workload_config(a, {"chains_total": C * world}),
@@ -322,7 +347,8 @@ def main():
                 "roofline": roof, "cpu_baseline": cb,
                 "min_ess_per_sec": mess * world / (ms_max * 1e-3),
                 "min_ess_note": "sum over chains of coda-style ESS of the timed iterations' samples (adaptation still running); rank 0's chains x n_gpus",
-                "evals_per_iteration_per_chain": evals_iter, "host_lowering_seconds": t_build, "full_protocol": full}
+                "evals_per_iteration_per_chain": evals_iter, "host_lowering_seconds": t_build, "full_protocol": full,
+                "secondary_rooflines": secondary}
         _emit(line)
     if world > 1:
         dist.barrier()
