@@ -1250,8 +1250,17 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
     m->launches++;
     if (!(shard && m->nccl_comm)) {
-      if (mode == 0) k_norm_reduce_finish<0><<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->T, na, lo, hi, idx, m->d_partials, nb, dst0, dst1);
-      else k_norm_reduce_finish<1><<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->T, na, lo, hi, idx, m->d_partials, nb, dst0, dst1);
+      {  // programmatic dependent launch: the finish kernel is scheduled while the streaming kernel still runs (fused_norm.cuh)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((C * 32 + 127) / 128); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = 0; cfg.stream = m->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = getenv("NIMB200_NO_PDL") ? 0 : 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        const double* parts = m->d_partials;
+        if (mode == 0) CK(cudaLaunchKernelEx(&cfg, k_norm_reduce_finish<0>, m->T, na, lo, hi, idx, parts, nb, dst0, dst1));
+        else CK(cudaLaunchKernelEx(&cfg, k_norm_reduce_finish<1>, m->T, na, lo, hi, idx, parts, nb, dst0, dst1));
+      }
     } else {
       k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nb, 1, C, m->d_normtmp, nullptr);
       m->launches++;

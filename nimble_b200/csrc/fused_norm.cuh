@@ -141,6 +141,7 @@ k_norm_stream_tma(DevTab T, NormArgs a, int lo, int hi, int nodes_per_warp, int 
     tma::bulk_g2s(st, a.y + n0, (uint32_t)(cnt * 8), b);
     if (IDX == 1) tma::bulk_g2s(st + NW_TILE * 8, a.gidx + n0, (uint32_t)(cnt * 4), b);
   };
+  cudaTriggerProgrammaticLaunchCompletion();  // lets the reduce / finish launch behind this kernel be scheduled as CTAs retire
   // the first copies start before anything else; warp 1 meanwhile evaluates the chain-level term (dependent global loads)
   if (lane == 0) {
     for (int s = 0; s < NW_STAGES; s++) tma::mbar_init(&bar[s], 1);
@@ -275,21 +276,29 @@ template <int MODE>
 __global__ void k_norm_reduce_finish(DevTab T, NormArgs a, int lo, int hi, const int32_t* idx, const double* __restrict__ partials,
                                      int nb, double* __restrict__ dst0, double* __restrict__ dst1) {
   int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (c >= T.C) return;
+  const bool live = c < T.C;
+  // Launched with programmatic stream serialization right behind the streaming kernel: everything that does not read the
+  // partials (the chain-level sd / tau through the interpreter, its logarithm) runs while that kernel drains; the grid
+  // dependency wait below returns once it has completed and its writes are visible.
+  const int count = hi - lo;
+  double par = 0.0;
+  if (live && lane == 0) {
+    if (MODE == 1) par = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
+    else { const nimb200_decl& d = T.decl[a.decl]; par = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, -1, 0.0); }
+  }
+  cudaGridDependencySynchronize();
+  if (!live) return;
   double S = 0.0;
   for (int b = lane; b < nb; b += 32) S += partials[(size_t)b * T.C + c];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
   if (lane != 0) return;
-  int count = hi - lo;
   if (MODE == 1) {
-    double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
-    dst0[c] = S * tau;
-    dst1[c] = (double)count * tau;
+    dst0[c] = S * par;
+    dst1[c] = (double)count * par;
     return;
   }
-  const nimb200_decl& d = T.decl[a.decl];
-  double sigma = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, -1, 0.0);
+  const double sigma = par;
   dst0[c] = (sigma == 0 && count > 0 && !isnan(S)) ? norm_sd0_sum(T, a, c, lo, hi, idx) : norm_sum_from_ss(sigma, S, count);
 }
 
