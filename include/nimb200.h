@@ -170,7 +170,7 @@ enum {
   NIMB_SAMPLER_CONJ_NORMAL = 5, /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
   NIMB_SAMPLER_CONJ_BETA = 6,   /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
   NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7, /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
-                                            distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbern) and recalculate it */
+                                            distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbin, dpois with mean <= 500) and recalculate it */
   NIMB_SAMPLER_CATEGORICAL = 9, /* MCMC_samplers.R:162-226: dcat target with K <= NIMB200_MAX_CATEGORIES categories: the conditional
                                    log-density of every category, then rcat (dists.cpp:936-961) on exp(logProb - max) */
   NIMB_SAMPLER_SLICE = 8 /* MCMC_samplers.R:864-972: stepping-out / shrinkage slice sampler with width adaptation; discrete
@@ -318,11 +318,11 @@ int nimb200_waic_get(nimb200_model *m, double *out4);
 /* initializeModel (P/R/initializeModel.R:78-139): every non-data stochastic node whose value is NaN (a missing initial value)
  * is simulated from its own distribution given its parents, declaration by declaration in the order given (parents first);
  * variates come from the counter (seed, chain; iteration 0, sampler id 0x7fff0000 + declaration, target = node).  Supported
- * for dnorm, dgamma, dbeta, dexp, dlogis and dbern nodes; a NaN left in any other declaration is an error. */
+ * for dnorm, dgamma, dbeta, dexp, dlogis, dbin and dpois (mean <= 500) nodes; a NaN left in any other declaration is an error. */
 int nimb200_initialize_model(nimb200_model *m, const int32_t *decl_order, int32_t n_order, uint64_t seed);
 
 /* draws: fills out[n] with the standard normals (kind 0), uniforms (kind 1), gamma(shape a, scale 1)
- * variates (kind 2) or beta(a, 1 + a/2) variates (kind 3) that sampler `sampler` would consume on the device for (chain, iter, target), so the
+ * variates (kind 2), beta(a, 1 + a/2) variates (kind 3), Poisson(a) variates (kind 4) or binomial(25, a) variates (kind 5) that sampler `sampler` would consume on the device for (chain, iter, target), so the
  * host can replay identical draws into another implementation. */
 int nimb200_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32_t target,
                   int32_t kind, double a, int32_t n, double *out);

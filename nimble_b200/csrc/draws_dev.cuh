@@ -181,4 +181,38 @@ __device__ __forceinline__ double rbeta1(const DrawKey& k, double a, double b) {
   return __ddiv_rn(x, __dadd_rn(x, y));
 }
 
+// Poisson(mu) by inversion from zero: p_0 = exp(-mu), p_{k+1} = p_k mu / (k + 1), one uniform (call `base`).  mu <= 500 (beyond it
+// exp(-mu) leaves too few bits and the walk too long): larger or invalid means return NaN.
+__device__ __forceinline__ double rpois_inv(const DrawKey& k, double mu, uint32_t base = 0) {
+  if (!(mu >= 0.0) || mu > 500.0) return NAN;
+  if (mu == 0.0) return 0.0;
+  double u, dummy;
+  unif2(k, base, u, dummy);
+  double p = det_exp(-mu), cdf = p;
+  int x = 0;
+  while (u > cdf && x < 5000) { x++; p = __ddiv_rn(__dmul_rn(p, mu), (double)x); cdf = __dadd_rn(cdf, p); }
+  return (double)x;
+}
+// binomial(n, pr) by inversion from zero: p_0 = (1 - pr)^n, p_{k+1} = p_k (n - k) / (k + 1) pr / (1 - pr), one uniform.
+// n an integer <= 100000 and (1 - pr)^n not underflowing; otherwise NaN.
+__device__ __forceinline__ double rbinom_inv(const DrawKey& k, double n, double pr, uint32_t base = 0) {
+  if (!(n >= 0.0) || n > 100000.0 || n != floor(n) || !(pr >= 0.0) || !(pr <= 1.0)) return NAN;
+  if (pr == 0.0 || n == 0.0) return 0.0;
+  if (pr == 1.0) return n;
+  double u, dummy;
+  unif2(k, base, u, dummy);
+  const double q = __dadd_rn(1.0, -pr), r = __ddiv_rn(pr, q);
+  double p = det_exp(__dmul_rn(n, det_log(q)));
+  if (!(p > 0.0)) return NAN;
+  double cdf = p;
+  int x = 0;
+  const int ni = (int)n;
+  while (u > cdf && x < ni) {
+    p = __dmul_rn(__ddiv_rn(__dmul_rn(p, (double)(ni - x)), (double)(x + 1)), r);
+    x++;
+    cdf = __dadd_rn(cdf, p);
+  }
+  return (double)x;
+}
+
 }  // namespace nimb

@@ -368,7 +368,8 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
       case NIMB_DBETA: nv = rbeta1(key, p0, p1); break;
       case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; break;
       case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); break;
-      case NIMB_DBINOM: unif2(key, 0, u, u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+      case NIMB_DBINOM: nv = rbinom_inv(key, p0, p1); break;
+      case NIMB_DPOIS: nv = rpois_inv(key, p0); break;
     }
     *sv = nv;
     return;
@@ -610,9 +611,8 @@ __device__ __forceinline__ bool simulate_node(const DevTab& T, int di, int node,
     case NIMB_DBETA: nv = rbeta1(key, p0, p1); return true;
     case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; return true;
     case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); return true;
-    case NIMB_DBINOM:
-      if (p0 != 1.0) return false;
-      unif2(key, 0, u, u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); return true;
+    case NIMB_DBINOM: nv = rbinom_inv(key, p0, p1); return !isnan(nv);
+    case NIMB_DPOIS: nv = rpois_inv(key, p0); return !isnan(nv);
   }
   return false;
 }
@@ -983,7 +983,9 @@ __global__ void k_draws(uint64_t seed, int chain, uint64_t iter, int sampler, in
   if (kind == 0) { normal2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
   else if (kind == 1) { unif2(key, k / 2, x0, x1); out[k] = (k & 1) ? x1 : x0; }
   else if (kind == 2) { key.target = (uint32_t)(target + k); out[k] = rgamma1(key, a); }
-  else { key.target = (uint32_t)(target + k); out[k] = rbeta1(key, a, 1.0 + 0.5 * a); }
+  else if (kind == 3) { key.target = (uint32_t)(target + k); out[k] = rbeta1(key, a, 1.0 + 0.5 * a); }
+  else if (kind == 4) { key.target = (uint32_t)(target + k); out[k] = rpois_inv(key, a); }
+  else { key.target = (uint32_t)(target + k); out[k] = rbinom_inv(key, 25.0, a); }
 }
 
 // ------------------------------------------------------------------------------------------------ host model
@@ -1404,7 +1406,7 @@ static int validate_table(const nimb200_table* t) {
     if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {
       const nimb200_decl& pd = t->decl[t->deps[sp.dep_off].decl];
       const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP ||
-                      pd.dist == NIMB_DLOGIS || pd.dist == NIMB_DBINOM;
+                      pd.dist == NIMB_DLOGIS || pd.dist == NIMB_DBINOM || pd.dist == NIMB_DPOIS;
       if (!ok || sp.n_dep != 1) return fail("posterior_predictive: unsupported target distribution, or the target has dependents");
     }
     if (sp.adaptive && sp.adapt_interval < 1) return fail("adaptInterval must be >= 1");
@@ -2419,7 +2421,7 @@ extern "C" int nimb200_initialize_model(nimb200_model* m, const int32_t* decl_or
   CK(cudaStreamSynchronize(m->stream));
   CK(cudaMemsetAsync(d_flag, 0, sizeof(int), m->stream));
   if (flag) return fail("initializeModel: a missing initial value cannot be simulated (declaration " + std::to_string(flag - 1) +
-                        ": only dnorm, dgamma, dbeta, dexp, dlogis and dbern nodes can)");
+                        ": only dnorm, dgamma, dbeta, dexp, dlogis, dbin and dpois (mean <= 500) nodes can)");
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   return 0;
 }

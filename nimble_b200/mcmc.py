@@ -160,7 +160,7 @@ class MCMCconf:
         self.samplerConfs = [sc for sc in self.samplerConfs if sc.type != T.SAMPLER_POSTERIOR_PREDICTIVE] + pp
 
     # default assignment rules, MCMC_configuration.R:340-446: conjugate -> binary -> (discrete: unsupported) -> RW
-    _PP_DISTS = (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS)
+    _PP_DISTS = (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM)
 
     def _is_terminal(self, decl):
         return not [d for d in self.model.dependents(decl.var) if d is not decl]
@@ -169,8 +169,7 @@ class MCMCconf:
         model = self.model
         # terminal (end) nodes are posterior predictive: simulated from their own distribution, MCMC_configuration.R:283-285, 368
         # (a predictive node that has predictive descendants keeps its ordinary sampler here)
-        if self._is_terminal(decl) and (decl.dist in self._PP_DISTS or
-                                        (decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0))):
+        if self._is_terminal(decl) and decl.dist in self._PP_DISTS:
             self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, decl.var, decl.pos, self.control_defaults))
             return
         conj = check_conjugacy(model, decl) if useConjugacy else None
@@ -262,7 +261,7 @@ class MCMCconf:
                 if not self._is_terminal(decl):
                     # MCMC_samplers.R:93-94
                     raise ValueError("posterior_predictive sampler should not be assigned to non-posterior-predictive nodes")
-                if not (decl.dist in self._PP_DISTS or (decl.dist == T.DBINOM and decl.params[0] == ("const", 1.0))):
+                if decl.dist not in self._PP_DISTS:
                     raise NotImplementedError("posterior_predictive: no device variate generator for the distribution of %s" % var)
             self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl))
         else:
@@ -892,7 +891,7 @@ class CompiledMCMC:
         bad = [v for v in missing if not model.simulable(v)]
         if bad:
             raise ModelError("initial values are required for %s: missing values can only be simulated for dnorm, dgamma, dbeta, "
-                             "dexp, dlogis and dbern nodes" % ", ".join(bad))
+                             "dexp, dlogis, dbin and dpois nodes" % ", ".join(bad))
         order = [self.lowering.decl_ids[d.index] for v in model.topo_vars() for d in model.decl_of(v)]
         dm.initialize_model(order, seed)
 

@@ -521,8 +521,7 @@ class Model:
 
     def simulable(self, var):
         """Can missing values of `var` be simulated on the device (a variate generator exists for its distribution)?"""
-        return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS) or
-                   (d.dist == T.DBINOM and d.params[0] == ("const", 1.0)) for d in self.decl_of(var))
+        return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM) for d in self.decl_of(var))
 
 
 def nimbleCode(text):

@@ -186,3 +186,29 @@ double ref_rgamma_at(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t samp
   }
   return (d * v) * boost;
 }
+
+/* Poisson / binomial by inversion from zero (same sequence of operations as draws_dev.cuh: rpois_inv, rbinom_inv) */
+double ref_rpois(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double mu) {
+  double u, dummy, p, cdf;
+  int x = 0;
+  if (!(mu >= 0.0) || mu > 500.0) return NAN;
+  if (mu == 0.0) return 0.0;
+  ref_unif2(seed, chain, iter, sampler, target, 0, &u, &dummy);
+  p = ref_det_exp(-mu); cdf = p;
+  while (u > cdf && x < 5000) { x++; p = (p * mu) / (double)x; cdf = cdf + p; }
+  return (double)x;
+}
+double ref_rbinom(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double n, double pr) {
+  double u, dummy, q, r, p, cdf;
+  int x = 0, ni;
+  if (!(n >= 0.0) || n > 100000.0 || n != floor(n) || !(pr >= 0.0) || !(pr <= 1.0)) return NAN;
+  if (pr == 0.0 || n == 0.0) return 0.0;
+  if (pr == 1.0) return n;
+  ref_unif2(seed, chain, iter, sampler, target, 0, &u, &dummy);
+  q = 1.0 - pr; r = pr / q;
+  p = ref_det_exp(n * ref_det_log(q));
+  if (!(p > 0.0)) return NAN;
+  cdf = p; ni = (int)n;
+  while (u > cdf && x < ni) { p = ((p * (double)(ni - x)) / (double)(x + 1)) * r; x++; cdf = cdf + p; }
+  return (double)x;
+}

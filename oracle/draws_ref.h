@@ -12,6 +12,8 @@ void ref_normal2(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler,
 double ref_rgamma(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a);
 double ref_rgamma_at(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, uint32_t base, double a);
 double ref_rbeta(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double a, double b);
+double ref_rpois(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double mu);
+double ref_rbinom(uint64_t seed, uint32_t chain, uint64_t iter, uint32_t sampler, uint32_t target, double n, double pr);
 double ref_det_log(double x);
 double ref_det_exp(double x);
 #ifdef __cplusplus

@@ -608,9 +608,8 @@ static int run_posterior_predictive(ref_model *m, int c, int sid, int t, uint64_
     case NIMB_DBETA: nv = ref_rbeta(seed, chain, iter, sid, t, p0, p1); break;
     case NIMB_DEXP: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
     case NIMB_DLOGIS: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
-    case NIMB_DBINOM:
-      if (p0 != 1.0) return fail("posterior_predictive: dbin with size != 1 is not supported");
-      ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+    case NIMB_DBINOM: nv = ref_rbinom(seed, chain, iter, sid, t, p0, p1); break;
+    case NIMB_DPOIS: nv = ref_rpois(seed, chain, iter, sid, t, p0); break;
     default: return fail("posterior_predictive: unsupported distribution");
   }
   st[slot] = nv;
@@ -960,11 +959,11 @@ int ref_initialize_model(ref_model *m, const int32_t *decl_order, int32_t n_orde
           case NIMB_DBETA: nv = ref_rbeta(seed, chain, 0, sid, node, p0, p1); break;
           case NIMB_DEXP: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
           case NIMB_DLOGIS: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
-          case NIMB_DBINOM:
-            if (p0 != 1.0) return fail("initializeModel: a missing initial value cannot be simulated");
-            ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = isnan(p1) ? NAN : (u < p1 ? 1.0 : 0.0); break;
+          case NIMB_DBINOM: nv = ref_rbinom(seed, chain, 0, sid, node, p0, p1); break;
+          case NIMB_DPOIS: nv = ref_rpois(seed, chain, 0, sid, node, p0); break;
           default: return fail("initializeModel: a missing initial value cannot be simulated");
         }
+        if (isnan(nv) && (d->dist == NIMB_DBINOM || d->dist == NIMB_DPOIS)) return fail("initializeModel: a missing initial value cannot be simulated");
         st[d->value_ref + node] = nv;
       }
     }
@@ -980,7 +979,9 @@ int ref_draws(uint64_t seed, int32_t chain, int64_t iter, int32_t sampler, int32
     if (kind == 0) { ref_normal2(seed, chain, iter, sampler, target, k / 2, &x0, &x1); out[k] = (k & 1) ? x1 : x0; }
     else if (kind == 1) { ref_unif2(seed, chain, iter, sampler, target, k / 2, &x0, &x1); out[k] = (k & 1) ? x1 : x0; }
     else if (kind == 2) out[k] = ref_rgamma(seed, chain, iter, sampler, target + k, a);
-    else out[k] = ref_rbeta(seed, chain, iter, sampler, target + k, a, 1.0 + 0.5 * a);
+    else if (kind == 3) out[k] = ref_rbeta(seed, chain, iter, sampler, target + k, a, 1.0 + 0.5 * a);
+    else if (kind == 4) out[k] = ref_rpois(seed, chain, iter, sampler, target + k, a);
+    else out[k] = ref_rbinom(seed, chain, iter, sampler, target + k, 25.0, a);
   }
   return 0;
 }

@@ -132,15 +132,19 @@ def predictive_nodes():
       pb ~ dbeta(2, a)
       pe ~ dexp(a)
       pl ~ dlogis(a, 2)
-      pz ~ dbern(0.3) }"""
-    m = nb.nimbleModel(code, data={"y": 1.5}, inits={"a": 1.0, "pn": 0.0, "pg": 1.0, "pb": 0.5, "pe": 1.0, "pl": 0.0, "pz": 0.0})
-    return m, nb.configureMCMC(m, monitors=["a", "pn", "pg", "pb", "pe", "pl", "pz"])
+      pz ~ dbern(0.3)
+      pp ~ dpois(3 * a)
+      pk ~ dbin(0.3, 12) }"""
+    m = nb.nimbleModel(code, data={"y": 1.5}, inits={"a": 1.0, "pn": 0.0, "pg": 1.0, "pb": 0.5, "pe": 1.0, "pl": 0.0, "pz": 0.0,
+                                                     "pp": 1.0, "pk": 3.0})
+    return m, nb.configureMCMC(m, monitors=["a", "pn", "pg", "pb", "pe", "pl", "pz", "pp", "pk"])
 
 
 def slice_targets():
     """A discrete and a continuous node with known marginals under the slice sampler: x ~ Poisson(3.5), g ~ Gamma(3, rate 2)."""
     m = nb.nimbleModel("{ x ~ dpois(3.5)\n g ~ dgamma(3, 2) }", inits={"x": 3.0, "g": 1.0})
-    conf = nb.configureMCMC(m, nodes=["x"])       # dpois end node: no device generator -> the discrete default, slice
+    conf = nb.configureMCMC(m, nodes=[])
+    conf.addSampler("x", type="slice")
     conf.addSampler("g", type="slice")
     return m, conf
 

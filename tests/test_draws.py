@@ -11,6 +11,11 @@ def test_oracle_draw_moments(oracle):
     for a in (0.3, 1.0, 2.5, 40.0):
         g = oracle.draws(7, 3, 11, 2, 0, 2, a, 100000)
         assert abs(g.mean() - a) < 0.03 * max(1, a) and abs(g.var() - a) < 0.08 * max(1, a)
+    for mu in (0.7, 42.0):  # kind 4: Poisson by inversion
+        x = oracle.draws(7, 3, 11, 2, 0, 4, mu, 100000)
+        assert np.all(x == np.floor(x)) and abs(x.mean() - mu) < 0.03 * max(1, mu ** 0.5) and abs(x.var() - mu) < 0.05 * max(1, mu)
+    x = oracle.draws(7, 3, 11, 2, 0, 5, 0.31, 100000)  # kind 5: binomial(25, 0.31)
+    assert x.min() >= 0 and x.max() <= 25 and abs(x.mean() - 7.75) < 0.03 and abs(x.var() - 25 * 0.31 * 0.69) < 0.1
     for a in (0.3, 6.5):  # kind 3: beta(a, 1 + a/2)
         b = 1.0 + 0.5 * a
         x = oracle.draws(7, 3, 11, 2, 0, 3, a, 100000)
@@ -39,7 +44,7 @@ def test_oracle_det_math(oracle):
 
 @pytest.mark.gpu
 def test_device_draws_bit_identical(oracle, b200):
-    for kind, a in ((0, 0.0), (1, 0.0), (2, 0.4), (2, 1.0), (2, 17.3), (3, 0.3), (3, 6.5)):
+    for kind, a in ((0, 0.0), (1, 0.0), (2, 0.4), (2, 1.0), (2, 17.3), (3, 0.3), (3, 6.5), (4, 0.7), (4, 42.0), (5, 0.31)):
         for key in ((5, 0, 1, 0, 0), (2 ** 40 + 9, 1023, 4999, 3, 77)):
             d = b200.draws(*key, kind, a, 4096)
             r = oracle.draws(*key, kind, a, 4096)

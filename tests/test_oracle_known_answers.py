@@ -142,7 +142,7 @@ def test_posterior_predictive_sampler(oracle):
     m, conf = sm.very_simple()                      # test-mcmc.R:209-227: z is the predictive node
     assert [(s.name, s.var) for s in conf.samplerConfs] == [("conjugate_dnorm", "x"), ("posterior_predictive", "z")]
     m, conf = sm.predictive_nodes()
-    assert [s.name for s in conf.samplerConfs] == ["RW"] + ["posterior_predictive"] * 6
+    assert [s.name for s in conf.samplerConfs] == ["RW"] + ["posterior_predictive"] * 8
     cm = compile_on(oracle, conf)
     s = pooled(run(cm, np.tile(m.init_vector(), (4, 1)), 30000, 1000, seed=5))
     col = {n: s[:, i] for i, n in enumerate(cm.colnames)}
@@ -154,6 +154,8 @@ def test_posterior_predictive_sampler(oracle):
     assert abs(col["pe"].mean() - (1 / a).mean()) < 0.08 * (1 / a).mean()
     assert abs(col["pl"].mean() - a.mean()) < se(col["pl"]) and abs(col["pl"].var() - (np.pi ** 2 / 12 + a.var())) < 0.2  # dlogis(location, rate = 2)
     assert set(np.unique(col["pz"])) == {0.0, 1.0} and abs(col["pz"].mean() - 0.3) < 0.01
+    assert abs(col["pp"].mean() - 3 * a.mean()) < se(col["pp"]) and np.all(col["pp"] == np.floor(col["pp"]))
+    assert abs(col["pk"].mean() - 3.6) < 0.03 and abs(col["pk"].var() - 12 * 0.3 * 0.7) < 0.06 and col["pk"].max() <= 12
     # explicit assignment and its guard
     conf2 = nb.configureMCMC(m, nodes=["a"])
     conf2.addSampler("pg", type="posterior_predictive")
@@ -235,7 +237,8 @@ def test_missing_initial_values_are_simulated(oracle):
     again = compile_on(oracle, conf)
     run(again, init, 0, 0, seed=3)
     assert np.array_equal(again.dm.get_values(), v)                   # same seed, same simulated inits
-    m2 = nb.nimbleModel("{ lam ~ dgamma(2, 1)\n n ~ dpois(lam)\n y ~ dbin(0.5, n) }", data={"y": 2.0}, inits={"lam": 3.0})
+    m2 = nb.nimbleModel("{ lam ~ dgamma(2, 1)\n n ~ dcat(w[1:3])\n y ~ dnorm(lam, sd = n) }", constants={"w": [0.2, 0.3, 0.5]},
+                        data={"y": 2.0}, inits={"lam": 3.0})
     with pytest.raises(nb.ModelError, match="initial values are required for n"):
         run(compile_on(oracle, nb.configureMCMC(m2)), np.tile(m2.init_vector(), (2, 1)), 5, 0, seed=1)
 
