@@ -91,7 +91,33 @@ def counts_and_labels(rng):
     return m
 
 
-TEMPLATES = [normal_hierarchy, poisson_hierarchy, bernoulli_layers, counts_and_labels]
+def mixed_bag(rng):
+    """Every remaining distribution as a likelihood or prior (dbeta, dexp, dlogis, dcat data, dbin with constant size), priors
+    that are not conjugate to them, and hand-assigned samplers: slice on a continuous node, RW on the log scale, reflective RW."""
+    n, K = int(rng.integers(1, 30)), int(rng.integers(2, 5))
+    size = rng.integers(1, 7, n).astype(float)
+    code = """{ p ~ dbeta(2, 3)
+      r ~ dexp(1.5)
+      loc ~ dlogis(0, 1)
+      sh ~ dgamma(3, 2)
+      q ~ dbeta(1.5, 1.5)
+      for (i in 1:n) {
+        k[i] ~ dbin(p, size[i])
+        t[i] ~ dexp(r * e[i])
+        l[i] ~ dlogis(loc, scale = sh)
+        b[i] ~ dbeta(sh, 2)
+        d[i] ~ dcat(w[1:K])
+        g[i] ~ dgamma(sh, rate = r)
+        f[i] ~ dbern(q * p) } }"""
+    data = {"k": rng.binomial(size.astype(int), 0.4).astype(float), "t": rng.exponential(1.0, n), "l": rng.logistic(0, 1, n),
+            "b": rng.beta(2, 2, n), "d": rng.integers(1, K + 1, n).astype(float), "g": rng.gamma(2, 1, n),
+            "f": (rng.random(n) < 0.3).astype(float)}
+    m = nb.nimbleModel(code, constants={"n": n, "K": K, "size": size, "e": 0.5 + rng.random(n), "w": rng.random(K) + 0.1}, data=data,
+                       inits={"p": 0.4, "r": 1.0, "loc": 0.1, "sh": 1.5, "q": 0.5})
+    return m
+
+
+TEMPLATES = [normal_hierarchy, poisson_hierarchy, bernoulli_layers, counts_and_labels, mixed_bag]
 
 
 def make_case(seed):
@@ -99,6 +125,17 @@ def make_case(seed):
     m = TEMPLATES[seed % len(TEMPLATES)](rng)
     conf = nb.configureMCMC(m, useConjugacy=bool(rng.random() < 0.7),
                             control={"adaptInterval": int(rng.choice([20, 50, 200]))})
+    if "loc" in m.var_slot:                         # mixed_bag: hand-assigned samplers on some of the scalars
+        choice = int(rng.integers(0, 4))
+        if choice == 0:
+            conf.removeSamplers("loc")
+            conf.addSampler("loc", type="slice", control={"sliceWidth": 0.7, "adaptInterval": 25})
+        elif choice == 1:
+            conf.removeSamplers("sh")
+            conf.addSampler("sh", type="RW", control={"log": True, "adaptInterval": 30})
+        elif choice == 2:
+            conf.removeSamplers("q")
+            conf.addSampler("q", type="RW", control={"reflective": True, "lower": 0.0, "upper": 1.0, "scale": 0.4, "adaptInterval": 30})
     if rng.random() < 0.3:                          # an RW_block over a vector parameter instead of its scalar samplers
         for var in ("u", "lam", "mu"):
             if var in m.var_slot and m.var_shape[var] and 1 < m.var_shape[var][0] <= 6:

@@ -9,7 +9,7 @@ from tests.helpers import compile_on, rel_err, run
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("NIMB200_FUZZ_CASES", "48"))))
+@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("NIMB200_FUZZ_CASES", "50"))))
 def test_random_model_matches_oracle(oracle, b200, seed):
     m, conf, nchains = make_case(seed)
     rng = np.random.default_rng(1000 + seed)
