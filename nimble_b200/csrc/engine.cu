@@ -338,6 +338,8 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 // butterfly -- used when there are few (target, chain) pairs but each has many dependents (tau_b / mu_b over 50 betas).
 template <int PHASE, int LANES>
 __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* buf) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
   const int lane = LANES == 1 ? 0 : (threadIdx.x & (LANES - 1));
@@ -661,6 +663,8 @@ __global__ void k_waic_update(DevTab T, int di, double* __restrict__ acc, long l
 template <int MODE>
 __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int cw_log2, int npt, double* partials,
                        double* out_nodes, nimb200_dep dp, int slot, int gam) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   extern __shared__ double sh[];
   int cw = 1 << cw_log2, nl = blockDim.x >> cw_log2;
   int lane_c = threadIdx.x & (cw - 1), lane_n = threadIdx.x >> cw_log2;
@@ -704,6 +708,8 @@ __global__ void k_eval(DevTab T, int di, int lo, int hi, const int32_t* idx, int
 // fixed-order reduction of the tile partials: dst[k][c] = sum_b partials[b][k][c].  One warp per (chain, k): lane l adds
 // tiles l, l+32, ... in order, then a butterfly over the lanes -- the same order every run, so sums are reproducible.
 __global__ void k_reduce(const double* __restrict__ partials, int nb, int K, int C, double* dst0, double* dst1) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= C * K) return;
   int c = w % C, kk = w / C;
@@ -716,6 +722,8 @@ __global__ void k_reduce(const double* __restrict__ partials, int nb, int K, int
 
 // wide RW: proposal for every chain; the old value is parked in tsave
 __global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* tsave, double* pls) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_sampler sp = T.samplers[sid];
@@ -760,6 +768,8 @@ __global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter,
 // wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
 __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
                             double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_sampler sp = T.samplers[sid];
@@ -856,6 +866,8 @@ __global__ void k_block_adapt(DevTab T, int sid, SamplerDev S) {
 
 // wide conjugate: draw from the posterior given the reduced contributions
 __global__ void k_conj_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, const double* contrib /*[n_dep][2][C]*/) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= T.C) return;
   const nimb200_sampler sp = T.samplers[sid];
@@ -942,6 +954,8 @@ __global__ void k_monitor(DevTab T, const int32_t* mon, int nmon, double* row /*
 // The last block to finish also advances the counter (every block has read it by then), which saves the separate launch.
 __global__ void k_monitor_ctr(DevTab T, const int32_t* mon, int nmon, double* samples, long long rows_before, long long iter0,
                               long long nburnin, int thin, unsigned long long* ctr, unsigned int* ticket) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   long long it = (long long)T.ctr[0] - iter0;
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (it > nburnin && (it - nburnin) % thin == 0 && gid < (size_t)nmon * T.C) {
@@ -1101,6 +1115,21 @@ int load_nccl() {
 
 static int allreduce_sum(nimb200_model* m, double* buf, size_t count);
 
+// Programmatic dependent launch: the kernel may be scheduled while its predecessor on the stream still runs; it must call
+// cudaGridDependencySynchronize() before touching anything the predecessor writes (every kernel launched through here does so
+// first thing, after letting its own successor be scheduled with cudaTriggerProgrammaticLaunchCompletion()).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  static const bool off = getenv("NIMB200_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = off ? 0 : 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static const int EVAL_THREADS = 256;
 static const int EVAL_NPT = 32;
 
@@ -1204,7 +1233,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     fused_bern_logit_launch(m->d_xpad[di], d.n, d.fam_arg[2], m->d_state, d.fam_arg[1], C, m->d_partials, lo / 128,
                             (hi + 127) / 128, m->stream);
     m->launches++;
-    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, 1, C, dst0, dst1);
+    CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, nt, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
@@ -1220,7 +1249,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
         const nimb200_sampler& o = m->samplers[s2];
         if (!m->norm_sweep[s2] || !m->norm_gs_valid[s2] || m->deps[o.dep_off + 1].decl != di) continue;
         if (o.target_slot != d.fam_arg[2] || o.n_targets != m->norm_vspan[di]) continue;
-        k_norm_conj_from_groups<<<C, 256, 0, m->stream>>>(m->T, na, m->d_norm_gs[s2], o.n_targets, slot, dst0, dst1);
+        CK(launch_pdl(k_norm_conj_from_groups, dim3(C), dim3(256), 0, m->stream, m->T, na, m->d_norm_gs[s2], o.n_targets, slot, dst0, dst1));
         m->launches++;
         CK(cudaGetLastError());
         return 0;
@@ -1264,7 +1293,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
         else CK(cudaLaunchKernelEx(&cfg, k_norm_reduce_finish<1>, m->T, na, lo, hi, idx, parts, nb, dst0, dst1));
       }
     } else {
-      k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nb, 1, C, m->d_normtmp, nullptr);
+      CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, nb, 1, C, m->d_normtmp, nullptr));
       m->launches++;
       if (allreduce_sum(m, m->d_normtmp, (size_t)C)) return 1;
       // after the all-reduce the sums cover the whole selection, not only this rank's slice
@@ -1283,7 +1312,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     dim3 grid((C + 31) / 32, chunks);
     k_bernlin_sum<<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
     m->launches++;
-    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
+    CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
@@ -1297,7 +1326,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     dim3 grid((C + 31) / 32, chunks);
     k_pois_sum<<<grid, PF_THREADS, 0, m->stream>>>(m->T, pa, (const PoisNode*)m->d_nodeconst[di], lo, hi, npc, m->d_partials);
     m->launches++;
-    k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C, dst0, dst1);
+    CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
     if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
@@ -1312,11 +1341,11 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   size_t shm = sizeof(double) * EVAL_THREADS * K;
   // a single tile (scalar priors, small declarations) is its own sum: the kernel writes the destination directly
   const bool direct = nt == 1 && mode == 0;
-  if (mode == 0) k_eval<0><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), direct ? dst0 : m->d_partials, nullptr, dd, slot, gam);
-  else k_eval<2><<<grid, EVAL_THREADS, shm, m->stream>>>(m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, nullptr, dd, slot, gam);
+  if (mode == 0) CK(launch_pdl(k_eval<0>, grid, dim3(EVAL_THREADS), shm, m->stream, m->T, di, lo, hi, idx, cwl, eval_npt(C, count), direct ? dst0 : m->d_partials, (double*)nullptr, dd, slot, gam));
+  else CK(launch_pdl(k_eval<2>, grid, dim3(EVAL_THREADS), shm, m->stream, m->T, di, lo, hi, idx, cwl, eval_npt(C, count), m->d_partials, (double*)nullptr, dd, slot, gam));
   m->launches++;
   if (!direct) {
-    k_reduce<<<(C * K * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, nt, K, C, dst0, dst1);
+    CK(launch_pdl(k_reduce, dim3((C * K * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, nt, K, C, dst0, dst1));
     m->launches++;
   }
   CK(cudaGetLastError());
@@ -2057,8 +2086,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       const int chunks = (sp.n_targets + CS_ROWS - 1) / CS_ROWS;
       for (int k = 0; k < 2; k++) {
         k_colsum<<<dim3((C + 31) / 32, chunks), 256, 0, m->stream>>>(k == 0 ? cz : cy, sp.n_targets, C, m->d_partials);
-        k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_partials, chunks, 1, C,
-                                                              m->d_depcache + (size_t)m->bern_byp_slot[s][k] * C, nullptr);
+        CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C,
+                                                              m->d_depcache + (size_t)m->bern_byp_slot[s][k] * C, nullptr));
         m->launches += 2;
         refreshed.push_back(m->bern_byp_slot[s][k]);
       }
@@ -2074,7 +2103,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       m->norm_gs_valid[s] = 1;
     }
     size_t total = (size_t)sp.n_targets * C;
-    k_norm_conj_draw<<<(unsigned)((total + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, na, m->d_norm_gs[s]);
+    CK(launch_pdl(k_norm_conj_draw, dim3((unsigned)((total + TB - 1) / TB)), dim3(TB), 0, m->stream, m->T, s, seed, iter, na, m->d_norm_gs[s]));
     m->launches++;
   } else if (!m->wide[s] && m->pois_sweep[s]) {
     size_t total = (size_t)sp.n_targets * C;
@@ -2094,8 +2123,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
                                                            byp ? m->d_pois_contrib[s] : nullptr);
       m->launches++;
       if (byp) {  // fixed-order sum over the targets -> the cached current-state block sum of the dependent declaration
-        k_reduce<<<(C * 32 + 127) / 128, 128, 0, m->stream>>>(m->d_pois_contrib[s], sp.n_targets, 1, C,
-                                                              m->d_depcache + (size_t)m->pois_byp_slot[s] * C, nullptr);
+        CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_pois_contrib[s], sp.n_targets, 1, C,
+                                                              m->d_depcache + (size_t)m->pois_byp_slot[s] * C, nullptr));
         m->launches++;
         refreshed.push_back(m->pois_byp_slot[s]);
       }
@@ -2123,8 +2152,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       k_sweep<2, 1><<<(unsigned)(((size_t)sp.n_targets * C + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       m->launches++;
     } else {
-      if (warp_per_pair) k_sweep<0, 32><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
-      else k_sweep<0, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], nullptr);
+      if (warp_per_pair) CK(launch_pdl(k_sweep<0, 32>, dim3(nb), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->sdev[s], (double*)nullptr));
+      else CK(launch_pdl(k_sweep<0, 1>, dim3(nb), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->sdev[s], (double*)nullptr));
       m->launches++;
     }
   } else if (sp.type == NIMB_SAMPLER_CONJ_GAMMA || sp.type == NIMB_SAMPLER_CONJ_NORMAL || sp.type == NIMB_SAMPLER_CONJ_BETA) {
@@ -2136,7 +2165,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       if (launch_eval_sum(m, 2, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + ((size_t)e * 2) * C, m->d_newsum + ((size_t)e * 2 + 1) * C,
                           &dp, sp.target_slot, gam)) return 1;
     }
-    k_conj_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->d_newsum);
+    CK(launch_pdl(k_conj_finish, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->d_newsum));
     m->launches++;
   } else {
     int tries = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.tries : 1;
@@ -2144,7 +2173,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     for (int tr = 0; tr < tries; tr++) {
       if (ensure_dep_sums(m, s)) return 1;
       if (sp.type == NIMB_SAMPLER_RW)
-        k_rw_propose<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls);
+        CK(launch_pdl(k_rw_propose, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls));
       else
         k_block_propose<<<(C + 15) / 16, dim3(16, NIMB200_MAX_BLOCK_D), 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
       m->launches++;
@@ -2154,8 +2183,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
         if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
       }
       int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;
-      k_mh_finish<<<(C + TB - 1) / TB, TB, 0, m->stream>>>(m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
-                                                           m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr);
+      CK(launch_pdl(k_mh_finish, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
+                                                           m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr));
       m->launches++;
       if (sp.type == NIMB_SAMPLER_RW_BLOCK && sp.adaptive) {
         m->ran[s]++;
@@ -2249,8 +2278,8 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     }
     if (nmon > 0) {
       size_t total = (size_t)nmon * C;
-      k_monitor_ctr<<<(unsigned)((total + 255) / 256), 256, 0, m->stream>>>(m->T, m->d_mon, nmon, m->d_samples, rows_before, iter0, nburnin, thin,
-                                                                          m->d_ctr, m->d_ticket);
+      CK(launch_pdl(k_monitor_ctr, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, m->stream, m->T, (const int32_t*)m->d_mon, nmon,
+                    m->d_samples, (long long)rows_before, (long long)iter0, (long long)nburnin, (int)thin, m->d_ctr, m->d_ticket));
       m->launches++;
     } else {
       k_bump_iter<<<1, 1, 0, m->stream>>>(m->d_ctr);

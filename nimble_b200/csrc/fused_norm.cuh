@@ -319,6 +319,8 @@ __global__ void k_norm_conj_finish(DevTab T, NormArgs a, int count, const double
 __global__ void __launch_bounds__(256)
 k_norm_conj_from_groups(DevTab T, NormArgs a, const double* __restrict__ gs, int G, int ov_slot,
                         double* __restrict__ dst0, double* __restrict__ dst1) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   __shared__ double sR[8], sN[8];
   const int c = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const double A0 = eval_prog(T, c, a.a_off, a.a_len, 0, 0, ov_slot, 0.0);
@@ -383,6 +385,8 @@ k_norm_group_sums(DevTab T, int sid, NormArgs a, double* __restrict__ gs) {
 }
 
 __global__ void k_norm_conj_draw(DevTab T, int sid, uint64_t seed, uint64_t iter, NormArgs a, const double* __restrict__ gs) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   int c = (int)(gid % T.C);
