@@ -308,6 +308,13 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
 int nimb200_bern_logit_block_logprob_noalloc(const double *d_X, int64_t ld, const double *d_y, int32_t n, int32_t p,
                                              const double *d_beta, int32_t nchains, double *d_out, void *cuda_stream);
 
+/* run(time = TRUE) / getTimes() (P/R/MCMC_build.R:281-285, 323-326): with timing enabled every sampler's launches are bracketed by
+ * CUDA events on the run stream and the elapsed times accumulated per sampler (milliseconds, all chains together; the run is then
+ * not captured into a CUDA graph and synchronises once per iteration, so it is a profiling mode).  sampler_times fills
+ * out_ms[n_samplers] with the totals since timing was last enabled. */
+int nimb200_mcmc_set_timing(nimb200_model *m, int32_t enable);
+int nimb200_mcmc_sampler_times(nimb200_model *m, double *out_ms, int32_t n);
+
 /* online conditional WAIC without grouping (P/R/MCMC_WAIC.R:209-282; call site MCMC_build.R:304-310): once enabled, every
  * post-burn-in iteration of every chain updates, per data node, a running log-sum-exp of its log-density (lppd) and a Welford
  * variance (pWAIC).  nimb200_mcmc_run(reset = 1) clears the statistics.  waic_get: out[0] = WAIC = -2 (lppd - pWAIC),

@@ -63,6 +63,8 @@ class Backend:
                                    C.c_int32, _dp])
         if has_device:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
+            self._set_timing = fn("mcmc_set_timing", [vp, C.c_int32])
+            self._sampler_times = fn("mcmc_sampler_times", [vp, _dp, C.c_int32])
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
             self._peaks = fn("measure_fp64_peaks", [C.c_int, _dp, _dp])
             self._mixed = fn("measure_fp64_mixed", [C.c_int, _dp])
@@ -154,6 +156,18 @@ class DeviceModel:
     def getLogProb(self, decl):
         out = np.empty(self.C)
         self.backend.check(self.backend._get_lp(self.h, decl, _ptr(out)))
+        return out
+
+    def set_timing(self, enable=True):
+        """run(time = TRUE): per-sampler CUDA-event timing (profiling mode, device back end only)."""
+        if not self.backend.has_device:
+            raise BackendError("per-sampler timing is a device feature")
+        self.backend.check(self.backend._set_timing(self.h, int(bool(enable))))
+
+    def sampler_times(self):
+        """Milliseconds per table sampler since timing was enabled."""
+        out = np.zeros(len(self.builder.samplers))
+        self.backend.check(self.backend._sampler_times(self.h, _ptr(out), int(out.size)))
         return out
 
     def waic_enable(self, enable=True):

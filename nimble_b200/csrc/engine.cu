@@ -1071,6 +1071,9 @@ struct nimb200_model {
   int64_t waic_count = 0;            // (iteration, chain) samples accumulated so far
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool time_samplers = false;            // run(time = TRUE): per-sampler CUDA-event timing
+  std::vector<cudaEvent_t> ev_s;         // 2 events per sampler
+  std::vector<double> sampler_ms;        // accumulated per sampler
   double last_ms = 0;
   int64_t last_launches = 0, launches = 0;
   std::vector<void*> allocs;
@@ -1459,6 +1462,7 @@ extern "C" int nimb200_model_free(nimb200_model* m) {
   if (m->graph_exec) cudaGraphExecDestroy(m->graph_exec);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
+  for (auto e : m->ev_s) cudaEventDestroy(e);
   if (m->stream) cudaStreamDestroy(m->stream);
   delete m;
   return 0;
@@ -2252,7 +2256,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   // CUDA graph and replayed (launch latency is what bounds small models).  Iterations in which an RW_block adaptation kernel is
   // due run through the ordinary launch path; so does everything when a NCCL all-reduce is part of the sequence.
   const char* genv = getenv("NIMB200_GRAPH");
-  const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8;
+  const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8 && !m->time_samplers;
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
   int64_t graph_launches = 0;
   std::vector<char> valid_prev;
@@ -2267,8 +2271,19 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   };
   const long long waic_base = m->waic_count;
   auto one_iteration = [&](uint64_t git) -> int {
-    for (size_t s = 0; s < m->samplers.size(); s++)
+    for (size_t s = 0; s < m->samplers.size(); s++) {
+      if (m->time_samplers) CK(cudaEventRecord(m->ev_s[2 * s], m->stream));
       if (run_sampler(m, (int)s, seed, git)) return 1;
+      if (m->time_samplers) CK(cudaEventRecord(m->ev_s[2 * s + 1], m->stream));
+    }
+    if (m->time_samplers) {  // profiling mode: one synchronisation per iteration
+      CK(cudaStreamSynchronize(m->stream));
+      for (size_t s = 0; s < m->samplers.size(); s++) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, m->ev_s[2 * s], m->ev_s[2 * s + 1]));
+        m->sampler_ms[s] += ms;
+      }
+    }
     if (m->waic) {  // before the monitor kernel, whose last block advances the iteration counter
       for (size_t i = 0; i < m->decl.size(); i++) {
         if (!m->d_waic[i] || m->decl[i].n == 0) continue;
@@ -2390,6 +2405,25 @@ extern "C" int nimb200_sampler_state(nimb200_model* m, int32_t s, int32_t what, 
   if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
   if (tmp) cudaFree(tmp);
   if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_set_timing(nimb200_model* m, int32_t enable) {
+  if (!m) return fail("null model");
+  CK(cudaSetDevice(m->device));
+  if (enable && m->ev_s.empty()) {
+    m->ev_s.resize(2 * m->samplers.size());
+    for (auto& e : m->ev_s) CK(cudaEventCreate(&e));
+  }
+  if (enable) m->sampler_ms.assign(m->samplers.size(), 0.0);
+  m->time_samplers = enable != 0;
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_sampler_times(nimb200_model* m, double* out_ms, int32_t n) {
+  if (!m || !out_ms) return fail("null argument");
+  if (n < (int)m->samplers.size()) return fail("output too small");
+  for (size_t s = 0; s < m->samplers.size(); s++) out_ms[s] = s < m->sampler_ms.size() ? m->sampler_ms[s] : 0.0;
   return 0;
 }
 

@@ -838,7 +838,19 @@ class CompiledMCMC:
             raise RuntimeError("WAIC was disabled based on the 'enableWAIC' argument to 'configureMCMC' or 'buildMCMC'")
         return self.dm.waic_get()
 
-    def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0, thin2=None):
+    def getTimes(self):
+        """mcmc$getTimes() after run(time = TRUE) (MCMC_build.R:323-326): seconds per configured sampler, in samplerConfs order
+        (a sampler lowered to several table samplers reports their sum)."""
+        if self.dm is None or not getattr(self, "_timed", False):
+            raise RuntimeError("getTimes: run the MCMC with time = True first")
+        ms = self.dm.sampler_times()
+        out = np.zeros(len(self.conf.samplerConfs))
+        index = {id(sc): i for i, sc in enumerate(self.conf.samplerConfs)}
+        for k, (sc, _) in enumerate(self.lowering.sampler_map):
+            out[index[id(sc)]] += ms[k] * 1e-3
+        return out
+
+    def run_chains(self, inits_matrix, niter, nburnin=0, thin=None, reset=True, seed=0, thin2=None, time=False):
         """All chains at once.  inits_matrix: [nchains][n_slots] (ignored when reset is False)."""
         if niter < 0:
             raise ValueError("cannot specify niter < 0")
@@ -854,6 +866,9 @@ class CompiledMCMC:
         if not reset and nburnin != 0:
             raise ValueError("cannot specify nburnin when using reset = FALSE.")
         dm = self._ensure(inits_matrix.shape[0])
+        if time or getattr(self, "_timed", False):
+            dm.set_timing(bool(time))
+            self._timed = bool(time)
         if reset:
             dm.set_values(inits_matrix)
             if np.any(np.isnan(inits_matrix)):

@@ -270,3 +270,20 @@ def test_sweep_by_products_keep_trajectories(oracle, b200, monkeypatch):
         plain = run(compile_on(b200, conf), inits, 150, 0, seed=3)
         monkeypatch.delenv("NIMB200_NO_BYPRODUCT")
         assert rel_err(plain, so).max() < RTOL_TRAJ and rel_err(plain, sg).max() < RTOL_TRAJ
+
+
+def test_sampler_timing_mode(b200):
+    """run(time = TRUE) / getTimes() (MCMC_build.R:281-285, 323-326): per-sampler device times, one entry per configured sampler;
+    the timed run takes the ordinary launch path (no CUDA graph) and must produce the same samples."""
+    m, conf = sm.SMALL["glmm"]()
+    inits = sm.random_inits(m, 6, 2, 0.1)
+    cg = compile_on(b200, conf)
+    plain = cg.run_chains(inits, 60, 0, 1, True, 4).copy()
+    with pytest.raises(RuntimeError, match="time = True"):
+        cg.getTimes()
+    timed = cg.run_chains(inits, 60, 0, 1, True, 4, time=True)
+    assert np.array_equal(plain, timed)
+    t = cg.getTimes()
+    assert t.shape == (len(conf.samplerConfs),) and np.all(t > 0)
+    total_ms, _ = cg.dm.last_timing()
+    assert t.sum() * 1e3 <= total_ms * 1.05
