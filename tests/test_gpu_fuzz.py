@@ -1,5 +1,7 @@
 """GPU fuzz: randomly assembled models (tests/fuzz_models.py), default sampler assignment, device against oracle through the
 C ABI -- monitored samples and the complete final state of every chain, across at least one adaptation step."""
+import os
+
 import numpy as np
 import pytest
 
@@ -9,7 +11,11 @@ from tests.helpers import compile_on, rel_err, run
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("seed", range(int(__import__("os").environ.get("NIMB200_FUZZ_CASES", "50"))))
+_FIRST = int(os.environ.get("NIMB200_FUZZ_FIRST", "0"))
+_CASES = int(os.environ.get("NIMB200_FUZZ_CASES", "50"))
+
+
+@pytest.mark.parametrize("seed", range(_FIRST, _FIRST + _CASES))
 def test_random_model_matches_oracle(oracle, b200, seed):
     m, conf, nchains = make_case(seed)
     rng = np.random.default_rng(1000 + seed)
