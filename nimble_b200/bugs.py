@@ -7,12 +7,12 @@ statements `lhs ~ dist(args)`, `lhs <- expr`, `link(lhs) <- expr`, nested `for (
 
 AST nodes are tuples:
   ('num', v)  ('var', name, [index, ...])  ('range', lo, hi)  ('call', fname, [args], {kw: arg})
-  ('bin', op, l, r)  ('neg', e)
+  ('bin', op, l, r)  ('neg', e)  ('sub', expr, [index, ...])   (op may be '%*%')
 Statements: ('for', var, lo, hi, [stmts])  ('stoch', lhs, dist, args, kwargs)  ('determ', link|None, lhs, expr)
 """
 import re
 
-_TOK = re.compile(r"\s*(?:(\d+\.\d*(?:[eE][-+]?\d+)?|\.\d+(?:[eE][-+]?\d+)?|\d+(?:[eE][-+]?\d+)?)|([A-Za-z_.][A-Za-z0-9_.]*)|(<-|[-+*/^()\[\]{},:~=;]))")
+_TOK = re.compile(r"\s*(?:(\d+\.\d*(?:[eE][-+]?\d+)?|\.\d+(?:[eE][-+]?\d+)?|\d+(?:[eE][-+]?\d+)?)|([A-Za-z_.][A-Za-z0-9_.]*)|(<-|%\*%|[-+*/^()\[\]{},:~=;]))")
 
 
 def _tokenize(text):
@@ -71,7 +71,7 @@ class _P:
 
     def term(self):
         e = self.unary()
-        while self.peek() in (("op", "*"), ("op", "/")):
+        while self.peek() in (("op", "*"), ("op", "/"), ("op", "%*%")):
             op = self.next()[1]
             e = ("bin", op, e, self.unary())
         return e
@@ -102,6 +102,12 @@ class _P:
         if k == "op" and v == "(":
             e = self.expr()
             self.expect(")")
+            if self.accept("["):   # (x[i, 1:p] %*% beta[1:p])[1, 1]: an index applied to an expression
+                idx = []
+                while not self.accept("]"):
+                    idx.append(self.index())
+                    self.accept(",")
+                return ("sub", e, idx)
             return e
         if k == "id":
             if self.accept("("):

@@ -16,25 +16,40 @@ from .model import Model, ModelError, tree_reads_var
 
 
 # ----------------------------------------------------------------------------- conjugacy (MCMC_conjugacy.R)
+def _read_key(pos):
+    """Which element of the variable a `cvar` read touches at each node: one element for all nodes, or one per node."""
+    if isinstance(pos, (int, np.integer)):
+        return ("el", int(pos))
+    return ("els", np.asarray(pos, dtype=np.int64).tobytes())
+
+
 def _linear_form(tree, var):
-    """Is `tree` a + b*target?  Returns None (not linear) or (has_offset, has_coeff).
-    Counterpart of cc_checkLinearity, P/R/MCMC_conjugacy.R:1397-1524."""
+    """Is `tree` a + b*target for every scalar element `target` of `var` it reads?  Returns None (not linear), "free" (does
+    not read var) or (has_offset, has_coeff, key).  Counterpart of cc_checkLinearity, P/R/MCMC_conjugacy.R:1397-1524, which
+    works on ONE scalar target node: the other elements of the same variable are ordinary terms of the offset.  `key` says
+    which element a node reads; when the expression reads several elements at one node (inprod over a slice, b[1] + b[2]*x)
+    the key is "mixed" and both an offset and a coefficient are present for each of them -- the `linear` link, whose offset
+    and coefficient the sampler finds per node by the set-to-0 / set-to-1 probing (MCMC_conjugacy.R:766-820)."""
     if not tree_reads_var(tree, var):
         return "free"
     k = tree[0]
     if k == "cvar":
-        return (False, False)
+        return (False, False, _read_key(tree[2]))
     if k == "inprod":
-        return (False, True)
+        # inprod(X[i, 1:p], beta[1:p]) seen from beta[j]: coefficient X[i, j], offset = the other p - 1 terms
+        # (test-mcmc.R:1684-1700: conjugate_dnorm_dnorm_linear)
+        if tree[4] == 1:
+            return (False, True, ("el", int(tree[3])))
+        return (True, True, "mixed")
     if k == "dyn":
         # mu[z[i]] as a function of one element of mu: that element (index equal) or another one -- offset and coefficient both
         # depend on the node, found by the numerical probing; the index itself must not read the target
         if tree_reads_var(tree[5], var):
             return None
-        return (True, True)
+        return (True, True, "mixed")
     if k == "un" and tree[1] == T.OP_NEG:
         f = _linear_form(tree[2], var)
-        return None if f in (None, "free") else (f[0], True)
+        return None if f in (None, "free") else (f[0], True, f[2])
     if k == "bin":
         op, l, r = tree[1], tree[2], tree[3]
         fl, fr = _linear_form(l, var), _linear_form(r, var)
@@ -42,23 +57,28 @@ def _linear_form(tree, var):
             return None
         if op in (T.OP_ADD, T.OP_SUB):
             if fl == "free":
-                return (True, fr[1] or op == T.OP_SUB)
+                return (True, fr[1] or op == T.OP_SUB, fr[2])
             if fr == "free":
-                return (True, fl[1])
-            return (fl[0] or fr[0], True)
+                return (True, fl[1], fl[2])
+            if fl[2] == fr[2] and fl[2] != "mixed":   # the same element on both sides: b + b, b - (a - b)
+                return (fl[0] or fr[0], True, fl[2])
+            return (True, True, "mixed")              # different elements: each is part of the other's offset
         if op == T.OP_MUL:
             if fl == "free":
-                return (fr[0], True)
+                return (fr[0], True, fr[2])
             if fr == "free":
-                return (fl[0], True)
+                return (fl[0], True, fl[2])
+            # target on both sides is not linear (cc_checkLinearity returns NULL); two provably different elements are
+            if fl[2] != "mixed" and fr[2] != "mixed" and fl[2][0] == "el" and fr[2][0] == "el" and fl[2] != fr[2]:
+                return (True, True, "mixed")
             return None
         if op == T.OP_DIV and fr == "free":
-            return (fl[0], True)
+            return (fl[0], True, fl[2])
     return None
 
 
 def _link_code(f):
-    off, co = f
+    off, co = f[0], f[1]
     if off and co:
         return T.LINK_LINEAR
     if off:

@@ -220,6 +220,14 @@ class Model:
             return ("const", float(e[1]))
         if k == "neg":
             return ("un", T.OP_NEG, self._lower(e[1], env, n, depth))
+        if k == "sub":
+            # (X[i, 1:p] %*% beta[1:p])[1, 1]: the single element of a row-by-vector product (test-mcmc.R:1793-1803)
+            inner = e[1]
+            if inner[0] == "bin" and inner[1] == "%*%" and all(x == ("num", 1.0) for x in e[2]):
+                return self._lower_inprod(inner[2], inner[3], env, n)
+            raise ModelError("indexing an expression is supported only as (row %*% vector)[1, 1]")
+        if k == "bin" and e[1] == "%*%":
+            return self._lower_inprod(e[2], e[3], env, n)
         if k == "bin":
             a, b = self._lower(e[2], env, n, depth), self._lower(e[3], env, n, depth)
             if e[1] == "^" and b == ("const", 2.0):
@@ -233,6 +241,9 @@ class Model:
                 return ("bin", T.OP_POW, self._lower(args[0], env, n, depth), self._lower(args[1], env, n, depth))
             if f == "inprod" and len(args) == 2:
                 return self._lower_inprod(args[0], args[1], env, n)
+            if f == "sum" and len(args) == 1 and args[0][0] == "bin" and args[0][1] == "*":
+                # sum(beta[1:p] * X[i, 1:p]) is the same node function as inprod() (MCMC_conjugacy.R:1478-1486)
+                return self._lower_inprod(args[0][2], args[0][3], env, n)
             raise ModelError("unsupported function in model code: %s()" % f)
         if k == "var":
             name_, idx = e[1], e[2]
