@@ -1273,8 +1273,8 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
       const int ix = na.mode < 0 ? 0 : (na.mode == NIMB_IDX_IARR ? 1 : 2);
 #define NIMB_NORM_TMA(M, I)                                                                                        \
   do {                                                                                                             \
-    static bool attr = false;                                                                                      \
-    if (!attr) { cudaFuncSetAttribute(k_norm_stream_tma<M, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NW_SMEM); attr = true; } \
+    static std::atomic<unsigned long long> attr{0};                                                                \
+    ensure_dyn_smem(k_norm_stream_tma<M, I>, NW_SMEM, attr);                                                       \
     k_norm_stream_tma<M, I><<<grid, NF_THREADS, NW_SMEM, m->stream>>>(m->T, na, lo, hi, npw, M == 1 ? slot : -1, m->d_partials); \
   } while (0)
       if (mode == 0) { if (ix == 0) NIMB_NORM_TMA(0, 0); else if (ix == 1) NIMB_NORM_TMA(0, 1); else NIMB_NORM_TMA(0, 2); }

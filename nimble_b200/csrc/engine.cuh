@@ -1,12 +1,26 @@
 // engine.cuh -- shared declarations of the sm_100a library (host model object + device table view).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <string>
 #include <vector>
 #include "../../include/nimb200.h"
 
 namespace nimb {
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute of a kernel: set it once for every device a
+// model is created on (`done` is one call site's bit mask of devices already configured; concurrent callers at worst
+// set the attribute twice).
+template <typename K>
+static inline void ensure_dyn_smem(K kernel, size_t bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  done.fetch_or(bit, std::memory_order_release);
+}
 
 // Device view of the node table + chain-major state.  Passed to kernels by value.
 struct DevTab {

@@ -183,15 +183,11 @@ __global__ void k_pad_x(const double* __restrict__ X, const double* __restrict__
 static int nk_of(int p) { int nk = (p + 3) / 4; return nk <= 4 ? 4 : nk <= 8 ? 8 : nk <= 13 ? 13 : 16; }
 static int p4_of(int p) { return 4 * nk_of(p); }
 
-static int g_chunks_cache_n = -1, g_chunks_cache = 0;
 static int chunks_for(int n) {
   // node chunks: aim at ~2 waves of 2 resident blocks per SM when there are 16 chain tiles; the count only
-  // depends on n so that the scratch size is known up front
-  if (n == g_chunks_cache_n) return g_chunks_cache;
+  // depends on n so that the scratch size is known up front (stateless: models on several devices / threads share it)
   int ntiles = (n + FT_M - 1) / FT_M;
-  int chunks = std::min(ntiles, 148);
-  g_chunks_cache_n = n; g_chunks_cache = chunks;
-  return chunks;
+  return std::min(ntiles, 148);
 }
 
 int fused_bern_logit_tiles(int n) { return chunks_for(n); }
@@ -215,11 +211,8 @@ template <int NK>
 static void launch_nk(const double* Xpad, const double* ypad, int n, int p, const double* state, int beta_slot, int C,
                       int chunks, int tpc, int tb, int te, double* partials, cudaStream_t st) {
   size_t smem = sizeof(double) * (2 * ((size_t)FT_M * 4 * NK + FT_M) + 2 * FT_NC) + 16 + sizeof(MathTab);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_fused_bern_logit<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> attr_set{0};
+  ensure_dyn_smem(k_fused_bern_logit<NK>, smem, attr_set);
   dim3 grid((C + FT_NC - 1) / FT_NC, chunks);
   k_fused_bern_logit<NK><<<grid, FT_THREADS, smem, st>>>(Xpad, ypad, n, p, state, beta_slot, C, tpc, tb, te, partials);
 }

@@ -140,6 +140,8 @@ extern "C" int nimb200_bern_logit_block_logprob_noalloc(const double* d_X, int64
                                                         void* cuda_stream) {
   if (!d_X || !d_y || !d_beta || !d_out) return fail("nimb200_bern_logit_block_logprob_noalloc: null pointer");
   if (n < 0) return fail("nimb200_bern_logit_block_logprob_noalloc: n < 0");
+  // the kernel's row counters are 32-bit: keep chunk starts and the 16-row stride clear of INT32_MAX
+  if (n > INT32_MAX - 32 * NA_CHUNKS) return fail("nimb200_bern_logit_block_logprob_noalloc: n exceeds " + std::to_string(INT32_MAX - 32 * NA_CHUNKS));
   if (p < 1 || p > 4 * NA_MAXK) return fail("nimb200_bern_logit_block_logprob_noalloc: p must be between 1 and 64");
   if (ld < p) return fail("nimb200_bern_logit_block_logprob_noalloc: row stride ld smaller than p");
   if (nchains < 1 || nchains > NIMB200_NOALLOC_MAX_CHAINS)
@@ -163,7 +165,7 @@ extern "C" int nimb200_bern_logit_block_logprob_noalloc(const double* d_X, int64
     scratch = g_scratch_addr[dev];
   }
   cudaStream_t st = (cudaStream_t)cuda_stream;
-  int rows_per_chunk = (n + NA_CHUNKS - 1) / NA_CHUNKS;
+  int rows_per_chunk = (int)(((long long)n + NA_CHUNKS - 1) / NA_CHUNKS);   // 64-bit: n may be within NA_CHUNKS of INT32_MAX
   rows_per_chunk = (rows_per_chunk + 15) & ~15;
   if (rows_per_chunk == 0) rows_per_chunk = 16;
   dim3 grid(NA_CHUNKS, (nchains + NA_NC - 1) / NA_NC);

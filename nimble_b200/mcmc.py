@@ -170,6 +170,7 @@ class MCMCconf:
         self.enableWAIC = bool(enableWAIC)   # online conditional WAIC, one data node per group (MCMC_configuration.R `enableWAIC`)
         self.control_defaults = dict(control or {})
         use = set(nodes) if nodes is not None else None
+        self._classify_predictive(use)
         for var in model.topo_vars():
             if use is not None and var not in use:
                 continue
@@ -185,12 +186,63 @@ class MCMCconf:
     def _is_terminal(self, decl):
         return not [d for d in self.model.dependents(decl.var) if d is not decl]
 
+    def _children(self, decl):
+        return [d for d in self.model.dependents(decl.var) if d is not decl]
+
+    def _downstream(self, decl):
+        """Declarations downstream of `decl` (not itself), parents first."""
+        seen, order = set(), []
+
+        def visit(d):
+            for c in self._children(d):
+                if c.index not in seen:
+                    seen.add(c.index)
+                    visit(c)
+                    order.append(c)
+        visit(decl)
+        rank = {v: i for i, v in enumerate(self.model.topo_vars())}
+        return sorted(order, key=lambda d: (rank.get(d.var, len(rank)), d.index))
+
+    def _classify_predictive(self, use):
+        """Predictive declarations: stochastic, not data, no data anywhere downstream (BUGS_model.R:442).  Among them, the
+        roots of simulable networks get ONE posterior_predictive sampler that simulates the whole downstream network, whose
+        members get no sampler of their own (MCMC_configuration.R:247-287; sampler MCMC_samplers.R:86-105).  Granularity is
+        the declaration: one whose nodes are only partly predictive is treated as non-predictive."""
+        model = self.model
+        pred = {d.index for d in model.decls if not d.is_data}
+        changed = True
+        while changed:
+            changed = False
+            for d in model.decls:
+                if d.index in pred and any(c.index not in pred for c in self._children(d)):
+                    pred.discard(d.index)
+                    changed = True
+        self.predictive_decls = pred
+        # a network can be simulated on the device when every member has a variate generator and does not read itself
+        ok = {i for i in pred if model.decls[i].dist in self._PP_DISTS
+              and not any(v == model.decls[i].var for v, _ in model.decls[i].reads())
+              and (use is None or model.decls[i].var in use)}
+        changed = True
+        while changed:
+            changed = False
+            for i in list(ok):
+                if any(c.index not in ok for c in self._children(model.decls[i])):
+                    ok.discard(i)
+                    changed = True
+        parents_ok = lambda d: any(model.decls[i].var == v for v, _ in d.reads() for i in ok)
+        self.pp_roots = {i for i in ok if not parents_ok(model.decls[i])}
+        self.pp_covered = ok - self.pp_roots
+
     def _add_default(self, decl, useConjugacy):
         model = self.model
-        # terminal (end) nodes are posterior predictive: simulated from their own distribution, MCMC_configuration.R:283-285, 368
-        # (a predictive node that has predictive descendants keeps its ordinary sampler here)
-        if self._is_terminal(decl) and decl.dist in self._PP_DISTS:
-            self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, decl.var, decl.pos, self.control_defaults))
+        # the root of an entirely non-data network (an end node included) gets a posterior_predictive sampler which simulates the
+        # root and everything downstream of it; the downstream members get nothing else (MCMC_configuration.R:283-287, 368)
+        if decl.index in self.pp_covered:
+            return
+        if decl.index in self.pp_roots:
+            sc = SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, decl.var, decl.pos, self.control_defaults)
+            sc.network = [d.index for d in self._downstream(decl)]
+            self.samplerConfs.append(sc)
             return
         conj = check_conjugacy(model, decl) if useConjugacy else None
         if conj is not None:
@@ -277,13 +329,18 @@ class MCMCconf:
                 raise ValueError("cannot use slice sampler on more than one target node")  # MCMC_samplers.R:891
             self.samplerConfs.append(SamplerConf(T.SAMPLER_SLICE, var, pos, ctrl))
         elif tname == "posterior_predictive":
+            net = []
             for decl in self.model.decl_of(var):
-                if not self._is_terminal(decl):
+                if decl.index not in self.predictive_decls:
                     # MCMC_samplers.R:93-94
                     raise ValueError("posterior_predictive sampler should not be assigned to non-posterior-predictive nodes")
-                if decl.dist not in self._PP_DISTS:
-                    raise NotImplementedError("posterior_predictive: no device variate generator for the distribution of %s" % var)
-            self.samplerConfs.append(SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl))
+                for d in [decl] + self._downstream(decl):
+                    if d.dist not in self._PP_DISTS:
+                        raise NotImplementedError("posterior_predictive: no device variate generator for the distribution of %s" % d.var)
+                net.extend(d.index for d in self._downstream(decl) if d.index not in net)
+            sc = SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, var, pos, ctrl)
+            sc.network = net
+            self.samplerConfs.append(sc)
         else:
             raise NotImplementedError("sampler type %r is not part of the B200 sampling path (supported: RW, "
                                       "RW_block, binary, conjugate, posterior_predictive, slice, categorical); there is no CPU fallback" % type)
@@ -616,7 +673,7 @@ class _Lowering:
         off = np.searchsorted(tgt[order], np.arange(Tn + 1), side="left")
         return (T.SEL_CSR, self.b.add_iarr(off), self.b.add_iarr(order))
 
-    def _emit_sampler(self, sc, positions, vectorised):
+    def _emit_sampler(self, sc, positions, vectorised, owner=None):
         model, b = self.model, self.b
         var = sc.var
         decl = [d for d in model.decl_of(var) if np.isin(positions[0], d.pos)][0]
@@ -685,8 +742,14 @@ class _Lowering:
             else:
                 dep0.sel, dep0.a = T.SEL_SAME, node0
             b.deps.append(dep0)
-        # stage 1: stochastic dependents
+        # stage 1: stochastic dependents.  Samplers of non-predictive targets leave predictive nodes out of their calculations
+        # (the reference's default MCMCusePredictiveDependenciesInCalculations = FALSE, P/R/options.R:190, MCMC_build.R:156-176);
+        # a sampler whose target is itself predictive keeps its whole Markov blanket (MCMC_utils.R:441-451)
+        predictive = getattr(self.conf, "predictive_decls", set())
+        skip_predictive = decl.index not in predictive
         for dep in model.dependents(var):
+            if skip_predictive and dep.index in predictive and dep is not decl:
+                continue
             tgt = self._target_of_nodes(dep, var, pos0, span)
             if tgt is None:
                 continue
@@ -715,6 +778,10 @@ class _Lowering:
                 sel = self._selection(tgt, dep.n, Tn)
             if dep.var == var and not dep.is_data:
                 if block:
+                    # x[t] ~ dnorm(x[t-1], ..): inside the block the prior nodes are the stage-0 entries above; a node OUTSIDE
+                    # the block whose prior reads a block element would silently drop out of the MH ratio -> refuse
+                    if np.any((dep.pos < pos0) | (dep.pos >= pos0 + span)):
+                        raise ModelError("%s: RW_block must cover every node of a declaration that reads the variable itself" % var)
                     continue
                 raise ModelError("%s: a node's own declaration reads the variable; not supported" % var)
             de = T.Dep()
@@ -727,7 +794,7 @@ class _Lowering:
             b.deps.append(de)
         s.n_dep = len(b.deps) - s.dep_off
         b.samplers.append(s)
-        self.sampler_map.append((sc, np.asarray(positions)))
+        self.sampler_map.append((owner if owner is not None else sc, np.asarray(positions)))
 
     def _separable(self, sc):
         """Can the targets of this scalar sampler be updated as one parallel sweep?  True when no
@@ -763,6 +830,16 @@ class _Lowering:
             else:
                 for p in sc.positions:
                     self._emit_sampler(sc, np.array([p]), False)
+            # posterior_predictive: model$simulate(simNodes) walks the whole downstream network in topological order
+            # (MCMC_samplers.R:91, 97) -- here one table sampler per member declaration, parents first, right after the root's
+            for di in getattr(sc, "network", []) if sc.type == T.SAMPLER_POSTERIOR_PREDICTIVE else []:
+                dd = model.decls[di]
+                sub = SamplerConf(T.SAMPLER_POSTERIOR_PREDICTIVE, dd.var, dd.pos, sc.control)
+                if self._separable(sub):
+                    self._emit_sampler(sub, sub.positions, True, owner=sc)
+                else:
+                    for p in sub.positions:
+                        self._emit_sampler(sub, np.array([p]), False, owner=sc)
         # the device records ONE set of columns: monitors, then those of monitors2 that are not among them; run_chains splits
         # the rows and columns into mvSamples / mvSamples2 again
         self.cols1, self.cols2, self.colnames2 = [], [], []
@@ -981,7 +1058,8 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
         raise TypeError("mcmc argument must be a *compiled* NIMBLE MCMC algorithm")
     if isinstance(inits, (list, tuple)) and len(inits) != nchains and len(inits) != 1:
         raise ValueError("inits list must be of length nchains")
-    seed = 0 if setSeed in (False, True, None) else int(setSeed)
+    # MCMC_run.R:130-134: TRUE -> seed 0 (plus the chain index), a number -> that seed; `1 == True` in Python, so test the type
+    seed = 0 if (setSeed is None or isinstance(setSeed, (bool, np.bool_))) else int(setSeed)
     if setSeed is False:
         seed = int(np.random.SeedSequence().entropy % (1 << 63))
     rows = []

@@ -6,8 +6,9 @@ synchronisation is not acceptable.  For them the library offers one entry point 
 device array built into the library.  This test calls it through the C ABI twice in a row (the second call with
 fewer chains and other parameters, so that stale contents of the shared scratch from the first call are present)
 and checks each result against the ordinary entry point nimb200_calculate() on the same X, y and beta, at the same
-tolerance the other parity tests use (1e-12 relative).  It also checks that a request beyond the built-in limit is
-refused with a clear message.  Collected last on purpose: a run that stops at the first failure has then already
+tolerance the other parity tests use (1e-12 relative), against the CPU oracle's block sum of the same declaration, and
+that the device's free memory is the same before and after each call (nothing was allocated behind the caller's back).
+It also checks that a request beyond the built-in limit is refused with a clear message.  Collected last on purpose: a run that stops at the first failure has then already
 run every other test."""
 import ctypes as C
 
@@ -28,11 +29,11 @@ def _noalloc(lib):
     return f
 
 
-def test_noalloc_matches_calculate_twice_in_a_row(b200):
+def test_noalloc_matches_calculate_twice_in_a_row(b200, oracle):
     import torch
     N, p = 5000, 50
     m, conf = configs.logistic(N=N, p=p, seed=77)
-    cg = compile_on(b200, conf)
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
     ydecl = len(cg.builder.decls) - 1
     X = np.ascontiguousarray(m.constants["X"])
     y = np.ascontiguousarray(m.data["y"])
@@ -48,15 +49,21 @@ def test_noalloc_matches_calculate_twice_in_a_row(b200):
         dm = cg._ensure(nchains)
         dm.set_values(inits)
         want = dm.calculate(ydecl)                              # existing entry point
+        do = co._ensure(nchains)
+        do.set_values(inits)
+        want_cpu = do.calculate(ydecl)                          # the oracle's left-to-right sum of dbinom(y, 1, ilogit(eta))
         dbeta = torch.tensor(np.ascontiguousarray(beta.T), dtype=torch.float64, device="cuda")   # [p][nchains]
         dout = torch.full((nchains,), float("nan"), dtype=torch.float64, device="cuda")
         torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]              # cudaMemGetInfo
         rc = f(dX.data_ptr(), p, dy.data_ptr(), N, p, dbeta.data_ptr(), nchains, dout.data_ptr(), None)
         assert rc == 0, b200._err()
         torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free_before
         got = dout.cpu().numpy()
         assert np.all(np.isfinite(got))
         assert rel_err(got, want).max() < RTOL_LP, rel_err(got, want).max()
+        assert rel_err(got, want_cpu).max() < RTOL_LP, rel_err(got, want_cpu).max()
 
 
 def test_noalloc_rejects_sizes_beyond_the_builtin_scratch(b200):
