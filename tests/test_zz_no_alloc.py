@@ -42,6 +42,10 @@ def test_noalloc_matches_calculate_twice_in_a_row(b200, oracle):
     f = _noalloc(b200.lib)
     rng = np.random.default_rng(3)
     bs = m.var_slot["beta"]
+    # the documented set-up call: the first call on a device resolves the scratch array's address (and, with CUDA's lazy
+    # module loading, brings the kernels' code onto the device) -- free memory is compared on the calls after it
+    d1 = torch.zeros(8, dtype=torch.float64, device="cuda")
+    assert f(d1.data_ptr(), 1, d1.data_ptr(), 1, 1, d1.data_ptr(), 1, d1.data_ptr(), None) == 0, b200._err()
     for nchains, scale in ((70, 0.8), (33, 2.5)):
         beta = scale * rng.standard_normal((nchains, p))
         inits = np.tile(m.init_vector(), (nchains, 1))
