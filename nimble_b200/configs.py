@@ -56,6 +56,7 @@ def logistic(N=1_000_000, p=50, seed=1001):
     y = (rng.random(N) < 1.0 / (1.0 + np.exp(-eta))).astype(np.float64)
     m = nimbleModel(LOGISTIC_CODE, constants={"N": N, "p": p, "X": X}, data={"y": y},
                     inits={"tau_b": 1.0, "mu_b": 0.0, "beta": np.zeros(p)}, name="logistic")
+    m.truth = {"beta": beta_true}
     conf = configureMCMC(m, monitors=["tau_b", "mu_b", "beta"])
     conf.removeSamplers("beta")
     conf.removeSamplers("tau_b")
@@ -96,6 +97,7 @@ def lmm(N=10_000_000, G=10_000, seed=1003, permute=False):
     y = 2.0 + u_true[grp - 1] + 1.5 * rng.standard_normal(N)
     m = nimbleModel(LMM_CODE, constants={"N": N, "G": G, "grp": grp}, data={"y": y},
                     inits={"mu": 0.0, "sig_u": 1.0, "sig_e": 1.0, "u": np.zeros(G)}, name="lmm")
+    m.truth = {"mu": 2.0, "sig_e": 1.5, "sig_u": 1.0, "u": u_true}
     conf = configureMCMC(m, monitors=["mu", "sig_u", "sig_e"])
     for v in ("sig_u", "sig_e"):
         conf.removeSamplers(v)
@@ -136,6 +138,7 @@ def occupancy(S=100_000, J=10, seed=1004):
     zinit[zinit == 0] = 1.0  # start every site occupied: always a valid state
     m = nimbleModel(OCCUPANCY_CODE, constants={"S": S, "J": J, "x": x, "w": w}, data={"y": y},
                     inits={"b0": 0.0, "b1": 0.0, "a0": 0.0, "a1": 0.0, "z": zinit}, name="occupancy")
+    m.truth = {"b0": 0.3, "b1": 1.0, "a0": -0.5, "a1": 0.7, "z": z}
     conf = configureMCMC(m, monitors=["b0", "b1", "a0", "a1"])
     return m, conf
 
@@ -166,6 +169,7 @@ def glmm(N=1_000_000, G=10_000, seed=1005):
     y = rng.poisson(lam_true[grp - 1] * np.exp(0.5 + 0.3 * x)).astype(np.float64)
     m = nimbleModel(GLMM_CODE, constants={"N": N, "G": G, "grp": grp, "x": x}, data={"y": y},
                     inits={"a": 1.0, "b": 1.0, "b0": 0.0, "b1": 0.0, "lam": np.ones(G)}, name="glmm")
+    m.truth = {"b0": 0.5, "b1": 0.3, "lam": lam_true}
     conf = configureMCMC(m, monitors=["a", "b", "b0", "b1"])
     conf.removeSamplers("a")
     conf.addSampler("a", type="RW", control={"log": True})
