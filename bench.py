@@ -41,10 +41,11 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true",
                     help="skip the live measurement of the HBM-bound kernel of configs[2] (rank 0, single-GPU runs only)")
-    ap.add_argument("--full", action="store_true",
-                    help="also run the full protocol of SURVEY 8d (niter 5000, nburnin 2500) and report min-ESS/s from it")
-    ap.add_argument("--full-niter", type=int, default=5000)
-    ap.add_argument("--ess-chains", type=int, default=64, help="chains used for the ESS estimate of the full run")
+    ap.add_argument("--ess-niter", type=int, default=5000,
+                    help="iterations of the min-ESS/s protocol run (SURVEY 8d: niter 5000, nburnin = niter / 2); 0 skips it")
+    ap.add_argument("--ess-chains", type=int, default=0, help="chains the ESS estimate uses (0 = all chains of the rank)")
+    ap.add_argument("--ref-ess-budget-s", type=float, default=420.0,
+                    help="reference arm: wall-clock budget of its min-ESS/s protocol run; it stops early (and says so) beyond it")
     return ap.parse_args()
 
 
@@ -105,24 +106,21 @@ def build_model(a):
     return m, conf, time.time() - t0
 
 
-def cpu_baseline(a, conf, model, niter, warm=1):
-    """The oracle (CPU restatement of compiled NIMBLE's sampling path) on the host cores: one chain per thread,
-    the one-process-per-core pattern of the NIMBLE manual (chapter_MCMC.Rmd:1223-1229)."""
+def _oracle_runner(a, conf, model, chains, seed):
+    """The oracle (CPU restatement of compiled NIMBLE's sampling path) with one chain per host thread, the
+    one-process-per-core pattern of the NIMBLE manual (chapter_MCMC.Rmd:1223-1229).  Returns (dm, run, evals_per_iteration)."""
     import nimble_b200 as nb
     from nimble_b200 import configs
     from oracle.oracle_capi import oracle_backend
     ob = oracle_backend()
-    cores = os.cpu_count() or 1
-    chains = a.cpu_chains or min(cores, 64)
     cm = nb.compileNimble(nb.buildMCMC(conf), backend=ob)
     dm = cm._ensure(chains)
     inits = np.stack([model.init_vector(i) for i in configs.logistic_inits(a.p, chains)])
     dm.set_values(inits)
-    evals_iter = configs.evals_per_iteration(cm)
 
     def run(n_it, reset):
         ob.check(ob.prepare(dm.h, n_it, 0, 1, 1 if reset else 0))
-        ths = [threading.Thread(target=ob.run_range, args=(dm.h, n_it, 0, 1, 1 if reset else 0, 12345, c, c + 1))
+        ths = [threading.Thread(target=ob.run_range, args=(dm.h, n_it, 0, 1, 1 if reset else 0, seed, c, c + 1))
                for c in range(chains)]
         t0 = time.perf_counter()
         for t in ths:
@@ -132,15 +130,50 @@ def cpu_baseline(a, conf, model, niter, warm=1):
         dt = time.perf_counter() - t0
         ob.check(ob.finish(dm.h, n_it, 0, 1))
         return dt
+    return dm, run, configs.evals_per_iteration(cm), cm
+
+
+def cpu_baseline(a, conf, model, niter, warm=1):
+    cores = os.cpu_count() or 1
+    chains = a.cpu_chains or min(cores, 64)
+    dm, run, evals_iter, _ = _oracle_runner(a, conf, model, chains, 12345)
     if warm:
         run(warm, True)
     dt = run(niter, False if warm else True)
-    samples = dm.samples()
     val = evals_iter * chains * niter / dt
     return {"value": val, "unit": UNIT, "cores": min(chains, cores), "kind": "port",
             "sample": "%d chains x %d iterations of the same N=%d p=%d workload, one chain per host thread (%d cores)"
                       % (chains, niter, a.n, a.p, cores),
-            "ms_per_iteration_per_chain": dt / niter * 1e3, "seconds": dt}, samples, dt, chains
+            "ms_per_iteration_per_chain": dt / niter * 1e3, "seconds": dt}, dt, chains
+
+
+ESS_SEED = 777
+
+
+def cpu_min_ess(a, conf, model):
+    """min-ESS/s of the reference arm from ITS OWN samples (MCMC efficiency as P/R/MCMC_autoBlock.R:297-306 defines it: min over
+    the monitored columns of effectiveSize / run time; sums over chains, run time includes burn-in).  Same protocol, seed and
+    initial values as the GPU arm's min_ess block, so these chains are the first `chains` chains of that run.  The run proceeds
+    in segments and stops early once the wall-clock budget is spent (the line then says how far it got)."""
+    from nimble_b200.ess import min_ess
+    cores = os.cpu_count() or 1
+    chains = a.cpu_chains or min(cores, 64)
+    dm, run, evals_iter, cm = _oracle_runner(a, conf, model, chains, ESS_SEED)
+    seg, done, wall = 250, 0, 0.0
+    while done < a.ess_niter:
+        n_it = min(seg, a.ess_niter - done)
+        if done and wall + wall / done * n_it > a.ref_ess_budget_s:
+            break
+        wall += run(n_it, done == 0)
+        done += n_it
+    s = dm.samples()[:, done // 2:done, :]
+    mess, tot = min_ess(s)
+    return {"min_ess_per_sec": mess / wall if wall > 0 else None, "min_ess_total": mess, "chains": chains, "niter": done,
+            "nburnin": done // 2, "protocol_niter": a.ess_niter, "complete": done == a.ess_niter, "seconds": wall,
+            "worst_column": cm.colnames[int(np.argmin(np.where(tot > 0, tot, np.inf)))] if np.any(tot > 0) else None,
+            "zero_ess_columns": int((tot <= 0).sum()), "seed": ESS_SEED, "cores": min(chains, cores),
+            "definition": "min over monitored columns of (sum over chains of coda-style effectiveSize of the post-burn-in "
+                          "samples) / wall seconds of the whole run incl. burn-in (MCMC_autoBlock.R:297-306)"}
 
 
 def _emit(line):
@@ -153,6 +186,101 @@ _REAL_STDOUT = os.dup(1)
 os.dup2(2, 1)
 
 
+def reference_arm(a):
+    model, conf, _ = build_model(a)
+    cb, dt, chains = cpu_baseline(a, conf, model, max(1, a.steps), warm=max(1, min(a.warmup, 3)))
+    ess = None
+    if a.ess_niter > 0 and a.gpus == 1:
+        ess = cpu_min_ess(a, conf, model)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": dt / max(1, a.steps) * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(a, {"chains": chains, "note": "reference's compiled NIMBLE cannot be built "
+                                          "here (no R / Rmath); this is its CPU restatement (oracle/), one chain per core"}),
+            "cpu_baseline": cb,
+            "min_ess_per_sec": ess["min_ess_per_sec"] if ess else None,
+            "min_ess": ess if ess else ("not run for --gpus > 1 (the CPU arm does not depend on the GPU count): see the --gpus 1 line"
+                                        if a.ess_niter > 0 else "skipped (--ess-niter 0)"),
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    _emit(line)
+    return 0
+
+
+def gpu_min_ess(a, nb, conf, backend, local, first_chain, inits, C, world, dist, torch):
+    """The SURVEY 8d protocol on this rank's chains: niter, nburnin = niter / 2, every chain; min-ESS/s by the reference's
+    definition of MCMC efficiency (MCMC_autoBlock.R:297-306).  ESS sums over all chains of all ranks, time is the slowest
+    rank's wall clock around the run (burn-in included, sample read-back excluded, as the reference times mcmc$run)."""
+    from nimble_b200.ess import min_ess
+    cm3 = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=local, first_chain=first_chain)
+    d3 = cm3._ensure(C)
+    d3.set_values(inits)
+    nb_it = a.ess_niter // 2
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    d3.run(a.ess_niter, nb_it, 1, True, ESS_SEED)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    ms_dev, _ = d3.last_timing()
+    sf = d3.samples()
+    d3.close()
+    nes = min(a.ess_chains or C, C)
+    t1 = time.perf_counter()
+    _, tot = min_ess(sf[:nes])
+    t_ess = time.perf_counter() - t1
+    tot = tot * (C / nes)
+    tt = torch.tensor(np.concatenate([tot, [0.0]]), dtype=torch.float64, device="cuda")
+    tw = torch.tensor([wall, ms_dev * 1e-3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+    tot = tt.cpu().numpy()[:-1]
+    wall, dev_s = (float(x) for x in tw.cpu().numpy())
+    nz = tot[tot > 0]
+    mess = float(nz.min()) if nz.size else 0.0
+    pooled = sf.reshape(-1, sf.shape[-1])
+    return {"min_ess_per_sec": mess / wall, "min_ess_total": mess, "chains": C * world, "niter": a.ess_niter, "nburnin": nb_it,
+            "seconds": wall, "device_seconds": dev_s, "ess_estimated_on_chains_per_rank": nes, "ess_host_seconds": t_ess,
+            "worst_column": cm3.colnames[int(np.argmin(np.where(tot > 0, tot, np.inf)))] if nz.size else None,
+            "zero_ess_columns": int((tot <= 0).sum()), "seed": ESS_SEED,
+            "posterior_mean_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.mean(0)[:4]])),
+            "posterior_sd_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.std(0)[:4]])),
+            "definition": "min over monitored columns of (sum over chains of coda-style effectiveSize of the post-burn-in "
+                          "samples) / wall seconds of the whole run incl. burn-in (MCMC_autoBlock.R:297-306)"}
+
+
+def strong_scaling_block(a, nb, conf, model, backend, local, rank, world, dist, torch, barrier, total_chains=1024):
+    """BASELINE.json configs[1] as north_star states it for the 8-GPU box: 1024 chains IN TOTAL, chain-sharded (1024 / N per
+    GPU, no collective).  Same K timed steps after W warm-up steps, device-timed, max over ranks."""
+    from nimble_b200 import configs
+    from nimble_b200.parallel import chain_range
+    lo, hi = chain_range(total_chains, rank, world)
+    Cs = hi - lo
+    inits_all = configs.logistic_inits(a.p, total_chains)
+    inits = np.stack([model.init_vector(i) for i in inits_all[lo:hi]])
+    cm = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=local, first_chain=lo)
+    evals_iter = configs.evals_per_iteration(cm)
+    dm = cm._ensure(Cs)
+    dm.set_values(inits)
+    dm.run(a.warmup, 0, 1, True, 2024)
+    barrier()
+    dm.run(a.steps, 0, 1, False, 2024)
+    barrier()
+    ms, launches = dm.last_timing()
+    ydecl = len(cm.builder.decls) - 1
+    k_ms = dm.time_calculate(ydecl, 10)
+    dm.close()
+    t = torch.tensor([ms, k_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, k_ms = (float(x) for x in t.cpu().numpy())
+    return {"what": "strong scaling: %d chains in total, %d per GPU, chain-sharded, no collective" % (total_chains, Cs),
+            "chains_total": total_chains, "chains_per_gpu": Cs, "ms_per_step": ms / a.steps,
+            "value": evals_iter * total_chains * a.steps / (ms * 1e-3), "unit": UNIT,
+            "fused_kernel_ms": k_ms, "non_kernel_ms_per_step": ms / a.steps - k_ms, "launches": int(launches)}
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -160,22 +288,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
 
     if a.impl == "reference":
-        if rank != 0:
-            return 0
-        model, conf, _ = build_model(a)
-        a.cpu_iters = max(1, a.steps)
-        cb, samples, dt, chains = cpu_baseline(a, conf, model, a.steps, warm=max(1, min(a.warmup, 3)))
-        from nimble_b200.ess import min_ess
-        mess = min_ess(samples[:, -a.steps:, :])[0] if a.steps >= 20 else None
-        line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
-                "warmup": a.warmup, "ms_per_step": dt / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": workload_config(a, {"chains": chains, "note": "reference's compiled NIMBLE cannot be built "
-                                              "here (no R / Rmath); this is its CPU restatement (oracle/), one chain per core"}),
-                "cpu_baseline": cb, "min_ess_per_sec": (mess / dt if mess is not None else None),
-                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        _emit(line)
-        return 0
+        return reference_arm(a) if rank == 0 else 0
 
     import torch
     import torch.distributed as dist
@@ -185,7 +298,6 @@ def main():
     torch.cuda.set_device(local)
     import nimble_b200 as nb
     from nimble_b200 import _capi, configs
-    from nimble_b200.ess import min_ess
 
     backend = _capi.default_backend()
     model, conf, t_build = build_model(a)
@@ -217,7 +329,6 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
-    samples = dm.samples()[:, -a.steps:, :]
     value = evals_iter * C * world * a.steps / (ms_max * 1e-3)
 
     # ---- end to end through the public API with host buffers: compile (lowering) once, then ONE runMCMC call that
@@ -225,8 +336,8 @@ def main():
     cm2 = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=local, first_chain=first_chain)
     barrier()
     t0 = time.perf_counter()
-    out = nb.runMCMC(cm2, niter=a.warmup + a.steps, nburnin=a.warmup, nchains=C, inits=inits_all[first_chain:first_chain + C],
-                     setSeed=2024)
+    nb.runMCMC(cm2, niter=a.warmup + a.steps, nburnin=a.warmup, nchains=C, inits=inits_all[first_chain:first_chain + C],
+               setSeed=2024)
     torch.cuda.synchronize()
     t_e2e = time.perf_counter() - t0
     te = torch.tensor([t_e2e], dtype=torch.float64, device="cuda")
@@ -240,11 +351,25 @@ def main():
     e2e_val = evals_iter * C * world * nsteps_e2e / t_e2e
     cm2.dm.close()
 
-    line = None
+    # ---- roofline inputs of the dominant kernel (measured on every rank's own device; rank 0's are reported)
+    ydecl = len(cm.builder.decls) - 1
+    k_ms = dm.time_calculate(ydecl, 10)
+
+    # ---- min-ESS/s, the first half of BASELINE.json's metric (every rank runs the protocol on its own chains)
+    ess = gpu_min_ess(a, nb, conf, backend, local, first_chain, inits, C, world, dist, torch) if a.ess_niter > 0 else None
+
+    # ---- N > 1: the north-star's own multi-GPU configurations next to the weak-scaling headline
+    strong = sharded = None
+    if world > 1:
+        dm.close()
+        strong = strong_scaling_block(a, nb, conf, model, backend, local, rank, world, dist, torch, barrier)
+        try:
+            from bench_sharded import data_sharded_block
+            sharded = data_sharded_block(a, nb, backend, local, rank, world, dist, torch, barrier)
+        except Exception as ex:  # the headline line must not depend on it
+            sharded = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
+
     if rank == 0:
-        # ---- roofline of the dominant kernel (fused dbern-logit-inprod block sum), timed alone
-        ydecl = len(cm.builder.decls) - 1
-        k_ms = dm.time_calculate(ydecl, 10)
         dfma, dmma = backend.fp64_peaks(local)
         mixed = backend.fp64_mixed_peak(local)
         peaks = {}
@@ -255,22 +380,23 @@ def main():
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_bytes = 8.0 * a.n * a.p + 8.0 * a.n + 8.0 * a.p * C
         contraction_flops = 2.0 * a.n * a.p * C
-        # FP64 work of the link + Bernoulli density per evaluation as the kernel implements it (DESIGN.md section 3,
-        # ncu profiles/r1f_summary.md): 24.8 FP64-pipe instructions on the reciprocal-free path every realistic linear
-        # predictor takes (table-driven exp 11, 1 + e, table-driven log 10, glue 2.8; 35.5 on the general path);
-        # one instruction = one multiplier slot = 2 flop in the units of the FMA peak.  Implementation-counted,
-        # reported next to the strict figure.
+        # FP64 work of the link + Bernoulli density per evaluation as the kernel implements it: 24.8
+        # FP64-pipe instructions on the reciprocal-free path every realistic linear predictor takes (ncu-counted); one
+        # instruction = one multiplier slot = 2 flop in the units of the FMA peak.  Reported next to the strict figure.
         epi_flops = 2.0 * 24.8 * a.n * C
         ach = contraction_flops / (k_ms * 1e-3) / 1e12
+        quoted = (a.n, a.p, C) == (1_000_000, 50, 1024)
         roof = {"bound": "tensor", "kernel": "k_fused_bern_logit", "achieved": ach, "peak": dmma, "unit": "TFLOP/s",
                 "frac": ach / dmma if dmma else None,
                 "peak_source": "FP64 mma.sync loop measured live (nimb200_measure_fp64_peaks); MEASURED_PEAKS.json has no FP64 "
                                "figure. DFMA loop: %.1f TFLOP/s; DMMA+DFMA issued together: %.1f TFLOP/s (the two share the FP64 "
                                "multipliers)" % (dfma, mixed),
                 "what": "strict algorithmic flops only: the 2*N*p*C contraction",
-                # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this kernel at the
-                # default workload (profiles/r1f_summary.md); not measurable live, so only quoted for that workload
-                "traffic": 429.9e6 if (a.n, a.p, C) == (1_000_000, 50, 1024) else None, "traffic_source": "profiles/r1f_summary.md",
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch cannot be measured inside this run: the figure is QUOTED
+                # from the committed ncu --set full capture of this kernel at this workload, null for any other workload
+                "traffic": 429.9e6 if quoted else None,
+                "traffic_kind": "quoted from the ncu capture in profiles/ (not measured by this run)" if quoted else None,
+                "traffic_source": "profiles/r1f_summary.md" if quoted else None,
                 "algorithmic_bytes": alg_bytes, "kernel_ms": k_ms, "evals_per_s_kernel": a.n * C / (k_ms * 1e-3),
                 "fp64_units": {"achieved": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12, "peak": mixed, "unit": "TFLOP/s",
                                "frac": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12 / mixed if mixed else None,
@@ -280,63 +406,14 @@ def main():
                         "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
                 "kernel_share_of_step": k_ms / (ms_max / a.steps)}
-        mess, per_col = min_ess(samples)
         cb = None
         if world == 1 and not a.no_cpu_baseline:
-            cb, _, _, _ = cpu_baseline(a, conf, model, a.cpu_iters)
-        full = None
-        if a.full:
-            # SURVEY 8d protocol: niter 5000, nburnin 2500, all chains; ESS (coda estimator) on a subset of chains, scaled
-            cm3 = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=local, first_chain=first_chain)
-            d3 = cm3._ensure(C)
-            d3.set_values(inits)
-            nb_it = a.full_niter // 2
-            tfull0 = time.perf_counter()
-            d3.run(a.full_niter, nb_it, 1, True, 777)
-            torch.cuda.synchronize()
-            wall = time.perf_counter() - tfull0
-            ms_full, _ = d3.last_timing()
-            sf = d3.samples()
-            nes = min(a.ess_chains, C)
-            mess_f, tot_f = min_ess(sf[:nes])
-            scale_c = C / nes
-            pooled = sf.reshape(-1, sf.shape[-1])
-            cpu_it_per_s = None
-            if cb is not None:
-                cpu_it_per_s = 1e3 / cb["ms_per_iteration_per_chain"] * cb["cores"]   # chain-iterations per second, all cores
-            ess_per_chain_iter = mess_f / nes / a.full_niter
-            full = {"niter": a.full_niter, "nburnin": nb_it, "chains": C, "device_seconds": ms_full * 1e-3, "wall_seconds": wall,
-                    "min_ess_total": mess_f * scale_c, "min_ess_per_sec": mess_f * scale_c / wall * world,
-                    "ess_estimated_on_chains": nes,
-                    "cpu_min_ess_per_sec_scaled": (ess_per_chain_iter * cpu_it_per_s if cpu_it_per_s else None),
-                    "cpu_scaling_note": "CPU figure = (min ESS per chain-iteration measured on the GPU chains; same algorithm and "
-                                        "draws) x (CPU chain-iterations/s of cpu_baseline, all cores): chains are independent",
-                    "posterior_mean_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.mean(0)[:4]])),
-                    "posterior_sd_first_cols": dict(zip(cm3.colnames[:4], [float(x) for x in pooled.std(0)[:4]]))}
-            d3.close()
+            cb, _, _ = cpu_baseline(a, conf, model, a.cpu_iters)
         secondary = None
         if world == 1 and not a.no_secondary:
-            # the one HBM-bound logProb kernel of the path, measured live on its own configuration (configs[2]: LMM, N = 1e7,
-            # 8 chains): block sum of the data declaration = streaming kernel + reduce/finish launch, CUDA events, min of 3 x 50
-            try:
-                m3, conf3 = configs.lmm()
-                cm_l = nb.compileNimble(nb.buildMCMC(conf3), backend=backend, device=local)
-                dl = cm_l._ensure(8)
-                dl.set_values(np.tile(m3.init_vector(), (8, 1)))
-                yd = len(cm_l.builder.decls) - 1
-                nn = cm_l.builder.decls[yd].n
-                ms_l = min(dl.time_calculate(yd, 50) for _ in range(3))
-                bytes_l = 12.0 * nn
-                secondary = [{"kernel": "k_norm_stream_tma + k_norm_reduce_finish", "bound": "hbm",
-                              "workload": "configs[2]: y[i] ~ dnorm(mu + u[grp[i]], sd) block sum, N = %d, 8 chains" % nn,
-                              "achieved": bytes_l / (ms_l * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                              "frac": bytes_l / (ms_l * 1e-3) / 1e9 / hbm_peak, "us_per_block_sum": ms_l * 1e3,
-                              "algorithmic_bytes": bytes_l,
-                              "note": "both launches of one block sum are inside the timed region; the streaming kernel alone is "
-                                      "23.9-26.3 us under ncu (profiles/r1e_summary.md), 0.70-0.77 of the measured peak"}]
-                dl.close()
-            except Exception as ex:  # the headline line must not depend on it
-                secondary = [{"error": str(ex)[:200]}]
+            dm.close()
+            from bench_secondary import secondary_rooflines
+            secondary = secondary_rooflines(nb, backend, local, hbm_peak, dfma)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": workload_config(a, {"chains_total": C * world}),
@@ -345,10 +422,9 @@ def main():
                         "seconds": t_e2e, "steps": nsteps_e2e,
                         "what": "one runMCMC() call on host buffers: table upload + inits + iterations + mvSamples read-back"},
                 "roofline": roof, "cpu_baseline": cb,
-                "min_ess_per_sec": mess * world / (ms_max * 1e-3),
-                "min_ess_note": "sum over chains of coda-style ESS of the timed iterations' samples (adaptation still running); rank 0's chains x n_gpus",
-                "evals_per_iteration_per_chain": evals_iter, "host_lowering_seconds": t_build, "full_protocol": full,
-                "secondary_rooflines": secondary}
+                "min_ess_per_sec": ess["min_ess_per_sec"] if ess else None, "min_ess": ess,
+                "evals_per_iteration_per_chain": evals_iter, "host_lowering_seconds": t_build,
+                "secondary_rooflines": secondary, "strong_scaling": strong, "data_sharded": sharded}
         _emit(line)
     if world > 1:
         dist.barrier()

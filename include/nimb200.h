@@ -169,8 +169,11 @@ enum {
   NIMB_SAMPLER_CONJ_GAMMA = 4, /* dgamma prior; dpois / dgamma(rate) / dnorm(tau) dependents, MCMC_conjugacy.R:80-93 */
   NIMB_SAMPLER_CONJ_NORMAL = 5, /* dnorm prior; dnorm(mean) dependents, MCMC_conjugacy.R:109-115 */
   NIMB_SAMPLER_CONJ_BETA = 6,   /* dbeta prior; dbern / dbin(prob) dependents, identity link, MCMC_conjugacy.R:4-15 */
-  NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7, /* MCMC_samplers.R:86-105 for a terminal node: simulate the target from its own
-                                            distribution (dnorm, dgamma, dbeta, dexp, dlogis, dbin, dpois with mean <= 500) and recalculate it */
+  NIMB_SAMPLER_POSTERIOR_PREDICTIVE = 7, /* MCMC_samplers.R:86-105: simulate the target from its own distribution (dnorm, dgamma,
+                                            dbeta, dexp, dlogis, dbin, dpois with mean <= 500).  The reference's sampler simulates the
+                                            whole predictive network downstream of its target in topological order; the host emits one
+                                            table sampler per member declaration, parents first, so a sequence of these is that
+                                            sampler.  Stage-1 entries name the dependents whose cached block sums the draw invalidates */
   NIMB_SAMPLER_CATEGORICAL = 9, /* MCMC_samplers.R:162-226: dcat target with K <= NIMB200_MAX_CATEGORIES categories: the conditional
                                    log-density of every category, then rcat (dists.cpp:936-961) on exp(logProb - max) */
   NIMB_SAMPLER_SLICE = 8 /* MCMC_samplers.R:864-972: stepping-out / shrinkage slice sampler with width adaptation; discrete

@@ -356,7 +356,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
   double* bp = buf + ((size_t)t * 3) * T.C + c;
   if (PHASE == 2) { v0 = bp[0]; v1 = bp[(size_t)T.C]; v2 = bp[2 * (size_t)T.C]; }
 
-  if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {  // MCMC_samplers.R:97-101 for a terminal node: simulate the target, nothing to decide
+  if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {  // MCMC_samplers.R:97-101: simulate the target, nothing to decide (its network follows as further table samplers)
     if (PHASE == 1 || lane != 0) return;
     const nimb200_dep tp = T.deps[sp.dep_off];
     const int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
@@ -1439,7 +1439,9 @@ static int validate_table(const nimb200_table* t) {
       const nimb200_decl& pd = t->decl[t->deps[sp.dep_off].decl];
       const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP ||
                       pd.dist == NIMB_DLOGIS || pd.dist == NIMB_DBINOM || pd.dist == NIMB_DPOIS;
-      if (!ok || sp.n_dep != 1) return fail("posterior_predictive: unsupported target distribution, or the target has dependents");
+      // dependents (the rest of the predictive network) are allowed: they are simulated by the table samplers that follow this
+      // one, and listing them here is what invalidates their cached block sums
+      if (!ok) return fail("posterior_predictive: no device variate generator for the target's distribution");
     }
     if (sp.adaptive && sp.adapt_interval < 1) return fail("adaptInterval must be >= 1");
     if (sp.tries < 1 && sp.type == NIMB_SAMPLER_RW_BLOCK) return fail("tries must be >= 1");
@@ -1711,7 +1713,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     } else if (sp.type == NIMB_SAMPLER_SLICE) {
       TRY(dev_alloc(m, &S.propCov, (size_t)TT * C));  // sumJumps
       if (dep_count_t0(m, sp) > 2048) { nimb200_model_free(m); return fail("slice sampler over more than 2048 dependents per target is not supported"); }
-    } else if (sp.n_targets == 1 && sp.type != NIMB_SAMPLER_BINARY && dep_count_t0(m, sp) > 2048) {
+    } else if (sp.n_targets == 1 && sp.type != NIMB_SAMPLER_BINARY && sp.type != NIMB_SAMPLER_POSTERIOR_PREDICTIVE &&
+               dep_count_t0(m, sp) > 2048) {
       m->wide[s] = 1;
     }
   }

@@ -49,15 +49,56 @@ def effective_size(x):
     return float(n * v / spec)
 
 
+def effective_size_batch(x):
+    """coda::effectiveSize of many series at once: x[series][n] -> ess[series].  Same estimator as effective_size() (AR order
+    by AIC over Yule-Walker fits from a Levinson-Durbin recursion), with the recursion carried over all series together."""
+    x = np.asarray(x, dtype=np.float64)
+    S, n = x.shape
+    if n < 4:
+        return np.zeros(S)
+    order_max = int(min(n - 1, np.floor(10 * np.log10(n))))
+    xc = x - x.mean(1, keepdims=True)
+    v = (xc * xc).sum(1) / (n - 1)
+    r = np.empty((order_max + 1, S))
+    for k in range(order_max + 1):
+        r[k] = np.einsum("sn,sn->s", xc[:, : n - k], xc[:, k:]) / n
+    ok = r[0] > 0
+    r0 = np.where(ok, r[0], 1.0)
+    vars_ = np.empty((order_max + 1, S))
+    coefs = np.zeros((order_max + 1, order_max + 1, S))
+    vars_[0] = r0
+    for k in range(1, order_max + 1):
+        acc = r[k].copy()
+        for j in range(1, k):
+            acc -= coefs[k - 1, j] * r[k - j]
+        phi = acc / vars_[k - 1]
+        coefs[k, k] = phi
+        for j in range(1, k):
+            coefs[k, j] = coefs[k - 1, j] - phi * coefs[k - 1, k - j]
+        vars_[k] = vars_[k - 1] * (1 - phi * phi)
+    aic = n * np.log(np.maximum(vars_, 1e-300)) + 2 * np.arange(order_max + 1)[:, None] + 2
+    order = np.argmin(aic, axis=0)
+    sidx = np.arange(S)
+    var_pred = vars_[order, sidx] * n / (n - (order + 1))
+    arsum = np.zeros(S)
+    for j in range(1, order_max + 1):
+        arsum += np.where(j <= order, coefs[order, j, sidx], 0.0)
+    spec = var_pred / (1 - arsum) ** 2
+    good = ok & (v > 0) & (spec > 0) & np.isfinite(spec)
+    return np.where(good, n * v / np.where(good, spec, 1.0), 0.0)
+
+
 def min_ess(samples):
     """samples: [nchains][nrows][ncols] -> (min over columns of the sum over chains of ESS, per-column sums).
     Columns with zero ESS are dropped, as in MCMC_autoBlock.R:303-306."""
     samples = np.asarray(samples)
     C, n, k = samples.shape
     tot = np.zeros(k)
-    for c in range(C):
-        for j in range(k):
-            tot[j] += effective_size(samples[c, :, j])
+    step = max(1, (1 << 24) // max(1, n * k))        # chains per batch: ~128 MB of doubles at a time
+    for c0 in range(0, C, step):
+        blk = samples[c0:c0 + step]
+        e = effective_size_batch(np.ascontiguousarray(blk.transpose(0, 2, 1)).reshape(-1, n))
+        tot += e.reshape(blk.shape[0], k).sum(0)
     nz = tot[tot > 0]
     return (float(nz.min()) if nz.size else 0.0), tot
 

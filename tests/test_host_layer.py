@@ -160,3 +160,22 @@ def test_initialize_model_warnings(oracle):
     cm = nb.compileNimble(nb.buildMCMC(nb.configureMCMC(m)), backend=oracle)
     with pytest.warns(RuntimeWarning, match="logProb is"):
         nb.runMCMC(cm, niter=5, setSeed=1)
+
+
+def test_batched_ess_equals_the_scalar_estimator():
+    # coda::effectiveSize restated twice (nimble_b200/ess.py): the batched form used by bench.py must give the scalar one's values
+    from nimble_b200.ess import effective_size, effective_size_batch, min_ess
+    rng = np.random.default_rng(0)
+    phi = np.array([0.0, 0.5, 0.9, 0.99, -0.5, 0.0, 0.7])
+    x = np.zeros((7, 1200))
+    e = rng.normal(size=x.shape)
+    for t in range(1, x.shape[1]):
+        x[:, t] = phi * x[:, t - 1] + e[:, t]
+    x[5] = 3.0                                        # a constant column has zero ESS and is dropped from the minimum
+    want = np.array([effective_size(r) for r in x])
+    got = effective_size_batch(x)
+    assert np.allclose(got, want, rtol=1e-9) and got[5] == 0.0
+    assert 1100 < want[0] < 1300 and want[3] < 40      # white noise ~ n, phi = 0.99 ~ n / 199
+    s = np.stack([x.T, x.T[::-1]])                     # [2 chains][rows][7 cols]
+    m, tot = min_ess(s)
+    assert abs(m - min(t for t in tot if t > 0)) < 1e-9 and tot[5] == 0.0
