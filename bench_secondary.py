@@ -32,7 +32,12 @@ def secondary_rooflines(nb, backend, local, hbm_peak, dfma_tflops):
         cm = nb.compileNimble(nb.buildMCMC(conf5), backend=backend, device=local)
         C = 8192
         dg = cm._ensure(C)
-        dg.set_values(np.tile(m5.init_vector(), (C, 1)))
+        init5 = np.tile(m5.init_vector(), (C, 1))
+        rng = np.random.default_rng(5)
+        init5[:, m5.var_slot["b0"]] = 0.5 + 0.1 * rng.standard_normal(C)
+        init5[:, m5.var_slot["b1"]] = 0.3 + 0.05 * rng.standard_normal(C)
+        init5[:, m5.var_slot["lam"]:m5.var_slot["lam"] + 10_000] = rng.gamma(2.0, 0.5, (C, 10_000))
+        dg.set_values(init5)
         yd = len(cm.builder.decls) - 1
         nn = cm.builder.decls[yd].n
         ms = _time(dg, yd, 5)
@@ -51,7 +56,11 @@ def secondary_rooflines(nb, backend, local, hbm_peak, dfma_tflops):
         cm = nb.compileNimble(nb.buildMCMC(conf4), backend=backend, device=local)
         C = 64
         do = cm._ensure(C)
-        do.set_values(np.tile(m4.init_vector(), (C, 1)))
+        init4 = np.tile(m4.init_vector(), (C, 1))
+        rng = np.random.default_rng(4)
+        for k, v in (("b0", 0.3), ("b1", 1.0), ("a0", -0.5), ("a1", 0.7)):   # chains spread around the generator's values
+            init4[:, m4.var_slot[k]] = v + 0.1 * rng.standard_normal(C)
+        do.set_values(init4)
         yd = [cm.lowering.decl_ids[d.index] for d in m4.decls if d.var == "y"][0]
         nn = cm.builder.decls[yd].n
         ms = _time(do, yd, 20)

@@ -282,6 +282,29 @@ int nimb200_sampler_state(nimb200_model *m, int32_t sampler, int32_t what, doubl
 int nimb200_nccl_unique_id(void *id128);
 int nimb200_enable_data_sharding(nimb200_model *m, int32_t nranks, int32_t rank, const void *id128, int32_t min_nodes);
 
+/* The same data-node sharding with the all-reduce done by a kernel of this library over NVLink peer memory instead of
+ * NCCL (no reference counterpart either: MCMC_run.R:127-153 is one sequential process).  The per-proposal message is
+ * `chains` doubles, so what matters is latency: every rank pushes its partial sums into every rank's exchange buffer with
+ * plain stores, publishes an epoch flag, waits for its peers' flags in its own memory and adds the contributions in rank
+ * order (identical bits, hence identical decisions, on all ranks).  Being ordinary kernels, these all-reduces are captured
+ * into the iteration's CUDA graph with everything else.  Protocol, 2 to 8 ranks of ONE node, one model per rank (separate
+ * processes, or several devices of one process):
+ *   1. every rank: nimb200_peer_export(m, nranks, handle) -- allocates and clears this rank's exchange buffer and writes an
+ *      opaque NIMB200_PEER_HANDLE_BYTES-byte handle;
+ *   2. the host gathers all handles to all ranks, in rank order (any all-gather; it doubles as the barrier that guarantees
+ *      every buffer is cleared before any peer writes to it);
+ *   3. every rank: nimb200_enable_data_sharding_peer(m, nranks, rank, handles[nranks][128], min_nodes).
+ * A rank whose peers do not arrive within a few seconds gives up (the run then returns an error) instead of spinning. */
+#define NIMB200_PEER_HANDLE_BYTES 128
+int nimb200_peer_export(nimb200_model *m, int32_t nranks, void *handle128);
+int nimb200_enable_data_sharding_peer(nimb200_model *m, int32_t nranks, int32_t rank, const void *handles, int32_t min_nodes);
+/* all-reduces enqueued by the last nimb200_mcmc_run (either transport), and whether its iterations were replayed from a
+ * captured CUDA graph; measurement only. */
+int nimb200_mcmc_last_allreduces(nimb200_model *m, int64_t *count_out, int32_t *graph_replayed_out);
+/* average device milliseconds of one all-reduce of `count` doubles through the data-sharded model's transport (every rank of
+ * the group makes the same call); measurement only. */
+int nimb200_time_allreduce(nimb200_model *m, int32_t count, int32_t reps, double *ms_avg);
+
 /* measurement hooks for bench.py (no counterpart in the reference, whose only profiling hook is
  * run(time=TRUE), MCMC_build.R:281-285): average device milliseconds of one launch of the block-sum kernel
  * behind nimb200_calculate(decl, whole range), and live FP64 peaks (DFMA loop, FP64 mma.sync loop). */

@@ -70,6 +70,10 @@ class Backend:
             self._mixed = fn("measure_fp64_mixed", [C.c_int, _dp])
             self._nccl_id = fn("nccl_unique_id", [C.c_void_p])
             self._shard = fn("enable_data_sharding", [vp, C.c_int32, C.c_int32, C.c_void_p, C.c_int32])
+            self._peer_export = fn("peer_export", [vp, C.c_int32, C.c_void_p])
+            self._shard_peer = fn("enable_data_sharding_peer", [vp, C.c_int32, C.c_int32, C.c_void_p, C.c_int32])
+            self._allreduces = fn("mcmc_last_allreduces", [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int32)])
+            self._time_ar = fn("time_allreduce", [vp, C.c_int32, C.c_int32, _dp])
 
     def check(self, rc):
         if rc != 0:
@@ -208,6 +212,29 @@ class DeviceModel:
         """Split large data declarations across the ranks of a group; unique_id=None keeps block sums as partial sums."""
         buf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
         self.backend.check(self.backend._shard(self.h, nranks, rank, buf, min_nodes))
+
+    def peer_export(self, nranks):
+        """Allocate this rank's exchange buffer for the device-side all-reduce; returns the 128-byte handle to gather."""
+        buf = C.create_string_buffer(128)
+        self.backend.check(self.backend._peer_export(self.h, nranks, buf))
+        return buf.raw
+
+    def enable_data_sharding_peer(self, nranks, rank, handles, min_nodes=65536):
+        """handles: the nranks exported handles in rank order (this rank's own included)."""
+        blob = b"".join(handles)
+        assert len(blob) == 128 * nranks
+        buf = C.create_string_buffer(blob, len(blob))
+        self.backend.check(self.backend._shard_peer(self.h, nranks, rank, buf, min_nodes))
+
+    def last_allreduces(self):
+        n, g = C.c_int64(), C.c_int32()
+        self.backend.check(self.backend._allreduces(self.h, C.byref(n), C.byref(g)))
+        return n.value, bool(g.value)
+
+    def time_allreduce(self, count, reps=100):
+        ms = C.c_double()
+        self.backend.check(self.backend._time_ar(self.h, count, reps, C.byref(ms)))
+        return ms.value
 
     def time_calculate(self, decl, reps=5):
         ms = C.c_double()

@@ -328,6 +328,7 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 #include "fused_pois.cuh"
 #include "fused_norm.cuh"
 #include "fused_bern.cuh"
+#include "peer_xchg.cuh"
 
 // ------------------------------------------------------------------------------------------------ sweep kernels
 // One thread = one (target t, chain c): the complete scalar sampler step.  Chains are the fast index, so the
@@ -1057,6 +1058,12 @@ struct nimb200_model {
   std::vector<int32_t> shard_lo, shard_hi, sharded;
   int32_t *d_shard_lo = nullptr, *d_shard_hi = nullptr, *d_sharded = nullptr;
   void* nccl_comm = nullptr;
+  // peer exchange (nimb200_peer_export / nimb200_enable_data_sharding_peer): device-side all-reduce over NVLink peer memory
+  PeerXchg xchg{};
+  bool xchg_on = false;
+  void* xchg_local = nullptr;               // this rank's exchange allocation
+  void* xchg_mapped[XCHG_MAX_RANKS] = {nullptr};  // peers' allocations opened through CUDA IPC (to be closed)
+  int64_t allreduces = 0;                   // all-reduces enqueued by the last run
   double* d_sweepbuf = nullptr;  // [T][3][C] partial sums of a sharded sweep
   size_t sweepbuf_cap = 0;
   std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
@@ -1084,6 +1091,7 @@ struct nimb200_model {
 // evaluation.  NCCL is loaded at run time (the copy torch already mapped if there is one) so that the library has no
 // link-time dependency on it and single-GPU users never touch it.
 #include <dlfcn.h>
+#include <unistd.h>
 namespace {
 struct NcclId { char internal[128]; };
 typedef int (*fn_getid)(NcclId*);
@@ -1117,6 +1125,7 @@ int load_nccl() {
 }  // namespace
 
 static int allreduce_sum(nimb200_model* m, double* buf, size_t count);
+static inline bool comm_on(const nimb200_model* m) { return m->nccl_comm != nullptr || m->xchg_on; }
 
 // Programmatic dependent launch: the kernel may be scheduled while its predecessor on the stream still runs; it must call
 // cudaGridDependencySynchronize() before touching anything the predecessor writes (every kernel launched through here does so
@@ -1222,7 +1231,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   if (count <= 0 && !(norm_family && gcount > 0)) {
     CK(cudaMemsetAsync(dst0, 0, sizeof(double) * C, m->stream));
     if (dst1) CK(cudaMemsetAsync(dst1, 0, sizeof(double) * C, m->stream));
-    if (m->nranks > 1 && m->sharded[di] && m->nccl_comm) {
+    if (m->nranks > 1 && m->sharded[di] && comm_on(m)) {
       if (allreduce_sum(m, dst0, C)) return 1;
       if (dst1 && allreduce_sum(m, dst1, C)) return 1;
     }
@@ -1239,7 +1248,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, nt, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
-    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    if (shard && comm_on(m)) return allreduce_sum(m, dst0, C);
     return 0;
   }
   if (d.family == NIMB_FAM_NORM_GATHER && m->norm_ok[di] &&
@@ -1283,7 +1292,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     } else if (mode == 0) k_norm_stream<0><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, -1, m->d_partials);
     else k_norm_stream<1><<<grid, NF_THREADS, 0, m->stream>>>(m->T, na, lo, hi, npb, idx, slot, m->d_partials);
     m->launches++;
-    if (!(shard && m->nccl_comm)) {
+    if (!(shard && comm_on(m))) {
       {  // programmatic dependent launch: the finish kernel is scheduled while the streaming kernel still runs (fused_norm.cuh)
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((C * 32 + 127) / 128); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = 0; cfg.stream = m->stream;
@@ -1318,7 +1327,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
-    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    if (shard && comm_on(m)) return allreduce_sum(m, dst0, C);
     return 0;
   }
   if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && C >= 32) {
@@ -1332,7 +1341,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
     CK(cudaGetLastError());
-    if (shard && m->nccl_comm) return allreduce_sum(m, dst0, C);
+    if (shard && comm_on(m)) return allreduce_sum(m, dst0, C);
     return 0;
   }
   int nt = eval_tiles(C, count);
@@ -1352,7 +1361,7 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     m->launches++;
   }
   CK(cudaGetLastError());
-  if (shard && m->nccl_comm) {
+  if (shard && comm_on(m)) {
     if (allreduce_sum(m, dst0, C)) return 1;
     if (dst1 && allreduce_sum(m, dst1, C)) return 1;
   }
@@ -1360,6 +1369,16 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
 }
 
 static int allreduce_sum(nimb200_model* m, double* buf, size_t count) {
+  m->allreduces++;
+  if (m->xchg_on) {  // one small kernel per piece of at most XCHG_CAP doubles: push to the peers, wait, fixed-order sum
+    for (size_t off = 0; off < count; off += XCHG_CAP) {
+      const size_t n = std::min(XCHG_CAP, count - off);
+      k_peer_allreduce<<<xchg_blocks(n), XCHG_THREADS, 0, m->stream>>>(m->xchg, buf + off, (int)n);
+      m->launches++;
+    }
+    CK(cudaGetLastError());
+    return 0;
+  }
   int rc = g_nccl.allreduce(buf, buf, count, /*ncclDouble*/ 8, /*ncclSum*/ 0, m->nccl_comm, m->stream);
   if (rc != 0) return fail(std::string("ncclAllReduce failed: ") + (g_nccl.errstr ? g_nccl.errstr(rc) : "?"));
   m->launches++;
@@ -1461,6 +1480,9 @@ extern "C" int nimb200_model_free(nimb200_model* m) {
   for (void* p : m->allocs) cudaFree(p);
   if (m->d_samples) cudaFree(m->d_samples);
   if (m->nccl_comm && g_nccl.destroy) g_nccl.destroy(m->nccl_comm);
+  for (int r = 0; r < XCHG_MAX_RANKS; r++)
+    if (m->xchg_mapped[r]) cudaIpcCloseMemHandle(m->xchg_mapped[r]);
+  if (m->xchg_local) cudaFree(m->xchg_local);
   if (m->graph_exec) cudaGraphExecDestroy(m->graph_exec);
   if (m->ev0) cudaEventDestroy(m->ev0);
   if (m->ev1) cudaEventDestroy(m->ev1);
@@ -1961,7 +1983,7 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
   const nimb200_decl& d = m->decl[di];
   bool fused = d.family == NIMB_FAM_BERN_LOGIT_INPROD && m->d_xpad[di];
   int C = m->C, cwl = cw_log2_for(C), cw = 1 << cwl;
-  bool family = d.family == NIMB_FAM_NORM_GATHER || d.family == NIMB_FAM_POIS_LOGLIN;
+  bool family = d.family == NIMB_FAM_NORM_GATHER || d.family == NIMB_FAM_POIS_LOGLIN || d.family == NIMB_FAM_BERN_LOGIT_LIN;
   CK(cudaEventRecord(m->ev0, m->stream));
   for (int r = 0; r < reps; r++) {
     if (family) {  // streaming families: the whole block-sum evaluation (main kernel + the small reduce / finish kernels)
@@ -1974,6 +1996,28 @@ extern "C" int nimb200_time_calculate(nimb200_model* m, int32_t di, int32_t reps
       k_eval<0><<<grid, EVAL_THREADS, sizeof(double) * EVAL_THREADS, m->stream>>>(m->T, di, 0, d.n, nullptr, cwl, eval_npt(C, d.n), m->d_partials, nullptr, dd, -1, 0);
     }
   }
+  CK(cudaEventRecord(m->ev1, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  CK(cudaGetLastError());
+  float ms = 0;
+  CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
+  *ms_avg = ms / reps;
+  return 0;
+}
+
+// average device milliseconds of one all-reduce of `count` doubles on the model's run stream, through whichever transport the
+// data-sharded model was given (every rank of the group must make the same call)
+extern "C" int nimb200_time_allreduce(nimb200_model* m, int32_t count, int32_t reps, double* ms_avg) {
+  if (!m || !ms_avg || reps < 1 || count < 1) return fail("bad argument");
+  if (!comm_on(m)) return fail("the model has no all-reduce transport (not data-sharded)");
+  if ((size_t)count > (size_t)2 * m->C) return fail("count exceeds the scratch vector (2 x chains)");
+  CK(cudaSetDevice(m->device));
+  CK(cudaMemsetAsync(m->d_newsum, 0, sizeof(double) * count, m->stream));
+  if (allreduce_sum(m, m->d_newsum, count)) return 1;  // warm
+  CK(cudaStreamSynchronize(m->stream));
+  CK(cudaEventRecord(m->ev0, m->stream));
+  for (int r = 0; r < reps; r++)
+    if (allreduce_sum(m, m->d_newsum, count)) return 1;
   CK(cudaEventRecord(m->ev1, m->stream));
   CK(cudaStreamSynchronize(m->stream));
   CK(cudaGetLastError());
@@ -2006,7 +2050,7 @@ extern "C" int nimb200_nccl_unique_id(void* id128) {
 // first run.  Data declarations with at least min_nodes instances are split into contiguous, 128-aligned slices;
 // id128 == NULL keeps the slices but creates no communicator (block sums are then this rank's partial sums: used by
 // tests that add the parts up themselves).
-extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, int32_t rank, const void* id128, int32_t min_nodes) {
+static int set_shards(nimb200_model* m, int32_t nranks, int32_t rank, int32_t min_nodes) {
   if (!m) return fail("null model");
   if (nranks < 1 || rank < 0 || rank >= nranks) return fail("bad rank / nranks");
   CK(cudaSetDevice(m->device));
@@ -2040,6 +2084,14 @@ extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, in
     if (dev_alloc(m, &m->d_sweepbuf, need)) return 1;
     m->sweepbuf_cap = need;
   }
+  CK(cudaStreamSynchronize(m->stream));
+  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
+  return 0;
+}
+
+extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, int32_t rank, const void* id128, int32_t min_nodes) {
+  if (set_shards(m, nranks, rank, min_nodes)) return 1;
   if (nranks > 1 && id128) {
     if (load_nccl()) return fail("NCCL library (libnccl.so.2) could not be loaded");
     NcclId id;
@@ -2047,8 +2099,80 @@ extern "C" int nimb200_enable_data_sharding(nimb200_model* m, int32_t nranks, in
     int rc = g_nccl.init(&m->nccl_comm, nranks, id, rank);
     if (rc != 0) return fail(std::string("ncclCommInitRank failed: ") + (g_nccl.errstr ? g_nccl.errstr(rc) : "?"));
   }
-  CK(cudaStreamSynchronize(m->stream));
-  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  return 0;
+}
+
+// ---- peer exchange: the all-reduce of the data-sharded mode as a kernel of ours over NVLink peer memory (peer_xchg.cuh)
+namespace {
+struct PeerHandle {          // what nimb200_peer_export writes into the caller's 128 bytes
+  uint64_t magic;            // 'NIMBXCHG'
+  uint64_t pid;              // exporting process: inside one process peers use the raw pointer, across processes CUDA IPC
+  uint64_t ptr;              // device address in the exporting process
+  int32_t device, nranks;
+  cudaIpcMemHandle_t ipc;    // 64 bytes
+};
+static_assert(sizeof(PeerHandle) <= NIMB200_PEER_HANDLE_BYTES, "peer handle does not fit");
+constexpr uint64_t XCHG_MAGIC = 0x4e494d4258434847ull;
+}  // namespace
+
+extern "C" int nimb200_peer_export(nimb200_model* m, int32_t nranks, void* handle128) {
+  if (!m || !handle128) return fail("null argument");
+  if (nranks < 2 || nranks > XCHG_MAX_RANKS) return fail("peer exchange supports 2 to 8 ranks (one NVSwitch box)");
+  CK(cudaSetDevice(m->device));
+  if (m->xchg_on) return fail("peer exchange is already attached");
+  if (m->xchg_local) { cudaFree(m->xchg_local); m->xchg_local = nullptr; }
+  CK(cudaMalloc(&m->xchg_local, xchg_bytes(nranks)));
+  CK(cudaMemset(m->xchg_local, 0, xchg_bytes(nranks)));   // flags and sequence number start at zero on every rank ...
+  CK(cudaDeviceSynchronize());                            // ... before any peer can learn this address
+  PeerHandle h{};
+  h.magic = XCHG_MAGIC; h.pid = (uint64_t)getpid(); h.ptr = (uint64_t)(uintptr_t)m->xchg_local; h.device = m->device; h.nranks = nranks;
+  CK(cudaIpcGetMemHandle(&h.ipc, m->xchg_local));
+  memset(handle128, 0, NIMB200_PEER_HANDLE_BYTES);
+  memcpy(handle128, &h, sizeof h);
+  return 0;
+}
+
+extern "C" int nimb200_enable_data_sharding_peer(nimb200_model* m, int32_t nranks, int32_t rank, const void* handles,
+                                                 int32_t min_nodes) {
+  if (!m || !handles) return fail("null argument");
+  if (nranks < 2 || nranks > XCHG_MAX_RANKS) return fail("peer exchange supports 2 to 8 ranks (one NVSwitch box)");
+  if (rank < 0 || rank >= nranks) return fail("bad rank / nranks");
+  if (!m->xchg_local) return fail("call nimb200_peer_export on this model first");
+  if (m->nccl_comm) return fail("this model already all-reduces over NCCL");
+  if (set_shards(m, nranks, rank, min_nodes)) return 1;
+  const char* hb = (const char*)handles;
+  PeerXchg X{};
+  X.nranks = nranks; X.rank = rank;
+  for (int r = 0; r < nranks; r++) {
+    PeerHandle h;
+    memcpy(&h, hb + (size_t)r * NIMB200_PEER_HANDLE_BYTES, sizeof h);
+    if (h.magic != XCHG_MAGIC || h.nranks != nranks) return fail("peer handle " + std::to_string(r) + " is not a handle of this exchange");
+    void* base = nullptr;
+    if (r == rank) {
+      if ((void*)(uintptr_t)h.ptr != m->xchg_local) return fail("handle[rank] is not this model's own export");
+      base = m->xchg_local;
+    } else if (h.pid == (uint64_t)getpid()) {  // same process, another device: plain peer access
+      int can = 0;
+      CK(cudaDeviceCanAccessPeer(&can, m->device, h.device));
+      if (!can) return fail("device " + std::to_string(m->device) + " cannot access device " + std::to_string(h.device));
+      cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+      cudaGetLastError();
+      base = (void*)(uintptr_t)h.ptr;
+    } else {
+      cudaError_t e = cudaIpcOpenMemHandle(&base, h.ipc, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) return fail(std::string("cudaIpcOpenMemHandle (rank ") + std::to_string(r) + "): " + cudaGetErrorString(e));
+      m->xchg_mapped[r] = base;
+    }
+    X.data[r] = (double*)base;
+    X.flags[r] = (unsigned long long*)((char*)base + xchg_data_doubles(nranks) * sizeof(double));
+  }
+  unsigned long long* tail = X.flags[rank] + (size_t)2 * nranks * XCHG_MAX_BLOCKS;
+  X.seq = tail;
+  X.ticket = (unsigned int*)(tail + 1);
+  X.err = X.ticket + 1;
+  m->xchg = X;
+  m->xchg_on = true;
   return 0;
 }
 
@@ -2106,7 +2230,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     if (!m->norm_gs_valid[s]) {
       k_norm_group_sums<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_norm_gs[s]);
       m->launches++;
-      if (m->nranks > 1 && m->sweep_sharded[s] && m->nccl_comm && allreduce_sum(m, m->d_norm_gs[s], (size_t)sp.n_targets * 2)) return 1;
+      if (m->nranks > 1 && m->sweep_sharded[s] && comm_on(m) && allreduce_sum(m, m->d_norm_gs[s], (size_t)sp.n_targets * 2)) return 1;
       m->norm_gs_valid[s] = 1;
     }
     size_t total = (size_t)sp.n_targets * C;
@@ -2120,7 +2244,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[m->deps[sp.dep_off + 1].decl],
                                                                            m->d_pois_ysum[s]);
       m->launches++;
-      if (sh && m->nccl_comm && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets * 3)) return 1;
+      if (sh && comm_on(m) && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets * 3)) return 1;
       m->pois_ysum_valid[s] = 1;
     }
     const unsigned nb = (unsigned)((total + PF_THREADS - 1) / PF_THREADS);
@@ -2139,7 +2263,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       if (total > m->sweepbuf_cap) return fail("internal: sweep buffer too small (poisson)");
       k_pois_conj_sweep<1><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf, nullptr);
       m->launches++;
-      if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, total)) return 1;
+      if (comm_on(m) && allreduce_sum(m, m->d_sweepbuf, total)) return 1;
       k_pois_conj_sweep<2><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_sweepbuf, nullptr);
       m->launches++;
     }
@@ -2155,7 +2279,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       if (warp_per_pair) k_sweep<1, 32><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       else k_sweep<1, 1><<<nb, TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       m->launches++;
-      if (m->nccl_comm && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
+      if (comm_on(m) && allreduce_sum(m, m->d_sweepbuf, need)) return 1;
       k_sweep<2, 1><<<(unsigned)(((size_t)sp.n_targets * C + TB - 1) / TB), TB, 0, m->stream>>>(m->T, s, seed, iter, m->sdev[s], m->d_sweepbuf);
       m->launches++;
     } else {
@@ -2250,6 +2374,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     m->d_samples = ns; m->cap = ncap;
   }
   m->launches = 0;
+  m->allreduces = 0;
   {
     unsigned long long first = (unsigned long long)(m->iter_done + 1);
     CK(cudaMemcpyAsync(m->d_ctr, &first, sizeof first, cudaMemcpyHostToDevice, m->stream));
@@ -2261,7 +2386,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   const char* genv = getenv("NIMB200_GRAPH");
   const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8 && !m->time_samplers;
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
-  int64_t graph_launches = 0;
+  int64_t graph_launches = 0, graph_allreduces = 0;
   std::vector<char> valid_prev;
   auto adapt_due = [&]() {
     for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -2312,6 +2437,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     if (m->graph_exec && !due) {
       CK(cudaGraphLaunch(m->graph_exec, m->stream));
       m->launches += graph_launches;
+      m->allreduces += graph_allreduces;
       for (size_t s = 0; s < m->samplers.size(); s++)
         if (m->samplers[s].type == NIMB_SAMPLER_RW_BLOCK && m->samplers[s].adaptive) m->ran[s] += m->samplers[s].tries;
       continue;
@@ -2320,7 +2446,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     valid_prev = m->dep_valid;
     if (capture) {
       std::vector<int> ran_before = m->ran;
-      int64_t l0 = m->launches;
+      int64_t l0 = m->launches, a0 = m->allreduces;
       cudaGraph_t g = nullptr;
       bool ok = cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
       if (ok && one_iteration(git)) ok = false;
@@ -2329,10 +2455,13 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       if (ok && cudaGraphInstantiate(&m->graph_exec, g, 0) != cudaSuccess) { m->graph_exec = nullptr; ok = false; }
       if (g) cudaGraphDestroy(g);
       graph_launches = m->launches - l0;
+      graph_allreduces = m->allreduces - a0;
       m->launches = l0;
+      m->allreduces = a0;
       if (ok) {
         CK(cudaGraphLaunch(m->graph_exec, m->stream));  // capturing did not execute anything
         m->launches += graph_launches;
+        m->allreduces += graph_allreduces;
         continue;
       }
       cudaGetLastError();
@@ -2347,6 +2476,11 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   CK(cudaEventRecord(m->ev1, m->stream));
   CK(cudaStreamSynchronize(m->stream));
   CK(cudaGetLastError());
+  if (m->xchg_on) {
+    unsigned int bad = 0;
+    CK(cudaMemcpy(&bad, m->xchg.err, sizeof bad, cudaMemcpyDeviceToHost));
+    if (bad) return fail("peer all-reduce timed out: a rank of the data-sharded group did not arrive (results are NaN)");
+  }
   float ms = 0;
   CK(cudaEventElapsedTime(&ms, m->ev0, m->ev1));
   m->last_ms = ms; m->last_launches = m->launches;
@@ -2371,6 +2505,13 @@ extern "C" int nimb200_mcmc_samples(nimb200_model* m, double* out, int64_t* nrow
   if (e == cudaSuccess) e = cudaStreamSynchronize(m->stream);
   cudaFree(tmp);
   if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int nimb200_mcmc_last_allreduces(nimb200_model* m, int64_t* count_out, int32_t* graph_replayed_out) {
+  if (!m) return fail("null model");
+  if (count_out) *count_out = m->allreduces;
+  if (graph_replayed_out) *graph_replayed_out = m->graph_exec ? 1 : 0;
   return 0;
 }
 

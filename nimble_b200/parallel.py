@@ -4,8 +4,9 @@ chain sharding  rank r owns chains [r*K/R, (r+1)*K/R) and a full replica of the 
                 while sampling, mvSamples are gathered once at the end.  The draw stream is keyed by the GLOBAL chain
                 index, so the result is bit-identical to a single-process run of all K chains.
 data sharding   every rank holds all chains but only a contiguous slice of each large data declaration; each
-                per-proposal block sum (and each conjugate contribution vector) is all-reduced over NCCL inside the
-                device library (nimb200_enable_data_sharding), after which every rank takes the same decision.
+                per-proposal block sum (and each conjugate contribution vector) is all-reduced inside the device
+                library -- by its own kernel over NVLink peer memory (nimb200_enable_data_sharding_peer, the default) or
+                over NCCL (nimb200_enable_data_sharding) -- after which every rank takes the same decision.
 
 The reference has no counterpart: runMCMC loops over chains in one process (P/R/MCMC_run.R:127-153) and the manual
 recommends one separately compiled model per worker (UserManual/src/chapter_MCMC.Rmd:1223-1229)."""
@@ -26,6 +27,31 @@ def node_range(n, rank, world, align=128):
     lo = min(n, rank * per)
     hi = min(n, (rank + 1) * per)
     return lo, hi
+
+
+def attach_data_sharding(dm, nranks, shard, group_ranks=None, transport="peer", min_nodes=1 << 16, group=None):
+    """Turn `dm` (a DeviceModel every rank of the group created alike) into this rank's share of a data-sharded group.
+
+    transport "peer": the all-reduce is a kernel of the device library over NVLink peer memory (every rank exports its exchange
+    buffer, the handles are all-gathered -- which is also the barrier the protocol needs -- and attached); "nccl": one NCCL
+    communicator per group, all-reduces issued from the host.  group_ranks: the global ranks of this group in shard order
+    (default: the whole default group)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    group_ranks = list(range(world)) if group_ranks is None else list(group_ranks)
+    assert len(group_ranks) == nranks and group_ranks[shard] == rank
+    if transport == "peer":
+        mine = dm.peer_export(nranks)
+        allh = [None] * world
+        dist.all_gather_object(allh, mine, group=group)
+        dm.enable_data_sharding_peer(nranks, shard, [allh[r] for r in group_ranks], min_nodes=min_nodes)
+    elif transport == "nccl":
+        ids = [None] * world
+        dist.all_gather_object(ids, dm.backend.nccl_unique_id() if shard == 0 else None, group=group)
+        dm.enable_data_sharding(nranks, shard, ids[group_ranks[0]], min_nodes=min_nodes)
+    else:
+        raise ValueError("transport must be 'peer' or 'nccl'")
 
 
 def run_chain_sharded(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, seed=0, group=None):
@@ -66,10 +92,12 @@ def hybrid_layout(rank, world, data_shards):
     return rank // data_shards, rank % data_shards, world // data_shards
 
 
-def run_hybrid(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, seed=0, data_shards=1, min_nodes=1 << 16):
+def run_hybrid(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, seed=0, data_shards=1, min_nodes=1 << 16,
+               transport="peer"):
     """Chain groups x data shards (third row): the world is cut into world/data_shards chain groups; group g
     owns chains chain_range(nchains, g, groups) and its data_shards ranks each hold a slice of every large data declaration,
-    all-reducing block sums inside the group only (one NCCL communicator per group, created inside the device library).
+    all-reducing block sums inside the group only (transport "peer": the library's own all-reduce kernel over NVLink peer memory,
+    captured into the iteration's CUDA graph; "nccl": one NCCL communicator per group, host-issued).
     data_shards = 1 is plain chain sharding, data_shards = world plain data sharding.
 
     mcmc_factory(first_chain, device_index) as for run_chain_sharded.  Returns on rank 0 the samples of all chains in global
@@ -88,11 +116,10 @@ def run_hybrid(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, se
         these = inits[c] if isinstance(inits, (list, tuple)) else inits
         rows.append(cm.model.init_vector(these))
     if data_shards > 1:
-        # every group leader makes an id; all ids travel in one collective and each rank picks its group's
-        ids = [None] * world
-        dist.all_gather_object(ids, cm.backend.nccl_unique_id() if shard == 0 else None)
+        # one exchange (peer buffers, or a NCCL communicator) per chain group; the handles / ids of all groups travel in one
+        # collective and each rank picks its own group's
         dm = cm._ensure(hi - lo)
-        dm.enable_data_sharding(data_shards, shard, ids[g * data_shards], min_nodes=min_nodes)
+        attach_data_sharding(dm, data_shards, shard, [g * data_shards + k for k in range(data_shards)], transport, min_nodes)
     local = cm.run_chains(np.stack(rows), niter, nburnin, thin, True, seed)
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(local if shard == 0 else None, gathered, dst=0)

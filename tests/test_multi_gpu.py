@@ -1,4 +1,5 @@
-"""GPU, two ranks on two GPUs: data-node sharding with the NCCL all-reduce inside the library, and chain sharding.
+"""GPU, two ranks on two GPUs: data-node sharding with the all-reduce inside the library (its own kernel over NVLink peer memory,
+or NCCL), and chain sharding.
 Skipped unless the box has at least two GPUs (never run two ranks on one GPU: kernels that wait on one another)."""
 import os
 import sys
@@ -15,7 +16,7 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
-def _data_shard_worker(rank, world, port, name, out_dir):
+def _data_shard_worker(rank, world, port, name, out_dir, transport="nccl"):
     sys.path.insert(0, ROOT)
     import torch
     import torch.distributed as dist
@@ -30,13 +31,16 @@ def _data_shard_worker(rank, world, port, name, out_dir):
     inits = sm.random_inits(m, C, 21, 0.1)
     if name == "occupancy":
         inits[:, m.var_slot["z"]:m.var_slot["z"] + 300] = 1.0
-    ids = [backend.nccl_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(ids, src=0)
+    from nimble_b200 import parallel
     cm = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=rank)
     dm = cm._ensure(C)
-    dm.enable_data_sharding(world, rank, ids[0], min_nodes=256)
+    parallel.attach_data_sharding(dm, world, rank, transport=transport, min_nodes=256)
     s = cm.run_chains(inits, 260, 10, 1, True, 17)
     np.save(os.path.join(out_dir, "rank%d.npy" % rank), s)
+    n_ar, replayed = dm.last_allreduces()
+    assert n_ar > 0
+    if transport == "peer":
+        assert replayed, "the peer all-reduce is an ordinary kernel: the iteration must have been replayed from its CUDA graph"
     if rank == 0:
         ref = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=0)
         np.save(os.path.join(out_dir, "single.npy"), ref.run_chains(inits, 260, 10, 1, True, 17))
@@ -44,13 +48,14 @@ def _data_shard_worker(rank, world, port, name, out_dir):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
 @pytest.mark.parametrize("name", ["logistic", "lmm", "glmm", "occupancy"])
-def test_data_sharded_run_matches_single_gpu(tmp_path, name):
+def test_data_sharded_run_matches_single_gpu(tmp_path, name, transport):
     if _ngpu() < 2:
         pytest.skip("needs two GPUs")
     import torch.multiprocessing as mp
     port = 29600 + os.getpid() % 2000
-    mp.spawn(_data_shard_worker, args=(2, port, name, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_data_shard_worker, args=(2, port, name, str(tmp_path), transport), nprocs=2, join=True)
     r0, r1 = np.load(tmp_path / "rank0.npy"), np.load(tmp_path / "rank1.npy")
     single = np.load(tmp_path / "single.npy")
     assert np.array_equal(r0, r1)                    # every rank took identical decisions
@@ -100,4 +105,42 @@ def test_hybrid_chain_groups_times_data_shards(tmp_path, world, data_shards):
     h, single = np.load(tmp_path / "hybrid.npy"), np.load(tmp_path / "single.npy")
     assert h.shape == single.shape
     err = np.abs(h - single) / np.maximum(1.0, np.abs(single))
+    assert err.max() < 1e-9, err.max()
+
+
+def test_two_devices_in_one_process_share_the_exchange():
+    """Two models on two devices of ONE process (per-device kernel attributes, the same-process branch of the peer exchange):
+    each is driven from its own host thread, because a run blocks its caller until the device is done and the two ranks wait
+    for one another on the device."""
+    if _ngpu() < 2:
+        pytest.skip("needs two GPUs")
+    import threading
+    import nimble_b200 as nb
+    from nimble_b200 import _capi
+    from tests import small_models as sm
+    backend = _capi.default_backend()
+    m, conf = sm.SMALL["logistic"]()
+    C = 4
+    inits = sm.random_inits(m, C, 21, 0.1)
+    cms = [nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=d) for d in (0, 1)]
+    dms = [cm._ensure(C) for cm in cms]
+    handles = [dm.peer_export(2) for dm in dms]
+    for r, dm in enumerate(dms):
+        dm.enable_data_sharding_peer(2, r, handles, min_nodes=256)
+    out, errs = [None, None], []
+
+    def work(r):
+        try:
+            out[r] = cms[r].run_chains(inits, 120, 10, 1, True, 17)
+        except Exception as ex:  # noqa: BLE001
+            errs.append(ex)
+    ths = [threading.Thread(target=work, args=(r,)) for r in (0, 1)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    assert np.array_equal(out[0], out[1])
+    single = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=1).run_chains(inits, 120, 10, 1, True, 17)  # fused kernel on device 1
+    err = np.abs(out[0] - single) / np.maximum(1.0, np.abs(single))
     assert err.max() < 1e-9, err.max()
