@@ -82,20 +82,16 @@ __global__ void __launch_bounds__(XCHG_THREADS) k_peer_allreduce(PeerXchg X, dou
     double* dst = X.data[p] + ((size_t)par * R + X.rank) * XCHG_CAP;
     for (int i = lo + tid; i < hi; i += XCHG_THREADS) st_relaxed_sys(dst + i, buf[i]);
   }
-  __threadfence_system();
   __syncthreads();
-  // 2. one thread per destination rank publishes the epoch (release: ordered after the barrier-ordered data stores)
-  if (tid < R) {
-    __threadfence_system();
-    st_release_sys(X.flags[tid] + ((size_t)par * R + X.rank) * XCHG_MAX_BLOCKS + b, e);
-  }
+  // 2. one thread per destination rank publishes the epoch.  st.release at system scope is cumulative over everything that
+  // happens-before it, and the CTA barrier orders every thread's data stores before it: no per-thread fence is needed
+  if (tid < R) st_release_sys(X.flags[tid] + ((size_t)par * R + X.rank) * XCHG_MAX_BLOCKS + b, e);
   // 3. one thread per source rank waits for that rank's epoch in MY memory
   if (tid < R) {
     const unsigned long long* f = X.flags[X.rank] + ((size_t)par * R + tid) * XCHG_MAX_BLOCKS + b;
     const long long t0 = clock64();
     while (ld_acquire_sys(f) < e) {
       if (clock64() - t0 > XCHG_TIMEOUT_CYCLES) { s_bad = 1; break; }
-      __nanosleep(20);
     }
   }
   __syncthreads();
