@@ -1052,6 +1052,8 @@ struct nimb200_model {
   std::vector<char> pois_ysum_valid;
   std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
   std::vector<char> norm_gs_valid;   // is computed (and, data-sharded, all-reduced) once and kept until the shards change
+  std::vector<double*> d_norm_gss;   // per such sampler: [n_targets] centred sum of squares of every target's nodes (data only too)
+  std::vector<char> norm_gss_ok;     // ... all finite and every node of the dependent declaration covered: block sums may use it
   double* d_normtmp = nullptr;       // [2][C]
   // data-node sharding (nimb200_enable_data_sharding)
   int rank = 0, nranks = 1;
@@ -1255,13 +1257,28 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
       (mode == 0 || (mode == 2 && dp && dp->param == 0 && (dp->link == NIMB_LINK_ADDITIVE || dp->link == NIMB_LINK_IDENTITY) &&
                      !gam && !(d.fam_arg[3] >= 0 && slot >= d.fam_arg[2] && slot < d.fam_arg[2] + m->norm_vspan[di])))) {
     NormArgs na = norm_args(m, di);
-    if (mode == 2 && !idx && lo == 0 && hi == d.n && !shard && na.mode >= 0 && !getenv("NIMB200_NO_BYPRODUCT")) {
+    if (mode == 0 && !idx && gcount == d.n && na.mode >= 0 && !getenv("NIMB200_NO_BYPRODUCT")) {
+      // whole-declaration block sum from the data-only group statistics the sweep over the gathered vector keeps: G terms per
+      // chain, no pass over the nodes; data-sharded, the statistics were all-reduced once, so every rank forms the full sum
+      // itself and nothing is exchanged
+      for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {
+        const nimb200_sampler& o = m->samplers[s2];
+        if (!m->norm_sweep[s2] || !m->norm_gs_valid[s2] || !m->norm_gss_ok[s2] || m->deps[o.dep_off + 1].decl != di) continue;
+        if (o.target_slot != d.fam_arg[2] || o.n_targets != m->norm_vspan[di]) continue;
+        CK(launch_pdl(k_norm_sum_from_groups, dim3(C), dim3(o.n_targets > 2048 ? 1024 : 256), 0, m->stream, m->T, na, (const double*)m->d_norm_gs[s2],
+                      (const double*)m->d_norm_gss[s2], o.n_targets, d.n, dst0));
+        m->launches++;
+        CK(cudaGetLastError());
+        return 0;
+      }
+    }
+    if (mode == 2 && !idx && gcount == d.n && (!shard || comm_on(m)) && na.mode >= 0 && !getenv("NIMB200_NO_BYPRODUCT")) {
       // the sweep over the gathered vector keeps (sum y, count) per group: G terms per chain instead of a pass over the nodes
       for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {
         const nimb200_sampler& o = m->samplers[s2];
         if (!m->norm_sweep[s2] || !m->norm_gs_valid[s2] || m->deps[o.dep_off + 1].decl != di) continue;
         if (o.target_slot != d.fam_arg[2] || o.n_targets != m->norm_vspan[di]) continue;
-        CK(launch_pdl(k_norm_conj_from_groups, dim3(C), dim3(256), 0, m->stream, m->T, na, m->d_norm_gs[s2], o.n_targets, slot, dst0, dst1));
+        CK(launch_pdl(k_norm_conj_from_groups, dim3(C), dim3(o.n_targets > 2048 ? 1024 : 256), 0, m->stream, m->T, na, m->d_norm_gs[s2], o.n_targets, slot, dst0, dst1));
         m->launches++;
         CK(cudaGetLastError());
         return 0;
@@ -1771,6 +1788,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->norm_sweep.assign(m->samplers.size(), 0);
   m->d_norm_gs.assign(m->samplers.size(), nullptr);
   m->norm_gs_valid.assign(m->samplers.size(), 0);
+  m->d_norm_gss.assign(m->samplers.size(), nullptr);
+  m->norm_gss_ok.assign(m->samplers.size(), 0);
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
     if (sp.type != NIMB_SAMPLER_CONJ_NORMAL || m->wide[s] || sp.n_dep != 2) continue;
@@ -1787,6 +1806,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (!a_reads_target) {
       m->norm_sweep[s] = 1;
       TRY(dev_alloc(m, &m->d_norm_gs[s], (size_t)sp.n_targets * 2));
+      TRY(dev_alloc(m, &m->d_norm_gss[s], (size_t)sp.n_targets));
     }
   }
   // Cache slots: the block sum of the CURRENT state over (declaration, selection).  Entries of wide samplers whose selection
@@ -2230,8 +2250,25 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     if (!m->norm_gs_valid[s]) {
       k_norm_group_sums<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_norm_gs[s]);
       m->launches++;
-      if (m->nranks > 1 && m->sweep_sharded[s] && comm_on(m) && allreduce_sum(m, m->d_norm_gs[s], (size_t)sp.n_targets * 2)) return 1;
+      const bool shx = m->nranks > 1 && m->sweep_sharded[s] && comm_on(m);
+      if (shx && allreduce_sum(m, m->d_norm_gs[s], (size_t)sp.n_targets * 2)) return 1;
+      k_norm_group_ss<<<sp.n_targets, 128, 0, m->stream>>>(m->T, s, na, m->d_norm_gs[s], m->d_norm_gss[s]);
+      m->launches++;
+      if (shx && allreduce_sum(m, m->d_norm_gss[s], (size_t)sp.n_targets)) return 1;
       m->norm_gs_valid[s] = 1;
+      // usable for whole-declaration block sums when every node belongs to a target and the statistics are finite (checked once,
+      // outside any graph capture: the first sweep always runs through the ordinary launch path)
+      m->norm_gss_ok[s] = 0;
+      if (!getenv("NIMB200_NO_BYPRODUCT") && !(m->nranks > 1 && m->sweep_sharded[s] && !comm_on(m))) {
+        std::vector<double> hg((size_t)sp.n_targets * 2), hs((size_t)sp.n_targets);
+        CK(cudaMemcpyAsync(hg.data(), m->d_norm_gs[s], sizeof(double) * hg.size(), cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(hs.data(), m->d_norm_gss[s], sizeof(double) * hs.size(), cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaStreamSynchronize(m->stream));
+        double nodes = 0;
+        bool fin = true;
+        for (int t = 0; t < sp.n_targets; t++) { nodes += hg[2 * (size_t)t + 1]; fin = fin && std::isfinite(hg[2 * (size_t)t]) && std::isfinite(hs[t]); }
+        m->norm_gss_ok[s] = fin && nodes == (double)m->decl[m->deps[sp.dep_off + 1].decl].n;
+      }
     }
     size_t total = (size_t)sp.n_targets * C;
     CK(launch_pdl(k_norm_conj_draw, dim3((unsigned)((total + TB - 1) / TB)), dim3(TB), 0, m->stream, m->T, s, seed, iter, na, m->d_norm_gs[s]));

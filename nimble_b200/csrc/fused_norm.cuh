@@ -316,23 +316,23 @@ __global__ void k_norm_conj_finish(DevTab T, NormArgs a, int count, const double
 // data-only sums gs[g] = (sum y, count) the sweep over v keeps:  sum_i (y_i - A(target := 0) - v[G(i)]) = sum_g (Sy_g - n_g (A0 + v_g)).
 // One block per chain, threads stride over the groups (four independent partial sums each, so the gathers overlap), fixed-order
 // butterfly and warp order: G terms per chain instead of a pass over the nodes.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_norm_conj_from_groups(DevTab T, NormArgs a, const double* __restrict__ gs, int G, int ov_slot,
                         double* __restrict__ dst0, double* __restrict__ dst1) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
-  __shared__ double sR[8], sN[8];
-  const int c = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ double sR[32], sN[32];
+  const int c = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NT = blockDim.x;
   const double A0 = eval_prog(T, c, a.a_off, a.a_len, 0, 0, ov_slot, 0.0);
   const double* __restrict__ vb = T.state + (size_t)a.v_slot * T.C + c;
   double R[4] = {0.0, 0.0, 0.0, 0.0}, cnt = 0.0;
-  for (int g0 = threadIdx.x; g0 < G; g0 += 4 * 256) {
+  for (int g0 = threadIdx.x; g0 < G; g0 += 4 * NT) {
     double sy[4], n[4], v[4];
 #pragma unroll
     for (int u = 0; u < 4; u++) {  // all loads of a trip first (clamped index, no branch in between), then the arithmetic
-      const int g = min(g0 + u * 256, G - 1);
+      const int g = min(g0 + u * NT, G - 1);
       const double2 q = reinterpret_cast<const double2*>(gs)[g];
-      sy[u] = q.x; n[u] = g0 + u * 256 < G ? q.y : 0.0;
+      sy[u] = q.x; n[u] = g0 + u * NT < G ? q.y : 0.0;
       v[u] = vb[(size_t)g * T.C];
     }
 #pragma unroll
@@ -348,7 +348,7 @@ k_norm_conj_from_groups(DevTab T, NormArgs a, const double* __restrict__ gs, int
   __syncthreads();
   if (threadIdx.x != 0) return;
   double rr = 0.0, nn = 0.0;
-  for (int w = 0; w < 8; w++) { rr += sR[w]; nn += sN[w]; }
+  for (int w = 0; w < (NT >> 5); w++) { rr += sR[w]; nn += sN[w]; }
   const double tau = get_param(T, a.decl, 0, c, NIMB_PARAM_TAU, -1, 0.0);
   dst0[c] = rr * tau;
   dst1[c] = nn * tau;
@@ -382,6 +382,78 @@ k_norm_group_sums(DevTab T, int sid, NormArgs a, double* __restrict__ gs) {
     gs[2 * (size_t)t] = ((red[0] + red[1]) + red[2]) + red[3];
     gs[2 * (size_t)t + 1] = (double)(cred[0] + cred[1] + cred[2] + cred[3]);
   }
+}
+
+// Second data-only statistic per target: the centred sum of squares  ss[t] = sum_i (y_i - ybar_t)^2  over the target's nodes,
+// with ybar_t from the (already complete, i.e. all-reduced when data-sharded) group sums.  Same node walk as above.
+__global__ void __launch_bounds__(128)
+k_norm_group_ss(DevTab T, int sid, NormArgs a, const double* __restrict__ gs, double* __restrict__ ss) {
+  __shared__ double red[4];
+  const nimb200_sampler sp = T.samplers[sid];
+  const int t = blockIdx.x;
+  const nimb200_dep dp = T.deps[sp.dep_off + 1];
+  Sel s = sel_of(T, dp, t);
+  const double n = gs[2 * (size_t)t + 1];
+  const double ybar = n > 0.0 ? gs[2 * (size_t)t] / n : 0.0;
+  double acc = 0.0;
+  for (int k = s.lo + threadIdx.x; k < s.hi; k += 128) {
+    int node = s.idx ? s.idx[k] : k;
+    if (s.idx && (node < s.nlo || node >= s.nhi)) continue;
+    const double d = a.y[node] - ybar;
+    acc += d * d;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) ss[t] = ((red[0] + red[1]) + red[2]) + red[3];
+}
+
+// Block sum of the whole declaration from the per-group data-only statistics (sum y, n, centred sum of squares):
+//   sum_i (y_i - A - v[G(i)])^2 = sum_g [ ss_g + n_g (ybar_g - A - v_g)^2 ]
+// -- every term non-negative, so nothing cancels -- then the same finish as the streaming kernel.  G terms per chain instead of a
+// pass over the N nodes: with the group statistics in place an MCMC iteration of the linear mixed model reads no data node at all.
+// One block per chain, fixed-order butterfly and warp order.
+__global__ void __launch_bounds__(1024)
+k_norm_sum_from_groups(DevTab T, NormArgs a, const double* __restrict__ gs, const double* __restrict__ ss, int G, int n_nodes,
+                       double* __restrict__ dst) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
+  __shared__ double sS[32];
+  const int c = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, NT = blockDim.x;
+  const double A = eval_prog(T, c, a.a_off, a.a_len, 0, 0, -1, 0.0);
+  const double* __restrict__ vb = T.state + (size_t)a.v_slot * T.C + c;
+  double S[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int g0 = threadIdx.x; g0 < G; g0 += 4 * NT) {
+    double sy[4], n[4], v[4], q2[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int g = min(g0 + u * NT, G - 1);
+      const double2 q = reinterpret_cast<const double2*>(gs)[g];
+      sy[u] = q.x; n[u] = g0 + u * NT < G ? q.y : 0.0;
+      q2[u] = ss[g];
+      v[u] = vb[(size_t)g * T.C];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const double e = sy[u] / fmax(n[u], 1.0) - (A + v[u]);
+      S[u] += n[u] > 0.0 ? q2[u] + n[u] * (e * e) : 0.0;
+    }
+  }
+  double r = (S[0] + S[1]) + (S[2] + S[3]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  if (lane == 0) sS[warp] = r;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  double tot = 0.0;
+  for (int w = 0; w < (NT >> 5); w++) tot += sS[w];
+  const nimb200_decl& d = T.decl[a.decl];
+  const double sigma = eval_prog(T, c, d.prog_off[1], d.prog_len[1], 0, 0, -1, 0.0);
+  // sd == 0: the result depends on how many residuals are exactly zero, which the group statistics cannot tell -- walk the nodes
+  // (data-sharded ranks only hold their slice, and report NaN like the all-reduced streaming path does)
+  if (sigma == 0 && n_nodes > 0 && !isnan(tot)) dst[c] = T.nranks > 1 ? NAN : norm_sd0_sum(T, a, c, 0, n_nodes, nullptr);
+  else dst[c] = norm_sum_from_ss(sigma, tot, n_nodes);
 }
 
 __global__ void k_norm_conj_draw(DevTab T, int sid, uint64_t seed, uint64_t iter, NormArgs a, const double* __restrict__ gs) {
