@@ -1069,6 +1069,7 @@ struct nimb200_model {
   double* d_sweepbuf = nullptr;  // [T][3][C] partial sums of a sharded sweep
   size_t sweepbuf_cap = 0;
   std::vector<char> sweep_sharded;  // per sampler: touches a sharded declaration
+  std::vector<char> target_sharded; // per sampler: conjugate sweep whose targets are OWNED by ranks (shards cut on group boundaries)
   std::vector<size_t> sweep_deps;   // per sampler: dependent nodes of target 0 (execution-shape heuristic)
   unsigned long long* d_ctr = nullptr;  // device iteration counter (DevTab::ctr)
   unsigned int* d_ticket = nullptr;     // block ticket of k_monitor_ctr (the last block advances the counter)
@@ -1621,6 +1622,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->T.ctr = m->d_ctr;
   m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
   m->sweep_sharded.assign(m->samplers.size(), 0);
+  m->target_sharded.assign(m->samplers.size(), 0);
   // fused family: re-lay X once (row-major, rows padded to a multiple of 4 doubles)
   m->d_xpad.assign(m->decl.size(), nullptr);
   for (size_t i = 0; i < m->decl.size(); i++) {
@@ -2088,6 +2090,40 @@ static int set_shards(nimb200_model* m, int32_t nranks, int32_t rank, int32_t mi
       m->shard_hi[i] = (int32_t)std::min<int64_t>(d.n, per * (rank + 1));
     } else { m->shard_lo[i] = 0; m->shard_hi[i] = d.n; }
   }
+  // Group-aligned shards: a conjugate gamma-Poisson sweep whose targets own contiguous runs of the sharded declaration's nodes
+  // (sorted groups) gets its shard boundaries moved onto target boundaries.  Every target's nodes then sit on ONE rank, that
+  // rank alone draws the target (no exchange of [targets][chains] rate sums, 655 MB per sweep for the GLMM at 8192 chains), and
+  // the target declaration itself becomes sharded by ownership: its block sums are formed from each rank's own targets and
+  // all-reduced like any other sharded declaration's.  Not done when a target is monitored (the other ranks' copies are stale).
+  std::fill(m->target_sharded.begin(), m->target_sharded.end(), 0);
+  for (size_t s = 0; s < m->samplers.size() && nranks > 1 && !getenv("NIMB200_NO_GROUP_SHARDS"); s++) {
+    if (!m->pois_sweep[s]) continue;
+    const nimb200_sampler& sp = m->samplers[s];
+    const nimb200_dep &tp = m->deps[sp.dep_off], &dp = m->deps[sp.dep_off + 1];
+    const nimb200_decl &td = m->decl[tp.decl], &dd = m->decl[dp.decl];
+    if (!m->sharded[dp.decl] || td.value_kind != 1 || tp.sel != NIMB_SEL_SAME || tp.a != 0 || sp.n_targets != td.n) continue;
+    bool claimed = false;   // one owner layout per declaration
+    for (size_t s2 = 0; s2 < s; s2++) claimed |= m->target_sharded[s2] && m->deps[m->samplers[s2].dep_off + 1].decl == dp.decl;
+    bool monitored = false;
+    for (int32_t slot : m->monitors) monitored |= slot >= sp.target_slot && slot < sp.target_slot + sp.n_targets;
+    if (claimed || monitored) continue;
+    std::vector<int64_t> off((size_t)sp.n_targets + 1);
+    if (dp.sel == NIMB_SEL_SAME) for (int t = 0; t <= sp.n_targets; t++) off[t] = (int64_t)dp.a + t;
+    else if (dp.sel == NIMB_SEL_STRIDE) for (int t = 0; t <= sp.n_targets; t++) off[t] = (int64_t)dp.a * t;
+    else if (dp.sel == NIMB_SEL_SEG) for (int t = 0; t <= sp.n_targets; t++) off[t] = m->h_iarr[dp.a][t];
+    else continue;
+    auto first_target_at = [&](int r) {  // first target whose nodes start at or after rank r's even share
+      const int64_t want = (int64_t)dd.n * r / nranks;
+      return (int)(std::lower_bound(off.begin(), off.end() - 1, want) - off.begin());
+    };
+    const int t_lo = rank == 0 ? 0 : first_target_at(rank), t_hi = rank == nranks - 1 ? sp.n_targets : first_target_at(rank + 1);
+    m->shard_lo[dp.decl] = rank == 0 ? 0 : (int32_t)off[t_lo];
+    m->shard_hi[dp.decl] = rank == nranks - 1 ? dd.n : (int32_t)off[t_hi];
+    m->sharded[tp.decl] = 1;
+    m->shard_lo[tp.decl] = t_lo;
+    m->shard_hi[tp.decl] = t_hi;
+    m->target_sharded[s] = 1;
+  }
   CK(cudaMemcpyAsync(m->d_shard_lo, m->shard_lo.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
   CK(cudaMemcpyAsync(m->d_shard_hi, m->shard_hi.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
   CK(cudaMemcpyAsync(m->d_sharded, m->sharded.data(), sizeof(int32_t) * m->decl.size(), cudaMemcpyHostToDevice, m->stream));
@@ -2275,7 +2311,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     m->launches++;
   } else if (!m->wide[s] && m->pois_sweep[s]) {
     size_t total = (size_t)sp.n_targets * C;
-    const bool sh = m->nranks > 1 && m->sweep_sharded[s];
+    // group-aligned shards: every rank updates the targets it owns, all of whose nodes are in its slice -- one phase, no exchange
+    const bool sh = m->nranks > 1 && m->sweep_sharded[s] && !m->target_sharded[s];
     PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
     if (!m->pois_ysum_valid[s]) {
       k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[m->deps[sp.dep_off + 1].decl],

@@ -210,6 +210,11 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   size_t tq = gid / T.C;
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
+  if (PHASE == 0) {  // targets sharded by ownership (group-aligned shards): the owner alone updates a target
+    const nimb200_dep tp0 = T.deps[sp.dep_off];
+    const int tn = (tp0.sel == NIMB_SEL_SAME ? tp0.a + t : tp0.a);
+    if (tn < T.shard_lo[tp0.decl] || tn >= T.shard_hi[tp0.decl]) return;
+  }
   const double b0 = T.state[(size_t)a.b0_slot * T.C + c], b1 = T.state[(size_t)a.b1_slot * T.C + c];
   const nimb200_dep dp = T.deps[sp.dep_off + 1];
   Sel s = sel_of(T, dp, t);

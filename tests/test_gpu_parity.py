@@ -375,6 +375,36 @@ def test_norm_family_block_sums_and_edges(oracle, b200):
     assert np.array_equal(dg.calculate(2), do.calculate(2)) and dg.calculate(2)[0] == np.inf and dg.calculate(2)[1] == -np.inf
 
 
+def test_norm_family_group_statistics_path(oracle, b200):
+    """After the first sweep over the gathered vector the device keeps (sum y, n, centred sum of squares) per group and forms
+    whole-declaration block sums from them, G terms per chain instead of a pass over the nodes: same values as the oracle's
+    node-by-node sum, also for sd <= 0 / Inf / NaN, non-finite means, permuted group indices and groups without nodes."""
+    for name in ("lmm", "lmm_perm"):
+        m, conf = sm.SMALL[name]()
+        C = 13
+        inits = sm.random_inits(m, C, 5, 0.3)
+        cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+        run(cg, inits, 5, 0, seed=3)          # the u sweep has run: group statistics are in place
+        state = cg.dm.get_values()
+        se, mu = m.var_slot["sig_e"], m.var_slot["mu"]
+        state[3, se], state[4, se], state[5, se], state[6, se] = 0.0, -1.0, np.inf, np.nan
+        state[7, mu], state[8, mu] = np.inf, np.nan
+        state[9, m.var_slot["u"] + 2] = 1e6
+        cg.dm.set_values(state)
+        do = co._ensure(C)
+        do.set_values(state)
+        y = len(cg.builder.decls) - 1
+        a, b = cg.dm.calculate(y), do.calculate(y)
+        assert np.array_equal(np.isnan(a), np.isnan(b)), (a, b)
+        assert np.array_equal(np.isinf(a), np.isinf(b)) and np.array_equal(np.sign(a[np.isinf(a)]), np.sign(b[np.isinf(b)]))
+        assert rel_err(a, b).max() < RTOL_LP, rel_err(a, b).max()
+        # and the streaming kernel on the same state (a node range never takes the group path)
+        n = cg.builder.decls[y].n
+        parts = cg.dm.calculate(y, 0, n // 2) + cg.dm.calculate(y, n // 2, n)
+        ok = np.isfinite(b)
+        assert rel_err(parts[ok], a[ok]).max() < RTOL_LP
+
+
 def test_bern_family_block_sums_and_edges(oracle, b200):
     """Bernoulli-logit-linear family (occupancy model) against the oracle for >= 32 chains: the data declaration with its
     latent gate, the latent declaration itself, and chains that must take the exact path (gate / value not 0 or 1, NaN)."""
