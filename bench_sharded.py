@@ -66,29 +66,62 @@ def data_sharded_block(a, nb, backend, local, rank, world, dist, torch, barrier)
         par["pass"] = par["ranks_bit_identical"] and par["max_rel_diff_vs_unsharded"] < 1e-9
     res["parity"] = par
     barrier()
-    # ---- timing at full size and at a size where sharding should pay
-    sizes = []
-    for N in (10_000_000, 80_000_000):
+    # ---- timing.  Cases: (1) the LMM as north_star names it, every block sum a streaming pass over this rank's slice plus an
+    # all-reduce (group-statistics shortcut switched off); (2) the LMM as the library runs it by default (block sums from data-only
+    # group statistics, all-reduced once: nothing left to exchange per iteration); (3) the same streaming layout at N = 8e7, where
+    # a slice is still 10x the L2; (4) configs[1] with few chains (64 in total, all on every GPU): the fused logistic kernel over
+    # each rank's tiles of X; (5) configs[4] at 8192 chains with group-aligned shards.
+    import os
+    cases = []
+
+    def case(label, make, C_, niter, warm, env=None, transports=("peer", "nccl")):
         t0 = time.time()
-        m, conf = configs.lmm(N=N, G=10_000, seed=1003)
-        inits = np.tile(m.init_vector(), (C, 1))
-        entry = {"N": N, "host_build_seconds": time.time() - t0}
-        for transport in ("peer", "nccl"):
-            r, _ = _sharded_run(nb, backend, conf, inits, local, rank, world, transport, 200, 20, 1 << 16, torch, dist, barrier)
-            entry[transport] = r
-        if rank == 0:   # the same model on one GPU, the other ranks wait
-            cm1 = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=local)
-            d1 = cm1._ensure(C)
-            d1.set_values(inits)
-            d1.run(20, 0, 1, True, 31)
-            d1.run(200, 0, 1, False, 31)
-            ms1, l1 = d1.last_timing()
-            d1.close()
-            entry["one_gpu_ms_per_iteration"] = ms1 / 200
-            entry["speedup_peer_vs_one_gpu"] = entry["one_gpu_ms_per_iteration"] / entry["peer"]["ms_per_iteration"]
-            entry["speedup_nccl_vs_one_gpu"] = entry["one_gpu_ms_per_iteration"] / entry["nccl"]["ms_per_iteration"]
-        barrier()
-        sizes.append(entry)
-        del m, conf
-    res["sizes"] = sizes
+        for k, v in (env or {}).items():
+            os.environ[k] = v
+        try:
+            m_, conf_, inits_ = make(C_)
+            entry = {"case": label, "chains": C_, "host_build_seconds": time.time() - t0}
+            for transport in transports:
+                r, _ = _sharded_run(nb, backend, conf_, inits_, local, rank, world, transport, niter, warm, 1 << 16, torch, dist, barrier)
+                entry[transport] = r
+            if rank == 0:   # the same model on one GPU, the other ranks wait
+                cm1 = nb.compileNimble(nb.buildMCMC(conf_), backend=backend, device=local)
+                d1 = cm1._ensure(C_)
+                d1.set_values(inits_)
+                d1.run(warm, 0, 1, True, 31)
+                d1.run(niter, 0, 1, False, 31)
+                ms1, _ = d1.last_timing()
+                d1.close()
+                entry["one_gpu_ms_per_iteration"] = ms1 / niter
+                for transport in transports:
+                    entry["speedup_%s_vs_one_gpu" % transport] = entry["one_gpu_ms_per_iteration"] / entry[transport]["ms_per_iteration"]
+            barrier()
+        except Exception as ex:  # noqa: BLE001 -- one case must not take the others down
+            entry = {"case": label, "error": "%s: %s" % (type(ex).__name__, str(ex)[:200])}
+        finally:
+            for k in (env or {}):
+                os.environ.pop(k, None)
+        cases.append(entry)
+
+    def lmm_of(N):
+        def make(C_):
+            m_, conf_ = configs.lmm(N=N, G=10_000, seed=1003)
+            return m_, conf_, np.tile(m_.init_vector(), (C_, 1))
+        return make
+
+    def logistic_few(C_):
+        m_, conf_ = configs.logistic(N=a.n, p=a.p, seed=1001)
+        return m_, conf_, np.stack([m_.init_vector(i) for i in configs.logistic_inits(a.p, C_)])
+
+    def glmm_full(C_):
+        m_, conf_ = configs.glmm()
+        return m_, conf_, np.tile(m_.init_vector(), (C_, 1))
+
+    stream = {"NIMB200_NO_BYPRODUCT": "1"}
+    case("lmm N=1e7, streaming block sums + all-reduce (NIMB200_NO_BYPRODUCT)", lmm_of(10_000_000), C, 200, 20, stream)
+    case("lmm N=1e7, default (group statistics)", lmm_of(10_000_000), C, 200, 20, None, ("peer",))
+    case("lmm N=8e7, streaming block sums + all-reduce (NIMB200_NO_BYPRODUCT)", lmm_of(80_000_000), C, 100, 10, stream, ("peer",))
+    case("logistic N=%d p=%d, 64 chains in total on every GPU" % (a.n, a.p), logistic_few, 64, 100, 10)
+    case("glmm N=1e6 G=1e4, 8192 chains, group-aligned shards", glmm_full, 8192, 20, 3, None, ("peer",))
+    res["cases"] = cases
     return res

@@ -2323,14 +2323,21 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     }
     const unsigned nb = (unsigned)((total + PF_THREADS - 1) / PF_THREADS);
     if (!sh) {
-      const bool byp = m->pois_byp_slot[s] >= 0 && m->nranks <= 1;
+      // group-aligned shards keep the by-product: each rank adds up the shares of the targets it owns, one all-reduce of `chains`
+      // doubles completes the cached block sum
+      const bool own = m->nranks > 1 && m->target_sharded[s];
+      const bool byp = m->pois_byp_slot[s] >= 0 && (m->nranks <= 1 || (own && comm_on(m)));
       k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr,
                                                            byp ? m->d_pois_contrib[s] : nullptr);
       m->launches++;
       if (byp) {  // fixed-order sum over the targets -> the cached current-state block sum of the dependent declaration
-        CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_pois_contrib[s], sp.n_targets, 1, C,
-                                                              m->d_depcache + (size_t)m->pois_byp_slot[s] * C, nullptr));
+        const int tdecl = m->deps[sp.dep_off].decl;
+        const int t_lo = own ? m->shard_lo[tdecl] : 0, t_hi = own ? m->shard_hi[tdecl] : sp.n_targets;
+        double* cache = m->d_depcache + (size_t)m->pois_byp_slot[s] * C;
+        CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, (const double*)(m->d_pois_contrib[s] + (size_t)t_lo * C),
+                      std::max(0, t_hi - t_lo), 1, C, cache, (double*)nullptr));
         m->launches++;
+        if (own && allreduce_sum(m, cache, C)) return 1;
         refreshed.push_back(m->pois_byp_slot[s]);
       }
     } else {  // data-sharded: this rank's share of every (target, chain) rate contribution -> all-reduce -> draws
