@@ -953,10 +953,17 @@ __global__ void k_monitor(DevTab T, const int32_t* mon, int nmon, double* row /*
 // graph-replayable form: decides from the device iteration counter whether this iteration is saved and where
 // (iteration it = ctr[0] - iter0 of this run; rows_before rows were already in the buffer)
 // The last block to finish also advances the counter (every block has read it by then), which saves the separate launch.
-__global__ void k_monitor_ctr(DevTab T, const int32_t* mon, int nmon, double* samples, long long rows_before, long long iter0,
-                              long long nburnin, int thin, unsigned long long* ctr, unsigned int* ticket) {
+// what changes from one nimb200_mcmc_run call to the next lives in device memory, not in kernel arguments, so that the captured
+// iteration graph of one call can be replayed by the next (a `reset = FALSE` continuation does not pay for a new capture)
+struct RunParams { long long rows_before, iter0, nburnin; int thin, pad; double* samples; };
+
+__global__ void k_monitor_ctr(DevTab T, const int32_t* mon, int nmon, const RunParams* __restrict__ rp, unsigned long long* ctr,
+                              unsigned int* ticket) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
+  const long long rows_before = rp->rows_before, iter0 = rp->iter0, nburnin = rp->nburnin;
+  const int thin = rp->thin;
+  double* samples = rp->samples;
   long long it = (long long)T.ctr[0] - iter0;
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (it > nburnin && (it - nburnin) % thin == 0 && gid < (size_t)nmon * T.C) {
@@ -1074,6 +1081,11 @@ struct nimb200_model {
   unsigned long long* d_ctr = nullptr;  // device iteration counter (DevTab::ctr)
   unsigned int* d_ticket = nullptr;     // block ticket of k_monitor_ctr (the last block advances the counter)
   cudaGraphExec_t graph_exec = nullptr;
+  // the captured iteration stays usable across runs as long as what was baked into it still holds
+  std::vector<char> graph_pattern;      // cache-validity pattern at the start of the captured iteration
+  uint64_t graph_seed = 0;
+  int64_t graph_launches = 0, graph_allreduces = 0;
+  void* d_runp = nullptr;               // RunParams
   double* d_samples = nullptr;  // [cap][nmon][C]
   int64_t rows = 0, cap = 0, iter_done = 0;
   bool waic = false;                 // online WAIC enabled
@@ -1618,6 +1630,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   TRY(dev_alloc(m, &m->d_ctr, 2));
   TRYCU(cudaMemsetAsync(m->d_ctr, 0, 2 * sizeof(unsigned long long), m->stream));
   TRY(dev_alloc(m, &m->d_ticket, 1));
+  { RunParams* rp = nullptr; TRY(dev_alloc(m, &rp, 1)); m->d_runp = rp; }
   TRYCU(cudaMemsetAsync(m->d_ticket, 0, sizeof(unsigned int), m->stream));
   m->T.ctr = m->d_ctr;
   m->T.shard_lo = m->d_shard_lo; m->T.shard_hi = m->d_shard_hi; m->T.sharded = m->d_sharded; m->T.rank = 0; m->T.nranks = 1;
@@ -2442,7 +2455,9 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     }
     CK(cudaGetLastError());
   }
-  std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  // cached block sums survive a `reset = FALSE` continuation: nothing but the samplers has touched the chain state since the
+  // last run (set_values / initialize_model / a new shard layout clear them themselves)
+  if (reset) std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   int64_t addrows = (niter - nburnin) / thin;
   if (m->rows + addrows > m->cap) {  // resize(mvSamples, ...), MCMC_build.R:262
     int64_t ncap = m->rows + addrows;
@@ -2456,19 +2471,24 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   }
   m->launches = 0;
   m->allreduces = 0;
+  const int64_t rows_before = m->rows, iter0 = m->iter_done;
   {
     unsigned long long first = (unsigned long long)(m->iter_done + 1);
     CK(cudaMemcpyAsync(m->d_ctr, &first, sizeof first, cudaMemcpyHostToDevice, m->stream));
+    RunParams rp{(long long)rows_before, (long long)iter0, (long long)nburnin, (int)thin, 0, m->d_samples};
+    CK(cudaMemcpyAsync(m->d_runp, &rp, sizeof rp, cudaMemcpyHostToDevice, m->stream));
   }
-  const int64_t rows_before = m->rows, iter0 = m->iter_done;
   // One iteration = a fixed sequence of launches once the pattern of valid cached sums has settled, so it is captured into a
   // CUDA graph and replayed (launch latency is what bounds small models).  Iterations in which an RW_block adaptation kernel is
-  // due run through the ordinary launch path; so does everything when a NCCL all-reduce is part of the sequence.
+  // due run through the ordinary launch path; so does everything when a NCCL all-reduce is part of the sequence (the library's
+  // own peer-memory all-reduce is an ordinary kernel and is captured).  What differs between calls (row offset, iteration
+  // offset, burn-in, thinning, the sample buffer) is read from device memory, so the graph of an earlier call is replayed by
+  // later ones whenever the seed and the cache pattern at the start of an iteration are those it was captured under.
   const char* genv = getenv("NIMB200_GRAPH");
   const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8 && !m->time_samplers;
-  if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
-  int64_t graph_launches = 0, graph_allreduces = 0;
+  if (m->graph_exec && (!want_graph || m->waic || m->graph_seed != seed)) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
   std::vector<char> valid_prev;
+  bool capture_failed = false;
   auto adapt_due = [&]() {
     for (size_t s = 0; s < m->samplers.size(); s++) {
       const nimb200_sampler& sp = m->samplers[s];
@@ -2503,7 +2523,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     if (nmon > 0) {
       size_t total = (size_t)nmon * C;
       CK(launch_pdl(k_monitor_ctr, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, m->stream, m->T, (const int32_t*)m->d_mon, nmon,
-                    m->d_samples, (long long)rows_before, (long long)iter0, (long long)nburnin, (int)thin, m->d_ctr, m->d_ticket));
+                    (const RunParams*)m->d_runp, m->d_ctr, m->d_ticket));
       m->launches++;
     } else {
       k_bump_iter<<<1, 1, 0, m->stream>>>(m->d_ctr);
@@ -2515,41 +2535,45 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   for (int64_t it = 1; it <= niter; it++) {
     uint64_t git = (uint64_t)(m->iter_done + it);
     bool due = adapt_due();
-    if (m->graph_exec && !due) {
+    if (m->graph_exec && !due && m->dep_valid == m->graph_pattern) {
       CK(cudaGraphLaunch(m->graph_exec, m->stream));
-      m->launches += graph_launches;
-      m->allreduces += graph_allreduces;
+      m->launches += m->graph_launches;
+      m->allreduces += m->graph_allreduces;
       for (size_t s = 0; s < m->samplers.size(); s++)
         if (m->samplers[s].type == NIMB_SAMPLER_RW_BLOCK && m->samplers[s].adaptive) m->ran[s] += m->samplers[s].tries;
       continue;
     }
-    bool capture = want_graph && !m->graph_exec && !due && it >= 3 && valid_prev == m->dep_valid;
+    // capture once the pattern repeats from one iteration to the next (and an older graph, if any, does not fit it)
+    bool capture = want_graph && !capture_failed && !due && it >= 3 && valid_prev == m->dep_valid;
     valid_prev = m->dep_valid;
     if (capture) {
       std::vector<int> ran_before = m->ran;
       int64_t l0 = m->launches, a0 = m->allreduces;
       cudaGraph_t g = nullptr;
+      if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
       bool ok = cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
       if (ok && one_iteration(git)) ok = false;
       if (cudaStreamEndCapture(m->stream, &g) != cudaSuccess || !g) ok = false;
       if (ok && m->dep_valid != valid_prev) ok = false;  // the cache pattern must repeat for the replay to be valid
       if (ok && cudaGraphInstantiate(&m->graph_exec, g, 0) != cudaSuccess) { m->graph_exec = nullptr; ok = false; }
       if (g) cudaGraphDestroy(g);
-      graph_launches = m->launches - l0;
-      graph_allreduces = m->allreduces - a0;
+      m->graph_launches = m->launches - l0;
+      m->graph_allreduces = m->allreduces - a0;
       m->launches = l0;
       m->allreduces = a0;
       if (ok) {
+        m->graph_pattern = valid_prev;
+        m->graph_seed = seed;
         CK(cudaGraphLaunch(m->graph_exec, m->stream));  // capturing did not execute anything
-        m->launches += graph_launches;
-        m->allreduces += graph_allreduces;
+        m->launches += m->graph_launches;
+        m->allreduces += m->graph_allreduces;
         continue;
       }
       cudaGetLastError();
       m->ran = ran_before;  // nothing ran: fall back to ordinary launches for good
       m->dep_valid = valid_prev;
       if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
-      valid_prev.assign(1, 2);  // never equal again -> no further capture attempts
+      capture_failed = true;
     }
     if (one_iteration(git)) return 1;
   }

@@ -287,3 +287,35 @@ def test_sampler_timing_mode(b200):
     assert t.shape == (len(conf.samplerConfs),) and np.all(t > 0)
     total_ms, _ = cg.dm.last_timing()
     assert t.sum() * 1e3 <= total_ms * 1.05
+
+
+def test_captured_iteration_is_replayed_by_continuation_runs(b200):
+    """A `reset = FALSE` continuation replays the CUDA graph an earlier call captured (row offset, iteration offset, burn-in,
+    thinning and the sample buffer are read from device memory): split runs, thinning changes and a grown sample buffer give
+    the bits of one ungraphed run."""
+    import os
+    m, conf = sm.SMALL["logistic"]()
+    inits = sm.random_inits(m, 9, 3, 0.1)
+    cm = compile_on(b200, conf)
+    run(cm, inits, 40, 10, seed=5)
+    a1 = cm.dm.samples().copy()
+    run(cm, inits, 25, 0, seed=5, reset=False)           # replayed from its first iteration
+    run(cm, inits, 30, 0, thin=3, seed=5, reset=False)   # other thinning, buffer grown twice by now
+    got = cm.dm.samples()
+    assert cm.dm.last_allreduces()[1], "the last run should have gone through the captured graph"
+    os.environ["NIMB200_GRAPH"] = "0"
+    try:
+        ref = compile_on(b200, conf)
+        run(ref, inits, 40, 10, seed=5)
+        run(ref, inits, 25, 0, seed=5, reset=False)
+        run(ref, inits, 30, 0, thin=3, seed=5, reset=False)
+        want = ref.dm.samples()
+    finally:
+        del os.environ["NIMB200_GRAPH"]
+    assert got.shape == want.shape == (9, 30 + 25 + 10, got.shape[2])
+    assert np.array_equal(got, want) and np.array_equal(got[:, :30], a1)
+    # another seed is another graph: same answer as a fresh model run with that seed
+    run(cm, inits, 30, 0, seed=6)
+    fresh = compile_on(b200, conf)
+    run(fresh, inits, 30, 0, seed=6)
+    assert np.array_equal(cm.dm.samples(), fresh.dm.samples())
