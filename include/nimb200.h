@@ -316,6 +316,13 @@ int nimb200_measure_fp64_mixed(int device, double *tflops);
 /* diagnostic: the fused kernels' own exp (which=0) / log (1) / reciprocal (2) / dbern-logit log-density for y=0 (3),
  * y=1 (4) applied to a host array, so that tests can measure their accuracy against libm. */
 int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
+/* diagnostic: the tcgen05 experiment (csrc/ozaki_logit.cu; no reference counterpart): the dbern-logit-inprod block sum with the
+ * contraction X.beta computed as exact int8 slice products on the 5th-generation tensor cores (tcgen05.mma kind::i8,
+ * accumulators in TMEM) and recombined in FP64.  HOST arrays X [n][p] row-major, y [n], beta [p][C] (chain fastest); eta_out
+ * [n][C], sums_out [C] and ms_out (average milliseconds of one launch) may each be NULL.  Allocates and frees its own device
+ * buffers.  Not used by the sampling path (measured slower than the FP64 mma.sync kernel). */
+int nimb200_debug_ozaki(const double *X, const double *y, int32_t n, int32_t p, const double *beta, int32_t C, double *eta_out,
+                        double *sums_out, double *ms_out);
 
 /* No counterpart in the reference (NIMBLE has no device code and nothing in it is asked to run without
  * allocating).  Per-chain block log-probability of y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))) -- the quantity
