@@ -1039,6 +1039,8 @@ struct nimb200_model {
   std::vector<SamplerDev> sdev;
   std::vector<char> wide;       // per sampler: wide path?
   std::vector<char> dep_valid;  // per cache slot: depcache row valid?
+  std::vector<char> lp_valid;   // per declaration: d_lpcache row holds the block sum of the CURRENT state (set by calculate() on the
+                                // whole declaration, cleared by anything that changes the chain state)
   std::vector<int32_t> dep_slot; // dependency entry -> cache slot: entries of wide samplers with the same (declaration, selection) share one
   int32_t* d_dep_slot = nullptr;
   std::vector<std::vector<int>> invalidates;  // per sampler: dependency entries (of any sampler) it invalidates
@@ -1159,6 +1161,54 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 
 static const int EVAL_THREADS = 256;
 static const int EVAL_NPT = 32;
+
+// Host -> device copy of a large pageable array through a ring of pinned staging buffers filled by several host threads: a plain
+// cudaMemcpy from pageable memory runs at ~10 GB/s (one thread copying into the driver's staging buffer); with four threads
+// filling 16 MiB pinned chunks while the previous chunk is in flight the copy approaches the PCIe rate.  Process-wide buffers,
+// allocated on first use (64 MiB of pinned host memory), guarded by a mutex.
+#include <mutex>
+#include <thread>
+namespace {
+constexpr size_t STAGE_BYTES = 16u << 20;
+constexpr int STAGE_BUFS = 4, STAGE_THREADS = 4;
+struct Staging {
+  std::mutex mu;
+  char* buf[STAGE_BUFS] = {nullptr};
+  cudaEvent_t done[STAGE_BUFS];
+  bool ready = false, failed = false;
+} g_stage;
+}  // namespace
+static cudaError_t upload_large(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes < (32u << 20) || getenv("NIMB200_NO_STAGED_UPLOAD")) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  std::lock_guard<std::mutex> lk(g_stage.mu);
+  if (!g_stage.ready && !g_stage.failed) {
+    for (int b = 0; b < STAGE_BUFS && !g_stage.failed; b++) {
+      if (cudaHostAlloc((void**)&g_stage.buf[b], STAGE_BYTES, cudaHostAllocPortable) != cudaSuccess) g_stage.failed = true;
+      else if (cudaEventCreateWithFlags(&g_stage.done[b], cudaEventDisableTiming) != cudaSuccess) g_stage.failed = true;
+    }
+    cudaGetLastError();
+    g_stage.ready = !g_stage.failed;
+  }
+  if (!g_stage.ready) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+  size_t off = 0;
+  for (int k = 0; off < bytes; k++) {
+    const int b = k % STAGE_BUFS;
+    const size_t n = std::min(STAGE_BYTES, bytes - off);
+    if (k >= STAGE_BUFS) { cudaError_t e = cudaEventSynchronize(g_stage.done[b]); if (e != cudaSuccess) return e; }
+    std::thread th[STAGE_THREADS];
+    const size_t per = (n + STAGE_THREADS - 1) / STAGE_THREADS;
+    for (int t = 0; t < STAGE_THREADS; t++) {
+      const size_t lo = std::min(n, per * t), hi = std::min(n, per * (t + 1));
+      th[t] = std::thread([=]() { if (hi > lo) memcpy(g_stage.buf[b] + lo, (const char*)src + off + lo, hi - lo); });
+    }
+    for (int t = 0; t < STAGE_THREADS; t++) th[t].join();
+    cudaError_t e = cudaMemcpyAsync((char*)dst + off, g_stage.buf[b], n, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaEventRecord(g_stage.done[b], st);
+    if (e != cudaSuccess) return e;
+    off += n;
+  }
+  return cudaStreamSynchronize(st);   // the staging buffers are free again when this returns
+}
 
 template <class Tp>
 static int dev_alloc(nimb200_model* m, Tp** p, size_t count) {
@@ -1552,7 +1602,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->h_iarr.resize(t->n_iarr);
   for (int i = 0; i < t->n_darr; i++) {
     TRY(dev_alloc(m, &m->d_darr[i], (size_t)t->darr_len[i]));
-    TRYCU(cudaMemcpyAsync(m->d_darr[i], t->darr[i], sizeof(double) * t->darr_len[i], cudaMemcpyHostToDevice, m->stream));
+    TRYCU(upload_large(m->d_darr[i], t->darr[i], sizeof(double) * t->darr_len[i], m->stream));
   }
   for (int i = 0; i < t->n_iarr; i++) {
     TRY(dev_alloc(m, &m->d_iarr[i], (size_t)t->iarr_len[i]));
@@ -1936,6 +1986,7 @@ extern "C" int nimb200_set_values(nimb200_model* m, const double* v) {
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
   return 0;
 }
 
@@ -1966,6 +2017,7 @@ extern "C" int nimb200_calculate(nimb200_model* m, int32_t di, int32_t lo, int32
   if (launch_eval_sum(m, 0, di, lo, hi, nullptr, dst, nullptr, nullptr, -1, 0)) return 1;
   CK(cudaMemcpyAsync(out, dst, sizeof(double) * m->C, cudaMemcpyDeviceToHost, m->stream));
   CK(cudaStreamSynchronize(m->stream));
+  if (whole) { if (m->lp_valid.size() != m->decl.size()) m->lp_valid.assign(m->decl.size(), 0); m->lp_valid[di] = 1; }
   return 0;
 }
 
@@ -2155,6 +2207,7 @@ static int set_shards(nimb200_model* m, int32_t nranks, int32_t rank, int32_t mi
   }
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
   return 0;
 }
@@ -2253,7 +2306,11 @@ static int ensure_dep_sums(nimb200_model* m, int s) {  // block sums of the curr
     if (m->dep_valid[slot]) continue;
     const nimb200_dep& dp = m->deps[g];
     HostSel hs = host_sel(m, dp, m->h_iarr);
-    if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)slot * m->C, nullptr, nullptr, -1, 0)) return 1;
+    if (!hs.idx && hs.lo == 0 && hs.hi == m->decl[dp.decl].n && dp.decl < (int)m->lp_valid.size() && m->lp_valid[dp.decl]) {
+      // initializeModel's calculate() of this declaration (P/R/initializeModel.R:78-96) was on this very state: reuse its sum
+      CK(cudaMemcpyAsync(m->d_depcache + (size_t)slot * m->C, m->d_lpcache + (size_t)dp.decl * m->C, sizeof(double) * m->C,
+                         cudaMemcpyDeviceToDevice, m->stream));
+    } else if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_depcache + (size_t)slot * m->C, nullptr, nullptr, -1, 0)) return 1;
     m->dep_valid[slot] = 1;
   }
   return 0;
@@ -2423,6 +2480,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   }
   for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
   for (int g : refreshed) m->dep_valid[g] = 1;
+  std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);   // the chain state has moved on
   CK(cudaGetLastError());
   return 0;
 }
@@ -2735,6 +2793,7 @@ extern "C" int nimb200_initialize_model(nimb200_model* m, const int32_t* decl_or
   if (flag) return fail("initializeModel: a missing initial value cannot be simulated (declaration " + std::to_string(flag - 1) +
                         ": only dnorm, dgamma, dbeta, dexp, dlogis, dbin and dpois (mean <= 500) nodes can)");
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
   return 0;
 }
 
