@@ -2480,7 +2480,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   }
   for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
   for (int g : refreshed) m->dep_valid[g] = 1;
-  std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);   // the chain state has moved on
+  for (int e = 0; e < sp.n_dep && !m->lp_valid.empty(); e++) m->lp_valid[m->deps[sp.dep_off + e].decl] = 0;  // these sums have moved on
   CK(cudaGetLastError());
   return 0;
 }
