@@ -394,9 +394,9 @@ def main():
                 "what": "strict algorithmic flops only: the 2*N*p*C contraction",
                 # dram__bytes_read.sum + dram__bytes_write.sum per launch cannot be measured inside this run: the figure is QUOTED
                 # from the committed ncu --set full capture of this kernel at this workload, null for any other workload
-                "traffic": 429.9e6 if quoted else None,
+                "traffic": 429.7e6 if quoted else None,
                 "traffic_kind": "quoted from the ncu capture in profiles/ (not measured by this run)" if quoted else None,
-                "traffic_source": "profiles/r1f_summary.md" if quoted else None,
+                "traffic_source": "profiles/r2f_fused_raw.csv (dram__bytes_read.sum 424.5 MB + dram__bytes_write.sum 5.2 MB)" if quoted else None,
                 "algorithmic_bytes": alg_bytes, "kernel_ms": k_ms, "evals_per_s_kernel": a.n * C / (k_ms * 1e-3),
                 "fp64_units": {"achieved": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12, "peak": mixed, "unit": "TFLOP/s",
                                "frac": (contraction_flops + epi_flops) / (k_ms * 1e-3) / 1e12 / mixed if mixed else None,

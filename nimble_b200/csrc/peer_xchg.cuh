@@ -15,7 +15,8 @@
 // which a peer writes after its own all-reduce e -- reads included -- has finished.
 // The sequence number lives in device memory and is advanced by the kernel itself (by its last block), so the kernel can
 // be captured into the iteration's CUDA graph and replayed.  A rank whose peers never arrive gives up after XCHG_TIMEOUT_CYCLES, raises the
-// error word and lets the stream drain (the host reports it) -- a kernel must never spin forever.
+// error word and lets the stream drain (the host reports it) -- a kernel must never spin forever; once the error word is set
+// every later all-reduce returns at once (NaN), so a broken group costs one time-out, not one per exchange.
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) k_peer_allreduce(PeerXchg X, dou
   const int b = blockIdx.x, R = X.nranks, tid = threadIdx.x;
   if (tid == 0) {
     s_epoch = *X.seq + 1;   // nobody advances seq before every block of this kernel has passed this read (see the end)
-    s_bad = 0;
+    s_bad = *(volatile unsigned int*)X.err != 0;   // a wait has timed out before: the group is broken, do not wait again
   }
   __syncthreads();
   const unsigned long long e = s_epoch;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) k_peer_allreduce(PeerXchg X, dou
   // happens-before it, and the CTA barrier orders every thread's data stores before it: no per-thread fence is needed
   if (tid < R) st_release_sys(X.flags[tid] + ((size_t)par * R + X.rank) * XCHG_MAX_BLOCKS + b, e);
   // 3. one thread per source rank waits for that rank's epoch in MY memory
-  if (tid < R) {
+  if (tid < R && !s_bad) {
     const unsigned long long* f = X.flags[X.rank] + ((size_t)par * R + tid) * XCHG_MAX_BLOCKS + b;
     const long long t0 = clock64();
     while (ld_acquire_sys(f) < e) {
