@@ -982,16 +982,23 @@ class CompiledMCMC:
         thin2 = self.thinFromConfVec[1] if thin2 in (None, -1) else thin2
         if thin2 < 1 or thin2 != int(thin2):
             raise ValueError("cannot use thin2 < 1")
-        if not reset:
-            raise NotImplementedError("reset = FALSE with a second monitor set is not supported")
         g = int(np.gcd(int(thin), int(thin2)))
         dm.run(int(niter), int(nburnin), g, reset, int(seed))
         allrows = dm.samples()
+        # this call's rows are the last (niter - nburnin) // g of the buffer; thinning restarts with every run() call, as the
+        # reference's loop counter does (MCMC_build.R:279-303), so a continuation selects inside its own rows and appends
+        n_call = (int(niter) - int(nburnin)) // g
+        mine = allrows[:, allrows.shape[1] - n_call:]
         n1, n2 = (int(niter) - int(nburnin)) // int(thin), (int(niter) - int(nburnin)) // int(thin2)
         r1 = (np.arange(1, n1 + 1) * (int(thin) // g) - 1).astype(np.int64)
         r2 = (np.arange(1, n2 + 1) * (int(thin2) // g) - 1).astype(np.int64)
-        self.mvSamples = np.ascontiguousarray(allrows[:, r1][:, :, low.cols1])
-        self.mvSamples2 = np.ascontiguousarray(allrows[:, r2][:, :, low.cols2])
+        new1 = np.ascontiguousarray(mine[:, r1][:, :, low.cols1])
+        new2 = np.ascontiguousarray(mine[:, r2][:, :, low.cols2])
+        if reset or self.mvSamples is None or self.mvSamples2 is None:
+            self.mvSamples, self.mvSamples2 = new1, new2
+        else:   # reset = FALSE: mvSamples and mvSamples2 grow (MCMC_build.R:257-263)
+            self.mvSamples = np.concatenate([self.mvSamples, new1], axis=1)
+            self.mvSamples2 = np.concatenate([self.mvSamples2, new2], axis=1)
         return self.mvSamples
 
     def _simulate_missing_inits(self, dm, inits_matrix, seed):

@@ -261,6 +261,17 @@ def test_monitors2_and_thin2(oracle):
     assert "theta[3]" in out["summary"] and "alpha" in out["summary"]
     one = nb.runMCMC(cm, niter=20, nchains=1, setSeed=1, thin2=4)
     assert np.asarray(one["samples2"]).shape == (5, 11) and np.asarray(one["samples"]).shape == (6, 2)
+    # reset = FALSE with a second monitor set: both sample sets grow, thinning restarts with the call (MCMC_build.R:257-263, 279-303)
+    inits = np.tile(m.init_vector(), (2, 1))
+    cm.run_chains(inits, 30, 0, 3, True, 4, thin2=5)
+    first1, first2 = cm.mvSamples.copy(), cm.mvSamples2.copy()
+    cm.run_chains(inits, 21, 0, 3, False, 4, thin2=5)
+    assert cm.mvSamples.shape[1] == 10 + 7 and cm.mvSamples2.shape[1] == 6 + 4
+    assert np.array_equal(cm.mvSamples[:, :10], first1) and np.array_equal(cm.mvSamples2[:, :6], first2)
+    solo = compile_on(oracle, nb.configureMCMC(m, monitors=["theta", "beta"], thin=5))
+    solo.run_chains(inits, 30, 0, 5, True, 4)
+    solo.run_chains(inits, 21, 0, 5, False, 4)
+    assert np.array_equal(cm.mvSamples2, solo.mvSamples)
 
 
 def _waic_case():
