@@ -768,7 +768,8 @@ __global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter,
 
 // wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
 __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
-                            double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls) {
+                            double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls,
+                            int* __restrict__ accept_out) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -784,6 +785,7 @@ __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int
   if (lp0 == -INFINITY) jump = false;
   else jump = decide(lp0 + lp1 + (pls ? pls[c] : 0.0), key, call);
   int d = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1;
+  if (accept_out) accept_out[c] = jump ? 1 : 0;
   if (jump) {
     for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c] = newsum[(size_t)e * T.C + c];
   } else {
@@ -1059,6 +1061,12 @@ struct nimb200_model {
   std::vector<int> pois_byp_slot;    // per such sweep: cache slot of the dependents' whole-declaration block sum it can refresh, or -1
   std::vector<double*> d_pois_contrib; // [n_targets][C] per-(target, chain) shares of that block sum
   std::vector<char> pois_ysum_valid;
+  // group sums S[t][c] = sum over target t's nodes of exp(b1 x) for chain c's CURRENT b1 (fused_pois.cuh): with them a block sum or
+  // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
+  std::vector<double*> d_pois_S, d_pois_Snew;
+  std::vector<char> pois_S_valid, pois_S_pending;
+  int* d_accept = nullptr;        // [C] accept flags of the last wide MH decision
+  int prop_lo = -1, prop_hi = -1; // state slots that currently hold a proposal (between propose and finish)
   std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
   std::vector<char> norm_gs_valid;   // is computed (and, data-sharded, all-reduced) once and kept until the shards change
   std::vector<double*> d_norm_gss;   // per such sampler: [n_targets] centred sum of squares of every target's nodes (data only too)
@@ -1283,6 +1291,35 @@ static int norm_blocks(int count) {
   return (count + npb - 1) / npb;
 }
 
+// Poisson family, group-sum path: is it usable for sampler s right now (not with ungrouped data shards)?
+static bool pois_S_usable(const nimb200_model* m, size_t s) {
+  return m->pois_sweep[s] && m->d_pois_S[s] && !getenv("NIMB200_NO_BYPRODUCT") &&
+         !(m->nranks > 1 && m->sweep_sharded[s] && !m->target_sharded[s]);
+}
+static int ensure_pois_ysum(nimb200_model* m, int s) {
+  if (m->pois_ysum_valid[s]) return 0;
+  const nimb200_sampler& sp = m->samplers[s];
+  const int dd = m->deps[sp.dep_off + 1].decl;
+  PoisArgs pa = pois_args(m, dd);
+  k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[dd], m->d_pois_ysum[s]);
+  m->launches++;
+  const bool sh = m->nranks > 1 && m->sweep_sharded[s] && !m->target_sharded[s];
+  if (sh && comm_on(m) && allreduce_sum(m, m->d_pois_ysum[s], (size_t)sp.n_targets * 3)) return 1;
+  m->pois_ysum_valid[s] = 1;
+  return 0;
+}
+// one pass over the nodes: S (or Snew) [t][c] = sum_i exp(b1 x_i) under the b1 values the state holds NOW
+static int launch_pois_S(nimb200_model* m, int s, double* out) {
+  const nimb200_sampler& sp = m->samplers[s];
+  PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
+  const size_t total = (size_t)sp.n_targets * m->C;
+  k_pois_conj_sweep<3><<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(
+      m->T, s, 0, 0, pa, m->d_pois_ysum[s], out, nullptr);
+  m->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
 // evaluate instances [lo,hi) (through idx) of declaration di for all chains; reduced sums land in dst0 (dst1)
 static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, const int32_t* idx, double* dst0, double* dst1,
                            const nimb200_dep* dp, int slot, int gam) {
@@ -1409,6 +1446,37 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     CK(cudaGetLastError());
     if (shard && comm_on(m)) return allreduce_sum(m, dst0, C);
     return 0;
+  }
+  if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && gcount == d.n) {
+    // whole declaration through the group sums: G terms per chain; a pass over the nodes only when the state's b1 is a proposal
+    for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {
+      if (!pois_S_usable(m, s2) || m->deps[m->samplers[s2].dep_off + 1].decl != di) continue;
+      const nimb200_sampler& o = m->samplers[s2];
+      PoisArgs pa = pois_args(m, di);
+      if (ensure_pois_ysum(m, (int)s2)) return 1;
+      const bool b1_proposed = pa.b1_slot >= m->prop_lo && pa.b1_slot < m->prop_hi;
+      const double* Suse = m->d_pois_S[s2];
+      if (b1_proposed) {
+        if (launch_pois_S(m, (int)s2, m->d_pois_Snew[s2])) return 1;
+        m->pois_S_pending[s2] = 1;
+        Suse = m->d_pois_Snew[s2];
+      } else if (!m->pois_S_valid[s2]) {
+        if (launch_pois_S(m, (int)s2, m->d_pois_S[s2])) return 1;
+        m->pois_S_valid[s2] = 1;
+      }
+      const int tdecl = m->deps[o.dep_off].decl;
+      const bool own = m->nranks > 1 && m->target_sharded[s2];
+      const int t_lo = own ? m->shard_lo[tdecl] : 0, t_hi = own ? m->shard_hi[tdecl] : o.n_targets;
+      const int chunks = std::max(1, (std::max(0, t_hi - t_lo) + PS_TPC - 1) / PS_TPC);
+      if ((size_t)chunks * C > m->partials_cap) break;   // fall through to the node kernel
+      k_pois_sum_from_S<<<dim3((C + 31) / 32, chunks), 256, 0, m->stream>>>(m->T, (int)s2, pa, m->d_pois_ysum[s2], Suse, o.n_targets, t_lo, t_hi, m->d_partials);
+      m->launches++;
+      CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
+      m->launches++;
+      CK(cudaGetLastError());
+      if (own && comm_on(m)) return allreduce_sum(m, dst0, C);
+      return 0;
+    }
   }
   if (mode == 0 && d.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[di] && !idx && C >= 32) {
     PoisArgs pa = pois_args(m, di);
@@ -1825,6 +1893,11 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->pois_sweep.assign(m->samplers.size(), 0);
   m->d_pois_ysum.assign(m->samplers.size(), nullptr);
   m->pois_ysum_valid.assign(m->samplers.size(), 0);
+  m->d_pois_S.assign(m->samplers.size(), nullptr);
+  m->d_pois_Snew.assign(m->samplers.size(), nullptr);
+  m->pois_S_valid.assign(m->samplers.size(), 0);
+  m->pois_S_pending.assign(m->samplers.size(), 0);
+  TRY(dev_alloc(m, &m->d_accept, (size_t)nchains));
   m->pois_byp_slot.assign(m->samplers.size(), -1);
   m->d_pois_contrib.assign(m->samplers.size(), nullptr);
   for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -1925,6 +1998,11 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       if (whole && ((int)g < sp.dep_off || (int)g >= sp.dep_off + sp.n_dep)) { m->pois_byp_slot[s] = m->dep_slot[g]; break; }
     }
     if (m->pois_byp_slot[s] >= 0) TRY(dev_alloc(m, &m->d_pois_contrib[s], (size_t)sp.n_targets * C));
+    // same eligibility (targets cover the declaration, small counts) for the group-sum path; two [targets][chains] arrays
+    if (m->pois_byp_slot[s] >= 0 && !getenv("NIMB200_NO_GROUPSUMS") && (size_t)sp.n_targets * C * 16 < ((size_t)8 << 30)) {
+      TRY(dev_alloc(m, &m->d_pois_S[s], (size_t)sp.n_targets * C));
+      TRY(dev_alloc(m, &m->d_pois_Snew[s], (size_t)sp.n_targets * C));
+    }
   }
   // The binary sweep of the occupancy family evaluates, for the state it leaves behind, every node of the sites' own declaration and
   // of the visits' declaration: when its targets cover both declarations it refreshes their cached block sums (fused_bern.cuh).
@@ -1987,6 +2065,7 @@ extern "C" int nimb200_set_values(nimb200_model* m, const double* v) {
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   return 0;
 }
 
@@ -2208,6 +2287,7 @@ static int set_shards(nimb200_model* m, int32_t nranks, int32_t rank, int32_t mi
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
   return 0;
 }
@@ -2397,8 +2477,16 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       // doubles completes the cached block sum
       const bool own = m->nranks > 1 && m->target_sharded[s];
       const bool byp = m->pois_byp_slot[s] >= 0 && (m->nranks <= 1 || (own && comm_on(m)));
-      k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr,
-                                                           byp ? m->d_pois_contrib[s] : nullptr);
+      if (pois_S_usable(m, s)) {   // rate sums from the group sums: exp(b0) S, no node is read
+        if (!m->pois_S_valid[s]) {
+          if (launch_pois_S(m, s, m->d_pois_S[s])) return 1;
+          m->pois_S_valid[s] = 1;
+        }
+        k_pois_conj_sweep<4><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_pois_S[s],
+                                                             byp ? m->d_pois_contrib[s] : nullptr);
+      } else
+        k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr,
+                                                             byp ? m->d_pois_contrib[s] : nullptr);
       m->launches++;
       if (byp) {  // fixed-order sum over the targets -> the cached current-state block sum of the dependent declaration
         const int tdecl = m->deps[sp.dep_off].decl;
@@ -2459,6 +2547,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       else
         k_block_propose<<<(C + 15) / 16, dim3(16, NIMB200_MAX_BLOCK_D), 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
       m->launches++;
+      m->prop_lo = sp.target_slot; m->prop_hi = sp.target_slot + (sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1);  // slots holding a proposal
       for (int e = 0; e < sp.n_dep; e++) {
         const nimb200_dep& dp = m->deps[sp.dep_off + e];
         HostSel hs = host_sel(m, dp, m->h_iarr);
@@ -2466,8 +2555,16 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       }
       int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;
       CK(launch_pdl(k_mh_finish, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
-                                                           m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr));
+                                                           m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr, m->d_accept));
       m->launches++;
+      m->prop_lo = m->prop_hi = -1;
+      for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {  // a proposal that moved b1 of a Poisson family: accepted chains take the new group sums
+        if (!m->pois_S_pending[s2]) continue;
+        const size_t tot = (size_t)m->samplers[s2].n_targets * C;
+        k_pois_S_commit<<<(unsigned)((tot + 255) / 256), 256, 0, m->stream>>>(m->d_pois_S[s2], m->d_pois_Snew[s2], m->d_accept, tot, C);
+        m->launches++;
+        m->pois_S_pending[s2] = 0;
+      }
       if (sp.type == NIMB_SAMPLER_RW_BLOCK && sp.adaptive) {
         m->ran[s]++;
         if (m->ran[s] % sp.adapt_interval == 0) {
@@ -2480,6 +2577,15 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
   }
   for (int g : m->invalidates[s]) m->dep_valid[g] = 0;
   for (int g : refreshed) m->dep_valid[g] = 1;
+  {  // group sums follow b1 only through the wide MH path (proposal pass + commit); any other sampler moving b1 stales them
+    const bool tracked = m->wide[s] && (sp.type == NIMB_SAMPLER_RW || sp.type == NIMB_SAMPLER_RW_BLOCK);
+    const int lo_t = sp.target_slot, hi_t = sp.target_slot + (sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : sp.n_targets);
+    for (size_t s2 = 0; s2 < m->samplers.size() && !tracked; s2++) {
+      if (!m->d_pois_S[s2]) continue;
+      const int b1s = m->decl[m->deps[m->samplers[s2].dep_off + 1].decl].fam_arg[5];
+      if (b1s >= lo_t && b1s < hi_t) m->pois_S_valid[s2] = 0;
+    }
+  }
   for (int e = 0; e < sp.n_dep && !m->lp_valid.empty(); e++) m->lp_valid[m->deps[sp.dep_off + e].decl] = 0;  // these sums have moved on
   CK(cudaGetLastError());
   return 0;
@@ -2515,7 +2621,9 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   }
   // cached block sums survive a `reset = FALSE` continuation: nothing but the samplers has touched the chain state since the
   // last run (set_values / initialize_model / a new shard layout clear them themselves)
-  if (reset) std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+  if (reset) { std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0); std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0); }
+  m->prop_lo = m->prop_hi = -1;
+  std::fill(m->pois_S_pending.begin(), m->pois_S_pending.end(), 0);
   int64_t addrows = (niter - nburnin) / thin;
   if (m->rows + addrows > m->cap) {  // resize(mvSamples, ...), MCMC_build.R:262
     int64_t ncap = m->rows + addrows;
@@ -2545,7 +2653,9 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   const char* genv = getenv("NIMB200_GRAPH");
   const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8 && !m->time_samplers;
   if (m->graph_exec && (!want_graph || m->waic || m->graph_seed != seed)) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
-  std::vector<char> valid_prev;
+  std::vector<char> valid_prev, dep_before;
+  // what decides the launch sequence of an iteration: which cached sums are valid, and which group sums are
+  auto pattern = [&]() { std::vector<char> v = m->dep_valid; v.insert(v.end(), m->pois_S_valid.begin(), m->pois_S_valid.end()); return v; };
   bool capture_failed = false;
   auto adapt_due = [&]() {
     for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -2593,7 +2703,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   for (int64_t it = 1; it <= niter; it++) {
     uint64_t git = (uint64_t)(m->iter_done + it);
     bool due = adapt_due();
-    if (m->graph_exec && !due && m->dep_valid == m->graph_pattern) {
+    if (m->graph_exec && !due && pattern() == m->graph_pattern) {
       CK(cudaGraphLaunch(m->graph_exec, m->stream));
       m->launches += m->graph_launches;
       m->allreduces += m->graph_allreduces;
@@ -2602,8 +2712,9 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       continue;
     }
     // capture once the pattern repeats from one iteration to the next (and an older graph, if any, does not fit it)
-    bool capture = want_graph && !capture_failed && !due && it >= 3 && valid_prev == m->dep_valid;
-    valid_prev = m->dep_valid;
+    bool capture = want_graph && !capture_failed && !due && it >= 3 && valid_prev == pattern();
+    valid_prev = pattern();
+    dep_before = m->dep_valid;
     if (capture) {
       std::vector<int> ran_before = m->ran;
       int64_t l0 = m->launches, a0 = m->allreduces;
@@ -2612,7 +2723,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       bool ok = cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
       if (ok && one_iteration(git)) ok = false;
       if (cudaStreamEndCapture(m->stream, &g) != cudaSuccess || !g) ok = false;
-      if (ok && m->dep_valid != valid_prev) ok = false;  // the cache pattern must repeat for the replay to be valid
+      if (ok && pattern() != valid_prev) ok = false;  // the cache pattern must repeat for the replay to be valid
       if (ok && cudaGraphInstantiate(&m->graph_exec, g, 0) != cudaSuccess) { m->graph_exec = nullptr; ok = false; }
       if (g) cudaGraphDestroy(g);
       m->graph_launches = m->launches - l0;
@@ -2629,7 +2740,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       }
       cudaGetLastError();
       m->ran = ran_before;  // nothing ran: fall back to ordinary launches for good
-      m->dep_valid = valid_prev;
+      m->dep_valid = dep_before;
       if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
       capture_failed = true;
     }
@@ -2794,6 +2905,7 @@ extern "C" int nimb200_initialize_model(nimb200_model* m, const int32_t* decl_or
                         ": only dnorm, dgamma, dbeta, dexp, dlogis, dbin and dpois (mean <= 500) nodes can)");
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   return 0;
 }
 

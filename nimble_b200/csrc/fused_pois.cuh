@@ -197,6 +197,9 @@ __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode*
 // PHASE 0: whole update (contrib, if given, receives each (target, chain)'s share of the dependents' block sum under the new
 // value).  Data-sharded runs: PHASE 1 leaves this rank's share of the rate contribution in part[t][c]
 // (sel_of clamps the target's nodes to the rank's slice), the caller all-reduces it, PHASE 2 draws from the reduced sums.
+// Group sums (round 2): exp(b0 + b1 x) = exp(b0) exp(b1 x), so  S[t][c] = sum_i exp(b1 x_i)  over a target's nodes depends on b1
+// alone.  PHASE 3 computes just that (part = S; the one pass over the nodes that an iteration still needs, when b1 moves);
+// PHASE 4 is the whole update from a valid S (c1 = exp(b0) S: no node is read).
 template <int PHASE>
 __global__ void __launch_bounds__(PF_THREADS)
 k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part,
@@ -210,12 +213,13 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   size_t tq = gid / T.C;
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
-  if (PHASE == 0) {  // targets sharded by ownership (group-aligned shards): the owner alone updates a target
+  if (PHASE == 0 || PHASE == 3 || PHASE == 4) {  // targets sharded by ownership (group-aligned shards): the owner alone updates a target
     const nimb200_dep tp0 = T.deps[sp.dep_off];
     const int tn = (tp0.sel == NIMB_SEL_SAME ? tp0.a + t : tp0.a);
     if (tn < T.shard_lo[tp0.decl] || tn >= T.shard_hi[tp0.decl]) return;
   }
-  const double b0 = T.state[(size_t)a.b0_slot * T.C + c], b1 = T.state[(size_t)a.b1_slot * T.C + c];
+  const double b0s = T.state[(size_t)a.b0_slot * T.C + c], b1 = T.state[(size_t)a.b1_slot * T.C + c];
+  const double b0 = PHASE == 3 ? 0.0 : b0s;
   const nimb200_dep dp = T.deps[sp.dep_off + 1];
   Sel s = sel_of(T, dp, t);
   double K[7];
@@ -240,6 +244,11 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   unsigned worst = 0;
   int k = s.lo;
   if (PHASE == 2) { k = s.hi; c1 = part[(size_t)t * T.C + c]; }
+  if (PHASE == 4) {  // regular chains: exp(b0) S; anything else (|b0| >= 300, S marked NaN by PHASE 3) walks the nodes below
+    const double Sg = part[(size_t)t * T.C + c];
+    if (fabs(b0) < 300.0 && isfinite(Sg)) { k = s.hi; c1 = exp(b0) * Sg; }
+    else { k = s.hi; worst = 0x7ff00000u; }
+  }
   for (; k + 1 < s.hi; k += 2) {
     const int n0 = s.idx ? s.idx[k] : k, n1 = s.idx ? s.idx[k + 1] : k + 1;
     const double x0 = a.x[n0], x1 = a.x[n1];
@@ -248,13 +257,16 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   }
   if (k < s.hi) c1 += expf(fma(b1, a.x[s.idx ? s.idx[k] : k], b0), worst);
   c1 += c1b;
-  if (worst >= 0x4085e000u) {  // |eta| >= 700 or NaN somewhere: redo with the library exp
+  if (PHASE != 2 && worst >= 0x4085e000u) {  // |eta| >= 700 or NaN somewhere: redo with the library exp
     c1 = 0.0;
     for (int kk = s.lo; kk < s.hi; kk++) {
       int node = s.idx ? s.idx[kk] : kk;
       c1 += 1.0 * exp(b0 + b1 * a.x[node]);
     }
   }
+  // PHASE 3: a group whose |b1 x| reaches 300 is marked NaN -- its users then take their exact per-node paths, because
+  // exp(b0) exp(b1 x) and exp(b0 + b1 x) part ways once either factor over- or underflows
+  if (PHASE == 3) { part[(size_t)t * T.C + c] = worst >= 0x4072c000u ? NAN : c1; return; }
   if (PHASE == 1) { part[(size_t)t * T.C + c] = c1; return; }
   const double c0 = ysum[t];
   const nimb200_dep tp = T.deps[sp.dep_off];
@@ -265,7 +277,7 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   double shape = prior_shape + c0, scale = 1 / (prior_rate + c1);
   const double nl = rgamma1(key, shape) * scale;
   T.state[(size_t)(sp.target_slot + t) * T.C + c] = nl;
-  if (PHASE == 0 && contrib) {
+  if ((PHASE == 0 || PHASE == 4) && contrib) {
     // by-product: the group's share of the dependents' block log-density under the value just drawn,
     //   sum_i [A_i + y_i (log lam + b0 + b1 x_i) - lam exp(b0 + b1 x_i)] = SA + Sy (log lam + b0) + b1 Sxy - lam c1,
     // so that the next MH step on this declaration finds its current-state sum without another pass over the nodes
@@ -275,6 +287,58 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
     else v = ((sa + c0 * (log(nl) + b0)) + b1 * sxy) - nl * c1;
     contrib[(size_t)t * T.C + c] = v;
   }
+}
+
+// Whole-declaration block sum from the data-only group sums (ysum = [sum y | sum A | sum x y] per target) and S:
+//   sum_i [A_i + y_i (log lam_g + b0 + b1 x_i) - lam_g exp(b0) exp(b1 x_i)]
+//     = sum_g [ SA_g + Sy_g (log lam_g + b0) + b1 Sxy_g - lam_g exp(b0) S_g ].
+// grid (chain tiles of 32, target chunks), lane = chain, the 8 warps of a block stride over the chunk's targets;
+// partials[chunk][C].  lam = 0 reproduces dpois(y, 0) (0 if the group's counts are all zero, -Inf otherwise); lam < 0 or NaN
+// gives NaN as the generic path does.
+static const int PS_TPC = 256;   // targets per chunk
+__global__ void __launch_bounds__(256)
+k_pois_sum_from_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ ysum, const double* __restrict__ S, int nT, int t_lo,
+                  int t_hi, double* __restrict__ partials) {
+  __shared__ double red[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int cc = c < T.C ? c : T.C - 1;
+  const size_t C = (size_t)T.C;
+  const double b0 = T.state[(size_t)a.b0_slot * C + cc], b1 = T.state[(size_t)a.b1_slot * C + cc];
+  const double eb0 = exp(b0);
+  const double* __restrict__ lamp = T.state + (size_t)a.lam_slot * C + cc;
+  const int lo = t_lo + blockIdx.y * PS_TPC, hi = min(t_hi, lo + PS_TPC);
+  double acc = 0.0;
+  for (int t = lo + warp; t < hi; t += 8) {
+    const double sy = ysum[t], sa = ysum[(size_t)nT + t], sxy = ysum[2 * (size_t)nT + t];
+    const double lam = lamp[(size_t)t * C], Sg = S[(size_t)t * C + cc];
+    double v;
+    if (!(fabs(b0) < 300.0) || !isfinite(Sg) || !(lam > 0.0 && lam < 1e300)) {
+      // irregular (target, chain): node by node through the generic density, as the node kernel's exact path does
+      const nimb200_sampler sp = T.samplers[sid];
+      Sel sl = sel_of(T, T.deps[sp.dep_off + 1], t);
+      v = 0.0;
+      for (int k = sl.lo; k < sl.hi; k++) {
+        const int node = sl.idx ? sl.idx[k] : k;
+        v += dpois(a.y[node], lam * exp(fma(b1, a.x[node], b0)));
+      }
+    } else v = ((sa + sy * (log(lam) + b0)) + b1 * sxy) - lam * (eb0 * Sg);
+    acc += v;
+  }
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < T.C) {
+    double s = 0.0;
+    for (int w = 0; w < 8; w++) s += red[w][lane];
+    partials[(size_t)blockIdx.y * C + c] = s;
+  }
+}
+
+// after the MH decision on a proposal that moved b1: the accepted chains take the proposed group sums
+__global__ void k_pois_S_commit(double* __restrict__ S, const double* __restrict__ Snew, const int* __restrict__ accept, size_t total, int C) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  if (accept[i % C]) S[i] = Snew[i];
 }
 
 }  // namespace nimb
