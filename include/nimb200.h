@@ -265,6 +265,11 @@ int nimb200_mcmc_run(nimb200_model *m, int64_t niter, int64_t nburnin, int32_t t
 /* as.matrix(mvSamples) for every chain: out[c][row][col], rows = saved samples, cols = monitors
  * (types_util.R:199-214).  *nrows_out receives the row count; out may be NULL to query it. */
 int nimb200_mcmc_samples(nimb200_model *m, double *out, int64_t *nrows_out);
+/* samplesSummary(samples) (P/R/MCMC_utils.R:315-341) computed on the device, without reading mvSamples back: out[5][n_monitors] =
+ * Mean, Median, St.Dev., 95%CI_low, 95%CI_upp of every monitored column over all saved rows of the chains [chain_lo, chain_hi)
+ * pooled (one chain: that chain's summary; all chains: runMCMC's `all.chains`).  Quantiles are exact order statistics with R's
+ * default (type 7) interpolation. */
+int nimb200_samples_summary(nimb200_model *m, int32_t chain_lo, int32_t chain_hi, double *out);
 /* device-side time of the last nimb200_mcmc_run in milliseconds (CUDA events on the run stream),
  * and how many kernels it launched. */
 int nimb200_mcmc_last_timing(nimb200_model *m, double *ms_out, int64_t *launches_out);

@@ -63,6 +63,7 @@ class Backend:
                                    C.c_int32, _dp])
         if has_device:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
+            self._summary = fn("samples_summary", [vp, C.c_int32, C.c_int32, _dp])
             self._set_timing = fn("mcmc_set_timing", [vp, C.c_int32])
             self._sampler_times = fn("mcmc_sampler_times", [vp, _dp, C.c_int32])
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
@@ -198,6 +199,12 @@ class DeviceModel:
         out = np.empty((self.C, n.value, self.n_mon))
         if out.size:
             self.backend.check(self.backend._samples(self.h, _ptr(out), C.byref(n)))
+        return out
+
+    def samples_summary(self, chain_lo=0, chain_hi=None):
+        """samplesSummary on the device: array [5][n_monitors] = Mean, Median, St.Dev., 95%CI_low, 95%CI_upp (chains pooled)."""
+        out = np.empty((5, self.n_mon))
+        self.backend.check(self.backend._summary(self.h, chain_lo, self.C if chain_hi is None else chain_hi, _ptr(out)))
         return out
 
     def sampler_state(self, sampler, what):

@@ -2782,6 +2782,202 @@ extern "C" int nimb200_mcmc_samples(nimb200_model* m, double* out, int64_t* nrow
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ samplesSummary on the device
+// samplesSummary (P/R/MCMC_utils.R:315-341): Mean, Median, St.Dev., 2.5 % and 97.5 % quantiles of every monitored column, over
+// the rows of the chains [chain_lo, chain_hi) pooled -- without bringing mvSamples to the host.  Exact order statistics by
+// radix selection on order-preserving 64-bit keys (six passes of 12 bits, one shared-memory histogram per column block and
+// wanted rank), quantiles by R's default (type 7) interpolation; moments by fixed-order two-stage sums.
+static const int SUM_RANKS = 3;                 // ranks floor((n-1) p) for p = 0.025, 0.5, 0.975
+static const int SUM_BINS = 4096;
+__device__ __forceinline__ unsigned long long ord_key(double x) {
+  unsigned long long u = (unsigned long long)__double_as_longlong(x);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__host__ __device__ inline double ord_unkey(unsigned long long k) {
+  unsigned long long u = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+  double d;
+  memcpy(&d, &u, sizeof d);
+  return d;
+}
+// element e of a column's pooled sample: row e / nc, chain c_lo + e % nc;  samples[row][col][chain]
+struct SumView { const double* s; long long rows; int nmon, C, c_lo, nc; };
+__device__ __forceinline__ double sum_elem(const SumView& v, int col, long long e) {
+  const long long row = e / v.nc;
+  const int c = v.c_lo + (int)(e % v.nc);
+  return v.s[((size_t)row * v.nmon + col) * v.C + c];
+}
+// grid (chunks, columns): pass = 0: sum; pass = 1: sum of squared deviations from mean[col].  partial[chunk][col]
+__global__ void k_sum_moments(SumView v, int pass, const double* __restrict__ mean, double* __restrict__ partial) {
+  __shared__ double red[8];
+  const int col = blockIdx.y;
+  const long long n = v.rows * v.nc, per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = blockIdx.x * per, hi = min(n, lo + per);
+  const double mu = pass ? mean[col] : 0.0;
+  double acc = 0.0;
+  for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
+    const double x = sum_elem(v, col, e) - mu;
+    acc += pass ? x * x : x;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += red[w];
+    partial[(size_t)blockIdx.x * gridDim.y + col] = t;
+  }
+}
+// one 12-bit digit of the radix selection: for each wanted rank r of the column, count the elements whose key agrees with
+// prefix[col][r] above bit (shift + 12) by their digit at `shift`.  hist[col][r][bin]
+__global__ void k_sum_hist(SumView v, int shift, int cmp_shift, unsigned int mask, int first, const unsigned long long* __restrict__ prefix,
+                           unsigned int* __restrict__ hist) {
+  extern __shared__ unsigned int sum_sh[];   // [SUM_RANKS][SUM_BINS]
+  unsigned int* sh = sum_sh;
+  for (int i = threadIdx.x; i < SUM_RANKS * SUM_BINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const int col = blockIdx.y;
+  const long long n = v.rows * v.nc, per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = blockIdx.x * per, hi = min(n, lo + per);
+  unsigned long long pf[SUM_RANKS];
+#pragma unroll
+  for (int r = 0; r < SUM_RANKS; r++) pf[r] = prefix[(size_t)col * SUM_RANKS + r];
+  for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
+    const unsigned long long k = ord_key(sum_elem(v, col, e));
+    const unsigned int bin = (unsigned int)(k >> shift) & mask;
+#pragma unroll
+    for (int r = 0; r < SUM_RANKS; r++)
+      if (first || (k >> cmp_shift) == (pf[r] >> cmp_shift)) atomicAdd(&sh[r * SUM_BINS + bin], 1u);
+  }
+  __syncthreads();
+  unsigned int* g = hist + (size_t)col * SUM_RANKS * SUM_BINS;
+  for (int i = threadIdx.x; i < SUM_RANKS * SUM_BINS; i += blockDim.x)
+    if (sh[i]) atomicAdd(&g[i], sh[i]);
+}
+// for each (column, rank): how many elements are <= the selected value, and the smallest key above it (the next order statistic)
+__global__ void k_sum_next(SumView v, const unsigned long long* __restrict__ sel, unsigned long long* __restrict__ count_le,
+                           unsigned long long* __restrict__ min_gt) {
+  const int col = blockIdx.y;
+  const long long n = v.rows * v.nc, per = (n + gridDim.x - 1) / gridDim.x;
+  const long long lo = blockIdx.x * per, hi = min(n, lo + per);
+  unsigned long long sk[SUM_RANKS], cnt[SUM_RANKS], mg[SUM_RANKS];
+#pragma unroll
+  for (int r = 0; r < SUM_RANKS; r++) { sk[r] = sel[(size_t)col * SUM_RANKS + r]; cnt[r] = 0; mg[r] = ~0ull; }
+  for (long long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
+    const unsigned long long k = ord_key(sum_elem(v, col, e));
+#pragma unroll
+    for (int r = 0; r < SUM_RANKS; r++) { if (k <= sk[r]) cnt[r]++; else mg[r] = min(mg[r], k); }
+  }
+#pragma unroll
+  for (int r = 0; r < SUM_RANKS; r++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      cnt[r] += __shfl_xor_sync(0xffffffffu, cnt[r], o);
+      mg[r] = min(mg[r], __shfl_xor_sync(0xffffffffu, mg[r], o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicAdd(&count_le[(size_t)col * SUM_RANKS + r], cnt[r]);
+      atomicMin(&min_gt[(size_t)col * SUM_RANKS + r], mg[r]);
+    }
+  }
+}
+
+extern "C" int nimb200_samples_summary(nimb200_model* m, int32_t chain_lo, int32_t chain_hi, double* out) {
+  if (!m || !out) return fail("null argument");
+  if (chain_lo < 0 || chain_hi > m->C || chain_lo >= chain_hi) return fail("bad chain range");
+  CK(cudaSetDevice(m->device));
+  const int nmon = (int)m->monitors.size();
+  const long long n = (long long)m->rows * (chain_hi - chain_lo);
+  if (nmon == 0) return 0;
+  if (n < 1) return fail("samplesSummary: no samples");
+  SumView v{m->d_samples, (long long)m->rows, nmon, m->C, chain_lo, chain_hi - chain_lo};
+  const int chunks = (int)std::max<long long>(1, std::min<long long>(64, n / 4096 + 1));
+  const size_t NR = (size_t)nmon * SUM_RANKS;
+  double *d_part = nullptr, *d_mean = nullptr;
+  unsigned long long *d_prefix = nullptr, *d_cnt = nullptr, *d_min = nullptr;
+  unsigned int* d_hist = nullptr;
+  cudaError_t e = cudaSuccess;
+  auto ck = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
+  ck(cudaMalloc(&d_part, sizeof(double) * (size_t)chunks * nmon));
+  ck(cudaMalloc(&d_mean, sizeof(double) * nmon));
+  ck(cudaMalloc(&d_prefix, sizeof(unsigned long long) * NR));
+  ck(cudaMalloc(&d_cnt, sizeof(unsigned long long) * NR));
+  ck(cudaMalloc(&d_min, sizeof(unsigned long long) * NR));
+  ck(cudaMalloc(&d_hist, sizeof(unsigned int) * NR * SUM_BINS));
+  std::vector<double> part((size_t)chunks * nmon), mean(nmon), sd(nmon);
+  std::vector<unsigned long long> prefix(NR, 0), want(NR), cnt(NR), mn(NR);
+  std::vector<unsigned int> hist(NR * SUM_BINS);
+  const double ps[SUM_RANKS] = {0.025, 0.5, 0.975};
+  if (e == cudaSuccess) {
+    // moments: fixed-order partial sums, finished on the host in chunk order
+    for (int pass = 0; pass < 2 && e == cudaSuccess; pass++) {
+      k_sum_moments<<<dim3(chunks, nmon), 256, 0, m->stream>>>(v, pass, d_mean, d_part);
+      ck(cudaMemcpyAsync(part.data(), d_part, sizeof(double) * part.size(), cudaMemcpyDeviceToHost, m->stream));
+      ck(cudaStreamSynchronize(m->stream));
+      for (int j = 0; j < nmon; j++) {
+        double t = 0.0;
+        for (int b = 0; b < chunks; b++) t += part[(size_t)b * nmon + j];
+        if (pass == 0) mean[j] = t / (double)n; else sd[j] = n > 1 ? std::sqrt(t / (double)(n - 1)) : NAN;
+      }
+      if (pass == 0) ck(cudaMemcpyAsync(d_mean, mean.data(), sizeof(double) * nmon, cudaMemcpyHostToDevice, m->stream));
+    }
+    // order statistics floor((n-1) p): radix selection, most significant digit first (digits at bits 52, 40, 28, 16, 4; then the low 4 bits)
+    for (size_t q = 0; q < NR; q++) want[q] = (unsigned long long)std::floor((double)(n - 1) * ps[q % SUM_RANKS]);
+    const int shifts[6] = {52, 40, 28, 16, 4, 0};   // five 12-bit digits, then the low 4 bits
+    for (int ps_ = 0; ps_ < 6 && e == cudaSuccess; ps_++) {
+      const int shift = shifts[ps_];
+      const bool last = ps_ == 5;
+      ck(cudaMemsetAsync(d_hist, 0, sizeof(unsigned int) * hist.size(), m->stream));
+      ck(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(unsigned long long) * NR, cudaMemcpyHostToDevice, m->stream));
+      k_sum_hist<<<dim3(chunks, nmon), 256, sizeof(unsigned int) * SUM_RANKS * SUM_BINS, m->stream>>>(
+          v, shift, last ? 4 : (ps_ == 0 ? 63 : shift + 12), last ? 15u : (unsigned)(SUM_BINS - 1), ps_ == 0, d_prefix, d_hist);
+      ck(cudaGetLastError());
+      ck(cudaMemcpyAsync(hist.data(), d_hist, sizeof(unsigned int) * hist.size(), cudaMemcpyDeviceToHost, m->stream));
+      ck(cudaStreamSynchronize(m->stream));
+      for (size_t q = 0; q < NR && e == cudaSuccess; q++) {
+        const unsigned int* h = hist.data() + q * SUM_BINS;
+        unsigned long long acc = 0;
+        int bin = 0;
+        for (; bin < SUM_BINS; bin++) { if (acc + h[bin] > want[q]) break; acc += h[bin]; }
+        if (bin == SUM_BINS) bin = SUM_BINS - 1;
+        want[q] -= acc;
+        prefix[q] |= (unsigned long long)bin << shift;
+      }
+    }
+    // the next order statistic above each selected value (type-7 interpolation needs ranks lo and lo + 1)
+    std::fill(cnt.begin(), cnt.end(), 0ull);
+    std::fill(mn.begin(), mn.end(), ~0ull);
+    ck(cudaMemcpyAsync(d_prefix, prefix.data(), sizeof(unsigned long long) * NR, cudaMemcpyHostToDevice, m->stream));
+    ck(cudaMemcpyAsync(d_cnt, cnt.data(), sizeof(unsigned long long) * NR, cudaMemcpyHostToDevice, m->stream));
+    ck(cudaMemcpyAsync(d_min, mn.data(), sizeof(unsigned long long) * NR, cudaMemcpyHostToDevice, m->stream));
+    k_sum_next<<<dim3(chunks, nmon), 256, 0, m->stream>>>(v, d_prefix, d_cnt, d_min);
+    ck(cudaGetLastError());
+    ck(cudaMemcpyAsync(cnt.data(), d_cnt, sizeof(unsigned long long) * NR, cudaMemcpyDeviceToHost, m->stream));
+    ck(cudaMemcpyAsync(mn.data(), d_min, sizeof(unsigned long long) * NR, cudaMemcpyDeviceToHost, m->stream));
+    ck(cudaStreamSynchronize(m->stream));
+  }
+  cudaFree(d_part); cudaFree(d_mean); cudaFree(d_prefix); cudaFree(d_cnt); cudaFree(d_min); cudaFree(d_hist);
+  if (e != cudaSuccess) return fail(std::string("CUDA error ") + cudaGetErrorString(e));
+  for (int j = 0; j < nmon; j++) {
+    double qv[SUM_RANKS];
+    for (int r = 0; r < SUM_RANKS; r++) {
+      const size_t q = (size_t)j * SUM_RANKS + r;
+      const double h = (double)(n - 1) * ps[r];
+      const long long lo = (long long)std::floor(h);
+      const double xlo = ord_unkey(prefix[q]);
+      // rank lo + 1: the same value when duplicates reach past rank lo, else the smallest larger element
+      const double xhi = (cnt[q] > (unsigned long long)(lo + 1) || mn[q] == ~0ull) ? xlo : ord_unkey(mn[q]);
+      qv[r] = xlo + (h - (double)lo) * (xhi - xlo);
+    }
+    out[0 * (size_t)nmon + j] = mean[j];
+    out[1 * (size_t)nmon + j] = qv[1];
+    out[2 * (size_t)nmon + j] = sd[j];
+    out[3 * (size_t)nmon + j] = qv[0];
+    out[4 * (size_t)nmon + j] = qv[2];
+  }
+  return 0;
+}
+
 extern "C" int nimb200_mcmc_last_allreduces(nimb200_model* m, int64_t* count_out, int32_t* graph_replayed_out) {
   if (!m) return fail("null model");
   if (count_out) *count_out = m->allreduces;

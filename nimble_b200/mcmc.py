@@ -1086,7 +1086,13 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
     if has2:  # MCMC_run.R:145-151, 183-207: a second list of matrices, `samples2`
         mats2 = [SampleMatrix(mcmc.mvSamples2[c], mcmc.colnames2) for c in range(nchains)]
         ret["samples2"] = mats2[0] if nchains == 1 else {"chain%d" % (c + 1): mats2[c] for c in range(nchains)}
-    if summary:
+    if summary and not has2 and mcmc.backend.has_device:
+        # samplesSummary on the device (nimb200_samples_summary): nothing but 5 numbers per column crosses the bus;
+        # all chains pooled, as the `all.chains` entry of the reference's summary (MCMC_run.R:196-207)
+        tab = mcmc.dm.samples_summary()
+        keys = ("Mean", "Median", "St.Dev.", "95%CI_low", "95%CI_upp")
+        ret["summary"] = {name: {k: float(tab[i, j]) for i, k in enumerate(keys)} for j, name in enumerate(mcmc.colnames)}
+    elif summary:
         from .ess import samples_summary
         summ = samples_summary(np.concatenate(mats, axis=0), mcmc.colnames)
         if has2:

@@ -319,3 +319,31 @@ def test_captured_iteration_is_replayed_by_continuation_runs(b200):
     fresh = compile_on(b200, conf)
     run(fresh, inits, 30, 0, seed=6)
     assert np.array_equal(cm.dm.samples(), fresh.dm.samples())
+
+
+def test_samples_summary_on_device_equals_numpy(b200):
+    """samplesSummary (P/R/MCMC_utils.R:315-341) computed on the device -- exact order statistics by radix selection, type-7
+    quantiles, two-stage moments -- against numpy on the samples read back: per chain, pooled, with ties (a binary column)
+    and with very few rows."""
+    m, conf = sm.binary_model()
+    cm = compile_on(b200, conf)
+    run(cm, np.tile(m.init_vector(), (5, 1)), 400, 0, seed=2)
+    s = cm.dm.samples()
+    for lo, hi in ((0, 5), (2, 3)):
+        want = s[lo:hi].reshape(-1, s.shape[-1])
+        got = cm.dm.samples_summary(lo, hi)
+        ref = np.stack([want.mean(0), np.median(want, 0), want.std(0, ddof=1), np.quantile(want, 0.025, 0), np.quantile(want, 0.975, 0)])
+        np.testing.assert_allclose(got, ref, rtol=1e-12, atol=1e-14)
+    m, conf = sm.SMALL["lmm"]()
+    conf.addMonitors("u")
+    cm = compile_on(b200, conf)
+    for niter in (3, 257):
+        run(cm, sm.random_inits(m, 9, 1, 0.1), niter, 0, seed=4)
+        s = cm.dm.samples()
+        want = s.reshape(-1, s.shape[-1])
+        got = cm.dm.samples_summary()
+        ref = np.stack([want.mean(0), np.median(want, 0), want.std(0, ddof=1), np.quantile(want, 0.025, 0), np.quantile(want, 0.975, 0)])
+        np.testing.assert_allclose(got, ref, rtol=1e-11, atol=1e-13)
+    out = nb.runMCMC(cm, niter=50, nchains=3, setSeed=1, summary=True)
+    pooled = np.concatenate([np.asarray(out["samples"]["chain%d" % k]) for k in (1, 2, 3)])
+    assert abs(out["summary"]["mu"]["Median"] - np.median(pooled[:, cm.colnames.index("mu")])) < 1e-12
