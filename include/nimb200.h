@@ -265,6 +265,13 @@ int nimb200_mcmc_run(nimb200_model *m, int64_t niter, int64_t nburnin, int32_t t
 /* as.matrix(mvSamples) for every chain: out[c][row][col], rows = saved samples, cols = monitors
  * (types_util.R:199-214).  *nrows_out receives the row count; out may be NULL to query it. */
 int nimb200_mcmc_samples(nimb200_model *m, double *out, int64_t *nrows_out);
+/* nimbleOptions(MCMCsaveHistory = TRUE) (P/R/MCMC_samplers.R:394-399, 726-739; getScaleHistory / getAcceptanceHistory /
+ * getPropCovHistory :421-448, 775-780): once enabled, every adaptation of every RW / RW_block sampler records the scale it used,
+ * the interval's acceptance rate and -- RW_block with d <= 10 (maxDimCovHistory) -- the proposal covariance it used, for up to
+ * max_adaptations adaptations since the last reset.  history(): what = 0 scaleHistory, 1 acceptanceHistory -> out[adaptation][T][C];
+ * 2 propCovHistory -> out[adaptation][d*d][C]; *n_adapt_out = adaptations recorded (out may be NULL to query it). */
+int nimb200_sampler_history_enable(nimb200_model *m, int32_t max_adaptations);
+int nimb200_sampler_history(nimb200_model *m, int32_t sampler, int32_t what, double *out, int64_t cap, int32_t *n_adapt_out);
 /* samplesSummary(samples) (P/R/MCMC_utils.R:315-341) computed on the device, without reading mvSamples back: out[5][n_monitors] =
  * Mean, Median, St.Dev., 95%CI_low, 95%CI_upp of every monitored column over all saved rows of the chains [chain_lo, chain_hi)
  * pooled (one chain: that chain's summary; all chains: runMCMC's `all.chains`).  Quantiles are exact order statistics with R's

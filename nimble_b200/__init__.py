@@ -5,9 +5,9 @@ nimbleCode / nimbleModel / configureMCMC / buildMCMC / compileNimble / runMCMC; 
 CUDA library nimble_b200/libnimb200.so behind the C ABI of include/nimb200.h."""
 from .model import Model, ModelError, nimbleCode, nimbleModel
 from .mcmc import (MCMCconf, CompiledMCMC, SampleMatrix, buildMCMC, check_conjugacy, compileNimble, configureMCMC,
-                   runMCMC)
+                   nimbleOptions, runMCMC)
 from .ess import effective_size, min_ess, samples_summary
 
 __all__ = ["Model", "ModelError", "nimbleCode", "nimbleModel", "MCMCconf", "CompiledMCMC", "SampleMatrix",
-           "buildMCMC", "check_conjugacy", "compileNimble", "configureMCMC", "runMCMC", "effective_size", "min_ess",
+           "buildMCMC", "check_conjugacy", "compileNimble", "configureMCMC", "runMCMC", "nimbleOptions", "effective_size", "min_ess",
            "samples_summary"]

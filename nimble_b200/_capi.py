@@ -64,6 +64,8 @@ class Backend:
         if has_device:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
             self._summary = fn("samples_summary", [vp, C.c_int32, C.c_int32, _dp])
+            self._hist_enable = fn("sampler_history_enable", [vp, C.c_int32])
+            self._hist = fn("sampler_history", [vp, C.c_int32, C.c_int32, _dp, C.c_int64, C.POINTER(C.c_int32)])
             self._set_timing = fn("mcmc_set_timing", [vp, C.c_int32])
             self._sampler_times = fn("mcmc_sampler_times", [vp, _dp, C.c_int32])
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
@@ -199,6 +201,21 @@ class DeviceModel:
         out = np.empty((self.C, n.value, self.n_mon))
         if out.size:
             self.backend.check(self.backend._samples(self.h, _ptr(out), C.byref(n)))
+        return out
+
+    def history_enable(self, max_adaptations=1024):
+        self.backend.check(self.backend._hist_enable(self.h, int(max_adaptations)))
+
+    def sampler_history(self, sampler, what):
+        """what 0 scaleHistory / 1 acceptanceHistory: [adaptations][T][C]; 2 propCovHistory: [adaptations][d*d][C]."""
+        n = C.c_int32()
+        self.backend.check(self.backend._hist(self.h, sampler, what, None, 0, C.byref(n)))
+        s = self.builder.samplers[sampler]
+        Tn = 1 if s.type == T.SAMPLER_RW_BLOCK else s.n_targets
+        inner = s.d * s.d if what == 2 else Tn
+        out = np.empty((n.value, inner, self.C))
+        if out.size:
+            self.backend.check(self.backend._hist(self.h, sampler, what, _ptr(out), out.size, C.byref(n)))
         return out
 
     def samples_summary(self, chain_lo=0, chain_hi=None):

@@ -290,12 +290,17 @@ __device__ __forceinline__ bool decide(double lMHr, const DrawKey& k, uint32_t c
 }
 
 // sampler_RW::adaptiveProcedure, P/R/MCMC_samplers.R:388-420
-__device__ __forceinline__ void rw_adapt(const nimb200_sampler& sp, const SamplerDev& S, size_t q, bool jump) {
+__device__ __forceinline__ void rw_adapt(const nimb200_sampler& sp, const SamplerDev& S, size_t q, bool jump, int gridDimC) {
   int ran = S.timesRan[q] + 1, acc = S.timesAccepted[q] + (jump ? 1 : 0);
   if (ran % sp.adapt_interval == 0) {
     double acceptanceRate = (double)acc / (double)ran;
     int adapted = S.timesAdapted[q] + 1;
     S.timesAdapted[q] = adapted;
+    if (S.hist && adapted <= S.hist_cap) {  // scaleHistory / acceptanceHistory, MCMC_samplers.R:394-399
+      const size_t TC = (size_t)sp.n_targets * gridDimC;
+      S.hist[((size_t)(adapted - 1) * S.hist_K + 0) * TC + q] = S.scale[q];
+      S.hist[((size_t)(adapted - 1) * S.hist_K + 1) * TC + q] = acceptanceRate;
+    }
     double gamma1 = 1 / pow((double)adapted + 3, sp.adapt_factor_exponent);
     double gamma2 = 10 * gamma1;
     double adaptFactor = exp(gamma2 * (acceptanceRate - 0.44));
@@ -410,7 +415,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
     if (v0 == -INFINITY) jump = false;
     else jump = decide(v0 + v1 + propLogScale, key, 1);
     if (jump) *sv = prop;
-    if (sp.adaptive) rw_adapt(sp, S, q, jump);
+    if (sp.adaptive) rw_adapt(sp, S, q, jump, T.C);
     return;
   }
   if (sp.type == NIMB_SAMPLER_BINARY) {  // MCMC_samplers.R:127-151
@@ -792,7 +797,7 @@ __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int
     for (int j = 0; j < d; j++) T.state[(size_t)(sp.target_slot + j) * T.C + c] = tsave[(size_t)j * T.C + c];
   }
   if (!sp.adaptive) return;
-  if (sp.type == NIMB_SAMPLER_RW) { rw_adapt(sp, S, c, jump); return; }
+  if (sp.type == NIMB_SAMPLER_RW) { rw_adapt(sp, S, c, jump, T.C); return; }
   // RW_block adaptiveProcedure, first half (MCMC_samplers.R:716-722); the covariance step is k_block_adapt
   int ran = S.timesRan[c] + 1;
   S.timesRan[c] = ran;
@@ -807,6 +812,7 @@ __global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int
 __global__ void k_block_adapt(DevTab T, int sid, SamplerDev S) {
   __shared__ double U[NIMB200_MAX_BLOCK_D * NIMB200_MAX_BLOCK_D];  // propCov, overwritten in place by its upper factor
   __shared__ double s_gamma1, s_scale, s_diag;
+  __shared__ int s_adapted;
   const nimb200_sampler sp = T.samplers[sid];
   int c = blockIdx.x, d = sp.d, AI = sp.adapt_interval, C = T.C;
   int tid = threadIdx.x, nt = blockDim.x;
@@ -816,6 +822,11 @@ __global__ void k_block_adapt(DevTab T, int sid, SamplerDev S) {
     double acceptanceRate = (double)S.timesAccepted[c] / (double)ran;
     int adapted = S.timesAdapted[c] + 1;
     S.timesAdapted[c] = adapted;
+    s_adapted = adapted;
+    if (S.hist && adapted <= S.hist_cap) {  // MCMC_samplers.R:726-739
+      S.hist[((size_t)(adapted - 1) * S.hist_K + 0) * C + c] = S.scale[c];
+      S.hist[((size_t)(adapted - 1) * S.hist_K + 1) * C + c] = acceptanceRate;
+    }
     double gamma1 = 1 / pow((double)adapted + 3, sp.adapt_factor_exponent);
     double adaptFactor = exp(10 * gamma1 * (acceptanceRate - optAR[d > 5 ? 4 : d - 1]));
     s_gamma1 = gamma1;
@@ -823,6 +834,8 @@ __global__ void k_block_adapt(DevTab T, int sid, SamplerDev S) {
     S.scale[c] = s_scale;
   }
   __syncthreads();
+  if (S.hist && S.hist_K > 2 && s_adapted <= S.hist_cap)   // propCovHistory: the covariance this interval's proposals were drawn with
+    for (int e = tid; e < d * d; e += nt) S.hist[((size_t)(s_adapted - 1) * S.hist_K + 2 + e) * C + c] = S.propCov[(size_t)e * C + c];
   if (!sp.adapt_scale_only) {
     for (int j = tid; j < d; j += nt) {  // centre the columns of empirSamp
       double mu = 0;
@@ -1872,6 +1885,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     TRY(dev_alloc(m, &S.timesAccepted, (size_t)TT * C));
     TRY(dev_alloc(m, &S.timesAdapted, (size_t)TT * C));
     S.propCov = S.chol = S.cholScale = S.empirSamp = nullptr;
+    S.hist = nullptr; S.hist_cap = 0; S.hist_K = 0;
     if (sp.type == NIMB_SAMPLER_RW_BLOCK) {
       size_t dd = (size_t)sp.d * sp.d;
       TRY(dev_alloc(m, &S.propCov, dd * C));
@@ -2880,6 +2894,53 @@ __global__ void k_sum_next(SumView v, const unsigned long long* __restrict__ sel
       atomicMin(&min_gt[(size_t)col * SUM_RANKS + r], mg[r]);
     }
   }
+}
+
+// MCMCsaveHistory (nimbleOptions(MCMCsaveHistory = TRUE); P/R/MCMC_samplers.R:394-399, 726-739, getScaleHistory :421-448): once
+// enabled, every adaptation of every RW / RW_block sampler records the scale it used, the interval's acceptance rate and (RW_block,
+// d <= 10 = maxDimCovHistory) the proposal covariance it used, for up to max_adaptations adaptations since the last reset.
+extern "C" int nimb200_sampler_history_enable(nimb200_model* m, int32_t max_adaptations) {
+  if (!m || max_adaptations < 1) return fail("bad argument");
+  CK(cudaSetDevice(m->device));
+  for (size_t s = 0; s < m->samplers.size(); s++) {
+    const nimb200_sampler& sp = m->samplers[s];
+    if (sp.type != NIMB_SAMPLER_RW && sp.type != NIMB_SAMPLER_RW_BLOCK) continue;
+    SamplerDev& S = m->sdev[s];
+    const int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+    const int K = 2 + (sp.type == NIMB_SAMPLER_RW_BLOCK && sp.d <= 10 ? sp.d * sp.d : 0);
+    const size_t n = (size_t)max_adaptations * K * TT * m->C;
+    if (dev_alloc(m, &S.hist, n)) return 1;
+    CK(cudaMemsetAsync(S.hist, 0, sizeof(double) * n, m->stream));
+    S.hist_cap = max_adaptations; S.hist_K = K;
+  }
+  CK(cudaStreamSynchronize(m->stream));
+  if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }   // the sampler descriptors are kernel arguments
+  return 0;
+}
+// what: 0 scaleHistory, 1 acceptanceHistory -> out[adaptation][T][C]; 2 propCovHistory -> out[adaptation][d*d][C] (column-major
+// d x d per adaptation and chain).  *n_adapt_out = adaptations recorded since the last reset; out may be NULL to query it.
+extern "C" int nimb200_sampler_history(nimb200_model* m, int32_t s, int32_t what, double* out, int64_t cap, int32_t* n_adapt_out) {
+  if (!m) return fail("null model");
+  if (s < 0 || s >= (int)m->samplers.size()) return fail("bad sampler index");
+  CK(cudaSetDevice(m->device));
+  const nimb200_sampler& sp = m->samplers[s];
+  const SamplerDev& S = m->sdev[s];
+  if (!S.hist) return fail("Please enable the sampler histories (MCMCsaveHistory) before running the MCMC.");
+  const int TT = sp.type == NIMB_SAMPLER_RW_BLOCK ? 1 : sp.n_targets;
+  int adapted = 0;
+  CK(cudaMemcpyAsync(&adapted, S.timesAdapted, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  adapted = std::min(adapted, S.hist_cap);
+  if (n_adapt_out) *n_adapt_out = adapted;
+  if (!out) return 0;
+  if (what < 0 || what > 2 || (what == 2 && S.hist_K <= 2)) return fail("no such history for this sampler (propCov histories are kept for RW_block with d <= 10)");
+  const size_t TC = (size_t)TT * m->C, per = what == 2 ? (size_t)(S.hist_K - 2) * TC : TC;
+  if ((int64_t)(per * adapted) > cap) return fail("output too small");
+  for (int a = 0; a < adapted; a++)
+    CK(cudaMemcpyAsync(out + (size_t)a * per, S.hist + ((size_t)a * S.hist_K + (what == 2 ? 2 : what)) * TC, sizeof(double) * per,
+                       cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return 0;
 }
 
 extern "C" int nimb200_samples_summary(nimb200_model* m, int32_t chain_lo, int32_t chain_hi, double* out) {

@@ -54,6 +54,10 @@ struct SamplerDev {
   double* chol;
   double* cholScale;
   double* empirSamp;
+  // MCMCsaveHistory (P/R/MCMC_samplers.R:394-399, 726-739): hist[adaptation][k][T*C], k = 0 scale before the update, 1 acceptance
+  // rate, 2.. the d*d entries of propCov before the update (RW_block with d <= 10); null when histories are off
+  double* hist;
+  int hist_cap, hist_K;
 };
 
 // fused y[i] ~ dbern(ilogit(X[i,] . beta)) block sum (fused_logit.cu).  partials: [n_tiles][C].

@@ -15,6 +15,20 @@ from . import table as T
 from .model import Model, ModelError, tree_reads_var
 
 
+# nimbleOptions(): the few system options of the reference that reach this path (P/R/options.R)
+_OPTIONS = {"MCMCsaveHistory": False}
+
+
+def nimbleOptions(**kw):
+    """nimbleOptions(MCMCsaveHistory = TRUE): RW / RW_block samplers keep their scale, acceptance-rate and proposal-covariance
+    histories (P/R/MCMC_samplers.R:394-399, 726-739).  Read when the compiled MCMC allocates its device model."""
+    for k, v in kw.items():
+        if k not in _OPTIONS:
+            raise KeyError("unknown option %s (supported: %s)" % (k, ", ".join(_OPTIONS)))
+        _OPTIONS[k] = v
+    return dict(_OPTIONS)
+
+
 # ----------------------------------------------------------------------------- conjugacy (MCMC_conjugacy.R)
 def _read_key(pos):
     """Which element of the variable a `cvar` read touches at each node: one element for all nodes, or one per node."""
@@ -927,7 +941,29 @@ class CompiledMCMC:
             self.dm = _capi.DeviceModel(self.backend, self.builder, nchains, self.first_chain, self.device)
             if self.enableWAIC:
                 self.dm.waic_enable(True)
+            if _OPTIONS["MCMCsaveHistory"] and self.backend.has_device:
+                self.dm.history_enable(1024)
         return self.dm
+
+    def _history(self, k, what):
+        if self.dm is None or not _OPTIONS["MCMCsaveHistory"]:
+            raise RuntimeError("Please set 'nimbleOptions(MCMCsaveHistory = TRUE)' before building the MCMC.")   # MCMC_samplers.R:426
+        sc = self.conf.samplerConfs[k]
+        parts = [self.dm.sampler_history(i, what) for i, (owner, _) in enumerate(self.lowering.sampler_map) if owner is sc]
+        return np.concatenate(parts, axis=1)
+
+    def getScaleHistory(self, k):
+        """samplerFunctions[[k]]$getScaleHistory(): [adaptations][targets][chains] (0-based sampler index k)."""
+        return self._history(k, 0)
+
+    def getAcceptanceHistory(self, k):
+        return self._history(k, 1)
+
+    def getPropCovHistory(self, k):
+        """[adaptations][d][d][chains] for an RW_block sampler with d <= 10 (maxDimCovHistory)."""
+        h = self._history(k, 2)
+        d = int(round(np.sqrt(h.shape[1])))
+        return h.reshape(h.shape[0], d, d, h.shape[2]).transpose(0, 2, 1, 3)   # device layout is column-major
 
     def getWAIC(self):
         """mcmc$getWAIC(): the online WAIC of everything sampled since the last reset (MCMC_build.R:323-326, MCMC_WAIC.R:269-300)."""

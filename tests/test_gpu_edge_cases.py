@@ -347,3 +347,36 @@ def test_samples_summary_on_device_equals_numpy(b200):
     out = nb.runMCMC(cm, niter=50, nchains=3, setSeed=1, summary=True)
     pooled = np.concatenate([np.asarray(out["samples"]["chain%d" % k]) for k in (1, 2, 3)])
     assert abs(out["summary"]["mu"]["Median"] - np.median(pooled[:, cm.colnames.index("mu")])) < 1e-12
+
+
+def test_sampler_histories(b200):
+    """nimbleOptions(MCMCsaveHistory = TRUE) (P/R/MCMC_samplers.R:394-399, 726-739): entry k of a history is what the sampler used
+    during adaptation interval k -- the scale / propCov read back after interval k - 1 -- and the interval's acceptance rate."""
+    m, conf = sm.basic_block("block_vector")            # RW_block on x[1:3], adaptInterval 500
+    conf.samplerConfs[0].control["adaptInterval"] = 40
+    conf.addSampler("x[2]", type="RW", control={"adaptInterval": 25})
+    nb.nimbleOptions(MCMCsaveHistory=True)
+    try:
+        cm = compile_on(b200, conf)
+        inits = sm.random_inits(m, 7, 2, 0.1)
+        scales, covs = [], []
+        run(cm, inits, 40, 0, seed=9)
+        for k in range(3):
+            scales.append(cm.dm.sampler_state(0, 0)[0].copy())
+            covs.append(cm.dm.sampler_state(0, 2).copy())
+            if k < 2:
+                run(cm, inits, 40, 0, seed=9, reset=False)
+        sh, ah, ch = cm.getScaleHistory(0), cm.getAcceptanceHistory(0), cm.getPropCovHistory(0)
+        assert sh.shape == (3, 1, 7) and ah.shape == (3, 1, 7) and ch.shape == (3, 3, 3, 7)
+        assert np.all(sh[0] == 1.0) and np.array_equal(sh[1, 0], scales[0]) and np.array_equal(sh[2, 0], scales[1])
+        assert np.all((ah >= 0) & (ah <= 1)) and np.all(ah * 40 == np.round(ah * 40))
+        assert np.all(ch[0] == np.eye(3)[:, :, None])
+        assert np.array_equal(ch[2].reshape(9, 7), covs[1].reshape(3, 3, 7).transpose(1, 0, 2).reshape(9, 7))
+        rw = cm.getScaleHistory(1)
+        assert rw.shape == (4, 1, 7) and np.all(rw[0] == 1.0)   # 120 iterations / 25
+        run(cm, inits, 10, 0, seed=9)                        # reset: histories start over
+        assert cm.getScaleHistory(0).shape[0] == 0
+    finally:
+        nb.nimbleOptions(MCMCsaveHistory=False)
+    with pytest.raises(RuntimeError, match="MCMCsaveHistory"):
+        compile_on(b200, conf).getScaleHistory(0)
