@@ -42,7 +42,8 @@ enum {
   NIMB_DBETA = 5,  /* (shape1, shape2)  inputList.R:70-75   */
   NIMB_DLOGIS = 6, /* (location, scale) inputList.R:139-142 */
   NIMB_DCAT = 7,   /* (prob[1:K]); K in fam_arg[0]; P/inst/CppCode/dists.cpp:914-934 */
-  NIMB_DEXP = 8    /* (rate): dexp_nimble, P/inst/CppCode/dists.cpp:1804-1807; inputList.R:96-100 */
+  NIMB_DEXP = 8,   /* (rate): dexp_nimble, P/inst/CppCode/dists.cpp:1804-1807; inputList.R:96-100 */
+  NIMB_DLNORM = 9  /* (meanlog, sdlog): Rmath dlnorm, sdlog = 1/sqrt(taulog), inputList.R:131-137 */
 };
 
 /* ---- expression programs: postfix, evaluated per (node instance i, chain c).

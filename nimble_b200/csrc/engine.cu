@@ -157,6 +157,7 @@ __device__ double calc_node(const DevTab& T, int di, int i, int c, int ov_slot, 
     case NIMB_DBETA: return dbeta(x, p0, p1);
     case NIMB_DLOGIS: return dlogis(x, p0, p1);
     case NIMB_DEXP: return dexp_nimble(x, p0);
+    case NIMB_DLNORM: return dlnorm(x, p0, p1);
   }
   return NAN;
 }
@@ -210,6 +211,7 @@ __device__ double calc_node_h(const DevTab& T, int di, int i, int c, int ov_slot
     case NIMB_DBETA: return dbeta(x, p0, p1);
     case NIMB_DLOGIS: return dlogis(x, p0, p1);
     case NIMB_DEXP: return dexp_nimble(x, p0);
+    case NIMB_DLNORM: return dlnorm(x, p0, p1);
   }
   return NAN;
 }
@@ -243,7 +245,7 @@ __host__ __device__ __forceinline__ int conj_kind(int sampler_type) {
 __device__ __forceinline__ double conj_par(const DevTab& T, const nimb200_dep& dp, int node, int c, int gam, bool* hoistable) {
   const nimb200_decl& dd = T.decl[dp.decl];
   if (dd.dist == NIMB_DBINOM) { *hoistable = T.pconst[3 * dp.decl] != 0; return get_param(T, dp.decl, node, c, 0, -1, 0.0); }  // size
-  if (dd.dist == NIMB_DNORM) {
+  if (dd.dist == NIMB_DNORM || dd.dist == NIMB_DLNORM) {
     *hoistable = T.pconst[3 * dp.decl + (gam == 1 ? 0 : 1)] != 0;
     return gam == 1 ? get_param(T, dp.decl, node, c, 0, -1, 0.0) : get_param(T, dp.decl, node, c, NIMB_PARAM_TAU, -1, 0.0);
   }
@@ -268,7 +270,9 @@ __device__ __forceinline__ void conj_contrib(const DevTab& T, const nimb200_dep&
     else if (dd.dist == NIMB_DGAMMA) { c0 += par; c1 += coeff * value; }
     else if (dd.dist == NIMB_DEXP) { c0 += 1.0; c1 += coeff * value; }
     else if (dd.dist == NIMB_DNORM) { c0 += 1. / 2; c1 += coeff / 2 * ((value - par) * (value - par)); }
+    else if (dd.dist == NIMB_DLNORM) { c0 += 1. / 2; c1 += coeff / 2 * ((log(value) - par) * (log(value) - par)); }
   } else {
+    if (dd.dist == NIMB_DLNORM) value = log(value);   // MCMC_conjugacy.R:113: a dlnorm dependent contributes through log(value)
     c0 += coeff * (value - offset) * par;
     c1 += coeff * coeff * par;
   }
@@ -375,6 +379,7 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
       case NIMB_DGAMMA: nv = rgamma1(key, p0) * p1; break;
       case NIMB_DBETA: nv = rbeta1(key, p0, p1); break;
       case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; break;
+      case NIMB_DLNORM: normal2(key, 0, u, u2); nv = det_exp(p0 + p1 * u); break;
       case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); break;
       case NIMB_DBINOM: nv = rbinom_inv(key, p0, p1); break;
       case NIMB_DPOIS: nv = rpois_inv(key, p0); break;
@@ -618,6 +623,7 @@ __device__ __forceinline__ bool simulate_node(const DevTab& T, int di, int node,
     case NIMB_DGAMMA: nv = rgamma1(key, p0) * p1; return true;
     case NIMB_DBETA: nv = rbeta1(key, p0, p1); return true;
     case NIMB_DEXP: unif2(key, 0, u, u2); nv = -det_log(u) / p0; return true;
+    case NIMB_DLNORM: normal2(key, 0, u, u2); nv = det_exp(p0 + p1 * u); return true;
     case NIMB_DLOGIS: unif2(key, 0, u, u2); nv = p0 + p1 * (det_log(u) - det_log(1.0 - u)); return true;
     case NIMB_DBINOM: nv = rbinom_inv(key, p0, p1); return !isnan(nv);
     case NIMB_DPOIS: nv = rpois_inv(key, p0); return !isnan(nv);
@@ -1576,7 +1582,7 @@ static int validate_table(const nimb200_table* t) {
   if (t->n_slots < 0 || t->n_decl < 0 || t->n_ops < 0) return fail("negative table size");
   for (int i = 0; i < t->n_decl; i++) {
     const nimb200_decl& d = t->decl[i];
-    if (d.dist < NIMB_DNORM || d.dist > NIMB_DEXP) return fail("unknown distribution id in declaration");
+    if (d.dist < NIMB_DNORM || d.dist > NIMB_DLNORM) return fail("unknown distribution id in declaration");
     if (d.n < 0) return fail("negative node count");
     if (d.value_kind == 0) {
       if (d.value_ref < 0 || d.value_ref >= t->n_darr || t->darr_len[d.value_ref] < d.n) return fail("data array too short for declaration");
@@ -1617,7 +1623,7 @@ static int validate_table(const nimb200_table* t) {
     }
     if (sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE) {
       const nimb200_decl& pd = t->decl[t->deps[sp.dep_off].decl];
-      const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP ||
+      const bool ok = pd.dist == NIMB_DNORM || pd.dist == NIMB_DGAMMA || pd.dist == NIMB_DBETA || pd.dist == NIMB_DEXP || pd.dist == NIMB_DLNORM ||
                       pd.dist == NIMB_DLOGIS || pd.dist == NIMB_DBINOM || pd.dist == NIMB_DPOIS;
       // dependents (the rest of the predictive network) are allowed: they are simulated by the table samplers that follow this
       // one, and listing them here is what invalidates their cached block sums

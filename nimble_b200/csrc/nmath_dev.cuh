@@ -177,6 +177,17 @@ __device__ __forceinline__ double dlogis(double x, double location, double scale
   return -(x + log(scale * f * f));
 }
 
+// [nmath/dlnorm.c]
+__device__ __forceinline__ double dlnorm(double x, double meanlog, double sdlog) {
+  if (isnan(x) || isnan(meanlog) || isnan(sdlog)) return x + meanlog + sdlog;
+  if (sdlog < 0) return NAN;
+  if (!isfinite(x) && log(x) == meanlog) return NAN;
+  if (sdlog == 0) return (log(x) == meanlog) ? INFINITY : -INFINITY;
+  if (x <= 0) return -INFINITY;
+  double y = (log(x) - meanlog) / sdlog;
+  return -(NIMB_LN_SQRT_2PI + 0.5 * y * y + log(x * sdlog));
+}
+
 // dexp_nimble(x, rate) = dexp(x, 1/rate): P/inst/CppCode/dists.cpp:1804-1807
 __device__ __forceinline__ double dexp_nimble(double x, double rate) {
   double scale = 1 / rate;

@@ -136,6 +136,8 @@ def check_conjugacy(model, decl):
                 pname, code = "tau", T.PARAM_TAU
             elif dep.dist == T.DEXP and only_in("rate"):
                 pname, code = "rate", 0
+            elif dep.dist == T.DLNORM and only_in("taulog"):   # MCMC_conjugacy.R:86-92 (dgamma prior on taulog)
+                pname, code = "taulog", T.PARAM_TAU
             else:
                 return None
             f = _linear_form(bp[pname], var)
@@ -144,6 +146,8 @@ def check_conjugacy(model, decl):
         else:
             if dep.dist == T.DNORM and only_in("mean"):
                 pname, code = "mean", 0
+            elif dep.dist == T.DLNORM and only_in("meanlog"):   # MCMC_conjugacy.R:113: through log(value)
+                pname, code = "meanlog", 0
             else:
                 return None
             f = _linear_form(bp[pname], var)
@@ -195,7 +199,7 @@ class MCMCconf:
         self.samplerConfs = [sc for sc in self.samplerConfs if sc.type != T.SAMPLER_POSTERIOR_PREDICTIVE] + pp
 
     # default assignment rules, MCMC_configuration.R:340-446: conjugate -> binary -> (discrete: unsupported) -> RW
-    _PP_DISTS = (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM)
+    _PP_DISTS = (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM, T.DLNORM)
 
     def _is_terminal(self, decl):
         return not [d for d in self.model.dependents(decl.var) if d is not decl]

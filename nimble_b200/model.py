@@ -26,7 +26,7 @@ _BIN = {"+": T.OP_ADD, "-": T.OP_SUB, "*": T.OP_MUL, "/": T.OP_DIV, "^": T.OP_PO
 _DIST_ARGS = {
     "dnorm": ["mean", "tau"], "dgamma": ["shape", "rate"], "dpois": ["lambda"], "dbern": ["prob"],
     "dbin": ["prob", "size"], "dbinom": ["prob", "size"], "dbeta": ["shape1", "shape2"],
-    "dlogis": ["location", "rate"], "dexp": ["rate"], "dcat": ["prob"],
+    "dlogis": ["location", "rate"], "dexp": ["rate"], "dcat": ["prob"], "dlnorm": ["meanlog", "taulog"],
 }
 
 
@@ -447,6 +447,14 @@ class Model:
         elif dist == "dexp":
             rate = low["rate"] if "rate" in low else inv(low["scale"])
             d.dist, d.params = T.DEXP, [rate]
+        elif dist == "dlnorm":   # dlnorm(meanlog, sdlog = 1/sqrt(taulog)) | sqrt(varlog), inputList.R:131-137
+            if "sdlog" in low:
+                sdl = low["sdlog"]
+            elif "varlog" in low:
+                sdl = ("un", T.OP_SQRT, low["varlog"])
+            else:
+                sdl = inv(("un", T.OP_SQRT, low["taulog"]))
+            d.dist, d.params = T.DLNORM, [low["meanlog"], sdl]
         return d
 
     def _check_coverage(self):
@@ -532,7 +540,7 @@ class Model:
 
     def simulable(self, var):
         """Can missing values of `var` be simulated on the device (a variate generator exists for its distribution)?"""
-        return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM) for d in self.decl_of(var))
+        return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM, T.DLNORM) for d in self.decl_of(var))
 
 
 def nimbleCode(text):

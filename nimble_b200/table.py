@@ -13,9 +13,9 @@ MAX_PARAM = 3
 MAX_BLOCK_D = 64
 
 # distributions
-DNORM, DGAMMA, DPOIS, DBINOM, DBETA, DLOGIS, DCAT, DEXP = 1, 2, 3, 4, 5, 6, 7, 8
+DNORM, DGAMMA, DPOIS, DBINOM, DBETA, DLOGIS, DCAT, DEXP, DLNORM = 1, 2, 3, 4, 5, 6, 7, 8, 9
 DIST_NAMES = {DNORM: "dnorm", DGAMMA: "dgamma", DPOIS: "dpois", DBINOM: "dbinom", DBETA: "dbeta",
-              DLOGIS: "dlogis", DCAT: "dcat", DEXP: "dexp"}
+              DLOGIS: "dlogis", DCAT: "dcat", DEXP: "dexp", DLNORM: "dlnorm"}
 # ops
 OP_CONST, OP_DATA, OP_CVAR, OP_CVARN, OP_INPROD, OP_DATAJ, OP_CVARJ = 1, 2, 3, 4, 5, 6, 7
 OP_CVAR_IDX, OP_DATA_IDX = 48, 49

@@ -158,6 +158,7 @@ static double calc_node(ref_model *m, const double *st, int di, int i) {
     case NIMB_DBETA: return ref_dbeta(x, p0, p1);
     case NIMB_DLOGIS: return ref_dlogis(x, p0, p1);
     case NIMB_DEXP: return ref_dexp_nimble(x, p0);
+    case NIMB_DLNORM: return ref_dlnorm(x, p0, p1);
   }
   return NAN;
 }
@@ -440,7 +441,7 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
     dval[q] = node_value(m, st, dd, node);
     /* neededParamsForPosterior: dnorm dependents need tau (dnorm prior) or mean (dgamma prior on tau);
        dgamma dependents need shape; dpois none */
-    if (dd->dist == NIMB_DNORM) dpar[q] = gam ? get_param(m, st, di, node, 0) : get_param(m, st, di, node, NIMB_PARAM_TAU);
+    if (dd->dist == NIMB_DNORM || dd->dist == NIMB_DLNORM) dpar[q] = gam ? get_param(m, st, di, node, 0) : get_param(m, st, di, node, NIMB_PARAM_TAU);
     else if (dd->dist == NIMB_DGAMMA) dpar[q] = get_param(m, st, di, node, 0);
     else if (dd->dist == NIMB_DBINOM) dpar[q] = get_param(m, st, di, node, 0); /* size (1 for dbern) */
     else dpar[q] = 0;
@@ -477,8 +478,10 @@ static void run_conjugate(ref_model *m, int c, int sid, int t, uint64_t seed, ui
       else if (dd->dist == NIMB_DGAMMA) { contrib0 += dpar[q]; contrib1 += coeff * value; }
       else if (dd->dist == NIMB_DEXP) { contrib0 += 1; contrib1 += coeff * value; }
       else if (dd->dist == NIMB_DNORM) { contrib0 += 1. / 2; contrib1 += coeff / 2 * ((value - dpar[q]) * (value - dpar[q])); }
-    } else { /* :109-115 */
+      else if (dd->dist == NIMB_DLNORM) { contrib0 += 1. / 2; contrib1 += coeff / 2 * ((log(value) - dpar[q]) * (log(value) - dpar[q])); }
+    } else { /* :109-115; a dlnorm dependent contributes through log(value) */
       double tau = dpar[q];
+      if (dd->dist == NIMB_DLNORM) value = log(value);
       contrib0 += coeff * (value - offset) * tau;
       contrib1 += coeff * coeff * tau;
     }
@@ -607,6 +610,7 @@ static int run_posterior_predictive(ref_model *m, int c, int sid, int t, uint64_
     case NIMB_DGAMMA: nv = ref_rgamma(seed, chain, iter, sid, t, p0) * p1; break;
     case NIMB_DBETA: nv = ref_rbeta(seed, chain, iter, sid, t, p0, p1); break;
     case NIMB_DEXP: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
+    case NIMB_DLNORM: ref_normal2(seed, chain, iter, sid, t, 0, &u, &u2); nv = ref_det_exp(p0 + p1 * u); break;
     case NIMB_DLOGIS: ref_unif2(seed, chain, iter, sid, t, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
     case NIMB_DBINOM: nv = ref_rbinom(seed, chain, iter, sid, t, p0, p1); break;
     case NIMB_DPOIS: nv = ref_rpois(seed, chain, iter, sid, t, p0); break;
@@ -958,6 +962,7 @@ int ref_initialize_model(ref_model *m, const int32_t *decl_order, int32_t n_orde
           case NIMB_DGAMMA: nv = ref_rgamma(seed, chain, 0, sid, node, p0) * p1; break;
           case NIMB_DBETA: nv = ref_rbeta(seed, chain, 0, sid, node, p0, p1); break;
           case NIMB_DEXP: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = -ref_det_log(u) / p0; break;
+          case NIMB_DLNORM: ref_normal2(seed, chain, 0, sid, node, 0, &u, &u2); nv = ref_det_exp(p0 + p1 * u); break;
           case NIMB_DLOGIS: ref_unif2(seed, chain, 0, sid, node, 0, &u, &u2); nv = p0 + p1 * (ref_det_log(u) - ref_det_log(1.0 - u)); break;
           case NIMB_DBINOM: nv = ref_rbinom(seed, chain, 0, sid, node, p0, p1); break;
           case NIMB_DPOIS: nv = ref_rpois(seed, chain, 0, sid, node, p0); break;

@@ -218,6 +218,18 @@ double ref_dlogis(double x, double location, double scale) {
   return -(x + log(scale * f * f));
 }
 
+/* [nmath/dlnorm.c] */
+double ref_dlnorm(double x, double meanlog, double sdlog) {
+  double y;
+  if (isnan(x) || isnan(meanlog) || isnan(sdlog)) return x + meanlog + sdlog;
+  if (sdlog < 0) return NAN;
+  if (!isfinite(x) && log(x) == meanlog) return NAN; /* log(x) - meanlog is NaN */
+  if (sdlog == 0) return (log(x) == meanlog) ? ML_POSINF : ML_NEGINF;
+  if (x <= 0) return ML_NEGINF;
+  y = (log(x) - meanlog) / sdlog;
+  return -(M_LN_SQRT_2PI_ + 0.5 * y * y + log(x * sdlog));
+}
+
 /* dexp_nimble(x, rate) = dexp(x, 1/rate): P/inst/CppCode/dists.cpp:1804-1807; [nmath/dexp.c] */
 double ref_dexp_nimble(double x, double rate) {
   double scale = 1 / rate;

@@ -17,6 +17,7 @@ double ref_lbeta(double a, double b);
 double ref_dbeta(double x, double a, double b);
 double ref_dlogis(double x, double location, double scale);
 double ref_dexp_nimble(double x, double rate);
+double ref_dlnorm(double x, double meanlog, double sdlog);
 double ref_dcat(double x, const double *prob, int K);
 #ifdef __cplusplus
 }

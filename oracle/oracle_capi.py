@@ -33,7 +33,7 @@ def oracle_backend():
         b.finish.argtypes = [vp, C.c_int64, C.c_int64, C.c_int32]
         b.eval_count = b.lib.ref_eval_count
         b.eval_count.argtypes, b.eval_count.restype = [vp], C.c_uint64
-        for name in ("dnorm", "dgamma", "dbinom", "dbeta", "dlogis"):
+        for name in ("dnorm", "dgamma", "dbinom", "dbeta", "dlogis", "dlnorm"):
             f = getattr(b.lib, "ref_" + name)
             f.argtypes, f.restype = [C.c_double] * 3, C.c_double
         for name in ("dpois", "dexp_nimble", "bd0", "lbeta"):

@@ -92,3 +92,36 @@ def rmnorm_chol_relation(backend, chains=3, niter=6, seed=29):
                 np.testing.assert_allclose(s[c, it], want, rtol=1e-12, atol=1e-12)
         prev = s[:, it].copy()
     assert moved >= chains * niter - 1
+
+
+def lognormal_cases():
+    """Normal-lognormal and gamma-lognormal conjugacy (P/R/MCMC_conjugacy.R:86, 113): a dlnorm dependent contributes through
+    log(value).  Returns (model, conf, {column: (posterior mean, posterior sd)}) with the closed forms computed here."""
+    rng = np.random.default_rng(11)
+    n = 25
+    y = np.exp(rng.normal(0.8, 0.5, n))
+    code = ("{ mu ~ dnorm(0, sd = 10)\n tau ~ dgamma(2, 1)\n for(i in 1:n) { y[i] ~ dlnorm(mu, sdlog = 0.5) }\n"
+            "for(i in 1:n) { w[i] ~ dlnorm(0.3, taulog = tau) }\n ypred ~ dlnorm(mu, sdlog = 0.5) }")
+    w = np.exp(rng.normal(0.3, 0.7, n))
+    m = nb.nimbleModel(code, constants={"n": n}, data={"y": y, "w": w}, inits={"mu": 0.0, "tau": 1.0, "ypred": 1.0})
+    conf = nb.configureMCMC(m, monitors=["mu", "tau", "ypred"])
+    prec = 1 / 100.0 + n / 0.25
+    mu_mean, mu_sd = (np.log(y).sum() / 0.25) / prec, prec ** -0.5
+    shape, rate = 2 + n / 2.0, 1 + 0.5 * np.sum((np.log(w) - 0.3) ** 2)
+    return m, conf, {"mu": (mu_mean, mu_sd), "tau": (shape / rate, np.sqrt(shape) / rate)}
+
+
+def check_lognormal(backend, chains, niter):
+    m, conf, want = lognormal_cases()
+    kinds = {s.var: s.name for s in conf.samplerConfs}
+    assert kinds == {"mu": "conjugate_dnorm", "tau": "conjugate_dgamma", "ypred": "posterior_predictive"}, kinds
+    cm = nb.compileNimble(nb.buildMCMC(conf), backend=backend)
+    s = cm.run_chains(np.tile(m.init_vector(), (chains, 1)), niter, niter // 10, 1, True, 3)
+    s = s.reshape(-1, s.shape[-1])
+    for name, (mean, sd) in want.items():
+        col = s[:, cm.colnames.index(name)]
+        assert abs(col.mean() - mean) < 5 * sd / np.sqrt(col.size) + 1e-3 * sd, (name, col.mean(), mean)
+        assert abs(col.std() / sd - 1) < 0.05, (name, col.std(), sd)
+    lp = np.log(s[:, cm.colnames.index("ypred")])      # predictive: log ypred ~ N(mu, 0.5^2) mixed over the posterior of mu
+    assert abs(lp.mean() - want["mu"][0]) < 0.02 and abs(lp.var() - (0.25 + want["mu"][1] ** 2)) < 0.02
+    return cm, s

@@ -50,6 +50,11 @@ def dexp(x, rate):
     return mp.log(F(rate)) - F(rate) * F(x)
 
 
+def dlnorm(x, ml, sl):
+    z = (mp.log(F(x)) - F(ml)) / F(sl)
+    return -mp.log(F(x)) - mp.log(F(sl)) - mp.log(2 * mp.pi) / 2 - z * z / 2
+
+
 rows = []
 
 
@@ -86,6 +91,10 @@ for K in [2, 5, 11]:
     prob = rng.random(K) * 3
     for x in range(1, K + 1):
         add("dcat", [x] + list(prob), mp.log(F(prob[x - 1])) - mp.log(mp.fsum([F(q) for q in prob])))
+for _ in range(30):   # appended last: the vectors above keep their values
+    ml, sl = rng.normal(0, 1.5), float(np.exp(rng.normal(0, 1)))
+    x = float(np.exp(rng.normal(ml, 2 * sl)))
+    add("dlnorm", (x, ml, sl), dlnorm(x, ml, sl))
 
 out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "density_vectors.json")
 with open(out, "w") as f:

@@ -144,7 +144,7 @@ def golden_models():
     decl = {
         "dnorm": "y[i] ~ dnorm(a[i], sd = b[i])", "dgamma": "y[i] ~ dgamma(a[i], scale = b[i])", "dpois": "y[i] ~ dpois(a[i])",
         "dbinom": "y[i] ~ dbin(b[i], a[i])", "dbeta": "y[i] ~ dbeta(a[i], b[i])", "dlogis": "y[i] ~ dlogis(a[i], scale = b[i])",
-        "dexp": "y[i] ~ dexp(a[i])",
+        "dexp": "y[i] ~ dexp(a[i])", "dlnorm": "y[i] ~ dlnorm(a[i], sdlog = b[i])",
     }
     for dist, rows in by.items():
         want = np.array([float(r["logp"]) for r in rows])
@@ -179,4 +179,4 @@ def check_golden_vectors(backend, tol):
         assert err.max() < tol, (dist, err.max(), int(err.argmax()) // 2)
         seen.add(dist.rstrip("0123456789"))
         dm.close()
-    assert seen == {"dnorm", "dgamma", "dpois", "dbinom", "dbeta", "dlogis", "dexp", "dcat"}
+    assert seen == {"dnorm", "dgamma", "dpois", "dbinom", "dbeta", "dlogis", "dexp", "dcat", "dlnorm"}

@@ -156,3 +156,7 @@ def test_two_coefficients_of_one_variable_on_oracle(oracle):
 
 def test_rmnorm_chol_relation_on_oracle(oracle):
     cc.rmnorm_chol_relation(oracle)
+
+
+def test_lognormal_conjugacies_on_oracle(oracle):
+    cc.check_lognormal(oracle, 4, 6000)

@@ -37,3 +37,11 @@ def test_formulations_give_equal_samples(b200, oracle):
 
 def test_rmnorm_chol_relation(b200):
     cc.rmnorm_chol_relation(b200)
+
+
+def test_lognormal_conjugacies(b200, oracle):
+    cc.check_lognormal(b200, 64, 1500)
+    m, conf, _ = cc.lognormal_cases()
+    inits = np.tile(m.init_vector(), (7, 1))
+    a, b = run(compile_on(b200, conf), inits, 200, 0, seed=2), run(compile_on(oracle, conf), inits, 200, 0, seed=2)
+    assert rel_err(a, b).max() < 1e-9

@@ -26,7 +26,7 @@ def test_all_golden_vectors(oracle):
         err = abs(got - want) / max(1.0, abs(want))
         worst[v["dist"]] = max(worst.get(v["dist"], 0.0), err)
         assert err < 5e-14, (v, got)
-    assert set(worst) == {"dnorm", "dgamma", "dpois", "dbinom", "dbeta", "dlogis", "dexp", "dcat"}
+    assert set(worst) == {"dnorm", "dgamma", "dpois", "dbinom", "dbeta", "dlogis", "dexp", "dcat", "dlnorm"}
 
 
 def test_edge_cases(oracle):
