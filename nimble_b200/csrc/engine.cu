@@ -346,13 +346,13 @@ __device__ __forceinline__ double rw_proposal(const nimb200_sampler& sp, double 
 // per-(target, chain) sums into buf[t][k][c] (k < 3), the host all-reduces buf, PHASE 2 decides / draws from it.
 // LANES = 32: one WARP per (target, chain), its lanes stride over the dependent nodes and the partial sums meet in a fixed-order
 // butterfly -- used when there are few (target, chain) pairs but each has many dependents (tau_b / mu_b over 50 betas).
+// gthread: index of the calling thread among the (target, chain, lane) work items of the sampler
 template <int PHASE, int LANES>
-__global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* buf) {
-  cudaTriggerProgrammaticLaunchCompletion();
-  cudaGridDependencySynchronize();
+__device__ __forceinline__ void sweep_body(const DevTab& T, int sid, uint64_t seed, uint64_t iter, const SamplerDev& S, double* buf,
+                                           size_t gthread) {
   const nimb200_sampler sp = T.samplers[sid];
-  size_t gid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) / LANES;
-  const int lane = LANES == 1 ? 0 : (threadIdx.x & (LANES - 1));
+  size_t gid = gthread / LANES;
+  const int lane = LANES == 1 ? 0 : (int)(gthread & (LANES - 1));
   int c = (int)(gid % T.C);
   size_t tq = gid / T.C;
   if (tq >= (size_t)sp.n_targets) return;
@@ -502,6 +502,45 @@ __global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
     nv = mean + sd * z;
   }
   *sv = nv;
+}
+
+template <int PHASE, int LANES>
+__global__ void k_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* buf) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
+  sweep_body<PHASE, LANES>(T, sid, seed, iter, S, buf, (size_t)blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// Small models (BASELINE config 1, the BUGS 'pump' example: 12 latent nodes, a handful of chains): an iteration is three or four
+// launches of a few dozen threads each and costs nothing but launch latency (~10 us per kernel even from a replayed graph).
+// When every sampler of the model is a scalar sweep with little work, ONE block runs whole iterations -- sampler after sampler
+// with a block barrier in between, then the monitor row and the iteration counter -- and n_it of them per launch.  Same
+// sweep_body, same draws, same results as the launch-per-sampler path.
+struct SmallPlan { int n; int sid[24]; int lanes[24]; };
+__global__ void __launch_bounds__(1024)
+k_small_iters(DevTab T, SmallPlan P, const SamplerDev* __restrict__ sdev, uint64_t seed, int n_it, const int32_t* __restrict__ mon,
+              int nmon, const long long* __restrict__ rp /* RunParams as words */, double* samples, unsigned long long* ctr) {
+  const long long rows_before = rp[0], iter0 = rp[1], nburnin = rp[2];
+  const int thin = (int)(rp[3] & 0xffffffffll);
+  for (int it = 0; it < n_it; it++) {
+    for (int j = 0; j < P.n; j++) {
+      const int sid = P.sid[j];
+      const size_t total = (size_t)T.samplers[sid].n_targets * T.C * P.lanes[j];
+      const SamplerDev S = sdev[sid];
+      if (P.lanes[j] == 32) { for (size_t g = threadIdx.x; g < total; g += blockDim.x) sweep_body<0, 32>(T, sid, seed, 0, S, nullptr, g); }
+      else { for (size_t g = threadIdx.x; g < total; g += blockDim.x) sweep_body<0, 1>(T, sid, seed, 0, S, nullptr, g); }
+      __syncthreads();
+    }
+    const long long itl = (long long)ctr[0] - iter0;
+    if (itl > nburnin && (itl - nburnin) % thin == 0) {
+      const long long row = rows_before + (itl - nburnin) / thin - 1;
+      for (size_t g = threadIdx.x; g < (size_t)nmon * T.C; g += blockDim.x)
+        samples[(size_t)row * nmon * T.C + g] = T.state[(size_t)mon[g / T.C] * T.C + (g % T.C)];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) ctr[0] += 1;
+    __syncthreads();
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ slice sampler
@@ -1084,6 +1123,8 @@ struct nimb200_model {
   // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
   std::vector<double*> d_pois_S, d_pois_Snew;
   std::vector<char> pois_S_valid, pois_S_pending;
+  SmallPlan small{};                // whole-iteration kernel for small all-sweep models (k_small_iters); small.n == 0: not eligible
+  SamplerDev* d_sdev = nullptr;     // device copy of sdev[] for it
   int* d_accept = nullptr;        // [C] accept flags of the last wide MH decision
   int prop_lo = -1, prop_hi = -1; // state slots that currently hold a proposal (between propose and finish)
   std::vector<double*> d_norm_gs;    // per such sampler: [n_targets][2] (sum y, count) of every target's nodes -- data only, so it
@@ -2056,6 +2097,25 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     m->bern_byp_slot[s] = slots;
     TRY(dev_alloc(m, &m->d_bern_contrib[s], (size_t)2 * sp.n_targets * C));
   }
+  {  // whole-iteration kernel: every sampler a plain scalar sweep with little work
+    SmallPlan P{};
+    bool ok = !getenv("NIMB200_NO_SMALL") && m->samplers.size() <= 24 && (size_t)t->n_monitors * C <= 65536;
+    for (size_t s = 0; s < m->samplers.size() && ok; s++) {
+      const nimb200_sampler& sp = m->samplers[s];
+      const bool plain = sp.type == NIMB_SAMPLER_RW || sp.type == NIMB_SAMPLER_BINARY || sp.type == NIMB_SAMPLER_CONJ_GAMMA ||
+                         sp.type == NIMB_SAMPLER_CONJ_NORMAL || sp.type == NIMB_SAMPLER_CONJ_BETA || sp.type == NIMB_SAMPLER_POSTERIOR_PREDICTIVE;
+      if (!plain || m->wide[s] || m->pois_sweep[s] || m->bern_sweep[s] || m->norm_sweep[s]) { ok = false; break; }
+      const size_t pairs = (size_t)sp.n_targets * C;
+      const bool wpp = pairs <= 65536 && m->sweep_deps[s] >= 8;      // the same choice run_sampler makes
+      if (pairs * (wpp ? 32 : 1) > 8192 || m->sweep_deps[s] > 4096) { ok = false; break; }
+      P.sid[P.n] = (int)s; P.lanes[P.n] = wpp ? 32 : 1; P.n++;
+    }
+    if (ok && P.n > 0) {
+      m->small = P;
+      TRY(dev_alloc(m, &m->d_sdev, m->samplers.size()));
+      TRYCU(cudaMemcpyAsync(m->d_sdev, m->sdev.data(), sizeof(SamplerDev) * m->sdev.size(), cudaMemcpyHostToDevice, m->stream));
+    }
+  }
   m->invalidates.resize(m->samplers.size());
   for (size_t s = 0; s < m->samplers.size(); s++) {
     const nimb200_sampler& sp = m->samplers[s];
@@ -2720,7 +2780,23 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     return 0;
   };
   CK(cudaEventRecord(m->ev0, m->stream));
-  for (int64_t it = 1; it <= niter; it++) {
+  const bool small_path = m->small.n > 0 && m->nranks <= 1 && !m->waic && !m->time_samplers && nmon >= 0;
+  if (small_path) {  // whole iterations inside one block, up to 256 of them per launch
+    int threads = 32;
+    for (int j = 0; j < m->small.n; j++) {
+      const size_t tot = (size_t)m->samplers[m->small.sid[j]].n_targets * C * m->small.lanes[j];
+      threads = std::max(threads, (int)std::min<size_t>(1024, (tot + 31) / 32 * 32));
+    }
+    for (int64_t done = 0; done < niter;) {
+      const int n_it = (int)std::min<int64_t>(256, niter - done);
+      k_small_iters<<<1, threads, 0, m->stream>>>(m->T, m->small, m->d_sdev, seed, n_it, (const int32_t*)m->d_mon, nmon,
+                                                  (const long long*)m->d_runp, m->d_samples, m->d_ctr);
+      m->launches++;
+      done += n_it;
+    }
+    CK(cudaGetLastError());
+  }
+  for (int64_t it = 1; it <= niter && !small_path; it++) {
     uint64_t git = (uint64_t)(m->iter_done + it);
     bool due = adapt_due();
     if (m->graph_exec && !due && pattern() == m->graph_pattern) {
@@ -2919,6 +2995,7 @@ extern "C" int nimb200_sampler_history_enable(nimb200_model* m, int32_t max_adap
     CK(cudaMemsetAsync(S.hist, 0, sizeof(double) * n, m->stream));
     S.hist_cap = max_adaptations; S.hist_K = K;
   }
+  if (m->d_sdev) CK(cudaMemcpyAsync(m->d_sdev, m->sdev.data(), sizeof(SamplerDev) * m->sdev.size(), cudaMemcpyHostToDevice, m->stream));
   CK(cudaStreamSynchronize(m->stream));
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }   // the sampler descriptors are kernel arguments
   return 0;
