@@ -42,9 +42,10 @@ static __device__ __noinline__ double bern_logit_lp_slow(double eta, bool y1) {
 }
 
 // SOFTPLUS: fast path on the softplus table sp (shared memory); else on the exp / log tables tab.  tab also serves the general path.
+// y1v: the value of each of the W nodes (the fused logistic kernel's W evaluations share one node, see the wrapper below)
 template <int W, bool VOTE = true, bool SOFTPLUS = false>
-__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const double* __restrict__ sp,
-                                                  const MathTab* __restrict__ tab) {
+__device__ __forceinline__ void bern_logit_lp_vecy(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
+                                                   const double* __restrict__ sp, const MathTab* __restrict__ tab) {
   double x[W], t[W], r[W], pl[W], e[W], d[W], p[W], q[W], u[W];
   int n[W];
   {  // the moderate case is recognised on the exponent bits (integer pipe), before anything touches the FP64 pipe
@@ -93,7 +94,7 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
 #pragma unroll
         for (int j = 0; j < W; j++) {
           bool neg = __double2hiint(eta[j]) < 0;
-          out[j] = (y1 == neg ? -x[j] : 0.0) - pl[j];
+          out[j] = (y1v[j] == neg ? -x[j] : 0.0) - pl[j];
         }
       } else {
 #pragma unroll
@@ -135,7 +136,7 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
           double lp = fma(rr * rr, Q, rr);
           double lg = (idx == 128 ? c_tab_misc[7] : tab->logA[idx]) + lp;
           bool neg = __double2hiint(eta[j]) < 0;
-          out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
+          out[j] = (y1v[j] == neg ? x[j] : 0.0) - lg;  // x = -|eta|
         }
       }
       return;
@@ -146,7 +147,7 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
   for (int j = 0; j < W; j++) slow |= !(eta[j] >= -690.0);
   if (VOTE ? __any_sync(0xffffffffu, slow) : slow) {  // warp-uniform with VOTE, practically never taken
 #pragma unroll
-    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1);
+    for (int j = 0; j < W; j++) out[j] = bern_logit_lp_slow(eta[j], y1v[j]);
     return;
   }
   // ---- e = exp(-eta): x = k ln2/64 + r, e = 2^(k>>6) T[k&63] (1 + r P(r)).  x is clamped at -708: below that e only has to
@@ -194,8 +195,8 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
   double dl[W];
 #pragma unroll
   for (int j = 0; j < W; j++) {
-    dl[j] = y1 ? 0.0 : (1.0 - q[j]) - p[j];  // exact
-    t[j] = y1 ? p[j] : q[j];
+    dl[j] = y1v[j] ? 0.0 : (1.0 - q[j]) - p[j];  // exact
+    t[j] = y1v[j] ? p[j] : q[j];
   }
   // ---- log(t), t = 0 or a normal number in [2^-1000, 1]: t = 2^e m, m in [1,2), centre c = 1 + j/128 (j = 128 -> e+1, c = 1)
 #pragma unroll
@@ -222,6 +223,15 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
     double lg = fma(kd, c_tab_misc[7], lc + lp);
     out[j] = zero ? -INFINITY : lg;
   }
+}
+
+template <int W, bool VOTE = true, bool SOFTPLUS = false>
+__device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y1, double (&out)[W], const double* __restrict__ sp,
+                                                  const MathTab* __restrict__ tab) {
+  bool yv[W];
+#pragma unroll
+  for (int j = 0; j < W; j++) yv[j] = y1;
+  bern_logit_lp_vecy<W, VOTE, SOFTPLUS>(eta, yv, out, sp, tab);
 }
 
 __device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)

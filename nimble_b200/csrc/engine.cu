@@ -1115,7 +1115,7 @@ struct nimb200_model {
   std::vector<char> norm_ok;         // per decl: streaming normal family usable
   std::vector<int> norm_vspan;       // per decl: number of elements of the gathered vector that are reachable
   std::vector<char> norm_sweep;      // per sampler: conjugate sweep served by k_norm_group_sums + k_norm_conj_draw
-  std::vector<double*> d_pois_ysum;  // per Poisson conjugate sweep: [3][n_targets] data-only sums over each target's nodes (y, A, x y)
+  std::vector<double*> d_pois_ysum;  // per Poisson conjugate sweep: [4][n_targets] data-only statistics of each target's nodes (sums of y, A, x y; max |x|)
   std::vector<int> pois_byp_slot;    // per such sweep: cache slot of the dependents' whole-declaration block sum it can refresh, or -1
   std::vector<double*> d_pois_contrib; // [n_targets][C] per-(target, chain) shares of that block sum
   std::vector<char> pois_ysum_valid;
@@ -1123,6 +1123,7 @@ struct nimb200_model {
   // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
   std::vector<double*> d_pois_S, d_pois_Snew;
   std::vector<char> pois_S_valid, pois_S_pending;
+  bool pois_series = true;   // group sums from the data-only moment series (fused_pois.cuh); NIMB200_NO_SERIES=1 keeps the node pass
   SmallPlan small{};                // whole-iteration kernel for small all-sweep models (k_small_iters); small.n == 0: not eligible
   SamplerDev* d_sdev = nullptr;     // device copy of sdev[] for it
   int* d_accept = nullptr;        // [C] accept flags of the last wide MH decision
@@ -1372,9 +1373,8 @@ static int ensure_pois_ysum(nimb200_model* m, int s) {
 static int launch_pois_S(nimb200_model* m, int s, double* out) {
   const nimb200_sampler& sp = m->samplers[s];
   PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
-  const size_t total = (size_t)sp.n_targets * m->C;
-  k_pois_conj_sweep<3><<<(unsigned)((total + PF_THREADS - 1) / PF_THREADS), PF_THREADS, 0, m->stream>>>(
-      m->T, s, 0, 0, pa, m->d_pois_ysum[s], out, nullptr);
+  k_pois_S<<<dim3((m->C + 31) / 32, (sp.n_targets + PS3_TPB - 1) / PS3_TPB), PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out,
+                                                                                                             m->pois_series ? 1 : 0);
   m->launches++;
   CK(cudaGetLastError());
   return 0;
@@ -1495,11 +1495,18 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
   }
   if (mode == 0 && d.family == NIMB_FAM_BERN_LOGIT_LIN && m->bern_ok[di] && !idx && C >= 32) {
     BernArgs ba = bern_args(m, di);
-    const int chunks = family_chunks(C, count, BF_TILE);
-    int npc = ((count + chunks - 1) / chunks + BF_TILE - 1) / BF_TILE * BF_TILE;
+    // one wave of equal blocks (3 resident CTAs per SM), each looping over its tiles: with few chains (64 in configs[3]) the
+    // grid is a few hundred CTAs and whole-wave quantisation would otherwise idle a third of the SMs
+    const int ctiles = (C + 31) / 32;
+    const int chunks = std::max(1, std::min(std::min(512, (148 * 3) / std::max(1, ctiles)), (count + 255) / 256));
+    int npc = ((count + chunks - 1) / chunks + 31) / 32 * 32;
     if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (bernoulli)");
     dim3 grid((C + 31) / 32, chunks);
-    k_bernlin_sum<<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    const bool latent = ba.vdata == nullptr, gated = ba.gate_slot >= 0;
+    if (latent && gated) k_bernlin_sum<true, true><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    else if (latent) k_bernlin_sum<true, false><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    else if (gated) k_bernlin_sum<false, true><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    else k_bernlin_sum<false, false><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
     m->launches++;
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
@@ -1969,7 +1976,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (dp.stage == 1 && dd.family == NIMB_FAM_POIS_LOGLIN && m->d_nodeconst[dp.decl] && dp.param == 0 &&
         dp.link == NIMB_LINK_MULTIPLICATIVE && sp.target_slot == dd.fam_arg[1] && m->deps[sp.dep_off].stage == 0) {
       m->pois_sweep[s] = 1;
-      TRY(dev_alloc(m, &m->d_pois_ysum[s], (size_t)sp.n_targets * 3));
+      TRY(dev_alloc(m, &m->d_pois_ysum[s], pois_stats_doubles((size_t)sp.n_targets)));
     }
   }
   m->bern_sweep.assign(m->samplers.size(), 0);
@@ -2061,6 +2068,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     if (m->pois_byp_slot[s] >= 0) TRY(dev_alloc(m, &m->d_pois_contrib[s], (size_t)sp.n_targets * C));
     // same eligibility (targets cover the declaration, small counts) for the group-sum path; two [targets][chains] arrays
     if (m->pois_byp_slot[s] >= 0 && !getenv("NIMB200_NO_GROUPSUMS") && (size_t)sp.n_targets * C * 16 < ((size_t)8 << 30)) {
+      m->pois_series = !getenv("NIMB200_NO_SERIES");
       TRY(dev_alloc(m, &m->d_pois_S[s], (size_t)sp.n_targets * C));
       TRY(dev_alloc(m, &m->d_pois_Snew[s], (size_t)sp.n_targets * C));
     }

@@ -32,49 +32,127 @@ __device__ __forceinline__ int bern_gate_index(const BernArgs& a, int i) {
   }
 }
 
-__device__ __forceinline__ double bernlin_lp(double v, double gate, double eta, const double* tab) {
+// scalar form: the exact generic path for anything irregular, the table-driven form otherwise (per lane, no warp vote)
+__device__ __forceinline__ double bernlin_lp(double v, double gate, double eta, const MathTab* tab) {
   bool v01 = v == 0.0 || v == 1.0;
-  if (v01 && gate == 1.0) return bern_logit_lp1(eta, v != 0.0, tab);
+  if (v01 && gate == 1.0) {
+    if (!(eta >= -690.0)) return bern_logit_lp_slow(eta, v != 0.0);
+    double in[1] = {eta}, o[1];
+    bern_logit_lp_vec<1, false, false>(in, v != 0.0, o, nullptr, tab);
+    return o[0];
+  }
   if (v01 && gate == 0.0 && eta == eta) return v == 0.0 ? 0.0 : -INFINITY;
   return dbinom(v, 1.0, gate * (1. / (1. + exp(-eta))));  // exact generic path
 }
 
+// out of line: the rare branches of the kernels below call it, and the hot loops stay small in the instruction cache
+static __device__ __noinline__ double bernlin_lp_cold(double v, double gate, double eta, const MathTab* tab) {
+  return bernlin_lp(v, gate, eta, tab);
+}
+
 static const int BF_THREADS = 256;
-static const int BF_TILE = 256;
+static const int BF_TILE = 2048;  // 32 KiB of staged nodes: a chunk is one or two tiles, so the staging latency is paid once
+static const int BF_W = 4;   // nodes in flight per lane: four independent exp / log chains keep the FP64 pipe fed
+
+// one staged node: 16 bytes (code: the data value 0 / 1, 2 = anything else)
+struct __align__(16) BernNode {
+  double x;
+  int code, g;
+};
+
+// is the double exactly 0.0 or 1.0?  On its bits (integer pipe): nonzero when it is neither
+__device__ __forceinline__ unsigned not01_bits(double v) {
+  const unsigned h = (unsigned)__double2hiint(v);
+  return (unsigned)__double2loint(v) | min(h, h ^ 0x3ff00000u);
+}
 
 // block sums: grid (chain tiles of 32, node chunks); lane = chain, the 8 warps of a CTA share the staged node tile
-// (warp w takes the w-th run of 32 consecutive nodes).  partials[chunk][C]
-__global__ void __launch_bounds__(BF_THREADS)
+// (warp w takes the w-th run of 256 consecutive nodes, BF_W at a time).  partials[chunk][C].
+// Round 2: (1) the softplus table cost 80 bytes of divergent shared-memory reads per evaluation and made this kernel
+// shared-memory-bound (ncu round 1: short_scoreboard 7.5 per issue, 87 instructions per evaluation); the exp / log-table form
+// of the fused logistic kernel reads 24 bytes, and BF_W evaluations per lane travel through it together.  (2) The per-chain
+// operands (gate = the latent site state, or the latent value itself) are loaded one trip ahead: their global-memory latency
+// was the top stall (long_scoreboard on the first use, 34 % of the samples).  (3) One instantiation per (latent, gated)
+// combination; the value / gate / predictor checks are integer tests on the bits, ORed into one flag per trip.
+template <bool LATENT, bool GATED>
+__global__ void __launch_bounds__(BF_THREADS, 3)
 k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
-  __shared__ double sx[BF_TILE], sv[BF_TILE];
-  __shared__ int sg[BF_TILE];
+  __shared__ BernNode sn[BF_TILE];
   __shared__ double red[BF_THREADS / 32][32];
-  __shared__ __align__(16) double tab[SOFTPLUS_DOUBLES];
-  load_softplus(tab, threadIdx.x, BF_THREADS);
+  __shared__ __align__(16) MathTab tab;
+  load_mathtab(&tab, threadIdx.x, BF_THREADS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = BF_THREADS / 32;
   const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
   const int cc = live ? c : T.C - 1;
-  const double c0 = T.state[(size_t)a.c0_slot * T.C + cc], c1 = T.state[(size_t)a.c1_slot * T.C + cc];
+  const size_t C = (size_t)T.C;
+  const double c0 = T.state[(size_t)a.c0_slot * C + cc], c1 = T.state[(size_t)a.c1_slot * C + cc];
   const int c_lo = lo + blockIdx.y * nodes_per_chunk, c_hi = min(hi, c_lo + nodes_per_chunk);
+  const double* __restrict__ gatep = T.state + (size_t)(GATED ? a.gate_slot : 0) * C + cc;
+  const double* __restrict__ valp = T.state + (size_t)(LATENT ? a.v_slot : 0) * C + cc;
   double acc = 0.0;
-  int gprev = -1;
-  double gate = 1.0;
   for (int t0 = c_lo; t0 < c_hi; t0 += BF_TILE) {
     __syncthreads();
-    int i = t0 + threadIdx.x;
-    if (i < c_hi) {
-      sx[threadIdx.x] = a.x[i];
-      if (a.vdata) sv[threadIdx.x] = a.vdata[i];
-      sg[threadIdx.x] = a.gate_slot >= 0 ? bern_gate_index(a, i) : 0;
+    for (int q = threadIdx.x; q < BF_TILE; q += BF_THREADS) {
+      const int i = t0 + q;
+      if (i < c_hi) {
+        BernNode nd;
+        nd.x = a.x[i];
+        const double v = LATENT ? 0.0 : a.vdata[i];
+        nd.code = v == 0.0 ? 0 : v == 1.0 ? 1 : 2;
+        nd.g = GATED ? bern_gate_index(a, i) : 0;
+        sn[q] = nd;
+      }
     }
     __syncthreads();
-    int cnt = min(BF_TILE, c_hi - t0);
-    const int per = BF_TILE / nw, k_hi = min(cnt, (warp + 1) * per);
-    for (int k = warp * per; k < k_hi; k++) {  // a contiguous run per warp: consecutive nodes mostly share the gate
-      if (a.gate_slot >= 0 && sg[k] != gprev) { gprev = sg[k]; gate = T.state[(size_t)(a.gate_slot + gprev) * T.C + cc]; }
-      double v = a.vdata ? sv[k] : T.state[(size_t)(a.v_slot + t0 + k) * T.C + cc];
-      acc += bernlin_lp(v, gate, fma(c1, sx[k], c0), tab);
+    const int cnt = min(BF_TILE, c_hi - t0);
+    const int per = ((cnt + nw - 1) / nw + BF_W - 1) & ~(BF_W - 1);   // a partial tile is still shared by all warps
+    const int k_lo = min(cnt, warp * per), k_hi = min(cnt, (warp + 1) * per);
+    const int k_full = k_lo + (max(0, k_hi - k_lo) & ~(BF_W - 1));
+    double gn[BF_W], vn[BF_W];   // the next trip's per-chain operands
+#pragma unroll
+    for (int j = 0; j < BF_W; j++) { gn[j] = 1.0; vn[j] = 0.0; }
+    auto fetch = [&](int k) {
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) {
+        if (GATED) gn[j] = gatep[(size_t)sn[k + j].g * C];
+        if (LATENT) vn[j] = valp[(size_t)(t0 + k + j) * C];
+      }
+    };
+    if (k_lo < k_full) fetch(k_lo);
+    for (int k = k_lo; k < k_full; k += BF_W) {
+      double eta[BF_W], gt[BF_W], vv[BF_W], lp[BF_W];
+      bool y1[BF_W];
+      unsigned irr = 0;
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) { gt[j] = gn[j]; vv[j] = vn[j]; }
+      if (k + BF_W < k_full) fetch(k + BF_W);
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) {
+        const BernNode nd = sn[k + j];
+        eta[j] = fma(c1, nd.x, c0);
+        // irregular: a value or gate that is not exactly 0 or 1, a linear predictor that is NaN or infinite
+        irr |= (unsigned)((__double2hiint(eta[j]) & 0x7ff00000) == 0x7ff00000);
+        if (LATENT) { y1[j] = __double2hiint(vv[j]) != 0; irr |= not01_bits(vv[j]); }
+        else { y1[j] = nd.code == 1; irr |= (unsigned)(nd.code & 2); }
+        if (GATED) irr |= not01_bits(gt[j]);
+      }
+      if (__any_sync(0xffffffffu, irr != 0)) {  // the scalar form sorts every case out (warp-uniform branch, practically never taken)
+#pragma unroll
+        for (int j = 0; j < BF_W; j++) acc += bernlin_lp_cold(LATENT ? vv[j] : a.vdata[t0 + k + j], gt[j], eta[j], &tab);
+        continue;
+      }
+      bern_logit_lp_vecy<BF_W, true, false>(eta, y1, lp, nullptr, &tab);
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) {
+        if (GATED) acc += __double2hiint(gt[j]) != 0 ? lp[j] : (y1[j] ? -INFINITY : 0.0);   // gate 0: dbinom(v, 1, 0)
+        else acc += lp[j];
+      }
+    }
+    for (int k = k_full; k < k_hi; k++) {   // at most BF_W - 1 nodes at the end of a chunk
+      const BernNode nd = sn[k];
+      const double v = LATENT ? valp[(size_t)(t0 + k) * C] : a.vdata[t0 + k];
+      acc += bernlin_lp_cold(v, GATED ? gatep[(size_t)nd.g * C] : 1.0, fma(c1, nd.x, c0), &tab);
     }
   }
   red[warp][lane] = acc;
@@ -88,11 +166,12 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
 
 // binary Gibbs sweep over latent 0/1 targets z[t] whose prior is  z[t] ~ dbern(ilogit(b0 + b1 xz[t]))  (pz) and whose dependents
 // are the data nodes of  y ~ dbern(z[G] * ilogit(a0 + a1 w))  (py) selected by the sampler's stage-1 entry.
+// With z = 0 a visit contributes 0 (y = 0) or -Inf (y = 1): only the z = 1 state needs the link, two visits at a time.
 __global__ void __launch_bounds__(BF_THREADS)
 k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs pz, BernArgs py, double* __restrict__ contrib_z,
                        double* __restrict__ contrib_y) {
-  __shared__ __align__(16) double tab[SOFTPLUS_DOUBLES];
-  load_softplus(tab, threadIdx.x, BF_THREADS);
+  __shared__ __align__(16) MathTab tab;
+  load_mathtab(&tab, threadIdx.x, BF_THREADS);
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -107,14 +186,64 @@ k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs
   const double b0 = T.state[(size_t)pz.c0_slot * T.C + c], b1 = T.state[(size_t)pz.c1_slot * T.C + c];
   const double a0 = T.state[(size_t)py.c0_slot * T.C + c], a1 = T.state[(size_t)py.c1_slot * T.C + c];
   const double eta_z = fma(b1, pz.x[znode], b0);
-  double curPrior = bernlin_lp(cur, 1.0, eta_z, tab), otherPrior = bernlin_lp(other, 1.0, eta_z, tab);
-  double curDeps = 0.0, otherDeps = 0.0;
-  Sel s = sel_of(T, d1, t);
-  for (int k = s.lo; k < s.hi; k++) {
-    int node = s.idx ? s.idx[k] : k;
-    double eta = fma(a1, py.x[node], a0), yv = py.vdata[node];
-    curDeps += bernlin_lp(yv, cur, eta, tab);
-    otherDeps += bernlin_lp(yv, other, eta, tab);
+  const Sel s = sel_of(T, d1, t);
+  double curPrior, otherPrior, curDeps = 0.0, otherDeps = 0.0;
+  bool fast = not01_bits(cur) == 0 && (__double2hiint(eta_z) & 0x7ff00000) != 0x7ff00000;
+  if (fast) {
+    const bool z1 = __double2hiint(cur) != 0;
+    {  // the prior under z = 1 and z = 0: one predictor, both values
+      const double e2[2] = {eta_z, eta_z};
+      const bool y2[2] = {true, false};
+      double l2[2];
+      bern_logit_lp_vecy<2, false, false>(e2, y2, l2, nullptr, &tab);
+      curPrior = z1 ? l2[0] : l2[1];
+      otherPrior = z1 ? l2[1] : l2[0];
+    }
+    // the visits' log-density with z = 1 (sum1, in visit order); with z = 0 it is 0, or -Inf once a visit detected the species.
+    // Two visits per trip, the next trip's (x, y) loaded before this trip's arithmetic (their latency was the top stall).
+    double sum1 = 0.0, xn[2], yn[2];
+    bool seen = false;
+    auto fetch = [&](int k) {
+#pragma unroll
+      for (int j = 0; j < 2; j++) {
+        const int kk = min(k + j, s.hi - 1);
+        const int node = s.idx ? s.idx[kk] : kk;
+        xn[j] = __ldg(py.x + node);
+        yn[j] = __ldg(py.vdata + node);
+      }
+    };
+    if (s.lo < s.hi) fetch(s.lo);
+    for (int k = s.lo; k < s.hi; k += 2) {
+      double eta[2], lp[2];
+      bool y1[2];
+      unsigned irr = 0;
+#pragma unroll
+      for (int j = 0; j < 2; j++) {
+        eta[j] = fma(a1, xn[j], a0);
+        y1[j] = __double2hiint(yn[j]) != 0;
+        irr |= not01_bits(yn[j]) | (unsigned)((__double2hiint(eta[j]) & 0x7ff00000) == 0x7ff00000);
+      }
+      if (k + 2 < s.hi) fetch(k + 2);
+      if (irr) { fast = false; break; }
+      bern_logit_lp_vecy<2, false, false>(eta, y1, lp, nullptr, &tab);
+      sum1 += lp[0];
+      seen |= y1[0];
+      if (k + 1 < s.hi) { sum1 += lp[1]; seen |= y1[1]; }
+    }
+    const double sum0 = seen ? -INFINITY : 0.0;
+    curDeps = z1 ? sum1 : sum0;
+    otherDeps = z1 ? sum0 : sum1;
+  }
+  if (!fast) {  // anything irregular: visit by visit through the scalar form
+    curPrior = bernlin_lp_cold(cur, 1.0, eta_z, &tab);
+    otherPrior = bernlin_lp_cold(other, 1.0, eta_z, &tab);
+    curDeps = 0.0; otherDeps = 0.0;
+    for (int k = s.lo; k < s.hi; k++) {
+      int node = s.idx ? s.idx[k] : k;
+      double eta = fma(a1, py.x[node], a0), yv = py.vdata[node];
+      curDeps += bernlin_lp_cold(yv, cur, eta, &tab);
+      otherDeps += bernlin_lp_cold(yv, other, eta, &tab);
+    }
   }
   double currentLogProb = curPrior + curDeps;
   double otherLogProb = (otherPrior == -INFINITY) ? otherPrior : otherPrior + otherDeps;

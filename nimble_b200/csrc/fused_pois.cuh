@@ -54,10 +54,16 @@ __global__ void k_pois_pack(PoisArgs a, PoisNode* __restrict__ out) {
   out[i] = nd;
 }
 
-// fast form; ok = false -> the value is discarded and the element is redone by pois_exact_run
-__device__ __forceinline__ double pois_fast(const PoisNode& nd, double lam, double L, double b0, double b1,
-                                            const double* __restrict__ expT, const double (&K)[7], bool& ok) {
-  const double eta = fma(b1, nd.x, b0);
+// table-driven exp (fastmath.cuh), |eta| < 700: 12 FP64 instructions, one 8-byte look-up, four integer instructions
+// (n & 63 -> table address, n & ~63 -> exponent increment: (n >> 6) << 20 = (n & ~63) * 2^14).
+// The table is held once per lane, expT[j][lane] (16 KiB per CTA; the argument points at this lane's column): the 32 lanes'
+// look-ups land in 32 different bank pairs whatever their indices, exactly two wavefronts -- with one shared 64-entry copy the
+// data-dependent indices cost 4.8 wavefronts per look-up and made the load/store pipe the busiest unit (ncu r2k: 72 %).
+static const int PF_EXPT_DOUBLES = 64 * 32;
+__device__ __forceinline__ void pois_load_expT(double* dst, int tid, int nthreads) {
+  for (int i = tid; i < PF_EXPT_DOUBLES; i += nthreads) dst[i] = g_mathtab.expT[i >> 5];
+}
+__device__ __forceinline__ double pois_exp_core(double eta, const double* __restrict__ expT, const double (&K)[7]) {
   double t = fma(eta, K[0], K[1]);
   const int n = __double2loint(t);
   t = t - K[1];
@@ -67,16 +73,29 @@ __device__ __forceinline__ double pois_fast(const PoisNode& nd, double lam, doub
   pl = fma(pl, r, K[6]);
   pl = fma(pl, r, 0.5);
   pl = fma(pl, r, 1.0);
-  const double Tj = expT[n & 63];
+  const double Tj = expT[(n & 63) * 32];
   const double v = fma(Tj * r, pl, Tj);
-  const double e = __hiloint2double(__double2hiint(v) + ((n >> 6) << 20), __double2loint(v));
-  const double mu = lam * e;
-  ok = (unsigned)(__double2hiint(eta) & 0x7fffffff) < 0x4085e000u &&                       // |eta| < 700, not NaN
-       (unsigned)(__double2hiint(mu) - 0x03c00000) < (unsigned)(0x7c300000 - 0x03c00000);  // 2^-963 <= mu < 2^964, not NaN
+  return __hiloint2double(__double2hiint(v) + (n & ~63) * 16384, __double2loint(v));
+}
+// the same with the range check folded into a running maximum of |eta|'s high word (integer pipe)
+__device__ __forceinline__ double pois_exp(double eta, const double* __restrict__ expT, const double (&K)[7], unsigned& worst) {
+  worst = max(worst, (unsigned)(__double2hiint(eta) & 0x7fffffff));
+  return pois_exp_core(eta, expT, K);
+}
+// a run is regular when every |eta| < 300 (not NaN: x is NaN for y > 1024) and every lam lies in [1e-150, 1e150]: then
+// mu = lam exp(eta) is a normal number and the fast form below is the density to ~4e-13 relative
+static const unsigned PF_ETA_LIMIT = 0x4072c000u;   // high word of 300.0
+__device__ __forceinline__ bool pois_lam_regular(double lam) { return lam >= 1e-150 && lam <= 1e150; }
+
+__device__ __forceinline__ double pois_fast(const PoisNode& nd, double lam, double L, double b0, double b1,
+                                            const double* __restrict__ expT, const double (&K)[7], unsigned& worst) {
+  const double eta = fma(b1, nd.x, b0);
+  const double mu = lam * pois_exp(eta, expT, K, worst);
   return fma(nd.y, L + eta, nd.A) - mu;
 }
 
-// exact generic path for the elements of a run that pois_fast refused (rare: kept out of line, out of the hot loop)
+// a run that holds an irregular element, redone element by element: the fast form where it applies, the generic density
+// elsewhere (rare: kept out of line, out of the hot loop)
 __device__ __noinline__ double pois_exact_run(const double* __restrict__ ya, const double* __restrict__ xa, const PoisNode* sn,
                                               int k_lo, int k_hi, int t0, const double* lamp, size_t C, double b0, double b1,
                                               const double* expT) {
@@ -87,27 +106,30 @@ __device__ __noinline__ double pois_exact_run(const double* __restrict__ ya, con
   for (int k = k_lo; k < k_hi; k++) {
     const PoisNode nd = sn[k];
     const double lam = lamp[(size_t)nd.g * C];
-    const bool lam_ok = lam > 0.0 && lam < 1e300;
-    bool ok;
-    pois_fast(nd, lam_ok ? lam : NAN, 0.0, b0, b1, expT, K, ok);
-    if (!ok) s += dpois(ya[t0 + k], lam * exp(fma(b1, xa[t0 + k], b0)));
+    unsigned w = 0;
+    const double v = pois_fast(nd, lam, log(lam), b0, b1, expT, K, w);
+    if (w < PF_ETA_LIMIT && pois_lam_regular(lam)) s += v;
+    else s += dpois(ya[t0 + k], lam * exp(fma(b1, xa[t0 + k], b0)));
   }
   return s;
 }
 
 static const int PF_THREADS = 256;  // 8 warps x 32 chains
-static const int PF_TILE = 1024;    // nodes staged per step
+static const int PF_TILE = 512;     // nodes staged per step (16 KiB; with the 16 KiB exp table the static shared memory stays under 48 KiB)
 
 // block sums: grid (chain tiles of 32, node chunks); lane = chain (lam gathers coalesced over the warp), the 8 warps of a
-// CTA share the staged node tile (warp w takes the w-th run of 128 consecutive nodes, two nodes per trip so that two
+// CTA share the staged node tile (warp w takes the w-th run of 64 consecutive nodes, two nodes per trip so that two
 // independent dependency chains are in flight).  partials[chunk][C].
+// Round 2: 16 FP64 instructions per evaluation against ~14 others (round 1: 16.5 against 31.5, issue-bound) -- the per-element
+// range tests and selects became one running maximum per run, the group test is per pair of nodes.
 __global__ void __launch_bounds__(PF_THREADS, 3)
 k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
   __shared__ PoisNode sn[PF_TILE];
   __shared__ double red[PF_THREADS / 32][32];
-  __shared__ double expT[64];
-  if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
+  __shared__ double expTs[PF_EXPT_DOUBLES];
+  pois_load_expT(expTs, threadIdx.x, PF_THREADS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = PF_THREADS / 32;
+  const double* __restrict__ expT = expTs + lane;
   const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
   const int cc = live ? c : T.C - 1;
@@ -119,8 +141,6 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
 #pragma unroll
   for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
   double acc0 = 0.0, acc1 = 0.0;
-  int gprev = -1;
-  double lam = 0.0, L = 0.0;
   for (int t0 = c_lo; t0 < c_hi; t0 += PF_TILE) {
     const int cnt = min(PF_TILE, c_hi - t0);
     __syncthreads();
@@ -131,35 +151,34 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
     }
     __syncthreads();
     const int per = PF_TILE / nw, k_lo = warp * per, k_hi = min(cnt, (warp + 1) * per);
-    bool bad = false;
-    auto regroup = [&](int g) {  // new group: this chain's lam and its logarithm (non-positive / huge / NaN -> exact path)
+    int gprev = -1;
+    double lam = 0.0, L = 0.0, r0 = 0.0, r1 = 0.0;
+    unsigned worst = 0;
+    auto regroup = [&](int g) {  // new group: this chain's lam and its logarithm
       gprev = g;
       lam = lamp[(size_t)g * C];
-      if (!(lam > 0.0 && lam < 1e300)) lam = NAN;
+      if (!pois_lam_regular(lam)) worst = 0x7ff00000u;
       L = log(lam);
     };
     int k = k_lo;
     for (; k + 1 < k_hi; k += 2) {
       const PoisNode n0 = sn[k], n1 = sn[k + 1];
-      if (n0.g != gprev) regroup(n0.g);
-      const double lam0 = lam, L0 = L;
-      if (n1.g != gprev) regroup(n1.g);
-      bool ok0, ok1;
-      const double v0 = pois_fast(n0, lam0, L0, b0, b1, expT, K, ok0);
-      const double v1 = pois_fast(n1, lam, L, b0, b1, expT, K, ok1);
-      acc0 += ok0 ? v0 : 0.0;
-      acc1 += ok1 ? v1 : 0.0;
-      bad |= !(ok0 && ok1);
+      double lam0 = lam, L0 = L;
+      if ((n0.g ^ gprev) | (n1.g ^ gprev)) {   // node-level, hence warp-uniform
+        if (n0.g != gprev) regroup(n0.g);
+        lam0 = lam; L0 = L;
+        if (n1.g != gprev) regroup(n1.g);
+      }
+      r0 += pois_fast(n0, lam0, L0, b0, b1, expT, K, worst);
+      r1 += pois_fast(n1, lam, L, b0, b1, expT, K, worst);
     }
     if (k < k_hi) {
       const PoisNode n0 = sn[k];
       if (n0.g != gprev) regroup(n0.g);
-      bool ok0;
-      const double v0 = pois_fast(n0, lam, L, b0, b1, expT, K, ok0);
-      acc0 += ok0 ? v0 : 0.0;
-      bad |= !ok0;
+      r0 += pois_fast(n0, lam, L, b0, b1, expT, K, worst);
     }
-    if (bad) acc1 += pois_exact_run(a.y, a.x, sn, k_lo, k_hi, t0, lamp, C, b0, b1, expT);
+    if (worst >= PF_ETA_LIMIT) acc1 += pois_exact_run(a.y, a.x, sn, k_lo, k_hi, t0, lamp, C, b0, b1, expT);
+    else { acc0 += r0; acc1 += r1; }
   }
   red[warp][lane] = acc0 + acc1;
   __syncthreads();
@@ -170,24 +189,51 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
   }
 }
 
-// data-only sums over each target's nodes, computed once per sampler: stats[t] = sum y (integers: exact in any order),
-// stats[nT + t] = sum of the node constants A, stats[2 nT + t] = sum x y -- the last two serve the block-sum by-product below
+// data-only statistics of each target's nodes, computed once per sampler: stats[t] = sum y (integers: exact in any order),
+// stats[nT + t] = sum of the node constants A, stats[2 nT + t] = sum x y -- these two serve the block-sum by-product below --
+// stats[3 nT + t] = xm = max |x| (this rank's nodes), and from stats[4 nT] on the scaled moments
+//   mom[t][k] = sum_i (x_i / xm)^k / k!,  k = 0 .. PF_MOM_K,
+// the coefficients of the group's moment series (k_pois_S).
+static const int PF_MOM_K = 24;
+static const int PF_MOM_N = PF_MOM_K + 1;
+static const double PF_MOM_UMAX = 2.0;   // the series serves |b1| max|x| <= 2
+__host__ __device__ inline size_t pois_stats_doubles(size_t nT) { return nT * (4 + PF_MOM_N); }
 __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode* __restrict__ pk, double* __restrict__ stats) {
   const nimb200_sampler sp = T.samplers[sid];
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= sp.n_targets) return;
   const nimb200_dep dp = T.deps[sp.dep_off + 1];
   Sel s = sel_of(T, dp, t);
-  double c0 = 0.0, sa = 0.0, sxy = 0.0;
+  double c0 = 0.0, sa = 0.0, sxy = 0.0, xm = 0.0;
   for (int k = s.lo; k < s.hi; k++) {
     int node = s.idx ? s.idx[k] : k;
     c0 += a.y[node];
     sa += pk[node].A;
     sxy += a.x[node] * a.y[node];
+    const double ax = fabs(a.x[node]);
+    xm = ax <= xm ? xm : ax;   // a NaN sticks (and then disables the group-sum path for this target)
   }
   stats[t] = c0;
   stats[(size_t)sp.n_targets + t] = sa;
   stats[2 * (size_t)sp.n_targets + t] = sxy;
+  stats[3 * (size_t)sp.n_targets + t] = xm;
+  double mom[PF_MOM_N];
+#pragma unroll
+  for (int k = 0; k < PF_MOM_N; k++) mom[k] = 0.0;
+  const bool usable = xm > 0.0 && xm < 1e300;   // all-zero covariates: mom[0] = n is the whole series
+  for (int k = s.lo; k < s.hi; k++) {
+    const int node = s.idx ? s.idx[k] : k;
+    const double r = usable ? a.x[node] / xm : 0.0;
+    double term = 1.0;   // r^k / k!
+#pragma unroll
+    for (int j = 0; j < PF_MOM_N; j++) {
+      mom[j] += term;
+      term = term * r / (double)(j + 1);
+    }
+  }
+  double* out = stats + 4 * (size_t)sp.n_targets + (size_t)t * PF_MOM_N;
+#pragma unroll
+  for (int k = 0; k < PF_MOM_N; k++) out[k] = mom[k];
 }
 
 // conjugate gamma-Poisson sweep over the lam[g] targets (MCMC_conjugacy.R:80-93: contribution_shape = value,
@@ -286,6 +332,86 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
     if (nl == 0.0) v = c0 == 0.0 ? 0.0 : -INFINITY;        // dpois(y, 0)
     else v = ((sa + c0 * (log(nl) + b0)) + b1 * sxy) - nl * c1;
     contrib[(size_t)t * T.C + c] = v;
+  }
+}
+
+// S[t][c] = sum over target t's nodes of exp(b1_c x_i): what an iteration of the group-sum path still computes when b1 moves.
+// Moment series (round 2): with u = b1 xm,  sum_i exp(b1 x_i) = sum_k u^k mom[t][k]  -- the group's covariates enter through
+// PF_MOM_N data-only coefficients, so a (target, chain) costs 24 fused multiply-adds (Horner) instead of one exp per node
+// (~1200 FP64 instructions for the benchmark's 100 nodes per group).  Truncation: |u| <= 2 leaves 2^25/25! = 2e-18 of n;
+// rounding: the terms are bounded by n e^|u| against a sum of at least n e^-|u|, i.e. <= e^4 x a few ulp.  Chains with
+// |u| > 2 take the node loop below: grid (chain tiles of 32, blocks of PS3_TPB targets), lane = chain, warp w takes targets
+// w, w + 8, ..; the warp stages the covariates in shared memory (coalesced loads, broadcast reads), four nodes per trip = four
+// independent 12-instruction exp chains per lane and five other instructions per evaluation.
+// A (target, chain) whose |b1| max|x| reaches 300 (or is NaN) is marked NaN -- its users then take their exact per-node paths,
+// because exp(b0) exp(b1 x) and exp(b0 + b1 x) part ways once either factor over- or underflows.  Targets sharded by ownership
+// (group-aligned shards): the owner alone computes a target's S.
+static const int PS3_TPB = 64;
+static const int PS3_XCH = 128;   // nodes of a target staged per step and warp
+__global__ void __launch_bounds__(PF_THREADS, 4)
+k_pois_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double* __restrict__ S, int use_series) {
+  __shared__ double expTs[PF_EXPT_DOUBLES];
+  __shared__ __align__(16) double xs[PF_THREADS / 32][PS3_XCH];
+  pois_load_expT(expTs, threadIdx.x, PF_THREADS);
+  __syncthreads();
+  const nimb200_sampler sp = T.samplers[sid];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double* __restrict__ expT = expTs + lane;
+  const int c = blockIdx.x * 32 + lane;
+  const int cc = c < T.C ? c : T.C - 1;
+  const size_t C = (size_t)T.C;
+  const double b1 = T.state[(size_t)a.b1_slot * C + cc];
+  const nimb200_dep tp0 = T.deps[sp.dep_off], dp = T.deps[sp.dep_off + 1];
+  const int t_lo = blockIdx.y * PS3_TPB, t_hi = min(sp.n_targets, t_lo + PS3_TPB);
+  const double* __restrict__ xmax = stats + 3 * (size_t)sp.n_targets;
+  const double* __restrict__ mom = stats + 4 * (size_t)sp.n_targets;
+  double K[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
+  const double* __restrict__ xa = a.x;
+  double* __restrict__ xw = xs[warp];
+  double sser = 0.0;
+  for (int t = t_lo + warp; t < t_hi; t += PF_THREADS / 32) {
+    const int tn = (tp0.sel == NIMB_SEL_SAME ? tp0.a + t : tp0.a);
+    if (tn < T.shard_lo[tp0.decl] || tn >= T.shard_hi[tp0.decl]) continue;
+    const Sel s = sel_of(T, dp, t);
+    const double u = b1 * xmax[t];
+    const bool regular = fabs(u) < 300.0;
+    const bool series = use_series && fabs(u) <= PF_MOM_UMAX;
+    if (use_series) {   // Horner on the 25 coefficients (the same addresses for all lanes: broadcast loads)
+      const double* __restrict__ mk = mom + (size_t)t * PF_MOM_N;
+      double h = __ldg(mk + PF_MOM_K);
+#pragma unroll
+      for (int k = PF_MOM_K - 1; k >= 0; k--) h = fma(h, u, __ldg(mk + k));
+      if (__all_sync(0xffffffffu, series)) {
+        if (c < T.C) S[(size_t)t * C + c] = h;
+        continue;
+      }
+      if (series) sser = h;
+    }
+    const double bb = regular ? b1 : 0.0;   // keeps the table index in range; the result is discarded
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int k0 = s.lo; k0 < s.hi; k0 += PS3_XCH) {
+      // the warp stages the next (up to) 128 covariates of the target: coalesced loads, then broadcast 16-byte reads
+      const int cnt = min(PS3_XCH, s.hi - k0);
+      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < PS3_XCH / 32; q++) {
+        const int k = k0 + q * 32 + lane;
+        if (k < s.hi) xw[q * 32 + lane] = __ldg(xa + (s.idx ? s.idx[k] : k));
+      }
+      __syncwarp();
+      int k = 0;
+      for (; k + 3 < cnt; k += 4) {
+        const double2 xa01 = *reinterpret_cast<const double2*>(xw + k), xa23 = *reinterpret_cast<const double2*>(xw + k + 2);
+        s0 += pois_exp_core(bb * xa01.x, expT, K);
+        s1 += pois_exp_core(bb * xa01.y, expT, K);
+        s2 += pois_exp_core(bb * xa23.x, expT, K);
+        s3 += pois_exp_core(bb * xa23.y, expT, K);
+      }
+      for (; k < cnt; k++) s0 += pois_exp_core(bb * xw[k], expT, K);
+    }
+    if (c < T.C) S[(size_t)t * C + c] = series ? sser : regular ? (s0 + s1) + (s2 + s3) : NAN;
   }
 }
 

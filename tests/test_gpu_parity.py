@@ -330,6 +330,32 @@ def test_pois_family_block_sums_and_edges(oracle, b200):
     assert rel_err(dg.calculate(y, 256, 3072), do.calculate(y, 256, 3072)).max() < RTOL_LP
 
 
+def test_pois_moment_series_and_node_pass_agree(oracle, b200, monkeypatch):
+    """Group sums S_g(b1) = sum exp(b1 x): the data-only moment series (|b1| max|x| <= 2) and the node pass give the same block
+    sums as the oracle; chains on both sides of the switch share warps, some far outside it."""
+    m, conf = sm.SMALL["glmm"]()
+    C = 96
+    inits = sm.random_inits(m, C, 9, 0.2)
+    b1s = m.var_slot["b1"]
+    inits[:, b1s] = np.linspace(-3.0, 3.0, C)          # max|x| ~ 3 in the small model: |u| runs from 0 to ~9
+    inits[5, b1s], inits[40, b1s], inits[41, b1s] = 150.0, -400.0, 0.0
+    co = compile_on(oracle, conf)
+    do = co._ensure(C)
+    do.set_values(inits)
+    y = len(co.builder.decls) - 1
+    want = do.calculate(y)
+    got = {}
+    for label, env in (("series", None), ("nodes", "1")):
+        if env:
+            monkeypatch.setenv("NIMB200_NO_SERIES", env)
+        dg = compile_on(b200, conf)._ensure(C)
+        dg.set_values(inits)
+        got[label] = dg.calculate(y)
+        assert np.array_equal(np.isnan(got[label]), np.isnan(want)) and np.array_equal(np.isinf(got[label]), np.isinf(want)), label
+        assert rel_err(got[label], want).max() < RTOL_LP, (label, rel_err(got[label], want).max())
+    assert rel_err(got["series"], got["nodes"]).max() < 1e-13
+
+
 def test_pois_family_trajectories(oracle, b200):
     m, conf = sm.SMALL["glmm"]()
     inits = sm.random_inits(m, 40, 8, 0.1)
