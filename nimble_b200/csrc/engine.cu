@@ -57,9 +57,17 @@ __device__ __forceinline__ double ld_state(const DevTab& T, int slot, int c, int
 }
 
 __device__ double eval_prog(const DevTab& T, int c, int off, int len, int i, int j, int ov_slot, double ov_val) {
+  const nimb200_op* ops = T.ops + off;
+  if (len >= 1 && len <= 2) {  // a constant or a chain variable, possibly inverted (rate -> scale): no stack, no dispatch loop
+    const nimb200_op o0 = ops[0];
+    if (o0.op == NIMB_OP_CONST || o0.op == NIMB_OP_CVAR) {
+      const double v = o0.op == NIMB_OP_CONST ? o0.k : ld_state(T, o0.a, c, ov_slot, ov_val);
+      if (len == 1) return v;
+      if (ops[1].op == NIMB_OP_INV) return 1. / v;
+    }
+  }
   double stk[16];
   int sp = 0;
-  const nimb200_op* ops = T.ops + off;
   for (int q = 0; q < len; q++) {
     const nimb200_op o = ops[q];
     switch (o.op) {
@@ -771,6 +779,71 @@ __global__ void k_reduce(const double* __restrict__ partials, int nb, int K, int
   if (lane == 0) (kk == 0 ? dst0 : dst1)[c] = s;
 }
 
+// ---- i.i.d. gamma declarations with chain-level parameters:  x[i] ~ dgamma(shape, scale),  x latent, i = 1..n
+// (the random-effect layer of configs[4]: lam[g] ~ dgamma(a, b)).  Its block sum and its conjugate contributions depend on the n
+// values only through  SL = sum log x  and  SM = sum x:
+//   sum_i dgamma(x_i) = n (-shape log scale - lgamma(shape)) + (shape - 1) SL - SM / scale,
+//   contributions to a dgamma prior on the rate (MCMC_conjugacy.R:85): (n shape, coeff SM).
+// k_gamma_stats makes one pass over the values when they have changed (fixed order: lane = chain, chunk partials, k_reduce);
+// k_gamma_from_stats serves every evaluation until the next change -- the RW step on the shape (two evaluations) and the
+// conjugate update of the rate cost O(1) per chain instead of three passes with one logarithm per node each.
+// A chain with a non-positive / non-finite value, or parameters outside the closed form's range, walks the nodes exactly as
+// k_eval does.
+static const int GS_ROWS = 256;
+__global__ void __launch_bounds__(256) k_gamma_stats(DevTab T, int di, double* __restrict__ partials) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
+  __shared__ double red[2][8][32];
+  const nimb200_decl& d = T.decl[di];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  const int r0 = blockIdx.y * GS_ROWS, r1 = min(d.n, r0 + GS_ROWS);
+  double sl = 0.0, sm = 0.0;
+  if (c < T.C) {
+    const double* __restrict__ xp = T.state + (size_t)d.value_ref * T.C + c;
+    for (int r = r0 + warp; r < r1; r += 8) {
+      const double x = xp[(size_t)r * T.C];
+      sl += log(x);
+      sm += x;
+    }
+  }
+  red[0][warp][lane] = sl; red[1][warp][lane] = sm;
+  __syncthreads();
+  if (warp < 2 && c < T.C) {
+    double s = 0.0;
+    for (int w = 0; w < 8; w++) s += red[warp][w][lane];
+    partials[((size_t)blockIdx.y * 2 + warp) * T.C + c] = s;
+  }
+}
+// MODE 0: block sum -> dst0.  MODE 2: conjugate contributions of the n dependents -> (dst0, dst1).
+template <int MODE>
+__global__ void k_gamma_from_stats(DevTab T, int di, const double* __restrict__ stats, nimb200_dep dp, int slot, int gam,
+                                   double* __restrict__ dst0, double* __restrict__ dst1) {
+  cudaTriggerProgrammaticLaunchCompletion();
+  cudaGridDependencySynchronize();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_decl& d = T.decl[di];
+  const double SL = stats[c], SM = stats[(size_t)T.C + c];
+  const bool fin = isfinite(SL) && isfinite(SM);
+  if (MODE == 0) {
+    const Hoist H = make_hoist(T, di, c, -1, 0.0);
+    if (H.gfast && fin) { dst0[c] = fma(H.p0 - 1.0, SL, (double)d.n * H.l1) - SM / H.p1; return; }
+    double a = 0.0;
+    for (int i = 0; i < d.n; i++) a += calc_node_h(T, di, i, c, -1, 0.0, H);
+    dst0[c] = a;
+  } else {
+    bool hp = false;
+    const double par = conj_par(T, dp, 0, c, gam, &hp);
+    double coeff = 1.0;
+    if (dp.link == NIMB_LINK_MULTIPLICATIVE) coeff = get_param(T, dp.decl, 0, c, dp.param, slot, 1.0);
+    if (fin && hp) { dst0[c] = (double)d.n * par; dst1[c] = coeff * SM; return; }
+    double a0 = 0.0, a1 = 0.0;
+    for (int i = 0; i < d.n; i++) conj_contrib(T, dp, i, c, slot, gam, a0, a1, hp, par);
+    dst0[c] = a0; dst1[c] = a1;
+  }
+}
+
 // wide RW: proposal for every chain; the old value is parked in tsave
 __global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* tsave, double* pls) {
   cudaTriggerProgrammaticLaunchCompletion();
@@ -1123,6 +1196,9 @@ struct nimb200_model {
   // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
   std::vector<double*> d_pois_S, d_pois_Snew;
   std::vector<char> pois_S_valid, pois_S_pending;
+  // i.i.d. gamma declarations with chain-level parameters (k_gamma_stats): eligibility, [2][C] statistics, validity
+  std::vector<char> gam_iid, gam_stats_valid;
+  std::vector<double*> d_gam_stats;
   bool pois_series = true;   // group sums from the data-only moment series (fused_pois.cuh); NIMB200_NO_SERIES=1 keeps the node pass
   SmallPlan small{};                // whole-iteration kernel for small all-sweep models (k_small_iters); small.n == 0: not eligible
   SamplerDev* d_sdev = nullptr;     // device copy of sdev[] for it
@@ -1559,6 +1635,27 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     if (shard && comm_on(m)) return allreduce_sum(m, dst0, C);
     return 0;
   }
+  if (di < (int)m->gam_iid.size() && m->gam_iid[di] && !idx && !shard && lo == 0 && hi == d.n &&
+      (mode == 0 || (mode == 2 && gam == 1 && dp && dp->decl == di && (dp->link == NIMB_LINK_IDENTITY || dp->link == NIMB_LINK_MULTIPLICATIVE)))) {
+    // i.i.d. gamma layer with chain-level parameters: from (sum log x, sum x), recomputed when a sampler has moved the values
+    const int chunks = (d.n + GS_ROWS - 1) / GS_ROWS;
+    if ((size_t)chunks * 2 * C <= m->partials_cap) {
+      if (!m->gam_stats_valid[di]) {
+        CK(launch_pdl(k_gamma_stats, dim3((C + 31) / 32, chunks), dim3(256), 0, m->stream, m->T, di, m->d_partials));
+        CK(launch_pdl(k_reduce, dim3((C * 2 * 32 + 127) / 128), dim3(128), 0, m->stream, (const double*)m->d_partials, chunks, 2, C,
+                      m->d_gam_stats[di], m->d_gam_stats[di] + C));
+        m->launches += 2;
+        m->gam_stats_valid[di] = 1;
+      }
+      nimb200_dep dd{};
+      if (dp) dd = *dp;
+      if (mode == 0) CK(launch_pdl(k_gamma_from_stats<0>, dim3((C + 127) / 128), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
+      else CK(launch_pdl(k_gamma_from_stats<2>, dim3((C + 127) / 128), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
+      m->launches++;
+      CK(cudaGetLastError());
+      return 0;
+    }
+  }
   int nt = eval_tiles(C, count);
   int K = mode == 2 ? 2 : 1;
   if ((size_t)nt * K * C > m->partials_cap) return fail("internal: partials scratch too small");
@@ -1811,6 +1908,15 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     TRYCU(cudaMemcpyAsync(dpc, pc.data(), sizeof(int32_t) * pc.size(), cudaMemcpyHostToDevice, m->stream));
     TRYCU(cudaStreamSynchronize(m->stream));
     m->T.pconst = dpc;
+    m->gam_iid.assign(m->decl.size(), 0);
+    m->gam_stats_valid.assign(m->decl.size(), 0);
+    m->d_gam_stats.assign(m->decl.size(), nullptr);
+    for (size_t i = 0; i < m->decl.size() && !getenv("NIMB200_NO_GAMMA_STATS"); i++) {
+      const nimb200_decl& d = m->decl[i];
+      if (d.dist != NIMB_DGAMMA || d.value_kind != 1 || d.nparam < 2 || !pc[3 * i] || !pc[3 * i + 1] || d.n < 256) continue;
+      m->gam_iid[i] = 1;
+      TRY(dev_alloc(m, &m->d_gam_stats[i], (size_t)2 * m->C));
+    }
   }
   TRY(dev_alloc(m, &m->d_ctr, 2));
   TRYCU(cudaMemsetAsync(m->d_ctr, 0, 2 * sizeof(unsigned long long), m->stream));
@@ -2153,6 +2259,7 @@ extern "C" int nimb200_set_values(nimb200_model* m, const double* v) {
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->gam_stats_valid.begin(), m->gam_stats_valid.end(), 0);
   std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   return 0;
 }
@@ -2375,6 +2482,7 @@ static int set_shards(nimb200_model* m, int32_t nranks, int32_t rank, int32_t mi
   CK(cudaStreamSynchronize(m->stream));
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->gam_stats_valid.begin(), m->gam_stats_valid.end(), 0);
   std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
   return 0;
@@ -2580,9 +2688,19 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
         const int tdecl = m->deps[sp.dep_off].decl;
         const int t_lo = own ? m->shard_lo[tdecl] : 0, t_hi = own ? m->shard_hi[tdecl] : sp.n_targets;
         double* cache = m->d_depcache + (size_t)m->pois_byp_slot[s] * C;
-        CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, (const double*)(m->d_pois_contrib[s] + (size_t)t_lo * C),
-                      std::max(0, t_hi - t_lo), 1, C, cache, (double*)nullptr));
-        m->launches++;
+        const int rows = std::max(0, t_hi - t_lo), cchunks = (rows + CS_ROWS - 1) / CS_ROWS;
+        if (rows > 1024 && (size_t)cchunks * C <= m->partials_cap) {
+          // many targets: coalesced column sums over chunks of rows first (k_reduce alone reads a column per warp, 32-byte
+          // sectors for 8 bytes: 0.46 ms for the benchmark's 655 MB), then the fixed-order sum of the chunk partials
+          k_colsum<<<dim3((C + 31) / 32, cchunks), 256, 0, m->stream>>>(m->d_pois_contrib[s] + (size_t)t_lo * C, rows, C, m->d_partials);
+          CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, (const double*)m->d_partials, cchunks, 1, C, cache,
+                        (double*)nullptr));
+          m->launches += 2;
+        } else {
+          CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, (const double*)(m->d_pois_contrib[s] + (size_t)t_lo * C),
+                        rows, 1, C, cache, (double*)nullptr));
+          m->launches++;
+        }
         if (own && allreduce_sum(m, cache, C)) return 1;
         refreshed.push_back(m->pois_byp_slot[s]);
       }
@@ -2675,6 +2793,11 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     }
   }
   for (int e = 0; e < sp.n_dep && !m->lp_valid.empty(); e++) m->lp_valid[m->deps[sp.dep_off + e].decl] = 0;  // these sums have moved on
+  {  // statistics of an i.i.d. gamma layer go stale when a sampler writes any of its values
+    const int lo_t = sp.target_slot, hi_t = sp.target_slot + (sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : sp.n_targets);
+    for (size_t i = 0; i < m->gam_iid.size(); i++)
+      if (m->gam_iid[i] && lo_t < m->decl[i].value_ref + m->decl[i].n && hi_t > m->decl[i].value_ref) m->gam_stats_valid[i] = 0;
+  }
   CK(cudaGetLastError());
   return 0;
 }
@@ -2709,7 +2832,11 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   }
   // cached block sums survive a `reset = FALSE` continuation: nothing but the samplers has touched the chain state since the
   // last run (set_values / initialize_model / a new shard layout clear them themselves)
-  if (reset) { std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0); std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0); }
+  if (reset) {
+    std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
+    std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
+    std::fill(m->gam_stats_valid.begin(), m->gam_stats_valid.end(), 0);
+  }
   m->prop_lo = m->prop_hi = -1;
   std::fill(m->pois_S_pending.begin(), m->pois_S_pending.end(), 0);
   int64_t addrows = (niter - nburnin) / thin;
@@ -2741,9 +2868,14 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   const char* genv = getenv("NIMB200_GRAPH");
   const bool want_graph = !(genv && genv[0] == '0') && !m->nccl_comm && niter >= 8 && !m->time_samplers;
   if (m->graph_exec && (!want_graph || m->waic || m->graph_seed != seed)) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
-  std::vector<char> valid_prev, dep_before;
+  std::vector<char> valid_prev, dep_before, gam_before;
   // what decides the launch sequence of an iteration: which cached sums are valid, and which group sums are
-  auto pattern = [&]() { std::vector<char> v = m->dep_valid; v.insert(v.end(), m->pois_S_valid.begin(), m->pois_S_valid.end()); return v; };
+  auto pattern = [&]() {
+    std::vector<char> v = m->dep_valid;
+    v.insert(v.end(), m->pois_S_valid.begin(), m->pois_S_valid.end());
+    v.insert(v.end(), m->gam_stats_valid.begin(), m->gam_stats_valid.end());
+    return v;
+  };
   bool capture_failed = false;
   auto adapt_due = [&]() {
     for (size_t s = 0; s < m->samplers.size(); s++) {
@@ -2819,6 +2951,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
     bool capture = want_graph && !capture_failed && !due && it >= 3 && valid_prev == pattern();
     valid_prev = pattern();
     dep_before = m->dep_valid;
+    gam_before = m->gam_stats_valid;
     if (capture) {
       std::vector<int> ran_before = m->ran;
       int64_t l0 = m->launches, a0 = m->allreduces;
@@ -2845,6 +2978,7 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
       cudaGetLastError();
       m->ran = ran_before;  // nothing ran: fall back to ordinary launches for good
       m->dep_valid = dep_before;
+      m->gam_stats_valid = gam_before;
       if (m->graph_exec) { cudaGraphExecDestroy(m->graph_exec); m->graph_exec = nullptr; }
       capture_failed = true;
     }
@@ -3253,6 +3387,7 @@ extern "C" int nimb200_initialize_model(nimb200_model* m, const int32_t* decl_or
                         ": only dnorm, dgamma, dbeta, dexp, dlogis, dbin and dpois (mean <= 500) nodes can)");
   std::fill(m->dep_valid.begin(), m->dep_valid.end(), 0);
   std::fill(m->lp_valid.begin(), m->lp_valid.end(), 0);
+  std::fill(m->gam_stats_valid.begin(), m->gam_stats_valid.end(), 0);
   std::fill(m->pois_S_valid.begin(), m->pois_S_valid.end(), 0);
   return 0;
 }

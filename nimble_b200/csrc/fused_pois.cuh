@@ -247,7 +247,7 @@ __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode*
 // alone.  PHASE 3 computes just that (part = S; the one pass over the nodes that an iteration still needs, when b1 moves);
 // PHASE 4 is the whole update from a valid S (c1 = exp(b0) S: no node is read).
 template <int PHASE>
-__global__ void __launch_bounds__(PF_THREADS)
+__global__ void __launch_bounds__(PF_THREADS, 4)
 k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part,
                   double* __restrict__ contrib) {
   __shared__ double expT[64];

@@ -356,6 +356,37 @@ def test_pois_moment_series_and_node_pass_agree(oracle, b200, monkeypatch):
     assert rel_err(got["series"], got["nodes"]).max() < 1e-13
 
 
+def test_gamma_layer_statistics_path(oracle, b200):
+    """An i.i.d. gamma layer with chain-level parameters (>= 256 nodes: lam[g] ~ dgamma(a, b)) is evaluated from (sum log lam,
+    sum lam): block sums, the conjugate update of the rate and whole trajectories agree with the oracle's node-by-node path,
+    including chains whose values or parameters fall outside the closed form (zero / negative / infinite lam, shape > 64)."""
+    m, conf = configs.glmm(N=3000, G=300, seed=12)
+    C = 40
+    inits = sm.random_inits(m, C, 3, 0.2)
+    lam0, a_s, b_s = m.var_slot["lam"], m.var_slot["a"], m.var_slot["b"]
+    inits[2, lam0 + 7] = 0.0
+    inits[3, lam0 + 299] = -0.5
+    inits[4, lam0] = np.inf
+    inits[5, a_s] = 70.0
+    inits[6, a_s] = -1.0
+    inits[7, b_s] = 0.0
+    inits[8, lam0 + 100] = np.nan
+    cg, co = compile_on(b200, conf), compile_on(oracle, conf)
+    dg, do = cg._ensure(C), co._ensure(C)
+    dg.set_values(inits)
+    do.set_values(inits)
+    ld = [i for i, d in enumerate(cg.builder.decls) if d.dist == T.DGAMMA and d.n == 300]
+    assert len(ld) == 1
+    for _ in range(2):   # the second call is served from the cached statistics
+        a, b = dg.calculate(ld[0]), do.calculate(ld[0])
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b)), (a[:10], b[:10])
+        assert rel_err(a, b).max() < RTOL_LP, rel_err(a, b).max()
+    good = sm.random_inits(m, C, 8, 0.1)
+    so, sg = run(co, good, 150, 10, seed=5), run(cg, good, 150, 10, seed=5)
+    assert rel_err(sg, so).max() < RTOL_TRAJ
+    assert rel_err(cg.dm.get_values(), co.dm.get_values()).max() < RTOL_TRAJ
+
+
 def test_pois_family_trajectories(oracle, b200):
     m, conf = sm.SMALL["glmm"]()
     inits = sm.random_inits(m, 40, 8, 0.1)
