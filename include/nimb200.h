@@ -326,6 +326,9 @@ int nimb200_measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tfl
 /* same, for a loop that issues FP64 mma.sync and DFMA together (equal flops of each): tells whether the FP64 tensor
  * sub-pipe and the FP64 pipe add up or share their multipliers. */
 int nimb200_measure_fp64_mixed(int device, double *tflops);
+/* DFMA TFLOP/s of a loop with 0, 4, 8 and 16 independent integer instructions per 8 DFMAs (tflops4[4]): how much of the FP64
+ * pipe a mixed instruction stream can use -- the issue model behind the family kernels' instruction budgets. */
+int nimb200_measure_fp64_issue_mix(int device, double *tflops4);
 /* diagnostic: the fused kernels' own exp (which=0) / log (1) / reciprocal (2) / dbern-logit log-density for y=0 (3),
  * y=1 (4) applied to a host array, so that tests can measure their accuracy against libm. */
 int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);

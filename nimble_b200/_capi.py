@@ -71,6 +71,7 @@ class Backend:
             self._time_calc = fn("time_calculate", [vp, C.c_int32, C.c_int32, _dp])
             self._peaks = fn("measure_fp64_peaks", [C.c_int, _dp, _dp])
             self._mixed = fn("measure_fp64_mixed", [C.c_int, _dp])
+            self._issue_mix = fn("measure_fp64_issue_mix", [C.c_int, _dp])
             self._nccl_id = fn("nccl_unique_id", [C.c_void_p])
             self._shard = fn("enable_data_sharding", [vp, C.c_int32, C.c_int32, C.c_void_p, C.c_int32])
             self._peer_export = fn("peer_export", [vp, C.c_int32, C.c_void_p])
@@ -101,6 +102,12 @@ class Backend:
         a = C.c_double()
         self.check(self._mixed(device, C.byref(a)))
         return a.value
+
+    def fp64_issue_mix(self, device=0):
+        """DFMA TFLOP/s of a loop with 0, 4, 8, 16 integer instructions per 8 DFMAs."""
+        out = np.zeros(4)
+        self.check(self._issue_mix(device, _ptr(out)))
+        return out
 
     def fp64_peaks(self, device=0):
         a, b = C.c_double(), C.c_double()

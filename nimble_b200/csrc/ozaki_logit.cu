@@ -12,9 +12,19 @@
 //
 // Structure (one CTA per SM, 576 threads): warp 0 = producer (one 1-D TMA bulk copy per 128-row tile: 64 KiB of slices laid
 // out in global memory exactly as the UMMA canonical K-major no-swizzle layout wants them in shared memory, plus y and the row
-// exponents), warp 1 = MMA issuer (72 tcgen05.mma per half tile, tcgen05.commit onto mbarriers), warps 2-17 = epilogue
-// (tcgen05.ld 32x32b, row = TMEM lane = thread).  A CTA owns 64 chains as two halves of 32: while the epilogue drains one
-// half's accumulators the tensor cores fill the other's -- the two halves are the two TMEM stages (2 x 8 x 32 = 512 columns).
+// exponents), warp 1 = MMA issuer, warps 2-17 = epilogue (tcgen05.ld 32x32b.x8, row = TMEM lane = thread).  A CTA owns 64
+// chains as two halves of 32: while the epilogue works on one half's accumulators the tensor cores fill the other's -- the two
+// halves are the two TMEM stages (2 x 8 x 32 = 512 columns).
+// MMA shape (round 2, second version): the beta slices of a half are stacked along N into ONE 256-row operand, so A slice s
+// against slices t = 0 .. 7 - s is one tcgen05.mma of N = (8 - s) 32 per K step whose accumulator columns are the weights
+// s .. 7 -- 16 MMAs per half tile instead of 72, 136 KiB of shared-memory operand reads instead of 360 (tensor + TMEM-load
+// pipeline alone: 2.97 -> 1.47 ms).  Epilogue: tables held 16 times (bank-conflict free), scale as two multiplies by
+// precomputed powers of two, 77 instructions per evaluation instead of 88.
+// Measured (profiles/r2q_ozaki_summary.md): 4.6 - 4.7 ms per launch against 4.85 ms for the FP64 tensor-core kernel, epilogue
+// alone 3.3 - 3.5 ms.  The clock64 timeline (nimb200_debug_ozaki_trace) shows why the two do not overlap: per half and warp
+// 1000 cycles of waiting for the tensor cores and 570 of TMEM loads against 3300 of arithmetic, the waits of the four warps
+// of a scheduler coincide, and the arithmetic itself runs 16 % slower while the MMAs stream their operands from shared memory.
+// Still a diagnostic (nimb200_debug_ozaki), not the sampling path: a 5 % gain does not pay for 524 bytes per row of sliced X.
 #include <cfloat>
 #include <cmath>
 #include <algorithm>
@@ -52,6 +62,7 @@ __device__ __forceinline__ void oz_mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(oz_smem(bar)) : "memory");
 }
 // bounded wait: a barrier that never completes (a protocol error) traps instead of hanging the GPU
+template <unsigned SLEEP = 0>
 __device__ __forceinline__ void oz_mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t a = oz_smem(bar);
   for (unsigned spins = 0;; spins++) {
@@ -66,6 +77,7 @@ __device__ __forceinline__ void oz_mbar_wait(uint64_t* bar, uint32_t parity) {
         : "r"(a), "r"(parity)
         : "memory");
     if (done) return;
+    if (SLEEP) __nanosleep(SLEEP);   // producer / MMA warps: a spinning warp must not take issue slots from the epilogue warps of its scheduler
     if (spins > (1u << 26)) __trap();
   }
 }
@@ -80,20 +92,22 @@ __device__ __forceinline__ uint64_t oz_desc(uint32_t saddr, uint32_t lbo, uint32
   return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) |
          (1ull << 46);
 }
-// instruction descriptor: D = S32, A = B = signed int8, both K-major, N = 32, M = 128
-static const uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(OZ_NH >> 3) << 17) | ((uint32_t)(OZ_M >> 4) << 24);
+// instruction descriptor: D = S32, A = B = signed int8, both K-major, M = 128, N given (a multiple of 32 up to 256)
+__host__ __device__ constexpr uint32_t oz_idesc(int N) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(OZ_M >> 4) << 24);
+}
 
 // The whole MMA warp runs the issue loop (warp-uniform control flow keeps the descriptors in uniform registers, which is what
 // the instruction reads); only the elected lane's instruction takes effect.
 template <int ACC>
-__device__ __forceinline__ void oz_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t leader) {
+__device__ __forceinline__ void oz_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t leader) {
   asm volatile(
       "{\n"
       ".reg .pred p, q;\n"
       "setp.ne.b32 p, %4, 0;\n"
       "setp.ne.b32 q, %6, 0;\n"
       "@q tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n"
-      "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(OZ_IDESC), "n"(ACC), "r"(0u), "r"(leader)
+      "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "n"(ACC), "r"(0u), "r"(leader)
       : "memory");
 }
 __device__ __forceinline__ void oz_commit(uint64_t* bar, uint32_t leader) {
@@ -120,6 +134,76 @@ __device__ __forceinline__ void oz_ld4(uint32_t taddr, int (&v)[4]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
                : "r"(taddr));
+}
+
+__device__ __forceinline__ void oz_ld8(uint32_t taddr, int (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
+}
+
+// The epilogue's look-up tables (2^(j/64), 1/c_j, log c_j) are held 16 times, T[j][copy]: lane l reads copy l & 15, so the 32
+// lanes of a load hit 16 different bank pairs whatever their indices -- exactly the two wavefronts a 64-bit load needs (one
+// shared copy: 4.8 wavefronts per look-up with realistic predictors, ncu r2o).  logc[128] = ln 2 here (the centre 2 of the
+// moderate path, bern_logit.cuh), so the look-up needs no special case.
+static const int OZ_TAB_ENTRIES = 64 + 129 + 129;
+static const int OZ_TAB_BYTES = OZ_TAB_ENTRIES * 16 * 8;
+
+// dbern-logit log-density of four nodes (one row, four chains): the moderate path of bern_logit_lp_vec (every |eta| < 8) on
+// the replicated tables, anything else on the general path.  ysign: the row's y as a sign mask test (y1 = y != 0).
+__device__ __forceinline__ void oz_bern_lp4(const double (&eta)[4], bool y1, double (&out)[4], const double* __restrict__ expL,
+                                            const MathTab* __restrict__ tab) {
+  const double* __restrict__ K = c_tab_misc;   // constant bank: 18 warps of 4-warp allocation granularity leave 96 registers
+  unsigned amax = 0;
+#pragma unroll
+  for (int j = 0; j < 4; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
+  if (!__all_sync(0xffffffffu, amax < 0x40200000u)) {   // warp-uniform, practically never taken
+    bern_logit_lp_vec<4, true, false>(eta, y1, out, nullptr, tab);
+    return;
+  }
+  const double* __restrict__ invL = expL + 64 * 16;
+  const double* __restrict__ logL = expL + (64 + 129) * 16;
+  double x[4], t[4], r[4], pl[4], d[4];
+  int n[4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) x[j] = __hiloint2double(__double2hiint(eta[j]) | (int)0x80000000, __double2loint(eta[j]));  // -|eta|
+#pragma unroll
+  for (int j = 0; j < 4; j++) t[j] = fma(x[j], K[0], K[1]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - K[1]; }
+#pragma unroll
+  for (int j = 0; j < 4; j++) r[j] = fma(t[j], K[2], x[j]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) r[j] = fma(t[j], K[3], r[j]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) pl[j] = fma(r[j], K[4], K[5]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], K[6]);
+#pragma unroll
+  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], 0.5);
+#pragma unroll
+  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const double Tj = expL[(n[j] & 63) * 16];
+    const double v = fma(Tj * r[j], pl[j], Tj);
+    const double e = __hiloint2double(__double2hiint(v) + (n[j] & ~63) * 16384, __double2loint(v));
+    d[j] = 1.0 + e;  // in (1, 2]
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 is the centre 2
+    const int idx = (__double2hiint(d[j]) - 0x3ff00000 + 0x1000) >> 13;
+    const double rr = fma(d[j], invL[idx * 16], -1.0);
+    double Q = fma(rr, K[8], K[9]);
+    Q = fma(Q, rr, K[10]);
+    Q = fma(Q, rr, K[11]);
+    Q = fma(Q, rr, 1.0 / 3.0);
+    Q = fma(Q, rr, -0.5);
+    const double lp = fma(rr * rr, Q, rr);
+    const double lg = logL[idx * 16] + lp;
+    const bool neg = __double2hiint(eta[j]) < 0;
+    out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------- slicing
@@ -166,6 +250,13 @@ __global__ void k_oz_slice_x(const double* __restrict__ X, const double* __restr
   et[r] = e;
 }
 
+// timeline diagnostic (nimb200_debug_ozaki_trace): clock64 stamps of CTA (0, 0), [warp 0..17][tile 0..63][half][4 events]
+__device__ long long* g_oz_trace = nullptr;
+#define OZ_STAMP(it, h, k)                                                                                           \
+  do {                                                                                                               \
+    if (trace && lane == 0 && (it) < 64) trace[(((size_t)warp * 64 + (it)) * 2 + (h)) * 4 + (k)] = clock64();        \
+  } while (0)
+
 // ---------------------------------------------------------------------------------------------------------------- main kernel
 // grid (chain tiles of 64, node chunks).  partials[chunk][C].  eta_out (diagnostic, may be null): [n][C] linear predictors.
 __global__ void __launch_bounds__(OZ_THREADS, 1)
@@ -180,16 +271,24 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
   uint32_t* s_tmem = (uint32_t*)(bars + 8);
   int* s_f = (int*)(s_tmem + 2);                                    // chain exponents [64]
   double* s_red = (double*)(s_f + OZ_NC);                           // [4 quarters][64 chains]
-  MathTab* tab = (MathTab*)(s_red + 4 * OZ_NC);
+  double* s_cs = s_red + 4 * OZ_NC;                                 // chain scales 2^f [64] (NaN: poisoned chain)
+  MathTab* tab = (MathTab*)(s_cs + OZ_NC);
+  double* s_rep = (double*)(tab + 1);                               // the replicated tables (OZ_TAB_BYTES)
   uint64_t *a_full = bars, *a_empty = bars + 2, *t_full = bars + 4, *t_empty = bars + 6;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  long long* trace = (blockIdx.x == 0 && blockIdx.y == 0) ? g_oz_trace : nullptr;
   const int chain0 = blockIdx.x * OZ_NC, chunk = blockIdx.y;
   const int tile_lo = tile_begin + chunk * tiles_per_chunk, tile_hi = min(tile_end, tile_lo + tiles_per_chunk);
   const int ntiles = max(0, tile_hi - tile_lo);
 
   for (int i = tid; i < (int)(sizeof(MathTab) / sizeof(double)); i += OZ_THREADS) ((double*)tab)[i] = ((const double*)&g_mathtab)[i];
-  // beta of this CTA's 64 chains -> int8 slices in the canonical layout [slice][k16 chunk][chain group 0..7][chain 0..7][16 B]
+  for (int i = tid; i < OZ_TAB_ENTRIES * 16; i += OZ_THREADS) {
+    const int e = i >> 4;
+    s_rep[i] = e < 64 ? g_mathtab.expT[e] : e < 64 + 129 ? g_mathtab.invc[e - 64] : (e - 193 == 128 ? c_tab_misc[7] : g_mathtab.logA[e - 193]);
+  }
+  // beta of this CTA's 64 chains -> int8 slices in the canonical layout [half][k16 chunk][slice][chain group 0..3][chain 0..7][16 B]:
+  // per half, the eight slices of its 32 chains stacked along N make ONE 256-row K-major operand
   if (tid < OZ_NC) {
     const int c = chain0 + tid;
     double mx = 0.0;
@@ -203,11 +302,14 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
     int f = (mx > 0.0 && !bad) ? ilogb(mx) + 2 : 0;
     if (f < -400 || f > 400) { bad = true; f = 0; }
     s_f[tid] = bad ? (1 << 20) : f;     // a non-finite or out-of-range beta poisons the chain: its sum is recomputed as NaN below
+    s_cs[tid] = bad ? __longlong_as_double(0x7ff8000000000000ll) : __hiloint2double((1023 + f) << 20, 0);
     for (int k = 0; k < OZ_K; k++) {
       double rem = (c < C && k < p && !bad) ? scalbn(state[(size_t)(beta_slot + k) * C + c], -f) : 0.0;
       for (int s = 0; s < OZ_S; s++) {
         const int d = oz_digit(rem);
-        sB[(size_t)s * OZ_SLICE_B + (k >> 4) * 1024 + (tid >> 3) * 128 + (tid & 7) * 16 + (k & 15)] = (unsigned char)(signed char)d;
+        // half h = tid / 32 holds one 256-row operand: row = slice * 32 + chain of the half (see the MMA loop)
+        sB[(size_t)(tid >> 5) * (OZ_S * OZ_NH * OZ_K) + (k >> 4) * (OZ_S * OZ_NH * 16) + (s * 4 + ((tid & 31) >> 3)) * 128 + (tid & 7) * 16 +
+           (k & 15)] = (unsigned char)(signed char)d;
       }
     }
   }
@@ -234,7 +336,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
     if (lane == 0) {
       for (int it = 0; it < ntiles; it++) {
         const int st = it & 1;
-        if (it >= 2) oz_mbar_wait(&a_empty[st], (uint32_t)(((it >> 1) - 1) & 1));
+        if (it >= 2) oz_mbar_wait<200>(&a_empty[st], (uint32_t)(((it >> 1) - 1) & 1));
         oz_mbar_expect_tx(&a_full[st], (uint32_t)OZ_TILE_BYTES);
         oz_bulk_g2s(sA + (size_t)st * OZ_TILE_BYTES, Xq + (size_t)(tile_lo + it) * OZ_TILE_BYTES, (uint32_t)OZ_TILE_BYTES, &a_full[st]);
       }
@@ -255,27 +357,31 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
         const uint64_t da0 = oz_desc(aA, 2048, 128);
 #pragma unroll
         for (int h = 0; h < 2; h++) {
+          OZ_STAMP(it, h, 0);
           if (it >= 1) {  // the epilogue has drained this half's accumulators of the previous tile
             oz_mbar_wait(&t_empty[h], (uint32_t)((it - 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           }
-          if (dbg == 2) { oz_commit(&t_full[h], leader); continue; }   // diagnostic: no tensor work
-          const uint64_t db0 = oz_desc(aB + h * 512, 1024, 128);
+          OZ_STAMP(it, h, 1);
+          if ((dbg & 3) == 2) { oz_commit(&t_full[h], leader); continue; }   // diagnostic: no tensor work
+          // A slice s against the stacked beta slices t = 0 .. 7 - s (rows 0 .. (8 - s) 32 of the half's operand) lands in the
+          // accumulator columns of the weights s .. 7: one MMA of N = (8 - s) 32 per K step instead of 8 - s MMAs of N = 32 --
+          // the A tile (4 KiB per K step) is read once per slice, not once per slice pair (round 2: 136 KiB of shared-memory
+          // operand reads per half tile instead of 360; the tensor work is the same 1152 cycles)
+          const uint64_t db0 = oz_desc(aB + h * (OZ_S * OZ_NH * OZ_K), OZ_S * OZ_NH * 16, 128);
           const uint32_t d0 = tmem + (uint32_t)(h * 256);
 #pragma unroll
-          for (int g = 0; g < OZ_S; g++) {
+          for (int s = 0; s < OZ_S; s++) {
 #pragma unroll
-            for (int s = 0; s <= g; s++) {
-#pragma unroll
-              for (int ks = 0; ks < 2; ks++) {
-                const uint64_t da = da0 + (uint64_t)((s * OZ_SLICE_A + ks * 4096) >> 4);
-                const uint64_t db = db0 + (uint64_t)(((g - s) * OZ_SLICE_B + ks * 2048) >> 4);
-                if ((s | ks) != 0) oz_mma<1>(d0 + (uint32_t)(g * OZ_NH), da, db, leader);
-                else oz_mma<0>(d0 + (uint32_t)(g * OZ_NH), da, db, leader);
-              }
+            for (int ks = 0; ks < 2; ks++) {
+              const uint64_t da = da0 + (uint64_t)((s * OZ_SLICE_A + ks * 4096) >> 4);
+              const uint64_t db = db0 + (uint64_t)((ks * 2 * OZ_S * OZ_NH * 16) >> 4);
+              if ((s | ks) != 0) oz_mma<1>(d0 + (uint32_t)(s * OZ_NH), da, db, oz_idesc((OZ_S - s) * OZ_NH), leader);
+              else oz_mma<0>(d0, da, db, oz_idesc(OZ_S * OZ_NH), leader);
             }
           }
           oz_commit(&t_full[h], leader);         // accumulators of (tile, half) complete -> epilogue
+          OZ_STAMP(it, h, 2);
         }
         oz_commit(&a_empty[st], leader);         // every MMA reading this A stage has completed
       }
@@ -286,6 +392,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
     const int q = warp & 3;                      // TMEM lane quarter this warp may touch
     const int cq = ew >> 2;                      // which 8 of a half's 32 columns
     const int row = q * 32 + lane;
+    const double* __restrict__ expL = s_rep + (lane & 15);
     double csum[2][8];
 #pragma unroll
     for (int h = 0; h < 2; h++)
@@ -299,44 +406,59 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
       const int er = ((const int*)(tile + OZ_S * OZ_SLICE_A + OZ_M * 8))[row];
       __syncwarp();
       if (lane == 0) oz_mbar_arrive(&a_empty[st]);            // this warp no longer needs the stage
-      const bool live = yv >= 0.0, y1 = yv != 0.0;
+      const bool live = __double2hiint(yv) >= 0, y1 = (__double2hiint(yv) | __double2loint(yv)) != 0;   // y is 0, 1 or -1 (past n)
+      const double rs = __hiloint2double((1023 + er - 35) << 20, 0);   // 2^(er - 35): the row's share of the scale
       const long long grow = (long long)(tile_lo + it) * OZ_M + row;
 #pragma unroll
       for (int h = 0; h < 2; h++) {
+        if (dbg & 4) asm volatile("bar.sync 1, %0;" ::"n"(32 * OZ_EPI_WARPS) : "memory");   // experiment: epilogue warps in lockstep
+        OZ_STAMP(it, h, 0);
         oz_mbar_wait(&t_full[h], (uint32_t)(it & 1));
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
-        for (int cb = 0; cb < 2; cb++) {          // 4 columns at a time: 8 weights x 4 columns = 32 accumulator registers in flight
-          int a[OZ_S][4];
-          const uint32_t base = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256 + cq * 8 + cb * 4);
-#pragma unroll
-          for (int g = 0; g < OZ_S; g++) oz_ld4(base + (uint32_t)(g * OZ_NH), a[g]);
+        OZ_STAMP(it, h, 1);
+        // the thread's 8 columns of the half, all eight weights, two weights (16 accumulator registers) per wait; exact
+        // recombination in 64-bit integers, then TMEM goes back to the tensor cores before any floating-point arithmetic
+        const uint32_t base = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * 256 + cq * 8);
+        long long hi[8], lo[8];
+        {
+          int a[2][8], b[8];
+          oz_ld8(base, a[0]); oz_ld8(base + (uint32_t)OZ_NH, a[1]);
           asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-          if (cb == 1) {                          // all of this thread's accumulators of the half are in registers: hand TMEM back
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) oz_mbar_arrive(&t_empty[h]);
-          }
-          if (dbg == 1) { csum[h][cb * 4] += (double)(a[0][0] + a[7][3]); continue; }   // diagnostic: no epilogue arithmetic
+#pragma unroll
+          for (int j = 0; j < 8; j++) b[j] = a[0][j] * 128 + a[1][j];
+          oz_ld8(base + (uint32_t)(2 * OZ_NH), a[0]); oz_ld8(base + (uint32_t)(3 * OZ_NH), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 8; j++) hi[j] = (long long)b[j] * 16384 + (a[0][j] * 128 + a[1][j]);
+          oz_ld8(base + (uint32_t)(4 * OZ_NH), a[0]); oz_ld8(base + (uint32_t)(5 * OZ_NH), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 8; j++) b[j] = a[0][j] * 128 + a[1][j];
+          oz_ld8(base + (uint32_t)(6 * OZ_NH), a[0]); oz_ld8(base + (uint32_t)(7 * OZ_NH), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) oz_mbar_arrive(&t_empty[h]);
+#pragma unroll
+          for (int j = 0; j < 8; j++) lo[j] = (long long)b[j] * 16384 + (a[0][j] * 128 + a[1][j]);
+        }
+        OZ_STAMP(it, h, 2);
+        if ((dbg & 3) == 1) { csum[h][0] += (double)(hi[0] + lo[7]); continue; }   // diagnostic: no epilogue arithmetic
+#pragma unroll
+        for (int cb = 0; cb < 2; cb++) {
           double eta[4], lp[4];
 #pragma unroll
           for (int j = 0; j < 4; j++) {
-            const int b01 = a[0][j] * 128 + a[1][j], b23 = a[2][j] * 128 + a[3][j];
-            const int b45 = a[4][j] * 128 + a[5][j], b67 = a[6][j] * 128 + a[7][j];
-            const long long hi = (long long)b01 * 16384 + b23, lo = (long long)b45 * 16384 + b67;
             // exact int64 -> double on the integer pipe (|hi|, |lo| < 2^51): 2^52 + 2^51 + x has x in its low mantissa bits;
             // for lo the same trick 28 binary places down yields lo 2^-28 directly.  Two exact subtractions, one rounding add.
-            const double dh = __longlong_as_double(hi + 0x4338000000000000ll) - 6755399441055744.0;
-            const double dl = __longlong_as_double(lo + 0x4178000000000000ll) - 25165824.0;
-            const double v = dh + dl;
-            const int f = s_f[h * OZ_NH + cq * 8 + cb * 4 + j];
-            // 2^(er + f - 35) built on the integer pipe; a poisoned chain (f = 2^20) becomes NaN
-            const double sc = f >= (1 << 20) ? __longlong_as_double(0x7ff8000000000000ll) : __hiloint2double((1023 + er + f - 35) << 20, 0);
-            eta[j] = v * sc;
+            const double dh = __longlong_as_double(hi[cb * 4 + j] + 0x4338000000000000ll) - 6755399441055744.0;
+            const double dl = __longlong_as_double(lo[cb * 4 + j] + 0x4178000000000000ll) - 25165824.0;
+            eta[j] = ((dh + dl) * rs) * s_cs[h * OZ_NH + cq * 8 + cb * 4 + j];
           }
-          bern_logit_lp_vec<4>(eta, y1, lp, nullptr, tab);
+          oz_bern_lp4(eta, y1, lp, expL, tab);
 #pragma unroll
-          for (int j = 0; j < 4; j++) csum[h][cb * 4 + j] += live ? lp[j] : 0.0;
+          for (int j = 0; j < 4; j++)
+            if (live) csum[h][cb * 4 + j] += lp[j];
           if (eta_out) {
 #pragma unroll
             for (int j = 0; j < 4; j++) {
@@ -345,6 +467,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
             }
           }
         }
+        OZ_STAMP(it, h, 3);
       }
     }
     // per-chain sums over the 128 rows: butterfly inside the warp, then the four lane quarters through shared memory
@@ -369,7 +492,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
 
 // ---------------------------------------------------------------------------------------------------------------- host side
 static size_t oz_smem_bytes() {
-  return 2 * (size_t)OZ_TILE_BYTES + OZ_S * OZ_SLICE_B + 8 * 8 + 8 + OZ_NC * 4 + 4 * OZ_NC * 8 + sizeof(MathTab) + 64;
+  return 2 * (size_t)OZ_TILE_BYTES + OZ_S * OZ_SLICE_B + 8 * 8 + 8 + OZ_NC * 4 + 4 * OZ_NC * 8 + OZ_NC * 8 + sizeof(MathTab) + OZ_TAB_BYTES + 64;
 }
 
 size_t ozaki_xq_bytes(int n, int p) {
@@ -405,6 +528,25 @@ void ozaki_bern_logit_launch(const unsigned char* Xq, int n, int p, const double
 }
 
 }  // namespace nimb
+
+// diagnostic: run nimb200_debug_ozaki-style launches with the timeline stamps of CTA (0, 0) switched on; out[18][64][2][4]
+extern "C" int nimb200_debug_ozaki_trace(long long* out_or_null_to_stop) {
+  using namespace nimb;
+  static long long* dbuf = nullptr;
+  const size_t n = (size_t)18 * 64 * 2 * 4;
+  if (!dbuf) {
+    if (cudaMalloc(&dbuf, n * sizeof(long long)) != cudaSuccess) return 1;
+    cudaMemset(dbuf, 0, n * sizeof(long long));
+    if (cudaMemcpyToSymbol(g_oz_trace, &dbuf, sizeof(dbuf)) != cudaSuccess) return 1;
+    return 0;
+  }
+  if (out_or_null_to_stop && cudaMemcpy(out_or_null_to_stop, dbuf, n * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
+  long long* z = nullptr;
+  cudaMemcpyToSymbol(g_oz_trace, &z, sizeof(z));
+  cudaFree(dbuf);
+  dbuf = nullptr;
+  return 0;
+}
 
 // diagnostic (tests, measurements): linear predictors and per-chain block sums of the tensor-core path for host arrays
 // X [n][p] row-major, y [n], beta [p][C] (chain fastest); eta_out [n][C] and sums_out [C] may each be null.

@@ -66,7 +66,69 @@ __global__ void k_mixed_peak(double* out, int iters, double seed) {
   if (s == 12345.678) out[0] = s;
 }
 
+// 8 independent DFMA chains with NI independent integer multiply-adds per trip: how much of the FP64 pipe is left when the
+// instruction stream is mixed?  (If a DFMA holds the scheduler's dispatch port for two cycles, every other instruction costs a
+// cycle on top of 2 x the FP64 count: the model behind the family kernels' instruction budgets in DESIGN.md.)
+template <int NI>
+__global__ void k_dfma_int_mix(double* out, int iters, double seed) {
+  double a[8];
+  unsigned x[NI > 0 ? NI : 1];
+#pragma unroll
+  for (int j = 0; j < 8; j++) a[j] = seed + j + threadIdx.x * 1e-9;
+#pragma unroll
+  for (int j = 0; j < NI; j++) x[j] = threadIdx.x * 7u + j;
+  double b = 1.0000001, c = 1e-7;
+  unsigned m = (unsigned)(seed * 3.0) | 1u;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int j = 0; j < 8; j++) a[j] = fma(a[j], b, c);
+#pragma unroll
+    for (int j = 0; j < NI; j++) x[j] = x[j] * m + (unsigned)i;
+  }
+  double s = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) s += a[j];
+  unsigned t = 0;
+#pragma unroll
+  for (int j = 0; j < NI; j++) t ^= x[j];
+  if (s == 12345.678 || t == 0x12345u) out[0] = s + t;
+}
+
 }  // namespace
+
+// DFMA TFLOP/s with 0, 4, 8 and 16 integer instructions per 8 DFMAs in the loop
+extern "C" int nimb200_measure_fp64_issue_mix(int device, double* tflops4) {
+  if (cudaSetDevice(device) != cudaSuccess) return 1;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 1;
+  double* out = nullptr;
+  if (cudaMalloc(&out, 8) != cudaSuccess) return 1;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int threads = 256, blocks = prop.multiProcessorCount * 8, iters = 4096;
+  for (int v = 0; v < 4; v++) {
+    double best = 0;
+    for (int rep = 0; rep < 4; rep++) {
+      float ms = 0;
+      cudaEventRecord(e0);
+      if (v == 0) k_dfma_int_mix<0><<<blocks, threads>>>(out, iters, 1.0);
+      else if (v == 1) k_dfma_int_mix<4><<<blocks, threads>>>(out, iters, 1.0);
+      else if (v == 2) k_dfma_int_mix<8><<<blocks, threads>>>(out, iters, 1.0);
+      else k_dfma_int_mix<16><<<blocks, threads>>>(out, iters, 1.0);
+      cudaEventRecord(e1);
+      cudaEventSynchronize(e1);
+      cudaEventElapsedTime(&ms, e0, e1);
+      const double flops = 2.0 * 8 * iters * (double)threads * blocks;
+      if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    tflops4[v] = best;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
 
 // flops of a loop that issues 4 DMMA (2048 flop/warp) and 32 DFMA (2048 flop/warp) per iteration
 extern "C" int nimb200_measure_fp64_mixed(int device, double* tflops) {
