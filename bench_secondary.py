@@ -47,7 +47,7 @@ def secondary_rooflines(nb, backend, local, hbm_peak, dfma_tflops):
             ms = _time(dg, yd, 5)
         finally:
             del os.environ["NIMB200_NO_BYPRODUCT"]
-        fp64_per_eval = 16.5     # FP64-pipe instructions per evaluation as implemented (ncu-counted, profiles/)
+        fp64_per_eval = 16.0     # FP64-pipe instructions per evaluation as implemented (ncu-counted, profiles/r2l_pois_sum_raw.csv)
         ach = 2.0 * fp64_per_eval * nn * C / (ms * 1e-3) / 1e12
         out.append({"kernel": "k_pois_sum", "bound": "fp64",
                     "workload": "configs[4]: y[i] ~ dpois(lam[grp[i]] exp(b0 + b1 x[i])) block sum, N = %d, %d chains" % (nn, C),
@@ -55,7 +55,8 @@ def secondary_rooflines(nb, backend, local, hbm_peak, dfma_tflops):
                     "ms_per_block_sum": ms, "evals_per_s": nn * C / (ms * 1e-3), "fp64_instructions_per_eval": fp64_per_eval,
                     "ms_per_block_sum_from_group_sums": ms_groups,
                     "note": "an MCMC iteration no longer runs this kernel: block sums and the conjugate sweep come from per-group sums "
-                            "S_g = sum exp(b1 x), one pass over the nodes per iteration (when b1 is proposed)",
+                            "S_g = sum exp(b1 x), themselves evaluated from 25 data-only moment coefficients per group (24 fused "
+                            "multiply-adds per group and chain) while |b1| max|x| <= 2, by a pass over the nodes otherwise",
                     "what": "FP64-pipe instructions the kernel issues per evaluation (2 flop each) against the DFMA peak measured live"})
         dg.close()
     except Exception as ex:
@@ -73,15 +74,21 @@ def secondary_rooflines(nb, backend, local, hbm_peak, dfma_tflops):
         yd = [cm.lowering.decl_ids[d.index] for d in m4.decls if d.var == "y"][0]
         nn = cm.builder.decls[yd].n
         ms = _time(do, yd, 20)
-        fp64_per_eval = 24.8
+        fp64_per_eval = 23.0
         ach = 2.0 * fp64_per_eval * nn * C / (ms * 1e-3) / 1e12
         out.append({"kernel": "k_bernlin_sum", "bound": "fp64",
                     "workload": "configs[3]: y[i,j] ~ dbern(z[i] ilogit(a0 + a1 w[i,j])) block sum, %d nodes, %d chains" % (nn, C),
                     "achieved": ach, "peak": dfma_tflops, "unit": "TFLOP/s", "frac": ach / dfma_tflops if dfma_tflops else None,
                     "us_per_block_sum": ms * 1e3, "evals_per_s": nn * C / (ms * 1e-3), "fp64_instructions_per_eval": fp64_per_eval,
                     "what": "FP64-pipe instructions of the reciprocal-free dbern-logit form per evaluation (2 flop each) against the "
-                            "DFMA peak measured live; the kernel is shared-memory-latency bound, see DESIGN.md"})
+                            "DFMA peak measured live; the kernel is issue-bound (57 other instructions per evaluation, each costing "
+                            "about a cycle on top of two per FP64 instruction), see DESIGN.md"})
         do.close()
     except Exception as ex:
         out.append({"kernel": "k_bernlin_sum", "error": str(ex)[:200]})
+    try:   # the issue model behind the instruction budgets: DFMA rate with 0 / 4 / 8 / 16 integer instructions per 8 DFMAs
+        mix = backend.fp64_issue_mix(local)
+        out.append({"kernel": "k_dfma_int_mix (microbenchmark)", "unit": "TFLOP/s", "dfma_tflops_with_0_4_8_16_int_per_8_dfma": [float(v) for v in mix]})
+    except Exception as ex:
+        out.append({"kernel": "k_dfma_int_mix", "error": str(ex)[:200]})
     return out

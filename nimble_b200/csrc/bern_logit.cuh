@@ -234,6 +234,77 @@ __device__ __forceinline__ void bern_logit_lp_vec(const double (&eta)[W], bool y
   bern_logit_lp_vecy<W, VOTE, SOFTPLUS>(eta, yv, out, sp, tab);
 }
 
+// ---- the moderate path on replicated tables (round 2) ----------------------------------------------------------------
+// The look-up tables (2^(j/64), 1/c_j, log c_j) held 16 times, T[j][copy]: lane l reads copy l & 15, so the 32 lanes of a load
+// hit 16 different bank pairs whatever their indices -- exactly the two wavefronts a 64-bit load needs (one shared copy: 4.8
+// wavefronts per look-up with realistic predictors, ncu r2o).  logc[128] = ln 2 here (the centre 2 of the moderate path), so
+// the look-up needs no special case; the exponent and table-index arithmetic is the four-instruction form of fused_pois.cuh.
+static const int BL_REP_ENTRIES = 64 + 129 + 129;
+static const int BL_REP_BYTES = BL_REP_ENTRIES * 16 * 8;
+__device__ __forceinline__ void load_bern_rep_tables(double* dst, int tid, int nthreads) {
+  for (int i = tid; i < BL_REP_ENTRIES * 16; i += nthreads) {
+    const int e = i >> 4;
+    dst[i] = e < 64 ? g_mathtab.expT[e] : e < 64 + 129 ? g_mathtab.invc[e - 64] : (e - 193 == 128 ? c_tab_misc[7] : g_mathtab.logA[e - 193]);
+  }
+}
+// W nodes at once; expL = the replicated tables + (lane & 15); tab = the plain tables for the general path.
+template <int W, bool VOTE>
+__device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
+                                                  const double* __restrict__ expL, const MathTab* __restrict__ tab) {
+  const double* __restrict__ K = c_tab_misc;
+  unsigned amax = 0;
+#pragma unroll
+  for (int j = 0; j < W; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
+  const bool mod = amax < 0x40200000u;   // every |eta| < 8 (NaN fails the test)
+  if (!(VOTE ? __all_sync(0xffffffffu, mod) : mod)) {
+    bern_logit_lp_vecy<W, VOTE, false>(eta, y1v, out, nullptr, tab);
+    return;
+  }
+  const double* __restrict__ invL = expL + 64 * 16;
+  const double* __restrict__ logL = expL + (64 + 129) * 16;
+  double x[W], t[W], r[W], pl[W], d[W];
+  int n[W];
+#pragma unroll
+  for (int j = 0; j < W; j++) x[j] = __hiloint2double(__double2hiint(eta[j]) | (int)0x80000000, __double2loint(eta[j]));  // -|eta|
+#pragma unroll
+  for (int j = 0; j < W; j++) t[j] = fma(x[j], K[0], K[1]);
+#pragma unroll
+  for (int j = 0; j < W; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - K[1]; }
+#pragma unroll
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], K[2], x[j]);
+#pragma unroll
+  for (int j = 0; j < W; j++) r[j] = fma(t[j], K[3], r[j]);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(r[j], K[4], K[5]);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], K[6]);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 0.5);
+#pragma unroll
+  for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
+#pragma unroll
+  for (int j = 0; j < W; j++) {
+    const double Tj = expL[(n[j] & 63) * 16];
+    const double v = fma(Tj * r[j], pl[j], Tj);
+    const double e = __hiloint2double(__double2hiint(v) + (n[j] & ~63) * 16384, __double2loint(v));
+    d[j] = 1.0 + e;  // in (1, 2]
+  }
+#pragma unroll
+  for (int j = 0; j < W; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 is the centre 2
+    const int idx = (__double2hiint(d[j]) - 0x3ff00000 + 0x1000) >> 13;
+    const double rr = fma(d[j], invL[idx * 16], -1.0);
+    double Q = fma(rr, K[8], K[9]);
+    Q = fma(Q, rr, K[10]);
+    Q = fma(Q, rr, K[11]);
+    Q = fma(Q, rr, 1.0 / 3.0);
+    Q = fma(Q, rr, -0.5);
+    const double lp = fma(rr * rr, Q, rr);
+    const double lg = logL[idx * 16] + lp;
+    const bool neg = __double2hiint(eta[j]) < 0;
+    out[j] = (y1v[j] == neg ? x[j] : 0.0) - lg;  // x = -|eta|
+  }
+}
+
 __device__ __forceinline__ double bern_logit_lp(double eta, bool y1) {  // scalar form (diagnostics)
   double in[1] = {eta}, o[1];
   bern_logit_lp_vec<1, true, false>(in, y1, o, nullptr, &g_mathtab);

@@ -815,32 +815,45 @@ __global__ void __launch_bounds__(256) k_gamma_stats(DevTab T, int di, double* _
     partials[((size_t)blockIdx.y * 2 + warp) * T.C + c] = s;
   }
 }
-// MODE 0: block sum -> dst0.  MODE 2: conjugate contributions of the n dependents -> (dst0, dst1).
+// MODE 0: block sum -> dst0.  MODE 2: conjugate contributions of the n dependents -> (dst0, dst1).  One warp per chain: the
+// closed form is lane 0's; a chain outside it (a proposed shape beyond 64 happens every few iterations while the RW scale is
+// unadapted) has its 32 lanes stride over the nodes, fixed-order butterfly at the end -- one thread walking 1e4 nodes through
+// nmath's dgamma took 10 ms.
 template <int MODE>
 __global__ void k_gamma_from_stats(DevTab T, int di, const double* __restrict__ stats, nimb200_dep dp, int slot, int gam,
                                    double* __restrict__ dst0, double* __restrict__ dst1) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (c >= T.C) return;
   const nimb200_decl& d = T.decl[di];
   const double SL = stats[c], SM = stats[(size_t)T.C + c];
   const bool fin = isfinite(SL) && isfinite(SM);
   if (MODE == 0) {
     const Hoist H = make_hoist(T, di, c, -1, 0.0);
-    if (H.gfast && fin) { dst0[c] = fma(H.p0 - 1.0, SL, (double)d.n * H.l1) - SM / H.p1; return; }
+    if (H.gfast && fin) {
+      if (lane == 0) dst0[c] = fma(H.p0 - 1.0, SL, (double)d.n * H.l1) - SM / H.p1;
+      return;
+    }
     double a = 0.0;
-    for (int i = 0; i < d.n; i++) a += calc_node_h(T, di, i, c, -1, 0.0, H);
-    dst0[c] = a;
+    for (int i = lane; i < d.n; i += 32) a += calc_node_h(T, di, i, c, -1, 0.0, H);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (lane == 0) dst0[c] = a;
   } else {
     bool hp = false;
     const double par = conj_par(T, dp, 0, c, gam, &hp);
     double coeff = 1.0;
     if (dp.link == NIMB_LINK_MULTIPLICATIVE) coeff = get_param(T, dp.decl, 0, c, dp.param, slot, 1.0);
-    if (fin && hp) { dst0[c] = (double)d.n * par; dst1[c] = coeff * SM; return; }
+    if (fin && hp) {
+      if (lane == 0) { dst0[c] = (double)d.n * par; dst1[c] = coeff * SM; }
+      return;
+    }
     double a0 = 0.0, a1 = 0.0;
-    for (int i = 0; i < d.n; i++) conj_contrib(T, dp, i, c, slot, gam, a0, a1, hp, par);
-    dst0[c] = a0; dst1[c] = a1;
+    for (int i = lane; i < d.n; i += 32) conj_contrib(T, dp, i, c, slot, gam, a0, a1, hp, par);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
+    if (lane == 0) { dst0[c] = a0; dst1[c] = a1; }
   }
 }
 
@@ -1579,10 +1592,20 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     if ((size_t)chunks * C > m->partials_cap) return fail("internal: partials scratch too small (bernoulli)");
     dim3 grid((C + 31) / 32, chunks);
     const bool latent = ba.vdata == nullptr, gated = ba.gate_slot >= 0;
-    if (latent && gated) k_bernlin_sum<true, true><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
-    else if (latent) k_bernlin_sum<true, false><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
-    else if (gated) k_bernlin_sum<false, true><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
-    else k_bernlin_sum<false, false><<<grid, BF_THREADS, 0, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    static std::atomic<unsigned long long> a11{0}, a10{0}, a01{0}, a00{0};
+    if (latent && gated) {
+      ensure_dyn_smem(k_bernlin_sum<true, true>, BF_SUM_SMEM, a11);
+      k_bernlin_sum<true, true><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    } else if (latent) {
+      ensure_dyn_smem(k_bernlin_sum<true, false>, BF_SUM_SMEM, a10);
+      k_bernlin_sum<true, false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    } else if (gated) {
+      ensure_dyn_smem(k_bernlin_sum<false, true>, BF_SUM_SMEM, a01);
+      k_bernlin_sum<false, true><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    } else {
+      ensure_dyn_smem(k_bernlin_sum<false, false>, BF_SUM_SMEM, a00);
+      k_bernlin_sum<false, false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    }
     m->launches++;
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));
     m->launches++;
@@ -1649,8 +1672,8 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
       }
       nimb200_dep dd{};
       if (dp) dd = *dp;
-      if (mode == 0) CK(launch_pdl(k_gamma_from_stats<0>, dim3((C + 127) / 128), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
-      else CK(launch_pdl(k_gamma_from_stats<2>, dim3((C + 127) / 128), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
+      if (mode == 0) CK(launch_pdl(k_gamma_from_stats<0>, dim3((C + 3) / 4), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
+      else CK(launch_pdl(k_gamma_from_stats<2>, dim3((C + 3) / 4), dim3(128), 0, m->stream, m->T, di, (const double*)m->d_gam_stats[di], dd, slot, gam, dst0, dst1));
       m->launches++;
       CK(cudaGetLastError());
       return 0;

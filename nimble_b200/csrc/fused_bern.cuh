@@ -51,7 +51,8 @@ static __device__ __noinline__ double bernlin_lp_cold(double v, double gate, dou
 }
 
 static const int BF_THREADS = 256;
-static const int BF_TILE = 2048;  // 32 KiB of staged nodes: a chunk is one or two tiles, so the staging latency is paid once
+static const int BF_TILE = 1024;  // 16 KiB of staged nodes (with the 41 KiB of tables three CTAs still fit an SM)
+static const size_t BF_SUM_SMEM = sizeof(double) * 2 * BF_TILE + BL_REP_BYTES;   // dynamic shared memory of k_bernlin_sum (BernNode = 16 bytes)
 static const int BF_W = 4;   // nodes in flight per lane: four independent exp / log chains keep the FP64 pipe fed
 
 // one staged node: 16 bytes (code: the data value 0 / 1, 2 = anything else)
@@ -77,11 +78,15 @@ __device__ __forceinline__ unsigned not01_bits(double v) {
 template <bool LATENT, bool GATED>
 __global__ void __launch_bounds__(BF_THREADS, 3)
 k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
-  __shared__ BernNode sn[BF_TILE];
+  extern __shared__ __align__(16) unsigned char bf_smem[];   // staged nodes | replicated tables (BL_REP_BYTES)
+  BernNode* sn = reinterpret_cast<BernNode*>(bf_smem);
+  double* rep = reinterpret_cast<double*>(bf_smem + sizeof(BernNode) * BF_TILE);
   __shared__ double red[BF_THREADS / 32][32];
   __shared__ __align__(16) MathTab tab;
   load_mathtab(&tab, threadIdx.x, BF_THREADS);
+  load_bern_rep_tables(rep, threadIdx.x, BF_THREADS);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = BF_THREADS / 32;
+  const double* __restrict__ expL = rep + (lane & 15);
   const int c = blockIdx.x * 32 + lane;
   const bool live = c < T.C;
   const int cc = live ? c : T.C - 1;
@@ -142,7 +147,7 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
         for (int j = 0; j < BF_W; j++) acc += bernlin_lp_cold(LATENT ? vv[j] : a.vdata[t0 + k + j], gt[j], eta[j], &tab);
         continue;
       }
-      bern_logit_lp_vecy<BF_W, true, false>(eta, y1, lp, nullptr, &tab);
+      bern_logit_lp_rep<BF_W, true>(eta, y1, lp, expL, &tab);
 #pragma unroll
       for (int j = 0; j < BF_W; j++) {
         if (GATED) acc += __double2hiint(gt[j]) != 0 ? lp[j] : (y1[j] ? -INFINITY : 0.0);   // gate 0: dbinom(v, 1, 0)
@@ -170,7 +175,7 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
 __global__ void __launch_bounds__(BF_THREADS)
 k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs pz, BernArgs py, double* __restrict__ contrib_z,
                        double* __restrict__ contrib_y) {
-  __shared__ __align__(16) MathTab tab;
+  __shared__ __align__(16) MathTab tab;   // plain tables: a CTA serves 256 (site, chain) pairs, too few to pay for 41 KiB of copies
   load_mathtab(&tab, threadIdx.x, BF_THREADS);
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];

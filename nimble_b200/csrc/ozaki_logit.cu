@@ -142,70 +142,6 @@ __device__ __forceinline__ void oz_ld8(uint32_t taddr, int (&v)[8]) {
                : "r"(taddr));
 }
 
-// The epilogue's look-up tables (2^(j/64), 1/c_j, log c_j) are held 16 times, T[j][copy]: lane l reads copy l & 15, so the 32
-// lanes of a load hit 16 different bank pairs whatever their indices -- exactly the two wavefronts a 64-bit load needs (one
-// shared copy: 4.8 wavefronts per look-up with realistic predictors, ncu r2o).  logc[128] = ln 2 here (the centre 2 of the
-// moderate path, bern_logit.cuh), so the look-up needs no special case.
-static const int OZ_TAB_ENTRIES = 64 + 129 + 129;
-static const int OZ_TAB_BYTES = OZ_TAB_ENTRIES * 16 * 8;
-
-// dbern-logit log-density of four nodes (one row, four chains): the moderate path of bern_logit_lp_vec (every |eta| < 8) on
-// the replicated tables, anything else on the general path.  ysign: the row's y as a sign mask test (y1 = y != 0).
-__device__ __forceinline__ void oz_bern_lp4(const double (&eta)[4], bool y1, double (&out)[4], const double* __restrict__ expL,
-                                            const MathTab* __restrict__ tab) {
-  const double* __restrict__ K = c_tab_misc;   // constant bank: 18 warps of 4-warp allocation granularity leave 96 registers
-  unsigned amax = 0;
-#pragma unroll
-  for (int j = 0; j < 4; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
-  if (!__all_sync(0xffffffffu, amax < 0x40200000u)) {   // warp-uniform, practically never taken
-    bern_logit_lp_vec<4, true, false>(eta, y1, out, nullptr, tab);
-    return;
-  }
-  const double* __restrict__ invL = expL + 64 * 16;
-  const double* __restrict__ logL = expL + (64 + 129) * 16;
-  double x[4], t[4], r[4], pl[4], d[4];
-  int n[4];
-#pragma unroll
-  for (int j = 0; j < 4; j++) x[j] = __hiloint2double(__double2hiint(eta[j]) | (int)0x80000000, __double2loint(eta[j]));  // -|eta|
-#pragma unroll
-  for (int j = 0; j < 4; j++) t[j] = fma(x[j], K[0], K[1]);
-#pragma unroll
-  for (int j = 0; j < 4; j++) { n[j] = __double2loint(t[j]); t[j] = t[j] - K[1]; }
-#pragma unroll
-  for (int j = 0; j < 4; j++) r[j] = fma(t[j], K[2], x[j]);
-#pragma unroll
-  for (int j = 0; j < 4; j++) r[j] = fma(t[j], K[3], r[j]);
-#pragma unroll
-  for (int j = 0; j < 4; j++) pl[j] = fma(r[j], K[4], K[5]);
-#pragma unroll
-  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], K[6]);
-#pragma unroll
-  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], 0.5);
-#pragma unroll
-  for (int j = 0; j < 4; j++) pl[j] = fma(pl[j], r[j], 1.0);
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    const double Tj = expL[(n[j] & 63) * 16];
-    const double v = fma(Tj * r[j], pl[j], Tj);
-    const double e = __hiloint2double(__double2hiint(v) + (n[j] & ~63) * 16384, __double2loint(v));
-    d[j] = 1.0 + e;  // in (1, 2]
-  }
-#pragma unroll
-  for (int j = 0; j < 4; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 is the centre 2
-    const int idx = (__double2hiint(d[j]) - 0x3ff00000 + 0x1000) >> 13;
-    const double rr = fma(d[j], invL[idx * 16], -1.0);
-    double Q = fma(rr, K[8], K[9]);
-    Q = fma(Q, rr, K[10]);
-    Q = fma(Q, rr, K[11]);
-    Q = fma(Q, rr, 1.0 / 3.0);
-    Q = fma(Q, rr, -0.5);
-    const double lp = fma(rr * rr, Q, rr);
-    const double lg = logL[idx * 16] + lp;
-    const bool neg = __double2hiint(eta[j]) < 0;
-    out[j] = (y1 == neg ? x[j] : 0.0) - lg;  // x = -|eta|
-  }
-}
-
 // ---------------------------------------------------------------------------------------------------------------- slicing
 // digit s of r (|r| < 1/2): d = rint(128 r), remainder 128 r - d (exact)
 __device__ __forceinline__ int oz_digit(double& r) {
@@ -273,7 +209,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
   double* s_red = (double*)(s_f + OZ_NC);                           // [4 quarters][64 chains]
   double* s_cs = s_red + 4 * OZ_NC;                                 // chain scales 2^f [64] (NaN: poisoned chain)
   MathTab* tab = (MathTab*)(s_cs + OZ_NC);
-  double* s_rep = (double*)(tab + 1);                               // the replicated tables (OZ_TAB_BYTES)
+  double* s_rep = (double*)(tab + 1);                               // the replicated tables (BL_REP_BYTES)
   uint64_t *a_full = bars, *a_empty = bars + 2, *t_full = bars + 4, *t_empty = bars + 6;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -283,10 +219,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
   const int ntiles = max(0, tile_hi - tile_lo);
 
   for (int i = tid; i < (int)(sizeof(MathTab) / sizeof(double)); i += OZ_THREADS) ((double*)tab)[i] = ((const double*)&g_mathtab)[i];
-  for (int i = tid; i < OZ_TAB_ENTRIES * 16; i += OZ_THREADS) {
-    const int e = i >> 4;
-    s_rep[i] = e < 64 ? g_mathtab.expT[e] : e < 64 + 129 ? g_mathtab.invc[e - 64] : (e - 193 == 128 ? c_tab_misc[7] : g_mathtab.logA[e - 193]);
-  }
+  load_bern_rep_tables(s_rep, tid, OZ_THREADS);
   // beta of this CTA's 64 chains -> int8 slices in the canonical layout [half][k16 chunk][slice][chain group 0..3][chain 0..7][16 B]:
   // per half, the eight slices of its 32 chains stacked along N make ONE 256-row K-major operand
   if (tid < OZ_NC) {
@@ -455,7 +388,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
             const double dl = __longlong_as_double(lo[cb * 4 + j] + 0x4178000000000000ll) - 25165824.0;
             eta[j] = ((dh + dl) * rs) * s_cs[h * OZ_NH + cq * 8 + cb * 4 + j];
           }
-          oz_bern_lp4(eta, y1, lp, expL, tab);
+          { const bool yv4[4] = {y1, y1, y1, y1}; bern_logit_lp_rep<4, true>(eta, yv4, lp, expL, tab); }
 #pragma unroll
           for (int j = 0; j < 4; j++)
             if (live) csum[h][cb * 4 + j] += lp[j];
@@ -492,7 +425,7 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
 
 // ---------------------------------------------------------------------------------------------------------------- host side
 static size_t oz_smem_bytes() {
-  return 2 * (size_t)OZ_TILE_BYTES + OZ_S * OZ_SLICE_B + 8 * 8 + 8 + OZ_NC * 4 + 4 * OZ_NC * 8 + OZ_NC * 8 + sizeof(MathTab) + OZ_TAB_BYTES + 64;
+  return 2 * (size_t)OZ_TILE_BYTES + OZ_S * OZ_SLICE_B + 8 * 8 + 8 + OZ_NC * 4 + 4 * OZ_NC * 8 + OZ_NC * 8 + sizeof(MathTab) + BL_REP_BYTES + 64;
 }
 
 size_t ozaki_xq_bytes(int n, int p) {
