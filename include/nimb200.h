@@ -339,6 +339,10 @@ int nimb200_debug_math(int32_t which, const double *x, int32_t n, double *out);
  * buffers.  Not used by the sampling path (measured slower than the FP64 mma.sync kernel). */
 int nimb200_debug_ozaki(const double *X, const double *y, int32_t n, int32_t p, const double *beta, int32_t C, double *eta_out,
                         double *sums_out, double *ms_out);
+/* diagnostic: clock64 timeline of CTA (0, 0) of that kernel.  First call (out = NULL) switches the stamps on; after one or more
+ * nimb200_debug_ozaki calls, the second call copies them out ([18 warps][64 tiles][2 halves][4 events], int64) and switches
+ * them off again (scripts/probe_ozaki_trace.py). */
+int nimb200_debug_ozaki_trace(long long *out_or_null);
 
 /* No counterpart in the reference (NIMBLE has no device code and nothing in it is asked to run without
  * allocating).  Per-chain block log-probability of y[i] ~ dbern(ilogit(inprod(X[i,1:p], beta[1:p]))) -- the quantity
@@ -370,6 +374,10 @@ int nimb200_mcmc_sampler_times(nimb200_model *m, double *out_ms, int32_t n);
  * out[1] = lppd, out[2] = pWAIC, out[3] = number of (iteration, chain) samples used.  Data-sharded models are not supported. */
 int nimb200_waic_enable(nimb200_model *m, int32_t enable);
 int nimb200_waic_get(nimb200_model *m, double *out4);
+/* data-sharded models: every rank accumulates the statistics of its own slice of the data nodes; out4 = {sum over those nodes
+ * of log(sum exp lp) (before the -n log(count) term), sum of the per-node sums of squares, number of nodes, count}.  The
+ * caller adds the first three over the ranks of the group: lppd = S0 - S2 log(count), pWAIC = S1 / (count - 1). */
+int nimb200_waic_partial(nimb200_model *m, double *out4);
 
 /* initializeModel (P/R/initializeModel.R:78-139): every non-data stochastic node whose value is NaN (a missing initial value)
  * is simulated from its own distribution given its parents, declaration by declaration in the order given (parents first);

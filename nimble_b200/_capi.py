@@ -63,6 +63,7 @@ class Backend:
                                    C.c_int32, _dp])
         if has_device:
             self._timing = fn("mcmc_last_timing", [vp, _dp, C.POINTER(C.c_int64)])
+            self._waic_partial = fn("waic_partial", [vp, _dp])
             self._summary = fn("samples_summary", [vp, C.c_int32, C.c_int32, _dp])
             self._hist_enable = fn("sampler_history_enable", [vp, C.c_int32])
             self._hist = fn("sampler_history", [vp, C.c_int32, C.c_int32, _dp, C.c_int64, C.POINTER(C.c_int32)])
@@ -186,6 +187,12 @@ class DeviceModel:
 
     def waic_enable(self, enable=True):
         self.backend.check(self.backend._waic_enable(self.h, int(bool(enable))))
+
+    def waic_partial(self):
+        """(log-sum part, sum of squares, nodes, count) over the data nodes this rank accounts for (data-sharded models)."""
+        out = np.zeros(4)
+        self.backend.check(self.backend._waic_partial(self.h, _ptr(out)))
+        return out
 
     def waic_get(self):
         """{'WAIC', 'lppd', 'pWAIC', 'n'} of the online conditional WAIC accumulated so far."""

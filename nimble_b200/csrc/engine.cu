@@ -697,7 +697,7 @@ __global__ void k_waic_update(DevTab T, int di, double* __restrict__ acc, long l
   if (it <= nburnin) return;
   const int n = T.decl[di].n;
   int node = blockIdx.x * blockDim.x + threadIdx.x;
-  if (node >= n) return;
+  if (node >= n || node < T.shard_lo[di] || node >= T.shard_hi[di]) return;   // data-sharded: this rank's slice of the data nodes
   double mx = acc[node], cs = acc[(size_t)n + node], mean = acc[2 * (size_t)n + node], ss = acc[3 * (size_t)n + node];
   long long cnt = base_count + (it - nburnin - 1) * (long long)T.C;
   for (int c = 0; c < T.C; c++) {
@@ -2572,6 +2572,8 @@ extern "C" int nimb200_enable_data_sharding_peer(nimb200_model* m, int32_t nrank
     if (r == rank) {
       if ((void*)(uintptr_t)h.ptr != m->xchg_local) return fail("handle[rank] is not this model's own export");
       base = m->xchg_local;
+    } else if (h.pid == (uint64_t)getpid() && h.device == m->device) {
+      base = (void*)(uintptr_t)h.ptr;          // same process, same device (two ranks sharing a GPU: tests on a one-GPU box)
     } else if (h.pid == (uint64_t)getpid()) {  // same process, another device: plain peer access
       int can = 0;
       CK(cudaDeviceCanAccessPeer(&can, m->device, h.device));
@@ -2834,7 +2836,6 @@ extern "C" int nimb200_mcmc_run(nimb200_model* m, int64_t niter, int64_t nburnin
   if (!reset && nburnin != 0) return fail("cannot specify nburnin when using reset = FALSE.");
   CK(cudaSetDevice(m->device));
   int C = m->C, nmon = (int)m->monitors.size();
-  if (m->waic && m->nranks > 1) return fail("online WAIC on a data-sharded model is not supported");
   if (reset) {
     m->rows = 0; m->iter_done = 0;
     if (m->waic) {
@@ -3366,23 +3367,47 @@ extern "C" int nimb200_waic_enable(nimb200_model* m, int32_t enable) {
   return 0;
 }
 
-extern "C" int nimb200_waic_get(nimb200_model* m, double* out4) {
-  if (!m || !out4) return fail("null argument");
+// the sums behind WAIC over the data nodes this rank accounts for: its slice of a sharded declaration; a replicated one on rank 0
+static int waic_sums(nimb200_model* m, double* logsum_out, double* ssq_out, long* nnodes_out) {
   if (m->d_waic.empty()) return fail("online WAIC was not enabled (nimb200_waic_enable)");
   CK(cudaSetDevice(m->device));
   CK(cudaStreamSynchronize(m->stream));
-  const double cnt = (double)m->waic_count;
   double logsum = 0.0, ssq = 0.0;
   long nnodes = 0;
   std::vector<double> h;
   for (size_t i = 0; i < m->decl.size(); i++) {
     if (!m->d_waic[i]) continue;
     const size_t n = (size_t)m->decl[i].n;
+    size_t lo = 0, hi = n;
+    if (m->nranks > 1) {
+      if (m->sharded[i]) { lo = (size_t)m->shard_lo[i]; hi = (size_t)m->shard_hi[i]; }
+      else if (m->rank != 0) hi = 0;
+    }
     h.resize(4 * n);
     CK(cudaMemcpy(h.data(), m->d_waic[i], sizeof(double) * 4 * n, cudaMemcpyDeviceToHost));
-    for (size_t j = 0; j < n; j++) { logsum += h[j] + log(h[n + j]); ssq += h[3 * n + j]; }  // MCMC_WAIC.R:276-278
-    nnodes += (long)n;
+    for (size_t j = lo; j < hi; j++) { logsum += h[j] + log(h[n + j]); ssq += h[3 * n + j]; }  // MCMC_WAIC.R:276-278
+    nnodes += (long)(hi > lo ? hi - lo : 0);
   }
+  *logsum_out = logsum; *ssq_out = ssq; *nnodes_out = nnodes;
+  return 0;
+}
+
+extern "C" int nimb200_waic_partial(nimb200_model* m, double* out4) {
+  if (!m || !out4) return fail("null argument");
+  double logsum, ssq;
+  long nnodes;
+  if (waic_sums(m, &logsum, &ssq, &nnodes)) return 1;
+  out4[0] = logsum; out4[1] = ssq; out4[2] = (double)nnodes; out4[3] = (double)m->waic_count;
+  return 0;
+}
+
+extern "C" int nimb200_waic_get(nimb200_model* m, double* out4) {
+  if (!m || !out4) return fail("null argument");
+  if (m->nranks > 1) return fail("data-sharded model: sum nimb200_waic_partial over the ranks of the group (nimble_b200.parallel.waic_sharded)");
+  const double cnt = (double)m->waic_count;
+  double logsum, ssq;
+  long nnodes;
+  if (waic_sums(m, &logsum, &ssq, &nnodes)) return 1;
   if (m->waic_count < 2) { out4[0] = out4[1] = out4[2] = NAN; out4[3] = cnt; return 0; }
   const double lppd = logsum - (double)nnodes * log(cnt), pwaic = ssq / (cnt - 1.0);
   out4[0] = -2.0 * (lppd - pwaic); out4[1] = lppd; out4[2] = pwaic; out4[3] = cnt;

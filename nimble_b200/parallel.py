@@ -54,6 +54,28 @@ def attach_data_sharding(dm, nranks, shard, group_ranks=None, transport="peer", 
         raise ValueError("transport must be 'peer' or 'nccl'")
 
 
+def waic_from_partials(parts):
+    """WAIC of a data-sharded run from the ranks' nimb200_waic_partial results (MCMC_WAIC.R:276-279)."""
+    parts = np.asarray(parts, dtype=np.float64).reshape(-1, 4)
+    logsum, ssq, nnodes = parts[:, 0].sum(), parts[:, 1].sum(), parts[:, 2].sum()
+    cnt = parts[0, 3]
+    if cnt < 2:
+        return {"WAIC": float("nan"), "lppd": float("nan"), "pWAIC": float("nan"), "count": cnt}
+    lppd = logsum - nnodes * np.log(cnt)
+    pwaic = ssq / (cnt - 1.0)
+    return {"WAIC": -2.0 * (lppd - pwaic), "lppd": lppd, "pWAIC": pwaic, "count": cnt}
+
+
+def waic_sharded(dm, group=None):
+    """Online WAIC of a data-sharded model: every rank holds the statistics of its slice of the data nodes; their sums over
+    the group's ranks give the same lppd and pWAIC as the unsharded run (every rank returns the same dictionary)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    parts = [None] * world
+    dist.all_gather_object(parts, dm.waic_partial().tolist(), group=group)
+    return waic_from_partials(parts)
+
+
 def run_chain_sharded(mcmc_factory, niter, nburnin=0, thin=1, nchains=1, inits=None, seed=0, group=None):
     """Run `nchains` chains split over the ranks of the default (or given) process group.
 

@@ -1,6 +1,8 @@
 """GPU, two ranks on two GPUs: data-node sharding with the all-reduce inside the library (its own kernel over NVLink peer memory,
 or NCCL), and chain sharding.
-Skipped unless the box has at least two GPUs (never run two ranks on one GPU: kernels that wait on one another)."""
+Skipped unless the box has at least two GPUs -- except test_two_ranks_on_one_device_share_the_exchange, which puts both ranks
+of a group on device 0 (their all-reduce kernels are one block each and co-resident; a rank that never arrives times out inside
+the kernel) so that the data-sharded path is exercised on a one-GPU box as well."""
 import os
 import sys
 
@@ -144,3 +146,18 @@ def test_two_devices_in_one_process_share_the_exchange():
     single = nb.compileNimble(nb.buildMCMC(conf), backend=backend, device=1).run_chains(inits, 120, 10, 1, True, 17)  # fused kernel on device 1
     err = np.abs(out[0] - single) / np.maximum(1.0, np.abs(single))
     assert err.max() < 1e-9, err.max()
+
+
+@pytest.mark.parametrize("name", ["logistic", "lmm", "glmm", "occupancy"])
+def test_two_ranks_on_one_device_share_the_exchange(name):
+    """The data-sharded path on a one-GPU box (tests/one_device_ranks.py): two models on device 0 of ONE process are the two
+    ranks of a group, each driven from its own host thread.  Run in a child process with eager module loading: loading a
+    kernel lazily synchronises the context, which cannot complete while the other rank's all-reduce kernel spins."""
+    if _ngpu() < 1:
+        pytest.skip("needs a GPU")
+    import subprocess
+    import sys
+    env = dict(os.environ, CUDA_MODULE_LOADING="EAGER")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "tests.one_device_ranks", name], cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
