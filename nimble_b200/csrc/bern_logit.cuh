@@ -248,7 +248,7 @@ __device__ __forceinline__ void load_bern_rep_tables(double* dst, int tid, int n
   }
 }
 // W nodes at once; expL = the replicated tables + (lane & 15); tab = the plain tables for the general path.
-template <int W, bool VOTE>
+template <int W, bool VOTE, int REP = 16>
 __device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
                                                   const double* __restrict__ expL, const MathTab* __restrict__ tab) {
   const double* __restrict__ K = c_tab_misc;
@@ -260,8 +260,8 @@ __device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const 
     bern_logit_lp_vecy<W, VOTE, false>(eta, y1v, out, nullptr, tab);
     return;
   }
-  const double* __restrict__ invL = expL + 64 * 16;
-  const double* __restrict__ logL = expL + (64 + 129) * 16;
+  const double* __restrict__ invL = expL + 64 * REP;
+  const double* __restrict__ logL = expL + (64 + 129) * REP;
   double x[W], t[W], r[W], pl[W], d[W];
   int n[W];
 #pragma unroll
@@ -284,7 +284,7 @@ __device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const 
   for (int j = 0; j < W; j++) pl[j] = fma(pl[j], r[j], 1.0);
 #pragma unroll
   for (int j = 0; j < W; j++) {
-    const double Tj = expL[(n[j] & 63) * 16];
+    const double Tj = expL[(n[j] & 63) * REP];
     const double v = fma(Tj * r[j], pl[j], Tj);
     const double e = __hiloint2double(__double2hiint(v) + (n[j] & ~63) * 16384, __double2loint(v));
     d[j] = 1.0 + e;  // in (1, 2]
@@ -292,14 +292,14 @@ __device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const 
 #pragma unroll
   for (int j = 0; j < W; j++) {  // log(d): centre c = 1 + idx/128, idx = 128 is the centre 2
     const int idx = (__double2hiint(d[j]) - 0x3ff00000 + 0x1000) >> 13;
-    const double rr = fma(d[j], invL[idx * 16], -1.0);
+    const double rr = fma(d[j], invL[idx * REP], -1.0);
     double Q = fma(rr, K[8], K[9]);
     Q = fma(Q, rr, K[10]);
     Q = fma(Q, rr, K[11]);
     Q = fma(Q, rr, 1.0 / 3.0);
     Q = fma(Q, rr, -0.5);
     const double lp = fma(rr * rr, Q, rr);
-    const double lg = logL[idx * 16] + lp;
+    const double lg = logL[idx * REP] + lp;
     const bool neg = __double2hiint(eta[j]) < 0;
     out[j] = (y1v[j] == neg ? x[j] : 0.0) - lg;  // x = -|eta|
   }

@@ -423,6 +423,218 @@ k_oz_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------------- two CTAs per SM
+// Third structure (round 2): a CTA owns 32 chains and ONE accumulator stage (8 weights x 32 columns = 256 TMEM columns), one
+// A stage, 8 epilogue warps (lane quarter x 16 columns) -- and two such CTAs share an SM.  Inside a CTA the chain
+// MMA -> TMEM loads -> arithmetic is serial apart from the second half of the arithmetic (the stage is handed back as soon
+// as the second batch of 8 columns is in registers); the other CTA's arithmetic fills the gap.  Why: with 16 epilogue warps on
+// two stages of one CTA the warps drift a whole tile apart and the four warps of a scheduler end up waiting for the tensor
+// cores together (timeline in profiles/r2q_ozaki_summary.md); two independent CTAs cannot wait together for long.
+static const int OZ2_NC = 32;                              // chains per CTA = UMMA rows of the stacked operand / 8
+static const int OZ2_EPI_WARPS = 8;
+static const int OZ2_THREADS = 64 + 32 * OZ2_EPI_WARPS;    // 320
+static const int OZ2_REP = 8;                              // copies of the look-up tables (two CTAs' shared memory must fit an SM)
+static const int OZ2_B_BYTES = OZ_S * OZ2_NC * OZ_K;       // 16384
+
+__global__ void __launch_bounds__(OZ2_THREADS, 2)
+k_oz2_bern_logit(const unsigned char* __restrict__ Xq, int n, int p, const double* __restrict__ state, int beta_slot, int C,
+                 int tiles_per_chunk, int tile_begin, int tile_end, double* __restrict__ partials, double* __restrict__ eta_out,
+                 int dbg) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  unsigned char* sA = smem;                                         // one stage: OZ_TILE_BYTES
+  unsigned char* sB = sA + OZ_TILE_BYTES;                           // OZ2_B_BYTES
+  uint64_t* bars = (uint64_t*)(sB + OZ2_B_BYTES);                   // a_full a_empty t_full t_empty
+  uint32_t* s_tmem = (uint32_t*)(bars + 4);
+  double* s_red = (double*)(s_tmem + 2);                            // [4 quarters][32 chains]
+  double* s_cs = s_red + 4 * OZ2_NC;                                // chain scales 2^f [32] (NaN: poisoned chain)
+  MathTab* tab = (MathTab*)(s_cs + OZ2_NC);
+  double* s_rep = (double*)(tab + 1);                               // tables, OZ2_REP copies
+  uint64_t *a_full = bars, *a_empty = bars + 1, *t_full = bars + 2, *t_empty = bars + 3;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  long long* trace = (blockIdx.x == 0 && blockIdx.y == 0) ? g_oz_trace : nullptr;
+  const int chain0 = blockIdx.x * OZ2_NC, chunk = blockIdx.y;
+  const int tile_lo = tile_begin + chunk * tiles_per_chunk, tile_hi = min(tile_end, tile_lo + tiles_per_chunk);
+  const int ntiles = max(0, tile_hi - tile_lo);
+
+  for (int i = tid; i < (int)(sizeof(MathTab) / sizeof(double)); i += OZ2_THREADS) ((double*)tab)[i] = ((const double*)&g_mathtab)[i];
+  for (int i = tid; i < BL_REP_ENTRIES * OZ2_REP; i += OZ2_THREADS) {
+    const int e = i / OZ2_REP;
+    s_rep[i] = e < 64 ? g_mathtab.expT[e] : e < 64 + 129 ? g_mathtab.invc[e - 64] : (e - 193 == 128 ? c_tab_misc[7] : g_mathtab.logA[e - 193]);
+  }
+  if (tid < OZ2_NC) {   // beta of this CTA's 32 chains -> [k16 chunk][slice][chain group 0..3][chain 0..7][16 B]: one 256-row operand
+    const int c = chain0 + tid;
+    double mx = 0.0;
+    bool bad = false;
+    if (c < C)
+      for (int k = 0; k < p; k++) {
+        const double v = state[(size_t)(beta_slot + k) * C + c];
+        bad |= !isfinite(v);
+        mx = fmax(mx, fabs(v));
+      }
+    int f = (mx > 0.0 && !bad) ? ilogb(mx) + 2 : 0;
+    if (f < -400 || f > 400) { bad = true; f = 0; }
+    s_cs[tid] = bad ? __longlong_as_double(0x7ff8000000000000ll) : __hiloint2double((1023 + f) << 20, 0);
+    for (int k = 0; k < OZ_K; k++) {
+      double rem = (c < C && k < p && !bad) ? scalbn(state[(size_t)(beta_slot + k) * C + c], -f) : 0.0;
+      for (int sl = 0; sl < OZ_S; sl++) {
+        const int d = oz_digit(rem);
+        sB[(k >> 4) * (OZ_S * OZ2_NC * 16) + (sl * 4 + (tid >> 3)) * 128 + (tid & 7) * 16 + (k & 15)] = (unsigned char)(signed char)d;
+      }
+    }
+  }
+  if (tid == 0) {
+    oz_mbar_init(a_full, 1);
+    oz_mbar_init(a_empty, 1 + OZ2_EPI_WARPS);
+    oz_mbar_init(t_full, 1);
+    oz_mbar_init(t_empty, OZ2_EPI_WARPS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // half of the SM's TMEM: the co-resident CTA takes the other half
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(oz_smem(s_tmem)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+
+  if (warp == 0) {
+    // ===================================================== producer: one bulk copy per tile into the single stage
+    if (lane == 0) {
+      for (int it = 0; it < ntiles; it++) {
+        if (it >= 1) oz_mbar_wait<100>(a_empty, (uint32_t)((it - 1) & 1));
+        oz_mbar_expect_tx(a_full, (uint32_t)OZ_TILE_BYTES);
+        oz_bulk_g2s(sA, Xq + (size_t)(tile_lo + it) * OZ_TILE_BYTES, (uint32_t)OZ_TILE_BYTES, a_full);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer: 8 slices x 2 K steps per tile, N = (8 - s) 32
+    const uint32_t aB = oz_smem(sB), aA = oz_smem(sA);
+    const uint32_t leader = oz_elect();
+    const uint64_t da0 = oz_desc(aA, 2048, 128);
+    const uint64_t db0 = oz_desc(aB, OZ_S * OZ2_NC * 16, 128);
+    for (int it = 0; it < ntiles; it++) {
+      OZ_STAMP(it, 0, 0);
+      oz_mbar_wait(a_full, (uint32_t)(it & 1));
+      if (it >= 1) oz_mbar_wait(t_empty, (uint32_t)((it - 1) & 1));
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      OZ_STAMP(it, 0, 1);
+      if ((dbg & 3) != 2) {
+#pragma unroll
+        for (int sl = 0; sl < OZ_S; sl++) {
+#pragma unroll
+          for (int ks = 0; ks < 2; ks++) {
+            const uint64_t da = da0 + (uint64_t)((sl * OZ_SLICE_A + ks * 4096) >> 4);
+            const uint64_t db = db0 + (uint64_t)((ks * 2 * OZ_S * OZ2_NC * 16) >> 4);
+            if ((sl | ks) != 0) oz_mma<1>(tmem + (uint32_t)(sl * OZ2_NC), da, db, oz_idesc((OZ_S - sl) * OZ2_NC), leader);
+            else oz_mma<0>(tmem, da, db, oz_idesc(OZ_S * OZ2_NC), leader);
+          }
+        }
+      }
+      oz_commit(t_full, leader);      // accumulators of the tile complete -> epilogue
+      oz_commit(a_empty, leader);     // every MMA reading the A stage has completed -> producer
+      OZ_STAMP(it, 0, 2);
+    }
+  } else {
+    // ===================================================== epilogue: row = TMEM lane = thread, 16 columns in two batches of 8
+    const int ew = warp - 2;
+    const int q = warp & 3;                      // TMEM lane quarter this warp may touch
+    const int c16 = (ew >> 2) * 16;              // which 16 of the 32 columns
+    const int row = q * 32 + lane;
+    const double* __restrict__ expL = s_rep + (lane & (OZ2_REP - 1));
+    double csum[2][8];
+#pragma unroll
+    for (int b8 = 0; b8 < 2; b8++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) csum[b8][j] = 0.0;
+    for (int it = 0; it < ntiles; it++) {
+      oz_mbar_wait(a_full, (uint32_t)(it & 1));   // y and the row exponents travel with the tile
+      const double yv = ((const double*)(sA + OZ_S * OZ_SLICE_A))[row];
+      const int er = ((const int*)(sA + OZ_S * OZ_SLICE_A + OZ_M * 8))[row];
+      __syncwarp();
+      if (lane == 0) oz_mbar_arrive(a_empty);     // this warp no longer needs the stage
+      const bool live = __double2hiint(yv) >= 0, y1 = (__double2hiint(yv) | __double2loint(yv)) != 0;   // y is 0, 1 or -1 (past n)
+      const double rs = __hiloint2double((1023 + er - 35) << 20, 0);   // 2^(er - 35): the row's share of the scale
+      const long long grow = (long long)(tile_lo + it) * OZ_M + row;
+      OZ_STAMP(it, 0, 0);
+      oz_mbar_wait(t_full, (uint32_t)(it & 1));
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      OZ_STAMP(it, 0, 1);
+#pragma unroll
+      for (int b8 = 0; b8 < 2; b8++) {
+        const uint32_t base = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(c16 + b8 * 8);
+        long long hi[8], lo[8];
+        {
+          int a[2][8], b[8];
+          oz_ld8(base, a[0]); oz_ld8(base + (uint32_t)OZ2_NC, a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 8; j++) b[j] = a[0][j] * 128 + a[1][j];
+          oz_ld8(base + (uint32_t)(2 * OZ2_NC), a[0]); oz_ld8(base + (uint32_t)(3 * OZ2_NC), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 8; j++) hi[j] = (long long)b[j] * 16384 + (a[0][j] * 128 + a[1][j]);
+          oz_ld8(base + (uint32_t)(4 * OZ2_NC), a[0]); oz_ld8(base + (uint32_t)(5 * OZ2_NC), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 8; j++) b[j] = a[0][j] * 128 + a[1][j];
+          oz_ld8(base + (uint32_t)(6 * OZ2_NC), a[0]); oz_ld8(base + (uint32_t)(7 * OZ2_NC), a[1]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (b8 == 1) {   // everything of the stage is in registers: hand it back before the arithmetic
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) oz_mbar_arrive(t_empty);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; j++) lo[j] = (long long)b[j] * 16384 + (a[0][j] * 128 + a[1][j]);
+        }
+        OZ_STAMP(it, b8, 2);
+        if ((dbg & 3) == 1) { csum[b8][0] += (double)(hi[0] + lo[7]); continue; }   // diagnostic: no epilogue arithmetic
+#pragma unroll
+        for (int cb = 0; cb < 2; cb++) {
+          double eta[4], lp[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const double dh = __longlong_as_double(hi[cb * 4 + j] + 0x4338000000000000ll) - 6755399441055744.0;
+            const double dl = __longlong_as_double(lo[cb * 4 + j] + 0x4178000000000000ll) - 25165824.0;
+            eta[j] = ((dh + dl) * rs) * s_cs[c16 + b8 * 8 + cb * 4 + j];
+          }
+          { const bool yv4[4] = {y1, y1, y1, y1}; bern_logit_lp_rep<4, true, OZ2_REP>(eta, yv4, lp, expL, tab); }
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if (live) csum[b8][cb * 4 + j] += lp[j];
+          if (eta_out) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+              const int c = chain0 + c16 + b8 * 8 + cb * 4 + j;
+              if (live && grow < n && c < C) eta_out[(size_t)grow * C + c] = eta[j];
+            }
+          }
+        }
+        OZ_STAMP(it, b8, 3);
+      }
+    }
+#pragma unroll
+    for (int b8 = 0; b8 < 2; b8++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        double v = csum[b8][j];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_red[q * OZ2_NC + c16 + b8 * 8 + j] = v;
+      }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (tid < OZ2_NC) {
+    const int c = chain0 + tid;
+    if (c < C) partials[(size_t)chunk * C + c] = ((s_red[tid] + s_red[OZ2_NC + tid]) + s_red[2 * OZ2_NC + tid]) + s_red[3 * OZ2_NC + tid];
+  }
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+}
+
 // ---------------------------------------------------------------------------------------------------------------- host side
 static size_t oz_smem_bytes() {
   return 2 * (size_t)OZ_TILE_BYTES + OZ_S * OZ_SLICE_B + 8 * 8 + 8 + OZ_NC * 4 + 4 * OZ_NC * 8 + OZ_NC * 8 + sizeof(MathTab) + BL_REP_BYTES + 64;
@@ -448,13 +660,25 @@ int ozaki_chunks(int n) {  // 16 chain tiles x 37 chunks = 4 waves of 148 one-CT
   return std::min((n + OZ_M - 1) / OZ_M, 37);
 }
 
+static size_t oz2_smem_bytes() {
+  return (size_t)OZ_TILE_BYTES + OZ2_B_BYTES + 4 * 8 + 8 + 4 * OZ2_NC * 8 + OZ2_NC * 8 + sizeof(MathTab) + BL_REP_ENTRIES * OZ2_REP * 8 + 64;
+}
+
 void ozaki_bern_logit_launch(const unsigned char* Xq, int n, int p, const double* state, int beta_slot, int C, double* partials,
                              int tile_begin, int tile_end, double* eta_out, cudaStream_t st) {
-  static std::atomic<unsigned long long> attr{0};
-  ensure_dyn_smem(k_oz_bern_logit, oz_smem_bytes(), attr);
+  static std::atomic<unsigned long long> attr{0}, attr2{0};
   const int chunks = ozaki_chunks(n);
   const int ntiles = std::max(0, tile_end - tile_begin);
   const int tpc = (ntiles + chunks - 1) / chunks;
+  const int dbg = getenv("NIMB200_OZ_DBG") ? atoi(getenv("NIMB200_OZ_DBG")) : 0;
+  if (!getenv("NIMB200_OZ_ONE_CTA")) {   // two CTAs of 32 chains per SM
+    ensure_dyn_smem(k_oz2_bern_logit, oz2_smem_bytes(), attr2);
+    dim3 grid2((C + OZ2_NC - 1) / OZ2_NC, chunks);
+    k_oz2_bern_logit<<<grid2, OZ2_THREADS, oz2_smem_bytes(), st>>>(Xq, n, p, state, beta_slot, C, std::max(1, tpc), tile_begin, tile_end,
+                                                                 partials, eta_out, dbg);
+    return;
+  }
+  ensure_dyn_smem(k_oz_bern_logit, oz_smem_bytes(), attr);
   dim3 grid((C + OZ_NC - 1) / OZ_NC, chunks);
   k_oz_bern_logit<<<grid, OZ_THREADS, oz_smem_bytes(), st>>>(Xq, n, p, state, beta_slot, C, std::max(1, tpc), tile_begin, tile_end,
                                                              partials, eta_out, getenv("NIMB200_OZ_DBG") ? atoi(getenv("NIMB200_OZ_DBG")) : 0);
