@@ -179,3 +179,20 @@ def test_batched_ess_equals_the_scalar_estimator():
     s = np.stack([x.T, x.T[::-1]])                     # [2 chains][rows][7 cols]
     m, tot = min_ess(s)
     assert abs(m - min(t for t in tot if t > 0)) < 1e-9 and tot[5] == 0.0
+
+
+def test_waic_from_rank_partials():
+    """Data-sharded WAIC: the ranks' partial sums (log-sum part, sum of squares, nodes, count) add up to the unsharded
+    statistics (MCMC_WAIC.R:276-279)."""
+    from nimble_b200.parallel import waic_from_partials
+    rng = np.random.default_rng(3)
+    n, cnt = 37, 50
+    lp = rng.normal(-1.0, 0.3, (cnt, n))                      # per-sample, per-node log-densities
+    logmeanexp = np.log(np.exp(lp).mean(0))
+    want_lppd, want_p = logmeanexp.sum(), lp.var(0, ddof=1).sum()
+    logsumexp, ssq = np.log(np.exp(lp).sum(0)), ((lp - lp.mean(0)) ** 2).sum(0)
+    parts = [[logsumexp[:20].sum(), ssq[:20].sum(), 20, cnt], [logsumexp[20:].sum(), ssq[20:].sum(), 17, cnt]]
+    w = waic_from_partials(parts)
+    assert abs(w["lppd"] - want_lppd) < 1e-10 and abs(w["pWAIC"] - want_p) < 1e-10
+    assert abs(w["WAIC"] + 2 * (want_lppd - want_p)) < 1e-10
+    assert np.isnan(waic_from_partials([[0.0, 0.0, 3, 1]])["WAIC"])
