@@ -1208,6 +1208,7 @@ struct nimb200_model {
   // group sums S[t][c] = sum over target t's nodes of exp(b1 x) for chain c's CURRENT b1 (fused_pois.cuh): with them a block sum or
   // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
   std::vector<double*> d_pois_S, d_pois_Snew;
+  std::vector<int32_t*> d_pois_list;   // per sweep: chains that need the node pass [C] + their count
   std::vector<char> pois_S_valid, pois_S_pending;
   // i.i.d. gamma declarations with chain-level parameters (k_gamma_stats): eligibility, [2][C] statistics, validity
   std::vector<char> gam_iid, gam_stats_valid;
@@ -1451,6 +1452,7 @@ static int ensure_pois_ysum(nimb200_model* m, int s) {
   const nimb200_sampler& sp = m->samplers[s];
   const int dd = m->deps[sp.dep_off + 1].decl;
   PoisArgs pa = pois_args(m, dd);
+  CK(cudaMemsetAsync(m->d_pois_ysum[s] + pois_stats_doubles((size_t)sp.n_targets) - 1, 0, sizeof(double), m->stream));   // max over targets
   k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[dd], m->d_pois_ysum[s]);
   m->launches++;
   const bool sh = m->nranks > 1 && m->sweep_sharded[s] && !m->target_sharded[s];
@@ -1462,8 +1464,16 @@ static int ensure_pois_ysum(nimb200_model* m, int s) {
 static int launch_pois_S(nimb200_model* m, int s, double* out) {
   const nimb200_sampler& sp = m->samplers[s];
   PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
-  k_pois_S<<<dim3((m->C + 31) / 32, (sp.n_targets + PS3_TPB - 1) / PS3_TPB), PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out,
-                                                                                                             m->pois_series ? 1 : 0);
+  const dim3 grid((m->C + 31) / 32, (sp.n_targets + PS3_TPB - 1) / PS3_TPB);
+  if (m->pois_series && m->d_pois_list[s]) {
+    // moment series where it applies; the node pass for the listed chains only (its grid is sized for all of them: blocks
+    // beyond the list return at once, so the launch sequence does not depend on the count and replays from the CUDA graph)
+    k_pois_S_series<<<grid, PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out);
+    k_pois_chain_list<<<1, 32, 0, m->stream>>>(m->T, pa, m->d_pois_ysum[s] + pois_stats_doubles((size_t)sp.n_targets) - 1, m->d_pois_list[s]);
+    k_pois_S<<<grid, PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out, (const int*)m->d_pois_list[s]);
+    m->launches += 2;
+  } else
+    k_pois_S<<<grid, PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out, (const int*)nullptr);
   m->launches++;
   CK(cudaGetLastError());
   return 0;
@@ -2092,6 +2102,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->pois_ysum_valid.assign(m->samplers.size(), 0);
   m->d_pois_S.assign(m->samplers.size(), nullptr);
   m->d_pois_Snew.assign(m->samplers.size(), nullptr);
+  m->d_pois_list.assign(m->samplers.size(), nullptr);
   m->pois_S_valid.assign(m->samplers.size(), 0);
   m->pois_S_pending.assign(m->samplers.size(), 0);
   TRY(dev_alloc(m, &m->d_accept, (size_t)nchains));
@@ -2200,6 +2211,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       m->pois_series = !getenv("NIMB200_NO_SERIES");
       TRY(dev_alloc(m, &m->d_pois_S[s], (size_t)sp.n_targets * C));
       TRY(dev_alloc(m, &m->d_pois_Snew[s], (size_t)sp.n_targets * C));
+      TRY(dev_alloc(m, &m->d_pois_list[s], (size_t)C + 1));
     }
   }
   // The binary sweep of the occupancy family evaluates, for the state it leaves behind, every node of the sites' own declaration and
@@ -2686,6 +2698,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     const bool sh = m->nranks > 1 && m->sweep_sharded[s] && !m->target_sharded[s];
     PoisArgs pa = pois_args(m, m->deps[sp.dep_off + 1].decl);
     if (!m->pois_ysum_valid[s]) {
+      CK(cudaMemsetAsync(m->d_pois_ysum[s] + pois_stats_doubles((size_t)sp.n_targets) - 1, 0, sizeof(double), m->stream));   // max over targets
       k_pois_group_ysum<<<(sp.n_targets + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, (const PoisNode*)m->d_nodeconst[m->deps[sp.dep_off + 1].decl],
                                                                            m->d_pois_ysum[s]);
       m->launches++;

@@ -197,7 +197,7 @@ k_pois_sum(DevTab T, PoisArgs a, const PoisNode* __restrict__ pk, int lo, int hi
 static const int PF_MOM_K = 24;
 static const int PF_MOM_N = PF_MOM_K + 1;
 static const double PF_MOM_UMAX = 2.0;   // the series serves |b1| max|x| <= 2
-__host__ __device__ inline size_t pois_stats_doubles(size_t nT) { return nT * (4 + PF_MOM_N); }
+__host__ __device__ inline size_t pois_stats_doubles(size_t nT) { return nT * (4 + PF_MOM_N) + 1; }   // + max over targets of xm
 __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode* __restrict__ pk, double* __restrict__ stats) {
   const nimb200_sampler sp = T.samplers[sid];
   int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -217,6 +217,9 @@ __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode*
   stats[(size_t)sp.n_targets + t] = sa;
   stats[2 * (size_t)sp.n_targets + t] = sxy;
   stats[3 * (size_t)sp.n_targets + t] = xm;
+  // max over the targets (non-negative doubles order like their bit patterns; a NaN counts as +Inf): the chain list's bound
+  atomicMax(reinterpret_cast<unsigned long long*>(stats + pois_stats_doubles((size_t)sp.n_targets) - 1),
+            (unsigned long long)__double_as_longlong(xm == xm ? xm : INFINITY));
   double mom[PF_MOM_N];
 #pragma unroll
   for (int k = 0; k < PF_MOM_N; k++) mom[k] = 0.0;
@@ -339,56 +342,94 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
 // Moment series (round 2): with u = b1 xm,  sum_i exp(b1 x_i) = sum_k u^k mom[t][k]  -- the group's covariates enter through
 // PF_MOM_N data-only coefficients, so a (target, chain) costs 24 fused multiply-adds (Horner) instead of one exp per node
 // (~1200 FP64 instructions for the benchmark's 100 nodes per group).  Truncation: |u| <= 2 leaves 2^25/25! = 2e-18 of n;
-// rounding: the terms are bounded by n e^|u| against a sum of at least n e^-|u|, i.e. <= e^4 x a few ulp.  Chains with
-// |u| > 2 take the node loop below: grid (chain tiles of 32, blocks of PS3_TPB targets), lane = chain, warp w takes targets
-// w, w + 8, ..; the warp stages the covariates in shared memory (coalesced loads, broadcast reads), four nodes per trip = four
-// independent 12-instruction exp chains per lane and five other instructions per evaluation.
+// rounding: the terms are bounded by n e^|u| against a sum of at least n e^-|u|, i.e. <= e^4 x a few ulp (k_pois_S_series).
+// Chains with |u| > 2 for some target are listed (k_pois_chain_list) and take the node pass (k_pois_S): grid (tiles of 32
+// listed chains, blocks of PS3_TPB targets), lane = chain, warp w takes targets w, w + 8, ..; the warp stages the covariates in
+// shared memory (coalesced loads, broadcast reads), four nodes per trip = four independent 12-instruction exp chains per lane
+// and five other instructions per evaluation.
 // A (target, chain) whose |b1| max|x| reaches 300 (or is NaN) is marked NaN -- its users then take their exact per-node paths,
 // because exp(b0) exp(b1 x) and exp(b0 + b1 x) part ways once either factor over- or underflows.  Targets sharded by ownership
 // (group-aligned shards): the owner alone computes a target's S.
 static const int PS3_TPB = 64;
 static const int PS3_XCH = 128;   // nodes of a target staged per step and warp
+
+// the series part: lane = chain, warp w takes targets w, w + 8, ..; writes S where |b1| max|x|_t <= 2 and nothing elsewhere
+// (those (target, chain) pairs belong to chains of the list below and are written by the node pass)
+__global__ void __launch_bounds__(PF_THREADS)
+k_pois_S_series(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double* __restrict__ S) {
+  const nimb200_sampler sp = T.samplers[sid];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  if (c >= T.C) return;
+  const size_t C = (size_t)T.C;
+  const double b1 = T.state[(size_t)a.b1_slot * C + c];
+  const nimb200_dep tp0 = T.deps[sp.dep_off];
+  const int t_lo = blockIdx.y * PS3_TPB, t_hi = min(sp.n_targets, t_lo + PS3_TPB);
+  const double* __restrict__ xmax = stats + 3 * (size_t)sp.n_targets;
+  const double* __restrict__ mom = stats + 4 * (size_t)sp.n_targets;
+  for (int t = t_lo + warp; t < t_hi; t += PF_THREADS / 32) {
+    const int tn = (tp0.sel == NIMB_SEL_SAME ? tp0.a + t : tp0.a);
+    if (tn < T.shard_lo[tp0.decl] || tn >= T.shard_hi[tp0.decl]) continue;
+    const double u = b1 * xmax[t];
+    const double* __restrict__ mk = mom + (size_t)t * PF_MOM_N;   // the same addresses for all lanes: broadcast loads
+    double h = __ldg(mk + PF_MOM_K);
+#pragma unroll
+    for (int k = PF_MOM_K - 1; k >= 0; k--) h = fma(h, u, __ldg(mk + k));
+    if (fabs(u) <= PF_MOM_UMAX) S[(size_t)t * C + c] = h;
+  }
+}
+
+// the chains that need the node pass for at least one target, in chain order: |b1| max_t max|x|_t > 2 (or NaN).  One warp,
+// ballot compaction: list[0 .. count), count in list[C].  While the RW scale on b1 is unadapted that is about half of the
+// chains, a few per cent of them for hundreds of iterations afterwards, none in the end -- and the node pass costs in
+// proportion, where a pass by tiles of 32 consecutive chains ran in full as long as one chain per tile was left.
+__global__ void k_pois_chain_list(DevTab T, PoisArgs a, const double* __restrict__ xmax_all, int* __restrict__ list) {
+  const int lane = threadIdx.x;
+  const double xm = *xmax_all;
+  int count = 0;
+  for (int base = 0; base < T.C; base += 32) {
+    const int c = base + lane;
+    const bool need = c < T.C && !(fabs(T.state[(size_t)a.b1_slot * T.C + c]) * xm <= PF_MOM_UMAX);
+    const unsigned mask = __ballot_sync(0xffffffffu, need);
+    if (need) list[count + __popc(mask & ((1u << lane) - 1u))] = c;
+    count += __popc(mask);
+  }
+  if (lane == 0) list[T.C] = count;
+}
+
+// the node pass.  list == nullptr: every chain, tile blockIdx.x of 32 consecutive chains (no series: NIMB200_NO_SERIES);
+// else: the chains of the list, tile blockIdx.x of it, and only the (target, chain) pairs the series did not serve are written.
 __global__ void __launch_bounds__(PF_THREADS, 4)
-k_pois_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double* __restrict__ S, int use_series) {
+k_pois_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double* __restrict__ S, const int* __restrict__ list) {
   __shared__ double expTs[PF_EXPT_DOUBLES];
   __shared__ __align__(16) double xs[PF_THREADS / 32][PS3_XCH];
+  const int count = list ? list[T.C] : T.C;
+  if (blockIdx.x * 32 >= count) return;
   pois_load_expT(expTs, threadIdx.x, PF_THREADS);
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const double* __restrict__ expT = expTs + lane;
-  const int c = blockIdx.x * 32 + lane;
-  const int cc = c < T.C ? c : T.C - 1;
+  const int ci = blockIdx.x * 32 + lane;
+  const bool live = ci < count;
+  const int c = list ? list[live ? ci : count - 1] : (live ? ci : count - 1);
   const size_t C = (size_t)T.C;
-  const double b1 = T.state[(size_t)a.b1_slot * C + cc];
+  const double b1 = T.state[(size_t)a.b1_slot * C + c];
   const nimb200_dep tp0 = T.deps[sp.dep_off], dp = T.deps[sp.dep_off + 1];
   const int t_lo = blockIdx.y * PS3_TPB, t_hi = min(sp.n_targets, t_lo + PS3_TPB);
   const double* __restrict__ xmax = stats + 3 * (size_t)sp.n_targets;
-  const double* __restrict__ mom = stats + 4 * (size_t)sp.n_targets;
   double K[7];
 #pragma unroll
   for (int j = 0; j < 7; j++) K[j] = c_tab_misc[j];
   const double* __restrict__ xa = a.x;
   double* __restrict__ xw = xs[warp];
-  double sser = 0.0;
   for (int t = t_lo + warp; t < t_hi; t += PF_THREADS / 32) {
     const int tn = (tp0.sel == NIMB_SEL_SAME ? tp0.a + t : tp0.a);
     if (tn < T.shard_lo[tp0.decl] || tn >= T.shard_hi[tp0.decl]) continue;
     const Sel s = sel_of(T, dp, t);
     const double u = b1 * xmax[t];
     const bool regular = fabs(u) < 300.0;
-    const bool series = use_series && fabs(u) <= PF_MOM_UMAX;
-    if (use_series) {   // Horner on the 25 coefficients (the same addresses for all lanes: broadcast loads)
-      const double* __restrict__ mk = mom + (size_t)t * PF_MOM_N;
-      double h = __ldg(mk + PF_MOM_K);
-#pragma unroll
-      for (int k = PF_MOM_K - 1; k >= 0; k--) h = fma(h, u, __ldg(mk + k));
-      if (__all_sync(0xffffffffu, series)) {
-        if (c < T.C) S[(size_t)t * C + c] = h;
-        continue;
-      }
-      if (series) sser = h;
-    }
+    const bool series = list != nullptr && fabs(u) <= PF_MOM_UMAX;   // served by k_pois_S_series
     const double bb = regular ? b1 : 0.0;   // keeps the table index in range; the result is discarded
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
     for (int k0 = s.lo; k0 < s.hi; k0 += PS3_XCH) {
@@ -411,7 +452,7 @@ k_pois_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double
       }
       for (; k < cnt; k++) s0 += pois_exp_core(bb * xw[k], expT, K);
     }
-    if (c < T.C) S[(size_t)t * C + c] = series ? sser : regular ? (s0 + s1) + (s2 + s3) : NAN;
+    if (live && !series) S[(size_t)t * C + c] = regular ? (s0 + s1) + (s2 + s3) : NAN;
   }
 }
 
