@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--ess-niter", type=int, default=5000,
                     help="iterations of the min-ESS/s protocol run (SURVEY 8d: niter 5000, nburnin = niter / 2); 0 skips it")
     ap.add_argument("--ess-chains", type=int, default=0, help="chains the ESS estimate uses (0 = all chains of the rank)")
-    ap.add_argument("--ref-ess-budget-s", type=float, default=420.0,
+    ap.add_argument("--ref-ess-budget-s", type=float, default=240.0,
                     help="reference arm: wall-clock budget of its min-ESS/s protocol run; it stops early (and says so) beyond it")
     return ap.parse_args()
 
