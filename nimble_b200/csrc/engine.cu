@@ -556,21 +556,23 @@ k_small_iters(DevTab T, SmallPlan P, const SamplerDev* __restrict__ sdev, uint64
 // dependent (stepping out, then shrinkage), so the whole update is one loop in one thread over the target's dependents with the
 // candidate value in the override register.  Uniforms: call 0 = (auxiliary exponential, interval offset), call 1 = (split of
 // maxSteps, first candidate), call 2 + j = j-th shrinkage candidate.
-__device__ double slice_lp(const DevTab& T, const nimb200_sampler& sp, int t, int c, int slot, double value) {
-  double lp[2] = {0.0, 0.0};
-  for (int stage = 0; stage < 2; stage++) {
-    for (int e = 0; e < sp.n_dep; e++) {
-      const nimb200_dep dp = T.deps[sp.dep_off + e];
-      if (dp.stage != stage) continue;
-      Sel s = sel_of(T, dp, t);
-      for (int k = s.lo; k < s.hi; k++) {
-        int node = s.idx ? s.idx[k] : k;
-        lp[stage] += calc_node(T, dp.decl, node, c, slot, value);
-      }
+__device__ double slice_lp_stage(const DevTab& T, const nimb200_sampler& sp, int t, int c, int slot, double value, int stage) {
+  double lp = 0.0;
+  for (int e = 0; e < sp.n_dep; e++) {
+    const nimb200_dep dp = T.deps[sp.dep_off + e];
+    if (dp.stage != stage) continue;
+    Sel s = sel_of(T, dp, t);
+    for (int k = s.lo; k < s.hi; k++) {
+      int node = s.idx ? s.idx[k] : k;
+      lp += calc_node(T, dp.decl, node, c, slot, value);
     }
-    if (stage == 0 && lp[0] == -INFINITY) return -INFINITY;  // setAndCalculateTarget: prior -Inf short-circuits
   }
-  return lp[0] + lp[1];
+  return lp;
+}
+__device__ double slice_lp(const DevTab& T, const nimb200_sampler& sp, int t, int c, int slot, double value) {
+  const double lp0 = slice_lp_stage(T, sp, t, c, slot, value, 0);
+  if (lp0 == -INFINITY) return -INFINITY;  // setAndCalculateTarget: prior -Inf short-circuits
+  return lp0 + slice_lp_stage(T, sp, t, c, slot, value, 1);
 }
 __global__ void k_slice(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S) {
   const nimb200_sampler sp = T.samplers[sid];
@@ -638,14 +640,56 @@ __global__ void k_categorical(DevTab T, int sid, uint64_t seed, uint64_t iter) {
   int t = (int)tq, slot = sp.target_slot + t;
   DrawKey key = make_key(T, seed, iter, sid, t, c);
   double* sv = T.state + (size_t)slot * T.C + c;
-  const int K = T.decl[T.deps[sp.dep_off].decl].fam_arg[0];
+  const nimb200_dep d0 = T.deps[sp.dep_off];
+  const nimb200_decl& td = T.decl[d0.decl];
+  const int K = td.fam_arg[0];
   double lps[NIMB200_MAX_CATEGORIES];
   double maxLP = -INFINITY;
-  for (int i = 1; i <= K; i++) {
-    double lp = slice_lp(T, sp, t, c, slot, (double)i);  // prior first (-Inf short-circuits), then the dependents
-    if (isnan(lp)) lp = -INFINITY;
-    lps[i - 1] = lp;
-    maxLP = fmax(maxLP, lp);
+  // The target's own dcat density is log(p_i) - log(sum p) for category i: the K probabilities and their sum do not depend on
+  // the candidate, so they are evaluated once instead of once per category (the same operations in the same order as
+  // calc_node's, hence the same bits) when the prior stage is exactly the target's own node.
+  bool own_prior = d0.stage == 0 && d0.sel == NIMB_SEL_SAME && td.dist == NIMB_DCAT;
+  for (int e = 1; e < sp.n_dep && own_prior; e++) own_prior = T.deps[sp.dep_off + e].stage != 0;
+  double logsum = 0.0;
+  bool bad = false;
+  if (own_prior) {
+    const int tnode = d0.a + t;
+    double sum = 0.0;
+    for (int j = 0; j < K; j++) {
+      const double pj = eval_prog(T, c, td.prog_off[0], td.prog_len[0], tnode, j, -1, 0.0);
+      bad |= isnan(pj) || pj < 0;
+      sum += pj;
+      lps[j] = pj;
+    }
+    logsum = log(sum);
+  }
+  if (own_prior) {
+    // dependents: entry by entry and node by node on the outside (selection and entry loaded once), categories on the inside;
+    // every category still adds its dependents up in the same order as slice_lp does
+    double dsum[NIMB200_MAX_CATEGORIES];
+    for (int i = 0; i < K; i++) dsum[i] = 0.0;
+    for (int e = 1; e < sp.n_dep; e++) {
+      const nimb200_dep dp = T.deps[sp.dep_off + e];
+      const Sel s = sel_of(T, dp, t);
+      for (int k = s.lo; k < s.hi; k++) {
+        const int node = s.idx ? s.idx[k] : k;
+        for (int i = 0; i < K; i++) dsum[i] += calc_node(T, dp.decl, node, c, slot, (double)(i + 1));
+      }
+    }
+    for (int i = 0; i < K; i++) {
+      const double lp0 = 0.0 + (bad ? NAN : log(lps[i]) - logsum);
+      double lp = lp0 == -INFINITY ? -INFINITY : lp0 + dsum[i];   // setAndCalculateTarget: a -Inf prior short-circuits
+      if (isnan(lp)) lp = -INFINITY;
+      lps[i] = lp;
+      maxLP = fmax(maxLP, lp);
+    }
+  } else {
+    for (int i = 1; i <= K; i++) {
+      double lp = slice_lp(T, sp, t, c, slot, (double)i);  // prior first (-Inf short-circuits), then the dependents
+      if (isnan(lp)) lp = -INFINITY;
+      lps[i - 1] = lp;
+      maxLP = fmax(maxLP, lp);
+    }
   }
   double sum = 0.0;
   for (int i = 0; i < K; i++) { lps[i] = det_exp(lps[i] - maxLP); sum += lps[i]; }
