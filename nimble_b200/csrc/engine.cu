@@ -1253,6 +1253,9 @@ struct nimb200_model {
   // a conjugate sweep of the Poisson family reads no node; one pass (k_pois_conj_sweep<3>) when b1 moves
   std::vector<double*> d_pois_S, d_pois_Snew;
   std::vector<int32_t*> d_pois_list;   // per sweep: chains that need the node pass [C] + their count
+  std::vector<double*> d_pois_chainpar;   // per sweep: [3][C] exp(b0), prior shape, prior rate (k_pois_chain_params)
+  std::vector<char> pois_chain_level;     // ... usable: the targets' prior parameter programs are chain-level
+  std::vector<int32_t> h_pconst;          // host copy of T.pconst
   std::vector<char> pois_S_valid, pois_S_pending;
   // i.i.d. gamma declarations with chain-level parameters (k_gamma_stats): eligibility, [2][C] statistics, validity
   std::vector<char> gam_iid, gam_stats_valid;
@@ -1985,6 +1988,7 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
     TRYCU(cudaMemcpyAsync(dpc, pc.data(), sizeof(int32_t) * pc.size(), cudaMemcpyHostToDevice, m->stream));
     TRYCU(cudaStreamSynchronize(m->stream));
     m->T.pconst = dpc;
+    m->h_pconst = pc;
     m->gam_iid.assign(m->decl.size(), 0);
     m->gam_stats_valid.assign(m->decl.size(), 0);
     m->d_gam_stats.assign(m->decl.size(), nullptr);
@@ -2147,6 +2151,8 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
   m->d_pois_S.assign(m->samplers.size(), nullptr);
   m->d_pois_Snew.assign(m->samplers.size(), nullptr);
   m->d_pois_list.assign(m->samplers.size(), nullptr);
+  m->d_pois_chainpar.assign(m->samplers.size(), nullptr);
+  m->pois_chain_level.assign(m->samplers.size(), 0);
   m->pois_S_valid.assign(m->samplers.size(), 0);
   m->pois_S_pending.assign(m->samplers.size(), 0);
   TRY(dev_alloc(m, &m->d_accept, (size_t)nchains));
@@ -2256,6 +2262,9 @@ extern "C" int nimb200_model_create(const nimb200_table* t, int32_t nchains, int
       TRY(dev_alloc(m, &m->d_pois_S[s], (size_t)sp.n_targets * C));
       TRY(dev_alloc(m, &m->d_pois_Snew[s], (size_t)sp.n_targets * C));
       TRY(dev_alloc(m, &m->d_pois_list[s], (size_t)C + 1));
+      TRY(dev_alloc(m, &m->d_pois_chainpar[s], (size_t)3 * C));
+      const int tdecl = m->deps[sp.dep_off].decl;
+      m->pois_chain_level[s] = m->decl[tdecl].nparam >= 2 && m->h_pconst[3 * tdecl] && m->h_pconst[3 * tdecl + 1];
     }
   }
   // The binary sweep of the occupancy family evaluates, for the state it leaves behind, every node of the sites' own declaration and
@@ -2760,8 +2769,14 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
           if (launch_pois_S(m, s, m->d_pois_S[s])) return 1;
           m->pois_S_valid[s] = 1;
         }
+        const bool chain_level = m->pois_chain_level[s] != 0;   // the targets' prior parameters read nothing indexed by the node
+        if (chain_level) {
+          k_pois_chain_params<<<(C + 127) / 128, 128, 0, m->stream>>>(m->T, s, pa, m->d_pois_chainpar[s]);
+          m->launches++;
+        }
         k_pois_conj_sweep<4><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], m->d_pois_S[s],
-                                                             byp ? m->d_pois_contrib[s] : nullptr);
+                                                             byp ? m->d_pois_contrib[s] : nullptr,
+                                                             chain_level ? (const double*)m->d_pois_chainpar[s] : (const double*)nullptr);
       } else
         k_pois_conj_sweep<0><<<nb, PF_THREADS, 0, m->stream>>>(m->T, s, seed, iter, pa, m->d_pois_ysum[s], nullptr,
                                                              byp ? m->d_pois_contrib[s] : nullptr);

@@ -252,7 +252,7 @@ __global__ void k_pois_group_ysum(DevTab T, int sid, PoisArgs a, const PoisNode*
 template <int PHASE>
 __global__ void __launch_bounds__(PF_THREADS, 4)
 k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, const double* __restrict__ ysum, double* __restrict__ part,
-                  double* __restrict__ contrib) {
+                  double* __restrict__ contrib, const double* __restrict__ chainpar = nullptr) {
   __shared__ double expT[64];
   if (threadIdx.x < 64) expT[threadIdx.x] = g_mathtab.expT[threadIdx.x];
   __syncthreads();
@@ -295,7 +295,7 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   if (PHASE == 2) { k = s.hi; c1 = part[(size_t)t * T.C + c]; }
   if (PHASE == 4) {  // regular chains: exp(b0) S; anything else (|b0| >= 300, S marked NaN by PHASE 3) walks the nodes below
     const double Sg = part[(size_t)t * T.C + c];
-    if (fabs(b0) < 300.0 && isfinite(Sg)) { k = s.hi; c1 = exp(b0) * Sg; }
+    if (fabs(b0) < 300.0 && isfinite(Sg)) { k = s.hi; c1 = (chainpar ? chainpar[c] : exp(b0)) * Sg; }
     else { k = s.hi; worst = 0x7ff00000u; }
   }
   for (; k + 1 < s.hi; k += 2) {
@@ -320,8 +320,10 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   const double c0 = ysum[t];
   const nimb200_dep tp = T.deps[sp.dep_off];
   int tnode = (tp.sel == NIMB_SEL_SAME ? tp.a + t : tp.a);
-  double prior_shape = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
-  double prior_rate = get_param(T, tp.decl, tnode, c, NIMB_PARAM_RATE, -1, 0.0);
+  // chain-level quantities (exp(b0), the prior's shape and rate when their programs read nothing indexed by the node) come
+  // from k_pois_chain_params: the same operations, once per chain instead of once per (target, chain)
+  double prior_shape = chainpar ? chainpar[(size_t)T.C + c] : get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+  double prior_rate = chainpar ? chainpar[2 * (size_t)T.C + c] : get_param(T, tp.decl, tnode, c, NIMB_PARAM_RATE, -1, 0.0);
   DrawKey key = make_key(T, seed, iter, sid, t, c);
   double shape = prior_shape + c0, scale = 1 / (prior_rate + c1);
   const double nl = rgamma1(key, shape) * scale;
@@ -454,6 +456,18 @@ k_pois_S(DevTab T, int sid, PoisArgs a, const double* __restrict__ stats, double
     }
     if (live && !series) S[(size_t)t * C + c] = regular ? (s0 + s1) + (s2 + s3) : NAN;
   }
+}
+
+// per chain: exp(b0), prior shape, prior rate of the sweep's targets (chain-level parameter programs only) -> out[3][C]
+__global__ void k_pois_chain_params(DevTab T, int sid, PoisArgs a, double* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= T.C) return;
+  const nimb200_sampler sp = T.samplers[sid];
+  const nimb200_dep tp = T.deps[sp.dep_off];
+  const int tnode = tp.sel == NIMB_SEL_SAME ? tp.a : tp.a;
+  out[c] = exp(T.state[(size_t)a.b0_slot * T.C + c]);
+  out[(size_t)T.C + c] = get_param(T, tp.decl, tnode, c, 0, -1, 0.0);
+  out[2 * (size_t)T.C + c] = get_param(T, tp.decl, tnode, c, NIMB_PARAM_RATE, -1, 0.0);
 }
 
 // Whole-declaration block sum from the data-only group sums (ysum = [sum y | sum A | sum x y] per target) and S:
