@@ -845,7 +845,17 @@ __global__ void __launch_bounds__(256) k_gamma_stats(DevTab T, int di, double* _
   double sl = 0.0, sm = 0.0;
   if (c < T.C) {
     const double* __restrict__ xp = T.state + (size_t)d.value_ref * T.C + c;
-    for (int r = r0 + warp; r < r1; r += 8) {
+    int r = r0 + warp;
+    for (; r + 24 < r1; r += 32) {   // four loads and four logarithms in flight; added in row order as below
+      double x4[4], l4[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) x4[j] = xp[(size_t)(r + 8 * j) * T.C];
+#pragma unroll
+      for (int j = 0; j < 4; j++) l4[j] = log(x4[j]);
+#pragma unroll
+      for (int j = 0; j < 4; j++) { sl += l4[j]; sm += x4[j]; }
+    }
+    for (; r < r1; r += 8) {
       const double x = xp[(size_t)r * T.C];
       sl += log(x);
       sm += x;
@@ -1515,8 +1525,8 @@ static int launch_pois_S(nimb200_model* m, int s, double* out) {
   if (m->pois_series && m->d_pois_list[s]) {
     // moment series where it applies; the node pass for the listed chains only (its grid is sized for all of them: blocks
     // beyond the list return at once, so the launch sequence does not depend on the count and replays from the CUDA graph)
-    k_pois_S_series<<<grid, PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out);
-    k_pois_chain_list<<<1, 32, 0, m->stream>>>(m->T, pa, m->d_pois_ysum[s] + pois_stats_doubles((size_t)sp.n_targets) - 1, m->d_pois_list[s]);
+    k_pois_S_series<<<dim3((m->C + 32 * PSS_CPT - 1) / (32 * PSS_CPT), grid.y), PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out);
+    k_pois_chain_list<<<1, 1024, 0, m->stream>>>(m->T, pa, m->d_pois_ysum[s] + pois_stats_doubles((size_t)sp.n_targets) - 1, m->d_pois_list[s]);
     k_pois_S<<<grid, PF_THREADS, 0, m->stream>>>(m->T, s, pa, m->d_pois_ysum[s], out, (const int*)m->d_pois_list[s]);
     m->launches += 2;
   } else
@@ -2863,8 +2873,8 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
       m->prop_lo = m->prop_hi = -1;
       for (size_t s2 = 0; s2 < m->samplers.size(); s2++) {  // a proposal that moved b1 of a Poisson family: accepted chains take the new group sums
         if (!m->pois_S_pending[s2]) continue;
-        const size_t tot = (size_t)m->samplers[s2].n_targets * C;
-        k_pois_S_commit<<<(unsigned)((tot + 255) / 256), 256, 0, m->stream>>>(m->d_pois_S[s2], m->d_pois_Snew[s2], m->d_accept, tot, C);
+        const int nT2 = m->samplers[s2].n_targets;
+        k_pois_S_commit<<<dim3((C + 255) / 256, (nT2 + 63) / 64), 256, 0, m->stream>>>(m->d_pois_S[s2], m->d_pois_Snew[s2], m->d_accept, nT2, C);
         m->launches++;
         m->pois_S_pending[s2] = 0;
       }
