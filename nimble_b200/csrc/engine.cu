@@ -838,6 +838,9 @@ __global__ void __launch_bounds__(256) k_gamma_stats(DevTab T, int di, double* _
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
   __shared__ double red[2][8][32];
+  __shared__ __align__(16) MathTab tab;
+  load_mathtab(&tab, threadIdx.x, 256);
+  __syncthreads();
   const nimb200_decl& d = T.decl[di];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
@@ -851,7 +854,8 @@ __global__ void __launch_bounds__(256) k_gamma_stats(DevTab T, int di, double* _
 #pragma unroll
       for (int j = 0; j < 4; j++) x4[j] = xp[(size_t)(r + 8 * j) * T.C];
 #pragma unroll
-      for (int j = 0; j < 4; j++) l4[j] = log(x4[j]);
+      for (int j = 0; j < 4; j++)   // table-driven logarithm for positive normal values (<= 1 ulp), the library's otherwise
+        l4[j] = (x4[j] >= 1e-300 && x4[j] < 1e300) ? log_tab(x4[j], &tab) : log(x4[j]);
 #pragma unroll
       for (int j = 0; j < 4; j++) { sl += l4[j]; sm += x4[j]; }
     }
