@@ -335,7 +335,10 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
     const double sa = ysum[(size_t)sp.n_targets + t], sxy = ysum[2 * (size_t)sp.n_targets + t];
     double v;
     if (nl == 0.0) v = c0 == 0.0 ? 0.0 : -INFINITY;        // dpois(y, 0)
-    else v = ((sa + c0 * (log(nl) + b0)) + b1 * sxy) - nl * c1;
+    else {   // table-driven logarithm for a positive normal draw (tables read through L1: a CTA serves only 256 pairs)
+      const double lg = (nl >= 1e-300 && nl < 1e300) ? log_tab(nl, &g_mathtab) : log(nl);
+      v = ((sa + c0 * (lg + b0)) + b1 * sxy) - nl * c1;
+    }
     contrib[(size_t)t * T.C + c] = v;
   }
 }
