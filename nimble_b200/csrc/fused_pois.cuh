@@ -10,8 +10,11 @@
 // divergence; log lam is taken when the group changes, and y = 0 needs no special case (A = 0, lp = -mu).
 // nmath evaluates bd0 by a Taylor series when y ~ mu to keep its RELATIVE accuracy; this form has absolute error
 // ~ 2e-16 y log y, which relative to lp (|lp| >= 0.5 log(2 pi y) for y >= 1) stays below 4e-13 for counts up to 1024:
-// inside the 1e-12 parity bar (tests/test_gpu_parity.py::test_pois_family_*).  Anything else (y > 1024, lam <= 0, NaN,
-// |eta| >= 700, mu outside [2^-963, 2^964)) takes the exact generic path per element, after the hot loop.
+// inside the 1e-12 parity bar (tests/test_gpu_parity.py::test_pois_family_*).  Anything else (y > 1024, lam outside
+// [1e-150, 1e150], NaN, |eta| >= 300) has the whole run of nodes redone, the exact generic path for those elements.
+// Round 2: an MCMC iteration no longer walks the nodes at all while proposals are of posterior width -- block sums and the
+// conjugate sweep come from per-group sums S_g(b1) = sum exp(b1 x), themselves evaluated from 25 data-only moment coefficients
+// per group (k_pois_S_series); see the comments at k_pois_conj_sweep and k_pois_S_series.
 #pragma once
 
 namespace nimb {
