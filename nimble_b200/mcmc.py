@@ -1109,7 +1109,7 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
     seed = 0 if (setSeed is None or isinstance(setSeed, (bool, np.bool_))) else int(setSeed)
     if setSeed is False:
         seed = int(np.random.SeedSequence().entropy % (1 << 63))
-    rows = []
+    per_chain = []
     for i in range(nchains):
         if callable(inits):
             these = inits()
@@ -1117,8 +1117,8 @@ def runMCMC(mcmc, niter=10000, nburnin=0, thin=None, inits=None, nchains=1, setS
             these = inits[i if len(inits) > 1 else 0]
         else:
             these = inits
-        rows.append(mcmc.model.init_vector(these))
-    samples = mcmc.run_chains(np.stack(rows), niter, nburnin, thin, True, seed, thin2=thin2)
+        per_chain.append(these)
+    samples = mcmc.run_chains(mcmc.model.init_matrix(per_chain), niter, nburnin, thin, True, seed, thin2=thin2)
     mats = [SampleMatrix(samples[c], mcmc.colnames) for c in range(nchains)]
     result = mats[0] if nchains == 1 else {"chain%d" % (c + 1): mats[c] for c in range(nchains)}
     ret = {"samples": result}

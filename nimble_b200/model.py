@@ -538,6 +538,34 @@ class Model:
         # (P/R/initializeModel.R:78-139; CompiledMCMC.run_chains -> nimb200_initialize_model)
         return out
 
+    def init_matrix(self, inits_list):
+        """init_vector for a list of per-chain inits at once ([chains][slots]): one assignment per variable when every
+        chain names the same variables (the usual case), instead of one Python pass over the variables per chain."""
+        n = len(inits_list)
+        dicts = [d or {} for d in inits_list]
+        keys = set(dicts[0])
+        if any(set(d) != keys for d in dicts):
+            return np.stack([self.init_vector(d) for d in dicts])
+        out = np.tile(self.init_vector(None), (n, 1))
+        for name_ in keys:
+            if name_ not in self.var_slot:
+                continue
+            slot, shape = self.var_slot[name_], self.var_shape[name_]
+            size = int(np.prod(shape)) if shape else 1
+            try:
+                vals = np.asarray([np.asarray(d[name_], dtype=np.float64) for d in dicts])
+            except ValueError:   # ragged: chain by chain
+                return np.stack([self.init_vector(d) for d in dicts])
+            if vals.size == n * size:
+                if vals.ndim > 2:   # arrays are stored column-major, as init_vector does
+                    vals = np.stack([v.reshape(-1, order="F") for v in vals])
+                out[:, slot:slot + size] = vals.reshape(n, size)
+            elif vals.size == n:    # a scalar broadcast over the variable
+                out[:, slot:slot + size] = vals.reshape(n, 1)
+            else:
+                return np.stack([self.init_vector(d) for d in dicts])
+        return out
+
     def simulable(self, var):
         """Can missing values of `var` be simulated on the device (a variate generator exists for its distribution)?"""
         return all(d.dist in (T.DNORM, T.DGAMMA, T.DBETA, T.DEXP, T.DLOGIS, T.DPOIS, T.DBINOM, T.DLNORM) for d in self.decl_of(var))
