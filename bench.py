@@ -275,10 +275,15 @@ def strong_scaling_block(a, nb, conf, model, backend, local, rank, world, dist, 
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, k_ms = (float(x) for x in t.cpu().numpy())
-    return {"what": "strong scaling: %d chains in total, %d per GPU, chain-sharded, no collective" % (total_chains, Cs),
-            "chains_total": total_chains, "chains_per_gpu": Cs, "ms_per_step": ms / a.steps,
-            "value": evals_iter * total_chains * a.steps / (ms * 1e-3), "unit": UNIT,
-            "fused_kernel_ms": k_ms, "non_kernel_ms_per_step": ms / a.steps - k_ms, "launches": int(launches)}
+    out = {"what": "strong scaling: %d chains in total, %d per GPU, chain-sharded, no collective" % (total_chains, Cs),
+           "chains_total": total_chains, "chains_per_gpu": Cs, "ms_per_step": ms / a.steps,
+           "value": evals_iter * total_chains * a.steps / (ms * 1e-3), "unit": UNIT,
+           "fused_kernel_ms": k_ms, "non_kernel_ms_per_step": ms / a.steps - k_ms, "launches": int(launches)}
+    if a.ess_niter > 0:   # the north-star's own figure: min-ESS/s of the 1024-chain job on N GPUs (same protocol and seed)
+        e = gpu_min_ess(a, nb, conf, backend, local, lo, inits, Cs, world, dist, torch)
+        out["min_ess_per_sec"] = e["min_ess_per_sec"]
+        out["min_ess"] = {k: e[k] for k in ("min_ess_total", "chains", "niter", "nburnin", "seconds", "worst_column")}
+    return out
 
 
 def main():
