@@ -196,3 +196,20 @@ def test_waic_from_rank_partials():
     assert abs(w["lppd"] - want_lppd) < 1e-10 and abs(w["pWAIC"] - want_p) < 1e-10
     assert abs(w["WAIC"] + 2 * (want_lppd - want_p)) < 1e-10
     assert np.isnan(waic_from_partials([[0.0, 0.0, 3, 1]])["WAIC"])
+
+
+def test_init_matrix_equals_per_chain_init_vectors():
+    """runMCMC flattens a list of per-chain inits per variable (Model.init_matrix): same rows as init_vector chain by chain --
+    scalars, vectors, a scalar broadcast over a vector, missing entries (NaN: simulated by initializeModel), ragged key sets."""
+    from nimble_b200 import configs
+    m, _ = configs.pump()
+    rng = np.random.default_rng(0)
+    cases = [
+        [{"alpha": 1.0 + k, "beta": 2.0, "theta": rng.random(10)} for k in range(7)],
+        [{"theta": 0.5 + k} for k in range(3)],                      # scalar broadcast over theta[1:10]
+        [None, {"alpha": 2.0}, {"alpha": 3.0, "beta": 1.0}],         # ragged: falls back to the per-chain path
+        [{} for _ in range(4)],
+    ]
+    for inits in cases:
+        want = np.stack([m.init_vector(i) for i in inits])
+        assert np.array_equal(m.init_matrix(inits), want, equal_nan=True)
