@@ -916,7 +916,10 @@ __global__ void k_gamma_from_stats(DevTab T, int di, const double* __restrict__ 
 }
 
 // wide RW: proposal for every chain; the old value is parked in tsave
-__global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* tsave, double* pls) {
+// prior_new (may be null): the target's own log-density under the proposal, i.e. what k_eval<0> would return for the
+// sampler's first dependency entry (one node) -- the same hoisted evaluation, one launch less per scalar RW step
+__global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S, double* tsave, double* pls,
+                             double* prior_new, int prior_node) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -930,6 +933,11 @@ __global__ void k_rw_propose(DevTab T, int sid, uint64_t seed, uint64_t iter, Sa
   tsave[c] = cur;
   *sv = rw_proposal(sp, cur, S.scale[c], z, propLogScale);
   pls[c] = propLogScale;
+  if (prior_new) {
+    const nimb200_dep d0 = T.deps[sp.dep_off];
+    const Hoist H = make_hoist(T, d0.decl, c, -1, 0.0);
+    prior_new[c] = 0.0 + calc_node_h(T, d0.decl, prior_node, c, -1, 0.0, H);
+  }
 }
 
 // wide RW_block: rmnorm_chol(values, chol_propCov_scale, prec_param = 0), dists.cpp:1132-1164.
@@ -2859,13 +2867,20 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
     int npair = (sp.d + 1) / 2;
     for (int tr = 0; tr < tries; tr++) {
       if (ensure_dep_sums(m, s)) return 1;
+      // scalar RW: the target's own density under the proposal comes out of the proposal kernel (entry 0 = the target's node)
+      const nimb200_dep& dp0 = m->deps[sp.dep_off];
+      const HostSel hs0 = host_sel(m, dp0, m->h_iarr);
+      const bool prior_fused = sp.type == NIMB_SAMPLER_RW && sp.n_targets == 1 && dp0.stage == 0 && !hs0.idx && hs0.hi - hs0.lo == 1 &&
+                               m->decl[dp0.decl].value_kind == 1 && m->decl[dp0.decl].value_ref + hs0.lo == sp.target_slot &&
+                               !(m->nranks > 1 && m->sharded[dp0.decl]) && !getenv("NIMB200_NO_FUSED_PRIOR");
       if (sp.type == NIMB_SAMPLER_RW)
-        CK(launch_pdl(k_rw_propose, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls));
+        CK(launch_pdl(k_rw_propose, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, m->sdev[s], m->d_tsave, m->d_pls,
+                      prior_fused ? m->d_newsum : (double*)nullptr, hs0.lo));
       else
         k_block_propose<<<(C + 15) / 16, dim3(16, NIMB200_MAX_BLOCK_D), 0, m->stream>>>(m->T, s, seed, iter, tr, m->sdev[s], m->d_tsave);
       m->launches++;
       m->prop_lo = sp.target_slot; m->prop_hi = sp.target_slot + (sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1);  // slots holding a proposal
-      for (int e = 0; e < sp.n_dep; e++) {
+      for (int e = prior_fused ? 1 : 0; e < sp.n_dep; e++) {
         const nimb200_dep& dp = m->deps[sp.dep_off + e];
         HostSel hs = host_sel(m, dp, m->h_iarr);
         if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
