@@ -224,6 +224,19 @@ __device__ double calc_node_h(const DevTab& T, int di, int i, int c, int ov_slot
   return NAN;
 }
 
+// thread index -> (target, chain), chains fastest.  A 64-bit division costs ~60 instructions; almost every launch has fewer than
+// 2^32 threads, where one 32-bit division does (warp-uniform choice)
+__device__ __forceinline__ void split_index(size_t gid, int C, size_t& tq, int& c) {
+  if ((gid >> 32) == 0) {
+    const unsigned g = (unsigned)gid, q = g / (unsigned)C;
+    tq = q;
+    c = (int)(g - q * (unsigned)C);
+  } else {
+    tq = gid / (size_t)C;
+    c = (int)(gid - tq * (size_t)C);
+  }
+}
+
 struct Sel { int lo, hi; const int32_t* idx; int nlo, nhi; };  // [nlo,nhi): node instances this rank owns (data sharding)
 __device__ __forceinline__ Sel sel_of(const DevTab& T, const nimb200_dep& dp, int t) {
   Sel s; s.idx = nullptr;
@@ -361,8 +374,9 @@ __device__ __forceinline__ void sweep_body(const DevTab& T, int sid, uint64_t se
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = gthread / LANES;
   const int lane = LANES == 1 ? 0 : (int)(gthread & (LANES - 1));
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
   int slot = sp.target_slot + t;
@@ -577,8 +591,9 @@ __device__ double slice_lp(const DevTab& T, const nimb200_sampler& sp, int t, in
 __global__ void k_slice(DevTab T, int sid, uint64_t seed, uint64_t iter, SamplerDev S) {
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq, slot = sp.target_slot + t;
   size_t q = (size_t)t * T.C + c;
@@ -634,8 +649,9 @@ __global__ void k_slice(DevTab T, int sid, uint64_t seed, uint64_t iter, Sampler
 __global__ void k_categorical(DevTab T, int sid, uint64_t seed, uint64_t iter) {
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq, slot = sp.target_slot + t;
   DrawKey key = make_key(T, seed, iter, sid, t, c);

@@ -180,8 +180,9 @@ k_bernlin_binary_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, BernArgs
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
   double* sv = T.state + (size_t)(sp.target_slot + t) * T.C + c;

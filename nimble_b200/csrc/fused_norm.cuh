@@ -461,8 +461,9 @@ __global__ void k_norm_conj_draw(DevTab T, int sid, uint64_t seed, uint64_t iter
   cudaGridDependencySynchronize();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
   const double ysum = gs[2 * (size_t)t], n = gs[2 * (size_t)t + 1];

@@ -261,8 +261,9 @@ k_pois_conj_sweep(DevTab T, int sid, uint64_t seed, uint64_t iter, PoisArgs a, c
   __syncthreads();
   const nimb200_sampler sp = T.samplers[sid];
   size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int c = (int)(gid % T.C);
-  size_t tq = gid / T.C;
+  int c;
+  size_t tq;
+  split_index(gid, T.C, tq, c);
   if (tq >= (size_t)sp.n_targets) return;
   int t = (int)tq;
   if (PHASE == 0 || PHASE == 3 || PHASE == 4) {  // targets sharded by ownership (group-aligned shards): the owner alone updates a target
