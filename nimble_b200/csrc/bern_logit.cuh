@@ -248,18 +248,32 @@ __device__ __forceinline__ void load_bern_rep_tables(double* dst, int tid, int n
   }
 }
 // W nodes at once; expL = the replicated tables + (lane & 15); tab = the plain tables for the general path.
-template <int W, bool VOTE, int REP = 16>
-__device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
-                                                  const double* __restrict__ expL, const MathTab* __restrict__ tab) {
-  const double* __restrict__ K = c_tab_misc;
+// is every |eta| < 8 (NaN fails)?  On the exponent bits, integer pipe.
+template <int W>
+__device__ __forceinline__ bool bern_logit_moderate(const double (&eta)[W]) {
   unsigned amax = 0;
 #pragma unroll
   for (int j = 0; j < W; j++) amax = max(amax, (unsigned)(__double2hiint(eta[j]) & 0x7fffffff));
-  const bool mod = amax < 0x40200000u;   // every |eta| < 8 (NaN fails the test)
+  return amax < 0x40200000u;
+}
+template <int W, int REP>
+__device__ __forceinline__ void bern_logit_lp_rep_mod(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
+                                                      const double* __restrict__ expL);
+template <int W, bool VOTE, int REP = 16>
+__device__ __forceinline__ void bern_logit_lp_rep(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
+                                                  const double* __restrict__ expL, const MathTab* __restrict__ tab) {
+  const bool mod = bern_logit_moderate<W>(eta);
   if (!(VOTE ? __all_sync(0xffffffffu, mod) : mod)) {
     bern_logit_lp_vecy<W, VOTE, false>(eta, y1v, out, nullptr, tab);
     return;
   }
+  bern_logit_lp_rep_mod<W, REP>(eta, y1v, out, expL);
+}
+// the moderate path itself: the caller has established that every |eta| < 8
+template <int W, int REP>
+__device__ __forceinline__ void bern_logit_lp_rep_mod(const double (&eta)[W], const bool (&y1v)[W], double (&out)[W],
+                                                      const double* __restrict__ expL) {
+  const double* __restrict__ K = c_tab_misc;
   const double* __restrict__ invL = expL + 64 * REP;
   const double* __restrict__ logL = expL + (64 + 129) * REP;
   double x[W], t[W], r[W], pl[W], d[W];

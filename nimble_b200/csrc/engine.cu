@@ -1694,12 +1694,22 @@ static int launch_eval_sum(nimb200_model* m, int mode, int di, int lo, int hi, c
     } else if (latent) {
       ensure_dyn_smem(k_bernlin_sum<true, false>, BF_SUM_SMEM, a10);
       k_bernlin_sum<true, false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+    } else if (getenv("NIMB200_BERN_GENERAL")) {   // the general kernel on a data declaration (comparison, tests)
+      if (gated) {
+        ensure_dyn_smem(k_bernlin_sum<false, true>, BF_SUM_SMEM, a01);
+        k_bernlin_sum<false, true><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+      } else {
+        ensure_dyn_smem(k_bernlin_sum<false, false>, BF_SUM_SMEM, a00);
+        k_bernlin_sum<false, false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+      }
     } else if (gated) {
-      ensure_dyn_smem(k_bernlin_sum<false, true>, BF_SUM_SMEM, a01);
-      k_bernlin_sum<false, true><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+      static std::atomic<unsigned long long> d1{0};
+      ensure_dyn_smem(k_bernlin_sum_data<true>, BF_SUM_SMEM, d1);
+      k_bernlin_sum_data<true><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
     } else {
-      ensure_dyn_smem(k_bernlin_sum<false, false>, BF_SUM_SMEM, a00);
-      k_bernlin_sum<false, false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
+      static std::atomic<unsigned long long> d0{0};
+      ensure_dyn_smem(k_bernlin_sum_data<false>, BF_SUM_SMEM, d0);
+      k_bernlin_sum_data<false><<<grid, BF_THREADS, BF_SUM_SMEM, m->stream>>>(m->T, ba, lo, hi, npc, m->d_partials);
     }
     m->launches++;
     CK(launch_pdl(k_reduce, dim3((C * 32 + 127) / 128), dim3(128), 0, m->stream, m->d_partials, chunks, 1, C, dst0, dst1));

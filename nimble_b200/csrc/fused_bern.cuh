@@ -169,6 +169,98 @@ k_bernlin_sum(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double*
   }
 }
 
+// The same block sum for a DATA declaration (values staged as codes), written for the issue slots: per evaluation the loop
+// holds one 16-byte node read, the gate's address and load (one trip ahead), four integer instructions of gate validation, the
+// moderate path's arithmetic and one select.  What the general kernel above checks per evaluation is established per tile
+// (values that are not 0 / 1: the whole tile goes through the scalar form) or per trip by the vote the moderate path needs anyway
+// (a predictor that is NaN, infinite or beyond 8 sends the trip through the scalar form, which also knows dbinom(v, 1, 0 * NaN)).
+template <bool GATED>
+__global__ void __launch_bounds__(BF_THREADS, 3)
+k_bernlin_sum_data(DevTab T, BernArgs a, int lo, int hi, int nodes_per_chunk, double* __restrict__ partials) {
+  extern __shared__ __align__(16) unsigned char bf_smem[];   // staged nodes | replicated tables (BL_REP_BYTES)
+  BernNode* sn = reinterpret_cast<BernNode*>(bf_smem);
+  double* rep = reinterpret_cast<double*>(bf_smem + sizeof(BernNode) * BF_TILE);
+  __shared__ double red[BF_THREADS / 32][32];
+  __shared__ __align__(16) MathTab tab;
+  load_mathtab(&tab, threadIdx.x, BF_THREADS);
+  load_bern_rep_tables(rep, threadIdx.x, BF_THREADS);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = BF_THREADS / 32;
+  const double* __restrict__ expL = rep + (lane & 15);
+  const int c = blockIdx.x * 32 + lane;
+  const bool live = c < T.C;
+  const int cc = live ? c : T.C - 1;
+  const size_t C = (size_t)T.C;
+  const double c0 = T.state[(size_t)a.c0_slot * C + cc], c1 = T.state[(size_t)a.c1_slot * C + cc];
+  const int c_lo = lo + blockIdx.y * nodes_per_chunk, c_hi = min(hi, c_lo + nodes_per_chunk);
+  const double* __restrict__ gatep = T.state + (size_t)(GATED ? a.gate_slot : 0) * C + cc;
+  double acc = 0.0;
+  for (int t0 = c_lo; t0 < c_hi; t0 += BF_TILE) {
+    __syncthreads();
+    int odd = 0;
+    for (int q = threadIdx.x; q < BF_TILE; q += BF_THREADS) {
+      const int i = t0 + q;
+      if (i < c_hi) {
+        BernNode nd;
+        nd.x = a.x[i];
+        const double v = a.vdata[i];
+        nd.code = v == 0.0 ? 0 : v == 1.0 ? 1 : 2;
+        nd.g = GATED ? bern_gate_index(a, i) : 0;
+        odd |= nd.code & 2;
+        sn[q] = nd;
+      }
+    }
+    const int tile_odd = __syncthreads_or(odd);   // a value that is neither 0 nor 1 somewhere in the tile
+    const int cnt = min(BF_TILE, c_hi - t0);
+    const int per = ((cnt + nw - 1) / nw + BF_W - 1) & ~(BF_W - 1);
+    const int k_lo = min(cnt, warp * per), k_hi = min(cnt, (warp + 1) * per);
+    const int k_full = tile_odd ? k_lo : k_lo + (max(0, k_hi - k_lo) & ~(BF_W - 1));
+    double gn[BF_W];   // the next trip's gates
+#pragma unroll
+    for (int j = 0; j < BF_W; j++) gn[j] = 1.0;
+    auto fetch = [&](int k) {
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) gn[j] = gatep[(size_t)sn[k + j].g * C];
+    };
+    if (GATED && k_lo < k_full) fetch(k_lo);
+    for (int k = k_lo; k < k_full; k += BF_W) {
+      double eta[BF_W], gt[BF_W], lp[BF_W];
+      bool y1[BF_W];
+      unsigned irr = 0;
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) {
+        const BernNode nd = sn[k + j];
+        eta[j] = fma(c1, nd.x, c0);
+        y1[j] = nd.code != 0;
+        gt[j] = gn[j];
+        if (GATED) irr |= not01_bits(gt[j]);
+      }
+      if (GATED && k + BF_W < k_full) fetch(k + BF_W);
+      if (!__all_sync(0xffffffffu, irr == 0 && bern_logit_moderate<BF_W>(eta))) {   // practically never: the scalar form sorts it out
+#pragma unroll
+        for (int j = 0; j < BF_W; j++) acc += bernlin_lp_cold(y1[j] ? 1.0 : 0.0, gt[j], eta[j], &tab);
+        continue;
+      }
+      bern_logit_lp_rep_mod<BF_W, 16>(eta, y1, lp, expL);
+#pragma unroll
+      for (int j = 0; j < BF_W; j++) {
+        if (GATED) acc += __double2hiint(gt[j]) != 0 ? lp[j] : (y1[j] ? -INFINITY : 0.0);   // gate 0: dbinom(v, 1, 0)
+        else acc += lp[j];
+      }
+    }
+    for (int k = k_full; k < k_hi; k++) {   // the end of a chunk, or a tile that holds an odd value
+      const BernNode nd = sn[k];
+      acc += bernlin_lp_cold(a.vdata[t0 + k], GATED ? gatep[(size_t)nd.g * C] : 1.0, fma(c1, nd.x, c0), &tab);
+    }
+  }
+  red[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && live) {
+    double s = 0.0;
+    for (int w = 0; w < nw; w++) s += red[w][lane];
+    partials[(size_t)blockIdx.y * T.C + c] = s;
+  }
+}
+
 // binary Gibbs sweep over latent 0/1 targets z[t] whose prior is  z[t] ~ dbern(ilogit(b0 + b1 xz[t]))  (pz) and whose dependents
 // are the data nodes of  y ~ dbern(z[G] * ilogit(a0 + a1 w))  (py) selected by the sampler's stage-1 entry.
 // With z = 0 a visit contributes 0 (y = 0) or -Inf (y = 1): only the z = 1 state needs the link, two visits at a time.
