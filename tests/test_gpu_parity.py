@@ -487,6 +487,54 @@ def test_bern_family_block_sums_and_edges(oracle, b200):
         assert rel_err(a, b).max() < RTOL_LP, (di, rel_err(a, b).max())
 
 
+def test_bern_data_kernel_agrees_with_the_general_kernel(oracle, b200, monkeypatch):
+    """The data-declaration block-sum kernel (value checks per tile, predictor checks by the moderate path's vote) against the
+    general kernel and the oracle, with odd gates and wild predictors -- and once more on data that hold a value that is neither
+    0 nor 1 (its tile goes through the scalar form; every chain's sum is then -Inf, as dbinom(0.5, 1, p) is)."""
+    from nimble_b200.configs import OCCUPANCY_CODE
+    for odd in (False, True):
+        rng = np.random.default_rng(5)
+        S, J = 700, 4
+        x, w = rng.standard_normal(S), rng.standard_normal((S, J))
+        y = (rng.random((S, J)) < 0.4).astype(np.float64)
+        if odd:
+            y[123, 2] = 0.5
+        m = nb.nimbleModel(OCCUPANCY_CODE, constants={"S": S, "J": J, "x": x, "w": w}, data={"y": y},
+                           inits={"b0": 0.0, "b1": 0.0, "a0": 0.0, "a1": 0.0, "z": np.ones(S)}, name="occ_odd")
+        conf = nb.configureMCMC(m, monitors=["a0"])
+        C = 40
+        inits = sm.random_inits(m, C, 4, 0.3)
+        z0 = m.var_slot["z"]
+        inits[:, z0:z0 + S] = np.maximum((rng.random((C, S)) < 0.6).astype(float), y.max(axis=1) >= 1.0)   # z = 1 where detected
+        inits[3, z0 + 5] = 0.5
+        inits[4, m.var_slot["a0"]] = 60.0
+        inits[5, m.var_slot["a0"]] = -800.0
+        inits[6, m.var_slot["a1"]] = np.nan
+        inits[7, m.var_slot["a0"]] = np.inf
+        inits[8, z0 + 9] = 0.0                                                # may contradict a detection: -Inf for that chain
+        co = compile_on(oracle, conf)
+        do = co._ensure(C)
+        do.set_values(inits)
+        yd = len(co.builder.decls) - 1
+        assert co.builder.decls[yd].family == T.FAM_BERN_LOGIT_LIN and co.builder.decls[yd].value_kind == 0
+        want = do.calculate(yd)
+        if not odd:
+            assert np.isfinite(want).sum() > C // 2
+        got = {}
+        for label, env in (("data", None), ("general", "1")):
+            if env:
+                monkeypatch.setenv("NIMB200_BERN_GENERAL", env)
+            else:
+                monkeypatch.delenv("NIMB200_BERN_GENERAL", raising=False)
+            dg = compile_on(b200, conf)._ensure(C)
+            dg.set_values(inits)
+            got[label] = dg.calculate(yd)
+            assert np.array_equal(np.isnan(got[label]), np.isnan(want)), (odd, label)
+            assert np.array_equal(np.isinf(got[label]), np.isinf(want)), (odd, label)
+            assert rel_err(got[label], want).max() < RTOL_LP, (odd, label, rel_err(got[label], want).max())
+        assert rel_err(got["data"], got["general"]).max() < 1e-13
+
+
 def test_bern_family_trajectories(oracle, b200):
     m, conf = sm.SMALL["occupancy"]()
     inits = sm.random_inits(m, 40, 8, 0.1)
