@@ -985,39 +985,59 @@ __global__ void k_block_propose(DevTab T, int sid, uint64_t seed, uint64_t iter,
 }
 
 // wide MH accept/reject + commit.  newsum[e][C] / oldsum = depcache rows of this sampler's dependency entries.
-__global__ void k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
-                            double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls,
-                            int* __restrict__ accept_out) {
+// Block = 32 chains (x) by MHF_J lanes (y): lane 0 of a chain takes the decision, then the chain's lanes share the per-element
+// work of a block sampler -- putting the old values back after a rejection and recording the iteration for the covariance
+// adaptation (one thread per chain walked 2 x 50 dependent loads and stores: 29 us per step at any chain count).
+static const int MHF_J = 16;
+__global__ void __launch_bounds__(32 * MHF_J)
+k_mh_finish(DevTab T, int sid, uint64_t seed, uint64_t iter, int call, SamplerDev S, const double* newsum,
+            double* depcache, const int32_t* __restrict__ dep_slot, const double* tsave, const double* pls,
+            int* __restrict__ accept_out) {
   cudaTriggerProgrammaticLaunchCompletion();
   cudaGridDependencySynchronize();
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= T.C) return;
+  __shared__ int s_jump[32], s_ran[32];
+  const int cx = threadIdx.x, jy = threadIdx.y;
+  const int c = blockIdx.x * 32 + cx;
+  const bool live = c < T.C;
   const nimb200_sampler sp = T.samplers[sid];
-  DrawKey key = make_key(T, seed, iter, sid, 0, c);
-  double lp0 = 0, lp1 = 0;
-  for (int e = 0; e < sp.n_dep; e++) {
-    double diff = newsum[(size_t)e * T.C + c] - depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c];
-    if (T.deps[sp.dep_off + e].stage == 0) lp0 += diff; else lp1 += diff;
+  const int d = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1;
+  if (jy == 0 && live) {
+    DrawKey key = make_key(T, seed, iter, sid, 0, c);
+    double lp0 = 0, lp1 = 0;
+    for (int e = 0; e < sp.n_dep; e++) {
+      double diff = newsum[(size_t)e * T.C + c] - depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c];
+      if (T.deps[sp.dep_off + e].stage == 0) lp0 += diff; else lp1 += diff;
+    }
+    bool jump;
+    if (lp0 == -INFINITY) jump = false;
+    else jump = decide(lp0 + lp1 + (pls ? pls[c] : 0.0), key, call);
+    if (accept_out) accept_out[c] = jump ? 1 : 0;
+    if (jump)
+      for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c] = newsum[(size_t)e * T.C + c];
+    int ran = 0;
+    if (sp.adaptive) {
+      if (sp.type == NIMB_SAMPLER_RW) rw_adapt(sp, S, c, jump, T.C);
+      else {  // RW_block adaptiveProcedure, first half (MCMC_samplers.R:716-722); the covariance step is k_block_adapt
+        ran = S.timesRan[c] + 1;
+        S.timesRan[c] = ran;
+        if (jump) S.timesAccepted[c] += 1;
+      }
+    }
+    s_jump[cx] = jump ? 1 : 0;
+    s_ran[cx] = ran;
   }
-  bool jump;
-  if (lp0 == -INFINITY) jump = false;
-  else jump = decide(lp0 + lp1 + (pls ? pls[c] : 0.0), key, call);
-  int d = sp.type == NIMB_SAMPLER_RW_BLOCK ? sp.d : 1;
-  if (accept_out) accept_out[c] = jump ? 1 : 0;
-  if (jump) {
-    for (int e = 0; e < sp.n_dep; e++) depcache[(size_t)dep_slot[sp.dep_off + e] * T.C + c] = newsum[(size_t)e * T.C + c];
-  } else {
-    for (int j = 0; j < d; j++) T.state[(size_t)(sp.target_slot + j) * T.C + c] = tsave[(size_t)j * T.C + c];
+  __syncthreads();
+  if (!live) return;
+  const bool jump = s_jump[cx] != 0;
+  const bool record = sp.adaptive && sp.type == NIMB_SAMPLER_RW_BLOCK && !sp.adapt_scale_only;
+  const int ran = s_ran[cx];
+  for (int j = jy; j < d; j += MHF_J) {
+    double* sv = T.state + (size_t)(sp.target_slot + j) * T.C + c;
+    double v;
+    if (jump) v = *sv;                                  // the proposal stays
+    else { v = tsave[(size_t)j * T.C + c]; *sv = v; }   // the old value comes back
+    if (record) S.empirSamp[((size_t)(ran - 1) + (size_t)j * sp.adapt_interval) * T.C + c] = v;
   }
-  if (!sp.adaptive) return;
-  if (sp.type == NIMB_SAMPLER_RW) { rw_adapt(sp, S, c, jump, T.C); return; }
-  // RW_block adaptiveProcedure, first half (MCMC_samplers.R:716-722); the covariance step is k_block_adapt
-  int ran = S.timesRan[c] + 1;
-  S.timesRan[c] = ran;
-  if (jump) S.timesAccepted[c] += 1;
-  if (!sp.adapt_scale_only)
-    for (int j = 0; j < d; j++)
-      S.empirSamp[((size_t)(ran - 1) + (size_t)j * sp.adapt_interval) * T.C + c] = T.state[(size_t)(sp.target_slot + j) * T.C + c];
 }
 
 // RW_block adaptation every adaptInterval iterations: one block per chain (MCMC_samplers.R:723-756,
@@ -2912,7 +2932,7 @@ static int run_sampler(nimb200_model* m, int s, uint64_t seed, uint64_t iter) {
         if (launch_eval_sum(m, 0, dp.decl, hs.lo, hs.hi, hs.idx, m->d_newsum + (size_t)e * C, nullptr, nullptr, -1, 0)) return 1;
       }
       int call = sp.type == NIMB_SAMPLER_RW ? 1 : tr * (npair + 1) + npair;
-      CK(launch_pdl(k_mh_finish, dim3((C + TB - 1) / TB), dim3(TB), 0, m->stream, m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
+      CK(launch_pdl(k_mh_finish, dim3((C + 31) / 32), dim3(32, MHF_J), 0, m->stream, m->T, s, seed, iter, call, m->sdev[s], m->d_newsum, m->d_depcache, m->d_dep_slot,
                                                            m->d_tsave, sp.type == NIMB_SAMPLER_RW ? m->d_pls : nullptr, m->d_accept));
       m->launches++;
       m->prop_lo = m->prop_hi = -1;
