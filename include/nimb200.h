@@ -371,7 +371,7 @@ int nimb200_mcmc_sampler_times(nimb200_model *m, double *out_ms, int32_t n);
 /* online conditional WAIC without grouping (P/R/MCMC_WAIC.R:209-282; call site MCMC_build.R:304-310): once enabled, every
  * post-burn-in iteration of every chain updates, per data node, a running log-sum-exp of its log-density (lppd) and a Welford
  * variance (pWAIC).  nimb200_mcmc_run(reset = 1) clears the statistics.  waic_get: out[0] = WAIC = -2 (lppd - pWAIC),
- * out[1] = lppd, out[2] = pWAIC, out[3] = number of (iteration, chain) samples used.  Data-sharded models are not supported. */
+ * out[1] = lppd, out[2] = pWAIC, out[3] = number of (iteration, chain) samples used.  Data-sharded models: nimb200_waic_partial below. */
 int nimb200_waic_enable(nimb200_model *m, int32_t enable);
 int nimb200_waic_get(nimb200_model *m, double *out4);
 /* data-sharded models: every rank accumulates the statistics of its own slice of the data nodes; out4 = {sum over those nodes

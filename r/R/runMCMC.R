@@ -25,15 +25,32 @@ runMCMC <- function(mcmc, niter = 10000, nburnin = 0, thin, thin2, nchains = 1, 
   }
   ptr <- .Call("CALL_nimb200_build", tab, as.integer(nchains), as.integer(first_chain), as.integer(device))
   on.exit(.Call("CALL_nimb200_clear", ptr), add = TRUE)
+  if (WAIC) .Call("CALL_nimb200_waic_enable", ptr, TRUE)                      # online accumulation on the device (MCMC_WAIC.R:246-268)
   .Call("CALL_nimb200_run", ptr, init, tab$decl_order, as.numeric(niter), as.numeric(nburnin), as.integer(thin), TRUE, as.numeric(seed))
   s <- aperm(.Call("CALL_nimb200_samples", ptr, length(tab$monitor_slots), as.integer(nchains)), c(2, 1, 3))
   mats <- lapply(seq_len(nchains), function(k) { m <- matrix(s[, , k], nrow = dim(s)[1]); colnames(m) <- tab$colnames; m })
   if (samplesAsCodaMCMC) mats <- lapply(mats, coda::as.mcmc)
   out <- if (nchains == 1) mats[[1]] else setNames(mats, paste0("chain", seq_len(nchains)))                                 # MCMC_run.R:183-189
-  if (!summary) return(out)
-  list(samples = out, summary = if (nchains == 1) nimble::samplesSummary(mats[[1]]) else
-         c(setNames(lapply(mats, nimble::samplesSummary), paste0("chain", seq_len(nchains))),
-           list(all.chains = nimble::samplesSummary(do.call(rbind, mats)))))
+  waic <- NULL
+  if (WAIC) {                                                                 # c(WAIC, lppd, pWAIC, n) over all chains pooled
+    w <- .Call("CALL_nimb200_waic_get", ptr)
+    waic <- list(WAIC = w[1], lppd = w[2], pWAIC = w[3])
+  }
+  if (!summary && !WAIC) return(out)
+  res <- list(samples = out)
+  if (summary) {
+    ## samplesSummary on the device (five numbers per column cross the bus): per chain, and all chains pooled (MCMC_run.R:196-207)
+    dev_summary <- function(lo, hi) {
+      m <- t(.Call("CALL_nimb200_samples_summary", ptr, as.integer(lo), as.integer(hi), length(tab$monitor_slots)))
+      dimnames(m) <- list(tab$colnames, c("Mean", "Median", "St.Dev.", "95%CI_low", "95%CI_upp"))
+      m
+    }
+    res$summary <- if (nchains == 1) dev_summary(0L, 1L) else
+      c(setNames(lapply(seq_len(nchains), function(k) dev_summary(k - 1L, k)), paste0("chain", seq_len(nchains))),
+        list(all.chains = dev_summary(0L, nchains)))
+  }
+  if (WAIC) res$WAIC <- waic
+  res
 }
 
 ## Compatibility route (SURVEY 8b-A): an object with the duck type the UNMODIFIED runMCMC loop touches -- $run(niter, nburnin =,
@@ -54,6 +71,14 @@ b200_mcmc <- function(mcmc, device = 0L) {
     invisible(NULL)
   }
   self$getTimes <- function() .Call("CALL_nimb200_times", self$ptr, ncol(tab$samplers_i))
+  ## nimbleOptions(MCMCsaveHistory = TRUE): call enableHistory() before run(); sampler is the 1-based index in conf$samplerConfs
+  self$enableHistory <- function(max_adaptations = 1000L) .Call("CALL_nimb200_history_enable", self$ptr, as.integer(max_adaptations))
+  self$getScaleHistory <- function(sampler) .Call("CALL_nimb200_history", self$ptr, as.integer(sampler - 1L), 0L, 1)
+  self$getAcceptanceHistory <- function(sampler) .Call("CALL_nimb200_history", self$ptr, as.integer(sampler - 1L), 1L, 1)
+  self$getPropCovHistory <- function(sampler, d) {
+    h <- .Call("CALL_nimb200_history", self$ptr, as.integer(sampler - 1L), 2L, d * d)
+    aperm(array(h, c(d, d, length(h) / (d * d))), c(3, 2, 1))                 # [adaptation, d, d], as MCMC_samplers.R:772-780 returns it
+  }
   class(self) <- "b200_mcmc"
   self
 }

@@ -188,6 +188,51 @@ SEXP CALL_nimb200_calculate(SEXP ptr, SEXP decl, SEXP n_nodes, SEXP nchains) {
   return out;
 }
 
+/* online WAIC: configureMCMC(enableWAIC = TRUE) / mcmc$getWAIC() (MCMC_WAIC.R:209-300) */
+SEXP CALL_nimb200_waic_enable(SEXP ptr, SEXP enable) {
+  if (nimb200_waic_enable(model_of(ptr), asLogical(enable))) Rf_error("%s", nimb200_last_error());
+  return R_NilValue;
+}
+SEXP CALL_nimb200_waic_get(SEXP ptr) {   /* c(WAIC, lppd, pWAIC, n) */
+  SEXP out = PROTECT(allocVector(REALSXP, 4));
+  if (nimb200_waic_get(model_of(ptr), REAL(out))) { UNPROTECT(1); Rf_error("%s", nimb200_last_error()); }
+  UNPROTECT(1);
+  return out;
+}
+
+/* samplesSummary (MCMC_utils.R:315-341) computed on the device over chains [chain_lo, chain_hi): 5 x n_monitors matrix
+ * (Mean, Median, St.Dev., 95%CI_low, 95%CI_upp), column-major as R stores it */
+SEXP CALL_nimb200_samples_summary(SEXP ptr, SEXP chain_lo, SEXP chain_hi, SEXP nmon) {
+  int n = asInteger(nmon);
+  SEXP buf = PROTECT(allocVector(REALSXP, (R_xlen_t)5 * n));      /* the library writes [5][nmon], row-major */
+  if (nimb200_samples_summary(model_of(ptr), asInteger(chain_lo), asInteger(chain_hi), REAL(buf))) { UNPROTECT(1); Rf_error("%s", nimb200_last_error()); }
+  SEXP out = PROTECT(allocMatrix(REALSXP, 5, n));
+  for (int i = 0; i < 5; i++)
+    for (int j = 0; j < n; j++) REAL(out)[i + 5 * (R_xlen_t)j] = REAL(buf)[(R_xlen_t)i * n + j];
+  UNPROTECT(2);
+  return out;
+}
+
+/* nimbleOptions(MCMCsaveHistory = TRUE): getScaleHistory / getAcceptanceHistory / getPropCovHistory (MCMC_samplers.R:394-448,
+ * 726-780).  what = 0, 1, 2; per_adaptation = doubles per recorded adaptation (chains, or d*d*chains for propCov) */
+SEXP CALL_nimb200_history_enable(SEXP ptr, SEXP max_adaptations) {
+  if (nimb200_sampler_history_enable(model_of(ptr), asInteger(max_adaptations))) Rf_error("%s", nimb200_last_error());
+  return R_NilValue;
+}
+SEXP CALL_nimb200_history(SEXP ptr, SEXP sampler, SEXP what, SEXP per_adaptation) {
+  nimb200_model *m = model_of(ptr);
+  int32_t n_adapt = 0;
+  if (nimb200_sampler_history(m, asInteger(sampler), asInteger(what), NULL, 0, &n_adapt)) Rf_error("%s", nimb200_last_error());
+  R_xlen_t n = (R_xlen_t)n_adapt * (R_xlen_t)asReal(per_adaptation);
+  SEXP out = PROTECT(allocVector(REALSXP, n));
+  if (n > 0 && nimb200_sampler_history(m, asInteger(sampler), asInteger(what), REAL(out), (int64_t)n, &n_adapt)) {
+    UNPROTECT(1);
+    Rf_error("%s", nimb200_last_error());
+  }
+  UNPROTECT(1);
+  return out;
+}
+
 /* explicit release (the finalizer does the same at garbage collection) */
 SEXP CALL_nimb200_clear(SEXP ptr) {
   model_finalizer(ptr);
@@ -205,6 +250,11 @@ static const R_CallMethodDef call_methods[] = {
   {"CALL_nimb200_set_timing", (DL_FUNC)&CALL_nimb200_set_timing, 2},
   {"CALL_nimb200_times", (DL_FUNC)&CALL_nimb200_times, 2},
   {"CALL_nimb200_calculate", (DL_FUNC)&CALL_nimb200_calculate, 4},
+  {"CALL_nimb200_waic_enable", (DL_FUNC)&CALL_nimb200_waic_enable, 2},
+  {"CALL_nimb200_waic_get", (DL_FUNC)&CALL_nimb200_waic_get, 1},
+  {"CALL_nimb200_samples_summary", (DL_FUNC)&CALL_nimb200_samples_summary, 4},
+  {"CALL_nimb200_history_enable", (DL_FUNC)&CALL_nimb200_history_enable, 2},
+  {"CALL_nimb200_history", (DL_FUNC)&CALL_nimb200_history, 4},
   {"CALL_nimb200_clear", (DL_FUNC)&CALL_nimb200_clear, 1},
   {NULL, NULL, 0}};
 void R_init_nimb200_R(DllInfo *dll) {
